@@ -1,0 +1,469 @@
+/*
+ * b200lab.h -- C ABI of libb200lab.so: the B200-native (sm_100a) non-physics step of Isaac Lab
+ * (ManagerBasedRLEnv.step MDP pipeline, actuator models, contact/ray-cast sensors) and the
+ * rsl_rl PPO hot path (GAE, minibatch gather, actor-critic MLP fwd/bwd, loss, Adam).
+ *
+ * The reference (godk1122/IsaacLab, Isaac Lab 2.1.0 + rsl_rl 3.0.0) is 100 % Python and has no FFI for
+ * this path, so every entry point below names the reference Python symbol it replaces
+ * (path:line relative to the reference root; LAB = source/isaaclab/isaaclab, RSL = source/rsl_rl/rsl_rl,
+ * TASKS = source/isaaclab_tasks/isaaclab_tasks).  INTEGRATION.md shows the ctypes binding a maintainer
+ * of the reference would add.
+ *
+ * Conventions (all entry points):
+ *   - plain C types only; every pointer inside an *Args struct is a DEVICE pointer unless the field
+ *     name starts with `h_` (host pointer);
+ *   - tensors are contiguous, env-major, fp32 unless stated (i64 = int64_t, u8 = uint8_t/bool);
+ *   - quaternions are (w, x, y, z) as in ArticulationData (LAB/assets/articulation/articulation_data.py:366);
+ *   - work is enqueued on `stream` (a cudaStream_t passed as void*) and the call returns without
+ *     synchronising; nothing is allocated on the hot path;
+ *   - return value 0 = ok, negative = error; b200lab_last_error() returns a static message;
+ *   - not thread-safe per device.  No CPU fallback exists: without a CUDA device every compute
+ *     entry point returns B200LAB_ERR_CUDA.
+ */
+#ifndef B200LAB_H_
+#define B200LAB_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200LAB_VERSION 100
+
+#define B200LAB_OK 0
+#define B200LAB_ERR_ARG (-1)
+#define B200LAB_ERR_CUDA (-2)
+#define B200LAB_ERR_UNSUPPORTED (-3)
+
+#define B200LAB_MAX_TERMS 32
+#define B200LAB_MAX_ACT_GROUPS 8
+#define B200LAB_MAX_INTERVAL_EVENTS 4
+
+const char* b200lab_last_error(void);
+int b200lab_version(void);
+/* number of kernels this library has launched since load (bench.py's `gpu_launches`) */
+int64_t b200lab_launch_count(void);
+/* sizeof() of the named *Args struct as compiled (binding self-check); -1 if unknown */
+int64_t b200lab_sizeof(const char* name);
+
+/* ------------------------------------------------------------------------------------------------
+ * Term programs: the compiled form of the manager term cfgs (`func(env, **params) -> Tensor`,
+ * LAB/managers/manager_term_cfg.py:28-344).  Host-side Python maps recognised `func` identities to
+ * the opcodes below; unknown user functions are evaluated in Python and enter as *_EXTERNAL columns.
+ * ---------------------------------------------------------------------------------------------- */
+enum B200LabRewardOp {
+  B200LAB_REW_IS_ALIVE = 1,                    /* LAB/envs/mdp/rewards.py:31 */
+  B200LAB_REW_IS_TERMINATED = 2,               /* rewards.py:36 */
+  B200LAB_REW_LIN_VEL_Z_L2 = 3,                /* rewards.py:76 */
+  B200LAB_REW_ANG_VEL_XY_L2 = 4,               /* rewards.py:83 */
+  B200LAB_REW_FLAT_ORIENTATION_L2 = 5,         /* rewards.py:90 */
+  B200LAB_REW_JOINT_TORQUES_L2 = 6,            /* rewards.py:136 */
+  B200LAB_REW_JOINT_VEL_L1 = 7,                /* rewards.py:146 */
+  B200LAB_REW_JOINT_VEL_L2 = 8,                /* rewards.py:153 */
+  B200LAB_REW_JOINT_ACC_L2 = 9,                /* rewards.py:163 */
+  B200LAB_REW_JOINT_DEVIATION_L1 = 10,         /* rewards.py:173 */
+  B200LAB_REW_JOINT_POS_LIMITS = 11,           /* rewards.py:182 */
+  B200LAB_REW_ACTION_RATE_L2 = 12,             /* rewards.py:245 */
+  B200LAB_REW_ACTION_L2 = 13,                  /* rewards.py:250 */
+  B200LAB_REW_UNDESIRED_CONTACTS = 14,         /* rewards.py:260  p[0]=threshold, body_mask */
+  B200LAB_REW_CONTACT_FORCES = 15,             /* rewards.py:271  p[0]=threshold, body_mask */
+  B200LAB_REW_TRACK_LIN_VEL_XY_EXP = 16,       /* rewards.py:287  p[0]=std**2 (fp32) */
+  B200LAB_REW_TRACK_ANG_VEL_Z_EXP = 17,        /* rewards.py:301  p[0]=std**2 */
+  B200LAB_REW_FEET_AIR_TIME = 18,              /* TASKS/manager_based/locomotion/velocity/mdp/rewards.py:25  p[0]=threshold, p[1]=step_dt+1e-8 */
+  B200LAB_REW_FEET_AIR_TIME_POSITIVE_BIPED = 19, /* same file :47  p[0]=threshold */
+  B200LAB_REW_FEET_SLIDE = 20,                 /* same file :69  body_mask=contact bodies, body_mask2 in i64[0] = asset bodies */
+  B200LAB_REW_TRACK_LIN_VEL_XY_YAW_FRAME_EXP = 21, /* same file :86 p[0]=std**2 */
+  B200LAB_REW_TRACK_ANG_VEL_Z_WORLD_EXP = 22,  /* same file :99 p[0]=std**2 */
+  B200LAB_REW_JOINT_POS_TARGET_L2 = 23,        /* TASKS/manager_based/classic/cartpole/mdp/rewards.py:19 p[0]=target */
+  B200LAB_REW_EXTERNAL = 100                   /* value read from ext_values[col=i0][N] (user Python term) */
+};
+
+enum B200LabTerminationOp {
+  B200LAB_TERM_TIME_OUT = 1,                   /* LAB/envs/mdp/terminations.py:30 */
+  B200LAB_TERM_ILLEGAL_CONTACT = 2,            /* terminations.py:150  p[0]=threshold, body_mask */
+  B200LAB_TERM_JOINT_POS_OUT_OF_MANUAL_LIMIT = 3, /* terminations.py:90  p[0]=lo p[1]=hi, joint_mask */
+  B200LAB_TERM_ROOT_HEIGHT_BELOW_MINIMUM = 4,  /* terminations.py:74  p[0]=minimum_height */
+  B200LAB_TERM_BAD_ORIENTATION = 5,            /* terminations.py:60  p[0]=limit_angle */
+  B200LAB_TERM_EXTERNAL = 100
+};
+
+enum B200LabObsOp {
+  B200LAB_OBS_BASE_LIN_VEL = 1,                /* LAB/envs/mdp/observations.py:40 */
+  B200LAB_OBS_BASE_ANG_VEL = 2,                /* observations.py:47 */
+  B200LAB_OBS_PROJECTED_GRAVITY = 3,           /* observations.py:54 */
+  B200LAB_OBS_GENERATED_COMMANDS = 4,          /* observations.py:529 */
+  B200LAB_OBS_JOINT_POS_REL = 5,               /* observations.py:114 */
+  B200LAB_OBS_JOINT_VEL_REL = 6,               /* observations.py:150 */
+  B200LAB_OBS_JOINT_POS = 7,                   /* observations.py:104 */
+  B200LAB_OBS_JOINT_VEL = 8,                   /* observations.py:140 */
+  B200LAB_OBS_LAST_ACTION = 9,                 /* observations.py:512 */
+  B200LAB_OBS_HEIGHT_SCAN = 10,                /* observations.py:165  p[0]=offset */
+  B200LAB_OBS_BASE_POS_Z = 11,                 /* observations.py:33 */
+  B200LAB_OBS_EXTERNAL = 100
+};
+
+enum B200LabNoiseKind {                        /* LAB/utils/noise/noise_model.py:20-98 */
+  B200LAB_NOISE_NONE = 0,
+  B200LAB_NOISE_UNIFORM_ADD = 1,               /* x + u*(hi-lo) + lo */
+  B200LAB_NOISE_UNIFORM_SCALE = 2,
+  B200LAB_NOISE_UNIFORM_ABS = 3,
+  B200LAB_NOISE_CONSTANT_ADD = 4               /* x + bias (n_lo) */
+};
+
+typedef struct B200LabTerm {
+  int32_t op;
+  int32_t time_out;          /* termination terms: 1 -> ORed into truncated, else terminated */
+  float weight;              /* reward terms */
+  float p[5];
+  uint64_t joint_mask;       /* bit j set -> joint j selected (SceneEntityCfg.joint_ids) */
+  uint64_t body_mask;        /* bit b set -> body b selected (SceneEntityCfg.body_ids) */
+  uint64_t body_mask2;
+  int32_t i0;                /* EXTERNAL: column */
+  int32_t dim;               /* obs terms: number of columns */
+  int32_t noise_kind;
+  int32_t clip_on;
+  float noise_lo, noise_span; /* n_min and fp32(n_max - n_min) */
+  float clip_lo, clip_hi;
+  float scale;               /* obs terms; 1.0 when cfg.scale is None */
+  int32_t scale_on;
+} B200LabTerm;
+
+enum B200LabActuatorKind {
+  B200LAB_ACT_IMPLICIT = 1,   /* LAB/actuators/actuator_pd.py:115-140 */
+  B200LAB_ACT_IDEAL_PD = 2,   /* actuator_pd.py:184-198 */
+  B200LAB_ACT_DC_MOTOR = 3,   /* actuator_pd.py:264-286 */
+  B200LAB_ACT_NET_LSTM = 4,   /* LAB/actuators/actuator_net.py:76-99 */
+  B200LAB_ACT_NET_MLP = 5     /* actuator_net.py:147-189 */
+};
+
+/* One actuator group (Articulation.actuators[name], LAB/assets/articulation/articulation.py:1432-1469).
+ * Per-joint parameter arrays have length J (articulation joint order); only joints in joint_mask are touched. */
+typedef struct B200LabActuatorGroup {
+  int32_t kind;
+  int32_t _pad;
+  uint64_t joint_mask;
+  const float* stiffness;      /* [J] */
+  const float* damping;        /* [J] */
+  const float* effort_limit;   /* [J] */
+  const float* velocity_limit; /* [J] */
+  float saturation_effort;     /* DCMotor; inf if None */
+  /* ActuatorNetLSTM: weights packed per layer l: W_ih[4H,in_l] W_hh[4H,H] b_ih[4H] b_hh[4H]; then head W[H] b[1].
+   * State h,c: [L, N*Jg, H] with row = env*Jg + local joint index (reference layout, actuator_net.py:56-64). */
+  int32_t lstm_layers, lstm_hidden;
+  const float* net_weights;
+  float* lstm_h;
+  float* lstm_c;
+  /* ActuatorNetMLP: layers n_layers; dims[0..n_layers]; weights packed W0[d1,d0] b0[d1] W1 ... ;
+   * activation 0=softsign 1=elu 2=relu 3=tanh.  History [N,Hist,Jg] x2 (reference layout, actuator_net.py:134-140). */
+  int32_t mlp_layers;
+  int32_t mlp_dims[6];
+  int32_t mlp_act;
+  int32_t mlp_hist;            /* history_length = max(input_idx)+1 */
+  int32_t mlp_num_idx;
+  int32_t mlp_input_idx[4];
+  int32_t mlp_vel_pos_order;   /* 0 = "pos_vel", 1 = "vel_pos" */
+  float mlp_pos_scale, mlp_vel_scale, mlp_torque_scale;
+  float* mlp_pos_hist;
+  float* mlp_vel_hist;
+  int32_t group_joints;        /* Jg */
+  int32_t _pad2;
+} B200LabActuatorGroup;
+
+/* ------------------------------------------------------------------------------------------------
+ * Environment state: raw views of the tensors the reference keeps in ArticulationData,
+ * ContactSensorData, RayCasterData and the managers.  Owned by the caller (torch tensors).
+ * ---------------------------------------------------------------------------------------------- */
+/* Views of the simulator's state tensors for the current physics step (PhysX tensor views in the reference:
+ * root_physx_view.get_root_transforms/velocities, get_dof_positions/velocities, contact_physx_view
+ * .get_net_contact_forces).  Passed per call so a recorded slab can be replayed without copies.
+ * root_state_w / joint_pos / joint_vel are in/out: reset events write the sampled reset state into them
+ * (the reference writes it to PhysX, LAB/assets/articulation/articulation.py:317-556). */
+typedef struct B200LabSimView {
+  float* root_state_w;         /* [N,13] pos, quat wxyz, lin vel, ang vel */
+  float* joint_pos;            /* [N,J] */
+  float* joint_vel;            /* [N,J] */
+  const float* net_forces_w;   /* [N,B,3] net contact forces of the current physics step (or NULL) */
+  const float* body_lin_vel_w; /* [N,B,3] or NULL */
+} B200LabSimView;
+
+typedef struct B200LabEnvState {
+  int32_t N, J, A, B, R;       /* envs, joints, action dim, bodies, rays */
+  int32_t hist;                /* contact history length (>=1) */
+  /* --- articulation constants --- */
+  const float* default_root_state; /* [13] (identical for all envs, articulation.py:1279) */
+  const float* default_joint_pos;  /* [J] */
+  const float* default_joint_vel;  /* [J] */
+  const float* soft_joint_pos_limits; /* [J,2] */
+  float* soft_joint_vel_limits;    /* [J] (written by the actuator pass, articulation.py:1466) */
+  /* --- articulation buffers --- */
+  float* joint_pos_target;     /* [N,J] */
+  float* joint_vel_target;     /* [N,J] */
+  float* joint_effort_target;  /* [N,J] */
+  float* computed_torque;      /* [N,J] */
+  float* applied_torque;       /* [N,J] */
+  float* joint_pos_target_sim; /* [N,J] implicit actuators: pos target handed to the simulator */
+  float* joint_effort_target_sim; /* [N,J] explicit actuators: effort handed to the simulator */
+  float* prev_joint_vel;       /* [N,J] */
+  float* joint_acc;            /* [N,J] */
+  /* --- action manager (LAB/managers/action_manager.py:318-339) --- */
+  float* action;               /* [N,A] */
+  float* prev_action;          /* [N,A] */
+  float* raw_actions;          /* [N,A] term raw actions (joint_actions.py:131) */
+  float* processed_actions;    /* [N,A] */
+  const float* action_scale;   /* [A] */
+  const float* action_offset;  /* [A] */
+  const float* action_clip;    /* [A,2] or NULL */
+  const int32_t* action_joint_ids; /* [A] joint index each action column drives */
+  int32_t action_kind;         /* 0 = joint position target, 1 = joint effort target */
+  int32_t num_act_groups;
+  int8_t joint_action_col[64]; /* joint -> action column driving it, -1 if none */
+  int8_t joint_group[64];      /* joint -> actuator group index, -1 if un-actuated */
+  int8_t joint_local[64];      /* joint -> index of the joint inside its group (row of the net state) */
+  B200LabActuatorGroup act[B200LAB_MAX_ACT_GROUPS];
+  /* --- contact sensor (LAB/sensors/contact_sensor/contact_sensor.py:320-379) --- */
+  float* cs_net_forces_w;      /* [N,B,3] */
+  float* cs_forces_hist;       /* [N,hist,B,3] */
+  float* cs_last_air_time;     /* [N,B] */
+  float* cs_current_air_time;  /* [N,B] */
+  float* cs_last_contact_time; /* [N,B] */
+  float* cs_current_contact_time; /* [N,B] */
+  float* cs_timestamp;         /* [N] */
+  float* cs_timestamp_last_update; /* [N] */
+  uint8_t* cs_is_outdated;     /* [N] */
+  float cs_force_threshold;
+  float cs_update_period;
+  /* --- ray caster (LAB/sensors/ray_caster/ray_caster.py:220-260) --- */
+  float* rc_timestamp;         /* [N] */
+  float* rc_timestamp_last_update; /* [N] */
+  uint8_t* rc_is_outdated;     /* [N] */
+  float* rc_drift;             /* [N,3] */
+  float* rc_pos_w;             /* [N,3] */
+  float* rc_quat_w;            /* [N,4] */
+  float* rc_ray_hits_w;        /* [N,R,3] */
+  const float* rc_ray_starts;  /* [R,3] local pattern incl. offset (identical per env) */
+  const float* rc_ray_dirs;    /* [R,3] */
+  float rc_update_period;
+  float rc_max_distance;
+  int32_t rc_attach_yaw_only;
+  float rc_drift_lo, rc_drift_hi;
+  const void* rc_mesh;         /* device-side mesh accel handle from b200lab_mesh_create (or NULL) */
+  /* --- env counters --- */
+  int64_t* episode_length_buf; /* [N] */
+  int64_t max_episode_length;
+  float step_dt;
+  float physics_dt;
+  float max_episode_length_s;
+  /* --- terminations (LAB/managers/termination_manager.py:151-174) --- */
+  int32_t num_term;
+  B200LabTerm term[B200LAB_MAX_TERMS];
+  uint8_t* term_dones;         /* [num_term, N] */
+  uint8_t* terminated;         /* [N] */
+  uint8_t* truncated;          /* [N] */
+  uint8_t* reset_buf;          /* [N] */
+  /* --- rewards (LAB/managers/reward_manager.py:128-157) --- */
+  int32_t num_rew;
+  B200LabTerm rew[B200LAB_MAX_TERMS];
+  float* reward_buf;           /* [N] */
+  float* episode_sums;         /* [num_rew, N] */
+  float* step_reward;          /* [N, num_rew] */
+  const float* ext_values;     /* [n_ext, N] external term columns or NULL */
+  /* --- command: UniformVelocityCommand (LAB/envs/mdp/commands/velocity_command.py:111-160) --- */
+  int32_t has_command;
+  int32_t cmd_heading_command;
+  float* cmd_vel_b;            /* [N,3] */
+  float* cmd_heading_target;   /* [N] */
+  uint8_t* cmd_is_heading;     /* [N] */
+  uint8_t* cmd_is_standing;    /* [N] */
+  float* cmd_time_left;        /* [N] */
+  int64_t* cmd_counter;        /* [N] */
+  float* cmd_metric_xy;        /* [N] */
+  float* cmd_metric_yaw;       /* [N] */
+  float cmd_resample_lo, cmd_resample_hi;
+  float cmd_range[8];          /* lin_x lo,hi, lin_y lo,hi, ang_z lo,hi, heading lo,hi */
+  float cmd_rel_standing, cmd_rel_heading, cmd_heading_stiffness;
+  float cmd_max_command_step;  /* resampling_time_range[1] / step_dt (fp32 of the double quotient) */
+  /* --- events --- */
+  int32_t ev_reset_root_state; /* reset_root_state_uniform present (LAB/envs/mdp/events.py:823) */
+  float ev_pose_range[12];     /* x y z roll pitch yaw  (lo,hi) */
+  float ev_vel_range[12];
+  int32_t ev_reset_joints;     /* 0 none, 1 by_scale (events.py:987), 2 by_offset (events.py:1020) */
+  float ev_joint_pos_range[2], ev_joint_vel_range[2];
+  int32_t ev_joint_u_base;     /* u_reset column of this event's [J] position draws (then [J] velocity draws) */
+  int32_t num_interval;        /* push_by_setting_velocity terms (events.py:795) */
+  float* ev_interval_time_left[B200LAB_MAX_INTERVAL_EVENTS]; /* [N] each */
+  float ev_interval_range[B200LAB_MAX_INTERVAL_EVENTS][2];
+  float ev_push_range[B200LAB_MAX_INTERVAL_EVENTS][12];
+  /* --- curriculum: terrain_levels_vel (TASKS/.../velocity/mdp/curriculums.py:26-55) --- */
+  int32_t has_terrain_curriculum;
+  int64_t* terrain_levels;     /* [N] */
+  const int64_t* terrain_types;/* [N] */
+  float* env_origins;          /* [N,3] */
+  const float* terrain_origins;/* [rows, cols, 3] */
+  int32_t terrain_rows, terrain_cols;
+  float terrain_size_x;        /* terrain_generator.size[0] */
+  /* --- observations (LAB/managers/observation_manager.py:260-335), one concatenated group --- */
+  int32_t num_obs;
+  int32_t obs_dim;
+  B200LabTerm obs[B200LAB_MAX_TERMS];
+  float* obs_buf;              /* [N, obs_dim] */
+  int32_t obs_enable_corruption;
+  /* --- randomness (SURVEY.md 7 hard part 3) --- */
+  /* parity mode: pre-drawn uniforms in [0,1): u_reset [N, n_u_reset], u_step [N, n_u_step], u_obs [N, obs_dim];
+   * perf mode (pointers NULL): Philox4x32-10 keyed by (seed, step_counter, env, slot). */
+  const float* u_reset;
+  const float* u_step;
+  const float* u_obs;
+  int32_t n_u_reset, n_u_step;
+  uint64_t seed;
+  /* --- episode log accumulators (extras["log"], LAB/envs/manager_based_rl_env.py:365-389) --- */
+  double* log_accum;           /* [B200LAB_LOG_SLOTS] doubles, zeroed by the caller before post_step */
+} B200LabEnvState;
+
+/* Layout of u_reset columns (per reset env): */
+#define B200LAB_U_RESET_CURRICULUM 0   /* randint_like(level, max_level) as floor(u*max_level) */
+#define B200LAB_U_RESET_DRIFT 1        /* 3: RayCaster.reset drift */
+#define B200LAB_U_RESET_POSE 4         /* 6 */
+#define B200LAB_U_RESET_VEL 10         /* 6 */
+#define B200LAB_U_RESET_CMD 16         /* 7: time_left, x, y, z, heading, is_heading, is_standing */
+#define B200LAB_U_RESET_JOINT 23       /* 2*J: joint pos scale/offset [J], joint vel [J] */
+/* Layout of u_step columns (per env): */
+#define B200LAB_U_STEP_CMD 0           /* 7 (same order as above) */
+#define B200LAB_U_STEP_INTERVAL 7      /* per interval term k: 7 at 7+7k: time, x y z roll pitch yaw */
+
+/* log_accum layout: [0] = number of reset envs; [1 .. 1+num_rew) = sum over reset envs of episode_sums;
+ * then num_term termination counts; then 2 command metric sums; then 1 terrain level sum (all envs). */
+#define B200LAB_LOG_SLOTS 128
+
+/* The env descriptor is uploaded to the device once; kernels read it through a pointer (it is constant per
+ * environment instance).  b200lab_env_update re-uploads after a cfg change (e.g. RewardManager.set_term_cfg). */
+void* b200lab_env_create(const B200LabEnvState* st);
+int b200lab_env_update(void* env, const B200LabEnvState* st);
+void b200lab_env_destroy(void* env);
+
+/* ActionManager.process_action (LAB/managers/action_manager.py:318-339) + JointAction.process_actions
+ * (LAB/envs/mdp/actions/joint_actions.py:130-139).  `action_in` [N,A]. */
+int b200lab_process_action(void* env, const float* action_in, void* stream);
+
+/* The two halves of one physics sub-step the reference has around sim.step() (manager_based_rl_env.py:182-196):
+ *   pre : action_manager.apply_action + scene.write_data_to_sim -> Articulation._apply_actuator_model
+ *         (reads the state BEFORE the physics step, writes the efforts/targets handed to the simulator)
+ *   post: scene.update(dt): ArticulationData.update (joint_acc), ContactSensor update, RayCaster timestamps
+ *         (reads the state AFTER the physics step) */
+int b200lab_substep_pre(void* env, const B200LabSimView* sim, void* stream);
+int b200lab_substep_post(void* env, const B200LabSimView* sim, void* stream);
+
+/* Everything in ManagerBasedRLEnv.step after the physics loop and before the observations
+ * (manager_based_rl_env.py:198-236): episode_length_buf += 1, TerminationManager.compute,
+ * RewardManager.compute, _reset_idx for the envs in reset_buf (masked, no host sync),
+ * CommandManager.compute, interval events.  `step_counter` keys the Philox streams (perf mode) and is
+ * env._sim_step_counter // decimation for the reset-event bookkeeping. */
+int b200lab_post_step(void* env, const B200LabSimView* sim, int64_t step_counter, void* stream);
+
+/* ObservationManager.compute (observation_manager.py:238-335) including RayCaster lazy update +
+ * raycast_mesh for outdated envs (ray_caster.py:220-260, LAB/utils/warp/ops.py:24-127). */
+int b200lab_compute_obs(void* env, const B200LabSimView* sim, int64_t step_counter, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Ray casting.  Replaces convert_to_warp_mesh (LAB/utils/warp/ops.py:130-145) and raycast_mesh
+ * (ops.py:24-127 / kernels.py:13-75).
+ * ---------------------------------------------------------------------------------------------- */
+/* Builds the device-side acceleration structure from HOST vertex/face arrays.  Returns an opaque handle
+ * (host pointer to a descriptor; `b200lab_mesh_device_ptr` gives the device-side struct for rc_mesh). */
+void* b200lab_mesh_create(const float* h_vertices, int64_t num_vertices, const int32_t* h_faces,
+                          int64_t num_faces, float cell_size);
+const void* b200lab_mesh_device_ptr(void* mesh);
+int64_t b200lab_mesh_bytes(void* mesh);
+void b200lab_mesh_destroy(void* mesh);
+/* ray_starts/ray_dirs [n,3]; ray_hits [n,3] (inf on miss); optional ray_distance [n], ray_normal [n,3],
+ * ray_face_id [n] (int32, -1 on miss) may be NULL. */
+int b200lab_raycast_mesh(void* mesh, const float* ray_starts, const float* ray_dirs, int64_t n, float max_dist,
+                         float* ray_hits, float* ray_distance, float* ray_normal, int32_t* ray_face_id,
+                         void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * rsl_rl hot path.
+ * ---------------------------------------------------------------------------------------------- */
+/* RolloutStorage.compute_returns (RSL/storage/rollout_storage.py:127-149).
+ * rewards, values [T,N]; dones u8 [T,N]; last_values [N]; returns, advantages [T,N] (out);
+ * scratch: >= 2*(number of CTAs)+2 doubles, see b200lab_gae_scratch_bytes. */
+int64_t b200lab_gae_scratch_bytes(int32_t T, int32_t N);
+int b200lab_gae(const float* rewards, const float* values, const uint8_t* dones, const float* last_values,
+                float* returns, float* advantages, int32_t T, int32_t N, float gamma, float lam,
+                int32_t normalize_advantage, void* scratch, void* stream);
+
+/* PPO.process_env_step time-out bootstrap + RolloutStorage.add_transitions (RSL/algorithms/ppo.py:142-169,
+ * rollout_storage.py:77-103) for one step `t` of the [T,N,.] slabs. */
+typedef struct B200LabTransition {
+  int32_t T, N, obs_dim, act_dim, t;
+  float gamma;
+  const float* obs;          /* [N,obs_dim] */
+  const float* actions;      /* [N,A] */
+  const float* rewards;      /* [N] */
+  const uint8_t* dones;      /* [N] (u8) */
+  const uint8_t* time_outs;  /* [N] or NULL */
+  const float* values;       /* [N] */
+  const float* log_prob;     /* [N] */
+  const float* mu;           /* [N,A] */
+  const float* sigma;        /* [N,A] */
+  float* s_obs; float* s_actions; float* s_rewards; uint8_t* s_dones; float* s_values;
+  float* s_log_prob; float* s_mu; float* s_sigma;
+} B200LabTransition;
+int b200lab_add_transition(const B200LabTransition* tr, void* stream);
+
+/* RolloutStorage.mini_batch_generator gathers (rollout_storage.py:188-197): one fused gather of the eight
+ * flattened [T*N,.] slabs by `idx` (int64 [M]). */
+typedef struct B200LabGather {
+  int64_t M; int32_t obs_dim, act_dim;
+  const int64_t* idx;
+  const float* obs; const float* actions; const float* values; const float* returns;
+  const float* log_prob; const float* advantages; const float* mu; const float* sigma;
+  float* o_obs; float* o_actions; float* o_values; float* o_returns;
+  float* o_log_prob; float* o_advantages; float* o_mu; float* o_sigma;
+} B200LabGather;
+int b200lab_gather_minibatch(const B200LabGather* g, void* stream);
+
+/* Actor-critic MLP (RSL/networks/mlp.py:60-80: Linear+ELU ... Linear).  Y = act(X W^T + b).
+ * X [M,K] row-major, W [Nout,K] row-major (nn.Linear.weight), b [Nout], Y [M,Nout].
+ * precision: 0 = fp32 FFMA (exact-order reference path), 1 = tcgen05 kind::tf32, 2 = tcgen05 3xTF32 split. */
+int b200lab_linear_fwd(const float* X, const float* W, const float* b, float* Y, int64_t M, int32_t K,
+                       int32_t Nout, int32_t elu, int32_t precision, void* stream);
+/* Backward of the same layer.  dY [M,Nout] is the gradient w.r.t. the POST-activation output; Y is the saved
+ * post-activation output (ELU'(x) recovered from Y).  dX may be NULL (first layer).  dW [Nout,K], db [Nout]
+ * are OVERWRITTEN.  dZ is a [M,Nout] scratch that receives dY*ELU'(.) */
+int b200lab_linear_bwd(const float* X, const float* W, const float* Y, const float* dY, float* dZ, float* dX,
+                       float* dW, float* db, int64_t M, int32_t K, int32_t Nout, int32_t elu, int32_t precision,
+                       void* stream);
+
+/* Rollout-side sampling (ActorCritic.act / get_actions_log_prob, RSL/modules/actor_critic.py:115-143):
+ * actions = mu + std*eps; log_prob = sum_a Normal(mu,std).log_prob(actions). eps [M,A] standard normal draws. */
+int b200lab_sample_actions(const float* mu, const float* std, const float* eps, float* actions, float* log_prob,
+                           float* sigma_out, int64_t M, int32_t A, void* stream);
+
+/* PPO loss forward+backward for one minibatch (RSL/algorithms/ppo.py:249-315).
+ * Outputs d_mu [M,A], d_value [M], d_std [A] (+=atomic, caller zeroes), and stats[8] (device):
+ * [0]=surrogate loss, [1]=value loss, [2]=mean entropy, [3]=mean KL, [4..7] scratch. */
+typedef struct B200LabPpoLoss {
+  int64_t M; int32_t A;
+  const float* mu; const float* std; const float* value;   /* current policy outputs: [M,A], [A], [M] */
+  const float* actions; const float* old_log_prob; const float* old_mu; const float* old_sigma;
+  const float* advantages; const float* returns; const float* target_values;
+  float clip_param, value_loss_coef, entropy_coef;
+  int32_t use_clipped_value_loss;
+  float* d_mu; float* d_value; float* d_std; float* stats;
+} B200LabPpoLoss;
+int b200lab_ppo_loss(const B200LabPpoLoss* a, void* stream);
+
+/* clip_grad_norm_ + Adam.step over flat parameter/gradient buffers (ppo.py:380-381).
+ * lr is read from device memory (lr_dev[0]) so that the KL-adaptive schedule needs no host sync;
+ * b200lab_adapt_lr updates it from stats[3] (ppo.py:260-294). */
+int b200lab_adapt_lr(float* lr_dev, const float* stats, float desired_kl, float inv_world_size, void* stream);
+int b200lab_grad_sumsq(const float* grad, int64_t n, float* out_sumsq, void* stream);
+int b200lab_adam_clip_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int64_t n,
+                           const float* lr_dev, const float* grad_sumsq, float grad_scale, float max_grad_norm,
+                           float beta1, float beta2, float eps, int64_t step, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200LAB_H_ */

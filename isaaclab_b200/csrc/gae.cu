@@ -1,0 +1,195 @@
+// gae.cu -- RolloutStorage.compute_returns (RSL/storage/rollout_storage.py:127-149), add_transitions
+// (rollout_storage.py:77-103 + PPO.process_env_step time-out bootstrap, RSL/algorithms/ppo.py:161-164) and the
+// minibatch gather of mini_batch_generator (rollout_storage.py:188-197).
+//
+// HBM-bound byte work: one thread per env scans the T steps of its column (coalesced across the warp for
+// every t), loads for a chunk of steps are issued before the dependent recurrence consumes them.
+// Compiled with -fmad=false: the recurrence keeps torch's eager rounding order.
+#include "common.cuh"
+
+namespace b200lab {
+
+constexpr int kGaeBlock = 64;
+constexpr int kGaeChunk = 8;
+
+__global__ void __launch_bounds__(kGaeBlock)
+gae_scan_kernel(const float* __restrict__ rewards, const float* __restrict__ values,
+                const uint8_t* __restrict__ dones, const float* __restrict__ last_values,
+                float* __restrict__ returns, float* __restrict__ advantages, int T, int N, float gamma,
+                float lam, double* __restrict__ partials) {
+  int n = blockIdx.x * kGaeBlock + threadIdx.x;
+  double s1 = 0.0, s2 = 0.0;
+  if (n < N) {
+    float adv = 0.0f;
+    float next_v = last_values[n];
+    for (int t0 = T; t0 > 0; t0 -= kGaeChunk) {
+      float r[kGaeChunk], v[kGaeChunk];
+      uint8_t d[kGaeChunk];
+#pragma unroll
+      for (int k = 0; k < kGaeChunk; ++k) {
+        int t = t0 - 1 - k;
+        if (t >= 0) {
+          size_t o = (size_t)t * N + n;
+          r[k] = __ldg(rewards + o);
+          v[k] = __ldg(values + o);
+          d[k] = __ldg(dones + o);
+        }
+      }
+#pragma unroll
+      for (int k = 0; k < kGaeChunk; ++k) {
+        int t = t0 - 1 - k;
+        if (t >= 0) {
+          float nnt = 1.0f - (float)d[k];
+          float ng = nnt * gamma;
+          float delta = (r[k] + ng * next_v) - v[k];
+          adv = delta + (ng * lam) * adv;
+          float ret = adv + v[k];
+          float a = ret - v[k];  // rollout_storage.py:146: advantages = returns - values
+          size_t o = (size_t)t * N + n;
+          returns[o] = ret;
+          advantages[o] = a;
+          s1 += (double)a;
+          s2 += (double)a * (double)a;
+          next_v = v[k];
+        }
+      }
+    }
+  }
+  // block reduction of (sum, sumsq) in double, fixed order
+  __shared__ double sh1[kGaeBlock / 32], sh2[kGaeBlock / 32];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    s1 += __shfl_xor_sync(0xffffffffu, s1, o);
+    s2 += __shfl_xor_sync(0xffffffffu, s2, o);
+  }
+  int w = threadIdx.x >> 5;
+  if ((threadIdx.x & 31) == 0) { sh1[w] = s1; sh2[w] = s2; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double a = 0.0, b = 0.0;
+    for (int i = 0; i < kGaeBlock / 32; ++i) { a += sh1[i]; b += sh2[i]; }
+    partials[2 * blockIdx.x] = a;
+    partials[2 * blockIdx.x + 1] = b;
+  }
+}
+
+// (adv - mean) / (std + 1e-8), std unbiased over all T*N elements (torch.Tensor.std default).
+__global__ void __launch_bounds__(256)
+gae_normalize_kernel(float* __restrict__ advantages, int64_t total, const double* __restrict__ partials,
+                     int num_partials) {
+  __shared__ float s_mean, s_inv;
+  if (threadIdx.x == 0) {
+    double a = 0.0, b = 0.0;
+    for (int i = 0; i < num_partials; ++i) { a += partials[2 * i]; b += partials[2 * i + 1]; }
+    double mean = a / (double)total;
+    double var = (b - a * mean) / (double)(total - 1);
+    if (var < 0.0) var = 0.0;
+    s_mean = (float)mean;
+    s_inv = (float)sqrt(var) + 1e-8f;
+  }
+  __syncthreads();
+  float mean = s_mean, den = s_inv;
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (; i < total; i += stride) advantages[i] = (advantages[i] - mean) / den;
+}
+
+// ---- add_transitions ----
+__global__ void __launch_bounds__(256)
+add_transition_kernel(B200LabTransition tr) {
+  int64_t n = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int N = tr.N;
+  int64_t total_obs = (int64_t)N * tr.obs_dim;
+  int64_t total_act = (int64_t)N * tr.act_dim;
+  int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  size_t t = (size_t)tr.t;
+  for (int64_t i = n; i < total_obs; i += stride) tr.s_obs[t * total_obs + i] = tr.obs[i];
+  for (int64_t i = n; i < total_act; i += stride) {
+    tr.s_actions[t * total_act + i] = tr.actions[i];
+    tr.s_mu[t * total_act + i] = tr.mu[i];
+    tr.s_sigma[t * total_act + i] = tr.sigma[i];
+  }
+  for (int64_t i = n; i < N; i += stride) {
+    float r = tr.rewards[i];
+    float v = tr.values[i];
+    if (tr.time_outs) r = r + tr.gamma * (v * (float)tr.time_outs[i]);  // ppo.py:161-164
+    tr.s_rewards[t * N + i] = r;
+    tr.s_dones[t * N + i] = tr.dones[i];
+    tr.s_values[t * N + i] = v;
+    tr.s_log_prob[t * N + i] = tr.log_prob[i];
+  }
+}
+
+// ---- minibatch gather: one warp per sample row, lanes stride the columns (coalesced) ----
+__global__ void __launch_bounds__(256)
+gather_minibatch_kernel(B200LabGather g) {
+  int lane = threadIdx.x & 31;
+  int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  for (int64_t m = warp; m < g.M; m += nwarps) {
+    int64_t src = __ldg(g.idx + m);
+    const float* so = g.obs + src * g.obs_dim;
+    float* dobs = g.o_obs + m * g.obs_dim;
+    for (int c = lane; c < g.obs_dim; c += 32) dobs[c] = __ldg(so + c);
+    for (int c = lane; c < g.act_dim; c += 32) {
+      g.o_actions[m * g.act_dim + c] = __ldg(g.actions + src * g.act_dim + c);
+      g.o_mu[m * g.act_dim + c] = __ldg(g.mu + src * g.act_dim + c);
+      g.o_sigma[m * g.act_dim + c] = __ldg(g.sigma + src * g.act_dim + c);
+    }
+    if (lane == 0) g.o_values[m] = __ldg(g.values + src);
+    if (lane == 1) g.o_returns[m] = __ldg(g.returns + src);
+    if (lane == 2) g.o_log_prob[m] = __ldg(g.log_prob + src);
+    if (lane == 3) g.o_advantages[m] = __ldg(g.advantages + src);
+  }
+}
+
+}  // namespace b200lab
+
+using namespace b200lab;
+
+extern "C" {
+
+int64_t b200lab_gae_scratch_bytes(int32_t T, int32_t N) {
+  (void)T;
+  return (int64_t)(2 * ceil_div(N, kGaeBlock) + 2) * (int64_t)sizeof(double);
+}
+
+int b200lab_gae(const float* rewards, const float* values, const uint8_t* dones, const float* last_values,
+                float* returns, float* advantages, int32_t T, int32_t N, float gamma, float lam,
+                int32_t normalize_advantage, void* scratch, void* stream) {
+  B200LAB_CHECK_ARG(T > 0 && N > 0, "T and N must be positive");
+  B200LAB_CHECK_ARG(rewards && values && dones && last_values && returns && advantages && scratch, "null pointer");
+  cudaStream_t s = (cudaStream_t)stream;
+  int blocks = (int)ceil_div(N, kGaeBlock);
+  gae_scan_kernel<<<blocks, kGaeBlock, 0, s>>>(rewards, values, dones, last_values, returns, advantages, T, N,
+                                               gamma, lam, (double*)scratch);
+  count_launch();
+  int rc = check_launch("gae_scan");
+  if (rc) return rc;
+  if (normalize_advantage) {
+    int64_t total = (int64_t)T * N;
+    int nb = (int)min64(ceil_div(total, 256 * 4), 4 * kNumSMs);
+    gae_normalize_kernel<<<nb, 256, 0, s>>>(advantages, total, (const double*)scratch, blocks);
+    count_launch();
+    rc = check_launch("gae_normalize");
+  }
+  return rc;
+}
+
+int b200lab_add_transition(const B200LabTransition* tr, void* stream) {
+  B200LAB_CHECK_ARG(tr && tr->t >= 0 && tr->t < tr->T, "bad transition index (rollout buffer overflow)");
+  int64_t work = (int64_t)tr->N * tr->obs_dim;
+  int nb = (int)min64(ceil_div(work, 256), 8 * kNumSMs);
+  add_transition_kernel<<<nb, 256, 0, (cudaStream_t)stream>>>(*tr);
+  count_launch();
+  return check_launch("add_transition");
+}
+
+int b200lab_gather_minibatch(const B200LabGather* g, void* stream) {
+  B200LAB_CHECK_ARG(g && g->M > 0, "bad gather args");
+  int nb = (int)min64(ceil_div(g->M * 32, 256), 16 * kNumSMs);
+  gather_minibatch_kernel<<<nb, 256, 0, (cudaStream_t)stream>>>(*g);
+  count_launch();
+  return check_launch("gather_minibatch");
+}
+}

@@ -1,0 +1,998 @@
+// mdp.cu -- the fused non-physics step of ManagerBasedRLEnv.step (LAB/envs/manager_based_rl_env.py:153-242).
+//
+// Kernels (one launch each, all on the caller's stream, no host sync anywhere):
+//   process_action_kernel : ActionManager.process_action + JointAction.process_actions
+//   substep_pre_kernel    : apply_action + Articulation._apply_actuator_model (Implicit/IdealPD/DCMotor/NetLSTM/NetMLP)
+//   substep_post_kernel   : ArticulationData.update (joint_acc) + ContactSensor update + RayCaster timestamps
+//   post_step_kernel      : terminations, rewards, masked _reset_idx, command compute, interval events (warp per env)
+//   compute_obs_kernel    : ObservationManager.compute incl. the height-scan ray cast (mdp_obs section below)
+//
+// Memory: everything is env-major fp32 as the reference keeps it; each warp / thread group touches contiguous
+// per-env rows so every sector read is fully used.  Compiled with -fmad=false (bit-exact masks); the tiny
+// actuator nets use explicit fmaf().
+#include <cstdlib>
+#include <cstring>
+
+#include "common.cuh"
+#include "raycast.cuh"
+
+namespace b200lab {
+
+struct EnvHandle {
+  B200LabEnvState host;
+  B200LabEnvState* dev;
+};
+
+typedef B200LabEnvState Env;
+typedef B200LabSimView Sim;
+
+// ------------------------------------------------------------------------------------------------
+// process_action
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+process_action_kernel(const Env* __restrict__ e, const float* __restrict__ in) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int A = e->A;
+  int64_t total = (int64_t)e->N * A;
+  if (i >= total) return;
+  int a = (int)(i % A);
+  float x = in[i];
+  e->prev_action[i] = e->action[i];  // action_manager.py:331
+  e->action[i] = x;                  // :332
+  e->raw_actions[i] = x;             // joint_actions.py:132
+  float p = x * e->action_scale[a] + e->action_offset[a];  // joint_actions.py:134
+  if (e->action_clip) p = fminf(fmaxf(p, e->action_clip[2 * a]), e->action_clip[2 * a + 1]);
+  e->processed_actions[i] = p;
+}
+
+// ------------------------------------------------------------------------------------------------
+// substep_pre: actuator models.  One thread per (env, joint).
+// ------------------------------------------------------------------------------------------------
+constexpr int kActBlock = 128;
+constexpr int kMaxNetFloats = 8192;  // staged net weights (32 KB)
+
+__device__ __forceinline__ float sigmoidf_(float x) { return 1.0f / (1.0f + expf(-x)); }
+
+__device__ __forceinline__ float dc_motor_clip(float tau, float qd, float sat, float vlim, float elim) {
+  // actuator_pd.py:276-286
+  float max_e = sat * (1.0f - qd / vlim);
+  max_e = fminf(fmaxf(max_e, 0.0f), elim);
+  float min_e = sat * (-1.0f - qd / vlim);
+  min_e = fminf(fmaxf(min_e, -elim), 0.0f);
+  return fminf(fmaxf(tau, min_e), max_e);
+}
+
+// LSTM cell stack, hidden size H compile-time; weights in shared memory (broadcast reads).
+template <int H>
+__device__ __forceinline__ float lstm_forward(const float* __restrict__ w, int L, float x0, float x1,
+                                              float* __restrict__ hs, float* __restrict__ cs, int64_t row,
+                                              int64_t rows) {
+  float xin[H];
+  xin[0] = x0;
+  xin[1] = x1;
+  int in_dim = 2;
+  for (int l = 0; l < L; ++l) {
+    const float* w_ih = w;
+    const float* w_hh = w_ih + 4 * H * in_dim;
+    const float* b_ih = w_hh + 4 * H * H;
+    const float* b_hh = b_ih + 4 * H;
+    w = b_hh + 4 * H;
+    float h[H], c[H];
+    float* hp = hs + ((int64_t)l * rows + row) * H;
+    float* cp = cs + ((int64_t)l * rows + row) * H;
+#pragma unroll
+    for (int k = 0; k < H; k += 4) {
+      float4 a = *reinterpret_cast<const float4*>(hp + k);
+      float4 b = *reinterpret_cast<const float4*>(cp + k);
+      h[k] = a.x; h[k + 1] = a.y; h[k + 2] = a.z; h[k + 3] = a.w;
+      c[k] = b.x; c[k + 1] = b.y; c[k + 2] = b.z; c[k + 3] = b.w;
+    }
+    float hn[H];
+#pragma unroll
+    for (int u = 0; u < H; ++u) {
+      float g4[4];
+#pragma unroll
+      for (int g = 0; g < 4; ++g) {
+        int r = g * H + u;
+        float acc = b_ih[r] + b_hh[r];
+        if (l == 0) {
+          acc = fmaf(w_ih[r * 2], xin[0], acc);
+          acc = fmaf(w_ih[r * 2 + 1], xin[1], acc);
+        } else {
+#pragma unroll
+          for (int k = 0; k < H; ++k) acc = fmaf(w_ih[r * H + k], xin[k], acc);
+        }
+#pragma unroll
+        for (int k = 0; k < H; ++k) acc = fmaf(w_hh[r * H + k], h[k], acc);
+        g4[g] = acc;
+      }
+      float ig = sigmoidf_(g4[0]), fg = sigmoidf_(g4[1]), gg = tanhf(g4[2]), og = sigmoidf_(g4[3]);
+      float cn = fmaf(fg, c[u], ig * gg);
+      c[u] = cn;
+      hn[u] = og * tanhf(cn);
+    }
+#pragma unroll
+    for (int k = 0; k < H; k += 4) {
+      *reinterpret_cast<float4*>(hp + k) = make_float4(hn[k], hn[k + 1], hn[k + 2], hn[k + 3]);
+      *reinterpret_cast<float4*>(cp + k) = make_float4(c[k], c[k + 1], c[k + 2], c[k + 3]);
+    }
+#pragma unroll
+    for (int k = 0; k < H; ++k) xin[k] = hn[k];
+    in_dim = H;
+  }
+  // head: Linear(H -> 1)
+  float out = w[H];
+#pragma unroll
+  for (int k = 0; k < H; ++k) out = fmaf(w[k], xin[k], out);
+  return out;
+}
+
+__device__ __forceinline__ float mlp_act(float x, int kind) {
+  switch (kind) {
+    case 0: return x / (1.0f + fabsf(x));            // softsign
+    case 1: return x > 0.0f ? x : expm1f(x);         // elu
+    case 2: return fmaxf(x, 0.0f);                   // relu
+    default: return tanhf(x);
+  }
+}
+
+// MLP with all widths <= 32; activations in registers, weights in shared memory.
+__device__ __forceinline__ float mlp_forward32(const float* __restrict__ w, const B200LabActuatorGroup& g,
+                                               const float* in) {
+  float a[32], b[32];
+  int d0 = g.mlp_dims[0];
+#pragma unroll
+  for (int i = 0; i < 32; ++i) a[i] = i < d0 ? in[i] : 0.0f;
+  for (int l = 0; l < g.mlp_layers; ++l) {
+    int din = g.mlp_dims[l], dout = g.mlp_dims[l + 1];
+    const float* W = w;
+    const float* bias = W + din * dout;
+    w = bias + dout;
+    bool last = (l == g.mlp_layers - 1);
+#pragma unroll
+    for (int o = 0; o < 32; ++o) {
+      float acc = 0.0f;
+      if (o < dout) {
+        acc = bias[o];
+#pragma unroll
+        for (int i = 0; i < 32; ++i)
+          if (i < din) acc = fmaf(W[o * din + i], a[i], acc);
+        if (!last) acc = mlp_act(acc, g.mlp_act);
+      }
+      b[o] = acc;
+    }
+#pragma unroll
+    for (int i = 0; i < 32; ++i) a[i] = b[i];
+  }
+  return a[0];
+}
+
+__global__ void __launch_bounds__(kActBlock)
+substep_pre_kernel(const Env* __restrict__ e, Sim sim) {
+  extern __shared__ float s_w[];
+  const int J = e->J, N = e->N;
+  // stage the weights of the (single) net-based group, if any, in shared memory
+  int net_group = -1;
+  for (int g = 0; g < e->num_act_groups; ++g)
+    if (e->act[g].kind == B200LAB_ACT_NET_LSTM || e->act[g].kind == B200LAB_ACT_NET_MLP) net_group = g;
+  if (net_group >= 0) {
+    const B200LabActuatorGroup& g = e->act[net_group];
+    int nw = 0;
+    if (g.kind == B200LAB_ACT_NET_LSTM) {
+      int H = g.lstm_hidden;
+      for (int l = 0; l < g.lstm_layers; ++l) nw += 4 * H * (l == 0 ? 2 : H) + 4 * H * H + 8 * H;
+      nw += H + 1;
+    } else {
+      for (int l = 0; l < g.mlp_layers; ++l) nw += g.mlp_dims[l] * g.mlp_dims[l + 1] + g.mlp_dims[l + 1];
+    }
+    for (int i = threadIdx.x; i < nw; i += blockDim.x) s_w[i] = g.net_weights[i];
+    __syncthreads();
+  }
+  int64_t gid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (gid >= (int64_t)N * J) return;
+  int n = (int)(gid / J), j = (int)(gid % J);
+  // action_manager.apply_action -> set_joint_{position,effort}_target (joint_actions.py:158-160, 223-225)
+  int col = e->joint_action_col[j];
+  if (col >= 0) {
+    float p = e->processed_actions[(int64_t)n * e->A + col];
+    if (e->action_kind == 0) e->joint_pos_target[gid] = p;
+    else e->joint_effort_target[gid] = p;
+  }
+  int gi = e->joint_group[j];
+  if (gi < 0) return;
+  const B200LabActuatorGroup& g = e->act[gi];
+  float q = sim.joint_pos[gid], qd = sim.joint_vel[gid];
+  float q_t = e->joint_pos_target[gid], qd_t = e->joint_vel_target[gid], ff = e->joint_effort_target[gid];
+  float err_p = q_t - q, err_v = qd_t - qd;
+  float computed, applied;
+  float elim = g.effort_limit[j];
+  if (g.kind == B200LAB_ACT_IMPLICIT || g.kind == B200LAB_ACT_IDEAL_PD || g.kind == B200LAB_ACT_DC_MOTOR) {
+    computed = (g.stiffness[j] * err_p + g.damping[j] * err_v) + ff;  // actuator_pd.py:136 / :190
+    if (g.kind == B200LAB_ACT_DC_MOTOR)
+      applied = dc_motor_clip(computed, qd, g.saturation_effort, g.velocity_limit[j], elim);
+    else
+      applied = fminf(fmaxf(computed, -elim), elim);  // actuator_base.py:309-318
+  } else if (g.kind == B200LAB_ACT_NET_LSTM) {
+    int64_t rows = (int64_t)N * g.group_joints;
+    int64_t row = (int64_t)n * g.group_joints + e->joint_local[j];
+    float t;
+    if (g.lstm_hidden == 8) t = lstm_forward<8>(s_w, g.lstm_layers, err_p, qd, g.lstm_h, g.lstm_c, row, rows);
+    else if (g.lstm_hidden == 16) t = lstm_forward<16>(s_w, g.lstm_layers, err_p, qd, g.lstm_h, g.lstm_c, row, rows);
+    else t = lstm_forward<4>(s_w, g.lstm_layers, err_p, qd, g.lstm_h, g.lstm_c, row, rows);
+    computed = t;  // actuator_net.py:90
+    applied = dc_motor_clip(computed, qd, g.saturation_effort, g.velocity_limit[j], elim);
+  } else {  // B200LAB_ACT_NET_MLP, actuator_net.py:147-189
+    int Jg = g.group_joints, Hh = g.mlp_hist, jl = e->joint_local[j];
+    float* ph = g.mlp_pos_hist + (int64_t)n * Hh * Jg + jl;
+    float* vh = g.mlp_vel_hist + (int64_t)n * Hh * Jg + jl;
+    // roll(1, dim=1): slot k <- slot k-1 ; slot 0 <- newest
+    for (int k = Hh - 1; k > 0; --k) {
+      ph[(int64_t)k * Jg] = ph[(int64_t)(k - 1) * Jg];
+      vh[(int64_t)k * Jg] = vh[(int64_t)(k - 1) * Jg];
+    }
+    ph[0] = err_p;
+    vh[0] = qd;
+    float in[32];
+    int ni = g.mlp_num_idx;
+    for (int k = 0; k < ni; ++k) {
+      float pv = ph[(int64_t)g.mlp_input_idx[k] * Jg] * g.mlp_pos_scale;
+      float vv = vh[(int64_t)g.mlp_input_idx[k] * Jg] * g.mlp_vel_scale;
+      if (g.mlp_vel_pos_order) { in[k] = vv; in[ni + k] = pv; }
+      else { in[k] = pv; in[ni + k] = vv; }
+    }
+    computed = mlp_forward32(s_w, g, in) * g.mlp_torque_scale;
+    applied = dc_motor_clip(computed, qd, g.saturation_effort, g.velocity_limit[j], elim);
+  }
+  e->computed_torque[gid] = computed;
+  e->applied_torque[gid] = applied;
+  if (g.kind == B200LAB_ACT_IMPLICIT) {
+    e->joint_pos_target_sim[gid] = q_t;      // control_action returned unchanged (actuator_pd.py:140)
+    e->joint_effort_target_sim[gid] = ff;
+  } else {
+    e->joint_effort_target_sim[gid] = applied;  // articulation.py:1460
+  }
+}
+
+
+// ------------------------------------------------------------------------------------------------
+// substep_post: scene.update(dt) -- ArticulationData.update (joint_acc, articulation_data.py:78-83,547-556),
+// SensorBase.update (sensor_base.py:197-205) for the contact sensor (recomputed every sub-step because
+// history_length > 0) and the ray caster (only marked outdated; lazily recomputed by compute_obs).
+// Thread layout: blocks own whole envs; W = max(J, B) lanes per env.
+// ------------------------------------------------------------------------------------------------
+constexpr int kPostBlock = 256;
+
+__global__ void __launch_bounds__(kPostBlock)
+substep_post_kernel(const Env* __restrict__ e, Sim sim, int W, int envs_per_block) {
+  const int N = e->N, J = e->J, B = e->B;
+  int el = threadIdx.x / W, i = threadIdx.x % W;
+  int n = blockIdx.x * envs_per_block + el;
+  bool active = el < envs_per_block && n < N;
+  float dt = e->physics_dt;
+  float ts = 0.f, tl = 0.f;
+  bool outdated = false;
+  if (active) {
+    if (i < J) {
+      // joint_acc = (joint_vel - previous_joint_vel) / time_elapsed ; previous <- joint_vel
+      int64_t o = (int64_t)n * J + i;
+      float qd = sim.joint_vel[o];
+      e->joint_acc[o] = (qd - e->prev_joint_vel[o]) / dt;
+      e->prev_joint_vel[o] = qd;
+    }
+    if (e->cs_timestamp) {
+      ts = e->cs_timestamp[n] + dt;                       // sensor_base.py:199
+      tl = e->cs_timestamp_last_update[n];
+      outdated = e->cs_is_outdated[n] || ((ts - tl) + 1e-6f >= e->cs_update_period);  // :200
+    }
+  }
+  __syncthreads();  // every lane of the env has read the env-level scalars
+  if (!active) return;
+  if (e->cs_timestamp && i < B) {
+    if (outdated) {
+      int64_t ob = (int64_t)n * B + i;
+      float fx = 0.f, fy = 0.f, fz = 0.f;
+      if (sim.net_forces_w) { fx = sim.net_forces_w[ob * 3]; fy = sim.net_forces_w[ob * 3 + 1]; fz = sim.net_forces_w[ob * 3 + 2]; }
+      e->cs_net_forces_w[ob * 3] = fx; e->cs_net_forces_w[ob * 3 + 1] = fy; e->cs_net_forces_w[ob * 3 + 2] = fz;
+      // history shift (contact_sensor.py:333-335)
+      int Hh = e->hist;
+      float* hp = e->cs_forces_hist + ((int64_t)n * Hh * B + i) * 3;
+      for (int k = Hh - 1; k > 0; --k) {
+        float* dst = hp + (int64_t)k * B * 3;
+        const float* src = hp + (int64_t)(k - 1) * B * 3;
+        dst[0] = src[0]; dst[1] = src[1]; dst[2] = src[2];
+      }
+      hp[0] = fx; hp[1] = fy; hp[2] = fz;
+      if (e->cs_current_air_time) {
+        float elapsed = ts - tl;  // contact_sensor.py:353
+        bool is_contact = norm3(fx, fy, fz) > e->cs_force_threshold;
+        float ca = e->cs_current_air_time[ob], cc = e->cs_current_contact_time[ob];
+        bool first_contact = (ca > 0.f) && is_contact;
+        bool first_detached = (cc > 0.f) && !is_contact;
+        if (first_contact) e->cs_last_air_time[ob] = ca + elapsed;
+        e->cs_current_air_time[ob] = !is_contact ? ca + elapsed : 0.f;
+        if (first_detached) e->cs_last_contact_time[ob] = cc + elapsed;
+        e->cs_current_contact_time[ob] = is_contact ? cc + elapsed : 0.f;
+      }
+    }
+  }
+  if (i == 0) {
+    if (e->cs_timestamp) {
+      e->cs_timestamp[n] = ts;
+      if (outdated) e->cs_timestamp_last_update[n] = ts;  // sensor_base.py:294
+      e->cs_is_outdated[n] = 0;
+    }
+    if (e->rc_timestamp) {
+      float rts = e->rc_timestamp[n] + dt;
+      e->rc_timestamp[n] = rts;
+      if ((rts - e->rc_timestamp_last_update[n]) + 1e-6f >= e->rc_update_period) e->rc_is_outdated[n] = 1;
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// post_step: one warp per env.
+// ------------------------------------------------------------------------------------------------
+struct EnvCtx {
+  int n, lane;
+  f4 q;
+  f3 pos, lin_w, ang_w, lin_b, ang_b, grav_b;
+  f3 cmd;
+  bool terminated;
+};
+
+__device__ __forceinline__ float u_reset_at(const Env* e, int n, int slot, int64_t step) {
+  return e->u_reset ? e->u_reset[(int64_t)n * e->n_u_reset + slot] : philox_uniform(e->seed, step, 1u, (uint32_t)n, (uint32_t)slot);
+}
+__device__ __forceinline__ float u_step_at(const Env* e, int n, int slot, int64_t step) {
+  return e->u_step ? e->u_step[(int64_t)n * e->n_u_step + slot] : philox_uniform(e->seed, step, 2u, (uint32_t)n, (uint32_t)slot);
+}
+
+__device__ __forceinline__ void derive_state(EnvCtx& c, const float* rs) {
+  c.pos = {rs[0], rs[1], rs[2]};
+  c.q = {rs[3], rs[4], rs[5], rs[6]};
+  c.lin_w = {rs[7], rs[8], rs[9]};
+  c.ang_w = {rs[10], rs[11], rs[12]};
+  c.lin_b = quat_rotate_inverse(c.q, c.lin_w);   // articulation_data.py:604-610
+  c.ang_b = quat_rotate_inverse(c.q, c.ang_w);   // :613-619
+  c.grav_b = quat_rotate_inverse(c.q, f3{0.f, 0.f, -1.f});  // :513-515
+}
+
+// max over the contact history of |F| for body b (net_forces_w_history[n, :, b])
+__device__ __forceinline__ float hist_max_norm(const Env* e, int n, int b) {
+  const float* hp = e->cs_forces_hist + ((int64_t)n * e->hist * e->B + b) * 3;
+  float m = -INFINITY;
+  for (int k = 0; k < e->hist; ++k) {
+    const float* f = hp + (int64_t)k * e->B * 3;
+    m = fmaxf(m, norm3(f[0], f[1], f[2]));
+  }
+  return m;
+}
+
+__device__ float eval_termination(const Env* e, const Sim& sim, const B200LabTerm& t, const EnvCtx& c, int64_t ep_len) {
+  const int n = c.n, lane = c.lane;
+  switch (t.op) {
+    case B200LAB_TERM_TIME_OUT:
+      return ep_len >= e->max_episode_length ? 1.f : 0.f;
+    case B200LAB_TERM_ILLEGAL_CONTACT: {
+      int any = 0;
+      for (int b = lane; b < e->B; b += 32)
+        if ((t.body_mask >> b) & 1ull) any |= hist_max_norm(e, n, b) > t.p[0];
+      return __any_sync(0xffffffffu, any) ? 1.f : 0.f;
+    }
+    case B200LAB_TERM_JOINT_POS_OUT_OF_MANUAL_LIMIT: {
+      int any = 0;
+      for (int j = lane; j < e->J; j += 32)
+        if ((t.joint_mask >> j) & 1ull) {
+          float q = sim.joint_pos[(int64_t)n * e->J + j];
+          any |= (q > t.p[1]) || (q < t.p[0]);
+        }
+      return __any_sync(0xffffffffu, any) ? 1.f : 0.f;
+    }
+    case B200LAB_TERM_ROOT_HEIGHT_BELOW_MINIMUM:
+      return c.pos.z < t.p[0] ? 1.f : 0.f;
+    case B200LAB_TERM_BAD_ORIENTATION:
+      return fabsf(acosf(-c.grav_b.z)) > t.p[0] ? 1.f : 0.f;
+    case B200LAB_TERM_EXTERNAL:
+      return e->ext_values[(int64_t)t.i0 * e->N + n] != 0.f ? 1.f : 0.f;
+  }
+  return 0.f;
+}
+
+__device__ float eval_reward(const Env* e, const Sim& sim, const B200LabTerm& t, const EnvCtx& c) {
+  const int n = c.n, lane = c.lane, J = e->J, B = e->B;
+  const int64_t jo = (int64_t)n * J;
+  switch (t.op) {
+    case B200LAB_REW_IS_ALIVE: return c.terminated ? 0.f : 1.f;
+    case B200LAB_REW_IS_TERMINATED: return c.terminated ? 1.f : 0.f;
+    case B200LAB_REW_LIN_VEL_Z_L2: return c.lin_b.z * c.lin_b.z;
+    case B200LAB_REW_ANG_VEL_XY_L2: return c.ang_b.x * c.ang_b.x + c.ang_b.y * c.ang_b.y;
+    case B200LAB_REW_FLAT_ORIENTATION_L2: return c.grav_b.x * c.grav_b.x + c.grav_b.y * c.grav_b.y;
+    case B200LAB_REW_JOINT_TORQUES_L2:
+    case B200LAB_REW_JOINT_VEL_L1:
+    case B200LAB_REW_JOINT_VEL_L2:
+    case B200LAB_REW_JOINT_ACC_L2:
+    case B200LAB_REW_JOINT_DEVIATION_L1:
+    case B200LAB_REW_JOINT_POS_LIMITS:
+    case B200LAB_REW_JOINT_POS_TARGET_L2: {
+      float acc = 0.f;
+      for (int j = lane; j < J; j += 32) {
+        if (!((t.joint_mask >> j) & 1ull)) continue;
+        float v;
+        switch (t.op) {
+          case B200LAB_REW_JOINT_TORQUES_L2: v = e->applied_torque[jo + j]; v = v * v; break;
+          case B200LAB_REW_JOINT_VEL_L1: v = fabsf(sim.joint_vel[jo + j]); break;
+          case B200LAB_REW_JOINT_VEL_L2: v = sim.joint_vel[jo + j]; v = v * v; break;
+          case B200LAB_REW_JOINT_ACC_L2: v = e->joint_acc[jo + j]; v = v * v; break;
+          case B200LAB_REW_JOINT_DEVIATION_L1: v = fabsf(sim.joint_pos[jo + j] - e->default_joint_pos[j]); break;
+          case B200LAB_REW_JOINT_POS_LIMITS: {
+            float q = sim.joint_pos[jo + j];
+            float lo = q - e->soft_joint_pos_limits[2 * j], hi = q - e->soft_joint_pos_limits[2 * j + 1];
+            v = -fminf(lo, 0.f) + fmaxf(hi, 0.f);   // rewards.py:190-196
+            break;
+          }
+          default: {  // JOINT_POS_TARGET_L2
+            float d = wrap_to_pi(sim.joint_pos[jo + j]) - t.p[0];
+            v = d * d;
+          }
+        }
+        acc += v;
+      }
+      return warp_sum(acc);
+    }
+    case B200LAB_REW_ACTION_RATE_L2:
+    case B200LAB_REW_ACTION_L2: {
+      float acc = 0.f;
+      for (int a = lane; a < e->A; a += 32) {
+        float x = e->action[(int64_t)n * e->A + a];
+        if (t.op == B200LAB_REW_ACTION_RATE_L2) x = x - e->prev_action[(int64_t)n * e->A + a];
+        acc += x * x;
+      }
+      return warp_sum(acc);
+    }
+    case B200LAB_REW_UNDESIRED_CONTACTS:
+    case B200LAB_REW_CONTACT_FORCES: {
+      float acc = 0.f;
+      for (int b = lane; b < B; b += 32)
+        if ((t.body_mask >> b) & 1ull) {
+          float m = hist_max_norm(e, n, b);
+          if (t.op == B200LAB_REW_UNDESIRED_CONTACTS) acc += (m > t.p[0]) ? 1.f : 0.f;
+          else acc += fmaxf(m - t.p[0], 0.f);
+        }
+      return warp_sum(acc);
+    }
+    case B200LAB_REW_TRACK_LIN_VEL_XY_EXP: {
+      float dx = c.cmd.x - c.lin_b.x, dy = c.cmd.y - c.lin_b.y;
+      return expf(-(dx * dx + dy * dy) / t.p[0]);
+    }
+    case B200LAB_REW_TRACK_ANG_VEL_Z_EXP: {
+      float d = c.cmd.z - c.ang_b.z;
+      return expf(-(d * d) / t.p[0]);
+    }
+    case B200LAB_REW_TRACK_LIN_VEL_XY_YAW_FRAME_EXP: {
+      f3 v = quat_rotate_inverse(yaw_quat(c.q), c.lin_w);
+      float dx = c.cmd.x - v.x, dy = c.cmd.y - v.y;
+      return expf(-(dx * dx + dy * dy) / t.p[0]);
+    }
+    case B200LAB_REW_TRACK_ANG_VEL_Z_WORLD_EXP: {
+      float d = c.cmd.z - c.ang_w.z;
+      return expf(-(d * d) / t.p[0]);
+    }
+    case B200LAB_REW_FEET_AIR_TIME: {
+      float acc = 0.f;
+      for (int b = lane; b < B; b += 32)
+        if ((t.body_mask >> b) & 1ull) {
+          float cc = e->cs_current_contact_time[(int64_t)n * B + b];
+          bool first = (cc > 0.f) && (cc < t.p[1]);   // contact_sensor.py:208-210
+          acc += (e->cs_last_air_time[(int64_t)n * B + b] - t.p[0]) * (first ? 1.f : 0.f);
+        }
+      float r = warp_sum(acc);
+      return r * ((sqrtf(c.cmd.x * c.cmd.x + c.cmd.y * c.cmd.y) > 0.1f) ? 1.f : 0.f);
+    }
+    case B200LAB_REW_FEET_AIR_TIME_POSITIVE_BIPED: {
+      int cnt = 0;
+      float mn = INFINITY;
+      for (int b = 0; b < B; ++b)
+        if ((t.body_mask >> b) & 1ull) cnt += e->cs_current_contact_time[(int64_t)n * B + b] > 0.f;
+      for (int b = 0; b < B; ++b)
+        if ((t.body_mask >> b) & 1ull) {
+          float ct = e->cs_current_contact_time[(int64_t)n * B + b];
+          float at = e->cs_current_air_time[(int64_t)n * B + b];
+          float mode = ct > 0.f ? ct : at;
+          mn = fminf(mn, cnt == 1 ? mode : 0.f);
+        }
+      float r = fminf(mn, t.p[0]);
+      return r * ((sqrtf(c.cmd.x * c.cmd.x + c.cmd.y * c.cmd.y) > 0.1f) ? 1.f : 0.f);
+    }
+    case B200LAB_REW_FEET_SLIDE: {
+      float acc = 0.f;
+      uint64_t m1 = t.body_mask, m2 = t.body_mask2;
+      while (m1 && m2) {
+        int b1 = __ffsll((long long)m1) - 1, b2 = __ffsll((long long)m2) - 1;
+        m1 &= m1 - 1; m2 &= m2 - 1;
+        bool contact = hist_max_norm(e, n, b1) > 1.0f;
+        const float* v = sim.body_lin_vel_w + ((int64_t)n * B + b2) * 3;
+        acc += sqrtf(v[0] * v[0] + v[1] * v[1]) * (contact ? 1.f : 0.f);
+      }
+      return acc;
+    }
+    case B200LAB_REW_EXTERNAL:
+      return e->ext_values[(int64_t)t.i0 * e->N + n];
+  }
+  return 0.f;
+}
+
+// UniformVelocityCommand._resample_command + CommandTerm._resample (velocity_command.py:122-138,
+// command_manager.py:176-187).  u[0..6] = time_left, x, y, z, heading, is_heading, is_standing.
+__device__ __forceinline__ void resample_command(const Env* e, int n, const float* u, f3& cmd) {
+  e->cmd_time_left[n] = u[0] * (e->cmd_resample_hi - e->cmd_resample_lo) + e->cmd_resample_lo;
+  e->cmd_counter[n] += 1;
+  const float* r = e->cmd_range;
+  cmd.x = u[1] * (r[1] - r[0]) + r[0];
+  cmd.y = u[2] * (r[3] - r[2]) + r[2];
+  cmd.z = u[3] * (r[5] - r[4]) + r[4];
+  if (e->cmd_heading_command) {
+    e->cmd_heading_target[n] = u[4] * (r[7] - r[6]) + r[6];
+    e->cmd_is_heading[n] = u[5] <= e->cmd_rel_heading;
+  }
+  e->cmd_is_standing[n] = u[6] <= e->cmd_rel_standing;
+}
+
+constexpr int kStepWarps = 4;
+
+__global__ void __launch_bounds__(kStepWarps * 32)
+post_step_kernel(const Env* __restrict__ e, Sim sim, int64_t step) {
+  const int lane = threadIdx.x & 31;
+  const int n = blockIdx.x * kStepWarps + (threadIdx.x >> 5);
+  const int N = e->N, J = e->J, B = e->B, A = e->A;
+  if (n >= N) return;
+  EnvCtx c;
+  c.n = n; c.lane = lane;
+  float rs[13];
+#pragma unroll
+  for (int k = 0; k < 13; ++k) rs[k] = sim.root_state_w[(int64_t)n * 13 + k];
+  derive_state(c, rs);
+  c.cmd = {0.f, 0.f, 0.f};
+  if (e->has_command) c.cmd = {e->cmd_vel_b[n * 3], e->cmd_vel_b[n * 3 + 1], e->cmd_vel_b[n * 3 + 2]};
+  // -- episode counter (manager_based_rl_env.py:200)
+  int64_t ep_len = e->episode_length_buf[n] + 1;
+  // -- terminations (termination_manager.py:151-174)
+  bool terminated = false, truncated = false;
+  for (int t = 0; t < e->num_term; ++t) {
+    bool v = eval_termination(e, sim, e->term[t], c, ep_len) != 0.f;
+    if (e->term[t].time_out) truncated |= v; else terminated |= v;
+    if (lane == 0) e->term_dones[(int64_t)t * N + n] = v;
+  }
+  c.terminated = terminated;
+  const bool reset = terminated || truncated;
+  // -- rewards (reward_manager.py:128-157)
+  {
+    float total = 0.f;
+    const float dt = e->step_dt;
+    for (int r = 0; r < e->num_rew; ++r) {
+      const B200LabTerm& t = e->rew[r];
+      if (t.weight == 0.0f) continue;
+      float value = eval_reward(e, sim, t, c) * t.weight * dt;
+      total += value;
+      if (lane == 0) {
+        e->episode_sums[(int64_t)r * N + n] += value;
+        e->step_reward[(int64_t)n * e->num_rew + r] = value / dt;
+      }
+    }
+    if (lane == 0) {
+      e->reward_buf[n] = total;
+      e->terminated[n] = terminated;
+      e->truncated[n] = truncated;
+      e->reset_buf[n] = reset;
+    }
+  }
+  __syncwarp();
+  // -- _reset_idx (manager_based_rl_env.py:347-392), masked per env
+  if (reset) {
+    // curriculum: terrain_levels_vel (curriculums.py:26-55) + update_env_origins (terrain_importer.py:307-322)
+    if (e->has_terrain_curriculum) {
+      float ox = e->env_origins[n * 3], oy = e->env_origins[n * 3 + 1];
+      float dx = c.pos.x - ox, dy = c.pos.y - oy;
+      float dist = sqrtf(dx * dx + dy * dy);
+      bool up = dist > e->terrain_size_x / 2.0f;
+      bool down = dist < sqrtf(c.cmd.x * c.cmd.x + c.cmd.y * c.cmd.y) * e->max_episode_length_s * 0.5f;
+      down = down && !up;
+      int64_t lvl = e->terrain_levels[n] + (up ? 1 : 0) - (down ? 1 : 0);
+      if (lvl >= e->terrain_rows) {
+        float u = u_reset_at(e, n, B200LAB_U_RESET_CURRICULUM, step);
+        lvl = min((int64_t)(u * (float)e->terrain_rows), (int64_t)e->terrain_rows - 1);
+      } else if (lvl < 0) lvl = 0;
+      const float* to = e->terrain_origins + ((int64_t)lvl * e->terrain_cols + e->terrain_types[n]) * 3;
+      __syncwarp();
+      if (lane == 0) {
+        e->terrain_levels[n] = lvl;
+        e->env_origins[n * 3] = to[0]; e->env_origins[n * 3 + 1] = to[1]; e->env_origins[n * 3 + 2] = to[2];
+      }
+      __syncwarp();
+    }
+    // scene.reset: actuators (actuator_net.py:70-74,142-145)
+    for (int g = 0; g < e->num_act_groups; ++g) {
+      const B200LabActuatorGroup& ag = e->act[g];
+      if (ag.kind == B200LAB_ACT_NET_LSTM) {
+        int per = ag.group_joints * ag.lstm_hidden;
+        int64_t rows = (int64_t)N * per;
+        for (int l = 0; l < ag.lstm_layers; ++l)
+          for (int k = lane; k < per; k += 32) {
+            ag.lstm_h[l * rows + (int64_t)n * per + k] = 0.f;
+            ag.lstm_c[l * rows + (int64_t)n * per + k] = 0.f;
+          }
+      } else if (ag.kind == B200LAB_ACT_NET_MLP) {
+        int per = ag.mlp_hist * ag.group_joints;
+        for (int k = lane; k < per; k += 32) {
+          ag.mlp_pos_hist[(int64_t)n * per + k] = 0.f;
+          ag.mlp_vel_hist[(int64_t)n * per + k] = 0.f;
+        }
+      }
+    }
+    // scene.reset: contact sensor (contact_sensor.py:143-162, sensor_base.py:182-195)
+    if (e->cs_timestamp) {
+      for (int k = lane; k < B * 3; k += 32) e->cs_net_forces_w[(int64_t)n * B * 3 + k] = 0.f;
+      for (int k = lane; k < e->hist * B * 3; k += 32) e->cs_forces_hist[(int64_t)n * e->hist * B * 3 + k] = 0.f;
+      if (e->cs_current_air_time)
+        for (int k = lane; k < B; k += 32) {
+          e->cs_current_air_time[(int64_t)n * B + k] = 0.f;
+          e->cs_last_air_time[(int64_t)n * B + k] = 0.f;
+          e->cs_current_contact_time[(int64_t)n * B + k] = 0.f;
+          e->cs_last_contact_time[(int64_t)n * B + k] = 0.f;
+        }
+      if (lane == 0) { e->cs_timestamp[n] = 0.f; e->cs_timestamp_last_update[n] = 0.f; e->cs_is_outdated[n] = 1; }
+    }
+    // scene.reset: ray caster (ray_caster.py:107-114)
+    if (e->rc_timestamp && lane == 0) {
+      e->rc_timestamp[n] = 0.f; e->rc_timestamp_last_update[n] = 0.f; e->rc_is_outdated[n] = 1;
+      for (int k = 0; k < 3; ++k)
+        e->rc_drift[n * 3 + k] = u_reset_at(e, n, B200LAB_U_RESET_DRIFT + k, step) * (e->rc_drift_hi - e->rc_drift_lo) + e->rc_drift_lo;
+    }
+    // reset events: reset_root_state_uniform (events.py:823-865)
+    if (e->ev_reset_root_state) {
+      float up[6], uv[6];
+#pragma unroll
+      for (int k = 0; k < 6; ++k) {
+        float a = u_reset_at(e, n, B200LAB_U_RESET_POSE + k, step), b = u_reset_at(e, n, B200LAB_U_RESET_VEL + k, step);
+        up[k] = a * (e->ev_pose_range[2 * k + 1] - e->ev_pose_range[2 * k]) + e->ev_pose_range[2 * k];
+        uv[k] = b * (e->ev_vel_range[2 * k + 1] - e->ev_vel_range[2 * k]) + e->ev_vel_range[2 * k];
+      }
+      const float* d = e->default_root_state;
+      const float* org = e->env_origins;
+      rs[0] = (d[0] + (org ? org[n * 3] : 0.f)) + up[0];
+      rs[1] = (d[1] + (org ? org[n * 3 + 1] : 0.f)) + up[1];
+      rs[2] = (d[2] + (org ? org[n * 3 + 2] : 0.f)) + up[2];
+      f4 dq = quat_from_euler_xyz(up[3], up[4], up[5]);
+      f4 qn = quat_mul(f4{d[3], d[4], d[5], d[6]}, dq);
+      rs[3] = qn.w; rs[4] = qn.x; rs[5] = qn.y; rs[6] = qn.z;
+#pragma unroll
+      for (int k = 0; k < 6; ++k) rs[7 + k] = d[7 + k] + uv[k];
+      if (lane < 13) sim.root_state_w[(int64_t)n * 13 + lane] = rs[lane];
+      derive_state(c, rs);
+    }
+    // reset events: reset_joints_by_scale / by_offset (events.py:987-1051)
+    if (e->ev_reset_joints) {
+      for (int j = lane; j < J; j += 32) {
+        float u0 = u_reset_at(e, n, e->ev_joint_u_base + j, step), u1 = u_reset_at(e, n, e->ev_joint_u_base + J + j, step);
+        float sp = u0 * (e->ev_joint_pos_range[1] - e->ev_joint_pos_range[0]) + e->ev_joint_pos_range[0];
+        float sv = u1 * (e->ev_joint_vel_range[1] - e->ev_joint_vel_range[0]) + e->ev_joint_vel_range[0];
+        float qp = e->default_joint_pos[j], qv = e->default_joint_vel[j];
+        if (e->ev_reset_joints == 1) { qp = qp * sp; qv = qv * sv; } else { qp = qp + sp; qv = qv + sv; }
+        qp = fminf(fmaxf(qp, e->soft_joint_pos_limits[2 * j]), e->soft_joint_pos_limits[2 * j + 1]);
+        float vl = e->soft_joint_vel_limits[j];
+        qv = fminf(fmaxf(qv, -vl), vl);
+        int64_t o = (int64_t)n * J + j;
+        sim.joint_pos[o] = qp;                 // articulation.py:514
+        sim.joint_vel[o] = qv;                 // :551-553
+        e->prev_joint_vel[o] = qv;
+        e->joint_acc[o] = 0.f;
+      }
+    }
+    // manager resets, in the order of manager_based_rl_env.py:364-389
+    // action manager (action_manager.py:296-316)
+    for (int a = lane; a < A; a += 32) {
+      e->prev_action[(int64_t)n * A + a] = 0.f;
+      e->action[(int64_t)n * A + a] = 0.f;
+      e->raw_actions[(int64_t)n * A + a] = 0.f;
+    }
+    // reward manager: episodic sums -> log, zero (reward_manager.py:100-126)
+    if (lane == 0 && e->log_accum) atomicAdd(e->log_accum, 1.0);
+    for (int r = lane; r < e->num_rew; r += 32) {
+      if (e->log_accum) atomicAdd(e->log_accum + 1 + r, (double)e->episode_sums[(int64_t)r * N + n]);
+      e->episode_sums[(int64_t)r * N + n] = 0.f;
+    }
+    // termination manager log (termination_manager.py:127-149)
+    if (e->log_accum)
+      for (int t = lane; t < e->num_term; t += 32)
+        if (e->term_dones[(int64_t)t * N + n]) atomicAdd(e->log_accum + 1 + e->num_rew + t, 1.0);
+    // command manager reset (command_manager.py:120-149)
+    if (e->has_command) {
+      if (lane == 0) {
+        if (e->log_accum) {
+          atomicAdd(e->log_accum + 1 + e->num_rew + e->num_term, (double)e->cmd_metric_xy[n]);
+          atomicAdd(e->log_accum + 2 + e->num_rew + e->num_term, (double)e->cmd_metric_yaw[n]);
+        }
+        e->cmd_metric_xy[n] = 0.f;
+        e->cmd_metric_yaw[n] = 0.f;
+        e->cmd_counter[n] = 0;
+      }
+      float u[7];
+#pragma unroll
+      for (int k = 0; k < 7; ++k) u[k] = u_reset_at(e, n, B200LAB_U_RESET_CMD + k, step);
+      __syncwarp();
+      if (lane == 0) resample_command(e, n, u, c.cmd);
+      c.cmd.x = __shfl_sync(0xffffffffu, c.cmd.x, 0);
+      c.cmd.y = __shfl_sync(0xffffffffu, c.cmd.y, 0);
+      c.cmd.z = __shfl_sync(0xffffffffu, c.cmd.z, 0);
+    }
+    ep_len = 0;  // manager_based_rl_env.py:392
+  }
+  if (lane == 0) e->episode_length_buf[n] = ep_len;
+  __syncwarp();
+  // -- command_manager.compute (command_manager.py:151-166)
+  if (e->has_command) {
+    if (lane == 0) {
+      // _update_metrics (velocity_command.py:111-120)
+      float ex = c.cmd.x - c.lin_b.x, ey = c.cmd.y - c.lin_b.y;
+      e->cmd_metric_xy[n] += sqrtf(ex * ex + ey * ey) / e->cmd_max_command_step;
+      e->cmd_metric_yaw[n] += fabsf(c.cmd.z - c.ang_b.z) / e->cmd_max_command_step;
+      float tl = e->cmd_time_left[n] - e->step_dt;
+      e->cmd_time_left[n] = tl;
+      if (tl <= 0.0f) {
+        float u[7];
+#pragma unroll
+        for (int k = 0; k < 7; ++k) u[k] = u_step_at(e, n, B200LAB_U_STEP_CMD + k, step);
+        resample_command(e, n, u, c.cmd);
+      }
+      // _update_command (velocity_command.py:140-160)
+      if (e->cmd_heading_command && e->cmd_is_heading[n]) {
+        f3 fw = quat_apply(c.q, f3{1.f, 0.f, 0.f});            // heading_w, articulation_data.py:518-526
+        float heading = atan2f(fw.y, fw.x);
+        float err = wrap_to_pi(e->cmd_heading_target[n] - heading);
+        c.cmd.z = fminf(fmaxf(e->cmd_heading_stiffness * err, e->cmd_range[4]), e->cmd_range[5]);
+      }
+      if (e->cmd_is_standing[n]) c.cmd = {0.f, 0.f, 0.f};
+      e->cmd_vel_b[n * 3] = c.cmd.x; e->cmd_vel_b[n * 3 + 1] = c.cmd.y; e->cmd_vel_b[n * 3 + 2] = c.cmd.z;
+    }
+  }
+  // -- interval events: push_by_setting_velocity (event_manager.py:204-229, events.py:795-820)
+  if (lane == 0) {
+    for (int k = 0; k < e->num_interval; ++k) {
+      float tl = e->ev_interval_time_left[k][n] - e->step_dt;
+      if (tl < 1e-6f) {
+        int base = B200LAB_U_STEP_INTERVAL + 7 * k;
+        tl = u_step_at(e, n, base, step) * (e->ev_interval_range[k][1] - e->ev_interval_range[k][0]) + e->ev_interval_range[k][0];
+        for (int a = 0; a < 6; ++a) {
+          float lo = e->ev_push_range[k][2 * a], hi = e->ev_push_range[k][2 * a + 1];
+          rs[7 + a] = rs[7 + a] + (u_step_at(e, n, base + 1 + a, step) * (hi - lo) + lo);
+          sim.root_state_w[(int64_t)n * 13 + 7 + a] = rs[7 + a];
+        }
+      }
+      e->ev_interval_time_left[k][n] = tl;
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// compute_obs: ObservationManager.compute_group (observation_manager.py:260-335) for one concatenated group.
+// Thread per (env, obs column); a block owns whole envs so the ray-caster bookkeeping of an env
+// (sensor_base.py:287-296) can be updated after all of its rays were cast.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+compute_obs_kernel(const Env* __restrict__ e, Sim sim, int64_t step, int Dpad, int envs_per_block) {
+  const int N = e->N, J = e->J, D = e->obs_dim;
+  int el = threadIdx.x / Dpad, k = threadIdx.x % Dpad;
+  int n = blockIdx.x * envs_per_block + el;
+  bool env_ok = el < envs_per_block && n < N;
+  bool rc_out = false;
+  if (env_ok && e->rc_is_outdated) rc_out = e->rc_is_outdated[n] != 0;
+  __syncthreads();
+  if (env_ok && k < D) {
+    // locate the term owning column k
+    int t = 0, off = 0;
+    while (t < e->num_obs - 1 && k >= off + e->obs[t].dim) { off += e->obs[t].dim; ++t; }
+    const B200LabTerm& tm = e->obs[t];
+    int li = k - off;
+    const float* rs = sim.root_state_w + (int64_t)n * 13;
+    float v = 0.f;
+    switch (tm.op) {
+      case B200LAB_OBS_BASE_LIN_VEL:
+      case B200LAB_OBS_BASE_ANG_VEL:
+      case B200LAB_OBS_PROJECTED_GRAVITY: {
+        f4 q{rs[3], rs[4], rs[5], rs[6]};
+        f3 w = tm.op == B200LAB_OBS_BASE_LIN_VEL ? f3{rs[7], rs[8], rs[9]}
+               : tm.op == B200LAB_OBS_BASE_ANG_VEL ? f3{rs[10], rs[11], rs[12]} : f3{0.f, 0.f, -1.f};
+        f3 r = quat_rotate_inverse(q, w);
+        v = li == 0 ? r.x : li == 1 ? r.y : r.z;
+        break;
+      }
+      case B200LAB_OBS_GENERATED_COMMANDS: v = e->cmd_vel_b[(int64_t)n * 3 + li]; break;
+      case B200LAB_OBS_JOINT_POS_REL:
+      case B200LAB_OBS_JOINT_VEL_REL:
+      case B200LAB_OBS_JOINT_POS:
+      case B200LAB_OBS_JOINT_VEL: {
+        // li-th selected joint of the mask
+        uint64_t m = tm.joint_mask;
+        for (int s = 0; s < li; ++s) m &= m - 1;
+        int j = __ffsll((long long)m) - 1;
+        int64_t o = (int64_t)n * J + j;
+        if (tm.op == B200LAB_OBS_JOINT_POS_REL) v = sim.joint_pos[o] - e->default_joint_pos[j];
+        else if (tm.op == B200LAB_OBS_JOINT_VEL_REL) v = sim.joint_vel[o] - e->default_joint_vel[j];
+        else if (tm.op == B200LAB_OBS_JOINT_POS) v = sim.joint_pos[o];
+        else v = sim.joint_vel[o];
+        break;
+      }
+      case B200LAB_OBS_LAST_ACTION: v = e->action[(int64_t)n * e->A + li]; break;
+      case B200LAB_OBS_BASE_POS_Z: v = rs[2]; break;
+      case B200LAB_OBS_EXTERNAL: v = e->ext_values[((int64_t)tm.i0 + li) * N + n]; break;
+      case B200LAB_OBS_HEIGHT_SCAN: {
+        float pz, hz;
+        if (rc_out) {
+          // RayCaster._update_buffers_impl (ray_caster.py:220-260)
+          f3 pos{rs[0] + e->rc_drift[n * 3], rs[1] + e->rc_drift[n * 3 + 1], rs[2] + e->rc_drift[n * 3 + 2]};
+          f4 q{rs[3], rs[4], rs[5], rs[6]};
+          f3 ls{e->rc_ray_starts[li * 3], e->rc_ray_starts[li * 3 + 1], e->rc_ray_starts[li * 3 + 2]};
+          f3 ld{e->rc_ray_dirs[li * 3], e->rc_ray_dirs[li * 3 + 1], e->rc_ray_dirs[li * 3 + 2]};
+          f3 st, dr;
+          if (e->rc_attach_yaw_only) { st = quat_apply(yaw_quat(q), ls); dr = ld; }
+          else { st = quat_apply(q, ls); dr = quat_apply(q, ld); }
+          st.x += pos.x; st.y += pos.y; st.z += pos.z;
+          float tt; int face;
+          f3 hit{INFINITY, INFINITY, INFINITY};
+          const MeshAccel* mesh = reinterpret_cast<const MeshAccel*>(e->rc_mesh);
+          if (mesh && raycast_mesh_dev(*mesh, st, dr, e->rc_max_distance, tt, face))
+            hit = {st.x + tt * dr.x, st.y + tt * dr.y, st.z + tt * dr.z};
+          float* hp = e->rc_ray_hits_w + ((int64_t)n * e->R + li) * 3;
+          hp[0] = hit.x; hp[1] = hit.y; hp[2] = hit.z;
+          pz = pos.z; hz = hit.z;
+        } else {
+          pz = e->rc_pos_w[n * 3 + 2];
+          hz = e->rc_ray_hits_w[((int64_t)n * e->R + li) * 3 + 2];
+        }
+        v = (pz - hz) - tm.p[0];  // observations.py:173
+        break;
+      }
+    }
+    // noise -> clip -> scale (observation_manager.py:313-318)
+    if (e->obs_enable_corruption && tm.noise_kind != B200LAB_NOISE_NONE) {
+      if (tm.noise_kind == B200LAB_NOISE_CONSTANT_ADD) v = v + tm.noise_lo;
+      else {
+        float u = e->u_obs ? e->u_obs[(int64_t)n * D + k] : philox_uniform(e->seed, step, 3u, (uint32_t)n, (uint32_t)k);
+        float nz = u * tm.noise_span + tm.noise_lo;
+        if (tm.noise_kind == B200LAB_NOISE_UNIFORM_ADD) v = (v + u * tm.noise_span) + tm.noise_lo;  // noise_model.py:64
+        else if (tm.noise_kind == B200LAB_NOISE_UNIFORM_SCALE) v = v * nz;
+        else v = nz;
+      }
+    }
+    if (tm.clip_on) v = fminf(fmaxf(v, tm.clip_lo), tm.clip_hi);
+    if (tm.scale_on) v = v * tm.scale;
+    e->obs_buf[(int64_t)n * D + k] = v;
+  }
+  if (env_ok && k == 0 && rc_out) {
+    const float* rs = sim.root_state_w + (int64_t)n * 13;
+    for (int a = 0; a < 3; ++a) e->rc_pos_w[n * 3 + a] = rs[a] + e->rc_drift[n * 3 + a];
+    for (int a = 0; a < 4; ++a) e->rc_quat_w[n * 4 + a] = rs[3 + a];
+    e->rc_timestamp_last_update[n] = e->rc_timestamp[n];
+    e->rc_is_outdated[n] = 0;
+  }
+}
+
+static int launch_geometry(int width, int* wpad, int* epb) {
+  int w = width < 1 ? 1 : width;
+  if (w > 256) return -1;
+  *wpad = w;
+  *epb = 256 / w;
+  return 0;
+}
+}  // namespace b200lab
+
+using namespace b200lab;
+
+extern "C" {
+
+void* b200lab_env_create(const B200LabEnvState* st) {
+  if (!st) { set_error("b200lab_env_create: null state"); return nullptr; }
+  EnvHandle* h = (EnvHandle*)malloc(sizeof(EnvHandle));
+  if (!h) return nullptr;
+  h->host = *st;
+  h->dev = nullptr;
+  cudaError_t err = cudaMalloc((void**)&h->dev, sizeof(B200LabEnvState));
+  if (err == cudaSuccess) err = cudaMemcpy(h->dev, st, sizeof(B200LabEnvState), cudaMemcpyHostToDevice);
+  if (err != cudaSuccess) {
+    set_error("b200lab_env_create: %s", cudaGetErrorString(err));
+    if (h->dev) cudaFree(h->dev);
+    free(h);
+    return nullptr;
+  }
+  return h;
+}
+
+int b200lab_env_update(void* env, const B200LabEnvState* st) {
+  B200LAB_CHECK_ARG(env && st, "null argument");
+  EnvHandle* h = (EnvHandle*)env;
+  h->host = *st;
+  cudaError_t err = cudaMemcpy(h->dev, st, sizeof(B200LabEnvState), cudaMemcpyHostToDevice);
+  if (err != cudaSuccess) { set_error("b200lab_env_update: %s", cudaGetErrorString(err)); return B200LAB_ERR_CUDA; }
+  return B200LAB_OK;
+}
+
+void b200lab_env_destroy(void* env) {
+  if (!env) return;
+  EnvHandle* h = (EnvHandle*)env;
+  if (h->dev) cudaFree(h->dev);
+  free(h);
+}
+
+int b200lab_process_action(void* env, const float* action_in, void* stream) {
+  B200LAB_CHECK_ARG(env && action_in, "null argument");
+  EnvHandle* h = (EnvHandle*)env;
+  int64_t total = (int64_t)h->host.N * h->host.A;
+  process_action_kernel<<<(unsigned)ceil_div(total, 256), 256, 0, (cudaStream_t)stream>>>(h->dev, action_in);
+  count_launch();
+  return check_launch("process_action");
+}
+
+int b200lab_substep_pre(void* env, const B200LabSimView* sim, void* stream) {
+  B200LAB_CHECK_ARG(env && sim && sim->joint_pos && sim->joint_vel, "null argument");
+  EnvHandle* h = (EnvHandle*)env;
+  const B200LabEnvState& s = h->host;
+  size_t smem = 0;
+  int nets = 0;
+  for (int g = 0; g < s.num_act_groups; ++g) {
+    const B200LabActuatorGroup& a = s.act[g];
+    size_t nw = 0;
+    if (a.kind == B200LAB_ACT_NET_LSTM) {
+      int H = a.lstm_hidden;
+      B200LAB_CHECK_ARG(H == 4 || H == 8 || H == 16, "ActuatorNetLSTM hidden size must be 4, 8 or 16");
+      for (int l = 0; l < a.lstm_layers; ++l) nw += 4 * H * (l == 0 ? 2 : H) + 4 * H * H + 8 * H;
+      nw += H + 1;
+      ++nets;
+    } else if (a.kind == B200LAB_ACT_NET_MLP) {
+      B200LAB_CHECK_ARG(a.mlp_layers >= 1 && a.mlp_layers <= 5, "ActuatorNetMLP supports 1..5 layers");
+      for (int l = 0; l <= a.mlp_layers; ++l) B200LAB_CHECK_ARG(a.mlp_dims[l] <= 32, "ActuatorNetMLP width must be <= 32");
+      B200LAB_CHECK_ARG(2 * a.mlp_num_idx == a.mlp_dims[0], "ActuatorNetMLP input dim must be 2*len(input_idx)");
+      for (int l = 0; l < a.mlp_layers; ++l) nw += a.mlp_dims[l] * a.mlp_dims[l + 1] + a.mlp_dims[l + 1];
+      ++nets;
+    }
+    if (nw * sizeof(float) > smem) smem = nw * sizeof(float);
+  }
+  B200LAB_CHECK_ARG(nets <= 1, "at most one network-based actuator group per articulation is supported");
+  B200LAB_CHECK_ARG(smem <= kMaxNetFloats * sizeof(float), "actuator network too large for shared-memory staging");
+  int64_t total = (int64_t)s.N * s.J;
+  substep_pre_kernel<<<(unsigned)ceil_div(total, kActBlock), kActBlock, smem, (cudaStream_t)stream>>>(h->dev, *sim);
+  count_launch();
+  return check_launch("substep_pre");
+}
+
+int b200lab_substep_post(void* env, const B200LabSimView* sim, void* stream) {
+  B200LAB_CHECK_ARG(env && sim && sim->joint_vel, "null argument");
+  EnvHandle* h = (EnvHandle*)env;
+  const B200LabEnvState& s = h->host;
+  int W, epb;
+  int width = s.J > s.B ? s.J : s.B;
+  B200LAB_CHECK_ARG(launch_geometry(width, &W, &epb) == 0, "max(J,B) must be <= 256");
+  substep_post_kernel<<<(unsigned)ceil_div(s.N, epb), kPostBlock, 0, (cudaStream_t)stream>>>(h->dev, *sim, W, epb);
+  count_launch();
+  return check_launch("substep_post");
+}
+
+int b200lab_post_step(void* env, const B200LabSimView* sim, int64_t step_counter, void* stream) {
+  B200LAB_CHECK_ARG(env && sim && sim->root_state_w && sim->joint_pos && sim->joint_vel, "null argument");
+  EnvHandle* h = (EnvHandle*)env;
+  const B200LabEnvState& s = h->host;
+  B200LAB_CHECK_ARG(s.J <= 64 && s.B <= 64, "joint/body masks support up to 64 joints/bodies");
+  post_step_kernel<<<(unsigned)ceil_div(s.N, kStepWarps), kStepWarps * 32, 0, (cudaStream_t)stream>>>(h->dev, *sim, step_counter);
+  count_launch();
+  return check_launch("post_step");
+}
+
+int b200lab_compute_obs(void* env, const B200LabSimView* sim, int64_t step_counter, void* stream) {
+  B200LAB_CHECK_ARG(env && sim && sim->root_state_w, "null argument");
+  EnvHandle* h = (EnvHandle*)env;
+  const B200LabEnvState& s = h->host;
+  int W, epb;
+  B200LAB_CHECK_ARG(launch_geometry(s.obs_dim, &W, &epb) == 0, "obs_dim must be <= 256 (one block per env)");
+  compute_obs_kernel<<<(unsigned)ceil_div(s.N, epb), 256, 0, (cudaStream_t)stream>>>(h->dev, *sim, step_counter, W, epb);
+  count_launch();
+  return check_launch("compute_obs");
+}
+}
