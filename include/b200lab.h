@@ -430,10 +430,12 @@ int b200lab_linear_fwd(const float* X, const float* W, const float* b, float* Y,
                        int32_t Nout, int32_t elu, int32_t precision, void* stream);
 /* Backward of the same layer.  dY [M,Nout] is the gradient w.r.t. the POST-activation output; Y is the saved
  * post-activation output (ELU'(x) recovered from Y).  dX may be NULL (first layer).  dW [Nout,K], db [Nout]
- * are OVERWRITTEN.  dZ is a [M,Nout] scratch that receives dY*ELU'(.) */
+ * are OVERWRITTEN.  dZ is a [M,Nout] scratch that receives dY*ELU'(.); `workspace` holds the split
+ * partial sums of the dW reduction (b200lab_linear_bwd_workspace_bytes). */
+int64_t b200lab_linear_bwd_workspace_bytes(int64_t M, int32_t K, int32_t Nout);
 int b200lab_linear_bwd(const float* X, const float* W, const float* Y, const float* dY, float* dZ, float* dX,
                        float* dW, float* db, int64_t M, int32_t K, int32_t Nout, int32_t elu, int32_t precision,
-                       void* stream);
+                       void* workspace, void* stream);
 
 /* Rollout-side sampling (ActorCritic.act / get_actions_log_prob, RSL/modules/actor_critic.py:115-143):
  * actions = mu + std*eps; log_prob = sum_a Normal(mu,std).log_prob(actions). eps [M,A] standard normal draws. */

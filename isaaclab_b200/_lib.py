@@ -108,8 +108,9 @@ _SIGS = {
     "b200lab_gather_minibatch": (C.c_int, [C.c_void_p, C.c_void_p]),
     "b200lab_linear_fwd": (C.c_int, [C.c_void_p] * 4 + [C.c_int64, C.c_int32, C.c_int32, C.c_int32, C.c_int32,
                                      C.c_void_p]),
+    "b200lab_linear_bwd_workspace_bytes": (C.c_int64, [C.c_int64, C.c_int32, C.c_int32]),
     "b200lab_linear_bwd": (C.c_int, [C.c_void_p] * 8 + [C.c_int64, C.c_int32, C.c_int32, C.c_int32, C.c_int32,
-                                     C.c_void_p]),
+                                     C.c_void_p, C.c_void_p]),
     "b200lab_sample_actions": (C.c_int, [C.c_void_p] * 6 + [C.c_int64, C.c_int32, C.c_void_p]),
     "b200lab_ppo_loss": (C.c_int, [C.c_void_p, C.c_void_p]),
     "b200lab_adapt_lr": (C.c_int, [C.c_void_p, C.c_void_p, C.c_float, C.c_float, C.c_void_p]),

@@ -27,6 +27,7 @@ UNITS = {
     "mdp.cu": ["-fmad=false"],
     "raycast.cu": ["-fmad=false"],
     "mlp.cu": [],
+    "mlp_tc.cu": [],
     "ppo.cu": [],
 }
 

@@ -40,6 +40,7 @@ int64_t b200lab_sizeof(const char* name) {
   std::string n(name);
   if (n == "B200LabTerm") return sizeof(B200LabTerm);
   if (n == "B200LabActuatorGroup") return sizeof(B200LabActuatorGroup);
+  if (n == "B200LabSimView") return sizeof(B200LabSimView);
   if (n == "B200LabEnvState") return sizeof(B200LabEnvState);
   if (n == "B200LabTransition") return sizeof(B200LabTransition);
   if (n == "B200LabGather") return sizeof(B200LabGather);

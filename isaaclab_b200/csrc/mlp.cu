@@ -1,0 +1,221 @@
+// mlp.cu -- actor-critic MLP layers (RSL/networks/mlp.py:60-80: Linear+ELU ... Linear), fp32 SIMT path.
+//
+// precision 0: fp32 FFMA register-tiled GEMM (the exact-order parity path; the reference's own CPU path is fp32).
+// precision 1/2: tcgen05 kind::tf32 paths live in mlp_tc.cu (dispatch below).
+//
+// Three GEMM shapes per layer (row-major everywhere, nn.Linear layout W[Nout,K]):
+//   fwd : Y[M,Nout]  = act(X[M,K] . W^T + b)
+//   dX  : dX[M,K]    = dZ[M,Nout] . W[Nout,K]
+//   dW  : dW[Nout,K] = dZ^T . X   (reduction over M: split across CTAs, deterministic two-pass reduce)
+// Tiles are staged through shared memory with 128-bit loads when the contiguous dimension allows it;
+// M is large (4096 .. 98304 rows), K/Nout <= 512, so grids are M/64 x Nout/64 CTAs -- several waves of 148 SMs.
+#include "common.cuh"
+
+namespace b200lab {
+
+int linear_fwd_tc(const float* X, const float* W, const float* b, float* Y, int64_t M, int K, int Nout, int elu,
+                  int precision, cudaStream_t s);
+
+constexpr int BM = 64, BN = 64, BK = 16;
+constexpr int kGemmThreads = 256;
+
+__device__ __forceinline__ float elu_f(float x) { return x > 0.0f ? x : expm1f(x); }
+
+// Generic strided tile GEMM: C[i,j] = sum_k A(i,k) * B(k,j), A(i,k) = A[i*lda_i + k*lda_k], B(k,j) = B[k*ldb_k + j*ldb_j].
+// grid.z splits the k range (used for the dW reduction over M); each z-slice writes its own C slab.
+// EPI: 0 = store, 1 = +bias, 2 = +bias then ELU.
+template <int EPI>
+__global__ void __launch_bounds__(kGemmThreads)
+sgemm_kernel(const float* __restrict__ A, int64_t lda_i, int64_t lda_k, const float* __restrict__ B, int64_t ldb_k,
+             int64_t ldb_j, float* __restrict__ C, int64_t ldc, int64_t M, int N, int64_t K, int64_t k_per_split,
+             const float* __restrict__ bias) {
+  __shared__ float sA[BK][BM + 4];
+  __shared__ float sB[BK][BN + 4];
+  const int tid = threadIdx.x;
+  const int tx = tid % 16, ty = tid / 16;  // 16 x 16 threads, 4 x 4 outputs each
+  const int64_t i0 = (int64_t)blockIdx.x * BM;
+  const int j0 = blockIdx.y * BN;
+  const int64_t k_begin = (int64_t)blockIdx.z * k_per_split;
+  const int64_t k_end = min64(K, k_begin + k_per_split);
+  float acc[4][4];
+#pragma unroll
+  for (int a = 0; a < 4; ++a)
+#pragma unroll
+    for (int b = 0; b < 4; ++b) acc[a][b] = 0.0f;
+
+  // loader mapping: choose the thread->element map so that the unit-stride dimension is the fastest
+  const bool a_k_contig = (lda_k == 1);
+  const bool b_k_contig = (ldb_k == 1);
+  for (int64_t k0 = k_begin; k0 < k_end; k0 += BK) {
+#pragma unroll
+    for (int r = 0; r < (BM * BK) / kGemmThreads; ++r) {
+      int e = tid + r * kGemmThreads;
+      int kk, ii;
+      if (a_k_contig) { kk = e % BK; ii = e / BK; } else { ii = e % BM; kk = e / BM; }
+      int64_t gi = i0 + ii, gk = k0 + kk;
+      sA[kk][ii] = (gi < M && gk < k_end) ? __ldg(A + gi * lda_i + gk * lda_k) : 0.0f;
+    }
+#pragma unroll
+    for (int r = 0; r < (BN * BK) / kGemmThreads; ++r) {
+      int e = tid + r * kGemmThreads;
+      int kk, jj;
+      if (b_k_contig) { kk = e % BK; jj = e / BK; } else { jj = e % BN; kk = e / BN; }
+      int64_t gk = k0 + kk;
+      int gj = j0 + jj;
+      sB[kk][jj] = (gj < N && gk < k_end) ? __ldg(B + gk * ldb_k + (int64_t)gj * ldb_j) : 0.0f;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int kk = 0; kk < BK; ++kk) {
+      float4 a4 = *reinterpret_cast<const float4*>(&sA[kk][ty * 4]);
+      float4 b4 = *reinterpret_cast<const float4*>(&sB[kk][tx * 4]);
+      float av[4] = {a4.x, a4.y, a4.z, a4.w}, bv[4] = {b4.x, b4.y, b4.z, b4.w};
+#pragma unroll
+      for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int b = 0; b < 4; ++b) acc[a][b] = fmaf(av[a], bv[b], acc[a][b]);
+    }
+    __syncthreads();
+  }
+  float* Cz = C + (int64_t)blockIdx.z * M * ldc;
+#pragma unroll
+  for (int a = 0; a < 4; ++a) {
+    int64_t gi = i0 + ty * 4 + a;
+    if (gi >= M) continue;
+#pragma unroll
+    for (int b = 0; b < 4; ++b) {
+      int gj = j0 + tx * 4 + b;
+      if (gj >= N) continue;
+      float v = acc[a][b];
+      if (EPI >= 1) v += __ldg(bias + gj);
+      if (EPI == 2) v = elu_f(v);
+      Cz[gi * ldc + gj] = v;
+    }
+  }
+}
+
+// dZ = dY * ELU'(pre-activation), recovered from the saved post-activation Y: Y > 0 -> 1, else Y + 1 (alpha = 1).
+__global__ void __launch_bounds__(256)
+elu_bwd_kernel(const float* __restrict__ Y, const float* __restrict__ dY, float* __restrict__ dZ, int64_t n) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (; i < n; i += stride) {
+    float y = __ldg(Y + i);
+    dZ[i] = __ldg(dY + i) * (y > 0.0f ? 1.0f : y + 1.0f);
+  }
+}
+
+// column sums of dZ[M,N] (bias gradient), partials per row-slab then a fixed-order reduce.
+__global__ void __launch_bounds__(256)
+colsum_partial_kernel(const float* __restrict__ dZ, int64_t M, int N, int64_t rows_per_block, float* __restrict__ part) {
+  // block handles rows [r0, r1), threads stride columns; 256 threads = 8 row-lanes x 32 col-lanes
+  __shared__ float sh[8][33];
+  int cl = threadIdx.x % 32, rl = threadIdx.x / 32;
+  int64_t r0 = (int64_t)blockIdx.x * rows_per_block, r1 = min64(M, r0 + rows_per_block);
+  for (int c0 = 0; c0 < N; c0 += 32) {
+    int c = c0 + cl;
+    float s = 0.0f;
+    if (c < N)
+      for (int64_t r = r0 + rl; r < r1; r += 8) s += __ldg(dZ + r * N + c);
+    sh[rl][cl] = s;
+    __syncthreads();
+    if (rl == 0 && c < N) {
+      float t = 0.0f;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) t += sh[k][cl];
+      part[(int64_t)blockIdx.x * N + c] = t;
+    }
+    __syncthreads();
+  }
+}
+
+// out[i] = sum_z part[z, i]  (fixed order => deterministic)
+__global__ void __launch_bounds__(256)
+reduce_slabs_kernel(const float* __restrict__ part, int splits, int64_t n, float* __restrict__ out) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  float s = 0.0f;
+  for (int z = 0; z < splits; ++z) s += __ldg(part + (int64_t)z * n + i);
+  out[i] = s;
+}
+
+static int dw_splits(int64_t M, int K, int Nout) {
+  int64_t tiles = ceil_div(Nout, BM) * ceil_div(K, BN);
+  int64_t want = ceil_div(4 * kNumSMs, tiles);
+  int64_t max_by_m = ceil_div(M, 256);
+  int64_t s = want < max_by_m ? want : max_by_m;
+  return (int)(s < 1 ? 1 : s);
+}
+
+}  // namespace b200lab
+
+using namespace b200lab;
+
+extern "C" {
+
+int64_t b200lab_linear_bwd_workspace_bytes(int64_t M, int32_t K, int32_t Nout) {
+  int splits = dw_splits(M, K, Nout);
+  int64_t colsum_blocks = ceil_div(M, 512);
+  return ((int64_t)splits * Nout * K + colsum_blocks * Nout) * (int64_t)sizeof(float);
+}
+
+int b200lab_linear_fwd(const float* X, const float* W, const float* b, float* Y, int64_t M, int32_t K, int32_t Nout,
+                       int32_t elu, int32_t precision, void* stream) {
+  B200LAB_CHECK_ARG(X && W && b && Y && M > 0 && K > 0 && Nout > 0, "bad argument");
+  cudaStream_t s = (cudaStream_t)stream;
+  if (precision != 0) return linear_fwd_tc(X, W, b, Y, M, K, Nout, elu, precision, s);
+  dim3 grid((unsigned)ceil_div(M, BM), (unsigned)ceil_div(Nout, BN), 1);
+  if (elu)
+    sgemm_kernel<2><<<grid, kGemmThreads, 0, s>>>(X, K, 1, W, 1, K, Y, Nout, M, Nout, K, K, b);
+  else
+    sgemm_kernel<1><<<grid, kGemmThreads, 0, s>>>(X, K, 1, W, 1, K, Y, Nout, M, Nout, K, K, b);
+  count_launch();
+  return check_launch("linear_fwd");
+}
+
+int b200lab_linear_bwd(const float* X, const float* W, const float* Y, const float* dY, float* dZ, float* dX,
+                       float* dW, float* db, int64_t M, int32_t K, int32_t Nout, int32_t elu, int32_t precision,
+                       void* workspace, void* stream) {
+  B200LAB_CHECK_ARG(X && W && dY && dW && db && workspace && M > 0 && K > 0 && Nout > 0, "bad argument");
+  B200LAB_CHECK_ARG(!elu || (Y && dZ), "ELU backward needs the saved output Y and the dZ scratch");
+  (void)precision;  // backward GEMMs run the fp32 path in this version
+  cudaStream_t s = (cudaStream_t)stream;
+  const float* dz = dY;
+  if (elu) {
+    int64_t n = M * Nout;
+    int nb = (int)min64(ceil_div(n, 256), 16 * kNumSMs);
+    elu_bwd_kernel<<<nb, 256, 0, s>>>(Y, dY, dZ, n);
+    count_launch();
+    dz = dZ;
+  }
+  if (dX) {  // dX[M,K] = dZ[M,Nout] . W[Nout,K]
+    dim3 grid((unsigned)ceil_div(M, BM), (unsigned)ceil_div(K, BN), 1);
+    sgemm_kernel<0><<<grid, kGemmThreads, 0, s>>>(dz, Nout, 1, W, K, 1, dX, K, M, K, Nout, Nout, nullptr);
+    count_launch();
+  }
+  // dW[Nout,K] = sum_m dZ[m,n] X[m,k]: A(i=n,k=m) = dZ[m*Nout + n], B(k=m,j=k) = X[m*K + k]
+  float* ws = (float*)workspace;
+  int splits = dw_splits(M, K, Nout);
+  int64_t k_per = ceil_div(ceil_div(M, splits), BK) * BK;
+  splits = (int)ceil_div(M, k_per);
+  {
+    dim3 grid((unsigned)ceil_div(Nout, BM), (unsigned)ceil_div(K, BN), (unsigned)splits);
+    float* dst = splits == 1 ? dW : ws;
+    sgemm_kernel<0><<<grid, kGemmThreads, 0, s>>>(dz, 1, Nout, X, K, 1, dst, K, Nout, K, M, k_per, nullptr);
+    count_launch();
+    if (splits > 1) {
+      int64_t n = (int64_t)Nout * K;
+      reduce_slabs_kernel<<<(unsigned)ceil_div(n, 256), 256, 0, s>>>(ws, splits, n, dW);
+      count_launch();
+    }
+  }
+  {
+    float* part = ws + (int64_t)dw_splits(M, K, Nout) * Nout * K;
+    int blocks = (int)ceil_div(M, 512);
+    colsum_partial_kernel<<<blocks, 256, 0, s>>>(dz, M, Nout, 512, part);
+    reduce_slabs_kernel<<<(unsigned)ceil_div(Nout, 256), 256, 0, s>>>(part, blocks, Nout, db);
+    count_launch(2);
+  }
+  return check_launch("linear_bwd");
+}
+}
