@@ -148,6 +148,11 @@ def lib() -> C.CDLL:
     return l
 
 
+def available() -> bool:
+    """True when the built library file is present (does not load it)."""
+    return os.path.exists(LIB_PATH)
+
+
 def check(rc: int):
     if rc != 0:
         raise RuntimeError(f"libb200lab error {rc}: {lib().b200lab_last_error().decode()}")

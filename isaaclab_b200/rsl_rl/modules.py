@@ -1,0 +1,228 @@
+"""`ActorCritic` with the rsl_rl 3.0.0 interface (RSL/modules/actor_critic.py:15-168) on libb200lab kernels.
+
+Same constructor kwargs, same method surface (`act`, `evaluate`, `act_inference`, `get_actions_log_prob`,
+`action_mean`, `action_std`, `entropy`, `update_normalization`, `reset`) and the same `state_dict()` keys
+(`actor.{0,2,..}.{weight,bias}`, `critic.*`, `std`) so checkpoints interchange with the reference
+(RSL/runners/on_policy_runner.py:289-324).
+
+All parameters are views into ONE flat fp32 buffer (and their `.grad`s into one flat gradient buffer), so the
+gradient all-reduce, the grad-norm and Adam are each a single pass over contiguous memory.  There is no autograd
+on this path: forward and backward are explicit kernel calls through the C ABI (include/b200lab.h).
+"""
+from __future__ import annotations
+
+import math
+
+import torch
+from torch import nn
+
+from .. import _lib
+
+
+def _mlp(in_dim, out_dim, hidden):
+    layers, d = [], in_dim
+    for h in hidden:
+        h = in_dim if h == -1 else h
+        layers += [nn.Linear(d, h), nn.ELU()]
+        d = h
+    layers.append(nn.Linear(d, out_dim))
+    return nn.Sequential(*layers)  # module names "0","1",... as RSL/networks/mlp.py:77-80
+
+
+class _Net:
+    """Per-network forward/backward driver over raw pointers."""
+
+    def __init__(self, seq: nn.Sequential):
+        self.linears = [m for m in seq if isinstance(m, nn.Linear)]
+        self.dims = [self.linears[0].in_features] + [l.out_features for l in self.linears]
+        self._cache = {}
+
+    def buffers(self, M, device):
+        key = (M, str(device))
+        b = self._cache.get(key)
+        if b is None:
+            if len(self._cache) > 4:
+                self._cache.clear()
+            acts = [torch.empty(M, d, device=device) for d in self.dims[1:]]
+            grads = [torch.empty(M, d, device=device) for d in self.dims[1:]]
+            dz = torch.empty(M, max(self.dims[1:]), device=device)
+            ws = max(_lib.lib().b200lab_linear_bwd_workspace_bytes(M, self.dims[i], self.dims[i + 1])
+                     for i in range(len(self.linears)))
+            work = torch.empty((ws + 3) // 4, device=device)
+            b = self._cache[key] = dict(acts=acts, grads=grads, dz=dz, work=work)
+        return b
+
+    def forward(self, x, precision):
+        L = _lib.lib()
+        M = x.shape[0]
+        b = self.buffers(M, x.device)
+        s = _lib.current_stream()
+        inp = x
+        for i, lin in enumerate(self.linears):
+            last = i == len(self.linears) - 1
+            _lib.check(L.b200lab_linear_fwd(_lib.ptr(inp), _lib.ptr(lin.weight), _lib.ptr(lin.bias),
+                                            _lib.ptr(b["acts"][i]), M, self.dims[i], self.dims[i + 1],
+                                            0 if last else 1, precision, s))
+            inp = b["acts"][i]
+        return inp
+
+    def backward(self, x, d_out, precision):
+        """Gradients of the last forward(x); d_out is dLoss/dOutput [M, out]; fills every layer's .grad view."""
+        L = _lib.lib()
+        M = x.shape[0]
+        b = self.buffers(M, x.device)
+        s = _lib.current_stream()
+        dy = d_out
+        for i in reversed(range(len(self.linears))):
+            lin = self.linears[i]
+            last = i == len(self.linears) - 1
+            inp = x if i == 0 else b["acts"][i - 1]
+            dx = None if i == 0 else b["grads"][i - 1]
+            _lib.check(L.b200lab_linear_bwd(_lib.ptr(inp), _lib.ptr(lin.weight), _lib.ptr(b["acts"][i]), _lib.ptr(dy),
+                                            _lib.ptr(b["dz"]), _lib.ptr(dx), _lib.ptr(lin.weight.grad),
+                                            _lib.ptr(lin.bias.grad), M, self.dims[i], self.dims[i + 1],
+                                            0 if last else 1, precision, _lib.ptr(b["work"]), s))
+            dy = dx
+
+
+class ActorCritic(nn.Module):
+    is_recurrent = False
+
+    def __init__(self, obs, obs_groups, num_actions, actor_obs_normalization=False, critic_obs_normalization=False,
+                 actor_hidden_dims=[256, 256, 256], critic_hidden_dims=[256, 256, 256], activation="elu",
+                 init_noise_std=1.0, noise_std_type: str = "scalar", device=None, precision: int = 0, **kwargs):
+        if kwargs:
+            print("ActorCritic.__init__ got unexpected arguments, which will be ignored: " + str(list(kwargs.keys())))
+        super().__init__()
+        if activation.lower() != "elu":
+            raise ValueError("isaaclab_b200 ActorCritic implements the ELU MLP used by the supported configs")
+        if noise_std_type != "scalar":
+            raise ValueError("isaaclab_b200 ActorCritic supports noise_std_type='scalar'")
+        if actor_obs_normalization or critic_obs_normalization:
+            raise NotImplementedError("empirical observation normalisation is not on the fused path yet")
+        self.obs_groups = obs_groups
+        num_actor_obs = sum(obs[g].shape[-1] for g in obs_groups["policy"])
+        num_critic_obs = sum(obs[g].shape[-1] for g in obs_groups["critic"])
+        for g in list(obs_groups["policy"]) + list(obs_groups["critic"]):
+            assert len(obs[g].shape) == 2, "The ActorCritic module only supports 1D observations."
+        if device is None:
+            device = next(iter(obs.values())).device if hasattr(obs, "values") else "cuda"
+        self.actor = _mlp(num_actor_obs, num_actions, actor_hidden_dims)
+        self.critic = _mlp(num_critic_obs, 1, critic_hidden_dims)
+        self.actor_obs_normalization = False
+        self.critic_obs_normalization = False
+        self.actor_obs_normalizer = nn.Identity()
+        self.critic_obs_normalizer = nn.Identity()
+        self.noise_std_type = noise_std_type
+        self.std = nn.Parameter(init_noise_std * torch.ones(num_actions))
+        self.num_actions = num_actions
+        self.precision = precision
+        self._flatten(torch.device(device))
+        self._a = _Net(self.actor)
+        self._c = _Net(self.critic)
+        self._mean = None
+        self._value = None
+        self._sigma_cache = {}
+
+    # -- flat parameter / gradient storage ---------------------------------------------------------
+    def _flatten(self, device):
+        params = list(self.parameters())
+        n = sum(p.numel() for p in params)
+        self.flat_param = torch.empty(n, device=device)
+        # gradient buffer carries 8 extra floats (loss statistics incl. the KL) so one all-reduce moves both
+        self.flat_grad_ext = torch.zeros(n + 8, device=device)
+        self.flat_grad = self.flat_grad_ext[:n]
+        self.stats = self.flat_grad_ext[n:]
+        off = 0
+        self._views = []
+        for p in params:
+            k = p.numel()
+            self.flat_param[off:off + k].copy_(p.data.reshape(-1))
+            p.data = self.flat_param[off:off + k].view(p.shape)
+            p.grad = self.flat_grad[off:off + k].view(p.shape)
+            p.requires_grad_(False)
+            self._views.append((off, k))
+            off += k
+        self.num_params = n
+        self._std_off = self._views[[id(p) for p in params].index(id(self.std))][0]
+
+    def _apply(self, fn, recurse=True):  # keep the flat views alive across .to()/.cuda() calls
+        probe = fn(self.flat_param)
+        if probe.device != self.flat_param.device or probe.dtype != self.flat_param.dtype:
+            raise RuntimeError("isaaclab_b200.ActorCritic lives on one CUDA device in fp32; construct it there")
+        return self
+
+    def load_state_dict(self, state_dict, strict=True):
+        own = dict(self.named_parameters())
+        missing = [k for k in own if k not in state_dict]
+        unexpected = [k for k in state_dict if k not in own]
+        if strict and (missing or unexpected):
+            raise RuntimeError(f"state_dict mismatch: missing {missing}, unexpected {unexpected}")
+        for k, p in own.items():
+            if k in state_dict:
+                p.data.copy_(state_dict[k].to(p.device))
+        return True  # training resumes (RSL/modules/actor_critic.py:166-168)
+
+    # -- rsl_rl surface ----------------------------------------------------------------------------
+    def reset(self, dones=None):
+        pass
+
+    def forward(self):
+        raise NotImplementedError
+
+    def get_actor_obs(self, obs):
+        ts = [obs[g] for g in self.obs_groups["policy"]]
+        return ts[0] if len(ts) == 1 else torch.cat(ts, dim=-1)
+
+    def get_critic_obs(self, obs):
+        ts = [obs[g] for g in self.obs_groups["critic"]]
+        return ts[0] if len(ts) == 1 else torch.cat(ts, dim=-1)
+
+    @property
+    def action_mean(self):
+        return self._mean
+
+    @property
+    def action_std(self):
+        M = self._mean.shape[0]
+        return self.std.detach().expand(M, -1)
+
+    @property
+    def entropy(self):
+        e = (0.5 + 0.5 * math.log(2 * math.pi) + torch.log(self.std.detach())).sum()
+        return e.expand(self._mean.shape[0])
+
+    def update_distribution(self, obs):
+        self._mean = self._a.forward(obs.contiguous().float(), self.precision)
+
+    def act(self, obs, eps=None, **kwargs):
+        """Normal(actor(obs), std).sample().  `eps` (standard-normal draws, [M,A]) may be passed explicitly
+        (parity mode); otherwise drawn from torch's CUDA generator."""
+        x = self.get_actor_obs(obs)
+        self.update_distribution(x)
+        M, A = self._mean.shape
+        if eps is None:
+            eps = torch.randn(M, A, device=x.device)
+        actions = torch.empty(M, A, device=x.device)
+        self._log_prob = torch.empty(M, device=x.device)
+        _lib.check(_lib.lib().b200lab_sample_actions(_lib.ptr(self._mean), _lib.ptr(self.std), _lib.ptr(eps),
+                                                    _lib.ptr(actions), _lib.ptr(self._log_prob), None, M, A,
+                                                    _lib.current_stream()))
+        self._last_actions = actions
+        return actions
+
+    def act_inference(self, obs):
+        return self._a.forward(self.get_actor_obs(obs).contiguous().float(), self.precision)
+
+    def evaluate(self, obs, **kwargs):
+        self._value = self._c.forward(self.get_critic_obs(obs).contiguous().float(), self.precision)
+        return self._value
+
+    def get_actions_log_prob(self, actions):
+        if actions is getattr(self, "_last_actions", None):
+            return self._log_prob
+        mu, sigma = self._mean, self.std.detach()
+        return (-((actions - mu) ** 2) / (2 * sigma ** 2) - torch.log(sigma) - 0.5 * math.log(2 * math.pi)).sum(-1)
+
+    def update_normalization(self, obs):
+        pass

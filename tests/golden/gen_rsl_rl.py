@@ -1,0 +1,103 @@
+"""Generate tests/golden/rsl_rl_*.pt by running the UNMODIFIED reference rsl_rl 3.0.0 on CPU.
+
+Run in the authoring container only (`python tests/golden/gen_rsl_rl.py`); /root/reference must exist.
+The fixture pins RolloutStorage.compute_returns, mini_batch_generator and PPO.update (reference:
+source/rsl_rl/rsl_rl/storage/rollout_storage.py:127-203, algorithms/ppo.py:129-422).
+"""
+import os
+import sys
+
+import torch
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, HERE)
+import ref_harness  # noqa: E402
+
+ref_harness.install()
+from rsl_rl.algorithms import PPO  # noqa: E402
+from rsl_rl.modules import ActorCritic  # noqa: E402
+
+TensorDict = ref_harness.TensorDict
+
+
+def run(name, N, T, obs_dim, act_dim, hidden, seed, entropy_coef, epochs=2, mini_batches=4, timeouts=True):
+    torch.manual_seed(seed)
+    torch.set_num_threads(1)
+    obs0 = TensorDict({"policy": torch.randn(N, obs_dim)}, batch_size=[N])
+    policy = ActorCritic(obs0, {"policy": ["policy"], "critic": ["policy"]}, act_dim, actor_hidden_dims=hidden,
+                         critic_hidden_dims=hidden, activation="elu", init_noise_std=1.0)
+    alg = PPO(policy, num_learning_epochs=epochs, num_mini_batches=mini_batches, clip_param=0.2, gamma=0.99, lam=0.95,
+              value_loss_coef=1.0, entropy_coef=entropy_coef, learning_rate=1e-3, max_grad_norm=1.0,
+              use_clipped_value_loss=True, schedule="adaptive", desired_kl=0.01, device="cpu")
+    alg.init_storage("rl", N, T, obs0, [act_dim])
+    out = {"cfg": dict(N=N, T=T, obs_dim=obs_dim, act_dim=act_dim, hidden=list(hidden), entropy_coef=entropy_coef,
+                       epochs=epochs, mini_batches=mini_batches, gamma=0.99, lam=0.95, clip_param=0.2,
+                       value_loss_coef=1.0, learning_rate=1e-3, max_grad_norm=1.0, desired_kl=0.01)}
+    out["state_dict_before"] = {k: v.clone() for k, v in policy.state_dict().items()}
+    g = torch.Generator().manual_seed(seed + 1)
+    obs = obs0
+    step_inputs = []
+    for t in range(T):
+        with torch.inference_mode():
+            actions = alg.act(obs)
+        rewards = torch.randn(N, generator=g) * 0.05
+        dones = (torch.rand(N, generator=g) < 0.05).long()
+        time_outs = ((torch.rand(N, generator=g) < 0.3) & (dones > 0)) if timeouts else None
+        next_obs = TensorDict({"policy": torch.randn(N, obs_dim, generator=g)}, batch_size=[N])
+        step_inputs.append(dict(obs=obs["policy"].clone(), actions=actions.clone(), rewards=rewards.clone(),
+                                dones=dones.clone(), time_outs=None if time_outs is None else time_outs.clone(),
+                                values=alg.transition.values.clone(), log_prob=alg.transition.actions_log_prob.clone(),
+                                mu=alg.transition.action_mean.clone(), sigma=alg.transition.action_sigma.clone()))
+        extras = {"time_outs": time_outs} if timeouts else {}
+        with torch.inference_mode():
+            alg.process_env_step(next_obs, rewards, dones, extras)
+        obs = next_obs
+    out["steps"] = step_inputs
+    out["last_obs"] = obs["policy"].clone()
+    with torch.inference_mode():
+        alg.compute_returns(obs)
+    st = alg.storage
+    out["storage"] = dict(observations=st.observations["policy"].clone(), actions=st.actions.clone(),
+                          rewards=st.rewards.clone(), dones=st.dones.clone(), values=st.values.clone(),
+                          actions_log_prob=st.actions_log_prob.clone(), mu=st.mu.clone(), sigma=st.sigma.clone(),
+                          returns=st.returns.clone(), advantages=st.advantages.clone())
+    out["last_values"] = policy.evaluate(obs).detach().clone()
+    # record the permutation the generator draws (rollout_storage.py:165)
+    recorded = {}
+    orig_randperm = torch.randperm
+
+    def randperm(*a, **k):
+        r = orig_randperm(*a, **k)
+        recorded["indices"] = r.clone()
+        return r
+
+    torch.randperm = randperm
+    lrs = []
+    orig_step = alg.optimizer.step
+
+    def step(*a, **k):
+        lrs.append(alg.learning_rate)
+        return orig_step(*a, **k)
+
+    alg.optimizer.step = step
+    try:
+        loss = alg.update()
+    finally:
+        torch.randperm = orig_randperm
+    out["indices"] = recorded["indices"]
+    out["lr_per_update"] = torch.tensor(lrs, dtype=torch.float64)
+    out["loss_dict"] = {k: float(v) for k, v in loss.items()}
+    out["state_dict_after"] = {k: v.clone() for k, v in policy.state_dict().items()}
+    opt = alg.optimizer.state_dict()["state"]
+    names = [n for n, _ in policy.named_parameters()]
+    out["adam_after"] = {names[i]: dict(exp_avg=s["exp_avg"].clone(), exp_avg_sq=s["exp_avg_sq"].clone(),
+                                        step=float(s["step"])) for i, s in opt.items()}
+    path = os.path.join(HERE, f"rsl_rl_{name}.pt")
+    torch.save(out, path)
+    print("wrote", path, os.path.getsize(path) // 1024, "KiB; loss", out["loss_dict"], "lr", lrs[-1])
+
+
+if __name__ == "__main__":
+    run("small", N=96, T=8, obs_dim=48, act_dim=12, hidden=[64, 64, 64], seed=7, entropy_coef=0.005)
+    run("ragged", N=50, T=5, obs_dim=37, act_dim=3, hidden=[32, 16], seed=11, entropy_coef=0.01, epochs=1,
+        mini_batches=3, timeouts=False)
