@@ -39,6 +39,7 @@ extern "C" {
 #define B200LAB_MAX_TERMS 32
 #define B200LAB_MAX_ACT_GROUPS 8
 #define B200LAB_MAX_INTERVAL_EVENTS 4
+#define B200LAB_MAX_RESET_JOINT_EVENTS 4
 
 const char* b200lab_last_error(void);
 int b200lab_version(void);
@@ -246,7 +247,7 @@ typedef struct B200LabEnvState {
   float rc_update_period;
   float rc_max_distance;
   int32_t rc_attach_yaw_only;
-  float rc_drift_lo, rc_drift_hi;
+  float rc_drift_lo, rc_drift_span;
   const void* rc_mesh;         /* device-side mesh accel handle from b200lab_mesh_create (or NULL) */
   /* --- env counters --- */
   int64_t* episode_length_buf; /* [N] */
@@ -279,21 +280,28 @@ typedef struct B200LabEnvState {
   int64_t* cmd_counter;        /* [N] */
   float* cmd_metric_xy;        /* [N] */
   float* cmd_metric_yaw;       /* [N] */
-  float cmd_resample_lo, cmd_resample_hi;
+  float cmd_resample_lo, cmd_resample_span;
   float cmd_range[8];          /* lin_x lo,hi, lin_y lo,hi, ang_z lo,hi, heading lo,hi */
+  float cmd_span[4];           /* fp32(hi) - fp32(lo) of the four ranges (Tensor.uniform_) */
   float cmd_rel_standing, cmd_rel_heading, cmd_heading_stiffness;
   float cmd_max_command_step;  /* resampling_time_range[1] / step_dt (fp32 of the double quotient) */
   /* --- events --- */
   int32_t ev_reset_root_state; /* reset_root_state_uniform present (LAB/envs/mdp/events.py:823) */
-  float ev_pose_range[12];     /* x y z roll pitch yaw  (lo,hi) */
+  /* every sampled range is passed as (lo, span): value = u * span + lo, with `span` computed by the host exactly
+   * as the reference computes `upper - lower` (fp32 tensor difference or python-double difference cast to fp32) */
+  float ev_pose_range[12];     /* x y z roll pitch yaw  (lo, span) */
   float ev_vel_range[12];
-  int32_t ev_reset_joints;     /* 0 none, 1 by_scale (events.py:987), 2 by_offset (events.py:1020) */
-  float ev_joint_pos_range[2], ev_joint_vel_range[2];
-  int32_t ev_joint_u_base;     /* u_reset column of this event's [J] position draws (then [J] velocity draws) */
+  /* reset_joints_by_scale (events.py:987) / reset_joints_by_offset (events.py:1020) terms in cfg order; each one
+   * rewrites ALL joints (the reference ignores asset_cfg.joint_ids here), so the last one determines the state.
+   * Term k reads u_reset columns [B200LAB_U_RESET_JOINT + 2*J*k, +J) for positions and the next J for velocities. */
+  int32_t ev_num_reset_joints;
+  int32_t ev_reset_joints_mode[B200LAB_MAX_RESET_JOINT_EVENTS];  /* 1 by_scale, 2 by_offset */
+  float ev_joint_pos_range[B200LAB_MAX_RESET_JOINT_EVENTS][2];   /* (lo, span) */
+  float ev_joint_vel_range[B200LAB_MAX_RESET_JOINT_EVENTS][2];
   int32_t num_interval;        /* push_by_setting_velocity terms (events.py:795) */
   float* ev_interval_time_left[B200LAB_MAX_INTERVAL_EVENTS]; /* [N] each */
-  float ev_interval_range[B200LAB_MAX_INTERVAL_EVENTS][2];
-  float ev_push_range[B200LAB_MAX_INTERVAL_EVENTS][12];
+  float ev_interval_range[B200LAB_MAX_INTERVAL_EVENTS][2];  /* (lo, span) */
+  float ev_push_range[B200LAB_MAX_INTERVAL_EVENTS][12];     /* (lo, span) x 6 */
   /* --- curriculum: terrain_levels_vel (TASKS/.../velocity/mdp/curriculums.py:26-55) --- */
   int32_t has_terrain_curriculum;
   int64_t* terrain_levels;     /* [N] */
@@ -316,6 +324,9 @@ typedef struct B200LabEnvState {
   const float* u_obs;
   int32_t n_u_reset, n_u_step;
   uint64_t seed;
+  /* optional device-side step counter (CUDA-graph replay): when non-NULL, process_action increments it and the
+   * kernels key their Philox streams on it instead of the host-passed `step_counter` argument */
+  int64_t* step_counter_dev;
   /* --- episode log accumulators (extras["log"], LAB/envs/manager_based_rl_env.py:365-389) --- */
   double* log_accum;           /* [B200LAB_LOG_SLOTS] doubles, zeroed by the caller before post_step */
 } B200LabEnvState;
@@ -326,7 +337,7 @@ typedef struct B200LabEnvState {
 #define B200LAB_U_RESET_POSE 4         /* 6 */
 #define B200LAB_U_RESET_VEL 10         /* 6 */
 #define B200LAB_U_RESET_CMD 16         /* 7: time_left, x, y, z, heading, is_heading, is_standing */
-#define B200LAB_U_RESET_JOINT 23       /* 2*J: joint pos scale/offset [J], joint vel [J] */
+#define B200LAB_U_RESET_JOINT 23       /* per reset-joints term: 2*J (joint pos scale/offset [J], joint vel [J]) */
 /* Layout of u_step columns (per env): */
 #define B200LAB_U_STEP_CMD 0           /* 7 (same order as above) */
 #define B200LAB_U_STEP_INTERVAL 7      /* per interval term k: 7 at 7+7k: time, x y z roll pitch yaw */

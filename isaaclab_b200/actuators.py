@@ -1,0 +1,52 @@
+"""Actuator cfg classes with the reference's names and fields (LAB/actuators/actuator_cfg.py): ImplicitActuatorCfg,
+IdealPDActuatorCfg, DCMotorCfg, ActuatorNetLSTMCfg, ActuatorNetMLPCfg.  The models themselves are fused into
+`substep_pre` (csrc/mdp.cu); `network_file` may be a TorchScript path or an in-memory module."""
+from __future__ import annotations
+
+from dataclasses import dataclass, field
+from typing import Any
+
+
+@dataclass
+class ActuatorBaseCfg:
+    joint_names_expr: list[str] = None
+    effort_limit: dict | float | None = None
+    velocity_limit: dict | float | None = None
+    stiffness: dict | float | None = None
+    damping: dict | float | None = None
+    armature: dict | float | None = None
+    friction: dict | float | None = None
+    kind: str = ""
+
+
+@dataclass
+class ImplicitActuatorCfg(ActuatorBaseCfg):
+    kind: str = "implicit"
+
+
+@dataclass
+class IdealPDActuatorCfg(ActuatorBaseCfg):
+    kind: str = "ideal_pd"
+
+
+@dataclass
+class DCMotorCfg(IdealPDActuatorCfg):
+    saturation_effort: float = None
+    kind: str = "dc_motor"
+
+
+@dataclass
+class ActuatorNetLSTMCfg(DCMotorCfg):
+    network_file: Any = None
+    kind: str = "lstm"
+
+
+@dataclass
+class ActuatorNetMLPCfg(DCMotorCfg):
+    network_file: Any = None
+    pos_scale: float = None
+    vel_scale: float = None
+    torque_scale: float = None
+    input_order: str = "pos_vel"
+    input_idx: list[int] = None
+    kind: str = "mlp"

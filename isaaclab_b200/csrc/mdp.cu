@@ -34,6 +34,7 @@ process_action_kernel(const Env* __restrict__ e, const float* __restrict__ in) {
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   int A = e->A;
   int64_t total = (int64_t)e->N * A;
+  if (i == 0 && e->step_counter_dev) *e->step_counter_dev += 1;  // first kernel of the step sequence
   if (i >= total) return;
   int a = (int)(i % A);
   float x = in[i];
@@ -524,14 +525,14 @@ __device__ float eval_reward(const Env* e, const Sim& sim, const B200LabTerm& t,
 // UniformVelocityCommand._resample_command + CommandTerm._resample (velocity_command.py:122-138,
 // command_manager.py:176-187).  u[0..6] = time_left, x, y, z, heading, is_heading, is_standing.
 __device__ __forceinline__ void resample_command(const Env* e, int n, const float* u, f3& cmd) {
-  e->cmd_time_left[n] = u[0] * (e->cmd_resample_hi - e->cmd_resample_lo) + e->cmd_resample_lo;
+  e->cmd_time_left[n] = u[0] * e->cmd_resample_span + e->cmd_resample_lo;
   e->cmd_counter[n] += 1;
   const float* r = e->cmd_range;
-  cmd.x = u[1] * (r[1] - r[0]) + r[0];
-  cmd.y = u[2] * (r[3] - r[2]) + r[2];
-  cmd.z = u[3] * (r[5] - r[4]) + r[4];
+  cmd.x = u[1] * e->cmd_span[0] + r[0];
+  cmd.y = u[2] * e->cmd_span[1] + r[2];
+  cmd.z = u[3] * e->cmd_span[2] + r[4];
   if (e->cmd_heading_command) {
-    e->cmd_heading_target[n] = u[4] * (r[7] - r[6]) + r[6];
+    e->cmd_heading_target[n] = u[4] * e->cmd_span[3] + r[6];
     e->cmd_is_heading[n] = u[5] <= e->cmd_rel_heading;
   }
   e->cmd_is_standing[n] = u[6] <= e->cmd_rel_standing;
@@ -541,6 +542,7 @@ constexpr int kStepWarps = 4;
 
 __global__ void __launch_bounds__(kStepWarps * 32)
 post_step_kernel(const Env* __restrict__ e, Sim sim, int64_t step) {
+  if (e->step_counter_dev) step = *e->step_counter_dev;
   const int lane = threadIdx.x & 31;
   const int n = blockIdx.x * kStepWarps + (threadIdx.x >> 5);
   const int N = e->N, J = e->J, B = e->B, A = e->A;
@@ -645,7 +647,7 @@ post_step_kernel(const Env* __restrict__ e, Sim sim, int64_t step) {
     if (e->rc_timestamp && lane == 0) {
       e->rc_timestamp[n] = 0.f; e->rc_timestamp_last_update[n] = 0.f; e->rc_is_outdated[n] = 1;
       for (int k = 0; k < 3; ++k)
-        e->rc_drift[n * 3 + k] = u_reset_at(e, n, B200LAB_U_RESET_DRIFT + k, step) * (e->rc_drift_hi - e->rc_drift_lo) + e->rc_drift_lo;
+        e->rc_drift[n * 3 + k] = u_reset_at(e, n, B200LAB_U_RESET_DRIFT + k, step) * e->rc_drift_span + e->rc_drift_lo;
     }
     // reset events: reset_root_state_uniform (events.py:823-865)
     if (e->ev_reset_root_state) {
@@ -653,8 +655,8 @@ post_step_kernel(const Env* __restrict__ e, Sim sim, int64_t step) {
 #pragma unroll
       for (int k = 0; k < 6; ++k) {
         float a = u_reset_at(e, n, B200LAB_U_RESET_POSE + k, step), b = u_reset_at(e, n, B200LAB_U_RESET_VEL + k, step);
-        up[k] = a * (e->ev_pose_range[2 * k + 1] - e->ev_pose_range[2 * k]) + e->ev_pose_range[2 * k];
-        uv[k] = b * (e->ev_vel_range[2 * k + 1] - e->ev_vel_range[2 * k]) + e->ev_vel_range[2 * k];
+        up[k] = a * e->ev_pose_range[2 * k + 1] + e->ev_pose_range[2 * k];
+        uv[k] = b * e->ev_vel_range[2 * k + 1] + e->ev_vel_range[2 * k];
       }
       const float* d = e->default_root_state;
       const float* org = e->env_origins;
@@ -670,13 +672,14 @@ post_step_kernel(const Env* __restrict__ e, Sim sim, int64_t step) {
       derive_state(c, rs);
     }
     // reset events: reset_joints_by_scale / by_offset (events.py:987-1051)
-    if (e->ev_reset_joints) {
+    for (int k = 0; k < e->ev_num_reset_joints; ++k) {
+      const int base = B200LAB_U_RESET_JOINT + 2 * J * k;
       for (int j = lane; j < J; j += 32) {
-        float u0 = u_reset_at(e, n, e->ev_joint_u_base + j, step), u1 = u_reset_at(e, n, e->ev_joint_u_base + J + j, step);
-        float sp = u0 * (e->ev_joint_pos_range[1] - e->ev_joint_pos_range[0]) + e->ev_joint_pos_range[0];
-        float sv = u1 * (e->ev_joint_vel_range[1] - e->ev_joint_vel_range[0]) + e->ev_joint_vel_range[0];
+        float u0 = u_reset_at(e, n, base + j, step), u1 = u_reset_at(e, n, base + J + j, step);
+        float sp = u0 * e->ev_joint_pos_range[k][1] + e->ev_joint_pos_range[k][0];
+        float sv = u1 * e->ev_joint_vel_range[k][1] + e->ev_joint_vel_range[k][0];
         float qp = e->default_joint_pos[j], qv = e->default_joint_vel[j];
-        if (e->ev_reset_joints == 1) { qp = qp * sp; qv = qv * sv; } else { qp = qp + sp; qv = qv + sv; }
+        if (e->ev_reset_joints_mode[k] == 1) { qp = qp * sp; qv = qv * sv; } else { qp = qp + sp; qv = qv + sv; }
         qp = fminf(fmaxf(qp, e->soft_joint_pos_limits[2 * j]), e->soft_joint_pos_limits[2 * j + 1]);
         float vl = e->soft_joint_vel_limits[j];
         qv = fminf(fmaxf(qv, -vl), vl);
@@ -760,10 +763,10 @@ post_step_kernel(const Env* __restrict__ e, Sim sim, int64_t step) {
       float tl = e->ev_interval_time_left[k][n] - e->step_dt;
       if (tl < 1e-6f) {
         int base = B200LAB_U_STEP_INTERVAL + 7 * k;
-        tl = u_step_at(e, n, base, step) * (e->ev_interval_range[k][1] - e->ev_interval_range[k][0]) + e->ev_interval_range[k][0];
+        tl = u_step_at(e, n, base, step) * e->ev_interval_range[k][1] + e->ev_interval_range[k][0];
         for (int a = 0; a < 6; ++a) {
-          float lo = e->ev_push_range[k][2 * a], hi = e->ev_push_range[k][2 * a + 1];
-          rs[7 + a] = rs[7 + a] + (u_step_at(e, n, base + 1 + a, step) * (hi - lo) + lo);
+          float lo = e->ev_push_range[k][2 * a], span = e->ev_push_range[k][2 * a + 1];
+          rs[7 + a] = rs[7 + a] + (u_step_at(e, n, base + 1 + a, step) * span + lo);
           sim.root_state_w[(int64_t)n * 13 + 7 + a] = rs[7 + a];
         }
       }
@@ -780,6 +783,7 @@ post_step_kernel(const Env* __restrict__ e, Sim sim, int64_t step) {
 __global__ void __launch_bounds__(256)
 compute_obs_kernel(const Env* __restrict__ e, Sim sim, int64_t step, int Dpad, int envs_per_block) {
   const int N = e->N, J = e->J, D = e->obs_dim;
+  if (e->step_counter_dev) step = *e->step_counter_dev;
   int el = threadIdx.x / Dpad, k = threadIdx.x % Dpad;
   int n = blockIdx.x * envs_per_block + el;
   bool env_ok = el < envs_per_block && n < N;

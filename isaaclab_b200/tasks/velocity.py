@@ -1,0 +1,236 @@
+"""Locomotion velocity-tracking task cfgs, as data: TASKS/manager_based/locomotion/velocity/velocity_env_cfg.py:66-310
+and config/{anymal_c,go1,h1}/rough_env_cfg.py + flat variants, written against isaaclab_b200's cfg classes (same
+field names and term identities as the reference)."""
+from __future__ import annotations
+
+import copy
+import math
+from dataclasses import dataclass, field
+
+from ..assets import ANYMAL_C_CFG, H1_MINIMAL_CFG, UNITREE_GO1_CFG
+from ..envs import mdp
+from ..envs.cfg import (ContactSensorCfg, GridPatternCfg, ManagerBasedRLEnvCfg, RayCasterCfg, SceneCfg, SimCfg,
+                        TerrainImporterCfg)
+from ..managers import CurriculumTermCfg as CurrTerm
+from ..managers import EventTermCfg as EventTerm
+from ..managers import ObservationGroupCfg as ObsGroup
+from ..managers import ObservationTermCfg as ObsTerm
+from ..managers import RewardTermCfg as RewTerm
+from ..managers import SceneEntityCfg
+from ..managers import TerminationTermCfg as DoneTerm
+from ..managers import UniformNoiseCfg as Unoise
+from ..terrains import ROUGH_TERRAINS_CFG
+
+
+class _Cfg:
+    """Attribute container; terms are listed in insertion order (as the reference iterates cfg.__dict__)."""
+
+    def terms(self):
+        return [(k, v) for k, v in self.__dict__.items() if v is not None and not k.startswith("_")]
+
+
+def _scene(robot):
+    return SceneCfg(
+        num_envs=4096, env_spacing=2.5, robot=robot,
+        terrain=TerrainImporterCfg(terrain_type="generator", terrain_generator=copy.deepcopy(ROUGH_TERRAINS_CFG),
+                                   max_init_terrain_level=5),
+        height_scanner=RayCasterCfg(prim_path="{ENV_REGEX_NS}/Robot/base", offset=RayCasterCfg.OffsetCfg(pos=(0.0, 0.0, 20.0)),
+                                    attach_yaw_only=True, pattern_cfg=GridPatternCfg(resolution=0.1, size=[1.6, 1.0])),
+        contact_forces=ContactSensorCfg(prim_path="{ENV_REGEX_NS}/Robot/.*", history_length=3, track_air_time=True))
+
+
+def _commands():
+    c = _Cfg()
+    c.base_velocity = mdp.UniformVelocityCommandCfg(
+        asset_name="robot", resampling_time_range=(10.0, 10.0), rel_standing_envs=0.02, rel_heading_envs=1.0,
+        heading_command=True, heading_control_stiffness=0.5,
+        ranges=mdp.UniformVelocityCommandCfg.Ranges(lin_vel_x=(-1.0, 1.0), lin_vel_y=(-1.0, 1.0), ang_vel_z=(-1.0, 1.0),
+                                                    heading=(-math.pi, math.pi)))
+    return c
+
+
+def _actions():
+    c = _Cfg()
+    c.joint_pos = mdp.JointPositionActionCfg(asset_name="robot", joint_names=[".*"], scale=0.5, use_default_offset=True)
+    return c
+
+
+def _observations():
+    c = _Cfg()
+    p = _Cfg()
+    p.base_lin_vel = ObsTerm(func=mdp.base_lin_vel, noise=Unoise(n_min=-0.1, n_max=0.1))
+    p.base_ang_vel = ObsTerm(func=mdp.base_ang_vel, noise=Unoise(n_min=-0.2, n_max=0.2))
+    p.projected_gravity = ObsTerm(func=mdp.projected_gravity, noise=Unoise(n_min=-0.05, n_max=0.05))
+    p.velocity_commands = ObsTerm(func=mdp.generated_commands, params={"command_name": "base_velocity"})
+    p.joint_pos = ObsTerm(func=mdp.joint_pos_rel, noise=Unoise(n_min=-0.01, n_max=0.01))
+    p.joint_vel = ObsTerm(func=mdp.joint_vel_rel, noise=Unoise(n_min=-1.5, n_max=1.5))
+    p.actions = ObsTerm(func=mdp.last_action)
+    p.height_scan = ObsTerm(func=mdp.height_scan, params={"sensor_cfg": SceneEntityCfg("height_scanner")},
+                            noise=Unoise(n_min=-0.1, n_max=0.1), clip=(-1.0, 1.0))
+    p._group = ObsGroup(enable_corruption=True, concatenate_terms=True)
+    c.policy = p
+    return c
+
+
+def _events():
+    c = _Cfg()
+    c.physics_material = EventTerm(func=mdp.randomize_rigid_body_material, mode="startup",
+                                   params={"asset_cfg": SceneEntityCfg("robot", body_names=".*"),
+                                           "static_friction_range": (0.8, 0.8), "dynamic_friction_range": (0.6, 0.6),
+                                           "restitution_range": (0.0, 0.0), "num_buckets": 64})
+    c.add_base_mass = EventTerm(func=mdp.randomize_rigid_body_mass, mode="startup",
+                                params={"asset_cfg": SceneEntityCfg("robot", body_names="base"),
+                                        "mass_distribution_params": (-5.0, 5.0), "operation": "add"})
+    c.base_external_force_torque = EventTerm(func=mdp.apply_external_force_torque, mode="reset",
+                                             params={"asset_cfg": SceneEntityCfg("robot", body_names="base"),
+                                                     "force_range": (0.0, 0.0), "torque_range": (-0.0, 0.0)})
+    c.reset_base = EventTerm(func=mdp.reset_root_state_uniform, mode="reset", params={
+        "pose_range": {"x": (-0.5, 0.5), "y": (-0.5, 0.5), "yaw": (-3.14, 3.14)},
+        "velocity_range": {k: (-0.5, 0.5) for k in ("x", "y", "z", "roll", "pitch", "yaw")}})
+    c.reset_robot_joints = EventTerm(func=mdp.reset_joints_by_scale, mode="reset",
+                                     params={"position_range": (0.5, 1.5), "velocity_range": (0.0, 0.0)})
+    c.push_robot = EventTerm(func=mdp.push_by_setting_velocity, mode="interval", interval_range_s=(10.0, 15.0),
+                             params={"velocity_range": {"x": (-0.5, 0.5), "y": (-0.5, 0.5)}})
+    return c
+
+
+def _rewards():
+    c = _Cfg()
+    c.track_lin_vel_xy_exp = RewTerm(func=mdp.track_lin_vel_xy_exp, weight=1.0,
+                                     params={"command_name": "base_velocity", "std": math.sqrt(0.25)})
+    c.track_ang_vel_z_exp = RewTerm(func=mdp.track_ang_vel_z_exp, weight=0.5,
+                                    params={"command_name": "base_velocity", "std": math.sqrt(0.25)})
+    c.lin_vel_z_l2 = RewTerm(func=mdp.lin_vel_z_l2, weight=-2.0)
+    c.ang_vel_xy_l2 = RewTerm(func=mdp.ang_vel_xy_l2, weight=-0.05)
+    c.dof_torques_l2 = RewTerm(func=mdp.joint_torques_l2, weight=-1.0e-5)
+    c.dof_acc_l2 = RewTerm(func=mdp.joint_acc_l2, weight=-2.5e-7)
+    c.action_rate_l2 = RewTerm(func=mdp.action_rate_l2, weight=-0.01)
+    c.feet_air_time = RewTerm(func=mdp.feet_air_time, weight=0.125,
+                              params={"sensor_cfg": SceneEntityCfg("contact_forces", body_names=".*FOOT"),
+                                      "command_name": "base_velocity", "threshold": 0.5})
+    c.undesired_contacts = RewTerm(func=mdp.undesired_contacts, weight=-1.0,
+                                   params={"sensor_cfg": SceneEntityCfg("contact_forces", body_names=".*THIGH"),
+                                           "threshold": 1.0})
+    c.flat_orientation_l2 = RewTerm(func=mdp.flat_orientation_l2, weight=0.0)
+    c.dof_pos_limits = RewTerm(func=mdp.joint_pos_limits, weight=0.0)
+    return c
+
+
+def _terminations():
+    c = _Cfg()
+    c.time_out = DoneTerm(func=mdp.time_out, time_out=True)
+    c.base_contact = DoneTerm(func=mdp.illegal_contact,
+                              params={"sensor_cfg": SceneEntityCfg("contact_forces", body_names="base"), "threshold": 1.0})
+    return c
+
+
+def _curriculum():
+    c = _Cfg()
+    c.terrain_levels = CurrTerm(func=mdp.terrain_levels_vel)
+    return c
+
+
+def LocomotionVelocityRoughEnvCfg(robot) -> ManagerBasedRLEnvCfg:
+    """velocity_env_cfg.py:282-310."""
+    cfg = ManagerBasedRLEnvCfg(scene=_scene(robot), observations=_observations(), actions=_actions(),
+                               commands=_commands(), rewards=_rewards(), terminations=_terminations(),
+                               events=_events(), curriculum=_curriculum(), decimation=4, episode_length_s=20.0,
+                               sim=SimCfg(dt=0.005, render_interval=4))
+    cfg.scene.height_scanner.update_period = cfg.decimation * cfg.sim.dt
+    cfg.scene.contact_forces.update_period = cfg.sim.dt
+    return cfg
+
+
+def AnymalCRoughEnvCfg() -> ManagerBasedRLEnvCfg:
+    """config/anymal_c/rough_env_cfg.py:17-24 (Isaac-Velocity-Rough-Anymal-C-v0)."""
+    return LocomotionVelocityRoughEnvCfg(ANYMAL_C_CFG.replace())
+
+
+def _flatten(cfg):
+    """config/anymal_c/flat_env_cfg.py:12-32: plane terrain, no height scan, no terrain curriculum."""
+    cfg.rewards.flat_orientation_l2.weight = -5.0
+    cfg.rewards.dof_torques_l2.weight = -2.5e-5
+    cfg.rewards.feet_air_time.weight = 0.5
+    cfg.scene.terrain.terrain_type = "plane"
+    cfg.scene.terrain.terrain_generator = None
+    cfg.scene.height_scanner = None
+    cfg.observations.policy.height_scan = None
+    cfg.curriculum.terrain_levels = None
+    return cfg
+
+
+def AnymalCFlatEnvCfg() -> ManagerBasedRLEnvCfg:
+    """Isaac-Velocity-Flat-Anymal-C-v0 (obs 48)."""
+    return _flatten(AnymalCRoughEnvCfg())
+
+
+def UnitreeGo1RoughEnvCfg() -> ManagerBasedRLEnvCfg:
+    """config/go1/rough_env_cfg.py:17-60 (Isaac-Velocity-Rough-Unitree-Go1-v0)."""
+    cfg = LocomotionVelocityRoughEnvCfg(UNITREE_GO1_CFG.replace())
+    cfg.scene.height_scanner.prim_path = "{ENV_REGEX_NS}/Robot/trunk"
+    gen = cfg.scene.terrain.terrain_generator
+    gen.sub_terrains["boxes"].grid_height_range = (0.025, 0.1)
+    gen.sub_terrains["random_rough"].noise_range = (0.01, 0.06)
+    gen.sub_terrains["random_rough"].noise_step = 0.01
+    cfg.actions.joint_pos.scale = 0.25
+    cfg.events.push_robot = None
+    cfg.events.add_base_mass.params["mass_distribution_params"] = (-1.0, 3.0)
+    cfg.events.add_base_mass.params["asset_cfg"].body_names = "trunk"
+    cfg.events.base_external_force_torque.params["asset_cfg"].body_names = "trunk"
+    cfg.events.reset_robot_joints.params["position_range"] = (1.0, 1.0)
+    cfg.events.reset_base.params = {"pose_range": {"x": (-0.5, 0.5), "y": (-0.5, 0.5), "yaw": (-3.14, 3.14)},
+                                    "velocity_range": {k: (0.0, 0.0) for k in ("x", "y", "z", "roll", "pitch", "yaw")}}
+    cfg.rewards.feet_air_time.params["sensor_cfg"].body_names = ".*_foot"
+    cfg.rewards.feet_air_time.weight = 0.01
+    cfg.rewards.undesired_contacts = None
+    cfg.rewards.dof_torques_l2.weight = -0.0002
+    cfg.rewards.track_lin_vel_xy_exp.weight = 1.5
+    cfg.rewards.track_ang_vel_z_exp.weight = 0.75
+    cfg.rewards.dof_acc_l2.weight = -2.5e-7
+    cfg.terminations.base_contact.params["sensor_cfg"].body_names = "trunk"
+    return cfg
+
+
+def H1RoughEnvCfg() -> ManagerBasedRLEnvCfg:
+    """config/h1/rough_env_cfg.py:22-150 (Isaac-Velocity-Rough-H1-v0)."""
+    cfg = LocomotionVelocityRoughEnvCfg(H1_MINIMAL_CFG.replace())
+    r = cfg.rewards
+    # H1Rewards(RewardsCfg): inherited fields keep their position, new fields are appended (dataclass field order)
+    r.lin_vel_z_l2 = None
+    r.track_lin_vel_xy_exp = RewTerm(func=mdp.track_lin_vel_xy_yaw_frame_exp, weight=1.0,
+                                     params={"command_name": "base_velocity", "std": 0.5})
+    r.track_ang_vel_z_exp = RewTerm(func=mdp.track_ang_vel_z_world_exp, weight=1.0,
+                                    params={"command_name": "base_velocity", "std": 0.5})
+    r.feet_air_time = RewTerm(func=mdp.feet_air_time_positive_biped, weight=0.25,
+                              params={"command_name": "base_velocity",
+                                      "sensor_cfg": SceneEntityCfg("contact_forces", body_names=".*ankle_link"),
+                                      "threshold": 0.4})
+    r.dof_pos_limits = RewTerm(func=mdp.joint_pos_limits, weight=-1.0,
+                               params={"asset_cfg": SceneEntityCfg("robot", joint_names=".*_ankle")})
+    r.termination_penalty = RewTerm(func=mdp.is_terminated, weight=-200.0)
+    r.feet_slide = RewTerm(func=mdp.feet_slide, weight=-0.25,
+                           params={"sensor_cfg": SceneEntityCfg("contact_forces", body_names=".*ankle_link"),
+                                   "asset_cfg": SceneEntityCfg("robot", body_names=".*ankle_link")})
+    r.joint_deviation_hip = RewTerm(func=mdp.joint_deviation_l1, weight=-0.2,
+                                    params={"asset_cfg": SceneEntityCfg("robot", joint_names=[".*_hip_yaw", ".*_hip_roll"])})
+    r.joint_deviation_arms = RewTerm(func=mdp.joint_deviation_l1, weight=-0.2,
+                                     params={"asset_cfg": SceneEntityCfg("robot", joint_names=[".*_shoulder_.*", ".*_elbow"])})
+    r.joint_deviation_torso = RewTerm(func=mdp.joint_deviation_l1, weight=-0.1,
+                                      params={"asset_cfg": SceneEntityCfg("robot", joint_names="torso")})
+    cfg.scene.height_scanner.prim_path = "{ENV_REGEX_NS}/Robot/torso_link"
+    cfg.events.push_robot = None
+    cfg.events.add_base_mass = None
+    cfg.events.reset_robot_joints.params["position_range"] = (1.0, 1.0)
+    cfg.events.base_external_force_torque.params["asset_cfg"].body_names = [".*torso_link"]
+    cfg.events.reset_base.params = {"pose_range": {"x": (-0.5, 0.5), "y": (-0.5, 0.5), "yaw": (-3.14, 3.14)},
+                                    "velocity_range": {k: (0.0, 0.0) for k in ("x", "y", "z", "roll", "pitch", "yaw")}}
+    r.undesired_contacts = None
+    r.flat_orientation_l2.weight = -1.0
+    r.dof_torques_l2.weight = 0.0
+    r.action_rate_l2.weight = -0.005
+    r.dof_acc_l2.weight = -1.25e-7
+    cfg.commands.base_velocity.ranges.lin_vel_x = (0.0, 1.0)
+    cfg.commands.base_velocity.ranges.lin_vel_y = (0.0, 0.0)
+    cfg.commands.base_velocity.ranges.ang_vel_z = (-1.0, 1.0)
+    cfg.terminations.base_contact.params["sensor_cfg"].body_names = ".*torso_link"
+    return cfg

@@ -1,0 +1,59 @@
+/* Oracle for raycast_mesh (test infrastructure only; see oracle/__init__.py).
+ *
+ * Contract restated from the reference wrapper -- LAB/utils/warp/kernels.py:13-75 (`raycast_mesh_kernel`:
+ * `wp.mesh_query_ray(mesh, start, dir, max_dist, t, u, v, sign, n, f)`; on hit `ray_hits = start + t * dir`)
+ * and LAB/utils/warp/ops.py:70 (`ray_hits` pre-filled with inf).  The ray query itself lives in warp-lang
+ * (third-party, version unpinned, absent here) => PARITY UNPINNED; this is a brute-force closest-hit
+ * Moeller-Trumbore over ALL triangles in fp64, two-sided, inclusive edges, 0 < t <= max_dist.
+ *
+ * Build: gcc -O3 -fopenmp -shared -fPIC (oracle/build.py).  Threads: OpenMP over rays.
+ */
+#include <math.h>
+#include <stdint.h>
+
+/* vertices [nv,3] f32, faces [nf,3] i32, starts/dirs [n,3] f32 -> hits [n,3] f32 (inf on miss), t_out [n] f64
+ * (inf on miss), face_out [n] i32 (-1 on miss). */
+void oracle_raycast_mesh(const float* V, const int32_t* F, int64_t nf, const float* starts, const float* dirs,
+                         int64_t n, double max_dist, float* hits, double* t_out, int32_t* face_out) {
+#pragma omp parallel for schedule(dynamic, 64)
+  for (int64_t i = 0; i < n; ++i) {
+    const double ox = starts[3 * i], oy = starts[3 * i + 1], oz = starts[3 * i + 2];
+    const double dx = dirs[3 * i], dy = dirs[3 * i + 1], dz = dirs[3 * i + 2];
+    const int vertical = (dx == 0.0 && dy == 0.0);
+    double best = INFINITY;
+    int32_t bf = -1;
+    for (int64_t f = 0; f < nf; ++f) {
+      const float* a = V + 3 * (int64_t)F[3 * f];
+      const float* b = V + 3 * (int64_t)F[3 * f + 1];
+      const float* c = V + 3 * (int64_t)F[3 * f + 2];
+      if (vertical) { /* exact reject: the ray's xy is outside the triangle's xy bounding box */
+        double x0 = fmin(a[0], fmin(b[0], c[0])), x1 = fmax(a[0], fmax(b[0], c[0]));
+        double y0 = fmin(a[1], fmin(b[1], c[1])), y1 = fmax(a[1], fmax(b[1], c[1]));
+        if (ox < x0 || ox > x1 || oy < y0 || oy > y1) continue;
+      }
+      const double e1x = (double)b[0] - a[0], e1y = (double)b[1] - a[1], e1z = (double)b[2] - a[2];
+      const double e2x = (double)c[0] - a[0], e2y = (double)c[1] - a[1], e2z = (double)c[2] - a[2];
+      const double px = dy * e2z - dz * e2y, py = dz * e2x - dx * e2z, pz = dx * e2y - dy * e2x;
+      const double det = e1x * px + e1y * py + e1z * pz;
+      if (fabs(det) < 1e-12) continue;
+      const double inv = 1.0 / det;
+      const double tx = ox - a[0], ty = oy - a[1], tz = oz - a[2];
+      const double u = (tx * px + ty * py + tz * pz) * inv;
+      if (u < 0.0 || u > 1.0) continue;
+      const double qx = ty * e1z - tz * e1y, qy = tz * e1x - tx * e1z, qz = tx * e1y - ty * e1x;
+      const double v = (dx * qx + dy * qy + dz * qz) * inv;
+      if (v < 0.0 || u + v > 1.0) continue;
+      const double t = (e2x * qx + e2y * qy + e2z * qz) * inv;
+      if (t > 0.0 && t <= max_dist && t < best) { best = t; bf = (int32_t)f; }
+    }
+    if (bf >= 0) {
+      hits[3 * i] = (float)(ox + best * dx);
+      hits[3 * i + 1] = (float)(oy + best * dy);
+      hits[3 * i + 2] = (float)(oz + best * dz);
+    } else {
+      hits[3 * i] = hits[3 * i + 1] = hits[3 * i + 2] = INFINITY;
+    }
+    if (t_out) t_out[i] = best;
+    if (face_out) face_out[i] = bf;
+  }
+}
