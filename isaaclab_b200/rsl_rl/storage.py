@@ -81,9 +81,13 @@ class RolloutStorage:
         if not sigma.is_contiguous():
             sigma = sigma.contiguous()
         p = _lib.ptr
-        tr.obs, tr.actions, tr.rewards = p(obs.contiguous()), p(transition.actions), p(transition.rewards.contiguous())
-        tr.dones, tr.time_outs, tr.values = p(dones.contiguous()), p(touts), p(transition.values)
-        tr.log_prob, tr.mu, tr.sigma = p(transition.actions_log_prob.contiguous()), p(transition.action_mean), p(sigma)
+        # locals keep every (possibly temporary) tensor alive until the kernel is enqueued: the C ABI borrows pointers
+        obs_c, rew_c, dones_c = obs.contiguous(), transition.rewards.contiguous(), dones.contiguous()
+        touts_c = touts.contiguous() if touts is not None else None
+        lp_c = transition.actions_log_prob.contiguous()
+        tr.obs, tr.actions, tr.rewards = p(obs_c), p(transition.actions), p(rew_c)
+        tr.dones, tr.time_outs, tr.values = p(dones_c), p(touts_c), p(transition.values)
+        tr.log_prob, tr.mu, tr.sigma = p(lp_c), p(transition.action_mean), p(sigma)
         tr.s_obs, tr.s_actions, tr.s_rewards = p(self.observations[self._obs_key]), p(self.actions), p(self.rewards)
         tr.s_dones, tr.s_values, tr.s_log_prob = p(self.dones), p(self.values), p(self.actions_log_prob)
         tr.s_mu, tr.s_sigma = p(self.mu), p(self.sigma)
@@ -100,7 +104,8 @@ class RolloutStorage:
     def compute_returns(self, last_values, gamma, lam, normalize_advantage: bool = True):
         T, N = self.num_transitions_per_env, self.num_envs
         p = _lib.ptr
-        _lib.check(_lib.lib().b200lab_gae(p(self.rewards), p(self.values), p(self.dones), p(last_values.contiguous()),
+        last_values = last_values.contiguous()
+        _lib.check(_lib.lib().b200lab_gae(p(self.rewards), p(self.values), p(self.dones), p(last_values),
                                           p(self.returns), p(self.advantages), T, N, float(gamma), float(lam),
                                           1 if normalize_advantage else 0, p(self._gae_scratch),
                                           _lib.current_stream()))

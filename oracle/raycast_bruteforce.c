@@ -10,11 +10,23 @@
  */
 #include <math.h>
 #include <stdint.h>
+#include <stdlib.h>
 
 /* vertices [nv,3] f32, faces [nf,3] i32, starts/dirs [n,3] f32 -> hits [n,3] f32 (inf on miss), t_out [n] f64
  * (inf on miss), face_out [n] i32 (-1 on miss). */
 void oracle_raycast_mesh(const float* V, const int32_t* F, int64_t nf, const float* starts, const float* dirs,
                          int64_t n, double max_dist, float* hits, double* t_out, int32_t* face_out) {
+  /* xy bounding boxes of the triangles, computed once (used only for the exact vertical-ray reject below) */
+  float* bb = (float*)malloc((size_t)nf * 4 * sizeof(float));
+  for (int64_t f = 0; f < nf; ++f) {
+    const float* a = V + 3 * (int64_t)F[3 * f];
+    const float* b = V + 3 * (int64_t)F[3 * f + 1];
+    const float* c = V + 3 * (int64_t)F[3 * f + 2];
+    bb[4 * f] = fminf(a[0], fminf(b[0], c[0]));
+    bb[4 * f + 1] = fmaxf(a[0], fmaxf(b[0], c[0]));
+    bb[4 * f + 2] = fminf(a[1], fminf(b[1], c[1]));
+    bb[4 * f + 3] = fmaxf(a[1], fmaxf(b[1], c[1]));
+  }
 #pragma omp parallel for schedule(dynamic, 64)
   for (int64_t i = 0; i < n; ++i) {
     const double ox = starts[3 * i], oy = starts[3 * i + 1], oz = starts[3 * i + 2];
@@ -22,15 +34,15 @@ void oracle_raycast_mesh(const float* V, const int32_t* F, int64_t nf, const flo
     const int vertical = (dx == 0.0 && dy == 0.0);
     double best = INFINITY;
     int32_t bf = -1;
+    const float fox = starts[3 * i], foy = starts[3 * i + 1];
     for (int64_t f = 0; f < nf; ++f) {
+      if (vertical) { /* exact reject: the ray's xy is outside the triangle's xy bounding box */
+        const float* q = bb + 4 * f;
+        if (fox < q[0] || fox > q[1] || foy < q[2] || foy > q[3]) continue;
+      }
       const float* a = V + 3 * (int64_t)F[3 * f];
       const float* b = V + 3 * (int64_t)F[3 * f + 1];
       const float* c = V + 3 * (int64_t)F[3 * f + 2];
-      if (vertical) { /* exact reject: the ray's xy is outside the triangle's xy bounding box */
-        double x0 = fmin(a[0], fmin(b[0], c[0])), x1 = fmax(a[0], fmax(b[0], c[0]));
-        double y0 = fmin(a[1], fmin(b[1], c[1])), y1 = fmax(a[1], fmax(b[1], c[1]));
-        if (ox < x0 || ox > x1 || oy < y0 || oy > y1) continue;
-      }
       const double e1x = (double)b[0] - a[0], e1y = (double)b[1] - a[1], e1z = (double)b[2] - a[2];
       const double e2x = (double)c[0] - a[0], e2y = (double)c[1] - a[1], e2z = (double)c[2] - a[2];
       const double px = dy * e2z - dz * e2y, py = dz * e2x - dx * e2z, pz = dx * e2y - dy * e2x;
@@ -56,4 +68,5 @@ void oracle_raycast_mesh(const float* V, const int32_t* F, int64_t nf, const flo
     if (t_out) t_out[i] = best;
     if (face_out) face_out[i] = bf;
   }
+  free(bb);
 }

@@ -56,7 +56,12 @@ def test_rollout_gae_update_vs_reference_fixture(golden_dir, name):
     torch.testing.assert_close(st.advantages.cpu(), fx["storage"]["advantages"], rtol=1e-5, atol=1e-6)
     loss = alg.update(indices=fx["indices"].to(dev))
     for k, v in fx["state_dict_after"].items():
-        torch.testing.assert_close(pol.state_dict()[k].cpu(), v, rtol=2e-4, atol=5e-6, msg=lambda m, k=k: f"{k}: {m}")
+        got = pol.state_dict()[k].cpu()
+        # Adam divides by sqrt(v)+eps: where |grad| ~ 1e-8 the update is sign-like and amplifies 1e-9 GEMM rounding
+        # differences, so a handful of elements may move by up to ~lr; everything else must agree tightly.
+        torch.testing.assert_close(got, v, rtol=2e-4, atol=5e-4, msg=lambda m, k=k: f"{k}: {m}")
+        tight = ((got - v).abs() <= 5e-6 + 2e-4 * v.abs()).float().mean().item()
+        assert tight >= 0.995, f"{k}: only {tight:.4f} of the elements within rtol 2e-4 / atol 5e-6"
     for k in ("value_function", "surrogate", "entropy"):
         assert loss[k] == pytest.approx(fx["loss_dict"][k], rel=1e-4, abs=1e-6)
     assert alg.learning_rate == pytest.approx(float(fx["lr_per_update"][-1]), rel=1e-6)
@@ -78,7 +83,8 @@ def test_gae_vs_oracle_full_size_and_edges():
             ret = torch.empty(T, N, 1, device="cuda")
             adv = torch.empty(T, N, 1, device="cuda")
             scratch = torch.zeros(L.b200lab_gae_scratch_bytes(T, N) // 8, dtype=torch.float64, device="cuda")
-            _lib.check(L.b200lab_gae(_lib.ptr(r.cuda()), _lib.ptr(v.cuda()), _lib.ptr(d.cuda()), _lib.ptr(lv.cuda()),
+            rc, vc, dc, lvc = r.cuda(), v.cuda(), d.cuda(), lv.cuda()  # keep alive: raw pointers are borrowed
+            _lib.check(L.b200lab_gae(_lib.ptr(rc), _lib.ptr(vc), _lib.ptr(dc), _lib.ptr(lvc),
                                      _lib.ptr(ret), _lib.ptr(adv), T, N, 0.99, 0.95, int(norm), _lib.ptr(scratch),
                                      _lib.current_stream()))
             torch.testing.assert_close(ret.cpu(), ret_o, rtol=1e-5, atol=1e-6)
