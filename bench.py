@@ -1,0 +1,328 @@
+"""bench.py -- headline benchmark of the B200-native non-physics step (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+
+One "step" = one ManagerBasedRLEnv.step worth of non-physics work over the env shard of one GPU:
+process_action + S x (actuator model, contact/joint-acc update) + terminations/rewards/resets/commands/events +
+observations incl. the 187-ray height scan -- on synthetic ArticulationData-shaped state (PhysX is out of scope).
+Workload at N=1: BASELINE.json configs[2] "Isaac-Velocity-Rough-Anymal-C-v0, 4096 envs/GPU" (the config the metric is
+quoted on).  Prints ONE JSON line (rank 0).  See DESIGN.md "Measurement" for every field.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+TASK = "Isaac-Velocity-Rough-Anymal-C-v0"
+ENVS_PER_GPU = 4096
+K_SLABS = 32
+METRIC = "non-physics env-steps/s (Anymal-C rough, 4096 envs/GPU)"
+UNIT = "env-steps/s"
+
+
+def algorithmic_bytes(spec):
+    """Compulsory HBM bytes per env per launch of each kernel (split per kernel)."""
+    J, A, B, S = spec["J"], spec["A"], spec["B"], spec["decimation"]
+    F = 4
+    Tr = len(spec["rewards"])
+    state = 0
+    for a in spec["actuators"]:
+        Jg = len(a["joint_ids"])
+        if a["kind"] == "lstm":
+            state += 16 * a["lstm"]["num_layers"] * Jg * a["lstm"]["hidden"]
+        elif a["kind"] == "mlp":
+            state += 16 * Jg + 8 * (max(a["mlp"]["input_idx"]) + 1) * Jg
+    obs = sum(_term_dim(spec, t) for t in spec["observations"]["terms"])
+    per = {
+        "process_action": 24 * A,
+        "substep_pre": 20 * J + state,
+        "substep_post": (12 * B + 12 * B + 32 * B if spec.get("contact") else 0) + 8 * J,
+        "post_step": 52 + 12 * J + 4 * J + 8 * A + 36 * B + 8 * F + 8 + 30 + 4 + 2 + 12 * Tr + 16 + 8 + 4 * J,
+        "compute_obs": (28 if spec.get("raycaster") else 0) + 4 * obs,
+    }
+    per_step = per["process_action"] * 0 + S * (per["substep_pre"] + per["substep_post"]) + per["post_step"] + per["compute_obs"]
+    return per, per_step
+
+
+def _term_dim(spec, t):
+    from isaaclab_b200.envs.term_dims import term_dim
+    return term_dim(spec, t)
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.stop_flag = index, [], False
+        self.proc = None
+
+    def run(self):
+        q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits", "-i",
+                                          str(self.index), "-lms", "100"], stdout=subprocess.PIPE, text=True)
+            for line in self.proc.stdout:
+                self.samples.append([x.strip() for x in line.split(",")])
+                if self.stop_flag:
+                    break
+        except Exception:
+            pass
+
+    def finish(self):
+        self.stop_flag = True
+        if self.proc:
+            self.proc.terminate()
+        sm = sorted(int(s[0]) for s in self.samples if s and s[0].isdigit())
+        mx = [int(s[1]) for s in self.samples if len(s) > 1 and s[1].isdigit()]
+        reasons = set()
+        for s in self.samples:
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), s[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def build_workload(device, seed):
+    from isaaclab_b200 import terrains
+    from isaaclab_b200.envs.compile import compile_env_cfg
+    from isaaclab_b200.sim.synthetic import generate_slabs, initial_env_state
+    from isaaclab_b200.tasks import TASKS
+    cfg = TASKS[TASK]()
+    terrain = terrains.TerrainGenerator(cfg.scene.terrain.terrain_generator)
+    spec = compile_env_cfg(cfg, num_envs=ENVS_PER_GPU, terrain=terrain, seed=seed)
+    slabs = generate_slabs(spec, K_SLABS, seed=1234 + 3 + seed)
+    init = initial_env_state(spec, seed=7 + seed)
+    return cfg, spec, slabs, init
+
+
+def time_kernels(fus, sim, action, steps):
+    """Per-kernel CUDA-event durations over `steps` env steps on the launching stream (ms per launch, averaged)."""
+    names = ["process_action", "substep_pre", "substep_post", "post_step", "compute_obs"]
+    ev = {n: [] for n in names}
+
+    def rec(name, fn, *a):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        fn(*a)
+        e1.record()
+        ev[name].append((e0, e1))
+
+    k0 = 1000
+    for k in range(steps):
+        prev = sim.views(k0 + k)[-1]
+        views = sim.views(k0 + k + 1)
+        rec("process_action", fus.process_action, action)
+        p = prev
+        for v in views:
+            rec("substep_pre", fus.substep_pre, p)
+            rec("substep_post", fus.substep_post, v)
+            p = v
+        rec("post_step", fus.post_step, p)
+        rec("compute_obs", fus.compute_obs, p)
+        fus.step_counter += 1
+    torch.cuda.synchronize()
+    return {n: sum(a.elapsed_time(b) for a, b in ev[n]) / max(1, len(ev[n])) for n in names}
+
+
+def run_ours(args):
+    import torch.distributed as dist
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    from isaaclab_b200 import _lib
+    from isaaclab_b200.envs.fused_env import FusedEnv
+    from isaaclab_b200.envs.manager_based_rl_env import HostReplaySim, ManagerBasedRLEnv
+    from isaaclab_b200.sim.synthetic import SyntheticSim
+    from tests.mdp_common import init_fused_state
+
+    cfg, spec, slabs, init = build_workload(dev, seed=rank)
+    N = spec["N"]
+    L = _lib.lib()
+    # ---- device-resident arm: inputs in HBM, K slabs (> L2) cycled
+    sim = SyntheticSim(spec, K=K_SLABS, device=dev, slabs=slabs)
+    fus = FusedEnv(spec, device=dev, seed=rank)
+    init_fused_state(fus, init)
+    g = torch.Generator().manual_seed(11 + rank)
+    action = torch.randn(N, spec["A"], generator=g).to(dev)
+
+    def one_step(k):
+        fus.step(action, sim.views(k + 1), sim.views(k)[-1])
+
+    for k in range(args.warmup):
+        one_step(k)
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    sampler = ClockSampler(local)
+    sampler.start()
+    torch.cuda.synchronize()
+    launches0 = L.b200lab_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for k in range(args.steps):
+        one_step(args.warmup + k)
+    e1.record()
+    torch.cuda.synchronize()
+    launches = L.b200lab_launch_count() - launches0
+    ms = e0.elapsed_time(e1)
+    t = torch.tensor([ms], device=dev)
+    if world > 1:
+        dist.barrier()
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    clocks = sampler.finish()
+    value = world * N * args.steps / (ms * 1e-3)
+    # ---- per-kernel timing + roofline of the dominant kernel
+    per_kernel_ms = time_kernels(fus, sim, action, max(8, min(args.steps, 64)))
+    bytes_per, bytes_step = algorithmic_bytes(spec)
+    S = spec["decimation"]
+    share = {n: per_kernel_ms[n] * (S if n.startswith("substep") else 1) for n in per_kernel_ms}
+    dom = max(share, key=share.get)
+    peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else {}
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    achieved = bytes_per[dom] * N / (per_kernel_ms[dom] * 1e-3) / 1e9
+    roof = {"bound": "hbm", "kernel": dom, "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
+            "frac": round(achieved / peak, 4), "traffic": None, "peak_source": "measured" if peaks else "fallback",
+            "algorithmic_bytes_per_launch": bytes_per[dom] * N,
+            "per_kernel_us": {n: round(v * 1e3, 2) for n, v in per_kernel_ms.items()},
+            "step_algorithmic_bytes": bytes_step * N,
+            "step_frac": round(bytes_step * N / (ms / args.steps * 1e-3) / 1e9 / peak, 4)}
+    # ---- end-to-end arm: public API with HOST buffers (pinned), H2D of each step's simulator state + action and
+    # D2H of obs / reward / dones inside the timed region
+    host_sim = HostReplaySim(spec, slabs, device=dev)
+    env = ManagerBasedRLEnv(cfg, sim=host_sim, device=dev, spec=spec, seed=rank)
+    init_fused_state(env.fused, init)
+    act_host = torch.randn(N, spec["A"], generator=g).pin_memory()
+    obs_host = torch.empty(N, env.fused.obs_dim).pin_memory()
+    rew_host = torch.empty(N).pin_memory()
+    done_host = torch.empty(N, dtype=torch.uint8).pin_memory()
+
+    def e2e_step():
+        obs, rew, term, trunc, _ = env.step(act_host)
+        obs_host.copy_(obs[env._group], non_blocking=True)
+        rew_host.copy_(rew, non_blocking=True)
+        done_host.copy_(env.fused.reset_buf, non_blocking=True)
+        torch.cuda.current_stream().synchronize()  # the caller consumes the result before the next step
+
+    for _ in range(args.warmup):
+        e2e_step()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    t0 = time.perf_counter()
+    e0.record()
+    for _ in range(args.steps):
+        e2e_step()
+    e1.record()
+    torch.cuda.synchronize()
+    ms_e2e = torch.tensor([e0.elapsed_time(e1)], device=dev)
+    if world > 1:
+        dist.all_reduce(ms_e2e, op=dist.ReduceOp.MAX)
+    ms_e2e = float(ms_e2e.item())
+    h2d = host_sim.h2d_bytes_per_step + act_host.numel() * 4
+    d2h = obs_host.numel() * 4 + rew_host.numel() * 4 + done_host.numel()
+    e2e = {"value": round(world * N * args.steps / (ms_e2e * 1e-3), 1), "unit": UNIT, "h2d_bytes_per_step": h2d,
+           "d2h_bytes_per_step": d2h, "ms_per_step": round(ms_e2e / args.steps, 4)}
+    out = {"metric": METRIC, "value": round(value, 1), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+           "warmup": args.warmup, "ms_per_step": round(ms / args.steps, 5), "higher_is_better": True, "scaling": "weak",
+           "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+           "config": {"workload": f"{TASK} non-physics step, {N} envs/GPU, 187-ray height scan, ActuatorNetLSTM, "
+                                  f"decimation {S}", "envs_per_gpu": N, "l2_policy": f"{K_SLABS} state slabs "
+                                  f"({sim.bytes() >> 20} MiB > 126 MiB L2) cycled", "parallelism": f"env-shard x{world}"},
+           "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roof}
+    if rank == 0:
+        if world == 1 and not args.no_cpu_baseline:
+            out["cpu_baseline"] = cpu_baseline(spec, slabs, init, budget_s=15.0)
+        print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def cpu_baseline(spec, slabs, init, budget_s=15.0, threads=None, max_steps=10**9):
+    """The oracle port of the reference torch path (device='cpu') on the host cores, bounded sample of the same
+    workload: full-size env steps (4096 envs) until `budget_s` is used (at least 2)."""
+    import copy
+
+    from oracle.mdp_env import OracleEnv, n_u_reset, n_u_step, obs_dim
+    from tests.mdp_common import init_oracle_state, slab_views_cpu
+    threads = threads or os.cpu_count()
+    torch.set_num_threads(threads)
+    os.environ.setdefault("OMP_NUM_THREADS", str(threads))
+    env = OracleEnv(copy.deepcopy(spec))
+    env.mesh.enable_grid(0.25)
+    init_oracle_state(env, init)
+    N = spec["N"]
+    g = torch.Generator().manual_seed(5)
+    action = torch.randn(N, spec["A"], generator=g)
+    n_done, t_used = 0, 0.0
+    prev = slab_views_cpu(slabs, 0)[-1]
+    k = 0
+    while (t_used < budget_s or n_done < 2) and k < slabs["root_state_w"].shape[0] - 1 and n_done < max_steps:
+        views = slab_views_cpu(slabs, k + 1)
+        u = (torch.rand(N, n_u_reset(spec), generator=g), torch.rand(N, n_u_step(spec), generator=g),
+             torch.rand(N, obs_dim(spec), generator=g))
+        t0 = time.perf_counter()
+        env.step(action, views, *u, prev)
+        dt = time.perf_counter() - t0
+        prev = views[-1]
+        k += 1
+        if k == 1:
+            continue  # warm-up step (thread pools, lazy init)
+        n_done += 1
+        t_used += dt
+    v = N * n_done / t_used
+    return {"value": round(v, 1), "unit": UNIT, "cores": threads, "kind": "port",
+            "sample": f"{n_done} full env steps of {N} envs (after 1 warm-up), torch CPU oracle + grid-prefiltered fp64 ray cast",
+            "ms_per_step": round(t_used / n_done * 1e3, 2)}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cfg, spec, slabs, init = build_workload("cpu", seed=0)
+    # each "step" of this arm = one full env step on the CPU; bounded so W+K steps end within minutes
+    cb = cpu_baseline(spec, slabs, init, budget_s=20.0, max_steps=max(2, args.steps))
+    out = {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": int(os.environ.get("WORLD_SIZE", "1")),
+           "steps": args.steps, "warmup": args.warmup, "ms_per_step": cb["ms_per_step"], "higher_is_better": True,
+           "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+           "config": {"workload": f"{TASK} non-physics step, {spec['N']} envs, reference torch path restated (oracle port) on CPU"},
+           "cpu_baseline": cb, "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(out))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", default="ours")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3)
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,199 @@
+"""`ManagerBasedRLEnv`: the reference's env interface (LAB/envs/manager_based_rl_env.py:153-242) over the fused kernels.
+
+`step(action) -> (obs_dict, reward, terminated, time_outs, extras)` keeps the reference's order of operations and
+its buffer-ownership convention (the same tensor objects are returned every step).  The simulator is a pluggable
+backend that exposes PhysX-view-shaped tensors (`SimBackend`): `SyntheticSim` / `HostReplaySim` replay generated or
+recorded ArticulationData; a live Isaac Sim would implement `physics_step` with `sim.step()` between the two
+sub-step kernels.
+
+Managers are thin views of the fused state with the reference's attribute surface (`reward_manager.compute`,
+`termination_manager.terminated`, `command_manager.get_command`, `action_manager.action`, ...).
+"""
+from __future__ import annotations
+
+import torch
+
+from .. import _lib
+from .compile import compile_env_cfg
+from .fused_env import FusedEnv, SimView
+
+
+class HostReplaySim:
+    """Simulator state arriving from the HOST every step (pinned memory -> one device staging set)."""
+
+    def __init__(self, spec, slabs_cpu: dict, device="cuda"):
+        self.spec, self.S = spec, spec["decimation"]
+        self.K = slabs_cpu["root_state_w"].shape[0]
+        self.host = {k: v.contiguous().pin_memory() for k, v in slabs_cpu.items()}
+        self.stage = {k: torch.empty_like(v[0], device=device) for k, v in slabs_cpu.items()}
+        st = self.stage
+        has_contact = spec.get("contact") is not None
+        self._views = [SimView(st["root_state_w"], st["joint_pos"][s], st["joint_vel"][s],
+                               st["net_forces_w"][s] if has_contact else None, st["body_lin_vel_w"]) for s in range(self.S)]
+        self.h2d_bytes_per_step = sum(v[0].numel() * v[0].element_size() for v in self.host.values())
+        self.k = -1
+
+    def advance(self):
+        """Bring the next env step's S physics states to the device (async H2D on the current stream)."""
+        self.k = (self.k + 1) % self.K
+        for name, dst in self.stage.items():
+            dst.copy_(self.host[name][self.k], non_blocking=True)
+        return self._views
+
+    def last_view(self):
+        return self._views[-1]
+
+
+class DeviceReplaySim:
+    """Device-resident slabs (SyntheticSim) behind the same `advance()` interface."""
+
+    def __init__(self, synthetic):
+        self.syn = synthetic
+        self.k = 0
+        self.h2d_bytes_per_step = 0
+
+    def advance(self):
+        self.k += 1
+        return self.syn.views(self.k)
+
+    def last_view(self):
+        return self.syn.views(self.k)[-1]
+
+
+class _ManagerView:
+    def __init__(self, env):
+        self._env = env
+
+
+class RewardManager(_ManagerView):
+    @property
+    def active_terms(self):
+        return [t["name"] for t in self._env.spec["rewards"]]
+
+    def compute(self, dt=None):
+        return self._env.reward_buf
+
+
+class TerminationManager(_ManagerView):
+    @property
+    def active_terms(self):
+        return [t["name"] for t in self._env.spec["terminations"]]
+
+    @property
+    def terminated(self):
+        return self._env.reset_terminated
+
+    @property
+    def time_outs(self):
+        return self._env.reset_time_outs
+
+    @property
+    def dones(self):
+        return self._env.reset_buf
+
+    def get_term(self, name):
+        return self._env.fused.term_dones[self.active_terms.index(name)].bool()
+
+
+class CommandManager(_ManagerView):
+    def get_command(self, name):
+        if self._env.spec.get("command") is None or name != self._env.spec["command"]["name"]:
+            raise ValueError(f"Command term '{name}' not found")
+        return self._env.fused.cmd_vel_b
+
+
+class ActionManager(_ManagerView):
+    @property
+    def action(self):
+        return self._env.fused.action
+
+    @property
+    def prev_action(self):
+        return self._env.fused.prev_action
+
+    @property
+    def total_action_dim(self):
+        return self._env.fused.A
+
+
+class ObservationManager(_ManagerView):
+    @property
+    def group_obs_dim(self):
+        return {self._env.spec["observations"]["group"]: (self._env.fused.obs_dim,)}
+
+    def compute(self):
+        return {self._env.spec["observations"]["group"]: self._env.fused.obs_buf}
+
+
+class ManagerBasedRLEnv:
+    def __init__(self, cfg, sim=None, device="cuda", num_envs=None, terrain=None, seed=0, spec=None, use_cuda_graph=False):
+        self.cfg = cfg
+        self.device = torch.device(device)
+        self.spec = spec if spec is not None else compile_env_cfg(cfg, num_envs=num_envs, terrain=terrain, seed=seed)
+        self.num_envs = self.spec["N"]
+        self.fused = FusedEnv(self.spec, device=device, seed=seed)
+        if sim is None:
+            from ..sim.synthetic import SyntheticSim
+            sim = DeviceReplaySim(SyntheticSim(self.spec, K=8, seed=1234 + seed, device=device))
+        self.sim = sim
+        self.step_dt, self.physics_dt = self.spec["step_dt"], self.spec["physics_dt"]
+        self.max_episode_length, self.max_episode_length_s = self.spec["max_episode_length"], self.spec["max_episode_length_s"]
+        self.reward_manager, self.termination_manager = RewardManager(self), TerminationManager(self)
+        self.command_manager, self.action_manager = CommandManager(self), ActionManager(self)
+        self.observation_manager = ObservationManager(self)
+        self.extras = {}
+        self.common_step_counter = 0
+        self._group = self.spec["observations"]["group"]
+        f = self.fused
+        self.reward_buf = f.reward_buf
+        self.reset_terminated, self.reset_time_outs, self.reset_buf = f.terminated.view(torch.bool), f.truncated.view(torch.bool), f.reset_buf.view(torch.bool)
+        self.obs_buf = {self._group: f.obs_buf}
+        self._action_dev = torch.zeros(self.num_envs, f.A, device=device)
+        self._prev_view = self.sim.last_view() if hasattr(self.sim, "last_view") else None
+
+    @property
+    def episode_length_buf(self):
+        return self.fused.episode_length_buf
+
+    @episode_length_buf.setter
+    def episode_length_buf(self, v):
+        self.fused.episode_length_buf.copy_(v)
+
+    @property
+    def num_actions(self):
+        return self.fused.A
+
+    def reset(self, seed=None):
+        """Initial observations (ManagerBasedEnv.reset, LAB/envs/manager_based_env.py:264): obs of the current state."""
+        self.fused.compute_obs(self.sim.last_view())
+        return self.obs_buf, self.extras
+
+    def step(self, action: torch.Tensor):
+        f = self.fused
+        if action.device != self.device:  # host action: staged through a fixed device buffer
+            self._action_dev.copy_(action, non_blocking=True)
+            action = self._action_dev
+        prev = self.sim.last_view()
+        views = self.sim.advance()
+        f.step(action, views, prev)
+        self.common_step_counter += 1
+        return self.obs_buf, self.reward_buf, self.reset_terminated, self.reset_time_outs, self.extras
+
+    def episode_log(self):
+        """extras["log"] aggregates (manager_based_rl_env.py:365-389) accumulated on the device since the last call;
+        ONE device->host read instead of the reference's per-reset `.item()` syncs."""
+        f, s = self.fused, self.spec
+        acc = f.log_accum.cpu()
+        f.log_accum.zero_()
+        n = float(acc[0])
+        log = {}
+        if n > 0:
+            nr, nt = len(s["rewards"]), len(s["terminations"])
+            for i, t in enumerate(s["rewards"]):
+                log["Episode_Reward/" + t["name"]] = float(acc[1 + i]) / n / s["max_episode_length_s"]
+            for i, t in enumerate(s["terminations"]):
+                log["Episode_Termination/" + t["name"]] = float(acc[1 + nr + i])
+            if s.get("command"):
+                log["Metrics/base_velocity/error_vel_xy"] = float(acc[1 + nr + nt]) / n
+                log["Metrics/base_velocity/error_vel_yaw"] = float(acc[2 + nr + nt]) / n
+        return log

@@ -22,6 +22,13 @@ def _clib():
         _lib.oracle_raycast_mesh.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_void_p,
                                              ctypes.c_void_p, ctypes.c_int64, ctypes.c_double, ctypes.c_void_p,
                                              ctypes.c_void_p, ctypes.c_void_p]
+        _lib.oracle_grid_build.restype = ctypes.c_void_p
+        _lib.oracle_grid_build.argtypes = [ctypes.c_void_p, ctypes.c_int64, ctypes.c_void_p, ctypes.c_int64, ctypes.c_float]
+        _lib.oracle_grid_free.argtypes = [ctypes.c_void_p]
+        _lib.oracle_raycast_mesh_grid.restype = None
+        _lib.oracle_raycast_mesh_grid.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64,
+                                                  ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_double,
+                                                  ctypes.c_void_p]
     return _lib
 
 
@@ -58,7 +65,21 @@ class Mesh:
         self.V = np.ascontiguousarray(np.asarray(vertices, dtype=np.float32).reshape(-1, 3))
         self.F = np.ascontiguousarray(np.asarray(faces, dtype=np.int32).reshape(-1, 3))
 
+    def enable_grid(self, cell=0.25):
+        """CPU-BASELINE mode (bench.py only): xy cell pre-filter for vertical rays; same results as brute force."""
+        lib = _clib()
+        if lib is None:
+            raise RuntimeError("oracle C library not built (python oracle/build.py)")
+        self._grid = lib.oracle_grid_build(self.V.ctypes.data, self.V.shape[0], self.F.ctypes.data, self.F.shape[0], cell)
+
     def raycast(self, starts, dirs, max_dist=1e6, return_t=False):
+        if getattr(self, "_grid", None) and not return_t:
+            s = np.ascontiguousarray(starts.detach().cpu().numpy().astype(np.float32))
+            d = np.ascontiguousarray(dirs.detach().cpu().numpy().astype(np.float32))
+            hits = np.empty((s.shape[0], 3), dtype=np.float32)
+            _clib().oracle_raycast_mesh_grid(self._grid, self.V.ctypes.data, self.F.ctypes.data, self.F.shape[0],
+                                             s.ctypes.data, d.ctypes.data, s.shape[0], float(max_dist), hits.ctypes.data)
+            return torch.from_numpy(hits)
         """starts/dirs: torch [n,3] f32 -> hits torch [n,3] f32 (inf on miss)."""
         s = np.ascontiguousarray(starts.detach().cpu().numpy().astype(np.float32))
         d = np.ascontiguousarray(dirs.detach().cpu().numpy().astype(np.float32))
