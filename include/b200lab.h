@@ -364,6 +364,14 @@ int b200lab_process_action(void* env, const float* action_in, void* stream);
 int b200lab_substep_pre(void* env, const B200LabSimView* sim, void* stream);
 int b200lab_substep_post(void* env, const B200LabSimView* sim, void* stream);
 
+/* REPLAY fast path: the whole physics loop of one env step in one launch, when the simulator states of all
+ * `num_substeps` (= decimation, <= 8) physics steps are already known (recorded Isaac Sim run or synthetic state):
+ * process_action, then for s = 0..S-1 { substep_pre on state s-1 (`prev` for s = 0); substep_post on `views[s]` }.
+ * Identical arithmetic and ordering to the three calls above; per-thread state stays in registers across sub-steps.
+ * `views` is a HOST array of num_substeps views. */
+int b200lab_decimation_fused(void* env, const float* action_in, const B200LabSimView* prev,
+                             const B200LabSimView* views, int32_t num_substeps, void* stream);
+
 /* Everything in ManagerBasedRLEnv.step after the physics loop and before the observations
  * (manager_based_rl_env.py:198-236): episode_length_buf += 1, TerminationManager.compute,
  * RewardManager.compute, _reset_idx for the envs in reset_buf (masked, no host sync),

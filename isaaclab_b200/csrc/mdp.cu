@@ -12,6 +12,7 @@
 // actuator nets use explicit fmaf().
 #include <cstdlib>
 #include <cstring>
+#include <vector>
 
 #include "common.cuh"
 #include "raycast.cuh"
@@ -21,6 +22,9 @@ namespace b200lab {
 struct EnvHandle {
   B200LabEnvState host;
   B200LabEnvState* dev;
+  float* derived;      // [N, kDerived] per-env derived state for compute_obs
+  uint8_t* col_term;   // [obs_dim] obs column -> term index
+  int16_t* col_src;    // [obs_dim] obs column -> joint index (joint terms) or index inside the term
 };
 
 typedef B200LabEnvState Env;
@@ -168,11 +172,8 @@ __device__ __forceinline__ float mlp_forward32(const float* __restrict__ w, cons
   return a[0];
 }
 
-__global__ void __launch_bounds__(kActBlock)
-substep_pre_kernel(const Env* __restrict__ e, Sim sim) {
-  extern __shared__ float s_w[];
-  const int J = e->J, N = e->N;
-  // stage the weights of the (single) net-based group, if any, in shared memory
+// stage the weights of the (single) net-based actuator group, if any, in shared memory (block-cooperative)
+__device__ __forceinline__ void stage_net_weights(const Env* __restrict__ e, float* s_w) {
   int net_group = -1;
   for (int g = 0; g < e->num_act_groups; ++g)
     if (e->act[g].kind == B200LAB_ACT_NET_LSTM || e->act[g].kind == B200LAB_ACT_NET_MLP) net_group = g;
@@ -187,25 +188,17 @@ substep_pre_kernel(const Env* __restrict__ e, Sim sim) {
       for (int l = 0; l < g.mlp_layers; ++l) nw += g.mlp_dims[l] * g.mlp_dims[l + 1] + g.mlp_dims[l + 1];
     }
     for (int i = threadIdx.x; i < nw; i += blockDim.x) s_w[i] = g.net_weights[i];
-    __syncthreads();
   }
-  int64_t gid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (gid >= (int64_t)N * J) return;
-  int n = (int)(gid / J), j = (int)(gid % J);
-  // action_manager.apply_action -> set_joint_{position,effort}_target (joint_actions.py:158-160, 223-225)
-  int col = e->joint_action_col[j];
-  if (col >= 0) {
-    float p = e->processed_actions[(int64_t)n * e->A + col];
-    if (e->action_kind == 0) e->joint_pos_target[gid] = p;
-    else e->joint_effort_target[gid] = p;
-  }
-  int gi = e->joint_group[j];
-  if (gi < 0) return;
-  const B200LabActuatorGroup& g = e->act[gi];
-  float q = sim.joint_pos[gid], qd = sim.joint_vel[gid];
-  float q_t = e->joint_pos_target[gid], qd_t = e->joint_vel_target[gid], ff = e->joint_effort_target[gid];
+  __syncthreads();
+}
+
+// One actuator evaluation for joint j of env n (Articulation._apply_actuator_model, articulation.py:1432-1469).
+// q, qd: joint state BEFORE the physics step; q_t, qd_t, ff: the joint targets.
+__device__ __forceinline__ void actuator_eval(const Env* __restrict__ e, const float* s_w, int n, int j, float q, float qd,
+                                              float q_t, float qd_t, float ff, float& computed, float& applied) {
+  const int N = e->N;
+  const B200LabActuatorGroup& g = e->act[e->joint_group[j]];
   float err_p = q_t - q, err_v = qd_t - qd;
-  float computed, applied;
   float elim = g.effort_limit[j];
   if (g.kind == B200LAB_ACT_IMPLICIT || g.kind == B200LAB_ACT_IDEAL_PD || g.kind == B200LAB_ACT_DC_MOTOR) {
     computed = (g.stiffness[j] * err_p + g.damping[j] * err_v) + ff;  // actuator_pd.py:136 / :190
@@ -244,6 +237,29 @@ substep_pre_kernel(const Env* __restrict__ e, Sim sim) {
     computed = mlp_forward32(s_w, g, in) * g.mlp_torque_scale;
     applied = dc_motor_clip(computed, qd, g.saturation_effort, g.velocity_limit[j], elim);
   }
+}
+
+__global__ void __launch_bounds__(kActBlock)
+substep_pre_kernel(const Env* __restrict__ e, Sim sim) {
+  extern __shared__ float s_w[];
+  const int J = e->J, N = e->N;
+  stage_net_weights(e, s_w);
+  int64_t gid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (gid >= (int64_t)N * J) return;
+  int n = (int)(gid / J), j = (int)(gid % J);
+  // action_manager.apply_action -> set_joint_{position,effort}_target (joint_actions.py:158-160, 223-225)
+  int col = e->joint_action_col[j];
+  if (col >= 0) {
+    float p = e->processed_actions[(int64_t)n * e->A + col];
+    if (e->action_kind == 0) e->joint_pos_target[gid] = p;
+    else e->joint_effort_target[gid] = p;
+  }
+  int gi = e->joint_group[j];
+  if (gi < 0) return;
+  const B200LabActuatorGroup& g = e->act[gi];
+  float q_t = e->joint_pos_target[gid], qd_t = e->joint_vel_target[gid], ff = e->joint_effort_target[gid];
+  float computed, applied;
+  actuator_eval(e, s_w, n, j, sim.joint_pos[gid], sim.joint_vel[gid], q_t, qd_t, ff, computed, applied);
   e->computed_torque[gid] = computed;
   e->applied_torque[gid] = applied;
   if (g.kind == B200LAB_ACT_IMPLICIT) {
@@ -327,6 +343,147 @@ substep_post_kernel(const Env* __restrict__ e, Sim sim, int W, int envs_per_bloc
       e->rc_timestamp[n] = rts;
       if ((rts - e->rc_timestamp_last_update[n]) + 1e-6f >= e->rc_update_period) e->rc_is_outdated[n] = 1;
     }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// decimation_fused: the whole physics loop of one env step in ONE launch, for replayed simulator state
+// (recorded or synthetic: all S post-physics states are known up front, manager_based_rl_env.py:173-196):
+//   process_action, then for s in 0..S-1: apply_action + actuator model on state s-1, scene.update on state s.
+// Same arithmetic and the same per-sub-step order as process_action / substep_pre / substep_post above; what changes
+// is data movement: action processing, joint targets, previous joint velocity, contact history and air-time state stay
+// in registers across the S sub-steps and are written once.  Thread layout as substep_post (W = max(J,B) lanes / env).
+// ------------------------------------------------------------------------------------------------
+constexpr int kMaxDecimation = 8;
+struct SimViews {
+  Sim prev;                  // state before the first physics step
+  Sim v[kMaxDecimation];     // state after each physics step
+  int S;
+};
+
+__global__ void __launch_bounds__(kPostBlock)
+decimation_fused_kernel(const Env* __restrict__ e, const float* __restrict__ action_in, SimViews sv, int W,
+                        int envs_per_block) {
+  extern __shared__ float s_w[];
+  stage_net_weights(e, s_w);
+  const int N = e->N, J = e->J, B = e->B, A = e->A, S = sv.S;
+  int el = threadIdx.x / W, i = threadIdx.x % W;
+  int n = blockIdx.x * envs_per_block + el;
+  if (blockIdx.x == 0 && threadIdx.x == 0 && e->step_counter_dev) *e->step_counter_dev += 1;
+  if (el >= envs_per_block || n >= N) return;
+  const float dt = e->physics_dt;
+  // ---- joint role
+  if (i < J) {
+    const int j = i;
+    const int64_t o = (int64_t)n * J + j;
+    // ActionManager.process_action + JointAction.process_actions for the action column driving this joint
+    int col = e->joint_action_col[j];
+    if (col >= 0) {
+      int64_t ao = (int64_t)n * A + col;
+      float x = action_in[ao];
+      e->prev_action[ao] = e->action[ao];
+      e->action[ao] = x;
+      e->raw_actions[ao] = x;
+      float p = x * e->action_scale[col] + e->action_offset[col];
+      if (e->action_clip) p = fminf(fmaxf(p, e->action_clip[2 * col]), e->action_clip[2 * col + 1]);
+      e->processed_actions[ao] = p;
+      if (e->action_kind == 0) e->joint_pos_target[o] = p; else e->joint_effort_target[o] = p;
+    }
+    const int gi = e->joint_group[j];
+    float q_t = e->joint_pos_target[o], qd_t = e->joint_vel_target[o], ff = e->joint_effort_target[o];
+    float prev_qd = e->prev_joint_vel[o], acc = e->joint_acc[o];
+    float computed = 0.f, applied = 0.f;
+    float q = sv.prev.joint_pos[o], qd = sv.prev.joint_vel[o];
+    for (int s = 0; s < S; ++s) {
+      if (gi >= 0) actuator_eval(e, s_w, n, j, q, qd, q_t, qd_t, ff, computed, applied);
+      q = sv.v[s].joint_pos[o];
+      qd = sv.v[s].joint_vel[o];
+      acc = (qd - prev_qd) / dt;  // ArticulationData.update (articulation_data.py:547-556)
+      prev_qd = qd;
+    }
+    e->prev_joint_vel[o] = prev_qd;
+    e->joint_acc[o] = acc;
+    if (gi >= 0 && S > 0) {
+      e->computed_torque[o] = computed;
+      e->applied_torque[o] = applied;
+      if (e->act[gi].kind == B200LAB_ACT_IMPLICIT) { e->joint_pos_target_sim[o] = q_t; e->joint_effort_target_sim[o] = ff; }
+      else e->joint_effort_target_sim[o] = applied;
+    }
+  }
+  // ---- body role: ContactSensor (contact_sensor.py:320-379) under SensorBase.update (sensor_base.py:197-205)
+  if (e->cs_timestamp && i < B) {
+    const int64_t ob = (int64_t)n * B + i;
+    const int Hh = e->hist;
+    float ts = e->cs_timestamp[n], tl = e->cs_timestamp_last_update[n];
+    bool outdated = e->cs_is_outdated[n] != 0;
+    const bool track = e->cs_current_air_time != nullptr;
+    float la = 0.f, ca = 0.f, lc = 0.f, cc = 0.f;
+    if (track) { la = e->cs_last_air_time[ob]; ca = e->cs_current_air_time[ob]; lc = e->cs_last_contact_time[ob]; cc = e->cs_current_contact_time[ob]; }
+    float* hp = e->cs_forces_hist + ((int64_t)n * Hh * B + i) * 3;
+    float hx[4], hy[4], hz[4];  // history depth <= 4 kept in registers
+    const bool hreg = Hh <= 4;
+    if (hreg)
+      for (int k = 0; k < Hh; ++k) { hx[k] = hp[(int64_t)k * B * 3]; hy[k] = hp[(int64_t)k * B * 3 + 1]; hz[k] = hp[(int64_t)k * B * 3 + 2]; }
+    float fx = e->cs_net_forces_w[ob * 3], fy = e->cs_net_forces_w[ob * 3 + 1], fz = e->cs_net_forces_w[ob * 3 + 2];
+    for (int s = 0; s < S; ++s) {
+      ts = ts + dt;
+      outdated = outdated || ((ts - tl) + 1e-6f >= e->cs_update_period);
+      if (outdated) {
+        fx = fy = fz = 0.f;
+        const float* nf = sv.v[s].net_forces_w;
+        if (nf) { fx = nf[ob * 3]; fy = nf[ob * 3 + 1]; fz = nf[ob * 3 + 2]; }
+        if (hreg) {
+#pragma unroll
+          for (int k = 3; k > 0; --k) if (k < Hh) { hx[k] = hx[k - 1]; hy[k] = hy[k - 1]; hz[k] = hz[k - 1]; }
+          hx[0] = fx; hy[0] = fy; hz[0] = fz;
+        } else {
+          for (int k = Hh - 1; k > 0; --k) {
+            float* dst = hp + (int64_t)k * B * 3; const float* src = hp + (int64_t)(k - 1) * B * 3;
+            dst[0] = src[0]; dst[1] = src[1]; dst[2] = src[2];
+          }
+          hp[0] = fx; hp[1] = fy; hp[2] = fz;
+        }
+        if (track) {
+          float elapsed = ts - tl;
+          bool is_contact = norm3(fx, fy, fz) > e->cs_force_threshold;
+          bool first_contact = (ca > 0.f) && is_contact;
+          bool first_detached = (cc > 0.f) && !is_contact;
+          if (first_contact) la = ca + elapsed;
+          ca = !is_contact ? ca + elapsed : 0.f;
+          if (first_detached) lc = cc + elapsed;
+          cc = is_contact ? cc + elapsed : 0.f;
+        }
+        tl = ts;
+        outdated = false;
+      }
+    }
+    e->cs_net_forces_w[ob * 3] = fx; e->cs_net_forces_w[ob * 3 + 1] = fy; e->cs_net_forces_w[ob * 3 + 2] = fz;
+    if (hreg)
+      for (int k = 0; k < Hh; ++k) { hp[(int64_t)k * B * 3] = hx[k]; hp[(int64_t)k * B * 3 + 1] = hy[k]; hp[(int64_t)k * B * 3 + 2] = hz[k]; }
+    if (track) { e->cs_last_air_time[ob] = la; e->cs_current_air_time[ob] = ca; e->cs_last_contact_time[ob] = lc; e->cs_current_contact_time[ob] = cc; }
+  }
+  // ---- env scalars (one lane).  The sensor timestamps are re-derived with the same fp32 recurrence; they are
+  // written after every lane of this env has read them (the block barrier below).
+  float cts = 0.f, ctl = 0.f; bool cout_ = false; float rts = 0.f; bool rc_mark = false;
+  if (i == 0) {
+    if (e->cs_timestamp) {
+      cts = e->cs_timestamp[n]; ctl = e->cs_timestamp_last_update[n]; cout_ = e->cs_is_outdated[n] != 0;
+      for (int s = 0; s < S; ++s) {
+        cts = cts + dt;
+        cout_ = cout_ || ((cts - ctl) + 1e-6f >= e->cs_update_period);
+        if (cout_) { ctl = cts; cout_ = false; }
+      }
+    }
+    if (e->rc_timestamp) {
+      rts = e->rc_timestamp[n];
+      float rtl = e->rc_timestamp_last_update[n];
+      for (int s = 0; s < S; ++s) { rts = rts + dt; if ((rts - rtl) + 1e-6f >= e->rc_update_period) rc_mark = true; }
+    }
+  }
+  __syncthreads();
+  if (i == 0) {
+    if (e->cs_timestamp) { e->cs_timestamp[n] = cts; e->cs_timestamp_last_update[n] = ctl; e->cs_is_outdated[n] = cout_ ? 1 : 0; }
+    if (e->rc_timestamp) { e->rc_timestamp[n] = rts; if (rc_mark) e->rc_is_outdated[n] = 1; }
   }
 }
 
@@ -775,109 +932,114 @@ post_step_kernel(const Env* __restrict__ e, Sim sim, int64_t step) {
   }
 }
 
+// Per-env derived quantities shared by all obs columns / rays of an env: [N, kDerived] floats in a scratch buffer owned
+// by the env handle, filled by derive_obs_kernel (one thread per env) right before compute_obs_kernel.
+//   0-2 lin_b, 3-5 ang_b, 6-8 grav_b, 9-11 sensor pos (root pos + drift), 12-15 sensor-frame quaternion (yaw-only when
+//   attach_yaw_only), 16 root z, 17 ray-caster outdated flag
+constexpr int kDerived = 20;
+
+__global__ void __launch_bounds__(128)
+derive_obs_kernel(const Env* __restrict__ e, Sim sim, float* __restrict__ derived) {
+  int n = blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= e->N) return;
+  const float* rs = sim.root_state_w + (int64_t)n * 13;
+  float* o = derived + (int64_t)n * kDerived;
+  f4 q{rs[3], rs[4], rs[5], rs[6]};
+  f3 lb = quat_rotate_inverse(q, f3{rs[7], rs[8], rs[9]});       // articulation_data.py:604-610
+  f3 ab = quat_rotate_inverse(q, f3{rs[10], rs[11], rs[12]});    // :613-619
+  f3 gb = quat_rotate_inverse(q, f3{0.f, 0.f, -1.f});            // :513-515
+  o[0] = lb.x; o[1] = lb.y; o[2] = lb.z;
+  o[3] = ab.x; o[4] = ab.y; o[5] = ab.z;
+  o[6] = gb.x; o[7] = gb.y; o[8] = gb.z;
+  o[16] = rs[2];
+  float rc_out = 0.f;
+  if (e->rc_is_outdated) {
+    rc_out = e->rc_is_outdated[n] != 0 ? 1.f : 0.f;
+    if (rc_out != 0.f) {
+      // RayCaster._update_buffers_impl (ray_caster.py:225-241): pose (+ drift) of the outdated sensors
+      float px = rs[0] + e->rc_drift[n * 3], py = rs[1] + e->rc_drift[n * 3 + 1], pz = rs[2] + e->rc_drift[n * 3 + 2];
+      o[9] = px; o[10] = py; o[11] = pz;
+      f4 qy = e->rc_attach_yaw_only ? yaw_quat(q) : q;
+      o[12] = qy.w; o[13] = qy.x; o[14] = qy.y; o[15] = qy.z;
+      e->rc_pos_w[n * 3] = px; e->rc_pos_w[n * 3 + 1] = py; e->rc_pos_w[n * 3 + 2] = pz;
+      e->rc_quat_w[n * 4] = q.w; e->rc_quat_w[n * 4 + 1] = q.x; e->rc_quat_w[n * 4 + 2] = q.y; e->rc_quat_w[n * 4 + 3] = q.z;
+      e->rc_timestamp_last_update[n] = e->rc_timestamp[n];   // sensor_base.py:294-296
+      e->rc_is_outdated[n] = 0;
+    } else {
+      o[11] = e->rc_pos_w[n * 3 + 2];
+    }
+  }
+  o[17] = rc_out;
+}
+
 // ------------------------------------------------------------------------------------------------
 // compute_obs: ObservationManager.compute_group (observation_manager.py:260-335) for one concatenated group.
-// Thread per (env, obs column); a block owns whole envs so the ray-caster bookkeeping of an env
-// (sensor_base.py:287-296) can be updated after all of its rays were cast.
+// One thread per (env, obs column), no barriers: the term of a column comes from the per-column table built at
+// env_create, the env-level quantities from the derived scratch.  Height-scan columns cast their ray.
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
-compute_obs_kernel(const Env* __restrict__ e, Sim sim, int64_t step, int Dpad, int envs_per_block) {
+compute_obs_kernel(const Env* __restrict__ e, Sim sim, int64_t step, const uint8_t* __restrict__ col_term,
+                   const int16_t* __restrict__ col_src, const float* __restrict__ derived) {
   const int N = e->N, J = e->J, D = e->obs_dim;
   if (e->step_counter_dev) step = *e->step_counter_dev;
-  int el = threadIdx.x / Dpad, k = threadIdx.x % Dpad;
-  int n = blockIdx.x * envs_per_block + el;
-  bool env_ok = el < envs_per_block && n < N;
-  bool rc_out = false;
-  if (env_ok && e->rc_is_outdated) rc_out = e->rc_is_outdated[n] != 0;
-  __syncthreads();
-  if (env_ok && k < D) {
-    // locate the term owning column k
-    int t = 0, off = 0;
-    while (t < e->num_obs - 1 && k >= off + e->obs[t].dim) { off += e->obs[t].dim; ++t; }
-    const B200LabTerm& tm = e->obs[t];
-    int li = k - off;
-    const float* rs = sim.root_state_w + (int64_t)n * 13;
-    float v = 0.f;
-    switch (tm.op) {
-      case B200LAB_OBS_BASE_LIN_VEL:
-      case B200LAB_OBS_BASE_ANG_VEL:
-      case B200LAB_OBS_PROJECTED_GRAVITY: {
-        f4 q{rs[3], rs[4], rs[5], rs[6]};
-        f3 w = tm.op == B200LAB_OBS_BASE_LIN_VEL ? f3{rs[7], rs[8], rs[9]}
-               : tm.op == B200LAB_OBS_BASE_ANG_VEL ? f3{rs[10], rs[11], rs[12]} : f3{0.f, 0.f, -1.f};
-        f3 r = quat_rotate_inverse(q, w);
-        v = li == 0 ? r.x : li == 1 ? r.y : r.z;
-        break;
+  int64_t gid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (gid >= (int64_t)N * D) return;
+  const int n = (int)(gid / D), k = (int)(gid % D);
+  const float* o = derived + (int64_t)n * kDerived;
+  const B200LabTerm& tm = e->obs[col_term[k]];
+  const int li = col_src[k];
+  float v = 0.f;
+  switch (tm.op) {
+    case B200LAB_OBS_BASE_LIN_VEL: v = o[li]; break;
+    case B200LAB_OBS_BASE_ANG_VEL: v = o[3 + li]; break;
+    case B200LAB_OBS_PROJECTED_GRAVITY: v = o[6 + li]; break;
+    case B200LAB_OBS_GENERATED_COMMANDS: v = e->cmd_vel_b[(int64_t)n * 3 + li]; break;
+    case B200LAB_OBS_JOINT_POS_REL: v = sim.joint_pos[(int64_t)n * J + li] - e->default_joint_pos[li]; break;
+    case B200LAB_OBS_JOINT_VEL_REL: v = sim.joint_vel[(int64_t)n * J + li] - e->default_joint_vel[li]; break;
+    case B200LAB_OBS_JOINT_POS: v = sim.joint_pos[(int64_t)n * J + li]; break;
+    case B200LAB_OBS_JOINT_VEL: v = sim.joint_vel[(int64_t)n * J + li]; break;
+    case B200LAB_OBS_LAST_ACTION: v = e->action[(int64_t)n * e->A + li]; break;
+    case B200LAB_OBS_BASE_POS_Z: v = o[16]; break;
+    case B200LAB_OBS_EXTERNAL: v = e->ext_values[((int64_t)tm.i0 + li) * N + n]; break;
+    case B200LAB_OBS_HEIGHT_SCAN: {
+      float pz = o[11], hz;
+      if (o[17] != 0.f) {
+        // ray start = quat_apply(_yaw)(q, local start) + pos ; directions unrotated when attach_yaw_only (ray_caster.py:243-253)
+        f4 qy{o[12], o[13], o[14], o[15]};
+        f3 ls{__ldg(e->rc_ray_starts + li * 3), __ldg(e->rc_ray_starts + li * 3 + 1), __ldg(e->rc_ray_starts + li * 3 + 2)};
+        f3 ld{__ldg(e->rc_ray_dirs + li * 3), __ldg(e->rc_ray_dirs + li * 3 + 1), __ldg(e->rc_ray_dirs + li * 3 + 2)};
+        f3 st = quat_apply(qy, ls);
+        f3 dr = e->rc_attach_yaw_only ? ld : quat_apply(qy, ld);
+        st.x += o[9]; st.y += o[10]; st.z += o[11];
+        float tt; int face;
+        f3 hit{INFINITY, INFINITY, INFINITY};
+        const MeshAccel* mesh = reinterpret_cast<const MeshAccel*>(e->rc_mesh);
+        if (mesh && raycast_mesh_dev(*mesh, st, dr, e->rc_max_distance, tt, face))
+          hit = {st.x + tt * dr.x, st.y + tt * dr.y, st.z + tt * dr.z};
+        float* hp = e->rc_ray_hits_w + ((int64_t)n * e->R + li) * 3;
+        hp[0] = hit.x; hp[1] = hit.y; hp[2] = hit.z;
+        hz = hit.z;
+      } else {
+        hz = e->rc_ray_hits_w[((int64_t)n * e->R + li) * 3 + 2];
       }
-      case B200LAB_OBS_GENERATED_COMMANDS: v = e->cmd_vel_b[(int64_t)n * 3 + li]; break;
-      case B200LAB_OBS_JOINT_POS_REL:
-      case B200LAB_OBS_JOINT_VEL_REL:
-      case B200LAB_OBS_JOINT_POS:
-      case B200LAB_OBS_JOINT_VEL: {
-        // li-th selected joint of the mask
-        uint64_t m = tm.joint_mask;
-        for (int s = 0; s < li; ++s) m &= m - 1;
-        int j = __ffsll((long long)m) - 1;
-        int64_t o = (int64_t)n * J + j;
-        if (tm.op == B200LAB_OBS_JOINT_POS_REL) v = sim.joint_pos[o] - e->default_joint_pos[j];
-        else if (tm.op == B200LAB_OBS_JOINT_VEL_REL) v = sim.joint_vel[o] - e->default_joint_vel[j];
-        else if (tm.op == B200LAB_OBS_JOINT_POS) v = sim.joint_pos[o];
-        else v = sim.joint_vel[o];
-        break;
-      }
-      case B200LAB_OBS_LAST_ACTION: v = e->action[(int64_t)n * e->A + li]; break;
-      case B200LAB_OBS_BASE_POS_Z: v = rs[2]; break;
-      case B200LAB_OBS_EXTERNAL: v = e->ext_values[((int64_t)tm.i0 + li) * N + n]; break;
-      case B200LAB_OBS_HEIGHT_SCAN: {
-        float pz, hz;
-        if (rc_out) {
-          // RayCaster._update_buffers_impl (ray_caster.py:220-260)
-          f3 pos{rs[0] + e->rc_drift[n * 3], rs[1] + e->rc_drift[n * 3 + 1], rs[2] + e->rc_drift[n * 3 + 2]};
-          f4 q{rs[3], rs[4], rs[5], rs[6]};
-          f3 ls{e->rc_ray_starts[li * 3], e->rc_ray_starts[li * 3 + 1], e->rc_ray_starts[li * 3 + 2]};
-          f3 ld{e->rc_ray_dirs[li * 3], e->rc_ray_dirs[li * 3 + 1], e->rc_ray_dirs[li * 3 + 2]};
-          f3 st, dr;
-          if (e->rc_attach_yaw_only) { st = quat_apply(yaw_quat(q), ls); dr = ld; }
-          else { st = quat_apply(q, ls); dr = quat_apply(q, ld); }
-          st.x += pos.x; st.y += pos.y; st.z += pos.z;
-          float tt; int face;
-          f3 hit{INFINITY, INFINITY, INFINITY};
-          const MeshAccel* mesh = reinterpret_cast<const MeshAccel*>(e->rc_mesh);
-          if (mesh && raycast_mesh_dev(*mesh, st, dr, e->rc_max_distance, tt, face))
-            hit = {st.x + tt * dr.x, st.y + tt * dr.y, st.z + tt * dr.z};
-          float* hp = e->rc_ray_hits_w + ((int64_t)n * e->R + li) * 3;
-          hp[0] = hit.x; hp[1] = hit.y; hp[2] = hit.z;
-          pz = pos.z; hz = hit.z;
-        } else {
-          pz = e->rc_pos_w[n * 3 + 2];
-          hz = e->rc_ray_hits_w[((int64_t)n * e->R + li) * 3 + 2];
-        }
-        v = (pz - hz) - tm.p[0];  // observations.py:173
-        break;
-      }
+      v = (pz - hz) - tm.p[0];  // observations.py:173
+      break;
     }
-    // noise -> clip -> scale (observation_manager.py:313-318)
-    if (e->obs_enable_corruption && tm.noise_kind != B200LAB_NOISE_NONE) {
-      if (tm.noise_kind == B200LAB_NOISE_CONSTANT_ADD) v = v + tm.noise_lo;
-      else {
-        float u = e->u_obs ? e->u_obs[(int64_t)n * D + k] : philox_uniform(e->seed, step, 3u, (uint32_t)n, (uint32_t)k);
-        float nz = u * tm.noise_span + tm.noise_lo;
-        if (tm.noise_kind == B200LAB_NOISE_UNIFORM_ADD) v = (v + u * tm.noise_span) + tm.noise_lo;  // noise_model.py:64
-        else if (tm.noise_kind == B200LAB_NOISE_UNIFORM_SCALE) v = v * nz;
-        else v = nz;
-      }
+  }
+  // noise -> clip -> scale (observation_manager.py:313-318)
+  if (e->obs_enable_corruption && tm.noise_kind != B200LAB_NOISE_NONE) {
+    if (tm.noise_kind == B200LAB_NOISE_CONSTANT_ADD) v = v + tm.noise_lo;
+    else {
+      float u = e->u_obs ? e->u_obs[(int64_t)n * D + k] : philox_uniform(e->seed, step, 3u, (uint32_t)n, (uint32_t)k);
+      float nz = u * tm.noise_span + tm.noise_lo;
+      if (tm.noise_kind == B200LAB_NOISE_UNIFORM_ADD) v = (v + u * tm.noise_span) + tm.noise_lo;  // noise_model.py:64
+      else if (tm.noise_kind == B200LAB_NOISE_UNIFORM_SCALE) v = v * nz;
+      else v = nz;
     }
-    if (tm.clip_on) v = fminf(fmaxf(v, tm.clip_lo), tm.clip_hi);
-    if (tm.scale_on) v = v * tm.scale;
-    e->obs_buf[(int64_t)n * D + k] = v;
   }
-  if (env_ok && k == 0 && rc_out) {
-    const float* rs = sim.root_state_w + (int64_t)n * 13;
-    for (int a = 0; a < 3; ++a) e->rc_pos_w[n * 3 + a] = rs[a] + e->rc_drift[n * 3 + a];
-    for (int a = 0; a < 4; ++a) e->rc_quat_w[n * 4 + a] = rs[3 + a];
-    e->rc_timestamp_last_update[n] = e->rc_timestamp[n];
-    e->rc_is_outdated[n] = 0;
-  }
+  if (tm.clip_on) v = fminf(fmaxf(v, tm.clip_lo), tm.clip_hi);
+  if (tm.scale_on) v = v * tm.scale;
+  e->obs_buf[gid] = v;
 }
 
 static int launch_geometry(int width, int* wpad, int* epb) {
@@ -891,6 +1053,41 @@ static int launch_geometry(int width, int* wpad, int* epb) {
 
 using namespace b200lab;
 
+// obs column -> (term, source index) tables, rebuilt whenever the descriptor changes
+static int upload_obs_tables(EnvHandle* h) {
+  const B200LabEnvState& s = h->host;
+  int D = s.obs_dim;
+  if (D <= 0) return B200LAB_OK;
+  std::vector<uint8_t> ct(D);
+  std::vector<int16_t> cs(D);
+  int k = 0;
+  for (int t = 0; t < s.num_obs; ++t) {
+    const B200LabTerm& tm = s.obs[t];
+    bool joint = tm.op == B200LAB_OBS_JOINT_POS_REL || tm.op == B200LAB_OBS_JOINT_VEL_REL ||
+                 tm.op == B200LAB_OBS_JOINT_POS || tm.op == B200LAB_OBS_JOINT_VEL;
+    uint64_t m = tm.joint_mask;
+    for (int li = 0; li < tm.dim; ++li) {
+      if (k >= D) { set_error("observation term dims exceed obs_dim"); return B200LAB_ERR_ARG; }
+      ct[k] = (uint8_t)t;
+      if (joint) {
+        if (!m) { set_error("observation term %d: dim exceeds the number of selected joints", t); return B200LAB_ERR_ARG; }
+        int j = __builtin_ctzll(m);
+        m &= m - 1;
+        cs[k] = (int16_t)j;
+      } else cs[k] = (int16_t)li;
+      ++k;
+    }
+  }
+  if (k != D) { set_error("observation term dims (%d) do not add up to obs_dim (%d)", k, D); return B200LAB_ERR_ARG; }
+  if (h->col_term) { cudaFree(h->col_term); cudaFree(h->col_src); h->col_term = nullptr; h->col_src = nullptr; }
+  cudaError_t err = cudaMalloc((void**)&h->col_term, D);
+  if (err == cudaSuccess) err = cudaMalloc((void**)&h->col_src, D * sizeof(int16_t));
+  if (err == cudaSuccess) err = cudaMemcpy(h->col_term, ct.data(), D, cudaMemcpyHostToDevice);
+  if (err == cudaSuccess) err = cudaMemcpy(h->col_src, cs.data(), D * sizeof(int16_t), cudaMemcpyHostToDevice);
+  if (err != cudaSuccess) { set_error("obs tables: %s", cudaGetErrorString(err)); return B200LAB_ERR_CUDA; }
+  return B200LAB_OK;
+}
+
 extern "C" {
 
 void* b200lab_env_create(const B200LabEnvState* st) {
@@ -899,10 +1096,15 @@ void* b200lab_env_create(const B200LabEnvState* st) {
   if (!h) return nullptr;
   h->host = *st;
   h->dev = nullptr;
+  h->col_term = nullptr;
+  h->col_src = nullptr;
+  h->derived = nullptr;
   cudaError_t err = cudaMalloc((void**)&h->dev, sizeof(B200LabEnvState));
+  if (err == cudaSuccess) err = cudaMalloc((void**)&h->derived, (size_t)st->N * 20 * sizeof(float));
   if (err == cudaSuccess) err = cudaMemcpy(h->dev, st, sizeof(B200LabEnvState), cudaMemcpyHostToDevice);
+  if (err == cudaSuccess && upload_obs_tables(h) != 0) err = cudaErrorUnknown;
   if (err != cudaSuccess) {
-    set_error("b200lab_env_create: %s", cudaGetErrorString(err));
+    if (err != cudaErrorUnknown) set_error("b200lab_env_create: %s", cudaGetErrorString(err));
     if (h->dev) cudaFree(h->dev);
     free(h);
     return nullptr;
@@ -916,13 +1118,16 @@ int b200lab_env_update(void* env, const B200LabEnvState* st) {
   h->host = *st;
   cudaError_t err = cudaMemcpy(h->dev, st, sizeof(B200LabEnvState), cudaMemcpyHostToDevice);
   if (err != cudaSuccess) { set_error("b200lab_env_update: %s", cudaGetErrorString(err)); return B200LAB_ERR_CUDA; }
-  return B200LAB_OK;
+  return upload_obs_tables(h);
 }
 
 void b200lab_env_destroy(void* env) {
   if (!env) return;
   EnvHandle* h = (EnvHandle*)env;
   if (h->dev) cudaFree(h->dev);
+  if (h->col_term) cudaFree(h->col_term);
+  if (h->col_src) cudaFree(h->col_src);
+  if (h->derived) cudaFree(h->derived);
   free(h);
 }
 
@@ -935,10 +1140,7 @@ int b200lab_process_action(void* env, const float* action_in, void* stream) {
   return check_launch("process_action");
 }
 
-int b200lab_substep_pre(void* env, const B200LabSimView* sim, void* stream) {
-  B200LAB_CHECK_ARG(env && sim && sim->joint_pos && sim->joint_vel, "null argument");
-  EnvHandle* h = (EnvHandle*)env;
-  const B200LabEnvState& s = h->host;
+static int net_smem_bytes(const B200LabEnvState& s, size_t* out) {
   size_t smem = 0;
   int nets = 0;
   for (int g = 0; g < s.num_act_groups; ++g) {
@@ -961,6 +1163,17 @@ int b200lab_substep_pre(void* env, const B200LabSimView* sim, void* stream) {
   }
   B200LAB_CHECK_ARG(nets <= 1, "at most one network-based actuator group per articulation is supported");
   B200LAB_CHECK_ARG(smem <= kMaxNetFloats * sizeof(float), "actuator network too large for shared-memory staging");
+  *out = smem;
+  return B200LAB_OK;
+}
+
+int b200lab_substep_pre(void* env, const B200LabSimView* sim, void* stream) {
+  B200LAB_CHECK_ARG(env && sim && sim->joint_pos && sim->joint_vel, "null argument");
+  EnvHandle* h = (EnvHandle*)env;
+  const B200LabEnvState& s = h->host;
+  size_t smem = 0;
+  int rc = net_smem_bytes(s, &smem);
+  if (rc) return rc;
   int64_t total = (int64_t)s.N * s.J;
   substep_pre_kernel<<<(unsigned)ceil_div(total, kActBlock), kActBlock, smem, (cudaStream_t)stream>>>(h->dev, *sim);
   count_launch();
@@ -979,6 +1192,31 @@ int b200lab_substep_post(void* env, const B200LabSimView* sim, void* stream) {
   return check_launch("substep_post");
 }
 
+int b200lab_decimation_fused(void* env, const float* action_in, const B200LabSimView* prev,
+                             const B200LabSimView* views, int32_t num_substeps, void* stream) {
+  B200LAB_CHECK_ARG(env && action_in && prev && views, "null argument");
+  B200LAB_CHECK_ARG(num_substeps >= 1 && num_substeps <= kMaxDecimation, "decimation must be in 1..8");
+  EnvHandle* h = (EnvHandle*)env;
+  const B200LabEnvState& s = h->host;
+  size_t smem = 0;
+  int rc = net_smem_bytes(s, &smem);
+  if (rc) return rc;
+  SimViews sv;
+  sv.prev = *prev;
+  sv.S = num_substeps;
+  for (int k = 0; k < num_substeps; ++k) {
+    B200LAB_CHECK_ARG(views[k].joint_pos && views[k].joint_vel, "null simulator view");
+    sv.v[k] = views[k];
+  }
+  for (int k = num_substeps; k < kMaxDecimation; ++k) sv.v[k] = views[num_substeps - 1];
+  int W, epb;
+  int width = s.J > s.B ? s.J : s.B;
+  B200LAB_CHECK_ARG(launch_geometry(width, &W, &epb) == 0, "max(J,B) must be <= 256");
+  decimation_fused_kernel<<<(unsigned)ceil_div(s.N, epb), kPostBlock, smem, (cudaStream_t)stream>>>(h->dev, action_in, sv, W, epb);
+  count_launch();
+  return check_launch("decimation_fused");
+}
+
 int b200lab_post_step(void* env, const B200LabSimView* sim, int64_t step_counter, void* stream) {
   B200LAB_CHECK_ARG(env && sim && sim->root_state_w && sim->joint_pos && sim->joint_vel, "null argument");
   EnvHandle* h = (EnvHandle*)env;
@@ -993,9 +1231,12 @@ int b200lab_compute_obs(void* env, const B200LabSimView* sim, int64_t step_count
   B200LAB_CHECK_ARG(env && sim && sim->root_state_w, "null argument");
   EnvHandle* h = (EnvHandle*)env;
   const B200LabEnvState& s = h->host;
-  int W, epb;
-  B200LAB_CHECK_ARG(launch_geometry(s.obs_dim, &W, &epb) == 0, "obs_dim must be <= 256 (one block per env)");
-  compute_obs_kernel<<<(unsigned)ceil_div(s.N, epb), 256, 0, (cudaStream_t)stream>>>(h->dev, *sim, step_counter, W, epb);
+  cudaStream_t st_ = (cudaStream_t)stream;
+  derive_obs_kernel<<<(unsigned)ceil_div(s.N, 128), 128, 0, st_>>>(h->dev, *sim, h->derived);
+  count_launch();
+  int64_t total = (int64_t)s.N * s.obs_dim;
+  compute_obs_kernel<<<(unsigned)ceil_div(total, 256), 256, 0, st_>>>(h->dev, *sim, step_counter, h->col_term, h->col_src,
+                                                                      h->derived);
   count_launch();
   return check_launch("compute_obs");
 }

@@ -14,6 +14,7 @@ struct MeshHandle {
   MeshAccel host;      // device pointers inside
   MeshAccel* dev;      // device copy of the descriptor
   int64_t bytes;
+  int64_t entries;
   void* buffers[4];
 };
 
@@ -57,7 +58,6 @@ extern "C" {
 
 void* b200lab_mesh_create(const float* V, int64_t nv, const int32_t* F, int64_t nf, float cell_size) {
   if (!V || !F || nv <= 0 || nf <= 0) { set_error("b200lab_mesh_create: empty mesh"); return nullptr; }
-  // bounds
   float xmin = INFINITY, ymin = INFINITY, zmin = INFINITY, xmax = -INFINITY, ymax = -INFINITY, zmax = -INFINITY;
   for (int64_t i = 0; i < nv; ++i) {
     xmin = std::min(xmin, V[3 * i]); xmax = std::max(xmax, V[3 * i]);
@@ -66,54 +66,76 @@ void* b200lab_mesh_create(const float* V, int64_t nv, const int32_t* F, int64_t 
   }
   for (int64_t f = 0; f < 3 * nf; ++f)
     if (F[f] < 0 || F[f] >= nv) { set_error("b200lab_mesh_create: face index out of range"); return nullptr; }
+  // triangle soup, packed records, xy areas
+  std::vector<float> tris((size_t)nf * 9);
+  std::vector<float> rec((size_t)nf * 12, 0.0f);
+  std::vector<double> areas;
+  areas.reserve(nf);
+  for (int64_t f = 0; f < nf; ++f) {
+    for (int k = 0; k < 3; ++k) {
+      const float* p = V + 3 * (int64_t)F[3 * f + k];
+      tris[f * 9 + 3 * k] = p[0]; tris[f * 9 + 3 * k + 1] = p[1]; tris[f * 9 + 3 * k + 2] = p[2];
+    }
+    const float* t = &tris[f * 9];
+    double e1x = (double)t[3] - t[0], e1y = (double)t[4] - t[1], e1z = (double)t[5] - t[2];
+    double e2x = (double)t[6] - t[0], e2y = (double)t[7] - t[1], e2z = (double)t[8] - t[2];
+    double det2 = e1x * e2y - e1y * e2x;
+    float* r = &rec[f * 12];
+    r[0] = t[0]; r[1] = t[1]; r[2] = t[2]; r[3] = std::fabs(det2) < 1e-12 ? 0.0f : (float)(1.0 / det2);
+    r[4] = (float)e1x; r[5] = (float)e1y; r[6] = (float)e1z; r[7] = (float)e2x;
+    r[8] = (float)e2y; r[9] = (float)e2z;
+    if (std::fabs(det2) > 1e-10) areas.push_back(0.5 * std::fabs(det2));
+  }
   double ex = std::max((double)xmax - xmin, 1e-3), ey = std::max((double)ymax - ymin, 1e-3);
   if (!(cell_size > 0.f)) {
-    // auto: about one triangle footprint per cell, bounded so the grid stays <= 16 M cells
-    double c = std::sqrt(ex * ey / (double)nf) * 1.5;
-    double cmin = std::sqrt(ex * ey / 16.0e6);
+    // auto: half the edge of a median triangle's bounding square, so a lattice-aligned height field puts 1-3 triangles
+    // in a cell; bounded so the grid stays <= 24 M cells
+    double med = 0.0;
+    if (!areas.empty()) {
+      std::nth_element(areas.begin(), areas.begin() + areas.size() / 2, areas.end());
+      med = areas[areas.size() / 2];
+    }
+    double c = med > 0.0 ? 0.5 * std::sqrt(2.0 * med) : std::sqrt(ex * ey / (double)nf);
+    double cmin = std::sqrt(ex * ey / 24.0e6);
     cell_size = (float)std::max(std::max(c, cmin), 1e-4);
   }
-  const float pad = cell_size * 0.5f;
+  const float pad = cell_size;
   MeshAccel m{};
-  m.ox = xmin - pad; m.oy = ymin - pad;
+  // the 0.37-cell shift keeps lattice-aligned triangle edges off the cell borders
+  m.ox = xmin - pad - 0.37f * cell_size; m.oy = ymin - pad - 0.37f * cell_size;
   m.cell = cell_size; m.inv_cell = 1.0f / cell_size;
   m.nx = (int)std::floor((xmax + pad - m.ox) / cell_size) + 1;
   m.ny = (int)std::floor((ymax + pad - m.oy) / cell_size) + 1;
   m.num_faces = (int)nf; m.zmin = zmin; m.zmax = zmax;
   const int64_t ncell = (int64_t)m.nx * m.ny;
-  if (ncell > (int64_t)64e6) { set_error("b200lab_mesh_create: grid too large (%lld cells)", (long long)ncell); return nullptr; }
-  // triangle soup + per-triangle cell range (XY bbox, conservative, one ulp-ish margin)
-  std::vector<float> tris((size_t)nf * 9);
+  if (ncell > (int64_t)100e6) { set_error("b200lab_mesh_create: grid too large (%lld cells)", (long long)ncell); return nullptr; }
   std::vector<int> cx0(nf), cx1(nf), cy0(nf), cy1(nf);
   std::vector<int> counts(ncell + 1, 0);
-  const float eps = cell_size * 1e-3f;
+  // conservative margin: covers the fp32 rounding of the ray's cell index (|x| / cell ulps) with room to spare
+  const float eps = std::max(cell_size * 2e-3f, 4e-6f * std::max(std::max(std::fabs(xmin), std::fabs(xmax)),
+                                                                     std::max(std::fabs(ymin), std::fabs(ymax))));
   for (int64_t f = 0; f < nf; ++f) {
-    float bx0 = INFINITY, bx1 = -INFINITY, by0 = INFINITY, by1 = -INFINITY;
-    for (int k = 0; k < 3; ++k) {
-      const float* p = V + 3 * (int64_t)F[3 * f + k];
-      tris[f * 9 + 3 * k] = p[0]; tris[f * 9 + 3 * k + 1] = p[1]; tris[f * 9 + 3 * k + 2] = p[2];
-      bx0 = std::min(bx0, p[0]); bx1 = std::max(bx1, p[0]);
-      by0 = std::min(by0, p[1]); by1 = std::max(by1, p[1]);
-    }
+    const float* t = &tris[f * 9];
+    float bx0 = std::min(t[0], std::min(t[3], t[6])), bx1 = std::max(t[0], std::max(t[3], t[6]));
+    float by0 = std::min(t[1], std::min(t[4], t[7])), by1 = std::max(t[1], std::max(t[4], t[7]));
     cx0[f] = std::max(0, (int)std::floor((bx0 - eps - m.ox) * m.inv_cell));
     cx1[f] = std::min(m.nx - 1, (int)std::floor((bx1 + eps - m.ox) * m.inv_cell));
     cy0[f] = std::max(0, (int)std::floor((by0 - eps - m.oy) * m.inv_cell));
     cy1[f] = std::min(m.ny - 1, (int)std::floor((by1 + eps - m.oy) * m.inv_cell));
   }
-  // exact-ish 2-D triangle/cell overlap (separating axes: the 3 edge normals; the bbox axes are implied by the range)
+  // 2-D triangle/cell overlap (separating axes: the 3 edge normals; the bbox axes are implied by the cell range)
   auto overlaps = [&](int64_t f, int cx, int cy) -> bool {
     const float* t = &tris[f * 9];
     double x0 = m.ox + (double)cx * cell_size - eps, x1 = m.ox + (double)(cx + 1) * cell_size + eps;
     double y0 = m.oy + (double)cy * cell_size - eps, y1 = m.oy + (double)(cy + 1) * cell_size + eps;
     double px[3] = {t[0], t[3], t[6]}, py[3] = {t[1], t[4], t[7]};
     double area2 = (px[1] - px[0]) * (py[2] - py[0]) - (px[2] - px[0]) * (py[1] - py[0]);
-    if (std::fabs(area2) < 1e-14) return true;  // degenerate in XY (vertical wall): keep, MT rejects it anyway
+    if (std::fabs(area2) < 1e-14) return true;  // degenerate in XY (vertical wall): keep for non-vertical rays
     for (int k = 0; k < 3; ++k) {
       int k2 = (k + 1) % 3, k3 = (k + 2) % 3;
       double nx_ = -(py[k2] - py[k]), ny_ = (px[k2] - px[k]);
-      double side = nx_ * (px[k3] - px[k]) + ny_ * (py[k3] - py[k]);  // interior side sign
+      double side = nx_ * (px[k3] - px[k]) + ny_ * (py[k3] - py[k]);
       double s = side > 0 ? 1.0 : -1.0;
-      // is the whole rectangle strictly on the outer side of this edge?
       double d0 = s * (nx_ * (x0 - px[k]) + ny_ * (y0 - py[k]));
       double d1 = s * (nx_ * (x1 - px[k]) + ny_ * (y0 - py[k]));
       double d2 = s * (nx_ * (x0 - px[k]) + ny_ * (y1 - py[k]));
@@ -123,35 +145,23 @@ void* b200lab_mesh_create(const float* V, int64_t nv, const int32_t* F, int64_t 
     }
     return true;
   };
-  // pass 1: count
-  for (int64_t f = 0; f < nf; ++f) {
+  for (int64_t f = 0; f < nf; ++f)
     for (int cy = cy0[f]; cy <= cy1[f]; ++cy)
       for (int cx = cx0[f]; cx <= cx1[f]; ++cx)
         if (overlaps(f, cx, cy)) counts[(int64_t)cy * m.nx + cx + 1]++;
-  }
   for (int64_t c = 0; c < ncell; ++c) counts[c + 1] += counts[c];
   const int64_t entries = counts[ncell];
   std::vector<int> cell_tris((size_t)std::max<int64_t>(entries, 1));
   std::vector<int> cursor(counts.begin(), counts.end() - 1);
-  std::vector<float> cz((size_t)ncell * 2);
-  for (int64_t c = 0; c < ncell; ++c) { cz[2 * c] = INFINITY; cz[2 * c + 1] = -INFINITY; }
-  for (int64_t f = 0; f < nf; ++f) {
-    float tz0 = std::min(tris[f * 9 + 2], std::min(tris[f * 9 + 5], tris[f * 9 + 8]));
-    float tz1 = std::max(tris[f * 9 + 2], std::max(tris[f * 9 + 5], tris[f * 9 + 8]));
+  for (int64_t f = 0; f < nf; ++f)
     for (int cy = cy0[f]; cy <= cy1[f]; ++cy)
       for (int cx = cx0[f]; cx <= cx1[f]; ++cx)
-        if (overlaps(f, cx, cy)) {
-          int64_t c = (int64_t)cy * m.nx + cx;
-          cell_tris[cursor[c]++] = (int)f;
-          cz[2 * c] = std::min(cz[2 * c], tz0);
-          cz[2 * c + 1] = std::max(cz[2 * c + 1], tz1);
-        }
-  }
+        if (overlaps(f, cx, cy)) cell_tris[cursor[(int64_t)cy * m.nx + cx]++] = (int)f;
   // upload
   MeshHandle* h = (MeshHandle*)calloc(1, sizeof(MeshHandle));
-  size_t sz[4] = {(size_t)(ncell + 1) * sizeof(int), cell_tris.size() * sizeof(int), cz.size() * sizeof(float),
+  size_t sz[4] = {(size_t)(ncell + 1) * sizeof(int), cell_tris.size() * sizeof(int), rec.size() * sizeof(float),
                   tris.size() * sizeof(float)};
-  const void* src[4] = {counts.data(), cell_tris.data(), cz.data(), tris.data()};
+  const void* src[4] = {counts.data(), cell_tris.data(), rec.data(), tris.data()};
   cudaError_t err = cudaSuccess;
   for (int k = 0; k < 4 && err == cudaSuccess; ++k) {
     err = cudaMalloc(&h->buffers[k], sz[k]);
@@ -161,9 +171,10 @@ void* b200lab_mesh_create(const float* V, int64_t nv, const int32_t* F, int64_t 
   if (err == cudaSuccess) {
     m.cell_start = (const int*)h->buffers[0];
     m.cell_tris = (const int*)h->buffers[1];
-    m.cell_z = (const float2*)h->buffers[2];
+    m.rec = (const float4*)h->buffers[2];
     m.tris = (const float*)h->buffers[3];
     h->host = m;
+    h->entries = entries;
     err = cudaMalloc((void**)&h->dev, sizeof(MeshAccel));
     if (err == cudaSuccess) err = cudaMemcpy(h->dev, &m, sizeof(MeshAccel), cudaMemcpyHostToDevice);
   }

@@ -388,6 +388,7 @@ class FusedEnv:
         self.log_accum = z(C["B200LAB_LOG_SLOTS"], dtype=torch.float64)
         st.log_accum = p(self.log_accum)
         self._u = (None, None, None)
+        self._view_arrays = {}
         self.handle = self.L.b200lab_env_create(ctypes.byref(st))
         if not self.handle:
             raise RuntimeError("b200lab_env_create failed: " + self.L.b200lab_last_error().decode())
@@ -431,15 +432,35 @@ class FusedEnv:
         _lib.check(self.L.b200lab_compute_obs(self.handle, sim.ref, self.step_counter, _lib.current_stream()))
         return self.obs_buf
 
-    def step(self, action, sims, sim_prev):
-        """process_action -> for each physics state in `sims`: pre(previous state), post(new state) -> post_step ->
-        compute_obs.  Mirrors oracle.mdp_env.OracleEnv.step / manager_based_rl_env.py:153-242."""
-        self.process_action(action)
-        prev = sim_prev
-        for sim in sims:
-            self.substep_pre(prev)
-            self.substep_post(sim)
-            prev = sim
+    def decimation_fused(self, action, sims, sim_prev):
+        """Replay fast path: process_action + all S (pre, post) sub-steps in one launch (b200lab_decimation_fused)."""
+        if action.shape != (self.N, self.A):
+            raise ValueError(f"Invalid action shape, expected: {self.A}, received: {action.shape[1]}.")
+        key = tuple(id(v) for v in sims)
+        arr = self._view_arrays.get(key)
+        if arr is None:
+            if len(self._view_arrays) > 256:
+                self._view_arrays.clear()
+            arr = (_lib.structs["B200LabSimView"] * len(sims))(*[v.c for v in sims])
+            self._view_arrays[key] = arr
+        action = action.contiguous()
+        _lib.check(self.L.b200lab_decimation_fused(self.handle, _lib.ptr(action), sim_prev.ref, arr, len(sims),
+                                                   _lib.current_stream()))
+
+    def step(self, action, sims, sim_prev, fused: bool = True):
+        """One env step on S known post-physics states: [process_action -> S x (pre(previous state), post(new state))]
+        -> post_step -> compute_obs (manager_based_rl_env.py:153-242; mirrors oracle.mdp_env.OracleEnv.step).
+        `fused=True` runs the bracketed part as one launch, `fused=False` as the 1 + 2S calls a live simulator uses."""
+        if fused and len(sims) <= 8:
+            self.decimation_fused(action, sims, sim_prev)
+            prev = sims[-1]
+        else:
+            self.process_action(action)
+            prev = sim_prev
+            for sim in sims:
+                self.substep_pre(prev)
+                self.substep_post(sim)
+                prev = sim
         self.post_step(prev)
         self.compute_obs(prev)
         self.step_counter += 1

@@ -26,8 +26,9 @@ def exact(a, b, name):
     assert torch.equal(a.to(b.dtype), b), f"{name}: {(a.to(b.dtype) != b).sum().item()} mismatches"
 
 
+@pytest.mark.parametrize("fused", [True, False], ids=["fused-decimation", "per-substep"])
 @pytest.mark.parametrize("task", TASKS)
-def test_fused_step_matches_oracle(task):
+def test_fused_step_matches_oracle(task, fused):
     from isaaclab_b200.envs.fused_env import FusedEnv
     from isaaclab_b200.sim.synthetic import SyntheticSim, generate_slabs, initial_env_state
     N, steps = (192, 6) if "Rough" in task else (384, 8)
@@ -51,7 +52,7 @@ def test_fused_step_matches_oracle(task):
         o_obs, o_rew, o_term, o_trunc = orc.step(action, views_cpu, u_r, u_s, u_o, prev_cpu)
         ur, us_, uo = u_r.cuda(), u_s.cuda(), u_o.cuda()
         fus.set_uniforms(ur, us_, uo)
-        f_obs, f_rew, f_term, f_trunc = fus.step(action.cuda(), sim.views(k + 1), prev_gpu)
+        f_obs, f_rew, f_term, f_trunc = fus.step(action.cuda(), sim.views(k + 1), prev_gpu, fused=fused)
         torch.cuda.synchronize()
         tag = f"{task} step {k}"
         exact(f_term, o_term, tag + " terminated")
