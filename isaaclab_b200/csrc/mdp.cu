@@ -23,6 +23,7 @@ struct EnvHandle {
   B200LabEnvState host;
   B200LabEnvState* dev;
   float* derived;      // [N, kDerived] per-env derived state for compute_obs
+  bool rays_vertical;  // all ray directions are (0,0,dz), dz != 0, and the sensor is yaw-only
   uint8_t* col_term;   // [obs_dim] obs column -> term index
   int16_t* col_src;    // [obs_dim] obs column -> joint index (joint terms) or index inside the term
 };
@@ -56,7 +57,15 @@ process_action_kernel(const Env* __restrict__ e, const float* __restrict__ in) {
 constexpr int kActBlock = 128;
 constexpr int kMaxNetFloats = 8192;  // staged net weights (32 KB)
 
-__device__ __forceinline__ float sigmoidf_(float x) { return 1.0f / (1.0f + expf(-x)); }
+// LSTM gate activations on the SFU path (ex2.approx + fast divide): |error| ~ 1e-6 absolute on the gate values, far below
+// the 2e-5 torque tolerance of the parity tests; the IEEE expf/tanhf/divide sequences were half of the actuator kernel's
+// instructions (profiles/r1_notes.md).
+__device__ __forceinline__ float sigmoidf_(float x) { return __fdividef(1.0f, 1.0f + __expf(-x)); }
+__device__ __forceinline__ float tanhf_(float x) {
+  float a = fabsf(x);
+  float t = 1.0f - __fdividef(2.0f, __expf(2.0f * a) + 1.0f);   // exp overflow -> inf -> t = 1
+  return copysignf(t, x);
+}
 
 __device__ __forceinline__ float dc_motor_clip(float tau, float qd, float sat, float vlim, float elim) {
   // actuator_pd.py:276-286
@@ -111,10 +120,10 @@ __device__ __forceinline__ float lstm_forward(const float* __restrict__ w, int L
         for (int k = 0; k < H; ++k) acc = fmaf(w_hh[r * H + k], h[k], acc);
         g4[g] = acc;
       }
-      float ig = sigmoidf_(g4[0]), fg = sigmoidf_(g4[1]), gg = tanhf(g4[2]), og = sigmoidf_(g4[3]);
+      float ig = sigmoidf_(g4[0]), fg = sigmoidf_(g4[1]), gg = tanhf_(g4[2]), og = sigmoidf_(g4[3]);
       float cn = fmaf(fg, c[u], ig * gg);
       c[u] = cn;
-      hn[u] = og * tanhf(cn);
+      hn[u] = og * tanhf_(cn);
     }
 #pragma unroll
     for (int k = 0; k < H; k += 4) {
@@ -362,18 +371,29 @@ struct SimViews {
 };
 
 __global__ void __launch_bounds__(kPostBlock)
-decimation_fused_kernel(const Env* __restrict__ e, const float* __restrict__ action_in, SimViews sv, int W,
-                        int envs_per_block) {
+decimation_fused_kernel(const Env* __restrict__ e, const float* __restrict__ action_in, SimViews sv, int joint_blocks,
+                        int W, int envs_per_block) {
   extern __shared__ float s_w[];
-  stage_net_weights(e, s_w);
   const int N = e->N, J = e->J, B = e->B, A = e->A, S = sv.S;
-  int el = threadIdx.x / W, i = threadIdx.x % W;
-  int n = blockIdx.x * envs_per_block + el;
-  if (blockIdx.x == 0 && threadIdx.x == 0 && e->step_counter_dev) *e->step_counter_dev += 1;
-  if (el >= envs_per_block || n >= N) return;
   const float dt = e->physics_dt;
+  // Blocks [0, joint_blocks): one thread per (env, joint), dense.  Blocks [joint_blocks, ...): whole envs, W = B lanes per
+  // env for the contact sensor + the env-level sensor clocks (they need a block barrier; see the end of the kernel).
+  int n, i;
+  const bool joint_role = (int)blockIdx.x < joint_blocks;
+  if (joint_role) {
+    stage_net_weights(e, s_w);
+    int64_t gid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (gid >= (int64_t)N * J) return;
+    n = (int)(gid / J); i = (int)(gid % J);
+  } else {
+    int el = threadIdx.x / W;
+    i = threadIdx.x % W;
+    n = ((int)blockIdx.x - joint_blocks) * envs_per_block + el;
+    if (blockIdx.x == joint_blocks && threadIdx.x == 0 && e->step_counter_dev) *e->step_counter_dev += 1;
+    if (el >= envs_per_block || n >= N) return;
+  }
   // ---- joint role
-  if (i < J) {
+  if (joint_role) {
     const int j = i;
     const int64_t o = (int64_t)n * J + j;
     // ActionManager.process_action + JointAction.process_actions for the action column driving this joint
@@ -411,6 +431,7 @@ decimation_fused_kernel(const Env* __restrict__ e, const float* __restrict__ act
     }
   }
   // ---- body role: ContactSensor (contact_sensor.py:320-379) under SensorBase.update (sensor_base.py:197-205)
+  if (joint_role) return;
   if (e->cs_timestamp && i < B) {
     const int64_t ob = (int64_t)n * B + i;
     const int Hh = e->hist;
@@ -490,12 +511,20 @@ decimation_fused_kernel(const Env* __restrict__ e, const float* __restrict__ act
 // ------------------------------------------------------------------------------------------------
 // post_step: one warp per env.
 // ------------------------------------------------------------------------------------------------
+// Per-env working set of one warp.  Everything the terms read is loaded ONCE, coalesced, at kernel entry -- lane l holds
+// joint l (and l+32), action column l (and l+32), body l (and l+32) -- so every term is register arithmetic plus warp
+// reductions; the reference re-reads (and re-derives) these tensors in every term function.
 struct EnvCtx {
   int n, lane;
   f4 q;
   f3 pos, lin_w, ang_w, lin_b, ang_b, grav_b;
   f3 cmd;
   bool terminated;
+  // lane-distributed rows (slot 0: index lane, slot 1: index lane + 32)
+  float jq[2], jqd[2], jacc[2], jtau[2], jdef[2], jlo[2], jhi[2];
+  float act[2], pact[2];
+  float bnorm[2];            // max over the contact history of |F| for the body (net_forces_w_history.norm(-1).max(1))
+  float b_cc[2], b_ca[2], b_la[2];  // current contact time, current air time, last air time
 };
 
 __device__ __forceinline__ float u_reset_at(const Env* e, int n, int slot, int64_t step) {
@@ -515,35 +544,62 @@ __device__ __forceinline__ void derive_state(EnvCtx& c, const float* rs) {
   c.grav_b = quat_rotate_inverse(c.q, f3{0.f, 0.f, -1.f});  // :513-515
 }
 
-// max over the contact history of |F| for body b (net_forces_w_history[n, :, b])
-__device__ __forceinline__ float hist_max_norm(const Env* e, int n, int b) {
-  const float* hp = e->cs_forces_hist + ((int64_t)n * e->hist * e->B + b) * 3;
-  float m = -INFINITY;
-  for (int k = 0; k < e->hist; ++k) {
-    const float* f = hp + (int64_t)k * e->B * 3;
-    m = fmaxf(m, norm3(f[0], f[1], f[2]));
+__device__ __forceinline__ void load_rows(EnvCtx& c, const Env* __restrict__ e, const Sim& sim) {
+  const int n = c.n, lane = c.lane, J = e->J, A = e->A, B = e->B;
+#pragma unroll
+  for (int sl = 0; sl < 2; ++sl) {
+    int j = lane + 32 * sl;
+    c.jq[sl] = c.jqd[sl] = c.jacc[sl] = c.jtau[sl] = c.jdef[sl] = c.jlo[sl] = c.jhi[sl] = 0.f;
+    c.act[sl] = c.pact[sl] = 0.f;
+    c.bnorm[sl] = -INFINITY; c.b_cc[sl] = c.b_ca[sl] = c.b_la[sl] = 0.f;
+    if (j < J) {
+      int64_t o = (int64_t)n * J + j;
+      c.jq[sl] = sim.joint_pos[o]; c.jqd[sl] = sim.joint_vel[o];
+      c.jacc[sl] = e->joint_acc[o]; c.jtau[sl] = e->applied_torque[o];
+      c.jdef[sl] = __ldg(e->default_joint_pos + j);
+      c.jlo[sl] = __ldg(e->soft_joint_pos_limits + 2 * j); c.jhi[sl] = __ldg(e->soft_joint_pos_limits + 2 * j + 1);
+    }
+    if (j < A) { c.act[sl] = e->action[(int64_t)n * A + j]; c.pact[sl] = e->prev_action[(int64_t)n * A + j]; }
+    if (j < B && e->cs_forces_hist) {
+      const float* hp = e->cs_forces_hist + ((int64_t)n * e->hist * B + j) * 3;
+      float m = -INFINITY;
+      for (int k = 0; k < e->hist; ++k) {
+        const float* f = hp + (int64_t)k * B * 3;
+        m = fmaxf(m, norm3(f[0], f[1], f[2]));
+      }
+      c.bnorm[sl] = m;
+      if (e->cs_current_air_time) {
+        c.b_cc[sl] = e->cs_current_contact_time[(int64_t)n * B + j];
+        c.b_ca[sl] = e->cs_current_air_time[(int64_t)n * B + j];
+        c.b_la[sl] = e->cs_last_air_time[(int64_t)n * B + j];
+      }
+    }
   }
-  return m;
+}
+
+__device__ __forceinline__ bool sel(uint64_t mask, int lane, int sl) { return (mask >> (lane + 32 * sl)) & 1ull; }
+
+// value held by the lane owning index `idx` (idx uniform across the warp)
+__device__ __forceinline__ float row_at(const float (&row)[2], int idx) {
+  float a = __shfl_sync(0xffffffffu, row[0], idx & 31);
+  float b = __shfl_sync(0xffffffffu, row[1], idx & 31);
+  return idx < 32 ? a : b;
 }
 
 __device__ float eval_termination(const Env* e, const Sim& sim, const B200LabTerm& t, const EnvCtx& c, int64_t ep_len) {
-  const int n = c.n, lane = c.lane;
+  const int lane = c.lane;
   switch (t.op) {
     case B200LAB_TERM_TIME_OUT:
       return ep_len >= e->max_episode_length ? 1.f : 0.f;
     case B200LAB_TERM_ILLEGAL_CONTACT: {
-      int any = 0;
-      for (int b = lane; b < e->B; b += 32)
-        if ((t.body_mask >> b) & 1ull) any |= hist_max_norm(e, n, b) > t.p[0];
+      int any = (sel(t.body_mask, lane, 0) && c.bnorm[0] > t.p[0]) || (sel(t.body_mask, lane, 1) && c.bnorm[1] > t.p[0]);
       return __any_sync(0xffffffffu, any) ? 1.f : 0.f;
     }
     case B200LAB_TERM_JOINT_POS_OUT_OF_MANUAL_LIMIT: {
       int any = 0;
-      for (int j = lane; j < e->J; j += 32)
-        if ((t.joint_mask >> j) & 1ull) {
-          float q = sim.joint_pos[(int64_t)n * e->J + j];
-          any |= (q > t.p[1]) || (q < t.p[0]);
-        }
+#pragma unroll
+      for (int sl = 0; sl < 2; ++sl)
+        if (sel(t.joint_mask, lane, sl) && lane + 32 * sl < e->J) any |= (c.jq[sl] > t.p[1]) || (c.jq[sl] < t.p[0]);
       return __any_sync(0xffffffffu, any) ? 1.f : 0.f;
     }
     case B200LAB_TERM_ROOT_HEIGHT_BELOW_MINIMUM:
@@ -551,14 +607,13 @@ __device__ float eval_termination(const Env* e, const Sim& sim, const B200LabTer
     case B200LAB_TERM_BAD_ORIENTATION:
       return fabsf(acosf(-c.grav_b.z)) > t.p[0] ? 1.f : 0.f;
     case B200LAB_TERM_EXTERNAL:
-      return e->ext_values[(int64_t)t.i0 * e->N + n] != 0.f ? 1.f : 0.f;
+      return e->ext_values[(int64_t)t.i0 * e->N + c.n] != 0.f ? 1.f : 0.f;
   }
   return 0.f;
 }
 
 __device__ float eval_reward(const Env* e, const Sim& sim, const B200LabTerm& t, const EnvCtx& c) {
   const int n = c.n, lane = c.lane, J = e->J, B = e->B;
-  const int64_t jo = (int64_t)n * J;
   switch (t.op) {
     case B200LAB_REW_IS_ALIVE: return c.terminated ? 0.f : 1.f;
     case B200LAB_REW_IS_TERMINATED: return c.terminated ? 1.f : 0.f;
@@ -573,23 +628,23 @@ __device__ float eval_reward(const Env* e, const Sim& sim, const B200LabTerm& t,
     case B200LAB_REW_JOINT_POS_LIMITS:
     case B200LAB_REW_JOINT_POS_TARGET_L2: {
       float acc = 0.f;
-      for (int j = lane; j < J; j += 32) {
-        if (!((t.joint_mask >> j) & 1ull)) continue;
+#pragma unroll
+      for (int sl = 0; sl < 2; ++sl) {
+        if (lane + 32 * sl >= J || !sel(t.joint_mask, lane, sl)) continue;
         float v;
         switch (t.op) {
-          case B200LAB_REW_JOINT_TORQUES_L2: v = e->applied_torque[jo + j]; v = v * v; break;
-          case B200LAB_REW_JOINT_VEL_L1: v = fabsf(sim.joint_vel[jo + j]); break;
-          case B200LAB_REW_JOINT_VEL_L2: v = sim.joint_vel[jo + j]; v = v * v; break;
-          case B200LAB_REW_JOINT_ACC_L2: v = e->joint_acc[jo + j]; v = v * v; break;
-          case B200LAB_REW_JOINT_DEVIATION_L1: v = fabsf(sim.joint_pos[jo + j] - e->default_joint_pos[j]); break;
+          case B200LAB_REW_JOINT_TORQUES_L2: v = c.jtau[sl] * c.jtau[sl]; break;
+          case B200LAB_REW_JOINT_VEL_L1: v = fabsf(c.jqd[sl]); break;
+          case B200LAB_REW_JOINT_VEL_L2: v = c.jqd[sl] * c.jqd[sl]; break;
+          case B200LAB_REW_JOINT_ACC_L2: v = c.jacc[sl] * c.jacc[sl]; break;
+          case B200LAB_REW_JOINT_DEVIATION_L1: v = fabsf(c.jq[sl] - c.jdef[sl]); break;
           case B200LAB_REW_JOINT_POS_LIMITS: {
-            float q = sim.joint_pos[jo + j];
-            float lo = q - e->soft_joint_pos_limits[2 * j], hi = q - e->soft_joint_pos_limits[2 * j + 1];
+            float lo = c.jq[sl] - c.jlo[sl], hi = c.jq[sl] - c.jhi[sl];
             v = -fminf(lo, 0.f) + fmaxf(hi, 0.f);   // rewards.py:190-196
             break;
           }
           default: {  // JOINT_POS_TARGET_L2
-            float d = wrap_to_pi(sim.joint_pos[jo + j]) - t.p[0];
+            float d = wrap_to_pi(c.jq[sl]) - t.p[0];
             v = d * d;
           }
         }
@@ -600,9 +655,11 @@ __device__ float eval_reward(const Env* e, const Sim& sim, const B200LabTerm& t,
     case B200LAB_REW_ACTION_RATE_L2:
     case B200LAB_REW_ACTION_L2: {
       float acc = 0.f;
-      for (int a = lane; a < e->A; a += 32) {
-        float x = e->action[(int64_t)n * e->A + a];
-        if (t.op == B200LAB_REW_ACTION_RATE_L2) x = x - e->prev_action[(int64_t)n * e->A + a];
+#pragma unroll
+      for (int sl = 0; sl < 2; ++sl) {
+        if (lane + 32 * sl >= e->A) continue;
+        float x = c.act[sl];
+        if (t.op == B200LAB_REW_ACTION_RATE_L2) x = x - c.pact[sl];
         acc += x * x;
       }
       return warp_sum(acc);
@@ -610,9 +667,10 @@ __device__ float eval_reward(const Env* e, const Sim& sim, const B200LabTerm& t,
     case B200LAB_REW_UNDESIRED_CONTACTS:
     case B200LAB_REW_CONTACT_FORCES: {
       float acc = 0.f;
-      for (int b = lane; b < B; b += 32)
-        if ((t.body_mask >> b) & 1ull) {
-          float m = hist_max_norm(e, n, b);
+#pragma unroll
+      for (int sl = 0; sl < 2; ++sl)
+        if (lane + 32 * sl < B && sel(t.body_mask, lane, sl)) {
+          float m = c.bnorm[sl];
           if (t.op == B200LAB_REW_UNDESIRED_CONTACTS) acc += (m > t.p[0]) ? 1.f : 0.f;
           else acc += fmaxf(m - t.p[0], 0.f);
         }
@@ -637,11 +695,12 @@ __device__ float eval_reward(const Env* e, const Sim& sim, const B200LabTerm& t,
     }
     case B200LAB_REW_FEET_AIR_TIME: {
       float acc = 0.f;
-      for (int b = lane; b < B; b += 32)
-        if ((t.body_mask >> b) & 1ull) {
-          float cc = e->cs_current_contact_time[(int64_t)n * B + b];
+#pragma unroll
+      for (int sl = 0; sl < 2; ++sl)
+        if (lane + 32 * sl < B && sel(t.body_mask, lane, sl)) {
+          float cc = c.b_cc[sl];
           bool first = (cc > 0.f) && (cc < t.p[1]);   // contact_sensor.py:208-210
-          acc += (e->cs_last_air_time[(int64_t)n * B + b] - t.p[0]) * (first ? 1.f : 0.f);
+          acc += (c.b_la[sl] - t.p[0]) * (first ? 1.f : 0.f);
         }
       float r = warp_sum(acc);
       return r * ((sqrtf(c.cmd.x * c.cmd.x + c.cmd.y * c.cmd.y) > 0.1f) ? 1.f : 0.f);
@@ -650,11 +709,10 @@ __device__ float eval_reward(const Env* e, const Sim& sim, const B200LabTerm& t,
       int cnt = 0;
       float mn = INFINITY;
       for (int b = 0; b < B; ++b)
-        if ((t.body_mask >> b) & 1ull) cnt += e->cs_current_contact_time[(int64_t)n * B + b] > 0.f;
+        if ((t.body_mask >> b) & 1ull) cnt += row_at(c.b_cc, b) > 0.f;
       for (int b = 0; b < B; ++b)
         if ((t.body_mask >> b) & 1ull) {
-          float ct = e->cs_current_contact_time[(int64_t)n * B + b];
-          float at = e->cs_current_air_time[(int64_t)n * B + b];
+          float ct = row_at(c.b_cc, b), at = row_at(c.b_ca, b);
           float mode = ct > 0.f ? ct : at;
           mn = fminf(mn, cnt == 1 ? mode : 0.f);
         }
@@ -667,7 +725,7 @@ __device__ float eval_reward(const Env* e, const Sim& sim, const B200LabTerm& t,
       while (m1 && m2) {
         int b1 = __ffsll((long long)m1) - 1, b2 = __ffsll((long long)m2) - 1;
         m1 &= m1 - 1; m2 &= m2 - 1;
-        bool contact = hist_max_norm(e, n, b1) > 1.0f;
+        bool contact = row_at(c.bnorm, b1) > 1.0f;
         const float* v = sim.body_lin_vel_w + ((int64_t)n * B + b2) * 3;
         acc += sqrtf(v[0] * v[0] + v[1] * v[1]) * (contact ? 1.f : 0.f);
       }
@@ -709,6 +767,7 @@ post_step_kernel(const Env* __restrict__ e, Sim sim, int64_t step) {
   float rs[13];
 #pragma unroll
   for (int k = 0; k < 13; ++k) rs[k] = sim.root_state_w[(int64_t)n * 13 + k];
+  load_rows(c, e, sim);
   derive_state(c, rs);
   c.cmd = {0.f, 0.f, 0.f};
   if (e->has_command) c.cmd = {e->cmd_vel_b[n * 3], e->cmd_vel_b[n * 3 + 1], e->cmd_vel_b[n * 3 + 2]};
@@ -727,15 +786,18 @@ post_step_kernel(const Env* __restrict__ e, Sim sim, int64_t step) {
   {
     float total = 0.f;
     const float dt = e->step_dt;
+    float mine = 0.f;        // lane r keeps term r's value: the per-term buffers are then updated by all lanes at once
+    bool mine_on = false;
     for (int r = 0; r < e->num_rew; ++r) {
       const B200LabTerm& t = e->rew[r];
       if (t.weight == 0.0f) continue;
       float value = eval_reward(e, sim, t, c) * t.weight * dt;
-      total += value;
-      if (lane == 0) {
-        e->episode_sums[(int64_t)r * N + n] += value;
-        e->step_reward[(int64_t)n * e->num_rew + r] = value / dt;
-      }
+      total += value;          // reward_buf += value, in term order (reward_manager.py:150)
+      if (lane == r) { mine = value; mine_on = true; }
+    }
+    if (mine_on) {
+      e->episode_sums[(int64_t)lane * N + n] += mine;
+      e->step_reward[(int64_t)n * e->num_rew + lane] = mine / dt;
     }
     if (lane == 0) {
       e->reward_buf[n] = total;
@@ -977,7 +1039,8 @@ derive_obs_kernel(const Env* __restrict__ e, Sim sim, float* __restrict__ derive
 // One thread per (env, obs column), no barriers: the term of a column comes from the per-column table built at
 // env_create, the env-level quantities from the derived scratch.  Height-scan columns cast their ray.
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256)
+template <bool kVerticalRays>
+__global__ void __launch_bounds__(256, kVerticalRays ? 4 : 2)
 compute_obs_kernel(const Env* __restrict__ e, Sim sim, int64_t step, const uint8_t* __restrict__ col_term,
                    const int16_t* __restrict__ col_src, const float* __restrict__ derived) {
   const int N = e->N, J = e->J, D = e->obs_dim;
@@ -1014,8 +1077,11 @@ compute_obs_kernel(const Env* __restrict__ e, Sim sim, int64_t step, const uint8
         float tt; int face;
         f3 hit{INFINITY, INFINITY, INFINITY};
         const MeshAccel* mesh = reinterpret_cast<const MeshAccel*>(e->rc_mesh);
-        if (mesh && raycast_mesh_dev(*mesh, st, dr, e->rc_max_distance, tt, face))
-          hit = {st.x + tt * dr.x, st.y + tt * dr.y, st.z + tt * dr.z};
+        // kVerticalRays: every pattern direction is (0, 0, dz) and the sensor is yaw-only (the height scanner) ->
+        // single-cell query, no DDA code in the kernel (fewer registers, higher occupancy)
+        bool ok = mesh && (kVerticalRays ? raycast_vertical(*mesh, st, dr.z, e->rc_max_distance, tt, face)
+                                         : raycast_mesh_dev(*mesh, st, dr, e->rc_max_distance, tt, face));
+        if (ok) hit = {st.x + tt * dr.x, st.y + tt * dr.y, st.z + tt * dr.z};
         float* hp = e->rc_ray_hits_w + ((int64_t)n * e->R + li) * 3;
         hp[0] = hit.x; hp[1] = hit.y; hp[2] = hit.z;
         hz = hit.z;
@@ -1056,6 +1122,15 @@ using namespace b200lab;
 // obs column -> (term, source index) tables, rebuilt whenever the descriptor changes
 static int upload_obs_tables(EnvHandle* h) {
   const B200LabEnvState& s = h->host;
+  h->rays_vertical = false;
+  if (s.R > 0 && s.rc_ray_dirs && s.rc_attach_yaw_only) {
+    std::vector<float> dirs((size_t)s.R * 3);
+    if (cudaMemcpy(dirs.data(), s.rc_ray_dirs, dirs.size() * sizeof(float), cudaMemcpyDeviceToHost) == cudaSuccess) {
+      bool ok = true;
+      for (int r = 0; r < s.R; ++r) ok = ok && dirs[3 * r] == 0.f && dirs[3 * r + 1] == 0.f && dirs[3 * r + 2] != 0.f;
+      h->rays_vertical = ok;
+    }
+  }
   int D = s.obs_dim;
   if (D <= 0) return B200LAB_OK;
   std::vector<uint8_t> ct(D);
@@ -1210,9 +1285,11 @@ int b200lab_decimation_fused(void* env, const float* action_in, const B200LabSim
   }
   for (int k = num_substeps; k < kMaxDecimation; ++k) sv.v[k] = views[num_substeps - 1];
   int W, epb;
-  int width = s.J > s.B ? s.J : s.B;
-  B200LAB_CHECK_ARG(launch_geometry(width, &W, &epb) == 0, "max(J,B) must be <= 256");
-  decimation_fused_kernel<<<(unsigned)ceil_div(s.N, epb), kPostBlock, smem, (cudaStream_t)stream>>>(h->dev, action_in, sv, W, epb);
+  B200LAB_CHECK_ARG(launch_geometry(s.B > 0 ? s.B : 1, &W, &epb) == 0, "B must be <= 256");
+  int joint_blocks = (int)ceil_div((int64_t)s.N * s.J, kPostBlock);
+  int body_blocks = (int)ceil_div(s.N, epb);
+  decimation_fused_kernel<<<(unsigned)(joint_blocks + body_blocks), kPostBlock, smem, (cudaStream_t)stream>>>(
+      h->dev, action_in, sv, joint_blocks, W, epb);
   count_launch();
   return check_launch("decimation_fused");
 }
@@ -1235,8 +1312,12 @@ int b200lab_compute_obs(void* env, const B200LabSimView* sim, int64_t step_count
   derive_obs_kernel<<<(unsigned)ceil_div(s.N, 128), 128, 0, st_>>>(h->dev, *sim, h->derived);
   count_launch();
   int64_t total = (int64_t)s.N * s.obs_dim;
-  compute_obs_kernel<<<(unsigned)ceil_div(total, 256), 256, 0, st_>>>(h->dev, *sim, step_counter, h->col_term, h->col_src,
-                                                                      h->derived);
+  if (h->rays_vertical)
+    compute_obs_kernel<true><<<(unsigned)ceil_div(total, 256), 256, 0, st_>>>(h->dev, *sim, step_counter, h->col_term,
+                                                                              h->col_src, h->derived);
+  else
+    compute_obs_kernel<false><<<(unsigned)ceil_div(total, 256), 256, 0, st_>>>(h->dev, *sim, step_counter, h->col_term,
+                                                                               h->col_src, h->derived);
   count_launch();
   return check_launch("compute_obs");
 }

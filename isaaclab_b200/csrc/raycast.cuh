@@ -87,7 +87,8 @@ __device__ __forceinline__ float ray_tri(const MeshAccel& m, int f, f3 o, f3 d) 
   return t > 0.0f ? t : -1.0f;
 }
 
-// Vertical closest hit: one cell.
+// Vertical closest hit: one cell.  Candidates are fetched two at a time so the dependent chain
+// cell_start -> cell_tris -> record is paid once per pair, not once per triangle.
 __device__ __forceinline__ bool raycast_vertical(const MeshAccel& m, f3 o, float dz, float max_dist, float& t_out,
                                                  int& face_out) {
   float t_best = max_dist;
@@ -97,10 +98,13 @@ __device__ __forceinline__ bool raycast_vertical(const MeshAccel& m, f3 o, float
     int c = cy * m.nx + cx;
     int s = __ldg(m.cell_start + c), e = __ldg(m.cell_start + c + 1);
     float inv_dz = 1.0f / dz;
-    for (int k = s; k < e; ++k) {
-      int f = __ldg(m.cell_tris + k);
-      float t = ray_tri_vertical(m, f, o, dz, inv_dz);
-      if (t > 0.0f && t <= t_best) { t_best = t; face_best = f; }
+    for (int k = s; k < e; k += 2) {
+      int f0 = __ldg(m.cell_tris + k);
+      int f1 = (k + 1 < e) ? __ldg(m.cell_tris + k + 1) : f0;
+      float t0 = ray_tri_vertical(m, f0, o, dz, inv_dz);
+      float t1 = ray_tri_vertical(m, f1, o, dz, inv_dz);
+      if (t0 > 0.0f && t0 <= t_best) { t_best = t0; face_best = f0; }
+      if (t1 > 0.0f && t1 <= t_best) { t_best = t1; face_best = f1; }
     }
   }
   t_out = t_best;
