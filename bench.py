@@ -52,7 +52,9 @@ def algorithmic_bytes(spec):
         "compute_obs": (28 if spec.get("raycaster") else 0) + 4 * obs,
     }
     per["decimation_fused"] = S * (per["substep_pre"] + per["substep_post"])
-    per_step = per["decimation_fused"] + per["post_step"] + per["compute_obs"]
+    # actuator pass of the write_data_to_sim() that follows _reset_idx (runs whenever any env reset: at 4096 envs, always)
+    per["post_reset_write"] = per["substep_pre"]
+    per_step = per["decimation_fused"] + per["post_step"] + per["post_reset_write"] + per["compute_obs"]
     return per, per_step
 
 
@@ -112,8 +114,9 @@ def build_workload(device, seed):
 
 def time_kernels(fus, sim, action, steps):
     """Per-kernel CUDA-event durations over `steps` env steps on the launching stream (ms per launch, averaged).
-    Replay path: decimation_fused (process_action + S x (pre, post)), post_step, compute_obs (derive + obs kernels)."""
-    names = ["decimation_fused", "post_step", "compute_obs"]
+    Replay path: decimation_fused (process_action + S x (pre, post)), post_step, post_reset_write (conditional actuator
+    pass), compute_obs (derive + obs kernels)."""
+    names = ["decimation_fused", "post_step", "post_reset_write", "compute_obs"]
     ev = {n: [] for n in names}
 
     def rec(name, fn, *a):
@@ -129,6 +132,7 @@ def time_kernels(fus, sim, action, steps):
         views = sim.views(k0 + k + 1)
         rec("decimation_fused", fus.decimation_fused, action, views, prev)
         rec("post_step", fus.post_step, views[-1])
+        rec("post_reset_write", fus.post_reset_write, views[-1])
         rec("compute_obs", fus.compute_obs, views[-1])
         fus.step_counter += 1
     torch.cuda.synchronize()

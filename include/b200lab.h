@@ -327,6 +327,9 @@ typedef struct B200LabEnvState {
   /* optional device-side step counter (CUDA-graph replay): when non-NULL, process_action increments it and the
    * kernels key their Philox streams on it instead of the host-passed `step_counter` argument */
   int64_t* step_counter_dev;
+  /* device flag "some env was reset in this step": cleared by process_action / decimation_fused, set by post_step,
+   * read by post_reset_write (required by that call, else optional) */
+  int32_t* any_reset_dev;
   /* --- episode log accumulators (extras["log"], LAB/envs/manager_based_rl_env.py:365-389) --- */
   double* log_accum;           /* [B200LAB_LOG_SLOTS] doubles, zeroed by the caller before post_step */
 } B200LabEnvState;
@@ -378,6 +381,13 @@ int b200lab_decimation_fused(void* env, const float* action_in, const B200LabSim
  * CommandManager.compute, interval events.  `step_counter` keys the Philox streams (perf mode) and is
  * env._sim_step_counter // decimation for the reset-event bookkeeping. */
 int b200lab_post_step(void* env, const B200LabSimView* sim, int64_t step_counter, void* stream);
+
+/* The `scene.write_data_to_sim()` that step() issues right after `_reset_idx` when ANY env was reset
+ * (manager_based_rl_env.py:217-223): Articulation._apply_actuator_model runs once more for ALL envs -- stateful
+ * actuator nets advance, computed/applied torque are rewritten -- on the joint state that holds the reset writes and
+ * the targets of the last apply_action.  The condition is evaluated on the device (`any_reset_dev`), so the call is
+ * unconditional on the host and needs no synchronisation; `sim` is the view post_step was given. */
+int b200lab_post_reset_write(void* env, const B200LabSimView* sim, void* stream);
 
 /* ObservationManager.compute (observation_manager.py:238-335) including RayCaster lazy update +
  * raycast_mesh for outdated envs (ray_caster.py:220-260, LAB/utils/warp/ops.py:24-127). */

@@ -39,7 +39,10 @@ process_action_kernel(const Env* __restrict__ e, const float* __restrict__ in) {
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   int A = e->A;
   int64_t total = (int64_t)e->N * A;
-  if (i == 0 && e->step_counter_dev) *e->step_counter_dev += 1;  // first kernel of the step sequence
+  if (i == 0) {  // first kernel of the step sequence
+    if (e->step_counter_dev) *e->step_counter_dev += 1;
+    if (e->any_reset_dev) *e->any_reset_dev = 0;
+  }
   if (i >= total) return;
   int a = (int)(i % A);
   float x = in[i];
@@ -249,16 +252,17 @@ __device__ __forceinline__ void actuator_eval(const Env* __restrict__ e, const f
 }
 
 __global__ void __launch_bounds__(kActBlock)
-substep_pre_kernel(const Env* __restrict__ e, Sim sim) {
+substep_pre_kernel(const Env* __restrict__ e, Sim sim, bool apply_action, bool only_if_any_reset) {
   extern __shared__ float s_w[];
   const int J = e->J, N = e->N;
+  if (only_if_any_reset && *e->any_reset_dev == 0) return;   // uniform over the grid
   stage_net_weights(e, s_w);
   int64_t gid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (gid >= (int64_t)N * J) return;
   int n = (int)(gid / J), j = (int)(gid % J);
   // action_manager.apply_action -> set_joint_{position,effort}_target (joint_actions.py:158-160, 223-225)
   int col = e->joint_action_col[j];
-  if (col >= 0) {
+  if (apply_action && col >= 0) {
     float p = e->processed_actions[(int64_t)n * e->A + col];
     if (e->action_kind == 0) e->joint_pos_target[gid] = p;
     else e->joint_effort_target[gid] = p;
@@ -389,7 +393,10 @@ decimation_fused_kernel(const Env* __restrict__ e, const float* __restrict__ act
     int el = threadIdx.x / W;
     i = threadIdx.x % W;
     n = ((int)blockIdx.x - joint_blocks) * envs_per_block + el;
-    if (blockIdx.x == joint_blocks && threadIdx.x == 0 && e->step_counter_dev) *e->step_counter_dev += 1;
+    if (blockIdx.x == joint_blocks && threadIdx.x == 0) {
+      if (e->step_counter_dev) *e->step_counter_dev += 1;
+      if (e->any_reset_dev) *e->any_reset_dev = 0;
+    }
     if (el >= envs_per_block || n >= N) return;
   }
   // ---- joint role
@@ -809,6 +816,7 @@ post_step_kernel(const Env* __restrict__ e, Sim sim, int64_t step) {
   __syncwarp();
   // -- _reset_idx (manager_based_rl_env.py:347-392), masked per env
   if (reset) {
+    if (lane == 0 && e->any_reset_dev) *e->any_reset_dev = 1;
     // curriculum: terrain_levels_vel (curriculums.py:26-55) + update_env_origins (terrain_importer.py:307-322)
     if (e->has_terrain_curriculum) {
       float ox = e->env_origins[n * 3], oy = e->env_origins[n * 3 + 1];
@@ -1250,9 +1258,25 @@ int b200lab_substep_pre(void* env, const B200LabSimView* sim, void* stream) {
   int rc = net_smem_bytes(s, &smem);
   if (rc) return rc;
   int64_t total = (int64_t)s.N * s.J;
-  substep_pre_kernel<<<(unsigned)ceil_div(total, kActBlock), kActBlock, smem, (cudaStream_t)stream>>>(h->dev, *sim);
+  substep_pre_kernel<<<(unsigned)ceil_div(total, kActBlock), kActBlock, smem, (cudaStream_t)stream>>>(h->dev, *sim, true,
+                                                                                                      false);
   count_launch();
   return check_launch("substep_pre");
+}
+
+int b200lab_post_reset_write(void* env, const B200LabSimView* sim, void* stream) {
+  B200LAB_CHECK_ARG(env && sim && sim->joint_pos && sim->joint_vel, "null argument");
+  EnvHandle* h = (EnvHandle*)env;
+  const B200LabEnvState& s = h->host;
+  B200LAB_CHECK_ARG(s.any_reset_dev != nullptr, "any_reset_dev is required by post_reset_write");
+  size_t smem = 0;
+  int rc = net_smem_bytes(s, &smem);
+  if (rc) return rc;
+  int64_t total = (int64_t)s.N * s.J;
+  substep_pre_kernel<<<(unsigned)ceil_div(total, kActBlock), kActBlock, smem, (cudaStream_t)stream>>>(h->dev, *sim, false,
+                                                                                                      true);
+  count_launch();
+  return check_launch("post_reset_write");
 }
 
 int b200lab_substep_post(void* env, const B200LabSimView* sim, void* stream) {

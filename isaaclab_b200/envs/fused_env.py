@@ -5,7 +5,7 @@ the reference-style manager cfg objects.  This module owns every tensor the refe
 ContactSensorData, RayCasterData and the managers (same shapes/dtypes, env-major), fills the `B200LabEnvState`
 descriptor (include/b200lab.h) with their raw pointers once, and launches
 
-    process_action -> S x (substep_pre, [simulator], substep_post) -> post_step -> compute_obs
+    process_action -> S x (substep_pre, [simulator], substep_post) -> post_step -> post_reset_write -> compute_obs
 
 through the C ABI on torch's current stream.  Nothing here computes on the host or falls back to torch ops.
 """
@@ -387,6 +387,8 @@ class FusedEnv:
         st.n_u_reset, st.n_u_step = self.n_u_reset, self.n_u_step
         self.log_accum = z(C["B200LAB_LOG_SLOTS"], dtype=torch.float64)
         st.log_accum = p(self.log_accum)
+        self.any_reset = z(1, dtype=torch.int32)
+        st.any_reset_dev = p(self.any_reset)
         self._u = (None, None, None)
         self._view_arrays = {}
         self.handle = self.L.b200lab_env_create(ctypes.byref(st))
@@ -428,6 +430,10 @@ class FusedEnv:
     def post_step(self, sim: SimView):
         _lib.check(self.L.b200lab_post_step(self.handle, sim.ref, self.step_counter, _lib.current_stream()))
 
+    def post_reset_write(self, sim: SimView):
+        """`scene.write_data_to_sim()` after `_reset_idx` (manager_based_rl_env.py:217-223); device-side condition."""
+        _lib.check(self.L.b200lab_post_reset_write(self.handle, sim.ref, _lib.current_stream()))
+
     def compute_obs(self, sim: SimView):
         _lib.check(self.L.b200lab_compute_obs(self.handle, sim.ref, self.step_counter, _lib.current_stream()))
         return self.obs_buf
@@ -462,6 +468,7 @@ class FusedEnv:
                 self.substep_post(sim)
                 prev = sim
         self.post_step(prev)
+        self.post_reset_write(prev)
         self.compute_obs(prev)
         self.step_counter += 1
         return self.obs_buf, self.reward_buf, self.terminated, self.truncated

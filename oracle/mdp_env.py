@@ -157,13 +157,23 @@ class OracleEnv:
     # of LAB/actuators/actuator_pd.py:115-140,184-198,264-286 and actuator_net.py:76-99,147-189
     # ---------------------------------------------------------------------------------------------
     def substep_pre(self, sim):
-        s = self.spec
-        a = s["action"]
+        self.apply_action()
+        self.write_data_to_sim(sim)
+
+    def apply_action(self):
+        """ActionManager.apply_action -> JointPositionAction/JointEffortAction.apply_actions (joint_actions.py:163-186)."""
+        a = self.spec["action"]
         ids = list(a["joint_ids"])
         if a["kind"] == "joint_position":
             self.joint_pos_target[:, ids] = self.processed_actions
         else:
             self.joint_effort_target[:, ids] = self.processed_actions
+
+    def write_data_to_sim(self, sim):
+        """Articulation.write_data_to_sim (articulation.py:173-200): the actuator models advance on EVERY call -- also on
+        the one `step` makes after `_reset_idx` (manager_based_rl_env.py:222), for all envs, with the targets of the
+        last `apply_action` and the joint state that holds the reset writes."""
+        s = self.spec
         for act, st in zip(s["actuators"], self.act_state):
             j = list(act["joint_ids"])
             q, qd = sim["joint_pos"][:, j], sim["joint_vel"][:, j]
@@ -591,6 +601,7 @@ class OracleEnv:
         self.last_reset_ids = ids
         if len(ids) > 0:
             self._reset_idx(ids, sim, u_reset)
+            self.write_data_to_sim(sim)   # manager_based_rl_env.py:221-223 (scene.write_data_to_sim(); sim.forward())
             d = self.derived(sim)
         if s.get("command"):
             self._command_compute(d, u_step)

@@ -106,3 +106,62 @@ def test_fused_step_matches_oracle(task, fused):
     for st_f, st_o in zip(fus.act_state, orc.act_state):
         for key in st_f:
             close(st_f[key], st_o[key], f"{task} actuator state {key}", rtol=1e-4, atol=1e-5)
+
+
+class _AsOracle:
+    """FusedEnv under OracleEnv's attribute names, for tests.test_oracle_mdp_golden.compare_state."""
+    _MAP = dict(cs_hist="cs_forces_hist", cs_last_air="cs_last_air_time", cs_cur_air="cs_current_air_time",
+                cs_last_contact="cs_last_contact_time", cs_cur_contact="cs_current_contact_time", rc_hits="rc_ray_hits_w")
+
+    def __init__(self, fus, spec):
+        self.f, self.spec = fus, spec
+
+    def __getattr__(self, name):
+        f, spec = self.__dict__["f"], self.__dict__["spec"]
+        if name == "term_dones":
+            return f.term_dones[:len(spec["terminations"])].cpu()
+        if name == "episode_sums":
+            return f.episode_sums[:len(spec["rewards"])].cpu()
+        if name == "step_reward":
+            return f.step_reward[:, :len(spec["rewards"])].cpu()
+        if name == "interval_time_left":
+            return [t.cpu() for t in f.interval_time_left]
+        v = getattr(f, self._MAP.get(name, name))
+        return v.cpu() if isinstance(v, torch.Tensor) else v
+
+
+@pytest.mark.parametrize("fused", [True, False], ids=["fused-decimation", "per-substep"])
+@pytest.mark.parametrize("task", TASKS)
+def test_fused_step_matches_reference_golden(task, fused):
+    """CUDA path against the fixtures recorded from the UNMODIFIED reference ManagerBasedRLEnv.step
+    (tests/golden/gen_mdp.py) -- no oracle in between."""
+    from isaaclab_b200.envs.fused_env import FusedEnv
+    from isaaclab_b200.sim.synthetic import SyntheticSim
+    from tests.test_oracle_mdp_golden import compare_state, load_fixture
+    fx = load_fixture(task)
+    N, steps = fx["N"], fx["steps"]
+    spec = make_spec(task, N)
+    fus = FusedEnv(spec, device="cuda")
+    init_fused_state(fus, fx["init"])
+    sim = SyntheticSim(spec, K=steps + 1, device="cuda", slabs={k: v.clone() for k, v in fx["slabs"].items()})
+    view = _AsOracle(fus, spec)
+    prev = sim.views(0)[-1]
+    for k in range(steps):
+        ref = fx["out"][k]
+        ur, us_, uo = ref["u_reset"].cuda(), ref["u_step"].cuda(), ref["u_obs"].cuda()
+        fus.set_uniforms(ur, us_, uo)
+        obs, rew, term, trunc = fus.step(ref["action_in"].cuda(), sim.views(k + 1), prev, fused=fused)
+        torch.cuda.synchronize()
+        tag = f"{task} step {k} (vs reference)"
+        compare_state(view, ref, spec, tag, rtol=1e-5, atol=2e-6, torque_tol=dict(rtol=2e-5, atol=2e-5), ray_tol=1e-4)
+        close(sim.dev["root_state_w"][k + 1], ref["root_state_w"], tag + " root_state_w after events", atol=2e-6)
+        close(sim.dev["joint_pos"][k + 1, -1], ref["joint_pos"], tag + " joint_pos after events")
+        close(sim.dev["joint_vel"][k + 1, -1], ref["joint_vel"], tag + " joint_vel after events")
+        close(obs, ref["obs"], tag + " obs", rtol=1e-5, atol=1e-4 if spec.get("raycaster") else 2e-6)
+        if spec.get("raycaster"):
+            D = fus.obs_dim - spec["R"]
+            close(obs[:, :D], ref["obs"][:, :D], tag + " obs (proprioceptive part)", atol=2e-6)
+        for st_f, st_r in zip(fus.act_state, ref["act_state"]):
+            for key in st_r:
+                close(st_f[key], st_r[key], tag + f" actuator state {key}", rtol=1e-4, atol=1e-5)
+        prev = sim.views(k + 1)[-1]
