@@ -20,12 +20,18 @@
 namespace b200lab {
 
 struct EnvHandle {
-  B200LabEnvState host;
-  B200LabEnvState* dev;
+  B200LabEnvState host;   // passed BY VALUE to the kernels whose descriptor reads are warp-uniform (__grid_constant__,
+                          // 12 KB of the 32 KB parameter space): constant-bank operands instead of global round trips
+  B200LabEnvState* dev;   // device copy for compute_obs, whose lanes index the term table divergently (one column each)
   float* derived;      // [N, kDerived] per-env derived state for compute_obs
   bool rays_vertical;  // all ray directions are (0,0,dz), dz != 0, and the sensor is yaw-only
   uint8_t* col_term;   // [obs_dim] obs column -> term index
   int16_t* col_src;    // [obs_dim] obs column -> joint index (joint terms) or index inside the term
+  // host copy of the ActuatorNetLSTM weights when their shape has a constant-bank instantiation (H=8, L=2: the ANYdrive
+  // net) -- handed to the kernels as a launch parameter
+  bool lstm_const;
+  const float* lstm_src;   // device pointer the copy was taken from
+  float lstm_w[1024];
 };
 
 typedef B200LabEnvState Env;
@@ -35,7 +41,9 @@ typedef B200LabSimView Sim;
 // process_action
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
-process_action_kernel(const Env* __restrict__ e, const float* __restrict__ in) {
+process_action_kernel(const __grid_constant__ Env env_param, const float* __restrict__ in) {
+  const Env* __restrict__ e = &env_param;
+
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   int A = e->A;
   int64_t total = (int64_t)e->N * A;
@@ -144,6 +152,95 @@ __device__ __forceinline__ float lstm_forward(const float* __restrict__ w, int L
   return out;
 }
 
+// ---- actuator-net weights as a KERNEL PARAMETER (constant bank, c[0][imm] operands) ---------------------------------
+// Every lane of a warp reads the same weight.  From shared memory that is one LDS per FMA, and the single LSU port per SM
+// (vs. four FMA pipes) makes the cell LDS-bound; as immediate-offset constant-bank operands the weights ride on the FFMA
+// itself and no load instruction is issued.  All indices below are compile-time after unrolling (H, L template params).
+struct NetNone { static constexpr bool kLstm = false; };
+
+template <int H, int L>
+struct NetLstm {
+  static constexpr bool kLstm = true;
+  static constexpr int kH = H, kL = L;
+  static constexpr int layer_off(int l) { return l == 0 ? 0 : (4 * H * 2 + 4 * H * H + 8 * H) + (l - 1) * (8 * H * H + 8 * H); }
+  static constexpr int kHead = layer_off(L);
+  static constexpr int kCount = kHead + H + 1;
+  float w[kCount];
+};
+
+template <class Net>
+__device__ __forceinline__ float lstm_cells_const(const Net& net, float x0, float x1, float (&h)[Net::kL][Net::kH],
+                                                  float (&c)[Net::kL][Net::kH]) {
+  constexpr int H = Net::kH, L = Net::kL;
+  float xin[H];
+  xin[0] = x0;
+  xin[1] = x1;
+#pragma unroll
+  for (int l = 0; l < L; ++l) {
+    constexpr int kIn0 = 2;
+    const int in_dim = l == 0 ? kIn0 : H;
+    const int o_ih = Net::layer_off(l), o_hh = o_ih + 4 * H * in_dim, o_bi = o_hh + 4 * H * H, o_bh = o_bi + 4 * H;
+    float hn[H];
+#pragma unroll
+    for (int u = 0; u < H; ++u) {
+      float g4[4];
+#pragma unroll
+      for (int g = 0; g < 4; ++g) {
+        const int r = g * H + u;
+        float acc = net.w[o_bi + r] + net.w[o_bh + r];
+        if (l == 0) {
+          acc = fmaf(net.w[o_ih + r * 2], xin[0], acc);
+          acc = fmaf(net.w[o_ih + r * 2 + 1], xin[1], acc);
+        } else {
+#pragma unroll
+          for (int k = 0; k < H; ++k) acc = fmaf(net.w[o_ih + r * H + k], xin[k], acc);
+        }
+#pragma unroll
+        for (int k = 0; k < H; ++k) acc = fmaf(net.w[o_hh + r * H + k], h[l][k], acc);
+        g4[g] = acc;
+      }
+      float ig = sigmoidf_(g4[0]), fg = sigmoidf_(g4[1]), gg = tanhf_(g4[2]), og = sigmoidf_(g4[3]);
+      float cn = fmaf(fg, c[l][u], ig * gg);
+      c[l][u] = cn;
+      hn[u] = og * tanhf_(cn);
+    }
+#pragma unroll
+    for (int k = 0; k < H; ++k) { h[l][k] = hn[k]; xin[k] = hn[k]; }
+  }
+  float out = net.w[Net::kHead + H];
+#pragma unroll
+  for (int k = 0; k < H; ++k) out = fmaf(net.w[Net::kHead + k], xin[k], out);
+  return out;
+}
+
+template <class Net>
+__device__ __forceinline__ void lstm_state_load(const B200LabActuatorGroup& g, int64_t row, int64_t rows,
+                                                float (&h)[Net::kL][Net::kH], float (&c)[Net::kL][Net::kH]) {
+#pragma unroll
+  for (int l = 0; l < Net::kL; ++l)
+#pragma unroll
+    for (int k = 0; k < Net::kH; k += 4) {
+      float4 a = *reinterpret_cast<const float4*>(g.lstm_h + ((int64_t)l * rows + row) * Net::kH + k);
+      float4 b = *reinterpret_cast<const float4*>(g.lstm_c + ((int64_t)l * rows + row) * Net::kH + k);
+      h[l][k] = a.x; h[l][k + 1] = a.y; h[l][k + 2] = a.z; h[l][k + 3] = a.w;
+      c[l][k] = b.x; c[l][k + 1] = b.y; c[l][k + 2] = b.z; c[l][k + 3] = b.w;
+    }
+}
+
+template <class Net>
+__device__ __forceinline__ void lstm_state_store(const B200LabActuatorGroup& g, int64_t row, int64_t rows,
+                                                 const float (&h)[Net::kL][Net::kH], const float (&c)[Net::kL][Net::kH]) {
+#pragma unroll
+  for (int l = 0; l < Net::kL; ++l)
+#pragma unroll
+    for (int k = 0; k < Net::kH; k += 4) {
+      *reinterpret_cast<float4*>(g.lstm_h + ((int64_t)l * rows + row) * Net::kH + k) =
+          make_float4(h[l][k], h[l][k + 1], h[l][k + 2], h[l][k + 3]);
+      *reinterpret_cast<float4*>(g.lstm_c + ((int64_t)l * rows + row) * Net::kH + k) =
+          make_float4(c[l][k], c[l][k + 1], c[l][k + 2], c[l][k + 3]);
+    }
+}
+
 __device__ __forceinline__ float mlp_act(float x, int kind) {
   switch (kind) {
     case 0: return x / (1.0f + fabsf(x));            // softsign
@@ -206,7 +303,7 @@ __device__ __forceinline__ void stage_net_weights(const Env* __restrict__ e, flo
 
 // One actuator evaluation for joint j of env n (Articulation._apply_actuator_model, articulation.py:1432-1469).
 // q, qd: joint state BEFORE the physics step; q_t, qd_t, ff: the joint targets.
-__device__ __forceinline__ void actuator_eval(const Env* __restrict__ e, const float* s_w, int n, int j, float q, float qd,
+__device__ __noinline__ void actuator_eval(const Env* __restrict__ e, const float* s_w, int n, int j, float q, float qd,
                                               float q_t, float qd_t, float ff, float& computed, float& applied) {
   const int N = e->N;
   const B200LabActuatorGroup& g = e->act[e->joint_group[j]];
@@ -251,12 +348,15 @@ __device__ __forceinline__ void actuator_eval(const Env* __restrict__ e, const f
   }
 }
 
+template <class Net>
 __global__ void __launch_bounds__(kActBlock)
-substep_pre_kernel(const Env* __restrict__ e, Sim sim, bool apply_action, bool only_if_any_reset) {
+substep_pre_kernel(const __grid_constant__ Env env_param, Sim sim, bool apply_action, bool only_if_any_reset,
+                   const __grid_constant__ Net net) {
+  const Env* __restrict__ e = &env_param;
   extern __shared__ float s_w[];
   const int J = e->J, N = e->N;
   if (only_if_any_reset && *e->any_reset_dev == 0) return;   // uniform over the grid
-  stage_net_weights(e, s_w);
+  if constexpr (!Net::kLstm) stage_net_weights(e, s_w);
   int64_t gid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (gid >= (int64_t)N * J) return;
   int n = (int)(gid / J), j = (int)(gid % J);
@@ -272,7 +372,20 @@ substep_pre_kernel(const Env* __restrict__ e, Sim sim, bool apply_action, bool o
   const B200LabActuatorGroup& g = e->act[gi];
   float q_t = e->joint_pos_target[gid], qd_t = e->joint_vel_target[gid], ff = e->joint_effort_target[gid];
   float computed, applied;
-  actuator_eval(e, s_w, n, j, sim.joint_pos[gid], sim.joint_vel[gid], q_t, qd_t, ff, computed, applied);
+  bool done = false;
+  if constexpr (Net::kLstm) {
+    if (g.kind == B200LAB_ACT_NET_LSTM) {
+      float h[Net::kL][Net::kH], c[Net::kL][Net::kH];
+      const int64_t rows = (int64_t)N * g.group_joints, row = (int64_t)n * g.group_joints + e->joint_local[j];
+      lstm_state_load<Net>(g, row, rows, h, c);
+      const float qd = sim.joint_vel[gid];
+      computed = lstm_cells_const(net, q_t - sim.joint_pos[gid], qd, h, c);   // actuator_net.py:76-90
+      applied = dc_motor_clip(computed, qd, g.saturation_effort, g.velocity_limit[j], g.effort_limit[j]);
+      lstm_state_store<Net>(g, row, rows, h, c);
+      done = true;
+    }
+  }
+  if (!done) actuator_eval(e, s_w, n, j, sim.joint_pos[gid], sim.joint_vel[gid], q_t, qd_t, ff, computed, applied);
   e->computed_torque[gid] = computed;
   e->applied_torque[gid] = applied;
   if (g.kind == B200LAB_ACT_IMPLICIT) {
@@ -293,7 +406,8 @@ substep_pre_kernel(const Env* __restrict__ e, Sim sim, bool apply_action, bool o
 constexpr int kPostBlock = 256;
 
 __global__ void __launch_bounds__(kPostBlock)
-substep_post_kernel(const Env* __restrict__ e, Sim sim, int W, int envs_per_block) {
+substep_post_kernel(const __grid_constant__ Env env_param, Sim sim, int W, int envs_per_block) {
+  const Env* __restrict__ e = &env_param;
   const int N = e->N, J = e->J, B = e->B;
   int el = threadIdx.x / W, i = threadIdx.x % W;
   int n = blockIdx.x * envs_per_block + el;
@@ -374,9 +488,14 @@ struct SimViews {
   int S;
 };
 
-__global__ void __launch_bounds__(kPostBlock)
-decimation_fused_kernel(const Env* __restrict__ e, const float* __restrict__ action_in, SimViews sv, int joint_blocks,
-                        int W, int envs_per_block) {
+constexpr int kFusedBlock = 128;   // 4 blocks / SM at <= 128 registers: the body-role blocks are pure memory latency
+
+template <class Net>
+__global__ void __launch_bounds__(kFusedBlock, 4)
+decimation_fused_kernel(const __grid_constant__ Env env_param, const float* __restrict__ action_in,
+                        const __grid_constant__ SimViews sv, int joint_blocks, int W, int envs_per_block,
+                        const __grid_constant__ Net net) {
+  const Env* __restrict__ e = &env_param;
   extern __shared__ float s_w[];
   const int N = e->N, J = e->J, B = e->B, A = e->A, S = sv.S;
   const float dt = e->physics_dt;
@@ -385,7 +504,7 @@ decimation_fused_kernel(const Env* __restrict__ e, const float* __restrict__ act
   int n, i;
   const bool joint_role = (int)blockIdx.x < joint_blocks;
   if (joint_role) {
-    stage_net_weights(e, s_w);
+    if constexpr (!Net::kLstm) stage_net_weights(e, s_w);
     int64_t gid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (gid >= (int64_t)N * J) return;
     n = (int)(gid / J); i = (int)(gid % J);
@@ -421,12 +540,40 @@ decimation_fused_kernel(const Env* __restrict__ e, const float* __restrict__ act
     float prev_qd = e->prev_joint_vel[o], acc = e->joint_acc[o];
     float computed = 0.f, applied = 0.f;
     float q = sv.prev.joint_pos[o], qd = sv.prev.joint_vel[o];
-    for (int s = 0; s < S; ++s) {
-      if (gi >= 0) actuator_eval(e, s_w, n, j, q, qd, q_t, qd_t, ff, computed, applied);
-      q = sv.v[s].joint_pos[o];
-      qd = sv.v[s].joint_vel[o];
-      acc = (qd - prev_qd) / dt;  // ArticulationData.update (articulation_data.py:547-556)
-      prev_qd = qd;
+    bool done = false;
+    if constexpr (Net::kLstm) {
+      if (gi >= 0 && e->act[gi].kind == B200LAB_ACT_NET_LSTM) {
+        // recurrent state stays in registers across the S evaluations (actuator_net.py:76-99)
+        const B200LabActuatorGroup& g = e->act[gi];
+        float h[Net::kL][Net::kH], c[Net::kL][Net::kH];
+        const int64_t rows = (int64_t)N * g.group_joints, row = (int64_t)n * g.group_joints + e->joint_local[j];
+        lstm_state_load<Net>(g, row, rows, h, c);
+        const float sat = g.saturation_effort, vlim = g.velocity_limit[j], elim = g.effort_limit[j];
+#pragma unroll 1
+        for (int s = 0; s < S; ++s) {
+          // next state requested before the cell math: its latency hides behind ~1k FFMAs
+          const float qn = sv.v[s].joint_pos[o], qdn = sv.v[s].joint_vel[o];
+          computed = lstm_cells_const(net, q_t - q, qd, h, c);
+          applied = dc_motor_clip(computed, qd, sat, vlim, elim);
+          acc = (qdn - prev_qd) / dt;
+          prev_qd = qdn;
+          q = qn;
+          qd = qdn;
+        }
+        lstm_state_store<Net>(g, row, rows, h, c);
+        done = true;
+      }
+    }
+    if (!done) {
+#pragma unroll 1
+      for (int s = 0; s < S; ++s) {
+        const float qn = sv.v[s].joint_pos[o], qdn = sv.v[s].joint_vel[o];
+        if (gi >= 0) actuator_eval(e, s_w, n, j, q, qd, q_t, qd_t, ff, computed, applied);
+        acc = (qdn - prev_qd) / dt;  // ArticulationData.update (articulation_data.py:547-556)
+        prev_qd = qdn;
+        q = qn;
+        qd = qdn;
+      }
     }
     e->prev_joint_vel[o] = prev_qd;
     e->joint_acc[o] = acc;
@@ -450,16 +597,29 @@ decimation_fused_kernel(const Env* __restrict__ e, const float* __restrict__ act
     float* hp = e->cs_forces_hist + ((int64_t)n * Hh * B + i) * 3;
     float hx[4], hy[4], hz[4];  // history depth <= 4 kept in registers
     const bool hreg = Hh <= 4;
-    if (hreg)
-      for (int k = 0; k < Hh; ++k) { hx[k] = hp[(int64_t)k * B * 3]; hy[k] = hp[(int64_t)k * B * 3 + 1]; hz[k] = hp[(int64_t)k * B * 3 + 2]; }
+    if (hreg) {
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+        if (k < Hh) { hx[k] = hp[(int64_t)k * B * 3]; hy[k] = hp[(int64_t)k * B * 3 + 1]; hz[k] = hp[(int64_t)k * B * 3 + 2]; }
+    }
     float fx = e->cs_net_forces_w[ob * 3], fy = e->cs_net_forces_w[ob * 3 + 1], fz = e->cs_net_forces_w[ob * 3 + 2];
-    for (int s = 0; s < S; ++s) {
+    // the S force samples are requested together (independent loads) instead of one dependent round trip per sub-step
+    float pfx[kMaxDecimation], pfy[kMaxDecimation], pfz[kMaxDecimation];
+#pragma unroll
+    for (int s = 0; s < kMaxDecimation; ++s) {
+      pfx[s] = pfy[s] = pfz[s] = 0.f;
+      if (s < S) {
+        const float* nf = sv.v[s].net_forces_w;
+        if (nf) { pfx[s] = nf[ob * 3]; pfy[s] = nf[ob * 3 + 1]; pfz[s] = nf[ob * 3 + 2]; }
+      }
+    }
+#pragma unroll
+    for (int s = 0; s < kMaxDecimation; ++s) {
+      if (s >= S) break;
       ts = ts + dt;
       outdated = outdated || ((ts - tl) + 1e-6f >= e->cs_update_period);
       if (outdated) {
-        fx = fy = fz = 0.f;
-        const float* nf = sv.v[s].net_forces_w;
-        if (nf) { fx = nf[ob * 3]; fy = nf[ob * 3 + 1]; fz = nf[ob * 3 + 2]; }
+        fx = pfx[s]; fy = pfy[s]; fz = pfz[s];
         if (hreg) {
 #pragma unroll
           for (int k = 3; k > 0; --k) if (k < Hh) { hx[k] = hx[k - 1]; hy[k] = hy[k - 1]; hz[k] = hz[k - 1]; }
@@ -486,8 +646,11 @@ decimation_fused_kernel(const Env* __restrict__ e, const float* __restrict__ act
       }
     }
     e->cs_net_forces_w[ob * 3] = fx; e->cs_net_forces_w[ob * 3 + 1] = fy; e->cs_net_forces_w[ob * 3 + 2] = fz;
-    if (hreg)
-      for (int k = 0; k < Hh; ++k) { hp[(int64_t)k * B * 3] = hx[k]; hp[(int64_t)k * B * 3 + 1] = hy[k]; hp[(int64_t)k * B * 3 + 2] = hz[k]; }
+    if (hreg) {
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+        if (k < Hh) { hp[(int64_t)k * B * 3] = hx[k]; hp[(int64_t)k * B * 3 + 1] = hy[k]; hp[(int64_t)k * B * 3 + 2] = hz[k]; }
+    }
     if (track) { e->cs_last_air_time[ob] = la; e->cs_current_air_time[ob] = ca; e->cs_last_contact_time[ob] = lc; e->cs_current_contact_time[ob] = cc; }
   }
   // ---- env scalars (one lane).  The sensor timestamps are re-derived with the same fp32 recurrence; they are
@@ -763,7 +926,8 @@ __device__ __forceinline__ void resample_command(const Env* e, int n, const floa
 constexpr int kStepWarps = 4;
 
 __global__ void __launch_bounds__(kStepWarps * 32)
-post_step_kernel(const Env* __restrict__ e, Sim sim, int64_t step) {
+post_step_kernel(const __grid_constant__ Env env_param, Sim sim, int64_t step) {
+  const Env* __restrict__ e = &env_param;   // descriptor in the constant bank: warp-uniform reads, no global round trips
   if (e->step_counter_dev) step = *e->step_counter_dev;
   const int lane = threadIdx.x & 31;
   const int n = blockIdx.x * kStepWarps + (threadIdx.x >> 5);
@@ -1009,7 +1173,8 @@ post_step_kernel(const Env* __restrict__ e, Sim sim, int64_t step) {
 constexpr int kDerived = 20;
 
 __global__ void __launch_bounds__(128)
-derive_obs_kernel(const Env* __restrict__ e, Sim sim, float* __restrict__ derived) {
+derive_obs_kernel(const __grid_constant__ Env env_param, Sim sim, float* __restrict__ derived) {
+  const Env* __restrict__ e = &env_param;
   int n = blockIdx.x * blockDim.x + threadIdx.x;
   if (n >= e->N) return;
   const float* rs = sim.root_state_w + (int64_t)n * 13;
@@ -1171,6 +1336,38 @@ static int upload_obs_tables(EnvHandle* h) {
   return B200LAB_OK;
 }
 
+typedef NetLstm<8, 2> NetLstm82;
+static_assert(NetLstm82::kCount <= 1024, "EnvHandle::lstm_w too small");
+
+static int stage_const_net(EnvHandle* h) {
+  const B200LabEnvState& s = h->host;
+  const B200LabActuatorGroup* net = nullptr;
+  for (int g = 0; g < s.num_act_groups; ++g)
+    if (s.act[g].kind == B200LAB_ACT_NET_LSTM) net = &s.act[g];
+  if (!net || net->lstm_hidden != NetLstm82::kH || net->lstm_layers != NetLstm82::kL || !net->net_weights) {
+    h->lstm_const = false;
+    h->lstm_src = nullptr;
+    return B200LAB_OK;
+  }
+  if (h->lstm_const && h->lstm_src == net->net_weights) return B200LAB_OK;
+  cudaError_t err = cudaMemcpy(h->lstm_w, net->net_weights, NetLstm82::kCount * sizeof(float), cudaMemcpyDeviceToHost);
+  if (err != cudaSuccess) { set_error("actuator net weights: %s", cudaGetErrorString(err)); return B200LAB_ERR_CUDA; }
+  h->lstm_const = true;
+  h->lstm_src = net->net_weights;
+  return B200LAB_OK;
+}
+
+static void launch_substep_pre(EnvHandle* h, const B200LabSimView* sim, bool apply_action, bool only_if_any_reset,
+                               size_t smem, cudaStream_t stream) {
+  int64_t total = (int64_t)h->host.N * h->host.J;
+  unsigned blocks = (unsigned)ceil_div(total, kActBlock);
+  if (h->lstm_const)
+    substep_pre_kernel<NetLstm82><<<blocks, kActBlock, 0, stream>>>(h->host, *sim, apply_action, only_if_any_reset,
+                                                                    *reinterpret_cast<const NetLstm82*>(h->lstm_w));
+  else
+    substep_pre_kernel<NetNone><<<blocks, kActBlock, smem, stream>>>(h->host, *sim, apply_action, only_if_any_reset, NetNone{});
+}
+
 extern "C" {
 
 void* b200lab_env_create(const B200LabEnvState* st) {
@@ -1178,16 +1375,20 @@ void* b200lab_env_create(const B200LabEnvState* st) {
   EnvHandle* h = (EnvHandle*)malloc(sizeof(EnvHandle));
   if (!h) return nullptr;
   h->host = *st;
-  h->dev = nullptr;
   h->col_term = nullptr;
   h->col_src = nullptr;
   h->derived = nullptr;
-  cudaError_t err = cudaMalloc((void**)&h->dev, sizeof(B200LabEnvState));
-  if (err == cudaSuccess) err = cudaMalloc((void**)&h->derived, (size_t)st->N * 20 * sizeof(float));
+  h->lstm_const = false;
+  h->lstm_src = nullptr;
+  h->dev = nullptr;
+  cudaError_t err = cudaMalloc((void**)&h->derived, (size_t)st->N * 20 * sizeof(float));
+  if (err == cudaSuccess) err = cudaMalloc((void**)&h->dev, sizeof(B200LabEnvState));
   if (err == cudaSuccess) err = cudaMemcpy(h->dev, st, sizeof(B200LabEnvState), cudaMemcpyHostToDevice);
   if (err == cudaSuccess && upload_obs_tables(h) != 0) err = cudaErrorUnknown;
+  if (err == cudaSuccess && stage_const_net(h) != 0) err = cudaErrorUnknown;
   if (err != cudaSuccess) {
     if (err != cudaErrorUnknown) set_error("b200lab_env_create: %s", cudaGetErrorString(err));
+    if (h->derived) cudaFree(h->derived);
     if (h->dev) cudaFree(h->dev);
     free(h);
     return nullptr;
@@ -1201,6 +1402,8 @@ int b200lab_env_update(void* env, const B200LabEnvState* st) {
   h->host = *st;
   cudaError_t err = cudaMemcpy(h->dev, st, sizeof(B200LabEnvState), cudaMemcpyHostToDevice);
   if (err != cudaSuccess) { set_error("b200lab_env_update: %s", cudaGetErrorString(err)); return B200LAB_ERR_CUDA; }
+  int rc = stage_const_net(h);
+  if (rc) return rc;
   return upload_obs_tables(h);
 }
 
@@ -1218,7 +1421,7 @@ int b200lab_process_action(void* env, const float* action_in, void* stream) {
   B200LAB_CHECK_ARG(env && action_in, "null argument");
   EnvHandle* h = (EnvHandle*)env;
   int64_t total = (int64_t)h->host.N * h->host.A;
-  process_action_kernel<<<(unsigned)ceil_div(total, 256), 256, 0, (cudaStream_t)stream>>>(h->dev, action_in);
+  process_action_kernel<<<(unsigned)ceil_div(total, 256), 256, 0, (cudaStream_t)stream>>>(h->host, action_in);
   count_launch();
   return check_launch("process_action");
 }
@@ -1258,8 +1461,7 @@ int b200lab_substep_pre(void* env, const B200LabSimView* sim, void* stream) {
   int rc = net_smem_bytes(s, &smem);
   if (rc) return rc;
   int64_t total = (int64_t)s.N * s.J;
-  substep_pre_kernel<<<(unsigned)ceil_div(total, kActBlock), kActBlock, smem, (cudaStream_t)stream>>>(h->dev, *sim, true,
-                                                                                                      false);
+  launch_substep_pre(h, sim, true, false, smem, (cudaStream_t)stream);
   count_launch();
   return check_launch("substep_pre");
 }
@@ -1273,8 +1475,7 @@ int b200lab_post_reset_write(void* env, const B200LabSimView* sim, void* stream)
   int rc = net_smem_bytes(s, &smem);
   if (rc) return rc;
   int64_t total = (int64_t)s.N * s.J;
-  substep_pre_kernel<<<(unsigned)ceil_div(total, kActBlock), kActBlock, smem, (cudaStream_t)stream>>>(h->dev, *sim, false,
-                                                                                                      true);
+  launch_substep_pre(h, sim, false, true, smem, (cudaStream_t)stream);
   count_launch();
   return check_launch("post_reset_write");
 }
@@ -1286,7 +1487,7 @@ int b200lab_substep_post(void* env, const B200LabSimView* sim, void* stream) {
   int W, epb;
   int width = s.J > s.B ? s.J : s.B;
   B200LAB_CHECK_ARG(launch_geometry(width, &W, &epb) == 0, "max(J,B) must be <= 256");
-  substep_post_kernel<<<(unsigned)ceil_div(s.N, epb), kPostBlock, 0, (cudaStream_t)stream>>>(h->dev, *sim, W, epb);
+  substep_post_kernel<<<(unsigned)ceil_div(s.N, epb), kPostBlock, 0, (cudaStream_t)stream>>>(h->host, *sim, W, epb);
   count_launch();
   return check_launch("substep_post");
 }
@@ -1309,11 +1510,18 @@ int b200lab_decimation_fused(void* env, const float* action_in, const B200LabSim
   }
   for (int k = num_substeps; k < kMaxDecimation; ++k) sv.v[k] = views[num_substeps - 1];
   int W, epb;
-  B200LAB_CHECK_ARG(launch_geometry(s.B > 0 ? s.B : 1, &W, &epb) == 0, "B must be <= 256");
-  int joint_blocks = (int)ceil_div((int64_t)s.N * s.J, kPostBlock);
+  B200LAB_CHECK_ARG(s.B <= kFusedBlock, "B must be <= 128");
+  W = s.B > 0 ? s.B : 1;
+  epb = kFusedBlock / W;
+  int joint_blocks = (int)ceil_div((int64_t)s.N * s.J, kFusedBlock);
   int body_blocks = (int)ceil_div(s.N, epb);
-  decimation_fused_kernel<<<(unsigned)(joint_blocks + body_blocks), kPostBlock, smem, (cudaStream_t)stream>>>(
-      h->dev, action_in, sv, joint_blocks, W, epb);
+  if (h->lstm_const) {
+    decimation_fused_kernel<NetLstm82><<<(unsigned)(joint_blocks + body_blocks), kFusedBlock, 0, (cudaStream_t)stream>>>(
+        h->host, action_in, sv, joint_blocks, W, epb, *reinterpret_cast<const NetLstm82*>(h->lstm_w));
+  } else {
+    decimation_fused_kernel<NetNone><<<(unsigned)(joint_blocks + body_blocks), kFusedBlock, smem, (cudaStream_t)stream>>>(
+        h->host, action_in, sv, joint_blocks, W, epb, NetNone{});
+  }
   count_launch();
   return check_launch("decimation_fused");
 }
@@ -1323,7 +1531,7 @@ int b200lab_post_step(void* env, const B200LabSimView* sim, int64_t step_counter
   EnvHandle* h = (EnvHandle*)env;
   const B200LabEnvState& s = h->host;
   B200LAB_CHECK_ARG(s.J <= 64 && s.B <= 64, "joint/body masks support up to 64 joints/bodies");
-  post_step_kernel<<<(unsigned)ceil_div(s.N, kStepWarps), kStepWarps * 32, 0, (cudaStream_t)stream>>>(h->dev, *sim, step_counter);
+  post_step_kernel<<<(unsigned)ceil_div(s.N, kStepWarps), kStepWarps * 32, 0, (cudaStream_t)stream>>>(h->host, *sim, step_counter);
   count_launch();
   return check_launch("post_step");
 }
@@ -1333,7 +1541,7 @@ int b200lab_compute_obs(void* env, const B200LabSimView* sim, int64_t step_count
   EnvHandle* h = (EnvHandle*)env;
   const B200LabEnvState& s = h->host;
   cudaStream_t st_ = (cudaStream_t)stream;
-  derive_obs_kernel<<<(unsigned)ceil_div(s.N, 128), 128, 0, st_>>>(h->dev, *sim, h->derived);
+  derive_obs_kernel<<<(unsigned)ceil_div(s.N, 128), 128, 0, st_>>>(h->host, *sim, h->derived);
   count_launch();
   int64_t total = (int64_t)s.N * s.obs_dim;
   if (h->rays_vertical)

@@ -87,8 +87,26 @@ __device__ __forceinline__ float ray_tri(const MeshAccel& m, int f, f3 o, f3 d) 
   return t > 0.0f ? t : -1.0f;
 }
 
-// Vertical closest hit: one cell.  Candidates are fetched two at a time so the dependent chain
-// cell_start -> cell_tris -> record is paid once per pair, not once per triangle.
+// Projected test on an already-fetched record.
+__device__ __forceinline__ float ray_tri_vertical_rec(const MeshAccel& m, int f, float4 a, float4 b, float4 c, f3 o, float dz,
+                                                      float inv_dz) {
+  float tx = o.x - a.x, ty = o.y - a.y;
+  if (a.w == 0.0f) return -1.0f;  // degenerate in xy (vertical wall): a vertical ray cannot hit its interior
+  float u = (tx * c.x - ty * b.w) * a.w;   // (tx*e2y - ty*e2x) / det2
+  float v = (ty * b.x - tx * b.y) * a.w;   // (ty*e1x - tx*e1y) / det2
+  float w = 1.0f - u - v;
+  if (u < -kBaryBand || v < -kBaryBand || w < -kBaryBand) return -1.0f;
+  if (u < kBaryBand || v < kBaryBand || w < kBaryBand) return ray_tri_f64(m.tris + (size_t)f * 9, o, f3{0.f, 0.f, dz});
+  float zh = a.z + u * b.z + v * c.y;
+  float t = (zh - o.z) * inv_dz;
+  return t > 0.0f ? t : -1.0f;
+}
+
+// Vertical closest hit: one cell.  The query is three dependent round trips to L2 (cell range -> triangle ids ->
+// records), so each level is requested for up to kVertBatch candidates at once: a typical cell (<= 4 candidates)
+// costs exactly three latencies, and every lane of a warp runs the same single trip.
+constexpr int kVertBatch = 2;
+
 __device__ __forceinline__ bool raycast_vertical(const MeshAccel& m, f3 o, float dz, float max_dist, float& t_out,
                                                  int& face_out) {
   float t_best = max_dist;
@@ -98,13 +116,21 @@ __device__ __forceinline__ bool raycast_vertical(const MeshAccel& m, f3 o, float
     int c = cy * m.nx + cx;
     int s = __ldg(m.cell_start + c), e = __ldg(m.cell_start + c + 1);
     float inv_dz = 1.0f / dz;
-    for (int k = s; k < e; k += 2) {
-      int f0 = __ldg(m.cell_tris + k);
-      int f1 = (k + 1 < e) ? __ldg(m.cell_tris + k + 1) : f0;
-      float t0 = ray_tri_vertical(m, f0, o, dz, inv_dz);
-      float t1 = ray_tri_vertical(m, f1, o, dz, inv_dz);
-      if (t0 > 0.0f && t0 <= t_best) { t_best = t0; face_best = f0; }
-      if (t1 > 0.0f && t1 <= t_best) { t_best = t1; face_best = f1; }
+    for (int k = s; k < e; k += kVertBatch) {
+      int f[kVertBatch];
+#pragma unroll
+      for (int i = 0; i < kVertBatch; ++i) f[i] = __ldg(m.cell_tris + min(k + i, e - 1));
+      float4 ra[kVertBatch], rb[kVertBatch], rc[kVertBatch];
+#pragma unroll
+      for (int i = 0; i < kVertBatch; ++i) {
+        const float4* r = m.rec + (size_t)f[i] * 3;
+        ra[i] = __ldg(r); rb[i] = __ldg(r + 1); rc[i] = __ldg(r + 2);
+      }
+#pragma unroll
+      for (int i = 0; i < kVertBatch; ++i) {
+        float t = ray_tri_vertical_rec(m, f[i], ra[i], rb[i], rc[i], o, dz, inv_dz);   // padded slots repeat the last id
+        if (t > 0.0f && t <= t_best) { t_best = t; face_best = f[i]; }
+      }
     }
   }
   t_out = t_best;
