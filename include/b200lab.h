@@ -393,6 +393,11 @@ int b200lab_post_reset_write(void* env, const B200LabSimView* sim, void* stream)
  * raycast_mesh for outdated envs (ray_caster.py:220-260, LAB/utils/warp/ops.py:24-127). */
 int b200lab_compute_obs(void* env, const B200LabSimView* sim, int64_t step_counter, void* stream);
 
+/* post_reset_write and compute_obs issued together: the actuator pass runs on a library-owned side stream forked from
+ * and joined back into `stream` (both are latency-bound and touch disjoint buffers), everything `stream` enqueues
+ * afterwards sees both results.  Same results as the two calls in sequence. */
+int b200lab_step_tail(void* env, const B200LabSimView* sim, int64_t step_counter, void* stream);
+
 /* ------------------------------------------------------------------------------------------------
  * Ray casting.  Replaces convert_to_warp_mesh (LAB/utils/warp/ops.py:130-145) and raycast_mesh
  * (ops.py:24-127 / kernels.py:13-75).

@@ -29,6 +29,8 @@ struct EnvHandle {
   int16_t* col_src;    // [obs_dim] obs column -> joint index (joint terms) or index inside the term
   // host copy of the ActuatorNetLSTM weights when their shape has a constant-bank instantiation (H=8, L=2: the ANYdrive
   // net) -- handed to the kernels as a launch parameter
+  cudaStream_t side;       // second stream + fork/join events of b200lab_step_tail
+  cudaEvent_t ev_fork, ev_join;
   bool lstm_const;
   const float* lstm_src;   // device pointer the copy was taken from
   float lstm_w[1024];
@@ -71,10 +73,14 @@ constexpr int kMaxNetFloats = 8192;  // staged net weights (32 KB)
 // LSTM gate activations on the SFU path (ex2.approx + fast divide): |error| ~ 1e-6 absolute on the gate values, far below
 // the 2e-5 torque tolerance of the parity tests; the IEEE expf/tanhf/divide sequences were half of the actuator kernel's
 // instructions (profiles/r1_notes.md).
-__device__ __forceinline__ float sigmoidf_(float x) { return __fdividef(1.0f, 1.0f + __expf(-x)); }
+__device__ __forceinline__ float ex2_ftz(float x) { float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+__device__ __forceinline__ float rcp_ftz(float x) { float y; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+// 4 instructions (FMUL, MUFU.EX2, FADD, MUFU.RCP); the non-ftz __expf/__fdividef forms add denormal range scaling
+// around each MUFU (~2.5x the instructions) for inputs the gates never see
+__device__ __forceinline__ float sigmoidf_(float x) { return rcp_ftz(1.0f + ex2_ftz(-1.4426950408889634f * x)); }
 __device__ __forceinline__ float tanhf_(float x) {
-  float a = fabsf(x);
-  float t = 1.0f - __fdividef(2.0f, __expf(2.0f * a) + 1.0f);   // exp overflow -> inf -> t = 1
+  float e = ex2_ftz(2.8853900817779268f * fabsf(x));   // exp(2|x|); overflow -> inf -> rcp -> 0 -> t = 1
+  float t = fmaf(-2.0f, rcp_ftz(e + 1.0f), 1.0f);
   return copysignf(t, x);
 }
 
@@ -925,7 +931,7 @@ __device__ __forceinline__ void resample_command(const Env* e, int n, const floa
 
 constexpr int kStepWarps = 4;
 
-__global__ void __launch_bounds__(kStepWarps * 32)
+__global__ void __launch_bounds__(kStepWarps * 32, 6)
 post_step_kernel(const __grid_constant__ Env env_param, Sim sim, int64_t step) {
   const Env* __restrict__ e = &env_param;   // descriptor in the constant bank: warp-uniform reads, no global round trips
   if (e->step_counter_dev) step = *e->step_counter_dev;
@@ -942,6 +948,19 @@ post_step_kernel(const __grid_constant__ Env env_param, Sim sim, int64_t step) {
   derive_state(c, rs);
   c.cmd = {0.f, 0.f, 0.f};
   if (e->has_command) c.cmd = {e->cmd_vel_b[n * 3], e->cmd_vel_b[n * 3 + 1], e->cmd_vel_b[n * 3 + 2]};
+  // Every per-env scalar the tail of the step reads is requested HERE, together with the rows above: the stores that
+  // follow (no-alias cannot be proven) would otherwise serialise each of these loads behind an L2 round trip.
+  float pre_mxy = 0.f, pre_myaw = 0.f, pre_tl = 0.f, pre_ht = 0.f;
+  bool pre_ih = false, pre_is = false;
+  if (e->has_command) {
+    pre_mxy = e->cmd_metric_xy[n]; pre_myaw = e->cmd_metric_yaw[n]; pre_tl = e->cmd_time_left[n];
+    pre_is = e->cmd_is_standing[n] != 0;
+    if (e->cmd_heading_command) { pre_ih = e->cmd_is_heading[n] != 0; pre_ht = e->cmd_heading_target[n]; }
+  }
+  float pre_itl[B200LAB_MAX_INTERVAL_EVENTS];
+#pragma unroll
+  for (int k = 0; k < B200LAB_MAX_INTERVAL_EVENTS; ++k) pre_itl[k] = k < e->num_interval ? e->ev_interval_time_left[k][n] : 0.f;
+  const float pre_esum = lane < e->num_rew ? e->episode_sums[(int64_t)lane * N + n] : 0.f;
   // -- episode counter (manager_based_rl_env.py:200)
   int64_t ep_len = e->episode_length_buf[n] + 1;
   // -- terminations (termination_manager.py:151-174)
@@ -967,7 +986,7 @@ post_step_kernel(const __grid_constant__ Env env_param, Sim sim, int64_t step) {
       if (lane == r) { mine = value; mine_on = true; }
     }
     if (mine_on) {
-      e->episode_sums[(int64_t)lane * N + n] += mine;
+      e->episode_sums[(int64_t)lane * N + n] = pre_esum + mine;
       e->step_reward[(int64_t)n * e->num_rew + lane] = mine / dt;
     }
     if (lane == 0) {
@@ -1119,6 +1138,11 @@ post_step_kernel(const __grid_constant__ Env env_param, Sim sim, int64_t step) {
       c.cmd.z = __shfl_sync(0xffffffffu, c.cmd.z, 0);
     }
     ep_len = 0;  // manager_based_rl_env.py:392
+    if (e->has_command) {   // the command reset above rewrote these (same lane: program order)
+      pre_mxy = 0.f; pre_myaw = 0.f; pre_tl = e->cmd_time_left[n];
+      pre_is = e->cmd_is_standing[n] != 0;
+      if (e->cmd_heading_command) { pre_ih = e->cmd_is_heading[n] != 0; pre_ht = e->cmd_heading_target[n]; }
+    }
   }
   if (lane == 0) e->episode_length_buf[n] = ep_len;
   __syncwarp();
@@ -1127,31 +1151,35 @@ post_step_kernel(const __grid_constant__ Env env_param, Sim sim, int64_t step) {
     if (lane == 0) {
       // _update_metrics (velocity_command.py:111-120)
       float ex = c.cmd.x - c.lin_b.x, ey = c.cmd.y - c.lin_b.y;
-      e->cmd_metric_xy[n] += sqrtf(ex * ex + ey * ey) / e->cmd_max_command_step;
-      e->cmd_metric_yaw[n] += fabsf(c.cmd.z - c.ang_b.z) / e->cmd_max_command_step;
-      float tl = e->cmd_time_left[n] - e->step_dt;
+      e->cmd_metric_xy[n] = pre_mxy + sqrtf(ex * ex + ey * ey) / e->cmd_max_command_step;
+      e->cmd_metric_yaw[n] = pre_myaw + fabsf(c.cmd.z - c.ang_b.z) / e->cmd_max_command_step;
+      float tl = pre_tl - e->step_dt;
       e->cmd_time_left[n] = tl;
       if (tl <= 0.0f) {
         float u[7];
 #pragma unroll
         for (int k = 0; k < 7; ++k) u[k] = u_step_at(e, n, B200LAB_U_STEP_CMD + k, step);
         resample_command(e, n, u, c.cmd);
+        pre_is = e->cmd_is_standing[n] != 0;
+        if (e->cmd_heading_command) { pre_ih = e->cmd_is_heading[n] != 0; pre_ht = e->cmd_heading_target[n]; }
       }
       // _update_command (velocity_command.py:140-160)
-      if (e->cmd_heading_command && e->cmd_is_heading[n]) {
+      if (e->cmd_heading_command && pre_ih) {
         f3 fw = quat_apply(c.q, f3{1.f, 0.f, 0.f});            // heading_w, articulation_data.py:518-526
         float heading = atan2f(fw.y, fw.x);
-        float err = wrap_to_pi(e->cmd_heading_target[n] - heading);
+        float err = wrap_to_pi(pre_ht - heading);
         c.cmd.z = fminf(fmaxf(e->cmd_heading_stiffness * err, e->cmd_range[4]), e->cmd_range[5]);
       }
-      if (e->cmd_is_standing[n]) c.cmd = {0.f, 0.f, 0.f};
+      if (pre_is) c.cmd = {0.f, 0.f, 0.f};
       e->cmd_vel_b[n * 3] = c.cmd.x; e->cmd_vel_b[n * 3 + 1] = c.cmd.y; e->cmd_vel_b[n * 3 + 2] = c.cmd.z;
     }
   }
   // -- interval events: push_by_setting_velocity (event_manager.py:204-229, events.py:795-820)
   if (lane == 0) {
-    for (int k = 0; k < e->num_interval; ++k) {
-      float tl = e->ev_interval_time_left[k][n] - e->step_dt;
+#pragma unroll
+    for (int k = 0; k < B200LAB_MAX_INTERVAL_EVENTS; ++k) {
+      if (k >= e->num_interval) break;
+      float tl = pre_itl[k] - e->step_dt;
       if (tl < 1e-6f) {
         int base = B200LAB_U_STEP_INTERVAL + 7 * k;
         tl = u_step_at(e, n, base, step) * e->ev_interval_range[k][1] + e->ev_interval_range[k][0];
@@ -1381,7 +1409,12 @@ void* b200lab_env_create(const B200LabEnvState* st) {
   h->lstm_const = false;
   h->lstm_src = nullptr;
   h->dev = nullptr;
+  h->side = nullptr;
+  h->ev_fork = h->ev_join = nullptr;
   cudaError_t err = cudaMalloc((void**)&h->derived, (size_t)st->N * 20 * sizeof(float));
+  if (err == cudaSuccess) err = cudaStreamCreateWithFlags(&h->side, cudaStreamNonBlocking);
+  if (err == cudaSuccess) err = cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming);
+  if (err == cudaSuccess) err = cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming);
   if (err == cudaSuccess) err = cudaMalloc((void**)&h->dev, sizeof(B200LabEnvState));
   if (err == cudaSuccess) err = cudaMemcpy(h->dev, st, sizeof(B200LabEnvState), cudaMemcpyHostToDevice);
   if (err == cudaSuccess && upload_obs_tables(h) != 0) err = cudaErrorUnknown;
@@ -1411,6 +1444,9 @@ void b200lab_env_destroy(void* env) {
   if (!env) return;
   EnvHandle* h = (EnvHandle*)env;
   if (h->dev) cudaFree(h->dev);
+  if (h->side) cudaStreamDestroy(h->side);
+  if (h->ev_fork) cudaEventDestroy(h->ev_fork);
+  if (h->ev_join) cudaEventDestroy(h->ev_join);
   if (h->col_term) cudaFree(h->col_term);
   if (h->col_src) cudaFree(h->col_src);
   if (h->derived) cudaFree(h->derived);
@@ -1552,5 +1588,24 @@ int b200lab_compute_obs(void* env, const B200LabSimView* sim, int64_t step_count
                                                                                h->col_src, h->derived);
   count_launch();
   return check_launch("compute_obs");
+}
+
+int b200lab_step_tail(void* env, const B200LabSimView* sim, int64_t step_counter, void* stream) {
+  B200LAB_CHECK_ARG(env && sim && sim->root_state_w && sim->joint_pos && sim->joint_vel, "null argument");
+  EnvHandle* h = (EnvHandle*)env;
+  cudaStream_t st_ = (cudaStream_t)stream;
+  // fork: the actuator pass and the observation kernels touch disjoint buffers (none of the library's observation terms
+  // reads actuator outputs) and are both latency-bound, so they share the SMs
+  cudaError_t err = cudaEventRecord(h->ev_fork, st_);
+  if (err == cudaSuccess) err = cudaStreamWaitEvent(h->side, h->ev_fork, 0);
+  if (err != cudaSuccess) { set_error("b200lab_step_tail: %s", cudaGetErrorString(err)); return B200LAB_ERR_CUDA; }
+  int rc = b200lab_post_reset_write(env, sim, h->side);
+  if (rc) return rc;
+  rc = b200lab_compute_obs(env, sim, step_counter, stream);
+  if (rc) return rc;
+  err = cudaEventRecord(h->ev_join, h->side);
+  if (err == cudaSuccess) err = cudaStreamWaitEvent(st_, h->ev_join, 0);
+  if (err != cudaSuccess) { set_error("b200lab_step_tail: %s", cudaGetErrorString(err)); return B200LAB_ERR_CUDA; }
+  return B200LAB_OK;
 }
 }

@@ -434,6 +434,11 @@ class FusedEnv:
         """`scene.write_data_to_sim()` after `_reset_idx` (manager_based_rl_env.py:217-223); device-side condition."""
         _lib.check(self.L.b200lab_post_reset_write(self.handle, sim.ref, _lib.current_stream()))
 
+    def step_tail(self, sim: SimView):
+        """post_reset_write + compute_obs, overlapped (b200lab_step_tail)."""
+        _lib.check(self.L.b200lab_step_tail(self.handle, sim.ref, self.step_counter, _lib.current_stream()))
+        return self.obs_buf
+
     def compute_obs(self, sim: SimView):
         _lib.check(self.L.b200lab_compute_obs(self.handle, sim.ref, self.step_counter, _lib.current_stream()))
         return self.obs_buf
@@ -468,7 +473,10 @@ class FusedEnv:
                 self.substep_post(sim)
                 prev = sim
         self.post_step(prev)
-        self.post_reset_write(prev)
-        self.compute_obs(prev)
+        if fused:
+            self.step_tail(prev)
+        else:
+            self.post_reset_write(prev)
+            self.compute_obs(prev)
         self.step_counter += 1
         return self.obs_buf, self.reward_buf, self.terminated, self.truncated
