@@ -12,6 +12,7 @@ from __future__ import annotations
 
 import argparse
 import json
+import math
 import os
 import subprocess
 import sys
@@ -248,12 +249,127 @@ def run_ours(args):
                                   f"decimation {S}", "envs_per_gpu": N, "l2_policy": f"{K_SLABS} state slabs "
                                   f"({sim.bytes() >> 20} MiB > 126 MiB L2) cycled", "parallelism": f"env-shard x{world}"},
            "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roof}
+    del env, host_sim, fus, sim
+    torch.cuda.empty_cache()
+    out["ppo_update"] = time_ppo_update(dev, precision=2)
+    out["ppo_update"]["fp32_ffma_s_per_iter"] = time_ppo_update(dev, precision=0)["s_per_iter"]
     if rank == 0:
         if world == 1 and not args.no_cpu_baseline:
             out["cpu_baseline"] = cpu_baseline(spec, slabs, init, budget_s=15.0)
+            out["cpu_baseline"]["ppo_update"] = cpu_ppo_baseline()
         print(json.dumps(out))
     if world > 1:
         dist.destroy_process_group()
+
+
+PPO_CFG = dict(N=ENVS_PER_GPU, T=24, obs_dim=235, act_dim=12, hidden=[512, 256, 128], epochs=5, mini_batches=4, clip_param=0.2,
+               gamma=0.99, lam=0.95, value_loss_coef=1.0, entropy_coef=0.005, learning_rate=1e-3, max_grad_norm=1.0,
+               desired_kl=0.01)   # config 3: TASKS/.../anymal_c/agents/rsl_rl_ppo_cfg.py (AnymalCRoughPPORunnerCfg)
+
+
+def synthetic_rollout(c, seed):
+    """SURVEY 8d rollout: obs N(0,1), actions N(0,1), mu N(0,1), sigma 1, values N(0,1), rewards N(0,0.05), dones
+    Bernoulli(0.01), log-prob consistent with (a, mu, sigma)."""
+    g = torch.Generator().manual_seed(seed)
+    T, N, D, A = c["T"], c["N"], c["obs_dim"], c["act_dim"]
+    r = dict(observations=torch.randn(T, N, D, generator=g), actions=torch.randn(T, N, A, generator=g),
+             mu=torch.randn(T, N, A, generator=g), sigma=torch.ones(T, N, A), values=torch.randn(T, N, 1, generator=g),
+             rewards=0.05 * torch.randn(T, N, 1, generator=g), dones=(torch.rand(T, N, 1, generator=g) < 0.01).to(torch.uint8))
+    r["actions_log_prob"] = (-0.5 * ((r["actions"] - r["mu"]) / r["sigma"]) ** 2 - torch.log(r["sigma"])
+                             - 0.5 * math.log(2 * math.pi)).sum(-1, keepdim=True)
+    r["last_values"] = torch.randn(N, 1, generator=g)
+    return r
+
+
+def ppo_flops_per_iter(c):
+    dims = [c["obs_dim"], *c["hidden"]]
+    fwd = 2 * (sum(a * b for a, b in zip(dims[:-1], dims[1:])) * 2 + c["hidden"][-1] * (c["act_dim"] + 1))
+    return 3.0 * fwd * c["T"] * c["N"] * c["epochs"]   # fwd + dX + dW (upper bound, SURVEY 8d)
+
+
+def time_ppo_update(dev, reps=3, precision=2):
+    """Second half of the metric: PPO update s/iter = GAE + 5 epochs x 4 minibatches (gather, actor/critic fwd, fused
+    loss fwd+bwd, bwd GEMMs, KL-adaptive LR, clip + Adam) at config-3 shapes, CUDA events on the launching stream."""
+    from isaaclab_b200.rsl_rl import PPO, ActorCritic, TensorDict
+    c = PPO_CFG
+    torch.manual_seed(1234 + 3)
+    obs0 = TensorDict({"policy": torch.zeros(c["N"], c["obs_dim"], device=dev)}, batch_size=[c["N"]])
+    pol = ActorCritic(obs0, {"policy": ["policy"], "critic": ["policy"]}, c["act_dim"], actor_hidden_dims=c["hidden"],
+                      critic_hidden_dims=c["hidden"], device=dev, precision=precision)
+    alg = PPO(pol, num_learning_epochs=c["epochs"], num_mini_batches=c["mini_batches"], clip_param=c["clip_param"],
+              gamma=c["gamma"], lam=c["lam"], value_loss_coef=c["value_loss_coef"], entropy_coef=c["entropy_coef"],
+              learning_rate=c["learning_rate"], max_grad_norm=c["max_grad_norm"], desired_kl=c["desired_kl"], device=dev)
+    alg.init_storage("rl", c["N"], c["T"], obs0, [c["act_dim"]])
+    roll = {k: v.to(dev) for k, v in synthetic_rollout(c, 1234 + 3).items()}
+    st = alg.storage
+    L = __import__("isaaclab_b200._lib", fromlist=["lib"]).lib()
+
+    def load():
+        st.observations["policy"].copy_(roll["observations"])
+        for k in ("actions", "rewards", "values", "actions_log_prob", "mu", "sigma", "dones"):
+            getattr(st, k).copy_(roll[k])
+        st.step = c["T"]
+
+    times_gae, times_upd, launches = [], [], 0
+    for i in range(reps + 1):
+        load()
+        torch.cuda.synchronize()
+        l0 = L.b200lab_launch_count()
+        e = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+        e[0].record()
+        st.compute_returns(roll["last_values"], c["gamma"], c["lam"])
+        e[1].record()
+        loss = alg.update()
+        e[2].record()
+        torch.cuda.synchronize()
+        if i > 0:   # first iteration = warm-up (buffer allocation)
+            times_gae.append(e[0].elapsed_time(e[1]))
+            times_upd.append(e[1].elapsed_time(e[2]))
+            launches = L.b200lab_launch_count() - l0
+    gae_ms, upd_ms = min(times_gae), sorted(times_upd)[len(times_upd) // 2]
+    s_iter = (gae_ms + upd_ms) * 1e-3
+    return {"s_per_iter": round(s_iter, 5), "gae_ms": round(gae_ms, 4), "update_ms": round(upd_ms, 3),
+            "tflops": round(ppo_flops_per_iter(c) / (upd_ms * 1e-3) / 1e12, 2), "gpu_launches": int(launches),
+            "precision": {0: "fp32 FFMA (SIMT)", 1: "tf32 tcgen05 (reduced precision)",
+                          2: "3xTF32 tcgen05 (fp32-accurate split; heads < 32 wide on FFMA)"}[pol.precision],
+            "config": f"cfg 3: N={c['N']} T={c['T']} obs={c['obs_dim']} act={c['act_dim']} hidden={c['hidden']} "
+                      f"{c['epochs']} epochs x {c['mini_batches']} minibatches of {c['N'] * c['T'] // c['mini_batches']}",
+            "loss": {k: round(float(v), 6) for k, v in loss.items()}}
+
+
+def cpu_ppo_baseline(budget_updates=2, threads=None):
+    """Oracle port of PPO.update on the host cores: `budget_updates` of the 20 minibatch updates of one iteration at
+    config-3 shapes (+ GAE), scaled to s/iter."""
+    from oracle import rsl_rl as O
+    threads = threads or os.cpu_count()
+    torch.set_num_threads(threads)
+    c = PPO_CFG
+    roll = synthetic_rollout(c, 1234 + 3)
+    g = torch.Generator().manual_seed(7)
+    dims = [c["obs_dim"], *c["hidden"]]
+    params = {}
+    for net, out in (("actor", c["act_dim"]), ("critic", 1)):
+        ds = dims + [out]
+        for i, (a, b) in enumerate(zip(ds[:-1], ds[1:])):
+            k = 1.0 / math.sqrt(a)
+            params[f"{net}.{2 * i}.weight"] = (torch.rand(b, a, generator=g) * 2 - 1) * k
+            params[f"{net}.{2 * i}.bias"] = (torch.rand(b, generator=g) * 2 - 1) * k
+    params["std"] = torch.ones(c["act_dim"])
+    t0 = time.perf_counter()
+    ret, adv = O.compute_returns(roll["rewards"], roll["values"], roll["dones"], roll["last_values"], c["gamma"], c["lam"])
+    gae_s = time.perf_counter() - t0
+    storage = dict(observations=roll["observations"], actions=roll["actions"], values=roll["values"], advantages=adv,
+                   returns=ret, actions_log_prob=roll["actions_log_prob"], mu=roll["mu"], sigma=roll["sigma"])
+    B = c["T"] * c["N"]
+    mb = B // c["mini_batches"]
+    idx = torch.randperm(B, generator=g)[: mb * budget_updates]
+    cfg = dict(c, mini_batches=budget_updates, epochs=1)
+    sub = {k: v.flatten(0, 1)[idx].unsqueeze(0) for k, v in storage.items()}   # [1, mb*k, .] -> k minibatches
+    t0 = time.perf_counter()
+    O.ppo_update(params, sub, torch.arange(mb * budget_updates), cfg, c["learning_rate"])
+    upd_s = (time.perf_counter() - t0) / budget_updates * c["mini_batches"] * c["epochs"]
+    return {"s_per_iter": round(gae_s + upd_s, 3), "gae_ms": round(gae_s * 1e3, 2), "cores": threads, "kind": "port",
+            "sample": f"GAE + {budget_updates} of {c['mini_batches'] * c['epochs']} minibatch updates (scaled), torch CPU autograd"}
 
 
 def cpu_baseline(spec, slabs, init, budget_s=15.0, threads=None, max_steps=10**9):

@@ -27,6 +27,7 @@ constexpr int kNumSMs = 148;  // B200
 
 __host__ __device__ inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
 __host__ __device__ inline int64_t min64(int64_t a, int64_t b) { return a < b ? a : b; }
+__device__ __forceinline__ float elu_f(float x) { return x > 0.0f ? x : expm1f(x); }   // nn.ELU, alpha = 1
 
 struct f3 {
   float x, y, z;

@@ -13,13 +13,16 @@
 
 namespace b200lab {
 
-int linear_fwd_tc(const float* X, const float* W, const float* b, float* Y, int64_t M, int K, int Nout, int elu,
-                  int precision, cudaStream_t s);
+// tcgen05 path (mlp_tc.cu): same operand contract as sgemm_kernel below
+int gemm_tc(const float* A, int64_t lda_i, int64_t lda_k, const float* B, int64_t ldb_k, int64_t ldb_j, float* C, int64_t ldc,
+            int64_t M, int N, int64_t K, int64_t k_per_split, int splits, const float* bias, int epi, int precision,
+            cudaStream_t s);
+// layers narrower than this (the 12-wide action head, the 1-wide value head) stay on the FFMA path: a 128 x 64 MMA tile
+// would be > 80 % padding
+constexpr int kMinTcWidth = 32;
 
 constexpr int BM = 64, BN = 64, BK = 16;
 constexpr int kGemmThreads = 256;
-
-__device__ __forceinline__ float elu_f(float x) { return x > 0.0f ? x : expm1f(x); }
 
 // Generic strided tile GEMM: C[i,j] = sum_k A(i,k) * B(k,j), A(i,k) = A[i*lda_i + k*lda_k], B(k,j) = B[k*ldb_k + j*ldb_j].
 // grid.z splits the k range (used for the dW reduction over M); each z-slice writes its own C slab.
@@ -139,6 +142,10 @@ reduce_slabs_kernel(const float* __restrict__ part, int splits, int64_t n, float
   out[i] = s;
 }
 
+// rows per block of the bias-gradient column sum: 64 rows -> M/64 blocks (384 at M = 24576: 2.6 waves of 148 SMs; at 512
+// rows per block the grid was 48 blocks and this memory-bound pass took longer than the GEMMs)
+constexpr int kColsumRows = 64;
+
 static int dw_splits(int64_t M, int K, int Nout) {
   int64_t tiles = ceil_div(Nout, BM) * ceil_div(K, BN);
   int64_t want = ceil_div(4 * kNumSMs, tiles);
@@ -155,7 +162,7 @@ extern "C" {
 
 int64_t b200lab_linear_bwd_workspace_bytes(int64_t M, int32_t K, int32_t Nout) {
   int splits = dw_splits(M, K, Nout);
-  int64_t colsum_blocks = ceil_div(M, 512);
+  int64_t colsum_blocks = ceil_div(M, kColsumRows);
   return ((int64_t)splits * Nout * K + colsum_blocks * Nout) * (int64_t)sizeof(float);
 }
 
@@ -163,7 +170,11 @@ int b200lab_linear_fwd(const float* X, const float* W, const float* b, float* Y,
                        int32_t elu, int32_t precision, void* stream) {
   B200LAB_CHECK_ARG(X && W && b && Y && M > 0 && K > 0 && Nout > 0, "bad argument");
   cudaStream_t s = (cudaStream_t)stream;
-  if (precision != 0) return linear_fwd_tc(X, W, b, Y, M, K, Nout, elu, precision, s);
+  if (precision != 0 && Nout >= kMinTcWidth && K >= kMinTcWidth) {
+    int rc = gemm_tc(X, K, 1, W, 1, K, Y, Nout, M, Nout, K, K, 1, b, elu ? 2 : 1, precision, s);
+    return rc ? rc : check_launch("linear_fwd (tcgen05)");
+  }
+  B200LAB_CHECK_ARG(precision >= 0 && precision <= 2, "precision must be 0 (fp32 FFMA), 1 (tf32) or 2 (tf32x3)");
   dim3 grid((unsigned)ceil_div(M, BM), (unsigned)ceil_div(Nout, BN), 1);
   if (elu)
     sgemm_kernel<2><<<grid, kGemmThreads, 0, s>>>(X, K, 1, W, 1, K, Y, Nout, M, Nout, K, K, b);
@@ -178,7 +189,8 @@ int b200lab_linear_bwd(const float* X, const float* W, const float* Y, const flo
                        void* workspace, void* stream) {
   B200LAB_CHECK_ARG(X && W && dY && dW && db && workspace && M > 0 && K > 0 && Nout > 0, "bad argument");
   B200LAB_CHECK_ARG(!elu || (Y && dZ), "ELU backward needs the saved output Y and the dZ scratch");
-  (void)precision;  // backward GEMMs run the fp32 path in this version
+  B200LAB_CHECK_ARG(precision >= 0 && precision <= 2, "precision must be 0 (fp32 FFMA), 1 (tf32) or 2 (tf32x3)");
+  const bool use_tc = precision != 0 && Nout >= kMinTcWidth && K >= kMinTcWidth;
   cudaStream_t s = (cudaStream_t)stream;
   const float* dz = dY;
   if (elu) {
@@ -189,20 +201,30 @@ int b200lab_linear_bwd(const float* X, const float* W, const float* Y, const flo
     dz = dZ;
   }
   if (dX) {  // dX[M,K] = dZ[M,Nout] . W[Nout,K]
-    dim3 grid((unsigned)ceil_div(M, BM), (unsigned)ceil_div(K, BN), 1);
-    sgemm_kernel<0><<<grid, kGemmThreads, 0, s>>>(dz, Nout, 1, W, K, 1, dX, K, M, K, Nout, Nout, nullptr);
-    count_launch();
+    if (use_tc) {
+      int rc = gemm_tc(dz, Nout, 1, W, K, 1, dX, K, M, K, Nout, Nout, 1, nullptr, 0, precision, s);
+      if (rc) return rc;
+    } else {
+      dim3 grid((unsigned)ceil_div(M, BM), (unsigned)ceil_div(K, BN), 1);
+      sgemm_kernel<0><<<grid, kGemmThreads, 0, s>>>(dz, Nout, 1, W, K, 1, dX, K, M, K, Nout, Nout, nullptr);
+      count_launch();
+    }
   }
   // dW[Nout,K] = sum_m dZ[m,n] X[m,k]: A(i=n,k=m) = dZ[m*Nout + n], B(k=m,j=k) = X[m*K + k]
   float* ws = (float*)workspace;
   int splits = dw_splits(M, K, Nout);
-  int64_t k_per = ceil_div(ceil_div(M, splits), BK) * BK;
+  int64_t k_per = ceil_div(ceil_div(M, splits), 32) * 32;   // multiple of both paths' K tile
   splits = (int)ceil_div(M, k_per);
   {
-    dim3 grid((unsigned)ceil_div(Nout, BM), (unsigned)ceil_div(K, BN), (unsigned)splits);
     float* dst = splits == 1 ? dW : ws;
-    sgemm_kernel<0><<<grid, kGemmThreads, 0, s>>>(dz, 1, Nout, X, K, 1, dst, K, Nout, K, M, k_per, nullptr);
-    count_launch();
+    if (use_tc) {
+      int rc = gemm_tc(dz, 1, Nout, X, K, 1, dst, K, Nout, K, M, k_per, splits, nullptr, 0, precision, s);
+      if (rc) return rc;
+    } else {
+      dim3 grid((unsigned)ceil_div(Nout, BM), (unsigned)ceil_div(K, BN), (unsigned)splits);
+      sgemm_kernel<0><<<grid, kGemmThreads, 0, s>>>(dz, 1, Nout, X, K, 1, dst, K, Nout, K, M, k_per, nullptr);
+      count_launch();
+    }
     if (splits > 1) {
       int64_t n = (int64_t)Nout * K;
       reduce_slabs_kernel<<<(unsigned)ceil_div(n, 256), 256, 0, s>>>(ws, splits, n, dW);
@@ -211,8 +233,8 @@ int b200lab_linear_bwd(const float* X, const float* W, const float* Y, const flo
   }
   {
     float* part = ws + (int64_t)dw_splits(M, K, Nout) * Nout * K;
-    int blocks = (int)ceil_div(M, 512);
-    colsum_partial_kernel<<<blocks, 256, 0, s>>>(dz, M, Nout, 512, part);
+    int blocks = (int)ceil_div(M, kColsumRows);
+    colsum_partial_kernel<<<blocks, 256, 0, s>>>(dz, M, Nout, kColsumRows, part);
     reduce_slabs_kernel<<<(unsigned)ceil_div(Nout, 256), 256, 0, s>>>(part, blocks, Nout, db);
     count_launch(2);
   }

@@ -141,3 +141,47 @@ def test_linear_fwd_bwd_vs_torch_fp32(M, K, N):
     torch.testing.assert_close(dX.cpu().double(), Xr.grad, rtol=1e-4, atol=1e-7)
     torch.testing.assert_close(dW.cpu().double(), Wr.grad, rtol=1e-4, atol=1e-6)
     torch.testing.assert_close(db.cpu().double(), br.grad, rtol=1e-4, atol=1e-6)
+
+
+@pytest.mark.parametrize("precision,tol", [(2, 3e-5), (1, 3e-3)], ids=["tf32x3", "tf32"])
+@pytest.mark.parametrize("M,K,N", [(24576, 512, 256), (24576, 235, 512), (1000, 128, 256), (384, 96, 128), (333, 77, 40),
+                                   (4096, 256, 128)])
+def test_linear_tcgen05_vs_fp64(M, K, N, precision, tol):
+    """tcgen05 kind::tf32 GEMM paths (csrc/mlp_tc.cu): forward with fused bias+ELU, dX and split-K dW, against torch fp64.
+    3xTF32 (precision 2) must stay at fp32-level accuracy; single TF32 (precision 1) at TF32 level.  Errors are measured
+    relative to the largest magnitude of each result (the layers' outputs are O(1), the gradients O(1/M))."""
+    from isaaclab_b200 import _lib
+    L = _lib.lib()
+    g = torch.Generator().manual_seed(M + K + N)
+    X = torch.randn(M, K, generator=g)
+    W = torch.randn(N, K, generator=g) / K ** 0.5
+    b = torch.randn(N, generator=g)
+    dY = torch.randn(M, N, generator=g) / M
+    Xr, Wr, br = X.double().requires_grad_(), W.double().requires_grad_(), b.double().requires_grad_()
+    Yr = torch.nn.functional.elu(torch.nn.functional.linear(Xr, Wr, br))
+    Yr.backward(dY.double())
+    Xc, Wc, bc, dYc = X.cuda(), W.cuda(), b.cuda(), dY.cuda()
+    Y = torch.empty(M, N, device="cuda")
+    s = _lib.current_stream()
+    _lib.check(L.b200lab_linear_fwd(_lib.ptr(Xc), _lib.ptr(Wc), _lib.ptr(bc), _lib.ptr(Y), M, K, N, 1, precision, s))
+    dZ = torch.empty(M, N, device="cuda"); dX = torch.empty(M, K, device="cuda")
+    dW = torch.empty(N, K, device="cuda"); db = torch.empty(N, device="cuda")
+    ws = torch.empty(L.b200lab_linear_bwd_workspace_bytes(M, K, N) // 4 + 1, device="cuda")
+    _lib.check(L.b200lab_linear_bwd(_lib.ptr(Xc), _lib.ptr(Wc), _lib.ptr(Y), _lib.ptr(dYc), _lib.ptr(dZ), _lib.ptr(dX),
+                                    _lib.ptr(dW), _lib.ptr(db), M, K, N, 1, precision, _lib.ptr(ws), s))
+    torch.cuda.synchronize()
+
+    def rel(a, r):
+        return ((a.cpu().double() - r).abs().max() / r.abs().max()).item()
+    assert rel(Y, Yr.detach()) < tol, f"fwd {rel(Y, Yr.detach()):.2e}"
+    assert rel(dX, Xr.grad) < tol, f"dX {rel(dX, Xr.grad):.2e}"
+    assert rel(dW, Wr.grad) < tol, f"dW {rel(dW, Wr.grad):.2e}"
+    assert rel(db, br.grad) < tol, f"db {rel(db, br.grad):.2e}"   # through ELU'(Y): inherits the forward error
+
+
+def test_linear_rejects_unknown_precision():
+    from isaaclab_b200 import _lib
+    L = _lib.lib()
+    x = torch.zeros(64, 64, device="cuda")
+    rc = L.b200lab_linear_fwd(_lib.ptr(x), _lib.ptr(x), _lib.ptr(x[0]), _lib.ptr(x.clone()), 64, 64, 64, 0, 7, _lib.current_stream())
+    assert rc != 0 and b"precision" in L.b200lab_last_error()
