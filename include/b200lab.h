@@ -457,6 +457,14 @@ typedef struct B200LabGather {
 } B200LabGather;
 int b200lab_gather_minibatch(const B200LabGather* g, void* stream);
 
+/* OnPolicyRunner.learn's finished-episode bookkeeping (RSL/runners/on_policy_runner.py:113-132): cur_reward_sum +=
+ * rewards, cur_episode_length += 1, push both for envs with dones > 0 (ascending env id, as nonzero()) into rings of
+ * `ring_size` (the reference's deque(maxlen=100)), zero them.  `pushed` (device int64) counts pushes since creation;
+ * slot = push index % ring_size.  dones_elem_size: 1 (u8/bool) or 8 (int64, the VecEnv contract's dtype). */
+int b200lab_episode_stats(const float* rewards, const void* dones, int32_t dones_elem_size, int32_t N,
+                          float* cur_reward_sum, float* cur_episode_length, float* ring_reward, float* ring_length,
+                          int32_t ring_size, int64_t* pushed, void* stream);
+
 /* Actor-critic MLP (RSL/networks/mlp.py:60-80: Linear+ELU ... Linear).  Y = act(X W^T + b).
  * X [M,K] row-major, W [Nout,K] row-major (nn.Linear.weight), b [Nout], Y [M,Nout].
  * precision: 0 = fp32 FFMA (exact-order reference path), 1 = tcgen05 kind::tf32, 2 = tcgen05 3xTF32 split. */

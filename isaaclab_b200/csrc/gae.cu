@@ -120,6 +120,59 @@ add_transition_kernel(B200LabTransition tr) {
   }
 }
 
+// ---- finished-episode bookkeeping of OnPolicyRunner.learn (RSL/runners/on_policy_runner.py:113-132) ----
+// The reference does `(dones > 0).nonzero()` + `.cpu().tolist()` into two deque(maxlen=100) every env step (a host
+// sync per step).  Here the deques are device rings with a device push counter; the host reads them once per iteration.
+// One CTA: thread i owns a contiguous span of envs so pushes keep nonzero()'s ascending env order.
+constexpr int kEpBlock = 1024;
+
+template <typename DoneT>
+__global__ void __launch_bounds__(kEpBlock)
+episode_stats_kernel(const float* __restrict__ rewards, const DoneT* __restrict__ dones, int N,
+                     float* __restrict__ cur_sum, float* __restrict__ cur_len, float* __restrict__ ring_rew,
+                     float* __restrict__ ring_len, int ring, long long* __restrict__ pushed) {
+  __shared__ int warp_tot[kEpBlock / 32];
+  int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  int span = (N + kEpBlock - 1) / kEpBlock;
+  int lo = min(tid * span, N), hi = min(lo + span, N);
+  int mine = 0;
+  for (int n = lo; n < hi; ++n) mine += dones[n] > 0;
+  int incl = mine;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    int v = __shfl_up_sync(0xffffffffu, incl, d);
+    if (lane >= d) incl += v;
+  }
+  if (lane == 31) warp_tot[wid] = incl;
+  __syncthreads();
+  int before = 0, total = 0;
+  for (int w = 0; w < kEpBlock / 32; ++w) {
+    int t = warp_tot[w];
+    if (w < wid) before += t;
+    total += t;
+  }
+  long long base = *pushed;
+  int rank = before + incl - mine;  // exclusive rank of this thread's first finished episode within the step
+  for (int n = lo; n < hi; ++n) {
+    float s = cur_sum[n] + rewards[n];
+    float l = cur_len[n] + 1.0f;
+    if (dones[n] > 0) {
+      if (total - rank <= ring) {  // older pushes of the same step would be evicted by deque(maxlen) anyway
+        int slot = (int)((base + rank) % ring);
+        ring_rew[slot] = s;
+        ring_len[slot] = l;
+      }
+      ++rank;
+      s = 0.0f;
+      l = 0.0f;
+    }
+    cur_sum[n] = s;
+    cur_len[n] = l;
+  }
+  __syncthreads();
+  if (tid == 0) *pushed = base + total;
+}
+
 // ---- minibatch gather: one warp per sample row, lanes stride the columns (coalesced) ----
 __global__ void __launch_bounds__(256)
 gather_minibatch_kernel(B200LabGather g) {
@@ -183,6 +236,26 @@ int b200lab_add_transition(const B200LabTransition* tr, void* stream) {
   add_transition_kernel<<<nb, 256, 0, (cudaStream_t)stream>>>(*tr);
   count_launch();
   return check_launch("add_transition");
+}
+
+int b200lab_episode_stats(const float* rewards, const void* dones, int32_t dones_elem_size, int32_t N,
+                          float* cur_reward_sum, float* cur_episode_length, float* ring_reward, float* ring_length,
+                          int32_t ring_size, int64_t* pushed, void* stream) {
+  B200LAB_CHECK_ARG(rewards && dones && cur_reward_sum && cur_episode_length && ring_reward && ring_length && pushed,
+                    "episode_stats: null pointer");
+  B200LAB_CHECK_ARG(N > 0 && ring_size > 0, "episode_stats: bad sizes");
+  B200LAB_CHECK_ARG(dones_elem_size == 1 || dones_elem_size == 8, "episode_stats: dones must be u8/bool or int64");
+  cudaStream_t s = (cudaStream_t)stream;
+  if (dones_elem_size == 1)
+    episode_stats_kernel<uint8_t><<<1, kEpBlock, 0, s>>>(rewards, (const uint8_t*)dones, N, cur_reward_sum,
+                                                         cur_episode_length, ring_reward, ring_length, ring_size,
+                                                         (long long*)pushed);
+  else
+    episode_stats_kernel<long long><<<1, kEpBlock, 0, s>>>(rewards, (const long long*)dones, N, cur_reward_sum,
+                                                           cur_episode_length, ring_reward, ring_length, ring_size,
+                                                           (long long*)pushed);
+  count_launch();
+  return check_launch("episode_stats");
 }
 
 int b200lab_gather_minibatch(const B200LabGather* g, void* stream) {

@@ -83,3 +83,4 @@ class ManagerBasedRLEnvCfg:
     episode_length_s: float = 10.0
     sim: SimCfg = field(default_factory=SimCfg)
     seed: int | None = None
+    is_finite_horizon: bool = False

@@ -163,6 +163,44 @@ class ManagerBasedRLEnv:
     def num_actions(self):
         return self.fused.A
 
+    @property
+    def unwrapped(self):
+        return self
+
+    def seed(self, seed: int = -1) -> int:
+        """Re-seeds the in-kernel Philox streams (ManagerBasedEnv.seed, LAB/envs/manager_based_env.py:239)."""
+        import ctypes
+        seed = int(seed) if seed is not None and seed >= 0 else int(torch.seed() & 0x7FFFFFFF)
+        self.fused._st.seed = seed
+        _lib.check(self.fused.L.b200lab_env_update(self.fused.handle, ctypes.byref(self.fused._st)))
+        return seed
+
+    def close(self):
+        """Releases the native env handle; the object must not be stepped afterwards."""
+        f = self.fused
+        if getattr(f, "handle", None):
+            f.L.b200lab_env_destroy(f.handle)
+            f.handle = None
+
+    def evaluate_term(self, fn, *args, **params):
+        """Value of a reward / termination term function called directly (`mdp.track_lin_vel_xy_exp(env, ...)`),
+        as the term programs evaluated it in the most recent `step` -- the state the reference function would read
+        between steps.  The term must be part of this env's cfg with the same params; anything else has no fused
+        program to run and raises."""
+        kind, op = getattr(fn, "_b200_kind", None), getattr(fn, "_b200_op", None)
+        table = {"rew": "rewards", "term": "terminations"}.get(kind)
+        if table is None:
+            raise NotImplementedError(f"term '{op}' ({kind}) is only evaluated inside the fused step kernels")
+        for i, t in enumerate(self.spec[table]):
+            if t["op"] != op:
+                continue
+            if kind == "term":
+                return self.fused.term_dones[i].bool()
+            if t["weight"] == 0.0:
+                raise ValueError(f"reward term '{t['name']}' has weight 0 and is skipped by the reward manager")
+            return self.fused.step_reward[:, i] / t["weight"]  # _step_reward = weighted value / dt (reward_manager.py:153)
+        raise KeyError(f"term function '{op}' is not part of this environment's {table} cfg")
+
     def reset(self, seed=None):
         """Initial observations (ManagerBasedEnv.reset, LAB/envs/manager_based_env.py:264): obs of the current state."""
         self.fused.compute_obs(self.sim.last_view())

@@ -1,6 +1,9 @@
 from .modules import ActorCritic
 from .ppo import PPO
+from .runner import EpisodeStats, OnPolicyRunner, resolve_obs_groups
 from .storage import RolloutStorage
 from .tensordict import TensorDict
+from .vecenv_wrapper import RslRlVecEnvWrapper
 
-__all__ = ["ActorCritic", "PPO", "RolloutStorage", "TensorDict"]
+__all__ = ["ActorCritic", "EpisodeStats", "OnPolicyRunner", "PPO", "RolloutStorage", "RslRlVecEnvWrapper",
+           "TensorDict", "resolve_obs_groups"]
