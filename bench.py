@@ -65,39 +65,94 @@ def _term_dim(spec, t):
 
 
 class ClockSampler(threading.Thread):
-    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    """SM clock and clock-event (throttle) reasons sampled DURING the timed region: NVML polled every 2 ms (the timed
+    region of a default run is well under a second -- nvidia-smi -lms cannot sample that), nvidia-smi as a fallback
+    (B200_PROFILING.md clocks line)."""
+
+    _REASONS = (("hw_slowdown", 0x8), ("hw_thermal_slowdown", 0x40), ("sw_thermal_slowdown", 0x20),
+                ("sw_power_cap", 0x4))
 
     def __init__(self, index):
         super().__init__(daemon=True)
         self.index, self.samples, self.stop_flag = index, [], False
-        self.proc = None
+        self.max_mhz, self.mask, self.proc, self.source = None, 0, None, "nvml"
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+        if vis:
+            try:
+                self.index = int(vis.split(",")[index])
+            except (ValueError, IndexError):
+                pass
 
-    def run(self):
+    def _run_nvml(self):
+        import pynvml as nv
+        nv.nvmlInit()
+        h = nv.nvmlDeviceGetHandleByIndex(self.index)
+        self.max_mhz = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+        reasons = getattr(nv, "nvmlDeviceGetCurrentClocksEventReasons", None) or nv.nvmlDeviceGetCurrentClocksThrottleReasons
+        while not self.stop_flag:
+            self.samples.append(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM))
+            self.mask |= int(reasons(h))
+            time.sleep(0.002)
+
+    def _run_smi(self):
+        self.source = "nvidia-smi"
         q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits", "-i",
+                                      str(self.index), "-lms", "20"], stdout=subprocess.PIPE, text=True)
+        for line in self.proc.stdout:
+            f = [x.strip() for x in line.split(",")]
+            if f and f[0].isdigit():
+                self.samples.append(int(f[0]))
+                if len(f) > 1 and f[1].isdigit():
+                    self.max_mhz = int(f[1])
+                for (name, bit), v in zip(self._REASONS, f[2:6]):
+                    if v.lower().startswith("active"):
+                        self.mask |= bit
+            if self.stop_flag:
+                break
+
+    def run(self):
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits", "-i",
-                                          str(self.index), "-lms", "100"], stdout=subprocess.PIPE, text=True)
-            for line in self.proc.stdout:
-                self.samples.append([x.strip() for x in line.split(",")])
-                if self.stop_flag:
-                    break
+            self._run_nvml()
         except Exception:
-            pass
+            try:
+                self._run_smi()
+            except Exception:
+                pass
 
     def finish(self):
         self.stop_flag = True
         if self.proc:
             self.proc.terminate()
-        sm = sorted(int(s[0]) for s in self.samples if s and s[0].isdigit())
-        mx = [int(s[1]) for s in self.samples if len(s) > 1 and s[1].isdigit()]
-        reasons = set()
-        for s in self.samples:
-            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), s[2:6]):
-                if v.lower().startswith("active"):
-                    reasons.add(name)
-        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(sm)}
+        self.join(timeout=2.0)
+        sm = sorted(self.samples)
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": self.max_mhz,
+                "reasons": [name for name, bit in self._REASONS if self.mask & bit], "samples": len(sm),
+                "source": self.source}
+
+
+_UNIT_BYTES = {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+_NCU_KERNEL = {"compute_obs": "compute_obs_kernel", "decimation_fused": "decimation_fused_kernel",
+               "post_step": "post_step_kernel", "post_reset_write": "substep_pre_kernel"}
+
+
+def ncu_traffic(kernel):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel` from the committed `ncu --set full` summary
+    (profiles/*_ncu_step_kernels.json, tools/ncu_summary.py); None when no capture is committed."""
+    import glob
+    for path in sorted(glob.glob(os.path.join(ROOT, "profiles", "*_ncu_step_kernels.json")), reverse=True):
+        for recs in json.load(open(path)).values():
+            for r in recs:
+                if _NCU_KERNEL.get(kernel, kernel) in r["kernel"] and "dram_read" in r:
+                    return int(r["dram_read"] * _UNIT_BYTES[r.get("dram_read_unit", "byte")]
+                               + r.get("dram_write", 0.0) * _UNIT_BYTES[r.get("dram_write_unit", "byte")])
+    return None
+
+
+def workload_name(spec):
+    return (f"{TASK} non-physics step, {spec['N']} envs/GPU, 187-ray height scan, ActuatorNetLSTM, "
+            f"decimation {spec['decimation']}")
 
 
 def build_workload(device, seed):
@@ -201,7 +256,7 @@ def run_ours(args):
     peak = float(peaks.get("hbm_gbs", 6650.0))
     achieved = bytes_per[dom] * N / (per_kernel_ms[dom] * 1e-3) / 1e9
     roof = {"bound": "hbm", "kernel": dom, "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
-            "frac": round(achieved / peak, 4), "traffic": None, "peak_source": "measured" if peaks else "fallback",
+            "frac": round(achieved / peak, 4), "traffic": ncu_traffic(dom), "peak_source": "measured" if peaks else "fallback",
             "algorithmic_bytes_per_launch": bytes_per[dom] * N,
             "per_kernel_us": {n: round(v * 1e3, 2) for n, v in per_kernel_ms.items()},
             "step_algorithmic_bytes": bytes_step * N,
@@ -212,15 +267,11 @@ def run_ours(args):
     env = ManagerBasedRLEnv(cfg, sim=host_sim, device=dev, spec=spec, seed=rank)
     init_fused_state(env.fused, init)
     act_host = torch.randn(N, spec["A"], generator=g).pin_memory()
-    obs_host = torch.empty(N, env.fused.obs_dim).pin_memory()
-    rew_host = torch.empty(N).pin_memory()
-    done_host = torch.empty(N, dtype=torch.uint8).pin_memory()
+    res_host = torch.empty(env.fused.result.numel(), dtype=torch.uint8).pin_memory()
 
     def e2e_step():
-        obs, rew, term, trunc, _ = env.step(act_host)
-        obs_host.copy_(obs[env._group], non_blocking=True)
-        rew_host.copy_(rew, non_blocking=True)
-        done_host.copy_(env.fused.reset_buf, non_blocking=True)
+        env.step(act_host)
+        env.read_results(res_host)   # obs, reward, terminated, time-outs, reset mask: one D2H copy
         torch.cuda.current_stream().synchronize()  # the caller consumes the result before the next step
 
     for _ in range(args.warmup):
@@ -239,14 +290,16 @@ def run_ours(args):
         dist.all_reduce(ms_e2e, op=dist.ReduceOp.MAX)
     ms_e2e = float(ms_e2e.item())
     h2d = host_sim.h2d_bytes_per_step + act_host.numel() * 4
-    d2h = obs_host.numel() * 4 + rew_host.numel() * 4 + done_host.numel()
+    d2h = res_host.numel()
     e2e = {"value": round(world * N * args.steps / (ms_e2e * 1e-3), 1), "unit": UNIT, "h2d_bytes_per_step": h2d,
            "d2h_bytes_per_step": d2h, "ms_per_step": round(ms_e2e / args.steps, 4)}
     out = {"metric": METRIC, "value": round(value, 1), "unit": UNIT, "n_gpus": world, "steps": args.steps,
            "warmup": args.warmup, "ms_per_step": round(ms / args.steps, 5), "higher_is_better": True, "scaling": "weak",
            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-           "config": {"workload": f"{TASK} non-physics step, {N} envs/GPU, 187-ray height scan, ActuatorNetLSTM, "
-                                  f"decimation {S}", "envs_per_gpu": N, "l2_policy": f"{K_SLABS} state slabs "
+           "config": {"workload": workload_name(spec), "envs_per_gpu": N,
+                      "e2e_mode": "ManagerBasedRLEnv.step with pinned host buffers; results (obs, reward, dones) read "
+                                  "back and synchronised every step; next step's simulator state prefetched H2D on a "
+                                  "copy stream while the current step computes", "l2_policy": f"{K_SLABS} state slabs "
                                   f"({sim.bytes() >> 20} MiB > 126 MiB L2) cycled", "parallelism": f"env-shard x{world}"},
            "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roof}
     del env, host_sim, fus, sim
@@ -267,17 +320,25 @@ PPO_CFG = dict(N=ENVS_PER_GPU, T=24, obs_dim=235, act_dim=12, hidden=[512, 256, 
                desired_kl=0.01)   # config 3: TASKS/.../anymal_c/agents/rsl_rl_ppo_cfg.py (AnymalCRoughPPORunnerCfg)
 
 
-def synthetic_rollout(c, seed):
-    """SURVEY 8d rollout: obs N(0,1), actions N(0,1), mu N(0,1), sigma 1, values N(0,1), rewards N(0,0.05), dones
-    Bernoulli(0.01), log-prob consistent with (a, mu, sigma)."""
+def synthetic_rollout(c, seed, forward=None):
+    """SURVEY 8d rollout: obs N(0,1), rewards N(0,0.05), dones Bernoulli(0.01), sigma 1.  With `forward`
+    (obs[M,D] -> (mu[M,A], value[M,1]), the arm's own random-init policy) the rollout is what `PPO.act` would have
+    stored: mu/values from the policy, actions = mu + sigma*eps, log-prob of those actions -- so the first minibatch
+    starts at ratio 1 as in training.  Without it mu/values are N(0,1)."""
     g = torch.Generator().manual_seed(seed)
     T, N, D, A = c["T"], c["N"], c["obs_dim"], c["act_dim"]
-    r = dict(observations=torch.randn(T, N, D, generator=g), actions=torch.randn(T, N, A, generator=g),
-             mu=torch.randn(T, N, A, generator=g), sigma=torch.ones(T, N, A), values=torch.randn(T, N, 1, generator=g),
+    r = dict(observations=torch.randn(T, N, D, generator=g), sigma=torch.ones(T, N, A),
              rewards=0.05 * torch.randn(T, N, 1, generator=g), dones=(torch.rand(T, N, 1, generator=g) < 0.01).to(torch.uint8))
+    eps = torch.randn(T, N, A, generator=g)
+    r["last_values"] = torch.randn(N, 1, generator=g)
+    if forward is None:
+        r["mu"], r["values"] = torch.randn(T, N, A, generator=g), torch.randn(T, N, 1, generator=g)
+    else:
+        mu, val = zip(*(forward(r["observations"][t]) for t in range(T)))
+        r["mu"], r["values"] = torch.stack([m.cpu() for m in mu]), torch.stack([v.cpu() for v in val])
+    r["actions"] = r["mu"] + r["sigma"] * eps
     r["actions_log_prob"] = (-0.5 * ((r["actions"] - r["mu"]) / r["sigma"]) ** 2 - torch.log(r["sigma"])
                              - 0.5 * math.log(2 * math.pi)).sum(-1, keepdim=True)
-    r["last_values"] = torch.randn(N, 1, generator=g)
     return r
 
 
@@ -300,7 +361,11 @@ def time_ppo_update(dev, reps=3, precision=2):
               gamma=c["gamma"], lam=c["lam"], value_loss_coef=c["value_loss_coef"], entropy_coef=c["entropy_coef"],
               learning_rate=c["learning_rate"], max_grad_norm=c["max_grad_norm"], desired_kl=c["desired_kl"], device=dev)
     alg.init_storage("rl", c["N"], c["T"], obs0, [c["act_dim"]])
-    roll = {k: v.to(dev) for k, v in synthetic_rollout(c, 1234 + 3).items()}
+    def forward(o):
+        od = TensorDict({"policy": o.to(dev)}, batch_size=[o.shape[0]])
+        return pol.act_inference(od).clone(), pol.evaluate(od).clone()
+
+    roll = {k: v.to(dev) for k, v in synthetic_rollout(c, 1234 + 3, forward).items()}
     st = alg.storage
     L = __import__("isaaclab_b200._lib", fromlist=["lib"]).lib()
 
@@ -344,7 +409,6 @@ def cpu_ppo_baseline(budget_updates=2, threads=None):
     threads = threads or os.cpu_count()
     torch.set_num_threads(threads)
     c = PPO_CFG
-    roll = synthetic_rollout(c, 1234 + 3)
     g = torch.Generator().manual_seed(7)
     dims = [c["obs_dim"], *c["hidden"]]
     params = {}
@@ -355,6 +419,19 @@ def cpu_ppo_baseline(budget_updates=2, threads=None):
             params[f"{net}.{2 * i}.weight"] = (torch.rand(b, a, generator=g) * 2 - 1) * k
             params[f"{net}.{2 * i}.bias"] = (torch.rand(b, generator=g) * 2 - 1) * k
     params["std"] = torch.ones(c["act_dim"])
+
+    def forward(o):
+        out = []
+        for net in ("actor", "critic"):
+            x = o
+            for i in range(len(dims)):
+                x = torch.nn.functional.linear(x, params[f"{net}.{2 * i}.weight"], params[f"{net}.{2 * i}.bias"])
+                if i < len(dims) - 1:
+                    x = torch.nn.functional.elu(x)
+            out.append(x)
+        return out
+
+    roll = synthetic_rollout(c, 1234 + 3, forward)
     t0 = time.perf_counter()
     ret, adv = O.compute_returns(roll["rewards"], roll["values"], roll["dones"], roll["last_values"], c["gamma"], c["lam"])
     gae_s = time.perf_counter() - t0
@@ -420,8 +497,9 @@ def run_reference(args):
     out = {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": int(os.environ.get("WORLD_SIZE", "1")),
            "steps": args.steps, "warmup": args.warmup, "ms_per_step": cb["ms_per_step"], "higher_is_better": True,
            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-           "config": {"workload": f"{TASK} non-physics step, {spec['N']} envs, reference torch path restated (oracle port) on CPU"},
-           "cpu_baseline": cb, "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+           "config": {"workload": workload_name(spec), "envs_per_gpu": spec["N"],
+                      "arm": "reference torch path restated (oracle port) on the host cores; each step = one full env step"},
+           "cpu_baseline": cb, "ppo_update": cpu_ppo_baseline(), "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(out))
 
 

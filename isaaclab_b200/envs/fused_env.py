@@ -277,8 +277,18 @@ class FusedEnv:
         for i, t in enumerate(s["rewards"]):
             self._term(st.rew[i], "rew", t)
         self.term_dones = z(max(nt, 1), N, dtype=torch.uint8)
-        self.terminated, self.truncated, self.reset_buf = (z(N, dtype=torch.uint8) for _ in range(3))
-        self.reward_buf, self.episode_sums, self.step_reward = z(N), z(max(nr, 1), N), z(N, max(nr, 1))
+        # what a caller reads every step lives in ONE slab so a host consumer needs one D2H copy:
+        # [obs N*D f32 | reward N f32 | terminated N u8 | truncated N u8 | reset_buf N u8]
+        from . import term_dims as _td
+        D_all = sum(_td.term_dim(s, t) for t in s["observations"]["terms"])
+        self.result = z(4 * N * D_all + 4 * N + 4 * N, dtype=torch.uint8)
+        o_rew, o_msk = 4 * N * D_all, 4 * N * D_all + 4 * N
+        self.obs_buf = self.result[:o_rew].view(torch.float32).view(N, D_all)
+        self.reward_buf = self.result[o_rew:o_msk].view(torch.float32)
+        self.terminated, self.truncated, self.reset_buf = (self.result[o_msk + i * N:o_msk + (i + 1) * N] for i in range(3))
+        self.result_layout = {"obs": (0, o_rew), "reward": (o_rew, o_msk), "terminated": (o_msk, o_msk + N),
+                              "truncated": (o_msk + N, o_msk + 2 * N), "reset_buf": (o_msk + 2 * N, o_msk + 3 * N)}
+        self.episode_sums, self.step_reward = z(max(nr, 1), N), z(N, max(nr, 1))
         st.term_dones, st.terminated, st.truncated, st.reset_buf = p(self.term_dones), p(self.terminated), p(self.truncated), p(self.reset_buf)
         st.reward_buf, st.episode_sums, st.step_reward = p(self.reward_buf), p(self.episode_sums), p(self.step_reward)
         # --- command
@@ -378,7 +388,7 @@ class FusedEnv:
             dst.scale = float(t["scale"]) if dst.scale_on else 1.0
         st.obs_dim = D
         self.obs_dim = D
-        self.obs_buf = z(N, D)
+        assert D == self.obs_buf.shape[1]
         st.obs_buf = p(self.obs_buf)
         # --- randomness / logs
         st.seed = int(seed)

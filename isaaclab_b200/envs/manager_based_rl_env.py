@@ -19,29 +19,83 @@ from .fused_env import FusedEnv, SimView
 
 
 class HostReplaySim:
-    """Simulator state arriving from the HOST every step (pinned memory -> one device staging set)."""
+    """Simulator state arriving from the HOST every step (pinned memory -> device staging sets).
 
-    def __init__(self, spec, slabs_cpu: dict, device="cuda"):
+    The S physics states of one env step are packed into one pinned slab, so a step's input is ONE H2D copy.  Three
+    device staging sets rotate (current / previous / next): while the kernels of env step k read sets k and k-1 on the
+    compute stream, step k+1's slab crosses PCIe on a copy stream into the third set (`prefetch_next`, called by the
+    env after it has queued the step's kernels).  A recorded source knows its next state in advance; a live
+    simulator filling pinned buffers would trigger the copy when its sub-steps are done."""
+
+    _SETS = 3
+    _ORDER = ("root_state_w", "joint_pos", "joint_vel", "net_forces_w", "body_lin_vel_w")
+
+    def __init__(self, spec, slabs_cpu: dict, device="cuda", prefetch: bool = True):
         self.spec, self.S = spec, spec["decimation"]
         self.K = slabs_cpu["root_state_w"].shape[0]
-        self.host = {k: v.contiguous().pin_memory() for k, v in slabs_cpu.items()}
-        self.stage = {k: torch.empty_like(v[0], device=device) for k, v in slabs_cpu.items()}
-        st = self.stage
         has_contact = spec.get("contact") is not None
-        self._views = [SimView(st["root_state_w"], st["joint_pos"][s], st["joint_vel"][s],
-                               st["net_forces_w"][s] if has_contact else None, st["body_lin_vel_w"]) for s in range(self.S)]
-        self.h2d_bytes_per_step = sum(v[0].numel() * v[0].element_size() for v in self.host.values())
+        self._fields, off = [], 0
+        for name in self._ORDER:
+            v = slabs_cpu[name]
+            nbytes = v[0].numel() * v.element_size()
+            self._fields.append((name, off, nbytes, tuple(v.shape[1:]), v.dtype))
+            off += (nbytes + 255) // 256 * 256
+        self.slab_bytes = off
+        self.host = torch.empty(self.K, off, dtype=torch.uint8).pin_memory()
+        for name, o, nbytes, shape, dtype in self._fields:
+            self.host[:, o:o + nbytes].view(dtype).view(self.K, *shape).copy_(slabs_cpu[name])
+        self.stage, self.dev, self._views = [], [], []
+        for _ in range(self._SETS):
+            buf = torch.empty(off, dtype=torch.uint8, device=device)
+            st = {name: buf[o:o + nbytes].view(dtype).view(*shape) for name, o, nbytes, shape, dtype in self._fields}
+            self.stage.append(buf)
+            self.dev.append(st)
+            self._views.append([SimView(st["root_state_w"], st["joint_pos"][s], st["joint_vel"][s],
+                                        st["net_forces_w"][s] if has_contact else None, st["body_lin_vel_w"])
+                                for s in range(self.S)])
+        self.h2d_bytes_per_step = sum(f[2] for f in self._fields)
+        self.prefetch_enabled = prefetch
+        self.copy_stream = torch.cuda.Stream(device=device) if prefetch else None
+        self._ready = [torch.cuda.Event() for _ in range(self._SETS)]
+        self._free = torch.cuda.Event()
+        self._staged = [None] * self._SETS  # which slab index each set holds (or is receiving)
         self.k = -1
+        self.slot = 0
+        self._copy(0, self.K - 1)  # "previous" state of the first step: the slab before slab 0 in the cycle
+        torch.cuda.current_stream().synchronize()
+
+    def _copy(self, slot, k):
+        self.stage[slot].copy_(self.host[k], non_blocking=True)
+        self._staged[slot] = k
+
+    def prefetch(self, slot, k):
+        """H2D of slab k into `slot` on the copy stream, after everything already queued on the compute stream (the
+        last readers of that set) has finished."""
+        self._free.record(torch.cuda.current_stream())
+        with torch.cuda.stream(self.copy_stream):
+            self.copy_stream.wait_event(self._free)
+            self._copy(slot, k)
+            self._ready[slot].record(self.copy_stream)
 
     def advance(self):
-        """Bring the next env step's S physics states to the device (async H2D on the current stream)."""
+        """Views of the next env step's S physics states."""
         self.k = (self.k + 1) % self.K
-        for name, dst in self.stage.items():
-            dst.copy_(self.host[name][self.k], non_blocking=True)
-        return self._views
+        self.slot = (self.slot + 1) % self._SETS
+        if not self.prefetch_enabled:
+            self._copy(self.slot, self.k)
+            return self._views[self.slot]
+        if self._staged[self.slot] != self.k:  # first call: nothing was prefetched yet
+            self.prefetch(self.slot, self.k)
+        torch.cuda.current_stream().wait_event(self._ready[self.slot])
+        return self._views[self.slot]
+
+    def prefetch_next(self):
+        """Queue the H2D of the step after the current one (its target set was last read by the previous step)."""
+        if self.prefetch_enabled:
+            self.prefetch((self.slot + 1) % self._SETS, (self.k + 1) % self.K)
 
     def last_view(self):
-        return self._views[-1]
+        return self._views[self.slot][-1]
 
 
 class DeviceReplaySim:
@@ -149,7 +203,7 @@ class ManagerBasedRLEnv:
         self.reset_terminated, self.reset_time_outs, self.reset_buf = f.terminated.view(torch.bool), f.truncated.view(torch.bool), f.reset_buf.view(torch.bool)
         self.obs_buf = {self._group: f.obs_buf}
         self._action_dev = torch.zeros(self.num_envs, f.A, device=device)
-        self._prev_view = self.sim.last_view() if hasattr(self.sim, "last_view") else None
+        self._prefetch_next = getattr(self.sim, "prefetch_next", None)
 
     @property
     def episode_length_buf(self):
@@ -214,8 +268,22 @@ class ManagerBasedRLEnv:
         prev = self.sim.last_view()
         views = self.sim.advance()
         f.step(action, views, prev)
+        if self._prefetch_next is not None:
+            self._prefetch_next()
         self.common_step_counter += 1
         return self.obs_buf, self.reward_buf, self.reset_terminated, self.reset_time_outs, self.extras
+
+    def read_results(self, host_slab: torch.Tensor):
+        """ONE device->host copy (async on the current stream) of everything `step` returned -- observations, reward,
+        terminated, time-outs, reset mask -- into a pinned uint8 slab of `fused.result.numel()` bytes; returns typed host
+        views of it (valid after the stream is synchronised)."""
+        f = self.fused
+        host_slab.copy_(f.result, non_blocking=True)
+        lay = f.result_layout
+        N = self.num_envs
+        return {"obs": host_slab[lay["obs"][0]:lay["obs"][1]].view(torch.float32).view(N, -1),
+                "reward": host_slab[lay["reward"][0]:lay["reward"][1]].view(torch.float32),
+                **{k: host_slab[lay[k][0]:lay[k][1]] for k in ("terminated", "truncated", "reset_buf")}}
 
     def episode_log(self):
         """extras["log"] aggregates (manager_based_rl_env.py:365-389) accumulated on the device since the last call;
