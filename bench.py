@@ -304,15 +304,16 @@ def run_ours(args):
            "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roof}
     del env, host_sim, fus, sim
     torch.cuda.empty_cache()
-    out["ppo_update"] = time_ppo_update(dev, precision=2)
-    out["ppo_update"]["fp32_ffma_s_per_iter"] = time_ppo_update(dev, precision=0)["s_per_iter"]
+    mg = {"global_rank": rank, "local_rank": local, "world_size": world} if world > 1 else None
+    out["ppo_update"] = time_ppo_update(dev, precision=2, multi_gpu_cfg=mg)   # N>1: one NCCL all-reduce per minibatch
+    out["ppo_update"]["fp32_ffma_s_per_iter"] = time_ppo_update(dev, precision=0, multi_gpu_cfg=mg)["s_per_iter"]
     if rank == 0:
         if world == 1 and not args.no_cpu_baseline:
             out["cpu_baseline"] = cpu_baseline(spec, slabs, init, budget_s=15.0)
             out["cpu_baseline"]["ppo_update"] = cpu_ppo_baseline()
-        print(json.dumps(out))
     if world > 1:
         dist.destroy_process_group()
+    return json.dumps(out) if rank == 0 else None
 
 
 PPO_CFG = dict(N=ENVS_PER_GPU, T=24, obs_dim=235, act_dim=12, hidden=[512, 256, 128], epochs=5, mini_batches=4, clip_param=0.2,
@@ -348,7 +349,7 @@ def ppo_flops_per_iter(c):
     return 3.0 * fwd * c["T"] * c["N"] * c["epochs"]   # fwd + dX + dW (upper bound)
 
 
-def time_ppo_update(dev, reps=3, precision=2):
+def time_ppo_update(dev, reps=3, precision=2, multi_gpu_cfg=None):
     """Second half of the metric: PPO update s/iter = GAE + 5 epochs x 4 minibatches (gather, actor/critic fwd, fused
     loss fwd+bwd, bwd GEMMs, KL-adaptive LR, clip + Adam) at config-3 shapes, CUDA events on the launching stream."""
     from isaaclab_b200.rsl_rl import PPO, ActorCritic, TensorDict
@@ -359,7 +360,10 @@ def time_ppo_update(dev, reps=3, precision=2):
                       critic_hidden_dims=c["hidden"], device=dev, precision=precision)
     alg = PPO(pol, num_learning_epochs=c["epochs"], num_mini_batches=c["mini_batches"], clip_param=c["clip_param"],
               gamma=c["gamma"], lam=c["lam"], value_loss_coef=c["value_loss_coef"], entropy_coef=c["entropy_coef"],
-              learning_rate=c["learning_rate"], max_grad_norm=c["max_grad_norm"], desired_kl=c["desired_kl"], device=dev)
+              learning_rate=c["learning_rate"], max_grad_norm=c["max_grad_norm"], desired_kl=c["desired_kl"], device=dev,
+              multi_gpu_cfg=multi_gpu_cfg)
+    if multi_gpu_cfg is not None:
+        alg.broadcast_parameters()
     alg.init_storage("rl", c["N"], c["T"], obs0, [c["act_dim"]])
     def forward(o):
         od = TensorDict({"policy": o.to(dev)}, batch_size=[o.shape[0]])
@@ -500,7 +504,7 @@ def run_reference(args):
            "config": {"workload": workload_name(spec), "envs_per_gpu": spec["N"],
                       "arm": "reference torch path restated (oracle port) on the host cores; each step = one full env step"},
            "cpu_baseline": cb, "ppo_update": cpu_ppo_baseline(), "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(out))
+    return json.dumps(out)
 
 
 def main():
@@ -512,10 +516,15 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
-    if args.impl == "reference":
-        run_reference(args)
-    else:
-        run_ours(args)
+    # The contract is ONE JSON line on stdout.  Native libraries write there too (NCCL prints its version banner to fd 1
+    # under NCCL_DEBUG=VERSION), so fd 1 is pointed at stderr for the run and the JSON line goes to the saved descriptor.
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    line = run_reference(args) if args.impl == "reference" else run_ours(args)
+    sys.stdout.flush()
+    if line is not None:
+        os.write(real_stdout, (line + "\n").encode())
 
 
 if __name__ == "__main__":
