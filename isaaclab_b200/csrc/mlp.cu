@@ -97,16 +97,7 @@ sgemm_kernel(const float* __restrict__ A, int64_t lda_i, int64_t lda_k, const fl
   }
 }
 
-// dZ = dY * ELU'(pre-activation), recovered from the saved post-activation Y: Y > 0 -> 1, else Y + 1 (alpha = 1).
-__global__ void __launch_bounds__(256)
-elu_bwd_kernel(const float* __restrict__ Y, const float* __restrict__ dY, float* __restrict__ dZ, int64_t n) {
-  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  int64_t stride = (int64_t)gridDim.x * blockDim.x;
-  for (; i < n; i += stride) {
-    float y = __ldg(Y + i);
-    dZ[i] = __ldg(dY + i) * (y > 0.0f ? 1.0f : y + 1.0f);
-  }
-}
+// ELU'(pre-activation) is recovered from the saved post-activation Y: Y > 0 -> 1, else Y + 1 (alpha = 1).
 
 // column sums of dZ[M,N] (bias gradient), partials per row-slab then a fixed-order reduce.
 __global__ void __launch_bounds__(256)
@@ -132,6 +123,50 @@ colsum_partial_kernel(const float* __restrict__ dZ, int64_t M, int N, int64_t ro
   }
 }
 
+// dZ = dY * ELU'(.) AND the per-slab column sums of dZ in one pass over the layer's [M,N] activations (the bias gradient
+// used to re-read dZ in a second kernel).  Same block geometry as colsum_partial_kernel.
+__global__ void __launch_bounds__(256)
+elu_bwd_colsum_kernel(const float* __restrict__ Y, const float* __restrict__ dY, float* __restrict__ dZ, int64_t M, int N,
+                      int64_t rows_per_block, float* __restrict__ part) {
+  __shared__ float sh[8][33];
+  int cl = threadIdx.x % 32, rl = threadIdx.x / 32;
+  int64_t r0 = (int64_t)blockIdx.x * rows_per_block, r1 = min64(M, r0 + rows_per_block);
+  for (int c0 = 0; c0 < N; c0 += 32) {
+    int c = c0 + cl;
+    float s = 0.0f;
+    if (c < N)
+      for (int64_t r = r0 + rl; r < r1; r += 8) {
+        float y = __ldg(Y + r * N + c);
+        float g = __ldg(dY + r * N + c) * (y > 0.0f ? 1.0f : y + 1.0f);
+        dZ[r * N + c] = g;
+        s += g;
+      }
+    sh[rl][cl] = s;
+    __syncthreads();
+    if (rl == 0 && c < N) {
+      float t = 0.0f;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) t += sh[k][cl];
+      part[(int64_t)blockIdx.x * N + c] = t;
+    }
+    __syncthreads();
+  }
+}
+
+// out[c] = sum_z part[z, c] for MANY slabs and few columns (bias gradient: 384 slabs x <= 512 columns): one warp per
+// column, lanes stride the slabs, fixed-order shuffle tree => deterministic.
+__global__ void __launch_bounds__(256)
+reduce_cols_kernel(const float* __restrict__ part, int slabs, int n, float* __restrict__ out) {
+  int lane = threadIdx.x & 31;
+  int c = blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (c >= n) return;
+  float s = 0.0f;
+  for (int z = lane; z < slabs; z += 32) s += __ldg(part + (int64_t)z * n + c);
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) s += __shfl_down_sync(0xffffffffu, s, d);
+  if (lane == 0) out[c] = s;
+}
+
 // out[i] = sum_z part[z, i]  (fixed order => deterministic)
 __global__ void __launch_bounds__(256)
 reduce_slabs_kernel(const float* __restrict__ part, int splits, int64_t n, float* __restrict__ out) {
@@ -146,9 +181,11 @@ reduce_slabs_kernel(const float* __restrict__ part, int splits, int64_t n, float
 // rows per block the grid was 48 blocks and this memory-bound pass took longer than the GEMMs)
 constexpr int kColsumRows = 64;
 
-static int dw_splits(int64_t M, int K, int Nout) {
-  int64_t tiles = ceil_div(Nout, BM) * ceil_div(K, BN);
-  int64_t want = ceil_div(4 * kNumSMs, tiles);
+// K-splits of the dW = dZ^T X reduction over the M samples.  SIMT path: ~4 CTAs per SM.  Tensor-core path (128 x 128|64
+// tiles, one CTA per SM): as many splits as still fit ONE wave -- 152 CTAs on 148 SMs would run as two.
+static int dw_splits(int64_t M, int K, int Nout, bool use_tc) {
+  int64_t tiles = use_tc ? ceil_div(Nout, 128) * ceil_div(K, K > 64 ? 128 : 64) : ceil_div(Nout, BM) * ceil_div(K, BN);
+  int64_t want = use_tc ? kNumSMs / tiles : ceil_div(4 * kNumSMs, tiles);
   int64_t max_by_m = ceil_div(M, 256);
   int64_t s = want < max_by_m ? want : max_by_m;
   return (int)(s < 1 ? 1 : s);
@@ -161,7 +198,8 @@ using namespace b200lab;
 extern "C" {
 
 int64_t b200lab_linear_bwd_workspace_bytes(int64_t M, int32_t K, int32_t Nout) {
-  int splits = dw_splits(M, K, Nout);
+  int s_simt = dw_splits(M, K, Nout, false), s_tc = dw_splits(M, K, Nout, true);
+  int splits = s_simt > s_tc ? s_simt : s_tc;   // the caller does not say which path will run
   int64_t colsum_blocks = ceil_div(M, kColsumRows);
   return ((int64_t)splits * Nout * K + colsum_blocks * Nout) * (int64_t)sizeof(float);
 }
@@ -193,13 +231,19 @@ int b200lab_linear_bwd(const float* X, const float* W, const float* Y, const flo
   const bool use_tc = precision != 0 && Nout >= kMinTcWidth && K >= kMinTcWidth;
   cudaStream_t s = (cudaStream_t)stream;
   const float* dz = dY;
-  if (elu) {
-    int64_t n = M * Nout;
-    int nb = (int)min64(ceil_div(n, 256), 16 * kNumSMs);
-    elu_bwd_kernel<<<nb, 256, 0, s>>>(Y, dY, dZ, n);
+  float* ws = (float*)workspace;
+  float* colsum_part = ws + (int64_t)dw_splits(M, K, Nout, use_tc) * Nout * K;
+  const int colsum_blocks = (int)ceil_div(M, kColsumRows);
+  if (elu) {   // dZ and the bias-gradient partial sums in one pass
+    elu_bwd_colsum_kernel<<<colsum_blocks, 256, 0, s>>>(Y, dY, dZ, M, Nout, kColsumRows, colsum_part);
     count_launch();
     dz = dZ;
+  } else {
+    colsum_partial_kernel<<<colsum_blocks, 256, 0, s>>>(dz, M, Nout, kColsumRows, colsum_part);
+    count_launch();
   }
+  reduce_cols_kernel<<<(unsigned)ceil_div(Nout, 8), 256, 0, s>>>(colsum_part, colsum_blocks, Nout, db);
+  count_launch();
   if (dX) {  // dX[M,K] = dZ[M,Nout] . W[Nout,K]
     if (use_tc) {
       int rc = gemm_tc(dz, Nout, 1, W, K, 1, dX, K, M, K, Nout, Nout, 1, nullptr, 0, precision, s);
@@ -211,8 +255,7 @@ int b200lab_linear_bwd(const float* X, const float* W, const float* Y, const flo
     }
   }
   // dW[Nout,K] = sum_m dZ[m,n] X[m,k]: A(i=n,k=m) = dZ[m*Nout + n], B(k=m,j=k) = X[m*K + k]
-  float* ws = (float*)workspace;
-  int splits = dw_splits(M, K, Nout);
+  int splits = dw_splits(M, K, Nout, use_tc);
   int64_t k_per = ceil_div(ceil_div(M, splits), 32) * 32;   // multiple of both paths' K tile
   splits = (int)ceil_div(M, k_per);
   {
@@ -230,13 +273,6 @@ int b200lab_linear_bwd(const float* X, const float* W, const float* Y, const flo
       reduce_slabs_kernel<<<(unsigned)ceil_div(n, 256), 256, 0, s>>>(ws, splits, n, dW);
       count_launch();
     }
-  }
-  {
-    float* part = ws + (int64_t)dw_splits(M, K, Nout) * Nout * K;
-    int blocks = (int)ceil_div(M, kColsumRows);
-    colsum_partial_kernel<<<blocks, 256, 0, s>>>(dz, M, Nout, kColsumRows, part);
-    reduce_slabs_kernel<<<(unsigned)ceil_div(Nout, 256), 256, 0, s>>>(part, blocks, Nout, db);
-    count_launch(2);
   }
   return check_launch("linear_bwd");
 }

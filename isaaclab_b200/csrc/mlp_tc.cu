@@ -5,35 +5,50 @@
 // Y = X W^T, dX = dZ W and dW = dZ^T X without transposed copies) and an optional split of K over grid.z.
 //
 // Arithmetic: the reference computes these layers in fp32 (torch's default: TF32 matmul off).  Tensor cores offer
-// kind::tf32 (10-bit mantissa), so every operand is split while it is staged into shared memory,
-//     x = hi + lo,  hi = x with the low 13 mantissa bits cleared (exactly representable in TF32),  lo = x - hi (exact),
-// and each K step issues THREE MMAs into the same fp32 TMEM accumulator:  Ahi.Bhi + Ahi.Blo + Alo.Bhi  ("3xTF32").
-// The dropped Alo.Blo term and the TF32 rounding of lo are O(2^-22) relative -- the result agrees with an fp32 FFMA
-// GEMM to a few ulp.  precision 1 = single TF32 MMA (fast, reduced precision, opt-in only), precision 2 = 3xTF32.
+// kind::tf32, which reads the top 19 bits of each 32-bit operand word and IGNORES the low 13 mantissa bits (measured:
+// tools/umma_probe.cu -- truncation, not rounding).  So the raw fp32 tile in shared memory already is the "hi" operand,
+//     x = hi + lo,  hi = x with the low 13 mantissa bits cleared,  lo = x - hi (exact in fp32),
+// only `lo` has to be computed, and each K step issues THREE MMAs into the same fp32 TMEM accumulator:
+//     Araw.Braw + Araw.Blo + Alo.Braw  ("3xTF32").  The dropped Alo.Blo term and the truncation of lo are O(2^-22)
+// relative: the result agrees with an fp32 FFMA GEMM to a few ulp.  precision 1 = the first MMA only (opt-in).
 //
-// Structure (one CTA = one 128 x BN tile, 256 threads, 1 CTA / SM):
-//   all 8 warps : global -> registers -> hi/lo split -> st.shared into the canonical K-major SWIZZLE_NONE UMMA layout
-//                 (core matrix = 8 rows x 16 B; LBO padded by 16 B so the 128-bit stores are bank-conflict free)
-//   thread 0    : tcgen05.mma.cta_group::1.kind::tf32 over the BK/8 K steps of the stage, tcgen05.commit -> mbarrier
-//   2 stages    : the MMAs of k-tile t run while every warp stages k-tile t+1
-//   epilogue    : tcgen05.ld (32 lanes x 32 bit, 16 columns at a time) -> +bias -> ELU -> global
-// Operands are split by the threads, so they cannot come through TMA; the staging traffic (L2 -> SM) is what bounds the
-// kernel, not the tensor pipe.
+// Structure (one CTA = one 128 x BN tile; 16 producer warps + 1 MMA warp; ring of kStages raw stages + 2 lo buffers):
+//   producer warps : cp.async global -> shared (16-byte copies wherever the operand is contiguous and aligned along K
+//                    or along M/N, 4-byte copies otherwise; zero-fill for out-of-range rows / K tail), then each thread
+//                    re-reads exactly the bytes it copied, writes lo = x - trunc(x) to the stage's lo buffer,
+//                    fence.proxy.async, mbarrier.arrive(full[s]).  Loads for tile kt+kStages-1 are issued right after
+//                    tile kt has been handed over, so kStages-2 tiles are always in flight under the MMAs.
+//   MMA warp       : one lane waits full[s], issues the BK/8 x {1,3} tcgen05.mma.cta_group::1.kind::tf32, and
+//                    tcgen05.commit -> empty[s] (releases the stage to the producers); the last commit -> done.
+//   epilogue       : producer warps tcgen05.ld the accumulator (lane = row), transpose 32x32 through shared memory,
+//                    +bias, ELU, coalesced stores.
+// Shared-memory operand layouts (word maps read back from the hardware with tools/umma_probe.cu):
+//   K-contiguous operand  : K-major SWIZZLE_128B (layout type 2): offset(r,k) = (r/8)*1024 + (r%8)*128 +
+//                           (((k/4) ^ (r%8))*16) + (k%4)*4 -- a row's 32 tf32 are one 128-byte line, so the copies of a
+//                           warp land as full 128-byte wavefronts (the un-swizzled core-matrix layout scatters a row's
+//                           16-byte chunks and cost 9x the shared-memory wavefronts: profiles/r1_notes.md)
+//   M/N-contiguous operand: MN-major SWIZZLE_128B_BASE32B (layout type 1, the only MN-major layout 32-bit operands
+//                           have): offset(mn,k) = swz((mn/32)*LBO + (k/4)*SBO + (k%4)*128 + (mn%32)*4), LBO = 4096,
+//                           SBO = 512, swz: byte-address bits [5,7) ^= bits [7,9)
+// so dX (B = W read along its rows) and dW (both operands read along the sample dimension) need no transposition.
 #include "common.cuh"
 
 namespace b200lab {
 
 namespace tc {
 
-constexpr int BM = 128;        // UMMA M (cta_group::1)
-constexpr int BK = 32;         // K elements per stage = 8 chunks of 4 tf32 (16 B) = 4 MMA K-steps of 8
-constexpr int kThreads = 256;
-constexpr int kStages = 1;     // one smem stage per CTA, 2-3 CTAs per SM: the CTAs' load latencies, stores and MMAs interleave
+constexpr int BM = 128;               // UMMA M (cta_group::1)
+constexpr int BK = 32;                // K elements per stage = 4 MMA K-steps of 8 tf32
+constexpr int kProducers = 512;       // 16 warps stage operands and run the epilogue (4 per scheduler hide the ALU latency)
+constexpr int kThreads = kProducers + 32;   // + the MMA warp
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
 __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   asm volatile(
@@ -50,6 +65,16 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src, uint32_t src_bytes) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async4(uint32_t dst, const void* src, uint32_t src_bytes) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(dst), "l"(src), "r"(src_bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
 __device__ __forceinline__ void tmem_alloc(uint32_t dst_smem, uint32_t ncols) {
   asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "r"(ncols) : "memory");
@@ -86,172 +111,171 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, float (&v)[16]) {
   for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
 }
 
-// Shared-memory matrix descriptor, K-major, SWIZZLE_NONE (cute::UMMA::SmemDescriptor bit layout, version 1):
-//   [0,14) start address >> 4 | [16,30) leading-dimension byte offset >> 4 (between the 16-byte K chunks)
-//   [32,46) stride-dimension byte offset >> 4 (between 8-row groups) | [46,48) version = 1 | [61,64) layout type = 0
-__device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t lbo, uint32_t sbo) {
+// Shared-memory matrix descriptor (cute::UMMA::SmemDescriptor bit layout, version 1):
+//   [0,14) start address >> 4 | [16,30) leading-dimension byte offset >> 4 | [32,46) stride-dimension byte offset >> 4
+//   [46,48) version = 1 | [61,64) layout type (0 = SWIZZLE_NONE, 1 = SWIZZLE_128B_BASE32B, 2 = SWIZZLE_128B)
+__device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t lbo, uint32_t sbo, uint32_t layout) {
   return (uint64_t)((saddr >> 4) & 0x3FFFu) | ((uint64_t)((lbo >> 4) & 0x3FFFu) << 16) |
-         ((uint64_t)((sbo >> 4) & 0x3FFFu) << 32) | (1ull << 46);
+         ((uint64_t)((sbo >> 4) & 0x3FFFu) << 32) | (1ull << 46) | ((uint64_t)layout << 61);
 }
 
 // Instruction descriptor (cute::UMMA::InstrDescriptor): c_format F32 = 1 @[4,6), a/b_format TF32 = 2 @[7,10)/[10,13),
-// a/b_major K = 0 @15/16, n_dim = N >> 3 @[17,23), m_dim = M >> 4 @[24,29)
+// a/b_major (0 = K, 1 = MN) @15/16, n_dim = N >> 3 @[17,23), m_dim = M >> 4 @[24,29)
 __host__ __device__ constexpr uint32_t make_idesc(int m, int n) {
   return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
 }
 
-// Operand tile of ROWS x BK tf32 values in the canonical K-major SWIZZLE_NONE layout: core matrix = 8 rows x 16 B (4 k),
-//   offset(r, k) = (k/4)*kLboK + r*16 + (k%4)*4          i.e. [K chunks][rows][4]
-// with the chunk stride padded by 16 B so that the lanes of a store instruction fall into different banks.
-template <int ROWS>
-struct Tile {
-  static constexpr uint32_t kLboK = ROWS * 16 + 16, kSboK = 128;
-  static constexpr uint32_t kBytes = (BK / 4) * kLboK;
+// How an operand tile of ROWS x BK elements (element (r, k) at src + r*ld_r + k*ld_k) is brought in and laid out.
+enum OperandMode {
+  kKVec = 0,      // ld_k == 1, rows 16-byte aligned      -> 16-byte copies along k,    K-major layout
+  kKScalar = 1,   // k fastest but unaligned (235-wide)   ->  4-byte copies,            K-major layout
+  kMnVec = 2,     // ld_r == 1, k-columns 16-byte aligned -> 16-byte copies along rows, MN-major layout
+  kMnScalar = 3,  // rows fastest but unaligned           ->  4-byte copies,            MN-major layout
 };
 
-// how an operand is brought in: scalar loads | float4 along k | float4 along the rows, transposed while it is stored
-enum StageMode { kScalarK = 0, kVecK = 1, kVecMN = 2 };
+template <int ROWS>
+struct Tile {
+  // K-major SWIZZLE_128B: a row's BK = 32 tf32 are one 128-byte line, 8-row groups 1024 B apart (SBO); LBO unused
+  static constexpr uint32_t kSboK = 1024;
+  // MN-major SWIZZLE_128B_BASE32B: 32 rows x 4 k atoms of 512 B; k-atoms adjacent (SBO), 32-row groups LBO apart
+  static constexpr uint32_t kLboMn = (BK / 4) * 512, kSboMn = 512;
+  static constexpr uint32_t kBytes = ROWS * BK * 4;   // either layout, no padding; buffers are 1024-byte aligned
+};
 
+// K-major SWIZZLE_128B: 16-byte chunk index ^= row % 8 (byte-address bits [4,7) ^= bits [7,10))
+__device__ __forceinline__ uint32_t k_offset(int r, int k) {
+  return ((uint32_t)(r >> 3) << 10) + ((uint32_t)(r & 7) << 7) + ((((uint32_t)(k >> 2) ^ (uint32_t)r) & 7u) << 4) + ((uint32_t)(k & 3) << 2);
+}
+__device__ __forceinline__ uint32_t swz_mn(uint32_t off) { return off ^ (((off >> 7) & 3u) << 5); }
+
+// Per-thread, per-operand addressing, fixed for the whole K loop (MODE is a template parameter: no runtime dispatch in
+// the loop).  Slot `it` of a thread copies the element(s) at row r_local + it*r_step, k = k_local + it*k_step (first
+// element of the 16-byte vector in the vec modes) from  cur + it*step  to shared offset  off0 + it*off_step;  `cur`
+// advances by BK*ld_k per k-tile.  One of r_step / k_step is always 0.
+template <int ROWS, int MODE>
+struct Cursor {
+  static constexpr bool kVec = MODE == kKVec || MODE == kMnVec;
+  static constexpr int kSlots = kVec ? ROWS * BK / 4 / kProducers : ROWS * BK / kProducers;
+  static constexpr int kRowsPerPass = MODE == kKVec ? kProducers / 8 : kProducers / BK;              // K-major modes
+  static constexpr int kKPerPass = MODE == kMnVec ? kProducers / (ROWS / 4) : kProducers / ROWS;     // MN-major modes
+  static constexpr bool kKMajor = MODE == kKVec || MODE == kKScalar;
+  static constexpr uint32_t kOffStep = kKMajor ? (uint32_t)(kRowsPerPass / 8) * Tile<ROWS>::kSboK : (uint32_t)(kKPerPass / 4) * Tile<ROWS>::kSboMn;
+  static_assert(!kKMajor || kRowsPerPass % 8 == 0, "K-major slots must keep their swizzle phase");
+  static_assert(kSlots >= 1, "tile too small for the producer count");
+  static_assert(kKMajor || kKPerPass % 4 == 0, "MN-major slots must keep their swizzle phase");
+  const float* cur;     // source of slot 0 for the NEXT k-tile to be issued
+  int64_t step, tile_step;
+  uint32_t off0;
+  uint32_t row_ok;      // K-major: bit it = slot's row is inside the matrix.  MN-major: valid rows of the vector / element (0..4)
+  int k_left;           // k elements left from slot 0's k for the next k-tile to be issued (may be <= 0)
+
+  __device__ __forceinline__ void init(const float* src, int64_t ld_r, int64_t ld_k, int64_t r0, int64_t rows_valid,
+                                       int64_t k_begin, int64_t k_end, int tid) {
+    int r_local, k_local;
+    if (MODE == kKVec)         { k_local = (tid & 7) * 4; r_local = tid >> 3; }
+    else if (MODE == kKScalar) { k_local = tid & (BK - 1); r_local = tid >> 5; }
+    else if (MODE == kMnVec)   { r_local = (tid % (ROWS / 4)) * 4; k_local = tid / (ROWS / 4); }
+    else                       { r_local = tid % ROWS; k_local = tid / ROWS; }
+    if (kKMajor) {
+      off0 = k_offset(r_local, k_local);
+      step = (int64_t)kRowsPerPass * ld_r;
+      row_ok = 0;
+#pragma unroll
+      for (int it = 0; it < kSlots; ++it)
+        if (r0 + r_local + it * kRowsPerPass < rows_valid) row_ok |= 1u << it;
+    } else {
+      off0 = swz_mn((uint32_t)(r_local >> 5) * Tile<ROWS>::kLboMn + (uint32_t)(k_local >> 2) * Tile<ROWS>::kSboMn +
+                    (uint32_t)(k_local & 3) * 128 + (uint32_t)(r_local & 31) * 4);
+      step = (int64_t)kKPerPass * ld_k;
+      const int64_t left = rows_valid - (r0 + r_local);
+      row_ok = (uint32_t)(left < 0 ? 0 : (left > 4 ? 4 : left));
+    }
+    cur = src + (r0 + r_local) * ld_r + (k_begin + k_local) * ld_k;
+    tile_step = (int64_t)BK * ld_k;
+    k_left = (int)min64(k_end - k_begin - k_local, 1 << 28);
+  }
+
+  // cp.async of this thread's slots of the next k-tile; rows outside the matrix and the K tail are zero-filled by the
+  // copy (src-size < cp-size reads only src-size bytes -- the address of a fully masked copy is never dereferenced)
+  __device__ __forceinline__ void issue(uint32_t s_raw) {
+    const float* p = cur;
+#pragma unroll
+    for (int it = 0; it < kSlots; ++it) {
+      uint32_t bytes;
+      if (MODE == kKVec) {
+        const int kl = k_left < 0 ? 0 : (k_left > 4 ? 4 : k_left);
+        bytes = ((row_ok >> it) & 1u) ? (uint32_t)kl * 4u : 0u;
+      } else if (MODE == kKScalar) {
+        bytes = (((row_ok >> it) & 1u) && k_left > 0) ? 4u : 0u;
+      } else if (MODE == kMnVec) {
+        bytes = (k_left - it * kKPerPass > 0) ? row_ok * 4u : 0u;
+      } else {
+        bytes = (k_left - it * kKPerPass > 0 && row_ok) ? 4u : 0u;
+      }
+      if (kVec) cp_async16(s_raw + off0 + (uint32_t)it * kOffStep, p, bytes);
+      else      cp_async4(s_raw + off0 + (uint32_t)it * kOffStep, p, bytes);
+      p += step;
+    }
+    cur += tile_step;
+    k_left -= BK;
+  }
+};
+
+// Shared memory: a ring of kStages RAW stages (A | B, filled by cp.async) and TWO lo buffers (A lo | B lo).  Only the
+// k-tile being multiplied needs its lo part, so the bytes in flight from L2 are not halved by it: kStages-1 raw tiles
+// are outstanding while one tile is split and another is multiplied.
 template <int BN>
 struct Smem {
+  static constexpr int kStages = BN > 64 ? 5 : 7;
   static constexpr uint32_t kA = Tile<BM>::kBytes, kB = Tile<BN>::kBytes;
-  static constexpr uint32_t kStage = 2 * kA + 2 * kB;         // A hi, A lo, B hi, B lo
-  static constexpr uint32_t kTotal = kStages * kStage + 64;   // + barriers / tmem pointer
+  static constexpr uint32_t kStage = kA + kB;                      // A raw, B raw   (lo buffer: A lo, B lo)
+  static constexpr uint32_t kLo = kStages * kStage;                // two lo buffers follow the raw ring
+  static constexpr uint32_t kCtl = kLo + 2 * kStage;               // full[kStages], empty[kStages], done, tmem pointer
+  static constexpr uint32_t kTotal = kCtl + 16 * kStages + 16 + 1024;   // + slack to align the base to 1024
 };
 
 __device__ __forceinline__ float exp2f_fast(float x) { float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
 
-__device__ __forceinline__ void split_tf32(float x, float& hi, float& lo) {
-  hi = __uint_as_float(__float_as_uint(x) & 0xFFFFE000u);
-  lo = x - hi;
-}
-
-// Staging of ROWS x BK elements of a strided operand (element (r, k) at src + r*ld_r + k*ld_k; rows < rows_valid,
-// k in [k0, k_end)) in two phases, so that ALL of a thread's loads are in flight together and -- issued right after the
-// MMAs of the previous k-tile -- complete under them:  load_operand (global -> registers, raw; out-of-range slots read
-// a safe address, no branches around the loads)  and  store_operand (zero out-of-range, hi/lo split, st.shared).
-//   kVecK   : ld_k == 1, 16-byte aligned rows      -> float4 along k
-//   kVecMN  : ld_r == 1, 16-byte aligned k-columns -> float4 along the rows, stored as 4 scalars (transposed into the
-//             K-major layout); lanes = 2 adjacent row groups x 16 k, which keeps both the 32-byte sectors of the loads
-//             full and the 32 scalar stores of a warp in 32 different banks
-//   kScalarK: anything else (e.g. the 235-wide observation rows) -> scalar loads, K-major layout
-template <int ROWS>
-struct Frag { float f[ROWS * BK / kThreads]; };
-
-// Per-thread addressing, fixed for the whole K loop: slot `it` lives at base + it*step (+ k0*ld_k per k-tile).
-template <int ROWS>
-struct Cursor {
-  const float* base;
-  int64_t step;
-  uint32_t row_ok;       // bit `it`: the slot's row(s) are inside the matrix
-  int k_local, k_step;   // k of slot `it` inside the k-tile = k_local + it * k_step
-  int r_local, r_step;   // row of slot `it` inside the tile = r_local + it * r_step
-};
-
-template <int ROWS>
-__device__ __forceinline__ Cursor<ROWS> make_cursor(const float* src, int64_t ld_r, int64_t ld_k, int64_t r0, int64_t rows_valid,
-                                                    int mode, int tid) {
-  constexpr int kElems = ROWS * BK / kThreads;
-  Cursor<ROWS> c;
-  c.row_ok = 0;
-  if (mode == kVecK) {            // slot it: k = 4*(tid%8), r = tid/8 + 32*it
-    c.k_local = (tid % (BK / 4)) * 4; c.k_step = 0;
-    c.r_local = tid / (BK / 4);       c.r_step = kThreads / (BK / 4);
-  } else if (mode == kVecMN) {    // slot it: k = 16*(warp%2) + lane/2, r = 4*(2*(warp/2 + 4*it) + lane%2)
-    const int warp = tid >> 5, lane = tid & 31;
-    c.k_local = (warp & 1) * 16 + (lane >> 1); c.k_step = 0;
-    c.r_local = ((warp >> 1) * 2 + (lane & 1)) * 4; c.r_step = 32;
-  } else if ((ld_k == 1) || (ld_k < ld_r)) {   // scalar, k fastest: k = tid%32, r = tid/32 + 8*it
-    c.k_local = tid % BK; c.k_step = 0;
-    c.r_local = tid / BK; c.r_step = kThreads / BK;
-  } else {                        // scalar, rows fastest: r = tid%ROWS, k = tid/ROWS + (256/ROWS)*it
-    c.r_local = tid % ROWS; c.r_step = 0;
-    c.k_local = tid / ROWS; c.k_step = kThreads / ROWS;
-  }
-  c.base = src + (r0 + c.r_local) * ld_r + c.k_local * ld_k;
-  c.step = c.r_step * ld_r + c.k_step * ld_k;
-  const int slots = (mode == kScalarK) ? kElems : kElems / 4;
+// lo = x - trunc_tf32(x) over a whole raw stage (A | B), written to the lo buffer in the SAME layout -- so the pass is a
+// linear sweep, independent of the operand layouts.  (Each thread must only touch bytes whose copies it can see: the
+// sweep runs after a CTA-wide hand-over of "my copies have landed", see the producer loop.)
+template <uint32_t BYTES>
+__device__ __forceinline__ void lo_sweep(const uint8_t* __restrict__ raw, uint8_t* __restrict__ lo, int tid) {
+  constexpr int kChunks = BYTES / 16;
 #pragma unroll
-  for (int it = 0; it < kElems; ++it)
-    if (it < slots && r0 + c.r_local + it * c.r_step < rows_valid) c.row_ok |= 1u << it;   // kVecMN: rows_valid % 4 == 0
-  return c;
-}
-
-template <int ROWS>
-__device__ __forceinline__ void load_operand(Frag<ROWS>& fr, const Cursor<ROWS>& c, const float* __restrict__ safe,
-                                             int64_t ld_k, int64_t k0, int64_t k_end, int mode) {
-  constexpr int kElems = ROWS * BK / kThreads;
-  const float* p = c.base + k0 * ld_k;
-  // raw values only: nothing may consume a load here, or the thread stalls on it instead of letting it fly under the
-  // MMAs -- out-of-range slots are zeroed in store_operand
-  if (mode != kScalarK) {
-#pragma unroll
-    for (int it = 0; it < kElems / 4; ++it) {
-      const bool ok = ((c.row_ok >> it) & 1u) && (k0 + c.k_local + it * c.k_step < k_end);
-      float4 v = __ldg(reinterpret_cast<const float4*>(ok ? p + it * c.step : safe));
-      fr.f[it * 4 + 0] = v.x; fr.f[it * 4 + 1] = v.y; fr.f[it * 4 + 2] = v.z; fr.f[it * 4 + 3] = v.w;
-    }
-  } else {
-#pragma unroll
-    for (int it = 0; it < kElems; ++it) {
-      const bool ok = ((c.row_ok >> it) & 1u) && (k0 + c.k_local + it * c.k_step < k_end);
-      fr.f[it] = __ldg(ok ? p + it * c.step : safe);
+  for (int c0 = 0; c0 < kChunks; c0 += kProducers) {
+    const int c = c0 + tid;
+    if (c0 + kProducers <= kChunks || c < kChunks) {
+      const float4 v = *reinterpret_cast<const float4*>(raw + (size_t)c * 16);
+      float4 l;
+      l.x = v.x - __uint_as_float(__float_as_uint(v.x) & 0xFFFFE000u);
+      l.y = v.y - __uint_as_float(__float_as_uint(v.y) & 0xFFFFE000u);
+      l.z = v.z - __uint_as_float(__float_as_uint(v.z) & 0xFFFFE000u);
+      l.w = v.w - __uint_as_float(__float_as_uint(v.w) & 0xFFFFE000u);
+      *reinterpret_cast<float4*>(lo + (size_t)c * 16) = l;
     }
   }
 }
 
-template <int ROWS, bool SPLIT>
-__device__ __forceinline__ void store_operand(const Frag<ROWS>& fr, const Cursor<ROWS>& c, int64_t k0, int64_t k_end, int mode,
-                                              uint8_t* s_hi, uint8_t* s_lo) {
-  constexpr int kElems = ROWS * BK / kThreads;
-  if (mode != kScalarK) {
-#pragma unroll
-    for (int it = 0; it < kElems / 4; ++it) {
-      const int k = c.k_local + it * c.k_step, r = c.r_local + it * c.r_step;
-      const int64_t gk = k0 + k;
-      const bool ok = ((c.row_ok >> it) & 1u) != 0;
-      const bool along_k = mode == kVecK;   // the 4 lanes of the float4 step along k (ragged K tail) or along rows
-      float x0 = (ok && gk < k_end) ? fr.f[it * 4 + 0] : 0.f;
-      float x1 = (ok && gk + (along_k ? 1 : 0) < k_end) ? fr.f[it * 4 + 1] : 0.f;
-      float x2 = (ok && gk + (along_k ? 2 : 0) < k_end) ? fr.f[it * 4 + 2] : 0.f;
-      float x3 = (ok && gk + (along_k ? 3 : 0) < k_end) ? fr.f[it * 4 + 3] : 0.f;
-      float4 h, l;
-      split_tf32(x0, h.x, l.x); split_tf32(x1, h.y, l.y); split_tf32(x2, h.z, l.z); split_tf32(x3, h.w, l.w);
-      const uint32_t off = (uint32_t)(k >> 2) * Tile<ROWS>::kLboK + (uint32_t)r * 16 + (uint32_t)(k & 3) * 4;
-      if (along_k) {
-        *reinterpret_cast<float4*>(s_hi + off) = h;
-        if (SPLIT) *reinterpret_cast<float4*>(s_lo + off) = l;
-      } else {   // the float4 runs along 4 consecutive rows of one k
-        *reinterpret_cast<float*>(s_hi + off) = h.x; *reinterpret_cast<float*>(s_hi + off + 16) = h.y;
-        *reinterpret_cast<float*>(s_hi + off + 32) = h.z; *reinterpret_cast<float*>(s_hi + off + 48) = h.w;
-        if (SPLIT) {
-          *reinterpret_cast<float*>(s_lo + off) = l.x; *reinterpret_cast<float*>(s_lo + off + 16) = l.y;
-          *reinterpret_cast<float*>(s_lo + off + 32) = l.z; *reinterpret_cast<float*>(s_lo + off + 48) = l.w;
-        }
-      }
-    }
-  } else {
-#pragma unroll
-    for (int it = 0; it < kElems; ++it) {
-      const int k = c.k_local + it * c.k_step, r = c.r_local + it * c.r_step;
-      const bool ok = ((c.row_ok >> it) & 1u) && (k0 + k < k_end);
-      float h, l;
-      split_tf32(ok ? fr.f[it] : 0.f, h, l);
-      const uint32_t off = (uint32_t)(k >> 2) * Tile<ROWS>::kLboK + (uint32_t)r * 16 + (uint32_t)(k & 3) * 4;
-      *reinterpret_cast<float*>(s_hi + off) = h;
-      if (SPLIT) *reinterpret_cast<float*>(s_lo + off) = l;
-    }
-  }
+template <int ROWS>
+__device__ __forceinline__ uint64_t operand_desc(uint32_t base, int ks, bool mn_major) {
+  // one MMA K-step = 8 tf32 = 32 bytes along the swizzled 128-byte row (K-major; the hardware applies the XOR to the
+  // final address) or two 4-row k-atoms (MN-major)
+  return mn_major ? make_desc(base + (uint32_t)ks * 2u * Tile<ROWS>::kSboMn, Tile<ROWS>::kLboMn, Tile<ROWS>::kSboMn, 1u)
+                  : make_desc(base + (uint32_t)ks * 32u, 16u, Tile<ROWS>::kSboK, 2u);
 }
 
-// EPI: 0 = store, 1 = +bias, 2 = +bias then ELU.  SPLIT: 3xTF32 (true) or single TF32 (false).
-template <int BN, int EPI, bool SPLIT>
-__global__ void __launch_bounds__(kThreads, 2)
+// epi: 0 = store, 1 = +bias, 2 = +bias then ELU.  split: 3xTF32 (1) or single TF32 (0).
+template <int BN, int AMODE, int BMODE>
+__global__ void __launch_bounds__(kThreads, 1)
 gemm_tf32_kernel(const float* __restrict__ A, int64_t lda_i, int64_t lda_k, const float* __restrict__ B, int64_t ldb_k,
                  int64_t ldb_j, float* __restrict__ C, int64_t ldc, int64_t M, int N, int64_t K, int64_t k_per_split,
-                 const float* __restrict__ bias, int a_mode, int b_mode) {
-  extern __shared__ __align__(1024) uint8_t smem[];
+                 const float* __restrict__ bias, int epi, int split) {
+  extern __shared__ uint8_t smem_dyn[];
   using S = Smem<BN>;
+  constexpr int kStages = S::kStages;
+  constexpr int kMmaWarp = kProducers / 32;
+  uint8_t* smem = smem_dyn + ((1024u - (smem_u32(smem_dyn) & 1023u)) & 1023u);   // MN-major swizzle atoms: 1024-byte aligned
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int64_t i0 = (int64_t)blockIdx.x * BM;
   const int j0 = blockIdx.y * BN;
@@ -259,86 +283,94 @@ gemm_tf32_kernel(const float* __restrict__ A, int64_t lda_i, int64_t lda_k, cons
   const int64_t k_end = min64(K, k_begin + k_per_split);
   const int num_kt = (int)((k_end - k_begin + BK - 1) / BK);
 
-  uint8_t* ctl = smem + kStages * S::kStage;
-  const uint32_t bar_stage0 = smem_u32(ctl), bar_done = smem_u32(ctl + 8 * kStages);
-  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(ctl + 8 * kStages + 8);
+  uint8_t* ctl = smem + S::kCtl;
+  const uint32_t bar_full = smem_u32(ctl), bar_empty = bar_full + 8 * kStages, bar_done = bar_full + 16 * kStages;
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(ctl + 16 * kStages + 8);
 
   if (tid == 0) {
-    for (int s = 0; s < kStages; ++s) mbar_init(bar_stage0 + 8 * s, 1);
+    for (int s = 0; s < kStages; ++s) {
+      mbar_init(bar_full + 8 * s, kProducers);
+      mbar_init(bar_empty + 8 * s, 1);
+    }
     mbar_init(bar_done, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  if (warp == 0) tmem_alloc(smem_u32(tmem_ptr_smem), BN);   // BN in {32,64,128,256}: power of two >= 32 columns
+  if (warp == kMmaWarp) tmem_alloc(smem_u32(tmem_ptr_smem), BN);   // BN in {64,128}: power of two >= 32 columns
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_d = *tmem_ptr_smem;
 
-  constexpr uint32_t idesc = make_idesc(BM, BN);   // both operands K-major in shared memory
-  uint32_t phase_bits = 0;   // bit s = parity to wait for on stage s
-  Frag<BM> fa;
-  Frag<BN> fb;
-  const Cursor<BM> ca = make_cursor<BM>(A, lda_i, lda_k, i0, M, a_mode, tid);
-  const Cursor<BN> cb = make_cursor<BN>(B, ldb_j, ldb_k, j0, N, b_mode, tid);
-  if (num_kt > 0) {
-    load_operand<BM>(fa, ca, A, lda_k, k_begin, k_end, a_mode);
-    load_operand<BN>(fb, cb, B, ldb_k, k_begin, k_end, b_mode);
-  }
-  for (int kt = 0; kt < num_kt; ++kt) {
-    const int s = kt % kStages;
-    uint8_t* st = smem + s * S::kStage;
-    uint8_t *a_hi = st, *a_lo = st + S::kA, *b_hi = st + 2 * S::kA, *b_lo = st + 2 * S::kA + S::kB;
-    if (kt >= kStages) {   // the MMAs that read this stage (k-tile kt - kStages) must have drained
-      mbar_wait(bar_stage0 + 8 * s, (phase_bits >> s) & 1u);
-      phase_bits ^= 1u << s;
+  if (warp < kMmaWarp) {
+    // ---------------- producers ----------------
+    Cursor<BM, AMODE> ca;
+    Cursor<BN, BMODE> cb;
+    ca.init(A, lda_i, lda_k, i0, M, k_begin, k_end, tid);
+    cb.init(B, ldb_j, ldb_k, j0, N, k_begin, k_end, tid);
+    auto issue = [&](int kt_new) {
+      const uint32_t st = smem_u32(smem + (kt_new % kStages) * S::kStage);
+      ca.issue(st);
+      cb.issue(st + S::kA);
+    };
+#pragma unroll
+    for (int p = 0; p < kStages - 1; ++p) {
+      if (p < num_kt) issue(p);
+      cp_async_commit();
     }
-    const int64_t k_cur = k_begin + (int64_t)kt * BK;
-    store_operand<BM, SPLIT>(fa, ca, k_cur, k_end, a_mode, a_hi, a_lo);
-    store_operand<BN, SPLIT>(fb, cb, k_cur, k_end, b_mode, b_hi, b_lo);
-    fence_proxy_async();   // generic-proxy smem writes -> visible to the tensor core (async proxy)
-    tc_fence_before();
-    __syncthreads();
-    if (tid == 0) {
+#pragma unroll 1
+    for (int kt = 0; kt < num_kt; ++kt) {
+      const int s = kt % kStages;
+      cp_async_wait<kStages - 2>();   // this thread's copies of k-tile kt have landed ...
+      if (split) {
+        // ... and, after the producers' barrier, everybody's: the lo sweep is linear over the stage, so a thread reads
+        // bytes other threads copied.  Lo buffer kt&1 was last read by the MMAs of k-tile kt-2 (waited for below, one
+        // iteration ago).
+        asm volatile("bar.sync 1, %0;" ::"n"(kProducers) : "memory");
+        lo_sweep<S::kStage>(smem + s * S::kStage, smem + S::kLo + (kt & 1) * S::kStage, tid);
+      }
+      fence_proxy_async();            // cp.async / st.shared (generic proxy) -> visible to the tensor core (async proxy)
+      mbar_arrive(bar_full + 8 * s);
+      // k-tile kt-1's MMAs done: its raw stage can be refilled (with k-tile kt+kStages-1) and, one iteration from now,
+      // its lo buffer rewritten -- so this wait is unconditional
+      if (kt >= 1) mbar_wait(bar_empty + 8 * ((kt - 1) % kStages), (uint32_t)(((kt - 1) / kStages) & 1));
+      if (kt + kStages - 1 < num_kt) issue(kt + kStages - 1);
+      cp_async_commit();
+    }
+  } else if (lane == 0) {
+    // ---------------- MMA issuer ----------------
+    constexpr bool a_mn = AMODE >= kMnVec, b_mn = BMODE >= kMnVec;
+    constexpr uint32_t idesc = make_idesc(BM, BN) | ((uint32_t)a_mn << 15) | ((uint32_t)b_mn << 16);
+#pragma unroll 1
+    for (int kt = 0; kt < num_kt; ++kt) {
+      const int s = kt % kStages;
+      const uint32_t sa = smem_u32(smem + s * S::kStage), sb = sa + S::kA;
+      const uint32_t sa_lo = smem_u32(smem + S::kLo + (kt & 1) * S::kStage), sb_lo = sa_lo + S::kA;
+      mbar_wait(bar_full + 8 * s, (uint32_t)((kt / kStages) & 1));
       tc_fence_after();
-      const uint32_t sa_hi = smem_u32(a_hi), sa_lo = smem_u32(a_lo), sb_hi = smem_u32(b_hi), sb_lo = smem_u32(b_lo);
 #pragma unroll
-#pragma unroll
-      for (int ks = 0; ks < BK / 8; ++ks) {   // one MMA K-step = 8 tf32 = two 16-byte chunks
-        const uint32_t oa = ks * 2 * Tile<BM>::kLboK, ob = ks * 2 * Tile<BN>::kLboK;
-        const uint64_t da_hi = make_desc(sa_hi + oa, Tile<BM>::kLboK, Tile<BM>::kSboK);
-        const uint64_t db_hi = make_desc(sb_hi + ob, Tile<BN>::kLboK, Tile<BN>::kSboK);
-        umma_tf32(tmem_d, da_hi, db_hi, idesc, (kt | ks) != 0);
-        if (SPLIT) {
-          const uint64_t da_lo = make_desc(sa_lo + oa, Tile<BM>::kLboK, Tile<BM>::kSboK);
-          const uint64_t db_lo = make_desc(sb_lo + ob, Tile<BN>::kLboK, Tile<BN>::kSboK);
-          umma_tf32(tmem_d, da_hi, db_lo, idesc, 1u);
-          umma_tf32(tmem_d, da_lo, db_hi, idesc, 1u);
+      for (int ks = 0; ks < BK / 8; ++ks) {
+        const uint64_t da = operand_desc<BM>(sa, ks, a_mn), db = operand_desc<BN>(sb, ks, b_mn);
+        umma_tf32(tmem_d, da, db, idesc, (kt | ks) != 0);
+        if (split) {
+          umma_tf32(tmem_d, da, operand_desc<BN>(sb_lo, ks, b_mn), idesc, 1u);
+          umma_tf32(tmem_d, operand_desc<BM>(sa_lo, ks, a_mn), db, idesc, 1u);
         }
       }
-      umma_commit(bar_stage0 + 8 * s);            // frees the stage for k-tile kt + kStages
-      if (kt == num_kt - 1) umma_commit(bar_done);  // accumulator complete
+      umma_commit(bar_empty + 8 * s);   // releases the stage once these MMAs have read it
     }
-    if (kt + 1 < num_kt) {   // next k-tile's loads fly under this k-tile's MMAs (issued AFTER the fence above: the
-                             // membar it lowers to would otherwise wait for them)
-      const int64_t k0 = k_begin + (int64_t)(kt + 1) * BK;
-      load_operand<BM>(fa, ca, A, lda_k, k0, k_end, a_mode);
-      load_operand<BN>(fb, cb, B, ldb_k, k0, k_end, b_mode);
-    }
+    if (num_kt > 0) umma_commit(bar_done);   // accumulator complete
   }
   // ---- epilogue: TMEM -> registers -> (32 x 32 transpose through shared memory) -> global.  Warp w may read TMEM lanes
-  // 32*(w%4)..+31 (= tile rows, one per lane); the two warps that share a lane quarter split the columns.  Written straight
-  // from the TMEM layout every store instruction would touch 32 rows (32 sectors); after the transpose it writes 128
-  // contiguous bytes of one row.
-  if (num_kt > 0) mbar_wait(bar_done, 0);
-  tc_fence_after();
-  {
-    const int q = warp & 3, half = warp >> 2;
+  // 32*(w%4)..+31 (= tile rows, one per lane); the warps that share a lane quarter split the columns in groups of 32.
+  // Written straight from the TMEM layout every store instruction would touch 32 rows (32 sectors); after the transpose
+  // it writes 128 contiguous bytes of one row.
+  if (warp < 4 * (BN / 32)) {
+    if (num_kt > 0) mbar_wait(bar_done, 0);
+    tc_fence_after();
+    const int q = warp & 3, c0 = (warp >> 2) * 32;
     float* Cz = C + (int64_t)blockIdx.z * M * ldc;
-    float* tile = reinterpret_cast<float*>(smem) + warp * (32 * 33);   // stage buffers are free: every MMA has completed
-    constexpr int kColsPerHalf = BN / 2;
-#pragma unroll 1
-    for (int c0 = half * kColsPerHalf; c0 < (half + 1) * kColsPerHalf; c0 += 32) {
-      if (j0 + c0 >= N) break;   // warp-uniform
+    float* tile = reinterpret_cast<float*>(smem) + warp * (32 * 33);   // raw stages are free: every MMA has completed
+    if (j0 + c0 < N) {   // warp-uniform
       float v[32];
       if (num_kt > 0) {
         float lo16[16], hi16[16];
@@ -356,56 +388,64 @@ gemm_tf32_kernel(const float* __restrict__ A, int64_t lda_i, int64_t lda_k, cons
       const int gj = j0 + c0 + lane;
       const bool col_ok = gj < N;
       float bv = 0.f;
-      if (EPI >= 1 && col_ok) bv = __ldg(bias + gj);
+      if (epi >= 1 && col_ok) bv = __ldg(bias + gj);
+      const bool elu = epi == 2;
 #pragma unroll 8
       for (int rr = 0; rr < 32; ++rr) {
         const int64_t gi = i0 + q * 32 + rr;
         if (gi >= M) break;      // warp-uniform
-        float x = tile[rr * 33 + lane];
-        if (EPI >= 1) x += bv;
-        if (EPI == 2) x = x > 0.0f ? x : exp2f_fast(1.4426950408889634f * x) - 1.0f;   // |abs err| ~1e-7
+        float x = tile[rr * 33 + lane] + bv;
+        if (elu) x = x > 0.0f ? x : exp2f_fast(1.4426950408889634f * x) - 1.0f;   // |abs err| ~1e-7
         if (col_ok) Cz[gi * ldc + gj] = x;
       }
-      __syncwarp();
     }
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 0) tmem_dealloc(tmem_d, BN);
+  if (warp == kMmaWarp) tmem_dealloc(tmem_d, BN);
 }
 
-template <int BN, int EPI, bool SPLIT>
+template <int BN, int AMODE, int BMODE>
 static int launch(const float* A, int64_t lda_i, int64_t lda_k, const float* B, int64_t ldb_k, int64_t ldb_j, float* C,
-                  int64_t ldc, int64_t M, int N, int64_t K, int64_t k_per_split, int splits, const float* bias,
-                  cudaStream_t s) {
-  auto kern = gemm_tf32_kernel<BN, EPI, SPLIT>;
+                  int64_t ldc, int64_t M, int N, int64_t K, int64_t k_per_split, int splits, const float* bias, int epi,
+                  int split, cudaStream_t s) {
+  auto kern = gemm_tf32_kernel<BN, AMODE, BMODE>;
   static bool configured = false;
   if (!configured) {
     cudaError_t err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Smem<BN>::kTotal);
     if (err != cudaSuccess) { set_error("tcgen05 gemm: %s", cudaGetErrorString(err)); return B200LAB_ERR_CUDA; }
     configured = true;
   }
-  // 128-bit loads along whichever dimension is contiguous; both need 16-byte aligned vectors, kVecK split boundaries on
-  // multiples of 4, kVecMN whole groups of 4 rows
-  auto mode_of = [&](const float* p, int64_t ld_r, int64_t ld_k, int64_t rows) -> int {
-    if ((uintptr_t)p % 16 != 0) return kScalarK;
-    if (ld_k == 1 && ld_r % 4 == 0 && k_per_split % 4 == 0) return kVecK;
-    if (ld_r == 1 && ld_k % 4 == 0 && rows % 4 == 0) return kVecMN;
-    return kScalarK;
-  };
   dim3 grid((unsigned)ceil_div(M, BM), (unsigned)ceil_div(N, BN), (unsigned)splits);
-  kern<<<grid, kThreads, Smem<BN>::kTotal, s>>>(A, lda_i, lda_k, B, ldb_k, ldb_j, C, ldc, M, N, K, k_per_split, bias,
-                                               mode_of(A, lda_i, lda_k, M), mode_of(B, ldb_j, ldb_k, N));
+  kern<<<grid, kThreads, Smem<BN>::kTotal, s>>>(A, lda_i, lda_k, B, ldb_k, ldb_j, C, ldc, M, N, K, k_per_split, bias, epi, split);
   count_launch();
   return B200LAB_OK;
 }
 
-template <int EPI, bool SPLIT>
-static int launch_bn(const float* A, int64_t lda_i, int64_t lda_k, const float* B, int64_t ldb_k, int64_t ldb_j, float* C,
-                     int64_t ldc, int64_t M, int N, int64_t K, int64_t k_per_split, int splits, const float* bias,
-                     cudaStream_t s) {
-  if (N > 64) return launch<128, EPI, SPLIT>(A, lda_i, lda_k, B, ldb_k, ldb_j, C, ldc, M, N, K, k_per_split, splits, bias, s);
-  return launch<64, EPI, SPLIT>(A, lda_i, lda_k, B, ldb_k, ldb_j, C, ldc, M, N, K, k_per_split, splits, bias, s);
+template <int BN, int AMODE>
+static int launch_b(int b_mode, const float* A, int64_t lda_i, int64_t lda_k, const float* B, int64_t ldb_k, int64_t ldb_j,
+                    float* C, int64_t ldc, int64_t M, int N, int64_t K, int64_t k_per_split, int splits, const float* bias,
+                    int epi, int split, cudaStream_t s) {
+#define B200LAB_TC_B(MODE) \
+  case MODE: return launch<BN, AMODE, MODE>(A, lda_i, lda_k, B, ldb_k, ldb_j, C, ldc, M, N, K, k_per_split, splits, bias, epi, split, s)
+  switch (b_mode) {
+    B200LAB_TC_B(kKVec); B200LAB_TC_B(kKScalar); B200LAB_TC_B(kMnVec);
+    default: return launch<BN, AMODE, kMnScalar>(A, lda_i, lda_k, B, ldb_k, ldb_j, C, ldc, M, N, K, k_per_split, splits, bias, epi, split, s);
+  }
+#undef B200LAB_TC_B
+}
+
+template <int BN>
+static int launch_a(int a_mode, int b_mode, const float* A, int64_t lda_i, int64_t lda_k, const float* B, int64_t ldb_k,
+                    int64_t ldb_j, float* C, int64_t ldc, int64_t M, int N, int64_t K, int64_t k_per_split, int splits,
+                    const float* bias, int epi, int split, cudaStream_t s) {
+#define B200LAB_TC_A(MODE) \
+  case MODE: return launch_b<BN, MODE>(b_mode, A, lda_i, lda_k, B, ldb_k, ldb_j, C, ldc, M, N, K, k_per_split, splits, bias, epi, split, s)
+  switch (a_mode) {
+    B200LAB_TC_A(kKVec); B200LAB_TC_A(kKScalar); B200LAB_TC_A(kMnVec);
+    default: return launch_b<BN, kMnScalar>(b_mode, A, lda_i, lda_k, B, ldb_k, ldb_j, C, ldc, M, N, K, k_per_split, splits, bias, epi, split, s);
+  }
+#undef B200LAB_TC_A
 }
 
 }  // namespace tc
@@ -418,14 +458,18 @@ int gemm_tc(const float* A, int64_t lda_i, int64_t lda_k, const float* B, int64_
     set_error("gemm: precision %d unknown (0 fp32 FFMA, 1 tf32, 2 tf32x3)", precision);
     return B200LAB_ERR_UNSUPPORTED;
   }
-  const bool split = precision == 2;
-#define B200LAB_TC_DISPATCH(E)                                                                                          \
-  return split ? tc::launch_bn<E, true>(A, lda_i, lda_k, B, ldb_k, ldb_j, C, ldc, M, N, K, k_per_split, splits, bias, s) \
-               : tc::launch_bn<E, false>(A, lda_i, lda_k, B, ldb_k, ldb_j, C, ldc, M, N, K, k_per_split, splits, bias, s)
-  if (epi == 2) { B200LAB_TC_DISPATCH(2); }
-  if (epi == 1) { B200LAB_TC_DISPATCH(1); }
-  B200LAB_TC_DISPATCH(0);
-#undef B200LAB_TC_DISPATCH
+  // 16-byte copies along whichever dimension is contiguous, when every vector is 16-byte aligned: base pointer, leading
+  // dimension and (K-major) the split boundaries multiples of 4 elements; tile origins are multiples of 64 already
+  auto mode_of = [&](const float* p, int64_t ld_r, int64_t ld_k) -> int {
+    const bool base_ok = (uintptr_t)p % 16 == 0;
+    if (ld_k == 1) return (base_ok && ld_r % 4 == 0 && (splits == 1 || k_per_split % 4 == 0)) ? tc::kKVec : tc::kKScalar;
+    if (ld_r == 1) return (base_ok && ld_k % 4 == 0) ? tc::kMnVec : tc::kMnScalar;
+    return ld_k < ld_r ? tc::kKScalar : tc::kMnScalar;
+  };
+  const int a_mode = mode_of(A, lda_i, lda_k), b_mode = mode_of(B, ldb_j, ldb_k);
+  const int split = precision == 2 ? 1 : 0;
+  if (N > 64) return tc::launch_a<128>(a_mode, b_mode, A, lda_i, lda_k, B, ldb_k, ldb_j, C, ldc, M, N, K, k_per_split, splits, bias, epi, split, s);
+  return tc::launch_a<64>(a_mode, b_mode, A, lda_i, lda_k, B, ldb_k, ldb_j, C, ldc, M, N, K, k_per_split, splits, bias, epi, split, s);
 }
 
 }  // namespace b200lab
