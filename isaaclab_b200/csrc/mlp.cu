@@ -17,8 +17,9 @@ namespace b200lab {
 int gemm_tc(const float* A, int64_t lda_i, int64_t lda_k, const float* B, int64_t ldb_k, int64_t ldb_j, float* C, int64_t ldc,
             int64_t M, int N, int64_t K, int64_t k_per_split, int splits, const float* bias, int epi, int precision,
             cudaStream_t s);
-// layers narrower than this (the 12-wide action head, the 1-wide value head) stay on the FFMA path: a 128 x 64 MMA tile
-// would be > 80 % padding
+// a layer goes to the tensor path when its input OR output is at least this wide: the 12-wide action head and the 1-wide
+// value head ride on zero-filled tiles (masked copies) -- mostly padding, but their cost is the [M,128] activation read,
+// and the FFMA kernel's 64 x 64 tiles were slower on them; layers narrow on both sides (cartpole's 4 -> 32) stay FFMA
 constexpr int kMinTcWidth = 32;
 
 constexpr int BM = 64, BN = 64, BK = 16;
@@ -124,30 +125,54 @@ colsum_partial_kernel(const float* __restrict__ dZ, int64_t M, int N, int64_t ro
 }
 
 // dZ = dY * ELU'(.) AND the per-slab column sums of dZ in one pass over the layer's [M,N] activations (the bias gradient
-// used to re-read dZ in a second kernel).  Same block geometry as colsum_partial_kernel.
+// used to re-read dZ in a second kernel).  A block owns `rows_per_block` rows; warp w takes rows w, w+8, ...; lanes take 4
+// consecutive columns (128-bit loads/stores, 512 B per warp instruction, 8 rows in flight); columns in chunks of 128.
+// VEC = false: scalar columns for N % 4 != 0.
+template <bool VEC>
 __global__ void __launch_bounds__(256)
 elu_bwd_colsum_kernel(const float* __restrict__ Y, const float* __restrict__ dY, float* __restrict__ dZ, int64_t M, int N,
                       int64_t rows_per_block, float* __restrict__ part) {
-  __shared__ float sh[8][33];
-  int cl = threadIdx.x % 32, rl = threadIdx.x / 32;
-  int64_t r0 = (int64_t)blockIdx.x * rows_per_block, r1 = min64(M, r0 + rows_per_block);
-  for (int c0 = 0; c0 < N; c0 += 32) {
-    int c = c0 + cl;
-    float s = 0.0f;
-    if (c < N)
-      for (int64_t r = r0 + rl; r < r1; r += 8) {
-        float y = __ldg(Y + r * N + c);
-        float g = __ldg(dY + r * N + c) * (y > 0.0f ? 1.0f : y + 1.0f);
-        dZ[r * N + c] = g;
-        s += g;
+  constexpr int kCols = VEC ? 128 : 32;
+  __shared__ float sh[8][kCols + 4];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int64_t r0 = (int64_t)blockIdx.x * rows_per_block, r1 = min64(M, r0 + rows_per_block);
+  for (int c0 = 0; c0 < N; c0 += kCols) {
+    if (VEC) {
+      const int c = c0 + lane * 4;
+      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (c < N) {
+#pragma unroll 8
+        for (int64_t r = r0 + warp; r < r1; r += 8) {
+          const float4 y = __ldg(reinterpret_cast<const float4*>(Y + r * N + c));
+          float4 g = __ldg(reinterpret_cast<const float4*>(dY + r * N + c));
+          g.x *= y.x > 0.0f ? 1.0f : y.x + 1.0f;
+          g.y *= y.y > 0.0f ? 1.0f : y.y + 1.0f;
+          g.z *= y.z > 0.0f ? 1.0f : y.z + 1.0f;
+          g.w *= y.w > 0.0f ? 1.0f : y.w + 1.0f;
+          *reinterpret_cast<float4*>(dZ + r * N + c) = g;
+          acc.x += g.x; acc.y += g.y; acc.z += g.z; acc.w += g.w;
+        }
       }
-    sh[rl][cl] = s;
+      sh[warp][lane * 4 + 0] = acc.x; sh[warp][lane * 4 + 1] = acc.y;
+      sh[warp][lane * 4 + 2] = acc.z; sh[warp][lane * 4 + 3] = acc.w;
+    } else {
+      const int c = c0 + lane;
+      float acc = 0.0f;
+      if (c < N)
+        for (int64_t r = r0 + warp; r < r1; r += 8) {
+          const float y = __ldg(Y + r * N + c);
+          const float g = __ldg(dY + r * N + c) * (y > 0.0f ? 1.0f : y + 1.0f);
+          dZ[r * N + c] = g;
+          acc += g;
+        }
+      sh[warp][lane] = acc;
+    }
     __syncthreads();
-    if (rl == 0 && c < N) {
+    if (threadIdx.x < kCols && c0 + (int)threadIdx.x < N) {
       float t = 0.0f;
 #pragma unroll
-      for (int k = 0; k < 8; ++k) t += sh[k][cl];
-      part[(int64_t)blockIdx.x * N + c] = t;
+      for (int k = 0; k < 8; ++k) t += sh[k][threadIdx.x];
+      part[(int64_t)blockIdx.x * N + c0 + threadIdx.x] = t;
     }
     __syncthreads();
   }
@@ -208,7 +233,7 @@ int b200lab_linear_fwd(const float* X, const float* W, const float* b, float* Y,
                        int32_t elu, int32_t precision, void* stream) {
   B200LAB_CHECK_ARG(X && W && b && Y && M > 0 && K > 0 && Nout > 0, "bad argument");
   cudaStream_t s = (cudaStream_t)stream;
-  if (precision != 0 && Nout >= kMinTcWidth && K >= kMinTcWidth) {
+  if (precision != 0 && (Nout >= kMinTcWidth || K >= kMinTcWidth)) {
     int rc = gemm_tc(X, K, 1, W, 1, K, Y, Nout, M, Nout, K, K, 1, b, elu ? 2 : 1, precision, s);
     return rc ? rc : check_launch("linear_fwd (tcgen05)");
   }
@@ -228,14 +253,16 @@ int b200lab_linear_bwd(const float* X, const float* W, const float* Y, const flo
   B200LAB_CHECK_ARG(X && W && dY && dW && db && workspace && M > 0 && K > 0 && Nout > 0, "bad argument");
   B200LAB_CHECK_ARG(!elu || (Y && dZ), "ELU backward needs the saved output Y and the dZ scratch");
   B200LAB_CHECK_ARG(precision >= 0 && precision <= 2, "precision must be 0 (fp32 FFMA), 1 (tf32) or 2 (tf32x3)");
-  const bool use_tc = precision != 0 && Nout >= kMinTcWidth && K >= kMinTcWidth;
+  const bool use_tc = precision != 0 && (Nout >= kMinTcWidth || K >= kMinTcWidth);
   cudaStream_t s = (cudaStream_t)stream;
   const float* dz = dY;
   float* ws = (float*)workspace;
   float* colsum_part = ws + (int64_t)dw_splits(M, K, Nout, use_tc) * Nout * K;
   const int colsum_blocks = (int)ceil_div(M, kColsumRows);
   if (elu) {   // dZ and the bias-gradient partial sums in one pass
-    elu_bwd_colsum_kernel<<<colsum_blocks, 256, 0, s>>>(Y, dY, dZ, M, Nout, kColsumRows, colsum_part);
+    const bool vec = Nout % 4 == 0 && ((uintptr_t)Y | (uintptr_t)dY | (uintptr_t)dZ) % 16 == 0;
+    if (vec) elu_bwd_colsum_kernel<true><<<colsum_blocks, 256, 0, s>>>(Y, dY, dZ, M, Nout, kColsumRows, colsum_part);
+    else     elu_bwd_colsum_kernel<false><<<colsum_blocks, 256, 0, s>>>(Y, dY, dZ, M, Nout, kColsumRows, colsum_part);
     count_launch();
     dz = dZ;
   } else {

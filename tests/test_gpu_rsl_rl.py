@@ -145,7 +145,7 @@ def test_linear_fwd_bwd_vs_torch_fp32(M, K, N):
 
 @pytest.mark.parametrize("precision,tol", [(2, 3e-5), (1, 3e-3)], ids=["tf32x3", "tf32"])
 @pytest.mark.parametrize("M,K,N", [(24576, 512, 256), (24576, 235, 512), (1000, 128, 256), (384, 96, 128), (333, 77, 40),
-                                   (4096, 256, 128)])
+                                   (4096, 256, 128), (24576, 128, 12), (5000, 128, 1), (777, 4, 32), (130, 33, 19)])
 def test_linear_tcgen05_vs_fp64(M, K, N, precision, tol):
     """tcgen05 kind::tf32 GEMM paths (csrc/mlp_tc.cu): forward with fused bias+ELU, dX and split-K dW, against torch fp64.
     3xTF32 (precision 2) must stay at fp32-level accuracy; single TF32 (precision 1) at TF32 level.  Errors are measured
