@@ -400,7 +400,7 @@ def time_ppo_update(dev, reps=3, precision=2, multi_gpu_cfg=None):
     return {"s_per_iter": round(s_iter, 5), "gae_ms": round(gae_ms, 4), "update_ms": round(upd_ms, 3),
             "tflops": round(ppo_flops_per_iter(c) / (upd_ms * 1e-3) / 1e12, 2), "gpu_launches": int(launches),
             "precision": {0: "fp32 FFMA (SIMT)", 1: "tf32 tcgen05 (reduced precision)",
-                          2: "3xTF32 tcgen05 (fp32-accurate split; heads < 32 wide on FFMA)"}[pol.precision],
+                          2: "3xTF32 tcgen05 (fp32-accurate hi/lo split, all layers)"}[pol.precision],
             "config": f"cfg 3: N={c['N']} T={c['T']} obs={c['obs_dim']} act={c['act_dim']} hidden={c['hidden']} "
                       f"{c['epochs']} epochs x {c['mini_batches']} minibatches of {c['N'] * c['T'] // c['mini_batches']}",
             "loss": {k: round(float(v), 6) for k, v in loss.items()}}

@@ -507,6 +507,14 @@ int b200lab_adam_clip_step(float* param, const float* grad, float* exp_avg, floa
                            const float* lr_dev, const float* grad_sumsq, float grad_scale, float max_grad_norm,
                            float beta1, float beta2, float eps, int64_t step, void* stream);
 
+/* EmpiricalNormalization (RSL/networks/normalization.py:14-72).  update: learn the batch x[M,D] into the running
+ * mean / var / std ([D] each); count_new = samples seen INCLUDING this batch (the host owns the counter: M is known
+ * there, and `until` is checked before the call).  apply: out = (x - mean) / (std + eps). */
+int b200lab_empirical_norm_update(const float* x, int64_t M, int32_t D, int64_t count_new, float* mean, float* var,
+                                  float* std, void* stream);
+int b200lab_empirical_norm_apply(const float* x, const float* mean, const float* std, float eps, float* out, int64_t M,
+                                 int32_t D, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

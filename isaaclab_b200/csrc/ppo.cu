@@ -174,6 +174,66 @@ adam_clip_kernel(float* __restrict__ p, const float* __restrict__ g, float* __re
   }
 }
 
+// ---- EmpiricalNormalization (RSL/networks/normalization.py:14-72) ----
+// update: batch mean / biased variance per column (two passes over the [M,D] batch, as torch.var does), then
+//   mean += rate*(mean_x - mean);  var += rate*(var_x - var + delta*(mean_x - mean_new));  std = sqrt(var)
+// with rate = M / count_new.  One CTA per 32 columns: 8 row-lanes x 32 column-lanes, coalesced along the columns.
+__global__ void __launch_bounds__(256)
+empirical_norm_update_kernel(const float* __restrict__ x, int64_t M, int D, float rate, float* __restrict__ mean,
+                             float* __restrict__ var, float* __restrict__ stdv) {
+  __shared__ float sh[8][33];
+  __shared__ float mean_x_s[32];
+  const int cl = threadIdx.x & 31, rl = threadIdx.x >> 5;
+  const int c = blockIdx.x * 32 + cl;
+  float s = 0.0f;
+  if (c < D)
+    for (int64_t r = rl; r < M; r += 8) s += __ldg(x + r * D + c);
+  sh[rl][cl] = s;
+  __syncthreads();
+  if (rl == 0) {
+    float t = 0.0f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) t += sh[k][cl];
+    mean_x_s[cl] = t / (float)M;
+  }
+  __syncthreads();
+  const float mx = mean_x_s[cl];
+  float q = 0.0f;
+  if (c < D)
+    for (int64_t r = rl; r < M; r += 8) {
+      float d = __ldg(x + r * D + c) - mx;
+      q += d * d;
+    }
+  __syncthreads();
+  sh[rl][cl] = q;
+  __syncthreads();
+  if (rl == 0 && c < D) {
+    float t = 0.0f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) t += sh[k][cl];
+    const float var_x = t / (float)M;
+    const float m_old = mean[c];
+    const float delta = mx - m_old;
+    const float m_new = m_old + rate * delta;
+    const float v_new = var[c] + rate * (var_x - var[c] + delta * (mx - m_new));
+    mean[c] = m_new;
+    var[c] = v_new;
+    stdv[c] = sqrtf(v_new);
+  }
+}
+
+// forward: (x - mean) / (std + eps)
+__global__ void __launch_bounds__(256)
+empirical_norm_apply_kernel(const float* __restrict__ x, const float* __restrict__ mean, const float* __restrict__ stdv,
+                            float eps, float* __restrict__ out, int64_t M, int D) {
+  const int64_t total = M * D;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const int c = (int)(i % D);
+    out[i] = (__ldg(x + i) - __ldg(mean + c)) / (__ldg(stdv + c) + eps);
+  }
+}
+
 }  // namespace b200lab
 
 using namespace b200lab;
@@ -226,5 +286,22 @@ int b200lab_adam_clip_step(float* param, const float* grad, float* exp_avg, floa
                                                          grad_scale, max_grad_norm, beta1, beta2, eps, bc1, bc2s);
   count_launch();
   return check_launch("adam_clip_step");
+}
+int b200lab_empirical_norm_update(const float* x, int64_t M, int32_t D, int64_t count_new, float* mean, float* var,
+                                  float* std, void* stream) {
+  B200LAB_CHECK_ARG(x && mean && var && std && M > 0 && D > 0 && count_new >= M, "bad argument");
+  const float rate = (float)((double)M / (double)count_new);
+  empirical_norm_update_kernel<<<(unsigned)ceil_div(D, 32), 256, 0, (cudaStream_t)stream>>>(x, M, D, rate, mean, var, std);
+  count_launch();
+  return check_launch("empirical_norm_update");
+}
+
+int b200lab_empirical_norm_apply(const float* x, const float* mean, const float* std, float eps, float* out, int64_t M,
+                                 int32_t D, void* stream) {
+  B200LAB_CHECK_ARG(x && mean && std && out && M > 0 && D > 0, "bad argument");
+  int nb = (int)min64(ceil_div(M * D, 256), 16 * kNumSMs);
+  empirical_norm_apply_kernel<<<nb, 256, 0, (cudaStream_t)stream>>>(x, mean, std, eps, out, M, D);
+  count_launch();
+  return check_launch("empirical_norm_apply");
 }
 }

@@ -85,6 +85,65 @@ class _Net:
             dy = dx
 
 
+class EmpiricalNormalization(nn.Module):
+    """Running mean / variance normalisation of observations (RSL/networks/normalization.py:14-72): same buffers
+    (`_mean`, `_var`, `_std` of shape [1, D], `count`) so state dicts interchange; `forward` and `update` are one kernel
+    each.  The sample counter is mirrored on the host (the batch size is known there), so neither call synchronises."""
+
+    def __init__(self, shape, eps=1e-2, until=None, device="cuda"):
+        super().__init__()
+        self.eps, self.until = eps, until
+        D = int(shape if isinstance(shape, int) else shape[0])
+        self.register_buffer("_mean", torch.zeros(1, D, device=device))
+        self.register_buffer("_var", torch.ones(1, D, device=device))
+        self.register_buffer("_std", torch.ones(1, D, device=device))
+        self.register_buffer("count", torch.tensor(0, dtype=torch.long, device=device))
+        self._count = 0
+        self._out = {}
+
+    @property
+    def mean(self):
+        return self._mean.squeeze(0).clone()
+
+    @property
+    def std(self):
+        return self._std.squeeze(0).clone()
+
+    def forward(self, x):
+        x = x.contiguous()
+        M, D = x.shape
+        out = self._out.get(M)
+        if out is None:
+            if len(self._out) > 4:
+                self._out.clear()
+            out = self._out[M] = torch.empty(M, D, device=x.device)
+        p = _lib.ptr
+        _lib.check(_lib.lib().b200lab_empirical_norm_apply(p(x), p(self._mean), p(self._std), float(self.eps), p(out),
+                                                          M, D, _lib.current_stream()))
+        return out
+
+    def update(self, x):
+        if not self.training:
+            return
+        if self.until is not None and self._count >= self.until:
+            return
+        x = x.contiguous()
+        M, D = x.shape
+        self._count += M
+        self.count.fill_(self._count)
+        p = _lib.ptr
+        _lib.check(_lib.lib().b200lab_empirical_norm_update(p(x), M, D, self._count, p(self._mean), p(self._var),
+                                                           p(self._std), _lib.current_stream()))
+
+    def inverse(self, y):
+        return y * (self._std + self.eps) + self._mean
+
+    def _load_from_state_dict(self, state_dict, prefix, *args, **kwargs):
+        super()._load_from_state_dict(state_dict, prefix, *args, **kwargs)
+        if prefix + "count" in state_dict:
+            self._count = int(state_dict[prefix + "count"])
+
+
 class ActorCritic(nn.Module):
     is_recurrent = False
 
@@ -98,8 +157,6 @@ class ActorCritic(nn.Module):
             raise ValueError("isaaclab_b200 ActorCritic implements the ELU MLP used by the supported configs")
         if noise_std_type != "scalar":
             raise ValueError("isaaclab_b200 ActorCritic supports noise_std_type='scalar'")
-        if actor_obs_normalization or critic_obs_normalization:
-            raise NotImplementedError("empirical observation normalisation is not on the fused path yet")
         self.obs_groups = obs_groups
         num_actor_obs = sum(obs[g].shape[-1] for g in obs_groups["policy"])
         num_critic_obs = sum(obs[g].shape[-1] for g in obs_groups["critic"])
@@ -109,10 +166,12 @@ class ActorCritic(nn.Module):
             device = next(iter(obs.values())).device if hasattr(obs, "values") else "cuda"
         self.actor = _mlp(num_actor_obs, num_actions, actor_hidden_dims)
         self.critic = _mlp(num_critic_obs, 1, critic_hidden_dims)
-        self.actor_obs_normalization = False
-        self.critic_obs_normalization = False
-        self.actor_obs_normalizer = nn.Identity()
-        self.critic_obs_normalizer = nn.Identity()
+        self.actor_obs_normalization = bool(actor_obs_normalization)
+        self.critic_obs_normalization = bool(critic_obs_normalization)
+        self.actor_obs_normalizer = (EmpiricalNormalization(num_actor_obs, device=device)
+                                     if actor_obs_normalization else nn.Identity())
+        self.critic_obs_normalizer = (EmpiricalNormalization(num_critic_obs, device=device)
+                                      if critic_obs_normalization else nn.Identity())
         self.noise_std_type = noise_std_type
         self.std = nn.Parameter(init_noise_std * torch.ones(num_actions))
         self.num_actions = num_actions
@@ -154,6 +213,7 @@ class ActorCritic(nn.Module):
 
     def load_state_dict(self, state_dict, strict=True):
         own = dict(self.named_parameters())
+        own.update(dict(self.named_buffers()))
         missing = [k for k in own if k not in state_dict]
         unexpected = [k for k in state_dict if k not in own]
         if strict and (missing or unexpected):
@@ -161,6 +221,9 @@ class ActorCritic(nn.Module):
         for k, p in own.items():
             if k in state_dict:
                 p.data.copy_(state_dict[k].to(p.device))
+        for m in (self.actor_obs_normalizer, self.critic_obs_normalizer):
+            if isinstance(m, EmpiricalNormalization):
+                m._count = int(m.count.item())
         return True  # training resumes (RSL/modules/actor_critic.py:166-168)
 
     # -- rsl_rl surface ----------------------------------------------------------------------------
@@ -177,6 +240,15 @@ class ActorCritic(nn.Module):
     def get_critic_obs(self, obs):
         ts = [obs[g] for g in self.obs_groups["critic"]]
         return ts[0] if len(ts) == 1 else torch.cat(ts, dim=-1)
+
+    def actor_input(self, obs):
+        """Actor observation set, normalised when enabled (actor_critic.py:115-117)."""
+        x = self.get_actor_obs(obs).contiguous().float()
+        return self.actor_obs_normalizer(x) if self.actor_obs_normalization else x
+
+    def critic_input(self, obs):
+        x = self.get_critic_obs(obs).contiguous().float()
+        return self.critic_obs_normalizer(x) if self.critic_obs_normalization else x
 
     @property
     def action_mean(self):
@@ -198,7 +270,7 @@ class ActorCritic(nn.Module):
     def act(self, obs, eps=None, **kwargs):
         """Normal(actor(obs), std).sample().  `eps` (standard-normal draws, [M,A]) may be passed explicitly
         (parity mode); otherwise drawn from torch's CUDA generator."""
-        x = self.get_actor_obs(obs)
+        x = self.actor_input(obs)
         self.update_distribution(x)
         M, A = self._mean.shape
         if eps is None:
@@ -212,10 +284,10 @@ class ActorCritic(nn.Module):
         return actions
 
     def act_inference(self, obs):
-        return self._a.forward(self.get_actor_obs(obs).contiguous().float(), self.precision)
+        return self._a.forward(self.actor_input(obs), self.precision)
 
     def evaluate(self, obs, **kwargs):
-        self._value = self._c.forward(self.get_critic_obs(obs).contiguous().float(), self.precision)
+        self._value = self._c.forward(self.critic_input(obs), self.precision)
         return self._value
 
     def get_actions_log_prob(self, actions):
@@ -225,4 +297,7 @@ class ActorCritic(nn.Module):
         return (-((actions - mu) ** 2) / (2 * sigma ** 2) - torch.log(sigma) - 0.5 * math.log(2 * math.pi)).sum(-1)
 
     def update_normalization(self, obs):
-        pass
+        if self.actor_obs_normalization:
+            self.actor_obs_normalizer.update(self.get_actor_obs(obs))
+        if self.critic_obs_normalization:
+            self.critic_obs_normalizer.update(self.get_critic_obs(obs))

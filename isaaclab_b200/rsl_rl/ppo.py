@@ -103,8 +103,8 @@ class PPO:
         for (obs_batch, actions_batch, target_values_batch, advantages_batch, returns_batch, old_lp_batch, old_mu_batch,
              old_sigma_batch, _, _) in self.storage.mini_batch_generator(self.num_mini_batches, self.num_learning_epochs,
                                                                          indices=indices):
-            x = pol.get_actor_obs(obs_batch)
-            xc = pol.get_critic_obs(obs_batch)
+            x = pol.actor_input(obs_batch)
+            xc = pol.critic_input(obs_batch)
             M, A = actions_batch.shape
             mu = pol._a.forward(x, pol.precision)
             value = pol._c.forward(xc, pol.precision)

@@ -162,3 +162,28 @@ def ppo_update(params, storage, indices, cfg, lr, world_size=1):
             sums[k] += float(info[k])
         n_upd += 1
     return {k: v / n_upd for k, v in sums.items()}, lr, lrs, adam
+
+
+class EmpiricalNormalization:
+    """RSL/networks/normalization.py:14-72 restated: running mean / biased variance over all samples seen."""
+
+    def __init__(self, dim, eps=1e-2, until=None):
+        self.eps, self.until = eps, until
+        self.mean, self.var, self.std = torch.zeros(1, dim), torch.ones(1, dim), torch.ones(1, dim)
+        self.count = 0
+
+    def __call__(self, x):
+        return (x - self.mean) / (self.std + self.eps)          # normalization.py:47
+
+    def update(self, x):
+        if self.until is not None and self.count >= self.until:  # normalization.py:55-56
+            return
+        n = x.shape[0]
+        self.count += n
+        rate = n / self.count
+        var_x = torch.var(x, dim=0, unbiased=False, keepdim=True)
+        mean_x = torch.mean(x, dim=0, keepdim=True)
+        delta = mean_x - self.mean
+        self.mean = self.mean + rate * delta                      # normalization.py:64
+        self.var = self.var + rate * (var_x - self.var + delta * (mean_x - self.mean))   # :65 (uses the NEW mean)
+        self.std = torch.sqrt(self.var)

@@ -20,21 +20,26 @@ from rsl_rl.modules import ActorCritic  # noqa: E402
 TensorDict = ref_harness.TensorDict
 
 
-def run(name, N, T, obs_dim, act_dim, hidden, seed, entropy_coef, epochs=2, mini_batches=4, timeouts=True):
+def run(name, N, T, obs_dim, act_dim, hidden, seed, entropy_coef, epochs=2, mini_batches=4, timeouts=True,
+        normalization=False):
     torch.manual_seed(seed)
     torch.set_num_threads(1)
     obs0 = TensorDict({"policy": torch.randn(N, obs_dim)}, batch_size=[N])
     policy = ActorCritic(obs0, {"policy": ["policy"], "critic": ["policy"]}, act_dim, actor_hidden_dims=hidden,
-                         critic_hidden_dims=hidden, activation="elu", init_noise_std=1.0)
+                         critic_hidden_dims=hidden, activation="elu", init_noise_std=1.0,
+                         actor_obs_normalization=normalization, critic_obs_normalization=normalization)
     alg = PPO(policy, num_learning_epochs=epochs, num_mini_batches=mini_batches, clip_param=0.2, gamma=0.99, lam=0.95,
               value_loss_coef=1.0, entropy_coef=entropy_coef, learning_rate=1e-3, max_grad_norm=1.0,
               use_clipped_value_loss=True, schedule="adaptive", desired_kl=0.01, device="cpu")
     alg.init_storage("rl", N, T, obs0, [act_dim])
     out = {"cfg": dict(N=N, T=T, obs_dim=obs_dim, act_dim=act_dim, hidden=list(hidden), entropy_coef=entropy_coef,
                        epochs=epochs, mini_batches=mini_batches, gamma=0.99, lam=0.95, clip_param=0.2,
-                       value_loss_coef=1.0, learning_rate=1e-3, max_grad_norm=1.0, desired_kl=0.01)}
+                       value_loss_coef=1.0, learning_rate=1e-3, max_grad_norm=1.0, desired_kl=0.01,
+                       normalization=normalization)}
     out["state_dict_before"] = {k: v.clone() for k, v in policy.state_dict().items()}
     g = torch.Generator().manual_seed(seed + 1)
+    col_scale = torch.ones(obs_dim) if not normalization else 0.5 + 3.0 * torch.rand(obs_dim, generator=g)
+    col_shift = torch.zeros(obs_dim) if not normalization else 2.0 * torch.randn(obs_dim, generator=g)
     obs = obs0
     step_inputs = []
     for t in range(T):
@@ -43,7 +48,8 @@ def run(name, N, T, obs_dim, act_dim, hidden, seed, entropy_coef, epochs=2, mini
         rewards = torch.randn(N, generator=g) * 0.05
         dones = (torch.rand(N, generator=g) < 0.05).long()
         time_outs = ((torch.rand(N, generator=g) < 0.3) & (dones > 0)) if timeouts else None
-        next_obs = TensorDict({"policy": torch.randn(N, obs_dim, generator=g)}, batch_size=[N])
+        # observations with per-column offset / scale so the empirical normalisation has something to learn
+        next_obs = TensorDict({"policy": torch.randn(N, obs_dim, generator=g) * col_scale + col_shift}, batch_size=[N])
         step_inputs.append(dict(obs=obs["policy"].clone(), actions=actions.clone(), rewards=rewards.clone(),
                                 dones=dones.clone(), time_outs=None if time_outs is None else time_outs.clone(),
                                 values=alg.transition.values.clone(), log_prob=alg.transition.actions_log_prob.clone(),
@@ -101,3 +107,5 @@ if __name__ == "__main__":
     run("small", N=96, T=8, obs_dim=48, act_dim=12, hidden=[64, 64, 64], seed=7, entropy_coef=0.005)
     run("ragged", N=50, T=5, obs_dim=37, act_dim=3, hidden=[32, 16], seed=11, entropy_coef=0.01, epochs=1,
         mini_batches=3, timeouts=False)
+    run("norm", N=64, T=6, obs_dim=20, act_dim=4, hidden=[32, 32], seed=23, entropy_coef=0.005, epochs=2, mini_batches=2,
+        normalization=True)

@@ -19,7 +19,8 @@ def _mk(fx, dev="cuda"):
     c = fx["cfg"]
     obs0 = TensorDict({"policy": torch.zeros(c["N"], c["obs_dim"], device=dev)}, batch_size=[c["N"]])
     pol = ActorCritic(obs0, {"policy": ["policy"], "critic": ["policy"]}, c["act_dim"], actor_hidden_dims=c["hidden"],
-                      critic_hidden_dims=c["hidden"], device=dev)
+                      critic_hidden_dims=c["hidden"], device=dev, actor_obs_normalization=c.get("normalization", False),
+                      critic_obs_normalization=c.get("normalization", False))
     pol.load_state_dict(fx["state_dict_before"])
     alg = PPO(pol, num_learning_epochs=c["epochs"], num_mini_batches=c["mini_batches"], clip_param=c["clip_param"],
               gamma=c["gamma"], lam=c["lam"], value_loss_coef=c["value_loss_coef"], entropy_coef=c["entropy_coef"],
@@ -28,7 +29,7 @@ def _mk(fx, dev="cuda"):
     return pol, alg, TensorDict
 
 
-@pytest.mark.parametrize("name", ["small", "ragged"])
+@pytest.mark.parametrize("name", ["small", "ragged", "norm"])
 def test_rollout_gae_update_vs_reference_fixture(golden_dir, name):
     fx = _load(golden_dir, name)
     c = fx["cfg"]
@@ -43,7 +44,9 @@ def test_rollout_gae_update_vs_reference_fixture(golden_dir, name):
         torch.testing.assert_close(a.cpu(), s["actions"], rtol=1e-5, atol=2e-6)
         torch.testing.assert_close(alg.transition.actions_log_prob.cpu(), s["log_prob"], rtol=1e-5, atol=2e-5)
         extras = {} if s["time_outs"] is None else {"time_outs": s["time_outs"].to(dev)}
-        alg.process_env_step(obs, s["rewards"].to(dev), s["dones"].to(dev), extras)
+        nxt = fx["steps"][t + 1]["obs"] if t + 1 < len(fx["steps"]) else fx["last_obs"]   # what update_normalization learns
+        alg.process_env_step(TensorDict({"policy": nxt.to(dev)}, batch_size=[c["N"]]), s["rewards"].to(dev),
+                             s["dones"].to(dev), extras)
     st = alg.storage
     torch.testing.assert_close(st.rewards.cpu(), fx["storage"]["rewards"], rtol=1e-5, atol=1e-6)
     assert torch.equal(st.dones.cpu(), fx["storage"]["dones"])

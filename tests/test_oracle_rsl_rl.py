@@ -49,3 +49,28 @@ def test_ppo_update_matches_reference(fx):
         assert loss[k] == pytest.approx(fx["loss_dict"][k], rel=1e-5, abs=1e-7)
     for k, s in fx["adam_after"].items():
         torch.testing.assert_close(adam.m[k], s["exp_avg"], rtol=1e-4, atol=1e-7)
+
+
+def test_empirical_normalization_matches_reference(golden_dir):
+    """oracle EmpiricalNormalization against the statistics the reference accumulated over the 'norm' rollout, and its
+    normalised forward against the reference actor's recorded means."""
+    import os
+    fx = torch.load(os.path.join(golden_dir, "rsl_rl_norm.pt"), weights_only=False)
+    c = fx["cfg"]
+    norm = O.EmpiricalNormalization(c["obs_dim"])
+    seen = [s["obs"] for s in fx["steps"][1:]] + [fx["last_obs"]]   # process_env_step learns the NEXT observation
+    for t, s in enumerate(fx["steps"]):
+        # the reference's act(obs_t) normalises with the statistics learnt so far
+        sd = fx["state_dict_before"]
+        x = norm(s["obs"])
+        for i in range(len(c["hidden"]) + 1):
+            x = torch.nn.functional.linear(x, sd[f"actor.{2 * i}.weight"], sd[f"actor.{2 * i}.bias"])
+            if i < len(c["hidden"]):
+                x = torch.nn.functional.elu(x)
+        torch.testing.assert_close(x, s["mu"], rtol=1e-5, atol=1e-6)
+        norm.update(seen[t])
+    after = fx["state_dict_after"]
+    assert norm.count == int(after["actor_obs_normalizer.count"])
+    torch.testing.assert_close(norm.mean, after["actor_obs_normalizer._mean"], rtol=1e-6, atol=1e-7)
+    torch.testing.assert_close(norm.var, after["actor_obs_normalizer._var"], rtol=1e-6, atol=1e-7)
+    torch.testing.assert_close(norm.std, after["actor_obs_normalizer._std"], rtol=1e-6, atol=1e-7)
