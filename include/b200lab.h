@@ -109,7 +109,14 @@ enum B200LabNoiseKind {                        /* LAB/utils/noise/noise_model.py
   B200LAB_NOISE_UNIFORM_ADD = 1,               /* x + u*(hi-lo) + lo */
   B200LAB_NOISE_UNIFORM_SCALE = 2,
   B200LAB_NOISE_UNIFORM_ABS = 3,
-  B200LAB_NOISE_CONSTANT_ADD = 4               /* x + bias (n_lo) */
+  B200LAB_NOISE_CONSTANT_ADD = 4,              /* x + bias (n_lo) */
+  B200LAB_NOISE_CONSTANT_SCALE = 5,            /* x * bias */
+  B200LAB_NOISE_CONSTANT_ABS = 6,              /* bias */
+  /* gaussian_noise (noise_model.py:73-98): z ~ N(0,1); noise_lo = mean, noise_span = std.  In parity mode the
+   * element's u_obs slot carries the recorded N(0,1) draw instead of a uniform. */
+  B200LAB_NOISE_GAUSSIAN_ADD = 7,              /* (x + mean) + std*z */
+  B200LAB_NOISE_GAUSSIAN_SCALE = 8,            /* x * (mean + std*z) */
+  B200LAB_NOISE_GAUSSIAN_ABS = 9               /* mean + std*z */
 };
 
 typedef struct B200LabTerm {

@@ -1295,12 +1295,27 @@ compute_obs_kernel(const Env* __restrict__ e, Sim sim, int64_t step, const uint8
   }
   // noise -> clip -> scale (observation_manager.py:313-318)
   if (e->obs_enable_corruption && tm.noise_kind != B200LAB_NOISE_NONE) {
-    if (tm.noise_kind == B200LAB_NOISE_CONSTANT_ADD) v = v + tm.noise_lo;
-    else {
+    const int kind = tm.noise_kind;
+    if (kind == B200LAB_NOISE_CONSTANT_ADD) v = v + tm.noise_lo;             // noise_model.py:33-38
+    else if (kind == B200LAB_NOISE_CONSTANT_SCALE) v = v * tm.noise_lo;
+    else if (kind == B200LAB_NOISE_CONSTANT_ABS) v = 0.0f + tm.noise_lo;
+    else if (kind <= B200LAB_NOISE_UNIFORM_ABS) {
       float u = e->u_obs ? e->u_obs[(int64_t)n * D + k] : philox_uniform(e->seed, step, 3u, (uint32_t)n, (uint32_t)k);
       float nz = u * tm.noise_span + tm.noise_lo;
-      if (tm.noise_kind == B200LAB_NOISE_UNIFORM_ADD) v = (v + u * tm.noise_span) + tm.noise_lo;  // noise_model.py:64
-      else if (tm.noise_kind == B200LAB_NOISE_UNIFORM_SCALE) v = v * nz;
+      if (kind == B200LAB_NOISE_UNIFORM_ADD) v = (v + u * tm.noise_span) + tm.noise_lo;  // noise_model.py:64
+      else if (kind == B200LAB_NOISE_UNIFORM_SCALE) v = v * nz;
+      else v = nz;
+    } else {
+      float z;
+      if (e->u_obs) z = e->u_obs[(int64_t)n * D + k];   // parity mode: the recorded randn_like draw
+      else {                                            // Box-Muller on two Philox uniforms of this element
+        float u1 = philox_uniform(e->seed, step, 3u, (uint32_t)n, (uint32_t)k);
+        float u2 = philox_uniform(e->seed, step, 4u, (uint32_t)n, (uint32_t)k);
+        z = sqrtf(-2.0f * logf(1.0f - u1)) * cospif(2.0f * u2);
+      }
+      float nz = tm.noise_lo + tm.noise_span * z;
+      if (kind == B200LAB_NOISE_GAUSSIAN_ADD) v = (v + tm.noise_lo) + tm.noise_span * z;   // noise_model.py:91
+      else if (kind == B200LAB_NOISE_GAUSSIAN_SCALE) v = v * nz;
       else v = nz;
     }
   }

@@ -14,7 +14,8 @@ import numpy as np
 
 from .. import terrains as terrain_mod
 from ..assets import ArticulationCfg, synthetic_lstm_net, synthetic_mlp_net, load_lstm_net
-from ..managers import (ConstantNoiseCfg, ManagerTermBaseCfg, ObservationGroupCfg, SceneEntityCfg, UniformNoiseCfg)
+from ..managers import (ConstantNoiseCfg, GaussianNoiseCfg, ManagerTermBaseCfg, ObservationGroupCfg, SceneEntityCfg,
+                        UniformNoiseCfg)
 from ..sensors.ray_caster import grid_pattern
 from ..utils.string import resolve_matching_names, resolve_matching_names_values
 from . import mdp
@@ -244,8 +245,14 @@ def compile_env_cfg(cfg: ManagerBasedRLEnvCfg, num_envs: int | None = None, terr
             raise NotImplementedError(f"observation term '{name}': modifiers / history are not on the fused path")
         f = _fused(t.func, name, ("obs",))
         d = {"name": name, "op": f._b200_op, **f._b200_defaults, **resolve_params(name, t.params)}
+        if t.noise is not None and t.noise.operation not in ("add", "scale", "abs"):
+            raise ValueError(f"Unknown operation in noise: {t.noise.operation}")   # noise_model.py:41,69,97
         if isinstance(t.noise, UniformNoiseCfg):
             d["noise"] = ("uniform", float(t.noise.n_min), float(t.noise.n_max), t.noise.operation)
+        elif isinstance(t.noise, GaussianNoiseCfg):
+            d["noise"] = ("gaussian", float(t.noise.mean), float(t.noise.std), t.noise.operation)
+        elif isinstance(t.noise, ConstantNoiseCfg):
+            d["noise"] = ("constant", float(t.noise.bias), 0.0, t.noise.operation)
         elif t.noise is not None:
             raise NotImplementedError(f"observation term '{name}': {type(t.noise).__name__}")
         d["clip"] = tuple(t.clip) if t.clip is not None else None

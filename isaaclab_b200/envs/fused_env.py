@@ -376,11 +376,12 @@ class FusedEnv:
             dst.noise_kind = C["B200LAB_NOISE_NONE"]
             if nz is not None:
                 kind, lo, hi, mode = nz
-                if kind != "uniform":
-                    raise ValueError("fused observation noise supports UniformNoiseCfg")
-                dst.noise_kind = C[{"add": "B200LAB_NOISE_UNIFORM_ADD", "scale": "B200LAB_NOISE_UNIFORM_SCALE",
-                                    "abs": "B200LAB_NOISE_UNIFORM_ABS"}[mode]]
-                dst.noise_lo, dst.noise_span = float(lo), _f32span_py(lo, hi)
+                if kind not in ("uniform", "gaussian", "constant"):
+                    raise ValueError(f"unknown observation noise kind '{kind}'")
+                dst.noise_kind = C[f"B200LAB_NOISE_{kind.upper()}_{mode.upper()}"]
+                # uniform: (n_min, n_max - n_min); gaussian: (mean, std); constant: (bias, -)
+                dst.noise_lo = float(lo)
+                dst.noise_span = _f32span_py(lo, hi) if kind == "uniform" else float(hi)
             dst.clip_on = 1 if t.get("clip") is not None else 0
             if dst.clip_on:
                 dst.clip_lo, dst.clip_hi = float(t["clip"][0]), float(t["clip"][1])

@@ -54,6 +54,12 @@ class ConstantNoiseCfg(NoiseCfg):
 
 
 @dataclass
+class GaussianNoiseCfg(NoiseCfg):
+    mean: float = 0.0
+    std: float = 1.0
+
+
+@dataclass
 class ObservationTermCfg(ManagerTermBaseCfg):
     modifiers: list | None = None
     noise: NoiseCfg | None = None

@@ -55,6 +55,30 @@ def term_dim(spec, t):
     raise ValueError(op)
 
 
+def apply_noise(x, u, nz):
+    """`nz = (kind, a, b, operation)`; `u` = the element-wise random draw the reference function makes (rand_like for
+    uniform, randn_like for gaussian, unused for constant)."""
+    kind, lo, hi, mode = nz
+    if kind == "uniform":       # noise_model.py:45-70; (lo, hi) = (n_min, n_max)
+        if mode == "add":
+            return x + u * (hi - lo) + lo
+        if mode == "scale":
+            return x * (u * (hi - lo) + lo)
+        return u * (hi - lo) + lo
+    if kind == "gaussian":      # noise_model.py:73-98; (lo, hi) = (mean, std)
+        if mode == "add":
+            return x + lo + hi * u
+        if mode == "scale":
+            return x * (lo + hi * u)
+        return lo + hi * u
+    assert kind == "constant"   # noise_model.py:20-42; lo = bias
+    if mode == "add":
+        return x + lo
+    if mode == "scale":
+        return x * lo
+    return torch.zeros_like(x) + lo
+
+
 class OracleEnv:
     def __init__(self, spec):
         self.spec = s = spec
@@ -632,14 +656,7 @@ class OracleEnv:
             nz = t.get("noise")
             if nz is not None and o.get("enable_corruption", True):
                 u = u_obs[:, col:col + w]
-                kind, lo, hi, mode = nz
-                assert kind == "uniform"
-                if mode == "add":
-                    x = x + u * (hi - lo) + lo
-                elif mode == "scale":
-                    x = x * (u * (hi - lo) + lo)
-                else:
-                    x = u * (hi - lo) + lo
+                x = apply_noise(x, u, nz)
             if t.get("clip") is not None:
                 x = x.clip_(min=t["clip"][0], max=t["clip"][1])
             if t.get("scale") is not None:

@@ -16,6 +16,38 @@ ref_harness.install()
 import isaaclab.utils.math as M  # noqa: E402
 
 
+def noise_vectors(g):
+    """constant / uniform / gaussian noise x add / scale / abs by the reference's noise_model functions
+    (LAB/utils/noise/noise_model.py:20-98) with the rand_like / randn_like draws recorded."""
+    from isaaclab.utils.noise import noise_cfg, noise_model
+    data = torch.randn(64, 5, generator=g) * 2.0
+    draws = {}
+    orig_rand, orig_randn = torch.rand_like, torch.randn_like
+
+    def rand_like(x, **k):
+        draws["u"] = torch.rand(x.shape, generator=g)
+        return draws["u"]
+
+    def randn_like(x, **k):
+        draws["u"] = torch.randn(x.shape, generator=g)
+        return draws["u"]
+
+    cases = []
+    torch.rand_like, torch.randn_like = rand_like, randn_like
+    try:
+        for op in ("add", "scale", "abs"):
+            for kind, cfg, fn, lo, hi in (
+                    ("constant", noise_cfg.ConstantNoiseCfg(bias=0.37, operation=op), noise_model.constant_noise, 0.37, 0.0),
+                    ("uniform", noise_cfg.UniformNoiseCfg(n_min=-0.1, n_max=0.25, operation=op), noise_model.uniform_noise, -0.1, 0.25),
+                    ("gaussian", noise_cfg.GaussianNoiseCfg(mean=0.05, std=0.3, operation=op), noise_model.gaussian_noise, 0.05, 0.3)):
+                draws.clear()
+                y = fn(data.clone(), cfg)
+                cases.append(dict(kind=kind, op=op, lo=lo, hi=hi, draw=draws.get("u", torch.zeros_like(data)).clone(), out=y.clone()))
+    finally:
+        torch.rand_like, torch.randn_like = orig_rand, orig_randn
+    return dict(data=data, cases=cases)
+
+
 def main():
     g = torch.Generator().manual_seed(11)
     n = 257
@@ -42,6 +74,7 @@ def main():
         "normalize": M.normalize(v),
         "reference": "isaaclab.utils.math (IsaacLab 2.1.0), torch CPU fp32",
     }
+    out["noise"] = noise_vectors(g)
     path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "math_utils.pt")
     torch.save(out, path)
     print("wrote", path)

@@ -206,3 +206,38 @@ def test_host_replay_prefetch_matches_device_replay(task):
         for k, (a, b) in enumerate(zip(outs[0], other)):
             for x, y, name in zip(a, b, ("obs", "reward", "terminated", "time_outs")):
                 assert torch.equal(x, y), f"{task} step {k}: {name} differs between device and host replay"
+
+
+def test_observation_noise_kinds_match_oracle():
+    """Every (constant | uniform | gaussian) x (add | scale | abs) noise model on the observation terms, CUDA against the
+    oracle (itself pinned bitwise to the reference noise functions, tests/test_oracle_math.py) on the same draws."""
+    from isaaclab_b200.envs.fused_env import FusedEnv
+    from isaaclab_b200.sim.synthetic import SyntheticSim, generate_slabs
+    task, N = "Isaac-Velocity-Flat-Anymal-C-v0", 128
+    spec = make_spec(task, N)
+    combos = [(k, a, b, op) for op in ("add", "scale", "abs")
+              for k, a, b in (("constant", 0.37, 0.0), ("uniform", -0.1, 0.25), ("gaussian", 0.05, 0.3))]
+    terms = spec["observations"]["terms"]
+    for i, t in enumerate(terms):
+        t["noise"] = combos[i % len(combos)]
+    assert len(terms) >= 7
+    slabs = generate_slabs(spec, 2, seed=3)
+    orc = OracleEnv(copy.deepcopy(spec))
+    fus = FusedEnv(spec, device="cuda")
+    sim = SyntheticSim(spec, K=2, device="cuda", slabs={k: v.clone() for k, v in slabs.items()})
+    g = torch.Generator().manual_seed(8)
+    u_obs = torch.randn(N, fus.obs_dim, generator=g)   # gaussian columns read it as N(0,1), uniform columns as a draw
+    fus.set_uniforms(None, None, u_obs.cuda())
+    got = fus.compute_obs(sim.views(1)[-1]).cpu()
+    want = orc.compute_obs(slab_views_cpu(slabs, 1)[-1], u_obs)
+    close(got, want, "obs with mixed noise models", rtol=1e-5, atol=2e-6)
+    # Philox path: gaussian columns must be standard-normal distributed around the clean value
+    clean = copy.deepcopy(spec)
+    for t in clean["observations"]["terms"]:
+        t["noise"] = None
+    for t in spec["observations"]["terms"]:
+        t["noise"] = ("gaussian", 0.0, 1.0, "add")
+    f_noisy, f_clean = FusedEnv(spec, device="cuda", seed=5), FusedEnv(clean, device="cuda", seed=5)
+    z = (f_noisy.compute_obs(sim.views(1)[-1]) - f_clean.compute_obs(sim.views(1)[-1])).flatten()
+    assert abs(float(z.mean())) < 0.05 and abs(float(z.std()) - 1.0) < 0.05, (float(z.mean()), float(z.std()))
+    assert abs(float((z ** 3).mean())) < 0.15 and abs(float((z ** 4).mean()) - 3.0) < 0.3

@@ -36,3 +36,15 @@ def test_quaternion_helpers_match_reference_bitwise():
     _eq(mu.quat_from_euler_xyz(e[:, 0], e[:, 1], e[:, 2]), FX["quat_from_euler_xyz"], "quat_from_euler_xyz")
     _eq(mu.quat_mul(q, q2), FX["quat_mul"], "quat_mul")
     _eq(mu.normalize(v), FX["normalize"], "normalize")
+
+
+def test_noise_models_match_reference():
+    """oracle.mdp_env.apply_noise against the reference noise_model functions (constant / uniform / gaussian x add / scale /
+    abs) on the recorded draws -- bitwise."""
+    import os
+    from oracle.mdp_env import apply_noise
+    fx = torch.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "math_utils.pt"), weights_only=False)["noise"]
+    assert len(fx["cases"]) == 9
+    for c in fx["cases"]:
+        got = apply_noise(fx["data"].clone(), c["draw"], (c["kind"], c["lo"], c["hi"], c["op"]))
+        assert torch.equal(got, c["out"]), f"{c['kind']}/{c['op']}: max diff {(got - c['out']).abs().max().item()}"
