@@ -374,6 +374,15 @@ int b200lab_process_action(void* env, const float* action_in, void* stream);
 int b200lab_substep_pre(void* env, const B200LabSimView* sim, void* stream);
 int b200lab_substep_post(void* env, const B200LabSimView* sim, void* stream);
 
+/* Speculative height scan.  Replaces nothing in the reference; it re-schedules RayCaster._update_buffers_impl
+ * (LAB/sensors/ray_caster/ray_caster.py:220-260): the sensor pose after the last physics sub-step only changes
+ * afterwards for envs that are reset, so the rays of the height scanner (vertical pattern, attach_yaw_only) can be cast
+ * from `sim` on an internal stream while the caller's stream runs the actuator / contact / termination / reward
+ * kernels.  b200lab_compute_obs joins the scan, uses its hits for every env whose sensor pose (root pose + drift) is
+ * bitwise the pose the scan was cast from, and casts the others (reset envs) in place -- results are identical with
+ * and without the call.  No-op for other sensor configurations.  b200lab_decimation_fused calls it itself. */
+int b200lab_height_scan_prefetch(void* env, const B200LabSimView* sim, void* stream);
+
 /* REPLAY fast path: the whole physics loop of one env step in one launch, when the simulator states of all
  * `num_substeps` (= decimation, <= 8) physics steps are already known (recorded Isaac Sim run or synthetic state):
  * process_action, then for s = 0..S-1 { substep_pre on state s-1 (`prev` for s = 0); substep_post on `views[s]` }.

@@ -94,6 +94,7 @@ _SIGS = {
     "b200lab_substep_pre": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
     "b200lab_substep_post": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
     "b200lab_decimation_fused": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int32, C.c_void_p]),
+    "b200lab_height_scan_prefetch": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
     "b200lab_post_step": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]),
     "b200lab_post_reset_write": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
     "b200lab_step_tail": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]),

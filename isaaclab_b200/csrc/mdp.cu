@@ -22,15 +22,24 @@ namespace b200lab {
 struct EnvHandle {
   B200LabEnvState host;   // passed BY VALUE to the kernels whose descriptor reads are warp-uniform (__grid_constant__,
                           // 12 KB of the 32 KB parameter space): constant-bank operands instead of global round trips
-  B200LabEnvState* dev;   // device copy for compute_obs, whose lanes index the term table divergently (one column each)
+  B200LabEnvState* dev;   // device copy (kept for callers that want the descriptor on the device)
   float* derived;      // [N, kDerived] per-env derived state for compute_obs
   bool rays_vertical;  // all ray directions are (0,0,dz), dz != 0, and the sensor is yaw-only
-  uint8_t* col_term;   // [obs_dim] obs column -> term index
-  int16_t* col_src;    // [obs_dim] obs column -> joint index (joint terms) or index inside the term
+  struct ObsCol* cols; // [obs_dim] per-column program of the observation group (compute_obs_kernel)
+  MeshAccel mesh;      // host copy of the ray-caster mesh descriptor (passed by value to compute_obs)
+  bool has_mesh;
   // host copy of the ActuatorNetLSTM weights when their shape has a constant-bank instantiation (H=8, L=2: the ANYdrive
   // net) -- handed to the kernels as a launch parameter
   cudaStream_t side;       // second stream + fork/join events of b200lab_step_tail
   cudaEvent_t ev_fork, ev_join;
+  // speculative height scan (b200lab_height_scan_prefetch): hit heights [N,R] and the sensor pose [N,8] they were cast
+  // from, produced on a third stream while the decimation / post_step kernels run
+  cudaStream_t side2;
+  cudaEvent_t ev_spec_fork, ev_spec_done;
+  float* spec_z;
+  float* spec_pose;
+  int64_t spec_cap;        // N*R the buffers were sized for
+  bool spec_pending;       // a prefetch has been enqueued and not yet joined
   bool lstm_const;
   const float* lstm_src;   // device pointer the copy was taken from
   float lstm_w[1024];
@@ -592,6 +601,7 @@ decimation_fused_kernel(const __grid_constant__ Env env_param, const float* __re
   }
   // ---- body role: ContactSensor (contact_sensor.py:320-379) under SensorBase.update (sensor_base.py:197-205)
   if (joint_role) return;
+
   if (e->cs_timestamp && i < B) {
     const int64_t ob = (int64_t)n * B + i;
     const int Hh = e->hist;
@@ -930,10 +940,27 @@ __device__ __forceinline__ void resample_command(const Env* e, int n, const floa
 }
 
 constexpr int kStepWarps = 4;
+#ifndef B200LAB_POST_BLOCKS
+#define B200LAB_POST_BLOCKS 6
+#endif
 
-__global__ void __launch_bounds__(kStepWarps * 32, 6)
-post_step_kernel(const __grid_constant__ Env env_param, Sim sim, int64_t step) {
+__global__ void __launch_bounds__(kStepWarps * 32, B200LAB_POST_BLOCKS)
+post_step_kernel(const __grid_constant__ Env env_param, Sim sim, int64_t step, const Env* __restrict__ env_dev) {
   const Env* __restrict__ e = &env_param;   // descriptor in the constant bank: warp-uniform reads, no global round trips
+  // The termination / reward term tables are staged from the device copy of the descriptor into shared memory: read
+  // through the constant bank they push the kernel's constant footprint past ~4 KB, where every launch pays several
+  // microseconds of serialised constant-cache misses (tools/imc_probe.cu).
+  extern __shared__ uint2 s_tab[];   // the tables sit at 8-byte-aligned offsets of the descriptor
+  {
+    const int n8_term = e->num_term * (int)(sizeof(B200LabTerm) / 8), n8_rew = e->num_rew * (int)(sizeof(B200LabTerm) / 8);
+    const uint2* g_term = reinterpret_cast<const uint2*>(env_dev->term);
+    const uint2* g_rew = reinterpret_cast<const uint2*>(env_dev->rew);
+    for (int i = threadIdx.x; i < n8_term; i += blockDim.x) s_tab[i] = __ldg(g_term + i);
+    for (int i = threadIdx.x; i < n8_rew; i += blockDim.x) s_tab[n8_term + i] = __ldg(g_rew + i);
+  }
+  __syncthreads();
+  const B200LabTerm* __restrict__ s_term = reinterpret_cast<const B200LabTerm*>(s_tab);
+  const B200LabTerm* __restrict__ s_rew = s_term + e->num_term;
   if (e->step_counter_dev) step = *e->step_counter_dev;
   const int lane = threadIdx.x & 31;
   const int n = blockIdx.x * kStepWarps + (threadIdx.x >> 5);
@@ -966,8 +993,8 @@ post_step_kernel(const __grid_constant__ Env env_param, Sim sim, int64_t step) {
   // -- terminations (termination_manager.py:151-174)
   bool terminated = false, truncated = false;
   for (int t = 0; t < e->num_term; ++t) {
-    bool v = eval_termination(e, sim, e->term[t], c, ep_len) != 0.f;
-    if (e->term[t].time_out) truncated |= v; else terminated |= v;
+    bool v = eval_termination(e, sim, s_term[t], c, ep_len) != 0.f;
+    if (s_term[t].time_out) truncated |= v; else terminated |= v;
     if (lane == 0) e->term_dones[(int64_t)t * N + n] = v;
   }
   c.terminated = terminated;
@@ -979,7 +1006,7 @@ post_step_kernel(const __grid_constant__ Env env_param, Sim sim, int64_t step) {
     float mine = 0.f;        // lane r keeps term r's value: the per-term buffers are then updated by all lanes at once
     bool mine_on = false;
     for (int r = 0; r < e->num_rew; ++r) {
-      const B200LabTerm& t = e->rew[r];
+      const B200LabTerm& t = s_rew[r];
       if (t.weight == 0.0f) continue;
       float value = eval_reward(e, sim, t, c) * t.weight * dt;
       total += value;          // reward_buf += value, in term order (reward_manager.py:150)
@@ -1200,8 +1227,17 @@ post_step_kernel(const __grid_constant__ Env env_param, Sim sim, int64_t step) {
 //   attach_yaw_only), 16 root z, 17 ray-caster outdated flag
 constexpr int kDerived = 20;
 
+// Per-column program of the concatenated group (48 B, three coalesced 128-bit loads per thread), built at env_create:
+//   a = {op | src << 8 | noise_kind << 24 | clip_on << 30 | scale_on << 31, noise_lo, noise_span, scale}
+//   b = {clip_lo, clip_hi, p[0], EXTERNAL column}
+//   c = {ray local start xyz, ray direction z}   (height-scan columns)
+struct ObsCol { float4 a, b, c; };
+
+constexpr int kSpecPose = 8;   // sensor position (root + drift) xyz, sensor-frame quaternion wxyz, pad
+
 __global__ void __launch_bounds__(128)
-derive_obs_kernel(const __grid_constant__ Env env_param, Sim sim, float* __restrict__ derived) {
+derive_obs_kernel(const __grid_constant__ Env env_param, Sim sim, float* __restrict__ derived,
+                  const float* __restrict__ spec_pose) {
   const Env* __restrict__ e = &env_param;
   int n = blockIdx.x * blockDim.x + threadIdx.x;
   if (n >= e->N) return;
@@ -1215,7 +1251,7 @@ derive_obs_kernel(const __grid_constant__ Env env_param, Sim sim, float* __restr
   o[3] = ab.x; o[4] = ab.y; o[5] = ab.z;
   o[6] = gb.x; o[7] = gb.y; o[8] = gb.z;
   o[16] = rs[2];
-  float rc_out = 0.f;
+  float rc_out = 0.f, spec_ok = 0.f;
   if (e->rc_is_outdated) {
     rc_out = e->rc_is_outdated[n] != 0 ? 1.f : 0.f;
     if (rc_out != 0.f) {
@@ -1228,11 +1264,56 @@ derive_obs_kernel(const __grid_constant__ Env env_param, Sim sim, float* __restr
       e->rc_quat_w[n * 4] = q.w; e->rc_quat_w[n * 4 + 1] = q.x; e->rc_quat_w[n * 4 + 2] = q.y; e->rc_quat_w[n * 4 + 3] = q.z;
       e->rc_timestamp_last_update[n] = e->rc_timestamp[n];   // sensor_base.py:294-296
       e->rc_is_outdated[n] = 0;
+      // the speculative scan is valid for this env iff it was cast from bitwise the same sensor pose
+      if (spec_pose) {
+        const float* sp = spec_pose + (int64_t)n * kSpecPose;
+        bool same = true;
+#pragma unroll
+        for (int k = 0; k < 7; ++k) same = same && __float_as_uint(sp[k]) == __float_as_uint(o[9 + k]);
+        spec_ok = same ? 1.f : 0.f;
+      }
     } else {
       o[11] = e->rc_pos_w[n * 3 + 2];
     }
   }
   o[17] = rc_out;
+  o[18] = spec_ok;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Speculative height scan (vertical rays, yaw-only sensor).  The sensor pose after the last physics sub-step is known
+// before the actuator / contact / termination / reward kernels of the step have run, and only a reset (which rewrites
+// the root pose and the drift) changes it afterwards.  One block per env: thread 0 derives the sensor pose exactly as
+// derive_obs_kernel does and records it; every thread casts its rays and stores the hit height.  compute_obs consumes
+// the heights of the envs whose recorded pose is bitwise the pose it derives itself and casts the others in place.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+height_scan_spec_kernel(const __grid_constant__ Env env_param, Sim sim, const ObsCol* __restrict__ ray_cols,
+                        const __grid_constant__ MeshAccel mesh, float* __restrict__ spec_z, float* __restrict__ spec_pose) {
+  const Env* __restrict__ e = &env_param;
+  __shared__ float s_pose[kSpecPose];
+  const int n = blockIdx.x;
+  if (threadIdx.x == 0) {
+    const float* rs = sim.root_state_w + (int64_t)n * 13;
+    f4 q{rs[3], rs[4], rs[5], rs[6]};
+    float px = rs[0] + e->rc_drift[n * 3], py = rs[1] + e->rc_drift[n * 3 + 1], pz = rs[2] + e->rc_drift[n * 3 + 2];
+    f4 qy = yaw_quat(q);
+    float* sp = spec_pose + (int64_t)n * kSpecPose;
+    s_pose[0] = px; s_pose[1] = py; s_pose[2] = pz; s_pose[3] = qy.w; s_pose[4] = qy.x; s_pose[5] = qy.y; s_pose[6] = qy.z;
+#pragma unroll
+    for (int k = 0; k < 7; ++k) sp[k] = s_pose[k];
+  }
+  __syncthreads();
+  const f4 qy{s_pose[3], s_pose[4], s_pose[5], s_pose[6]};
+  for (int r = threadIdx.x; r < e->R; r += blockDim.x) {
+    const float4 cc = __ldg(&ray_cols[r].c);
+    f3 st = quat_apply(qy, f3{cc.x, cc.y, cc.z});
+    st.x += s_pose[0]; st.y += s_pose[1]; st.z += s_pose[2];
+    float tt; int face;
+    float z = INFINITY;
+    if (raycast_vertical(mesh, st, cc.w, e->rc_max_distance, tt, face)) z = st.z + tt * cc.w;
+    spec_z[(int64_t)n * e->R + r] = z;
+  }
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -1240,87 +1321,102 @@ derive_obs_kernel(const __grid_constant__ Env env_param, Sim sim, float* __restr
 // One thread per (env, obs column), no barriers: the term of a column comes from the per-column table built at
 // env_create, the env-level quantities from the derived scratch.  Height-scan columns cast their ray.
 // ------------------------------------------------------------------------------------------------
+
+#ifndef B200LAB_OBS_BLOCKS
+#define B200LAB_OBS_BLOCKS 4
+#endif
 template <bool kVerticalRays>
-__global__ void __launch_bounds__(256, kVerticalRays ? 4 : 2)
-compute_obs_kernel(const Env* __restrict__ e, Sim sim, int64_t step, const uint8_t* __restrict__ col_term,
-                   const int16_t* __restrict__ col_src, const float* __restrict__ derived) {
-  const int N = e->N, J = e->J, D = e->obs_dim;
-  if (e->step_counter_dev) step = *e->step_counter_dev;
-  int64_t gid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (gid >= (int64_t)N * D) return;
-  const int n = (int)(gid / D), k = (int)(gid % D);
-  const float* o = derived + (int64_t)n * kDerived;
-  const B200LabTerm& tm = e->obs[col_term[k]];
-  const int li = col_src[k];
+__global__ void __launch_bounds__(256, kVerticalRays ? B200LAB_OBS_BLOCKS : 2)
+compute_obs_kernel(const __grid_constant__ Env env_param, Sim sim, int64_t step, const ObsCol* __restrict__ cols,
+                   const float* __restrict__ derived, const __grid_constant__ MeshAccel mesh, int has_mesh,
+                   const float* __restrict__ spec_z) {
+  const Env* __restrict__ e = &env_param;
+  const unsigned N = (unsigned)e->N, D = (unsigned)e->obs_dim;
+  const unsigned gid = blockIdx.x * blockDim.x + threadIdx.x;   // host guarantees N * D < 2^31
+  if (gid >= N * D) return;
+  const unsigned n = gid / D, k = gid - n * D;
+  const float* o = derived + (size_t)n * kDerived;
+  const ObsCol* col = cols + k;
+  const float4 ca = __ldg(&col->a), cb = __ldg(&col->b);
+  const unsigned w0 = __float_as_uint(ca.x);
+  const int op = w0 & 0xffu, li = (w0 >> 8) & 0xffffu, kind = (w0 >> 24) & 0x3fu;
   float v = 0.f;
-  switch (tm.op) {
+  switch (op) {
     case B200LAB_OBS_BASE_LIN_VEL: v = o[li]; break;
     case B200LAB_OBS_BASE_ANG_VEL: v = o[3 + li]; break;
     case B200LAB_OBS_PROJECTED_GRAVITY: v = o[6 + li]; break;
-    case B200LAB_OBS_GENERATED_COMMANDS: v = e->cmd_vel_b[(int64_t)n * 3 + li]; break;
-    case B200LAB_OBS_JOINT_POS_REL: v = sim.joint_pos[(int64_t)n * J + li] - e->default_joint_pos[li]; break;
-    case B200LAB_OBS_JOINT_VEL_REL: v = sim.joint_vel[(int64_t)n * J + li] - e->default_joint_vel[li]; break;
-    case B200LAB_OBS_JOINT_POS: v = sim.joint_pos[(int64_t)n * J + li]; break;
-    case B200LAB_OBS_JOINT_VEL: v = sim.joint_vel[(int64_t)n * J + li]; break;
-    case B200LAB_OBS_LAST_ACTION: v = e->action[(int64_t)n * e->A + li]; break;
+    case B200LAB_OBS_GENERATED_COMMANDS: v = e->cmd_vel_b[n * 3 + li]; break;
+    case B200LAB_OBS_JOINT_POS_REL: v = sim.joint_pos[(size_t)n * e->J + li] - e->default_joint_pos[li]; break;
+    case B200LAB_OBS_JOINT_VEL_REL: v = sim.joint_vel[(size_t)n * e->J + li] - e->default_joint_vel[li]; break;
+    case B200LAB_OBS_JOINT_POS: v = sim.joint_pos[(size_t)n * e->J + li]; break;
+    case B200LAB_OBS_JOINT_VEL: v = sim.joint_vel[(size_t)n * e->J + li]; break;
+    case B200LAB_OBS_LAST_ACTION: v = e->action[(size_t)n * e->A + li]; break;
     case B200LAB_OBS_BASE_POS_Z: v = o[16]; break;
-    case B200LAB_OBS_EXTERNAL: v = e->ext_values[((int64_t)tm.i0 + li) * N + n]; break;
+    case B200LAB_OBS_EXTERNAL: v = e->ext_values[((size_t)__float_as_int(cb.w) + li) * N + n]; break;
     case B200LAB_OBS_HEIGHT_SCAN: {
       float pz = o[11], hz;
+      float* hp = e->rc_ray_hits_w + ((size_t)n * e->R + li) * 3;
       if (o[17] != 0.f) {
         // ray start = quat_apply(_yaw)(q, local start) + pos ; directions unrotated when attach_yaw_only (ray_caster.py:243-253)
+        const float4 cc = __ldg(&col->c);
         f4 qy{o[12], o[13], o[14], o[15]};
-        f3 ls{__ldg(e->rc_ray_starts + li * 3), __ldg(e->rc_ray_starts + li * 3 + 1), __ldg(e->rc_ray_starts + li * 3 + 2)};
-        f3 ld{__ldg(e->rc_ray_dirs + li * 3), __ldg(e->rc_ray_dirs + li * 3 + 1), __ldg(e->rc_ray_dirs + li * 3 + 2)};
-        f3 st = quat_apply(qy, ls);
-        f3 dr = e->rc_attach_yaw_only ? ld : quat_apply(qy, ld);
+        f3 st = quat_apply(qy, f3{cc.x, cc.y, cc.z});
         st.x += o[9]; st.y += o[10]; st.z += o[11];
         float tt; int face;
         f3 hit{INFINITY, INFINITY, INFINITY};
-        const MeshAccel* mesh = reinterpret_cast<const MeshAccel*>(e->rc_mesh);
         // kVerticalRays: every pattern direction is (0, 0, dz) and the sensor is yaw-only (the height scanner) ->
         // single-cell query, no DDA code in the kernel (fewer registers, higher occupancy)
-        bool ok = mesh && (kVerticalRays ? raycast_vertical(*mesh, st, dr.z, e->rc_max_distance, tt, face)
-                                         : raycast_mesh_dev(*mesh, st, dr, e->rc_max_distance, tt, face));
-        if (ok) hit = {st.x + tt * dr.x, st.y + tt * dr.y, st.z + tt * dr.z};
-        float* hp = e->rc_ray_hits_w + ((int64_t)n * e->R + li) * 3;
+        if (kVerticalRays) {
+          if (o[18] != 0.f) {   // speculative scan cast from this very pose (height_scan_spec_kernel)
+            float z = spec_z[(size_t)n * e->R + li];
+            if (z != INFINITY) hit = {st.x, st.y, z};
+          } else if (has_mesh && raycast_vertical(mesh, st, cc.w, e->rc_max_distance, tt, face)) {
+            hit = {st.x, st.y, st.z + tt * cc.w};
+          }
+        } else {
+          f3 ld{__ldg(e->rc_ray_dirs + li * 3), __ldg(e->rc_ray_dirs + li * 3 + 1), __ldg(e->rc_ray_dirs + li * 3 + 2)};
+          f3 dr = e->rc_attach_yaw_only ? ld : quat_apply(qy, ld);
+          if (has_mesh && raycast_mesh_dev(mesh, st, dr, e->rc_max_distance, tt, face))
+            hit = {st.x + tt * dr.x, st.y + tt * dr.y, st.z + tt * dr.z};
+        }
         hp[0] = hit.x; hp[1] = hit.y; hp[2] = hit.z;
         hz = hit.z;
       } else {
-        hz = e->rc_ray_hits_w[((int64_t)n * e->R + li) * 3 + 2];
+        hz = hp[2];
       }
-      v = (pz - hz) - tm.p[0];  // observations.py:173
+      v = (pz - hz) - cb.z;  // observations.py:173
       break;
     }
   }
   // noise -> clip -> scale (observation_manager.py:313-318)
-  if (e->obs_enable_corruption && tm.noise_kind != B200LAB_NOISE_NONE) {
-    const int kind = tm.noise_kind;
-    if (kind == B200LAB_NOISE_CONSTANT_ADD) v = v + tm.noise_lo;             // noise_model.py:33-38
-    else if (kind == B200LAB_NOISE_CONSTANT_SCALE) v = v * tm.noise_lo;
-    else if (kind == B200LAB_NOISE_CONSTANT_ABS) v = 0.0f + tm.noise_lo;
+  if (kind != B200LAB_NOISE_NONE) {
+    const float noise_lo = ca.y, noise_span = ca.z;
+    if (e->step_counter_dev) step = *e->step_counter_dev;
+    if (kind == B200LAB_NOISE_CONSTANT_ADD) v = v + noise_lo;             // noise_model.py:33-38
+    else if (kind == B200LAB_NOISE_CONSTANT_SCALE) v = v * noise_lo;
+    else if (kind == B200LAB_NOISE_CONSTANT_ABS) v = 0.0f + noise_lo;
     else if (kind <= B200LAB_NOISE_UNIFORM_ABS) {
-      float u = e->u_obs ? e->u_obs[(int64_t)n * D + k] : philox_uniform(e->seed, step, 3u, (uint32_t)n, (uint32_t)k);
-      float nz = u * tm.noise_span + tm.noise_lo;
-      if (kind == B200LAB_NOISE_UNIFORM_ADD) v = (v + u * tm.noise_span) + tm.noise_lo;  // noise_model.py:64
+      float u = e->u_obs ? e->u_obs[gid] : philox_uniform(e->seed, step, 3u, n, k);
+      float nz = u * noise_span + noise_lo;
+      if (kind == B200LAB_NOISE_UNIFORM_ADD) v = (v + u * noise_span) + noise_lo;  // noise_model.py:64
       else if (kind == B200LAB_NOISE_UNIFORM_SCALE) v = v * nz;
       else v = nz;
     } else {
       float z;
-      if (e->u_obs) z = e->u_obs[(int64_t)n * D + k];   // parity mode: the recorded randn_like draw
-      else {                                            // Box-Muller on two Philox uniforms of this element
-        float u1 = philox_uniform(e->seed, step, 3u, (uint32_t)n, (uint32_t)k);
-        float u2 = philox_uniform(e->seed, step, 4u, (uint32_t)n, (uint32_t)k);
+      if (e->u_obs) z = e->u_obs[gid];   // parity mode: the recorded randn_like draw
+      else {                             // Box-Muller on two Philox uniforms of this element
+        float u1 = philox_uniform(e->seed, step, 3u, n, k);
+        float u2 = philox_uniform(e->seed, step, 4u, n, k);
         z = sqrtf(-2.0f * logf(1.0f - u1)) * cospif(2.0f * u2);
       }
-      float nz = tm.noise_lo + tm.noise_span * z;
-      if (kind == B200LAB_NOISE_GAUSSIAN_ADD) v = (v + tm.noise_lo) + tm.noise_span * z;   // noise_model.py:91
+      float nz = noise_lo + noise_span * z;
+      if (kind == B200LAB_NOISE_GAUSSIAN_ADD) v = (v + noise_lo) + noise_span * z;   // noise_model.py:91
       else if (kind == B200LAB_NOISE_GAUSSIAN_SCALE) v = v * nz;
       else v = nz;
     }
   }
-  if (tm.clip_on) v = fminf(fmaxf(v, tm.clip_lo), tm.clip_hi);
-  if (tm.scale_on) v = v * tm.scale;
+  if (w0 & (1u << 30)) v = fminf(fmaxf(v, cb.x), cb.y);
+  if (w0 & (1u << 31)) v = v * ca.w;
   e->obs_buf[gid] = v;
 }
 
@@ -1335,46 +1431,82 @@ static int launch_geometry(int width, int* wpad, int* epb) {
 
 using namespace b200lab;
 
-// obs column -> (term, source index) tables, rebuilt whenever the descriptor changes
+// per-column observation program, rebuilt whenever the descriptor changes
 static int upload_obs_tables(EnvHandle* h) {
   const B200LabEnvState& s = h->host;
   h->rays_vertical = false;
-  if (s.R > 0 && s.rc_ray_dirs && s.rc_attach_yaw_only) {
-    std::vector<float> dirs((size_t)s.R * 3);
-    if (cudaMemcpy(dirs.data(), s.rc_ray_dirs, dirs.size() * sizeof(float), cudaMemcpyDeviceToHost) == cudaSuccess) {
+  h->has_mesh = false;
+  std::vector<float> starts, dirs;
+  if (s.R > 0 && s.rc_ray_dirs && s.rc_ray_starts) {
+    starts.resize((size_t)s.R * 3);
+    dirs.resize((size_t)s.R * 3);
+    cudaError_t err = cudaMemcpy(dirs.data(), s.rc_ray_dirs, dirs.size() * sizeof(float), cudaMemcpyDeviceToHost);
+    if (err == cudaSuccess) err = cudaMemcpy(starts.data(), s.rc_ray_starts, starts.size() * sizeof(float), cudaMemcpyDeviceToHost);
+    if (err != cudaSuccess) { set_error("ray pattern: %s", cudaGetErrorString(err)); return B200LAB_ERR_CUDA; }
+    if (s.rc_attach_yaw_only) {
       bool ok = true;
       for (int r = 0; r < s.R; ++r) ok = ok && dirs[3 * r] == 0.f && dirs[3 * r + 1] == 0.f && dirs[3 * r + 2] != 0.f;
       h->rays_vertical = ok;
     }
   }
+  if (s.rc_mesh) {
+    cudaError_t err = cudaMemcpy(&h->mesh, s.rc_mesh, sizeof(MeshAccel), cudaMemcpyDeviceToHost);
+    if (err != cudaSuccess) { set_error("ray-caster mesh descriptor: %s", cudaGetErrorString(err)); return B200LAB_ERR_CUDA; }
+    h->has_mesh = true;
+  }
+  // speculative-scan buffers; any descriptor change invalidates the recorded poses (NaN never compares equal to a pose)
+  if (h->side2) cudaStreamSynchronize(h->side2);
+  h->spec_pending = false;
+  const int64_t need = h->rays_vertical && h->has_mesh ? (int64_t)s.N * s.R : 0;
+  if (need > h->spec_cap) {
+    if (h->spec_z) cudaFree(h->spec_z);
+    if (h->spec_pose) cudaFree(h->spec_pose);
+    h->spec_z = h->spec_pose = nullptr;
+    h->spec_cap = 0;
+    cudaError_t err = cudaMalloc((void**)&h->spec_z, (size_t)need * sizeof(float));
+    if (err == cudaSuccess) err = cudaMalloc((void**)&h->spec_pose, (size_t)s.N * kSpecPose * sizeof(float));
+    if (err != cudaSuccess) { set_error("speculative scan buffers: %s", cudaGetErrorString(err)); return B200LAB_ERR_CUDA; }
+    h->spec_cap = need;
+  }
+  if (h->spec_pose) cudaMemset(h->spec_pose, 0xFF, (size_t)s.N * kSpecPose * sizeof(float));
   int D = s.obs_dim;
   if (D <= 0) return B200LAB_OK;
-  std::vector<uint8_t> ct(D);
-  std::vector<int16_t> cs(D);
+  if ((int64_t)s.N * D >= (int64_t)1 << 31) { set_error("N * obs_dim must be < 2^31"); return B200LAB_ERR_ARG; }
+  std::vector<ObsCol> cols((size_t)D);
+  auto as_f = [](uint32_t u) { float f; memcpy(&f, &u, 4); return f; };
   int k = 0;
   for (int t = 0; t < s.num_obs; ++t) {
     const B200LabTerm& tm = s.obs[t];
     bool joint = tm.op == B200LAB_OBS_JOINT_POS_REL || tm.op == B200LAB_OBS_JOINT_VEL_REL ||
                  tm.op == B200LAB_OBS_JOINT_POS || tm.op == B200LAB_OBS_JOINT_VEL;
+    if (tm.op < 0 || tm.op > 255 || tm.noise_kind < 0 || tm.noise_kind > 63) { set_error("observation term %d: bad op / noise kind", t); return B200LAB_ERR_ARG; }
     uint64_t m = tm.joint_mask;
     for (int li = 0; li < tm.dim; ++li) {
       if (k >= D) { set_error("observation term dims exceed obs_dim"); return B200LAB_ERR_ARG; }
-      ct[k] = (uint8_t)t;
+      int src = li;
       if (joint) {
         if (!m) { set_error("observation term %d: dim exceeds the number of selected joints", t); return B200LAB_ERR_ARG; }
-        int j = __builtin_ctzll(m);
+        src = __builtin_ctzll(m);
         m &= m - 1;
-        cs[k] = (int16_t)j;
-      } else cs[k] = (int16_t)li;
+      }
+      if (src > 0xffff) { set_error("observation term %d: more than 65535 columns", t); return B200LAB_ERR_ARG; }
+      uint32_t kind = s.obs_enable_corruption ? (uint32_t)tm.noise_kind : (uint32_t)B200LAB_NOISE_NONE;
+      uint32_t w0 = (uint32_t)tm.op | ((uint32_t)src << 8) | (kind << 24) | (tm.clip_on ? 1u << 30 : 0u) | (tm.scale_on ? 1u << 31 : 0u);
+      ObsCol& c = cols[k];
+      c.a = make_float4(as_f(w0), tm.noise_lo, tm.noise_span, tm.scale);
+      c.b = make_float4(tm.clip_lo, tm.clip_hi, tm.p[0], as_f((uint32_t)tm.i0));
+      c.c = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (tm.op == B200LAB_OBS_HEIGHT_SCAN) {
+        if (li >= s.R || starts.empty()) { set_error("height_scan term wider than the ray pattern"); return B200LAB_ERR_ARG; }
+        c.c = make_float4(starts[3 * li], starts[3 * li + 1], starts[3 * li + 2], dirs[3 * li + 2]);
+      }
       ++k;
     }
   }
   if (k != D) { set_error("observation term dims (%d) do not add up to obs_dim (%d)", k, D); return B200LAB_ERR_ARG; }
-  if (h->col_term) { cudaFree(h->col_term); cudaFree(h->col_src); h->col_term = nullptr; h->col_src = nullptr; }
-  cudaError_t err = cudaMalloc((void**)&h->col_term, D);
-  if (err == cudaSuccess) err = cudaMalloc((void**)&h->col_src, D * sizeof(int16_t));
-  if (err == cudaSuccess) err = cudaMemcpy(h->col_term, ct.data(), D, cudaMemcpyHostToDevice);
-  if (err == cudaSuccess) err = cudaMemcpy(h->col_src, cs.data(), D * sizeof(int16_t), cudaMemcpyHostToDevice);
+  if (h->cols) { cudaFree(h->cols); h->cols = nullptr; }
+  cudaError_t err = cudaMalloc((void**)&h->cols, (size_t)D * sizeof(ObsCol));
+  if (err == cudaSuccess) err = cudaMemcpy(h->cols, cols.data(), (size_t)D * sizeof(ObsCol), cudaMemcpyHostToDevice);
   if (err != cudaSuccess) { set_error("obs tables: %s", cudaGetErrorString(err)); return B200LAB_ERR_CUDA; }
   return B200LAB_OK;
 }
@@ -1418,8 +1550,13 @@ void* b200lab_env_create(const B200LabEnvState* st) {
   EnvHandle* h = (EnvHandle*)malloc(sizeof(EnvHandle));
   if (!h) return nullptr;
   h->host = *st;
-  h->col_term = nullptr;
-  h->col_src = nullptr;
+  h->cols = nullptr;
+  h->has_mesh = false;
+  h->side2 = nullptr;
+  h->ev_spec_fork = h->ev_spec_done = nullptr;
+  h->spec_z = h->spec_pose = nullptr;
+  h->spec_cap = 0;
+  h->spec_pending = false;
   h->derived = nullptr;
   h->lstm_const = false;
   h->lstm_src = nullptr;
@@ -1430,6 +1567,9 @@ void* b200lab_env_create(const B200LabEnvState* st) {
   if (err == cudaSuccess) err = cudaStreamCreateWithFlags(&h->side, cudaStreamNonBlocking);
   if (err == cudaSuccess) err = cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming);
   if (err == cudaSuccess) err = cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming);
+  if (err == cudaSuccess) err = cudaStreamCreateWithFlags(&h->side2, cudaStreamNonBlocking);
+  if (err == cudaSuccess) err = cudaEventCreateWithFlags(&h->ev_spec_fork, cudaEventDisableTiming);
+  if (err == cudaSuccess) err = cudaEventCreateWithFlags(&h->ev_spec_done, cudaEventDisableTiming);
   if (err == cudaSuccess) err = cudaMalloc((void**)&h->dev, sizeof(B200LabEnvState));
   if (err == cudaSuccess) err = cudaMemcpy(h->dev, st, sizeof(B200LabEnvState), cudaMemcpyHostToDevice);
   if (err == cudaSuccess && upload_obs_tables(h) != 0) err = cudaErrorUnknown;
@@ -1462,8 +1602,12 @@ void b200lab_env_destroy(void* env) {
   if (h->side) cudaStreamDestroy(h->side);
   if (h->ev_fork) cudaEventDestroy(h->ev_fork);
   if (h->ev_join) cudaEventDestroy(h->ev_join);
-  if (h->col_term) cudaFree(h->col_term);
-  if (h->col_src) cudaFree(h->col_src);
+  if (h->cols) cudaFree(h->cols);
+  if (h->side2) { cudaStreamSynchronize(h->side2); cudaStreamDestroy(h->side2); }
+  if (h->ev_spec_fork) cudaEventDestroy(h->ev_spec_fork);
+  if (h->ev_spec_done) cudaEventDestroy(h->ev_spec_done);
+  if (h->spec_z) cudaFree(h->spec_z);
+  if (h->spec_pose) cudaFree(h->spec_pose);
   if (h->derived) cudaFree(h->derived);
   free(h);
 }
@@ -1543,6 +1687,36 @@ int b200lab_substep_post(void* env, const B200LabSimView* sim, void* stream) {
   return check_launch("substep_post");
 }
 
+int b200lab_height_scan_prefetch(void* env, const B200LabSimView* sim, void* stream) {
+  B200LAB_CHECK_ARG(env && sim && sim->root_state_w, "null argument");
+  EnvHandle* h = (EnvHandle*)env;
+  const B200LabEnvState& s = h->host;
+  // only the height-scanner configuration (vertical pattern, yaw-only attachment) is speculated; otherwise a no-op
+  if (!h->rays_vertical || !h->has_mesh || !h->spec_z || s.R <= 0 || !s.rc_drift) return B200LAB_OK;
+  cudaStream_t st_ = (cudaStream_t)stream;
+  cudaError_t err = cudaEventRecord(h->ev_spec_fork, st_);
+  if (err == cudaSuccess) err = cudaStreamWaitEvent(h->side2, h->ev_spec_fork, 0);
+  if (err != cudaSuccess) { set_error("b200lab_height_scan_prefetch: %s", cudaGetErrorString(err)); return B200LAB_ERR_CUDA; }
+  int threads = ((s.R + 31) / 32) * 32;
+  if (threads > 256) threads = 256;
+  // the ray columns of the observation program carry the local ray starts; a sensor that is not observed has none
+  const ObsCol* ray_cols = nullptr;
+  int k = 0;
+  for (int t = 0; t < s.num_obs && !ray_cols; ++t) {
+    if (s.obs[t].op == B200LAB_OBS_HEIGHT_SCAN && s.obs[t].dim == s.R) ray_cols = h->cols + k;
+    k += s.obs[t].dim;
+  }
+  if (!ray_cols) return B200LAB_OK;
+  height_scan_spec_kernel<<<(unsigned)s.N, threads, 0, h->side2>>>(h->host, *sim, ray_cols, h->mesh, h->spec_z, h->spec_pose);
+  count_launch();
+  int rc = check_launch("height_scan_prefetch");
+  if (rc) return rc;
+  err = cudaEventRecord(h->ev_spec_done, h->side2);
+  if (err != cudaSuccess) { set_error("b200lab_height_scan_prefetch: %s", cudaGetErrorString(err)); return B200LAB_ERR_CUDA; }
+  h->spec_pending = true;
+  return B200LAB_OK;
+}
+
 int b200lab_decimation_fused(void* env, const float* action_in, const B200LabSimView* prev,
                              const B200LabSimView* views, int32_t num_substeps, void* stream) {
   B200LAB_CHECK_ARG(env && action_in && prev && views, "null argument");
@@ -1560,6 +1734,12 @@ int b200lab_decimation_fused(void* env, const float* action_in, const B200LabSim
     sv.v[k] = views[k];
   }
   for (int k = num_substeps; k < kMaxDecimation; ++k) sv.v[k] = views[num_substeps - 1];
+  // replayed state: the post-physics pose of the step is already known -> start the height scan now, next to the
+  // actuator / contact kernels (joined by b200lab_compute_obs)
+  if (views[num_substeps - 1].root_state_w) {
+    rc = b200lab_height_scan_prefetch(env, &views[num_substeps - 1], stream);
+    if (rc) return rc;
+  }
   int W, epb;
   B200LAB_CHECK_ARG(s.B <= kFusedBlock, "B must be <= 128");
   W = s.B > 0 ? s.B : 1;
@@ -1582,7 +1762,9 @@ int b200lab_post_step(void* env, const B200LabSimView* sim, int64_t step_counter
   EnvHandle* h = (EnvHandle*)env;
   const B200LabEnvState& s = h->host;
   B200LAB_CHECK_ARG(s.J <= 64 && s.B <= 64, "joint/body masks support up to 64 joints/bodies");
-  post_step_kernel<<<(unsigned)ceil_div(s.N, kStepWarps), kStepWarps * 32, 0, (cudaStream_t)stream>>>(h->host, *sim, step_counter);
+  const size_t tab_bytes = (size_t)(s.num_term + s.num_rew) * sizeof(B200LabTerm);
+  post_step_kernel<<<(unsigned)ceil_div(s.N, kStepWarps), kStepWarps * 32, tab_bytes, (cudaStream_t)stream>>>(
+      h->host, *sim, step_counter, h->dev);
   count_launch();
   return check_launch("post_step");
 }
@@ -1592,15 +1774,22 @@ int b200lab_compute_obs(void* env, const B200LabSimView* sim, int64_t step_count
   EnvHandle* h = (EnvHandle*)env;
   const B200LabEnvState& s = h->host;
   cudaStream_t st_ = (cudaStream_t)stream;
-  derive_obs_kernel<<<(unsigned)ceil_div(s.N, 128), 128, 0, st_>>>(h->host, *sim, h->derived);
+  if (h->spec_pending) {   // join the speculative scan
+    cudaError_t err = cudaStreamWaitEvent(st_, h->ev_spec_done, 0);
+    if (err != cudaSuccess) { set_error("b200lab_compute_obs: %s", cudaGetErrorString(err)); return B200LAB_ERR_CUDA; }
+    h->spec_pending = false;
+  }
+  derive_obs_kernel<<<(unsigned)ceil_div(s.N, 128), 128, 0, st_>>>(h->host, *sim, h->derived,
+                                                                   h->rays_vertical && h->has_mesh ? h->spec_pose : nullptr);
   count_launch();
   int64_t total = (int64_t)s.N * s.obs_dim;
+  if (total <= 0) return check_launch("compute_obs");
   if (h->rays_vertical)
-    compute_obs_kernel<true><<<(unsigned)ceil_div(total, 256), 256, 0, st_>>>(h->dev, *sim, step_counter, h->col_term,
-                                                                              h->col_src, h->derived);
+    compute_obs_kernel<true><<<(unsigned)ceil_div(total, 256), 256, 0, st_>>>(h->host, *sim, step_counter, h->cols,
+                                                                              h->derived, h->mesh, h->has_mesh ? 1 : 0, h->spec_z);
   else
-    compute_obs_kernel<false><<<(unsigned)ceil_div(total, 256), 256, 0, st_>>>(h->dev, *sim, step_counter, h->col_term,
-                                                                               h->col_src, h->derived);
+    compute_obs_kernel<false><<<(unsigned)ceil_div(total, 256), 256, 0, st_>>>(h->host, *sim, step_counter, h->cols,
+                                                                               h->derived, h->mesh, h->has_mesh ? 1 : 0, h->spec_z);
   count_launch();
   return check_launch("compute_obs");
 }

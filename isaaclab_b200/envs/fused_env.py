@@ -438,6 +438,11 @@ class FusedEnv:
     def substep_post(self, sim: SimView):
         _lib.check(self.L.b200lab_substep_post(self.handle, sim.ref, _lib.current_stream()))
 
+    def height_scan_prefetch(self, sim: SimView):
+        """Live-simulator path: start the height scan from the post-physics state `sim` on the library's side stream; the
+        next `compute_obs` joins it (b200lab_height_scan_prefetch).  `decimation_fused` does this itself."""
+        _lib.check(self.L.b200lab_height_scan_prefetch(self.handle, sim.ref, _lib.current_stream()))
+
     def post_step(self, sim: SimView):
         _lib.check(self.L.b200lab_post_step(self.handle, sim.ref, self.step_counter, _lib.current_stream()))
 
@@ -483,6 +488,7 @@ class FusedEnv:
                 self.substep_pre(prev)
                 self.substep_post(sim)
                 prev = sim
+            self.height_scan_prefetch(prev)
         self.post_step(prev)
         if fused:
             self.step_tail(prev)
