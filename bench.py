@@ -264,15 +264,16 @@ def run_ours(args):
     # ---- end-to-end arm: public API with HOST buffers (pinned), H2D of each step's simulator state + action and
     # D2H of obs / reward / dones inside the timed region
     host_sim = HostReplaySim(spec, slabs, device=dev)
-    env = ManagerBasedRLEnv(cfg, sim=host_sim, device=dev, spec=spec, seed=rank)
+    env = ManagerBasedRLEnv(cfg, sim=host_sim, device=dev, spec=spec, seed=rank, use_cuda_graph=True)
     init_fused_state(env.fused, init)
     act_host = torch.randn(N, spec["A"], generator=g).pin_memory()
+    env.result_chunks = 4
     res_host = torch.empty(env.fused.result.numel(), dtype=torch.uint8).pin_memory()
 
     def e2e_step():
-        env.step(act_host)
-        env.read_results(res_host)   # obs, reward, terminated, time-outs, reset mask: one D2H copy
-        torch.cuda.current_stream().synchronize()  # the caller consumes the result before the next step
+        # obs, reward, terminated, time-outs, reset mask stream into the pinned slab behind the kernels that produce them
+        env.step(act_host, results_out=res_host)
+        env.wait_results()  # the caller consumes the result before the next step
 
     for _ in range(args.warmup):
         e2e_step()
@@ -297,9 +298,11 @@ def run_ours(args):
            "warmup": args.warmup, "ms_per_step": round(ms / args.steps, 5), "higher_is_better": True, "scaling": "weak",
            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
            "config": {"workload": workload_name(spec), "envs_per_gpu": N,
-                      "e2e_mode": "ManagerBasedRLEnv.step with pinned host buffers; results (obs, reward, dones) read "
-                                  "back and synchronised every step; next step's simulator state prefetched H2D on a "
-                                  "copy stream while the current step computes", "l2_policy": f"{K_SLABS} state slabs "
+                      "e2e_mode": "ManagerBasedRLEnv.step(action, results_out) with pinned host buffers, the step captured "
+                                  "as a CUDA graph per staging set (H2D action, kernels, D2H of reward/masks after "
+                                  "post_step and of the obs rows range by range behind the obs kernels); results "
+                                  "synchronised every step; next step's simulator state prefetched H2D on a copy "
+                                  "stream while the current step computes", "l2_policy": f"{K_SLABS} state slabs "
                                   f"({sim.bytes() >> 20} MiB > 126 MiB L2) cycled", "parallelism": f"env-shard x{world}"},
            "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roof}
     del env, host_sim, fus, sim

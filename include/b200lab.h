@@ -380,7 +380,8 @@ int b200lab_substep_post(void* env, const B200LabSimView* sim, void* stream);
  * from `sim` on an internal stream while the caller's stream runs the actuator / contact / termination / reward
  * kernels.  b200lab_compute_obs joins the scan, uses its hits for every env whose sensor pose (root pose + drift) is
  * bitwise the pose the scan was cast from, and casts the others (reset envs) in place -- results are identical with
- * and without the call.  No-op for other sensor configurations.  b200lab_decimation_fused calls it itself. */
+ * and without the call.  No-op for other sensor configurations.  Opt-in: on B200 at 4096 envs the step kernels already
+ * fill the register file, so the overlap only re-distributes time (measurement). */
 int b200lab_height_scan_prefetch(void* env, const B200LabSimView* sim, void* stream);
 
 /* REPLAY fast path: the whole physics loop of one env step in one launch, when the simulator states of all
@@ -413,6 +414,16 @@ int b200lab_compute_obs(void* env, const B200LabSimView* sim, int64_t step_count
  * and joined back into `stream` (both are latency-bound and touch disjoint buffers), everything `stream` enqueues
  * afterwards sees both results.  Same results as the two calls in sequence. */
 int b200lab_step_tail(void* env, const B200LabSimView* sim, int64_t step_counter, void* stream);
+
+/* The same work split so that the caller can pipeline its own consumers behind the observation kernels: `_begin` forks
+ * the conditional post-reset actuator pass onto the library's side stream, `b200lab_compute_obs_range` computes the
+ * observation rows of envs [env_begin, env_end) (any partition of [0, N) gives the rows b200lab_compute_obs gives),
+ * `_end` joins the side stream.  bench.py's end-to-end arm copies each finished range to the host while the next one
+ * is computed. */
+int b200lab_step_tail_begin(void* env, const B200LabSimView* sim, void* stream);
+int b200lab_compute_obs_range(void* env, const B200LabSimView* sim, int64_t step_counter, int32_t env_begin,
+                              int32_t env_end, void* stream);
+int b200lab_step_tail_end(void* env, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * Ray casting.  Replaces convert_to_warp_mesh (LAB/utils/warp/ops.py:130-145) and raycast_mesh

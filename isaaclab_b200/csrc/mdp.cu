@@ -42,7 +42,7 @@ struct EnvHandle {
   bool spec_pending;       // a prefetch has been enqueued and not yet joined
   bool lstm_const;
   const float* lstm_src;   // device pointer the copy was taken from
-  float lstm_w[1024];
+  float lstm_w[1024];   // packed NetLstm<8,2> image (see NetLstm)
 };
 
 typedef B200LabEnvState Env;
@@ -173,15 +173,32 @@ __device__ __forceinline__ float lstm_forward(const float* __restrict__ w, int L
 // itself and no load instruction is issued.  All indices below are compile-time after unrolling (H, L template params).
 struct NetNone { static constexpr bool kLstm = false; };
 
+// Packed layout for the two-wide FMA (fma.rn.f32x2 -> FFMA2, one FMA-pipe slot for two IEEE fp32 FMAs; the cell is
+// FMA-pipe bound).  Two gate rows of the same hidden unit share their input vector, so the rows are paired --
+// (input, forget) and (cell, output) -- and their weights interleaved: per layer l, per unit u, per pair:
+//   {bias_a, bias_b} with bias = b_ih + b_hh (summed in fp32 on the host: the same IEEE add the kernel did), then
+//   in_l x {w_ih[a][k], w_ih[b][k]}, then H x {w_hh[a][k], w_hh[b][k]}.
+// Every half of an FFMA2 is the scalar fmaf of the unpacked code, in the same order: results are bitwise unchanged.
 template <int H, int L>
 struct NetLstm {
   static constexpr bool kLstm = true;
   static constexpr int kH = H, kL = L;
-  static constexpr int layer_off(int l) { return l == 0 ? 0 : (4 * H * 2 + 4 * H * H + 8 * H) + (l - 1) * (8 * H * H + 8 * H); }
-  static constexpr int kHead = layer_off(L);
-  static constexpr int kCount = kHead + H + 1;
-  float w[kCount];
+  static constexpr int kRawCount = (4 * H * 2 + 4 * H * H + 8 * H) + (L - 1) * (8 * H * H + 8 * H) + H + 1;
+  static constexpr int in_dim(int l) { return l == 0 ? 2 : H; }
+  static constexpr int pair_len(int l) { return 1 + in_dim(l) + H; }                 // float2 per (unit, pair)
+  static constexpr int layer_off(int l) { return l == 0 ? 0 : 2 * H * pair_len(0) + (l - 1) * 2 * H * pair_len(1); }
+  static constexpr int kPairs = layer_off(L);
+  float2 w2[kPairs];
+  float head[H + 1];
 };
+
+__device__ __forceinline__ uint64_t pack2(float a, float b) { uint64_t r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b)); return r; }
+__device__ __forceinline__ void unpack2(uint64_t v, float& a, float& b) { asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v)); }
+__device__ __forceinline__ uint64_t fma2(uint64_t a, uint64_t b, uint64_t c) {
+  uint64_t d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
 
 template <class Net>
 __device__ __forceinline__ float lstm_cells_const(const Net& net, float x0, float x1, float (&h)[Net::kL][Net::kH],
@@ -192,27 +209,21 @@ __device__ __forceinline__ float lstm_cells_const(const Net& net, float x0, floa
   xin[1] = x1;
 #pragma unroll
   for (int l = 0; l < L; ++l) {
-    constexpr int kIn0 = 2;
-    const int in_dim = l == 0 ? kIn0 : H;
-    const int o_ih = Net::layer_off(l), o_hh = o_ih + 4 * H * in_dim, o_bi = o_hh + 4 * H * H, o_bh = o_bi + 4 * H;
+    const int in_dim = Net::in_dim(l), plen = Net::pair_len(l);
     float hn[H];
 #pragma unroll
     for (int u = 0; u < H; ++u) {
       float g4[4];
 #pragma unroll
-      for (int g = 0; g < 4; ++g) {
-        const int r = g * H + u;
-        float acc = net.w[o_bi + r] + net.w[o_bh + r];
-        if (l == 0) {
-          acc = fmaf(net.w[o_ih + r * 2], xin[0], acc);
-          acc = fmaf(net.w[o_ih + r * 2 + 1], xin[1], acc);
-        } else {
+      for (int pr = 0; pr < 2; ++pr) {
+        const int o = Net::layer_off(l) + (u * 2 + pr) * plen;
+        uint64_t acc = pack2(net.w2[o].x, net.w2[o].y);
 #pragma unroll
-          for (int k = 0; k < H; ++k) acc = fmaf(net.w[o_ih + r * H + k], xin[k], acc);
-        }
+        for (int k = 0; k < in_dim; ++k) acc = fma2(pack2(net.w2[o + 1 + k].x, net.w2[o + 1 + k].y), pack2(xin[k], xin[k]), acc);
 #pragma unroll
-        for (int k = 0; k < H; ++k) acc = fmaf(net.w[o_hh + r * H + k], h[l][k], acc);
-        g4[g] = acc;
+        for (int k = 0; k < H; ++k)
+          acc = fma2(pack2(net.w2[o + 1 + in_dim + k].x, net.w2[o + 1 + in_dim + k].y), pack2(h[l][k], h[l][k]), acc);
+        unpack2(acc, g4[2 * pr], g4[2 * pr + 1]);
       }
       float ig = sigmoidf_(g4[0]), fg = sigmoidf_(g4[1]), gg = tanhf_(g4[2]), og = sigmoidf_(g4[3]);
       float cn = fmaf(fg, c[l][u], ig * gg);
@@ -222,9 +233,9 @@ __device__ __forceinline__ float lstm_cells_const(const Net& net, float x0, floa
 #pragma unroll
     for (int k = 0; k < H; ++k) { h[l][k] = hn[k]; xin[k] = hn[k]; }
   }
-  float out = net.w[Net::kHead + H];
+  float out = net.head[H];
 #pragma unroll
-  for (int k = 0; k < H; ++k) out = fmaf(net.w[Net::kHead + k], xin[k], out);
+  for (int k = 0; k < H; ++k) out = fmaf(net.head[k], xin[k], out);
   return out;
 }
 
@@ -1237,10 +1248,10 @@ constexpr int kSpecPose = 8;   // sensor position (root + drift) xyz, sensor-fra
 
 __global__ void __launch_bounds__(128)
 derive_obs_kernel(const __grid_constant__ Env env_param, Sim sim, float* __restrict__ derived,
-                  const float* __restrict__ spec_pose) {
+                  const float* __restrict__ spec_pose, int env_begin, int env_end) {
   const Env* __restrict__ e = &env_param;
-  int n = blockIdx.x * blockDim.x + threadIdx.x;
-  if (n >= e->N) return;
+  int n = env_begin + blockIdx.x * blockDim.x + threadIdx.x;
+  if (n >= env_end) return;
   const float* rs = sim.root_state_w + (int64_t)n * 13;
   float* o = derived + (int64_t)n * kDerived;
   f4 q{rs[3], rs[4], rs[5], rs[6]};
@@ -1329,12 +1340,13 @@ template <bool kVerticalRays>
 __global__ void __launch_bounds__(256, kVerticalRays ? B200LAB_OBS_BLOCKS : 2)
 compute_obs_kernel(const __grid_constant__ Env env_param, Sim sim, int64_t step, const ObsCol* __restrict__ cols,
                    const float* __restrict__ derived, const __grid_constant__ MeshAccel mesh, int has_mesh,
-                   const float* __restrict__ spec_z) {
+                   const float* __restrict__ spec_z, unsigned env_begin, unsigned env_count) {
   const Env* __restrict__ e = &env_param;
   const unsigned N = (unsigned)e->N, D = (unsigned)e->obs_dim;
-  const unsigned gid = blockIdx.x * blockDim.x + threadIdx.x;   // host guarantees N * D < 2^31
-  if (gid >= N * D) return;
-  const unsigned n = gid / D, k = gid - n * D;
+  const unsigned lid = blockIdx.x * blockDim.x + threadIdx.x;   // host guarantees N * D < 2^31
+  if (lid >= env_count * D) return;
+  const unsigned n = env_begin + lid / D, k = lid - (lid / D) * D;
+  const unsigned gid = n * D + k;
   const float* o = derived + (size_t)n * kDerived;
   const ObsCol* col = cols + k;
   const float4 ca = __ldg(&col->a), cb = __ldg(&col->b);
@@ -1512,7 +1524,7 @@ static int upload_obs_tables(EnvHandle* h) {
 }
 
 typedef NetLstm<8, 2> NetLstm82;
-static_assert(NetLstm82::kCount <= 1024, "EnvHandle::lstm_w too small");
+static_assert(sizeof(NetLstm82) <= 1024 * sizeof(float), "EnvHandle::lstm_w too small");
 
 static int stage_const_net(EnvHandle* h) {
   const B200LabEnvState& s = h->host;
@@ -1525,8 +1537,33 @@ static int stage_const_net(EnvHandle* h) {
     return B200LAB_OK;
   }
   if (h->lstm_const && h->lstm_src == net->net_weights) return B200LAB_OK;
-  cudaError_t err = cudaMemcpy(h->lstm_w, net->net_weights, NetLstm82::kCount * sizeof(float), cudaMemcpyDeviceToHost);
+  // raw layout (b200lab.h): per layer W_ih[4H,in] W_hh[4H,H] b_ih[4H] b_hh[4H]; then head W[H] b[1] -> packed image
+  std::vector<float> raw(NetLstm82::kRawCount);
+  cudaError_t err = cudaMemcpy(raw.data(), net->net_weights, raw.size() * sizeof(float), cudaMemcpyDeviceToHost);
   if (err != cudaSuccess) { set_error("actuator net weights: %s", cudaGetErrorString(err)); return B200LAB_ERR_CUDA; }
+  {
+    constexpr int H = NetLstm82::kH, L = NetLstm82::kL;
+    NetLstm82* pk = reinterpret_cast<NetLstm82*>(h->lstm_w);
+    const float* w = raw.data();
+    for (int l = 0; l < L; ++l) {
+      const int in = NetLstm82::in_dim(l), plen = NetLstm82::pair_len(l);
+      const float* w_ih = w;
+      const float* w_hh = w_ih + 4 * H * in;
+      const float* b_ih = w_hh + 4 * H * H;
+      const float* b_hh = b_ih + 4 * H;
+      w = b_hh + 4 * H;
+      for (int u = 0; u < H; ++u)
+        for (int pr = 0; pr < 2; ++pr) {
+          const int ra = (2 * pr) * H + u, rb = (2 * pr + 1) * H + u;   // gate order i, f, g, o (torch.nn.LSTM)
+          float2* o = pk->w2 + NetLstm82::layer_off(l) + (u * 2 + pr) * plen;
+          volatile float ba = b_ih[ra] + b_hh[ra], bb = b_ih[rb] + b_hh[rb];   // fp32 adds, as the kernel performed them
+          o[0] = make_float2(ba, bb);
+          for (int k = 0; k < in; ++k) o[1 + k] = make_float2(w_ih[ra * in + k], w_ih[rb * in + k]);
+          for (int k = 0; k < H; ++k) o[1 + in + k] = make_float2(w_hh[ra * H + k], w_hh[rb * H + k]);
+        }
+    }
+    for (int k = 0; k <= H; ++k) pk->head[k] = w[k];
+  }
   h->lstm_const = true;
   h->lstm_src = net->net_weights;
   return B200LAB_OK;
@@ -1734,12 +1771,6 @@ int b200lab_decimation_fused(void* env, const float* action_in, const B200LabSim
     sv.v[k] = views[k];
   }
   for (int k = num_substeps; k < kMaxDecimation; ++k) sv.v[k] = views[num_substeps - 1];
-  // replayed state: the post-physics pose of the step is already known -> start the height scan now, next to the
-  // actuator / contact kernels (joined by b200lab_compute_obs)
-  if (views[num_substeps - 1].root_state_w) {
-    rc = b200lab_height_scan_prefetch(env, &views[num_substeps - 1], stream);
-    if (rc) return rc;
-  }
   int W, epb;
   B200LAB_CHECK_ARG(s.B <= kFusedBlock, "B must be <= 128");
   W = s.B > 0 ? s.B : 1;
@@ -1769,32 +1800,42 @@ int b200lab_post_step(void* env, const B200LabSimView* sim, int64_t step_counter
   return check_launch("post_step");
 }
 
-int b200lab_compute_obs(void* env, const B200LabSimView* sim, int64_t step_counter, void* stream) {
+int b200lab_compute_obs_range(void* env, const B200LabSimView* sim, int64_t step_counter, int32_t env_begin,
+                              int32_t env_end, void* stream) {
   B200LAB_CHECK_ARG(env && sim && sim->root_state_w, "null argument");
   EnvHandle* h = (EnvHandle*)env;
   const B200LabEnvState& s = h->host;
+  B200LAB_CHECK_ARG(env_begin >= 0 && env_begin <= env_end && env_end <= s.N, "env range out of bounds");
   cudaStream_t st_ = (cudaStream_t)stream;
   if (h->spec_pending) {   // join the speculative scan
     cudaError_t err = cudaStreamWaitEvent(st_, h->ev_spec_done, 0);
     if (err != cudaSuccess) { set_error("b200lab_compute_obs: %s", cudaGetErrorString(err)); return B200LAB_ERR_CUDA; }
     h->spec_pending = false;
   }
-  derive_obs_kernel<<<(unsigned)ceil_div(s.N, 128), 128, 0, st_>>>(h->host, *sim, h->derived,
-                                                                   h->rays_vertical && h->has_mesh ? h->spec_pose : nullptr);
+  const int cnt = env_end - env_begin;
+  if (cnt == 0) return B200LAB_OK;
+  derive_obs_kernel<<<(unsigned)ceil_div(cnt, 128), 128, 0, st_>>>(h->host, *sim, h->derived,
+                                                                 h->rays_vertical && h->has_mesh ? h->spec_pose : nullptr,
+                                                                 env_begin, env_end);
   count_launch();
-  int64_t total = (int64_t)s.N * s.obs_dim;
+  int64_t total = (int64_t)cnt * s.obs_dim;
   if (total <= 0) return check_launch("compute_obs");
   if (h->rays_vertical)
-    compute_obs_kernel<true><<<(unsigned)ceil_div(total, 256), 256, 0, st_>>>(h->host, *sim, step_counter, h->cols,
-                                                                              h->derived, h->mesh, h->has_mesh ? 1 : 0, h->spec_z);
+    compute_obs_kernel<true><<<(unsigned)ceil_div(total, 256), 256, 0, st_>>>(
+        h->host, *sim, step_counter, h->cols, h->derived, h->mesh, h->has_mesh ? 1 : 0, h->spec_z, (unsigned)env_begin, (unsigned)cnt);
   else
-    compute_obs_kernel<false><<<(unsigned)ceil_div(total, 256), 256, 0, st_>>>(h->host, *sim, step_counter, h->cols,
-                                                                               h->derived, h->mesh, h->has_mesh ? 1 : 0, h->spec_z);
+    compute_obs_kernel<false><<<(unsigned)ceil_div(total, 256), 256, 0, st_>>>(
+        h->host, *sim, step_counter, h->cols, h->derived, h->mesh, h->has_mesh ? 1 : 0, h->spec_z, (unsigned)env_begin, (unsigned)cnt);
   count_launch();
   return check_launch("compute_obs");
 }
 
-int b200lab_step_tail(void* env, const B200LabSimView* sim, int64_t step_counter, void* stream) {
+int b200lab_compute_obs(void* env, const B200LabSimView* sim, int64_t step_counter, void* stream) {
+  B200LAB_CHECK_ARG(env, "null argument");
+  return b200lab_compute_obs_range(env, sim, step_counter, 0, ((EnvHandle*)env)->host.N, stream);
+}
+
+int b200lab_step_tail_begin(void* env, const B200LabSimView* sim, void* stream) {
   B200LAB_CHECK_ARG(env && sim && sim->root_state_w && sim->joint_pos && sim->joint_vel, "null argument");
   EnvHandle* h = (EnvHandle*)env;
   cudaStream_t st_ = (cudaStream_t)stream;
@@ -1805,11 +1846,24 @@ int b200lab_step_tail(void* env, const B200LabSimView* sim, int64_t step_counter
   if (err != cudaSuccess) { set_error("b200lab_step_tail: %s", cudaGetErrorString(err)); return B200LAB_ERR_CUDA; }
   int rc = b200lab_post_reset_write(env, sim, h->side);
   if (rc) return rc;
-  rc = b200lab_compute_obs(env, sim, step_counter, stream);
-  if (rc) return rc;
   err = cudaEventRecord(h->ev_join, h->side);
-  if (err == cudaSuccess) err = cudaStreamWaitEvent(st_, h->ev_join, 0);
   if (err != cudaSuccess) { set_error("b200lab_step_tail: %s", cudaGetErrorString(err)); return B200LAB_ERR_CUDA; }
   return B200LAB_OK;
+}
+
+int b200lab_step_tail_end(void* env, void* stream) {
+  B200LAB_CHECK_ARG(env, "null argument");
+  EnvHandle* h = (EnvHandle*)env;
+  cudaError_t err = cudaStreamWaitEvent((cudaStream_t)stream, h->ev_join, 0);
+  if (err != cudaSuccess) { set_error("b200lab_step_tail: %s", cudaGetErrorString(err)); return B200LAB_ERR_CUDA; }
+  return B200LAB_OK;
+}
+
+int b200lab_step_tail(void* env, const B200LabSimView* sim, int64_t step_counter, void* stream) {
+  int rc = b200lab_step_tail_begin(env, sim, stream);
+  if (rc) return rc;
+  rc = b200lab_compute_obs(env, sim, step_counter, stream);
+  if (rc) return rc;
+  return b200lab_step_tail_end(env, stream);
 }
 }

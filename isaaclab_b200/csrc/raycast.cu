@@ -4,7 +4,6 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdlib>
-#include <thread>
 #include <vector>
 
 #include "raycast.cuh"
@@ -16,7 +15,7 @@ struct MeshHandle {
   MeshAccel* dev;      // device copy of the descriptor
   int64_t bytes;
   int64_t entries;
-  void* buffers[5];
+  void* buffers[4];
 };
 
 __global__ void __launch_bounds__(256)
@@ -105,7 +104,6 @@ void* b200lab_mesh_create(const float* V, int64_t nv, const int32_t* F, int64_t 
   // the 0.37-cell shift keeps lattice-aligned triangle edges off the cell borders
   m.ox = xmin - pad - 0.37f * cell_size; m.oy = ymin - pad - 0.37f * cell_size;
   m.cell = cell_size; m.inv_cell = 1.0f / cell_size;
-  m.inv_sub = 8.0f * m.inv_cell;   // exact scaling: floor(t * inv_sub) >> 3 == floor(t * inv_cell)
   m.nx = (int)std::floor((xmax + pad - m.ox) / cell_size) + 1;
   m.ny = (int)std::floor((ymax + pad - m.oy) / cell_size) + 1;
   m.num_faces = (int)nf; m.zmin = zmin; m.zmax = zmax;
@@ -159,68 +157,13 @@ void* b200lab_mesh_create(const float* V, int64_t nv, const int32_t* F, int64_t 
     for (int cy = cy0[f]; cy <= cy1[f]; ++cy)
       for (int cx = cx0[f]; cx <= cx1[f]; ++cx)
         if (overlaps(f, cx, cy)) cell_tris[cursor[(int64_t)cy * m.nx + cx]++] = (int)f;
-  // vertical-ray entries: 8x8 sub-cell coverage mask per (cell, triangle).  A sub-cell box (grown by the same margin as
-  // the cells) misses the triangle iff it lies outside the triangle's XY bounding box or entirely outside one edge; for
-  // an edge, "entirely outside" is decided at the box corner farthest along the edge's inward normal.
-  std::vector<uint32_t> ent((size_t)std::max<int64_t>(entries, 1) * 4, 0u);
-  {
-    const double sub = (double)cell_size / 8.0;
-    auto cell_masks = [&](int64_t c0, int64_t c1) {
-      for (int64_t c = c0; c < c1; ++c) {
-        const int cy = (int)(c / m.nx), cx = (int)(c % m.nx);
-        const double bx = (double)m.ox + (double)cx * cell_size, by = (double)m.oy + (double)cy * cell_size;
-        for (int k = counts[c]; k < counts[c + 1]; ++k) {
-          const int f = cell_tris[k];
-          const float* t = &tris[(size_t)f * 9];
-          const double px[3] = {t[0], t[3], t[6]}, py[3] = {t[1], t[4], t[7]};
-          uint64_t mask = 0;
-          const double area2 = (px[1] - px[0]) * (py[2] - py[0]) - (px[2] - px[0]) * (py[1] - py[0]);
-          if (rec[(size_t)f * 12 + 3] != 0.0f && std::fabs(area2) >= 1e-14) {
-            const double tx0 = std::min(px[0], std::min(px[1], px[2])), tx1 = std::max(px[0], std::max(px[1], px[2]));
-            const double ty0 = std::min(py[0], std::min(py[1], py[2])), ty1 = std::max(py[0], std::max(py[1], py[2]));
-            double ea[3], eb[3], ec[3];   // inside <=> ea*x + eb*y + ec >= 0 for the three edges
-            for (int q = 0; q < 3; ++q) {
-              const int q2 = (q + 1) % 3, q3 = (q + 2) % 3;
-              double nx_ = -(py[q2] - py[q]), ny_ = (px[q2] - px[q]);
-              const double side = nx_ * (px[q3] - px[q]) + ny_ * (py[q3] - py[q]);
-              if (side < 0) { nx_ = -nx_; ny_ = -ny_; }
-              ea[q] = nx_; eb[q] = ny_;
-              ec[q] = -(nx_ * px[q] + ny_ * py[q]) + 1e-9 * (std::fabs(nx_) + std::fabs(ny_));
-            }
-            for (int sy = 0; sy < 8; ++sy) {
-              const double y0 = by + sy * sub - eps, y1 = by + (sy + 1) * sub + eps;
-              if (y1 < ty0 || y0 > ty1) continue;
-              for (int sx = 0; sx < 8; ++sx) {
-                const double x0 = bx + sx * sub - eps, x1 = bx + (sx + 1) * sub + eps;
-                if (x1 < tx0 || x0 > tx1) continue;
-                bool out = false;
-                for (int q = 0; q < 3 && !out; ++q)
-                  out = ea[q] * (ea[q] > 0 ? x1 : x0) + eb[q] * (eb[q] > 0 ? y1 : y0) + ec[q] < 0;
-                if (!out) mask |= 1ull << (sy * 8 + sx);
-              }
-            }
-          }
-          uint32_t* en = &ent[(size_t)k * 4];
-          en[0] = (uint32_t)f; en[1] = 0u; en[2] = (uint32_t)mask; en[3] = (uint32_t)(mask >> 32);
-        }
-      }
-    };
-    unsigned nt = std::max(1u, std::min(32u, std::thread::hardware_concurrency()));
-    std::vector<std::thread> pool;
-    const int64_t chunk = (ncell + nt - 1) / nt;
-    for (unsigned w = 0; w < nt; ++w) {
-      const int64_t c0 = (int64_t)w * chunk, c1 = std::min<int64_t>(ncell, c0 + chunk);
-      if (c0 < c1) pool.emplace_back(cell_masks, c0, c1);
-    }
-    for (auto& th : pool) th.join();
-  }
   // upload
   MeshHandle* h = (MeshHandle*)calloc(1, sizeof(MeshHandle));
-  size_t sz[5] = {(size_t)(ncell + 1) * sizeof(int), cell_tris.size() * sizeof(int), rec.size() * sizeof(float),
-                  tris.size() * sizeof(float), ent.size() * sizeof(uint32_t)};
-  const void* src[5] = {counts.data(), cell_tris.data(), rec.data(), tris.data(), ent.data()};
+  size_t sz[4] = {(size_t)(ncell + 1) * sizeof(int), cell_tris.size() * sizeof(int), rec.size() * sizeof(float),
+                  tris.size() * sizeof(float)};
+  const void* src[4] = {counts.data(), cell_tris.data(), rec.data(), tris.data()};
   cudaError_t err = cudaSuccess;
-  for (int k = 0; k < 5 && err == cudaSuccess; ++k) {
+  for (int k = 0; k < 4 && err == cudaSuccess; ++k) {
     err = cudaMalloc(&h->buffers[k], sz[k]);
     if (err == cudaSuccess) err = cudaMemcpy(h->buffers[k], src[k], sz[k], cudaMemcpyHostToDevice);
     h->bytes += (int64_t)sz[k];
@@ -230,7 +173,6 @@ void* b200lab_mesh_create(const float* V, int64_t nv, const int32_t* F, int64_t 
     m.cell_tris = (const int*)h->buffers[1];
     m.rec = (const float4*)h->buffers[2];
     m.tris = (const float*)h->buffers[3];
-    m.cell_ent = (const uint4*)h->buffers[4];
     h->host = m;
     h->entries = entries;
     err = cudaMalloc((void**)&h->dev, sizeof(MeshAccel));
@@ -238,7 +180,7 @@ void* b200lab_mesh_create(const float* V, int64_t nv, const int32_t* F, int64_t 
   }
   if (err != cudaSuccess) {
     set_error("b200lab_mesh_create: %s", cudaGetErrorString(err));
-    for (int k = 0; k < 5; ++k) if (h->buffers[k]) cudaFree(h->buffers[k]);
+    for (int k = 0; k < 4; ++k) if (h->buffers[k]) cudaFree(h->buffers[k]);
     if (h->dev) cudaFree(h->dev);
     free(h);
     return nullptr;
@@ -252,7 +194,7 @@ int64_t b200lab_mesh_bytes(void* mesh) { return mesh ? ((MeshHandle*)mesh)->byte
 void b200lab_mesh_destroy(void* mesh) {
   if (!mesh) return;
   MeshHandle* h = (MeshHandle*)mesh;
-  for (int k = 0; k < 5; ++k) if (h->buffers[k]) cudaFree(h->buffers[k]);
+  for (int k = 0; k < 4; ++k) if (h->buffers[k]) cudaFree(h->buffers[k]);
   if (h->dev) cudaFree(h->dev);
   free(h);
 }

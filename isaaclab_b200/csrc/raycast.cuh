@@ -8,15 +8,6 @@
 // XY projection with a 2-D DDA.  Closest hit over all candidates => the result of a brute-force query (the oracle),
 // independent of traversal order.
 //
-// Vertical rays additionally use a per-(cell, triangle) 8x8 SUB-CELL COVERAGE MASK (`cell_ent`: {face id, -, mask lo,
-// mask hi}, 16 B, same CSR order as `cell_tris`): bit (sy*8+sx) is set iff the triangle's XY footprint overlaps sub-cell
-// (sx, sy) of the cell (conservatively, same margin as the cell binning; never set for triangles that are degenerate in
-// XY, which a vertical ray cannot hit).  The ray locates its sub-cell, scans the cell's entries (one batch of loads) and
-// fetches + tests only the triangles whose mask covers that sub-cell: ~1.2 triangle tests per ray instead of 2-6, and
-// nearly uniform work across the lanes of a warp (a quarter of the cells of a height-field terrain hold a lattice vertex
-// and therefore six candidates).  The set of triangles tested is a superset of those the point can lie in, in list order,
-// so the closest hit (and the face id on ties) is unchanged.
-//
 // Per-triangle record (48 B, three 128-bit loads): v0.xyz | 1/det2d, e1.xyz | e2.x, e2.yz.  Vertical rays use the
 // projected 2-D form of Moeller-Trumbore (u, v from xy only, hit z by barycentric interpolation): ~20 flops.
 // Barycentrics within 2e-5 of an edge are re-evaluated in fp64 from the original vertices so the accept/reject decision
@@ -29,11 +20,9 @@ namespace b200lab {
 struct MeshAccel {
   float ox, oy;          // grid origin (min corner)
   float cell, inv_cell;  // cell edge
-  float inv_sub;         // 8 / cell: sub-cell index of the vertical-ray masks
   int nx, ny;
   const int* cell_start;   // [nx*ny + 1]
   const int* cell_tris;    // [entries] triangle ids
-  const uint4* cell_ent;   // [entries] {triangle id, 0, mask lo, mask hi} (vertical rays)
   const float4* rec;       // [F, 3] packed records (see above)
   const float* tris;       // [F, 9] original v0 v1 v2 (fp64 re-checks, normals)
   int num_faces;
@@ -60,6 +49,23 @@ static __device__ __noinline__ float ray_tri_f64(const float* __restrict__ tp, f
 }
 
 constexpr float kBaryBand = 2e-5f;
+
+// Vertical ray (d = (0, 0, dz)): projected form.  Returns t (>0) or -1.
+__device__ __forceinline__ float ray_tri_vertical(const MeshAccel& m, int f, f3 o, float dz, float inv_dz) {
+  const float4* r = m.rec + (size_t)f * 3;
+  float4 a = __ldg(r), b = __ldg(r + 1);
+  float tx = o.x - a.x, ty = o.y - a.y;
+  if (a.w == 0.0f) return -1.0f;  // degenerate in xy (vertical wall): a vertical ray cannot hit its interior
+  float4 c = __ldg(r + 2);
+  float u = (tx * c.x - ty * b.w) * a.w;   // (tx*e2y - ty*e2x) / det2
+  float v = (ty * b.x - tx * b.y) * a.w;   // (ty*e1x - tx*e1y) / det2
+  float w = 1.0f - u - v;
+  if (u < -kBaryBand || v < -kBaryBand || w < -kBaryBand) return -1.0f;
+  if (u < kBaryBand || v < kBaryBand || w < kBaryBand) return ray_tri_f64(m.tris + (size_t)f * 9, o, f3{0.f, 0.f, dz});
+  float zh = a.z + u * b.z + v * c.y;
+  float t = (zh - o.z) * inv_dz;
+  return t > 0.0f ? t : -1.0f;
+}
 
 // General ray: Moeller-Trumbore from the packed record.
 __device__ __forceinline__ float ray_tri(const MeshAccel& m, int f, f3 o, f3 d) {
@@ -96,52 +102,38 @@ __device__ __forceinline__ float ray_tri_vertical_rec(const MeshAccel& m, int f,
   return t > 0.0f ? t : -1.0f;
 }
 
-// Vertical closest hit: one cell.  Three dependent round trips to L2 (cell range -> entries -> records of the entries
-// whose mask covers the ray's sub-cell); every level is requested for all its items at once.
-#ifndef B200LAB_ENT_BATCH
-#define B200LAB_ENT_BATCH 6
-#endif
-constexpr int kEntBatch = B200LAB_ENT_BATCH;   // a lattice-vertex cell of a height field holds 6 triangles
-
-__device__ __forceinline__ bool ent_covers(const uint4& en, int bit) {
-  uint32_t wsel = bit & 32 ? en.w : en.z;
-  return (wsel >> (bit & 31)) & 1u;
-}
-
-__device__ __forceinline__ void vertical_test(const MeshAccel& m, int f, f3 o, float dz, float inv_dz, float& t_best,
-                                              int& face_best) {
-  const float4* r = m.rec + (size_t)f * 3;
-  float4 a = __ldg(r), b = __ldg(r + 1), c = __ldg(r + 2);
-  float t = ray_tri_vertical_rec(m, f, a, b, c, o, dz, inv_dz);
-  if (t > 0.0f && t <= t_best) { t_best = t; face_best = f; }
-}
+// Vertical closest hit: one cell.  The query is three dependent round trips to L2 (cell range -> triangle ids ->
+// records), so each level is requested for up to kVertBatch candidates at once: a typical cell (<= 4 candidates)
+// costs exactly three latencies, and every lane of a warp runs the same single trip.
+// Measured alternatives at 4096 envs (compute_obs, us per launch; profiles/r1_notes.md): batch 2 with padded slots 55 |
+// batch 1: 59 | batch 3: 66 | batch 2 with the padded slots predicated off: 61 | a per-(cell, triangle) 8x8 sub-cell
+// coverage mask that cut the triangle tests from ~3 to ~1.2 per ray: 62 (16-byte entries triple the bytes of the middle
+// round trip).  The kernel is bound by the number of divergent L2 requests in flight, not by the tests.
+constexpr int kVertBatch = 2;
 
 __device__ __forceinline__ bool raycast_vertical(const MeshAccel& m, f3 o, float dz, float max_dist, float& t_out,
                                                  int& face_out) {
   float t_best = max_dist;
   int face_best = -1;
-  int gx = (int)floorf((o.x - m.ox) * m.inv_sub), gy = (int)floorf((o.y - m.oy) * m.inv_sub);
-  int cx = gx >> 3, cy = gy >> 3;
+  int cx = (int)floorf((o.x - m.ox) * m.inv_cell), cy = (int)floorf((o.y - m.oy) * m.inv_cell);
   if (cx >= 0 && cy >= 0 && cx < m.nx && cy < m.ny) {
-    const int c = cy * m.nx + cx;
-    const int s = __ldg(m.cell_start + c), e = __ldg(m.cell_start + c + 1);
-    const int bit = ((gy & 7) << 3) | (gx & 7);
-    const float inv_dz = 1.0f / dz;
-    // scan a batch of entries into a match bitmap, then test the matches in list order (usually one)
-    for (int k = s; k < e; k += kEntBatch) {
-      uint4 en[kEntBatch];
+    int c = cy * m.nx + cx;
+    int s = __ldg(m.cell_start + c), e = __ldg(m.cell_start + c + 1);
+    float inv_dz = 1.0f / dz;
+    for (int k = s; k < e; k += kVertBatch) {
+      int f[kVertBatch];
 #pragma unroll
-      for (int i = 0; i < kEntBatch; ++i) en[i] = __ldg(m.cell_ent + min(k + i, e - 1));
-      unsigned mm = 0;
+      for (int i = 0; i < kVertBatch; ++i) f[i] = __ldg(m.cell_tris + min(k + i, e - 1));
+      float4 ra[kVertBatch], rb[kVertBatch], rc[kVertBatch];
 #pragma unroll
-      for (int i = 0; i < kEntBatch; ++i) mm |= (k + i < e && ent_covers(en[i], bit)) ? 1u << i : 0u;
-      while (mm) {
-        const int i = __ffs(mm) - 1;
-        mm &= mm - 1;
-        int f = (int)en[0].x;
+      for (int i = 0; i < kVertBatch; ++i) {
+        const float4* r = m.rec + (size_t)f[i] * 3;
+        ra[i] = __ldg(r); rb[i] = __ldg(r + 1); rc[i] = __ldg(r + 2);
+      }
 #pragma unroll
-        for (int q = 1; q < kEntBatch; ++q) f = i == q ? (int)en[q].x : f;
-        vertical_test(m, f, o, dz, inv_dz, t_best, face_best);
+      for (int i = 0; i < kVertBatch; ++i) {
+        float t = ray_tri_vertical_rec(m, f[i], ra[i], rb[i], rc[i], o, dz, inv_dz);   // padded slots repeat the last id
+        if (t > 0.0f && t <= t_best) { t_best = t; face_best = f[i]; }
       }
     }
   }

@@ -406,6 +406,7 @@ class FusedEnv:
         if not self.handle:
             raise RuntimeError("b200lab_env_create failed: " + self.L.b200lab_last_error().decode())
         self.step_counter = 0
+        self.speculative_scan = False   # opt-in: see b200lab_height_scan_prefetch
 
     def __del__(self):
         try:
@@ -414,6 +415,15 @@ class FusedEnv:
                 self.handle = None
         except Exception:
             pass
+
+    def use_device_step_counter(self):
+        """Keeps the step counter (the Philox key of perf mode) on the device: `process_action` / `decimation_fused`
+        increment it, the other kernels read it, and the `step_counter` argument of the entry points is ignored -- which
+        is what makes a whole step capturable in a CUDA graph."""
+        if getattr(self, "step_counter_t", None) is None:
+            self.step_counter_t = torch.full((1,), self.step_counter - 1, dtype=torch.int64, device=self.device)
+            self._st.step_counter_dev = _lib.ptr(self.step_counter_t)
+            _lib.check(self.L.b200lab_env_update(self.handle, ctypes.byref(self._st)))
 
     # ------------------------------------------------------------------------------------------------
     def set_uniforms(self, u_reset=None, u_step=None, u_obs=None):
@@ -439,8 +449,8 @@ class FusedEnv:
         _lib.check(self.L.b200lab_substep_post(self.handle, sim.ref, _lib.current_stream()))
 
     def height_scan_prefetch(self, sim: SimView):
-        """Live-simulator path: start the height scan from the post-physics state `sim` on the library's side stream; the
-        next `compute_obs` joins it (b200lab_height_scan_prefetch).  `decimation_fused` does this itself."""
+        """Start the height scan from the post-physics state `sim` on the library's side stream; the next `compute_obs`
+        joins it (b200lab_height_scan_prefetch).  `step` does this when `speculative_scan` is set."""
         _lib.check(self.L.b200lab_height_scan_prefetch(self.handle, sim.ref, _lib.current_stream()))
 
     def post_step(self, sim: SimView):
@@ -459,6 +469,18 @@ class FusedEnv:
         _lib.check(self.L.b200lab_compute_obs(self.handle, sim.ref, self.step_counter, _lib.current_stream()))
         return self.obs_buf
 
+    def step_tail_ranges(self, sim: SimView, ranges, after_range):
+        """`step_tail` with the observation rows computed range by range (b200lab_step_tail_begin /
+        b200lab_compute_obs_range / b200lab_step_tail_end); `after_range(begin, end)` runs after each range has been
+        queued, e.g. to start its device->host copy on another stream while the next range is computed."""
+        st = _lib.current_stream()
+        _lib.check(self.L.b200lab_step_tail_begin(self.handle, sim.ref, st))
+        for b, e in ranges:
+            _lib.check(self.L.b200lab_compute_obs_range(self.handle, sim.ref, self.step_counter, b, e, st))
+            after_range(b, e)
+        _lib.check(self.L.b200lab_step_tail_end(self.handle, st))
+        return self.obs_buf
+
     def decimation_fused(self, action, sims, sim_prev):
         """Replay fast path: process_action + all S (pre, post) sub-steps in one launch (b200lab_decimation_fused)."""
         if action.shape != (self.N, self.A):
@@ -474,7 +496,7 @@ class FusedEnv:
         _lib.check(self.L.b200lab_decimation_fused(self.handle, _lib.ptr(action), sim_prev.ref, arr, len(sims),
                                                    _lib.current_stream()))
 
-    def step(self, action, sims, sim_prev, fused: bool = True):
+    def step(self, action, sims, sim_prev, fused: bool = True, obs_ranges=None, after_post_step=None, after_range=None):
         """One env step on S known post-physics states: [process_action -> S x (pre(previous state), post(new state))]
         -> post_step -> compute_obs (manager_based_rl_env.py:153-242; mirrors oracle.mdp_env.OracleEnv.step).
         `fused=True` runs the bracketed part as one launch, `fused=False` as the 1 + 2S calls a live simulator uses."""
@@ -488,9 +510,14 @@ class FusedEnv:
                 self.substep_pre(prev)
                 self.substep_post(sim)
                 prev = sim
+        if self.speculative_scan:
             self.height_scan_prefetch(prev)
         self.post_step(prev)
-        if fused:
+        if after_post_step is not None:
+            after_post_step()
+        if fused and obs_ranges is not None:
+            self.step_tail_ranges(prev, obs_ranges, after_range)
+        elif fused:
             self.step_tail(prev)
         else:
             self.post_reset_write(prev)

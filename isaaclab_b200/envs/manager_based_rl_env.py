@@ -11,6 +11,8 @@ Managers are thin views of the fused state with the reference's attribute surfac
 """
 from __future__ import annotations
 
+import gc
+
 import torch
 
 from .. import _lib
@@ -68,10 +70,17 @@ class HostReplaySim:
         self.stage[slot].copy_(self.host[k], non_blocking=True)
         self._staged[slot] = k
 
-    def prefetch(self, slot, k):
-        """H2D of slab k into `slot` on the copy stream, after everything already queued on the compute stream (the
-        last readers of that set) has finished."""
+    def mark_free(self):
+        """Records, on the compute stream, the point after which the staging set of the NEXT step is free (its last
+        reader was the previous step): `prefetch_next(marked=True)` then waits for this point only, so the env can queue
+        the current step's kernels first and the copy still overlaps them."""
         self._free.record(torch.cuda.current_stream())
+
+    def prefetch(self, slot, k, marked=False):
+        """H2D of slab k into `slot` on the copy stream, after everything already queued on the compute stream (the
+        last readers of that set) has finished -- or after the last `mark_free()` when `marked`."""
+        if not marked:
+            self._free.record(torch.cuda.current_stream())
         with torch.cuda.stream(self.copy_stream):
             self.copy_stream.wait_event(self._free)
             self._copy(slot, k)
@@ -89,10 +98,10 @@ class HostReplaySim:
         torch.cuda.current_stream().wait_event(self._ready[self.slot])
         return self._views[self.slot]
 
-    def prefetch_next(self):
+    def prefetch_next(self, marked=False):
         """Queue the H2D of the step after the current one (its target set was last read by the previous step)."""
         if self.prefetch_enabled:
-            self.prefetch((self.slot + 1) % self._SETS, (self.k + 1) % self.K)
+            self.prefetch((self.slot + 1) % self._SETS, (self.k + 1) % self.K, marked)
 
     def last_view(self):
         return self._views[self.slot][-1]
@@ -204,6 +213,16 @@ class ManagerBasedRLEnv:
         self.obs_buf = {self._group: f.obs_buf}
         self._action_dev = torch.zeros(self.num_envs, f.A, device=device)
         self._prefetch_next = getattr(self.sim, "prefetch_next", None)
+        # pipelined result read-back (`step(..., results_out=pinned_slab)`): the small results leave after post_step and
+        # each finished range of observation rows leaves while the next range is computed
+        self._d2h_stream = None
+        self._d2h_events = []
+        self._d2h_done = None
+        self.result_chunks = 4
+        self.use_cuda_graph = bool(use_cuda_graph)
+        self._graphs, self._graph_warm = {}, False
+        if self.use_cuda_graph:
+            f.use_device_step_counter()
 
     @property
     def episode_length_buf(self):
@@ -260,18 +279,112 @@ class ManagerBasedRLEnv:
         self.fused.compute_obs(self.sim.last_view())
         return self.obs_buf, self.extras
 
-    def step(self, action: torch.Tensor):
+    def _setup_d2h(self):
+        self._d2h_stream = torch.cuda.Stream(device=self.device)
+        self._d2h_events = [torch.cuda.Event() for _ in range(self.result_chunks + 2)]
+        N, C = self.num_envs, max(1, min(self.result_chunks, self.num_envs))
+        edges = [N * i // C for i in range(C + 1)]
+        self._d2h_ranges = [(edges[i], edges[i + 1]) for i in range(C) if edges[i + 1] > edges[i]]
+
+    def wait_results(self):
+        """Blocks until the `results_out` slab of the last `step` is complete on the host."""
+        if self._d2h_done is not None:
+            self._d2h_done.synchronize()
+
+    def _step_body(self, action, views, prev, results_out, pipelined):
+        """The device work of one step on the current stream: stage a host action, the fused kernels, and -- when a
+        pinned `results_out` slab is given -- the read-back.  `pipelined`: reward / masks leave right after post_step and
+        each finished range of observation rows leaves on a copy stream while the next range is computed (used inside
+        a captured graph, where the extra enqueue calls cost nothing at replay); otherwise one copy at the end."""
         f = self.fused
+        if results_out is None or not pipelined:
+            f.step(action, views, prev)
+            if results_out is not None:
+                results_out.copy_(f.result, non_blocking=True)
+            return
+        if self._d2h_stream is None:
+            self._setup_d2h()
+        cur, cs, it = torch.cuda.current_stream(), self._d2h_stream, iter(self._d2h_events)
+        row = f.obs_buf.shape[1] * 4
+        o_rew = f.result_layout["reward"][0]
+
+        def push(lo, hi):
+            e = next(it)
+            e.record(cur)
+            cs.wait_event(e)
+            with torch.cuda.stream(cs):
+                results_out[lo:hi].copy_(f.result[lo:hi], non_blocking=True)
+
+        f.step(action, views, prev, obs_ranges=self._d2h_ranges,
+               after_post_step=lambda: push(o_rew, f.result.numel()),
+               after_range=lambda b, e: push(b * row, e * row))
+        e = next(it)
+        e.record(cs)
+        cur.wait_event(e)   # join: everything is ordered on the current stream again
+
+    def step(self, action: torch.Tensor, results_out: torch.Tensor | None = None):
+        """`results_out`: optional pinned uint8 host slab of `fused.result.numel()` bytes (layout `fused.result_layout`,
+        typed views from `result_views`) that receives observations, reward, terminated, time-outs and the reset mask;
+        call `wait_results()` before reading it.  With `use_cuda_graph=True` the whole step -- action staging, kernels,
+        pipelined read-back -- is captured once per (action buffer, result slab, simulator staging set) and replayed
+        with one launch; the first step runs eagerly."""
+        prev = self.sim.last_view()
+        views = self.sim.advance()
         if action.device != self.device:  # host action: staged through a fixed device buffer
             self._action_dev.copy_(action, non_blocking=True)
             action = self._action_dev
-        prev = self.sim.last_view()
-        views = self.sim.advance()
-        f.step(action, views, prev)
+        # The staging set of the NEXT step was last read by the previous step, which precedes everything queued below on
+        # this stream: its H2D copy only has to wait for this point (after the small action copy -- H2D copies share one
+        # engine and run in issue order) and crosses PCIe while this step's kernels run.  The copy itself is queued after
+        # the kernels so that the GPU is not idle while the host enqueues it.
+        mark = getattr(self.sim, "mark_free", None) if self._prefetch_next is not None else None
+        if mark is not None:
+            mark()
+        graph = None
+        if self.use_cuda_graph:
+            key = (action.data_ptr(), -1 if results_out is None else results_out.data_ptr(),
+                   tuple(id(v) for v in views), id(prev))
+            graph = self._graphs.get(key)
+            if graph is None and self._graph_warm:
+                if len(self._graphs) >= 64:
+                    self._graphs.clear()
+                graph = torch.cuda.CUDAGraph()
+                # a collection that frees another env / mesh (cudaFree) while the stream is capturing would invalidate
+                # the capture
+                gc_was_enabled = gc.isenabled()
+                gc.collect()
+                gc.disable()
+                try:
+                    with torch.cuda.graph(graph):
+                        self._step_body(action, views, prev, results_out, pipelined=True)
+                finally:
+                    if gc_was_enabled:
+                        gc.enable()
+                self._graphs[key] = graph
+        if graph is not None:
+            graph.replay()
+            self.fused.step_counter += 1
+        else:
+            self._step_body(action, views, prev, results_out, pipelined=False)
+            self._graph_warm = True
+        if results_out is not None:
+            if self._d2h_done is None:
+                self._d2h_done = torch.cuda.Event()
+            self._d2h_done.record(torch.cuda.current_stream())
         if self._prefetch_next is not None:
-            self._prefetch_next()
+            if mark is not None:
+                self._prefetch_next(marked=True)
+            else:
+                self._prefetch_next()
         self.common_step_counter += 1
         return self.obs_buf, self.reward_buf, self.reset_terminated, self.reset_time_outs, self.extras
+
+    def result_views(self, host_slab: torch.Tensor):
+        """Typed views of a result slab filled by `step(..., results_out=host_slab)` or `read_results`."""
+        lay, N = self.fused.result_layout, self.num_envs
+        return {"obs": host_slab[lay["obs"][0]:lay["obs"][1]].view(torch.float32).view(N, -1),
+                "reward": host_slab[lay["reward"][0]:lay["reward"][1]].view(torch.float32),
+                **{k: host_slab[lay[k][0]:lay[k][1]] for k in ("terminated", "truncated", "reset_buf")}}
 
     def read_results(self, host_slab: torch.Tensor):
         """ONE device->host copy (async on the current stream) of everything `step` returned -- observations, reward,

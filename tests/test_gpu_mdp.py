@@ -26,7 +26,7 @@ def exact(a, b, name):
     assert torch.equal(a.to(b.dtype), b), f"{name}: {(a.to(b.dtype) != b).sum().item()} mismatches"
 
 
-@pytest.mark.parametrize("fused", [True, False], ids=["fused-decimation", "per-substep"])
+@pytest.mark.parametrize("fused", [True, False, "spec"], ids=["fused-decimation", "per-substep", "fused+speculative-scan"])
 @pytest.mark.parametrize("task", TASKS)
 def test_fused_step_matches_oracle(task, fused):
     from isaaclab_b200.envs.fused_env import FusedEnv
@@ -38,6 +38,8 @@ def test_fused_step_matches_oracle(task, fused):
     init["episode_length_buf"][::7] = spec["max_episode_length"] - 2  # force time-outs within the test horizon
     orc = OracleEnv(copy.deepcopy(spec))
     fus = FusedEnv(spec, device="cuda")
+    fus.speculative_scan = fused == "spec"   # height scan cast ahead on a side stream, reset envs recast (same results)
+    fused = bool(fused)
     init_oracle_state(orc, init)
     init_fused_state(fus, init)
     sim = SyntheticSim(spec, K=steps + 1, device="cuda", slabs={k: v.clone() for k, v in slabs.items()})
@@ -179,7 +181,7 @@ def test_host_replay_prefetch_matches_device_replay(task):
     slabs = generate_slabs(spec, K, seed=77)
     g = torch.Generator().manual_seed(5)
     outs = []
-    for kind in ("device", "host", "host-noprefetch"):
+    for kind in ("device", "host", "host-noprefetch", "host-pipelined", "host-graph"):
         if kind == "device":
             syn = SyntheticSim(spec, K=K, device="cuda", slabs={k: v.clone() for k, v in slabs.items()})
             sim = DeviceReplaySim(syn)
@@ -190,22 +192,33 @@ def test_host_replay_prefetch_matches_device_replay(task):
                 return sim.syn.views(sim.k)
             sim.advance = advance
         else:
-            sim = HostReplaySim(spec, {k: v.clone() for k, v in slabs.items()}, device="cuda", prefetch=kind == "host")
-        env = ManagerBasedRLEnv(TASKS[task](), sim=sim, device="cuda", spec=copy.deepcopy(spec), seed=3)
+            sim = HostReplaySim(spec, {k: v.clone() for k, v in slabs.items()}, device="cuda", prefetch=kind != "host-noprefetch")
+        env = ManagerBasedRLEnv(TASKS[task](), sim=sim, device="cuda", spec=copy.deepcopy(spec), seed=3,
+                                use_cuda_graph=kind == "host-graph")
         env.episode_length_buf[::5] = spec["max_episode_length"] - 3
+        act_pinned = torch.empty(N, spec["A"]).pin_memory()
         g.manual_seed(5)
         rec = []
+        slab = torch.empty(env.fused.result.numel(), dtype=torch.uint8).pin_memory()
         for _ in range(K - 1):
             act = torch.randn(N, spec["A"], generator=g)
+            if kind in ("host-pipelined", "host-graph"):   # results land in a pinned slab; graph: captured per staging set
+                act_pinned.copy_(act)
+                env.step(act_pinned, results_out=slab)
+                env.wait_results()
+                v = env.result_views(slab)
+                rec.append((v["obs"].clone().cuda(), v["reward"].clone().cuda(), v["terminated"].bool().cuda(),
+                            v["truncated"].bool().cuda()))
+                continue
             obs, rew, term, trunc, _ = env.step(act.pin_memory())
             rec.append((obs["policy"].clone(), rew.clone(), term.clone(), trunc.clone()))
         torch.cuda.synchronize()
         outs.append(rec)
     assert any(bool(r[3].any()) for r in outs[0]), "no time-outs in the horizon"
-    for other in outs[1:]:
+    for arm, other in zip(("host", "host-noprefetch", "host-pipelined", "host-graph"), outs[1:]):
         for k, (a, b) in enumerate(zip(outs[0], other)):
             for x, y, name in zip(a, b, ("obs", "reward", "terminated", "time_outs")):
-                assert torch.equal(x, y), f"{task} step {k}: {name} differs between device and host replay"
+                assert torch.equal(x, y), f"{task} step {k}: {name} differs between device and {arm} replay"
 
 
 def test_observation_noise_kinds_match_oracle():
