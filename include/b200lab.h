@@ -407,7 +407,11 @@ int b200lab_post_step(void* env, const B200LabSimView* sim, int64_t step_counter
 int b200lab_post_reset_write(void* env, const B200LabSimView* sim, void* stream);
 
 /* ObservationManager.compute (observation_manager.py:238-335) including RayCaster lazy update +
- * raycast_mesh for outdated envs (ray_caster.py:220-260, LAB/utils/warp/ops.py:24-127). */
+ * raycast_mesh for outdated envs (ray_caster.py:220-260, LAB/utils/warp/ops.py:24-127).  * The per-env quantities shared by the columns (base-frame velocities, projected gravity, sensor pose; the ray-caster's
+ * outdated/timestamp bookkeeping of sensor_base.py:287-296) are derived by b200lab_post_step from the state it leaves and
+ * stay valid until the next call that advances the env (process_action, decimation_fused, substep_pre/post,
+ * env_update); called without a preceding post_step on the same view, compute_obs derives them itself.  Writing the
+ * simulator tensors between post_step and compute_obs therefore requires b200lab_env_update. */
 int b200lab_compute_obs(void* env, const B200LabSimView* sim, int64_t step_counter, void* stream);
 
 /* post_reset_write and compute_obs issued together: the actuator pass runs on a library-owned side stream forked from

@@ -40,6 +40,10 @@ struct EnvHandle {
   float* spec_pose;
   int64_t spec_cap;        // N*R the buffers were sized for
   bool spec_pending;       // a prefetch has been enqueued and not yet joined
+  // post_step leaves the derived per-env quantities of its final state in `derived`; they stay valid -- and the
+  // observation kernels use them instead of running derive_obs_kernel -- until the next entry point that advances the
+  // env (process_action, decimation_fused, substep_pre/post, env_update)
+  const float* derived_root;   // root_state_w pointer of the view post_step derived from (or NULL)
   bool lstm_const;
   const float* lstm_src;   // device pointer the copy was taken from
   float lstm_w[1024];   // packed NetLstm<8,2> image (see NetLstm)
@@ -950,13 +954,66 @@ __device__ __forceinline__ void resample_command(const Env* e, int n, const floa
   e->cmd_is_standing[n] = u[6] <= e->cmd_rel_standing;
 }
 
+// Per-env derived quantities shared by all obs columns / rays of an env: [N, kDerived] floats in a scratch buffer owned
+// by the env handle, filled by derive_env -- at the end of post_step (lane 0, from the root state it holds in registers)
+// or by derive_obs_kernel when compute_obs is called on its own.
+//   0-2 lin_b, 3-5 ang_b, 6-8 grav_b, 9-11 sensor pos (root pos + drift), 12-15 sensor-frame quaternion (yaw-only when
+//   attach_yaw_only), 16 root z, 17 ray-caster outdated flag, 18 speculative scan valid
+constexpr int kDerived = 20;
+constexpr int kSpecPose = 8;   // sensor position (root + drift) xyz, sensor-frame quaternion wxyz, pad
+
+// `rc_flag`, `drift`, `rc_ts`: the ray caster's is_outdated flag, drift and timestamp of this env (callers that hold them
+// in registers avoid two dependent round trips at the end of their serial chain)
+__device__ __forceinline__ void derive_env(const Env* __restrict__ e, const float (&rs)[13], int n, float* __restrict__ derived,
+                                           const float* __restrict__ spec_pose, bool rc_flag, const float (&drift)[3],
+                                           float rc_ts) {
+  float* o = derived + (int64_t)n * kDerived;
+  f4 q{rs[3], rs[4], rs[5], rs[6]};
+  f3 lb = quat_rotate_inverse(q, f3{rs[7], rs[8], rs[9]});       // articulation_data.py:604-610
+  f3 ab = quat_rotate_inverse(q, f3{rs[10], rs[11], rs[12]});    // :613-619
+  f3 gb = quat_rotate_inverse(q, f3{0.f, 0.f, -1.f});            // :513-515
+  o[0] = lb.x; o[1] = lb.y; o[2] = lb.z;
+  o[3] = ab.x; o[4] = ab.y; o[5] = ab.z;
+  o[6] = gb.x; o[7] = gb.y; o[8] = gb.z;
+  o[16] = rs[2];
+  float rc_out = 0.f, spec_ok = 0.f;
+  if (e->rc_is_outdated) {
+    rc_out = rc_flag ? 1.f : 0.f;
+    if (rc_out != 0.f) {
+      // RayCaster._update_buffers_impl (ray_caster.py:225-241): pose (+ drift) of the outdated sensors
+      float px = rs[0] + drift[0], py = rs[1] + drift[1], pz = rs[2] + drift[2];
+      o[9] = px; o[10] = py; o[11] = pz;
+      f4 qy = e->rc_attach_yaw_only ? yaw_quat(q) : q;
+      o[12] = qy.w; o[13] = qy.x; o[14] = qy.y; o[15] = qy.z;
+      e->rc_pos_w[n * 3] = px; e->rc_pos_w[n * 3 + 1] = py; e->rc_pos_w[n * 3 + 2] = pz;
+      e->rc_quat_w[n * 4] = q.w; e->rc_quat_w[n * 4 + 1] = q.x; e->rc_quat_w[n * 4 + 2] = q.y; e->rc_quat_w[n * 4 + 3] = q.z;
+      e->rc_timestamp_last_update[n] = rc_ts;   // sensor_base.py:294-296
+      e->rc_is_outdated[n] = 0;
+      // the speculative scan is valid for this env iff it was cast from bitwise the same sensor pose
+      if (spec_pose) {
+        const float* sp = spec_pose + (int64_t)n * kSpecPose;
+        const float pose[7] = {px, py, pz, qy.w, qy.x, qy.y, qy.z};
+        bool same = true;
+#pragma unroll
+        for (int k = 0; k < 7; ++k) same = same && __float_as_uint(sp[k]) == __float_as_uint(pose[k]);
+        spec_ok = same ? 1.f : 0.f;
+      }
+    } else {
+      o[11] = e->rc_pos_w[n * 3 + 2];
+    }
+  }
+  o[17] = rc_out;
+  o[18] = spec_ok;
+}
+
 constexpr int kStepWarps = 4;
 #ifndef B200LAB_POST_BLOCKS
 #define B200LAB_POST_BLOCKS 6
 #endif
 
 __global__ void __launch_bounds__(kStepWarps * 32, B200LAB_POST_BLOCKS)
-post_step_kernel(const __grid_constant__ Env env_param, Sim sim, int64_t step, const Env* __restrict__ env_dev) {
+post_step_kernel(const __grid_constant__ Env env_param, Sim sim, int64_t step, const Env* __restrict__ env_dev,
+                 float* __restrict__ derived) {
   const Env* __restrict__ e = &env_param;   // descriptor in the constant bank: warp-uniform reads, no global round trips
   // The termination / reward term tables are staged from the device copy of the descriptor into shared memory: read
   // through the constant bank they push the kernel's constant footprint past ~4 KB, where every launch pays several
@@ -999,6 +1056,14 @@ post_step_kernel(const __grid_constant__ Env env_param, Sim sim, int64_t step, c
 #pragma unroll
   for (int k = 0; k < B200LAB_MAX_INTERVAL_EVENTS; ++k) pre_itl[k] = k < e->num_interval ? e->ev_interval_time_left[k][n] : 0.f;
   const float pre_esum = lane < e->num_rew ? e->episode_sums[(int64_t)lane * N + n] : 0.f;
+  bool pre_rc_flag = false;
+  float pre_drift[3] = {0.f, 0.f, 0.f}, pre_rc_ts = 0.f;
+  if (derived && e->rc_is_outdated) {
+    pre_rc_flag = e->rc_is_outdated[n] != 0;
+    pre_rc_ts = e->rc_timestamp[n];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) pre_drift[k] = e->rc_drift[n * 3 + k];
+  }
   // -- episode counter (manager_based_rl_env.py:200)
   int64_t ep_len = e->episode_length_buf[n] + 1;
   // -- terminations (termination_manager.py:151-174)
@@ -1094,8 +1159,11 @@ post_step_kernel(const __grid_constant__ Env env_param, Sim sim, int64_t step, c
     // scene.reset: ray caster (ray_caster.py:107-114)
     if (e->rc_timestamp && lane == 0) {
       e->rc_timestamp[n] = 0.f; e->rc_timestamp_last_update[n] = 0.f; e->rc_is_outdated[n] = 1;
-      for (int k = 0; k < 3; ++k)
-        e->rc_drift[n * 3 + k] = u_reset_at(e, n, B200LAB_U_RESET_DRIFT + k, step) * e->rc_drift_span + e->rc_drift_lo;
+      pre_rc_ts = 0.f; pre_rc_flag = true;
+      for (int k = 0; k < 3; ++k) {
+        pre_drift[k] = u_reset_at(e, n, B200LAB_U_RESET_DRIFT + k, step) * e->rc_drift_span + e->rc_drift_lo;
+        e->rc_drift[n * 3 + k] = pre_drift[k];
+      }
     }
     // reset events: reset_root_state_uniform (events.py:823-865)
     if (e->ev_reset_root_state) {
@@ -1229,14 +1297,11 @@ post_step_kernel(const __grid_constant__ Env env_param, Sim sim, int64_t step, c
       }
       e->ev_interval_time_left[k][n] = tl;
     }
+    // the quantities compute_obs shares across the columns of this env, from the final root state of the step (lane 0
+    // holds it: resets were applied by every lane, pushes by lane 0) -- saves the derive launch on the critical path
+    if (derived) derive_env(e, rs, n, derived, nullptr, pre_rc_flag, pre_drift, pre_rc_ts);
   }
 }
-
-// Per-env derived quantities shared by all obs columns / rays of an env: [N, kDerived] floats in a scratch buffer owned
-// by the env handle, filled by derive_obs_kernel (one thread per env) right before compute_obs_kernel.
-//   0-2 lin_b, 3-5 ang_b, 6-8 grav_b, 9-11 sensor pos (root pos + drift), 12-15 sensor-frame quaternion (yaw-only when
-//   attach_yaw_only), 16 root z, 17 ray-caster outdated flag
-constexpr int kDerived = 20;
 
 // Per-column program of the concatenated group (48 B, three coalesced 128-bit loads per thread), built at env_create:
 //   a = {op | src << 8 | noise_kind << 24 | clip_on << 30 | scale_on << 31, noise_lo, noise_span, scale}
@@ -1244,7 +1309,6 @@ constexpr int kDerived = 20;
 //   c = {ray local start xyz, ray direction z}   (height-scan columns)
 struct ObsCol { float4 a, b, c; };
 
-constexpr int kSpecPose = 8;   // sensor position (root + drift) xyz, sensor-frame quaternion wxyz, pad
 
 __global__ void __launch_bounds__(128)
 derive_obs_kernel(const __grid_constant__ Env env_param, Sim sim, float* __restrict__ derived,
@@ -1252,43 +1316,18 @@ derive_obs_kernel(const __grid_constant__ Env env_param, Sim sim, float* __restr
   const Env* __restrict__ e = &env_param;
   int n = env_begin + blockIdx.x * blockDim.x + threadIdx.x;
   if (n >= env_end) return;
-  const float* rs = sim.root_state_w + (int64_t)n * 13;
-  float* o = derived + (int64_t)n * kDerived;
-  f4 q{rs[3], rs[4], rs[5], rs[6]};
-  f3 lb = quat_rotate_inverse(q, f3{rs[7], rs[8], rs[9]});       // articulation_data.py:604-610
-  f3 ab = quat_rotate_inverse(q, f3{rs[10], rs[11], rs[12]});    // :613-619
-  f3 gb = quat_rotate_inverse(q, f3{0.f, 0.f, -1.f});            // :513-515
-  o[0] = lb.x; o[1] = lb.y; o[2] = lb.z;
-  o[3] = ab.x; o[4] = ab.y; o[5] = ab.z;
-  o[6] = gb.x; o[7] = gb.y; o[8] = gb.z;
-  o[16] = rs[2];
-  float rc_out = 0.f, spec_ok = 0.f;
-  if (e->rc_is_outdated) {
-    rc_out = e->rc_is_outdated[n] != 0 ? 1.f : 0.f;
-    if (rc_out != 0.f) {
-      // RayCaster._update_buffers_impl (ray_caster.py:225-241): pose (+ drift) of the outdated sensors
-      float px = rs[0] + e->rc_drift[n * 3], py = rs[1] + e->rc_drift[n * 3 + 1], pz = rs[2] + e->rc_drift[n * 3 + 2];
-      o[9] = px; o[10] = py; o[11] = pz;
-      f4 qy = e->rc_attach_yaw_only ? yaw_quat(q) : q;
-      o[12] = qy.w; o[13] = qy.x; o[14] = qy.y; o[15] = qy.z;
-      e->rc_pos_w[n * 3] = px; e->rc_pos_w[n * 3 + 1] = py; e->rc_pos_w[n * 3 + 2] = pz;
-      e->rc_quat_w[n * 4] = q.w; e->rc_quat_w[n * 4 + 1] = q.x; e->rc_quat_w[n * 4 + 2] = q.y; e->rc_quat_w[n * 4 + 3] = q.z;
-      e->rc_timestamp_last_update[n] = e->rc_timestamp[n];   // sensor_base.py:294-296
-      e->rc_is_outdated[n] = 0;
-      // the speculative scan is valid for this env iff it was cast from bitwise the same sensor pose
-      if (spec_pose) {
-        const float* sp = spec_pose + (int64_t)n * kSpecPose;
-        bool same = true;
+  float rs[13];
 #pragma unroll
-        for (int k = 0; k < 7; ++k) same = same && __float_as_uint(sp[k]) == __float_as_uint(o[9 + k]);
-        spec_ok = same ? 1.f : 0.f;
-      }
-    } else {
-      o[11] = e->rc_pos_w[n * 3 + 2];
-    }
+  for (int k = 0; k < 13; ++k) rs[k] = sim.root_state_w[(int64_t)n * 13 + k];
+  bool rc_flag = false;
+  float drift[3] = {0.f, 0.f, 0.f}, rc_ts = 0.f;
+  if (e->rc_is_outdated) {
+    rc_flag = e->rc_is_outdated[n] != 0;
+    rc_ts = e->rc_timestamp[n];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) drift[k] = e->rc_drift[n * 3 + k];
   }
-  o[17] = rc_out;
-  o[18] = spec_ok;
+  derive_env(e, rs, n, derived, spec_pose, rc_flag, drift, rc_ts);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -1469,6 +1508,7 @@ static int upload_obs_tables(EnvHandle* h) {
   // speculative-scan buffers; any descriptor change invalidates the recorded poses (NaN never compares equal to a pose)
   if (h->side2) cudaStreamSynchronize(h->side2);
   h->spec_pending = false;
+  h->derived_root = nullptr;
   const int64_t need = h->rays_vertical && h->has_mesh ? (int64_t)s.N * s.R : 0;
   if (need > h->spec_cap) {
     if (h->spec_z) cudaFree(h->spec_z);
@@ -1652,6 +1692,7 @@ void b200lab_env_destroy(void* env) {
 int b200lab_process_action(void* env, const float* action_in, void* stream) {
   B200LAB_CHECK_ARG(env && action_in, "null argument");
   EnvHandle* h = (EnvHandle*)env;
+  h->derived_root = nullptr;
   int64_t total = (int64_t)h->host.N * h->host.A;
   process_action_kernel<<<(unsigned)ceil_div(total, 256), 256, 0, (cudaStream_t)stream>>>(h->host, action_in);
   count_launch();
@@ -1688,6 +1729,7 @@ static int net_smem_bytes(const B200LabEnvState& s, size_t* out) {
 int b200lab_substep_pre(void* env, const B200LabSimView* sim, void* stream) {
   B200LAB_CHECK_ARG(env && sim && sim->joint_pos && sim->joint_vel, "null argument");
   EnvHandle* h = (EnvHandle*)env;
+  h->derived_root = nullptr;
   const B200LabEnvState& s = h->host;
   size_t smem = 0;
   int rc = net_smem_bytes(s, &smem);
@@ -1715,6 +1757,7 @@ int b200lab_post_reset_write(void* env, const B200LabSimView* sim, void* stream)
 int b200lab_substep_post(void* env, const B200LabSimView* sim, void* stream) {
   B200LAB_CHECK_ARG(env && sim && sim->joint_vel, "null argument");
   EnvHandle* h = (EnvHandle*)env;
+  h->derived_root = nullptr;
   const B200LabEnvState& s = h->host;
   int W, epb;
   int width = s.J > s.B ? s.J : s.B;
@@ -1759,6 +1802,7 @@ int b200lab_decimation_fused(void* env, const float* action_in, const B200LabSim
   B200LAB_CHECK_ARG(env && action_in && prev && views, "null argument");
   B200LAB_CHECK_ARG(num_substeps >= 1 && num_substeps <= kMaxDecimation, "decimation must be in 1..8");
   EnvHandle* h = (EnvHandle*)env;
+  h->derived_root = nullptr;
   const B200LabEnvState& s = h->host;
   size_t smem = 0;
   int rc = net_smem_bytes(s, &smem);
@@ -1794,8 +1838,11 @@ int b200lab_post_step(void* env, const B200LabSimView* sim, int64_t step_counter
   const B200LabEnvState& s = h->host;
   B200LAB_CHECK_ARG(s.J <= 64 && s.B <= 64, "joint/body masks support up to 64 joints/bodies");
   const size_t tab_bytes = (size_t)(s.num_term + s.num_rew) * sizeof(B200LabTerm);
+  // a pending speculative scan is validated by the stand-alone derive kernel (it must be joined first)
+  const bool fuse_derive = !h->spec_pending && s.obs_dim > 0;
   post_step_kernel<<<(unsigned)ceil_div(s.N, kStepWarps), kStepWarps * 32, tab_bytes, (cudaStream_t)stream>>>(
-      h->host, *sim, step_counter, h->dev);
+      h->host, *sim, step_counter, h->dev, fuse_derive ? h->derived : nullptr);
+  h->derived_root = fuse_derive ? sim->root_state_w : nullptr;
   count_launch();
   return check_launch("post_step");
 }
@@ -1814,10 +1861,12 @@ int b200lab_compute_obs_range(void* env, const B200LabSimView* sim, int64_t step
   }
   const int cnt = env_end - env_begin;
   if (cnt == 0) return B200LAB_OK;
-  derive_obs_kernel<<<(unsigned)ceil_div(cnt, 128), 128, 0, st_>>>(h->host, *sim, h->derived,
-                                                                 h->rays_vertical && h->has_mesh ? h->spec_pose : nullptr,
-                                                                 env_begin, env_end);
-  count_launch();
+  if (!(h->derived_root && h->derived_root == sim->root_state_w)) {
+    derive_obs_kernel<<<(unsigned)ceil_div(cnt, 128), 128, 0, st_>>>(h->host, *sim, h->derived,
+                                                                   h->rays_vertical && h->has_mesh ? h->spec_pose : nullptr,
+                                                                   env_begin, env_end);
+    count_launch();
+  }
   int64_t total = (int64_t)cnt * s.obs_dim;
   if (total <= 0) return check_launch("compute_obs");
   if (h->rays_vertical)
