@@ -355,7 +355,9 @@ class ManagerBasedRLEnv:
                 gc.collect()
                 gc.disable()
                 try:
-                    with torch.cuda.graph(graph):
+                    # thread_local: other threads of the process (e.g. the NCCL watchdog polling its events) must not
+                    # invalidate the capture
+                    with torch.cuda.graph(graph, capture_error_mode="thread_local"):
                         self._step_body(action, views, prev, results_out, pipelined=True)
                 finally:
                     if gc_was_enabled:
