@@ -517,7 +517,13 @@ def main():
     ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--impl", default="ours")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--envs", type=int, default=ENVS_PER_GPU,
+                    help="envs per GPU; anything but the default is an exploration run, not the headline workload")
     args = ap.parse_args()
+    if args.envs != ENVS_PER_GPU:
+        globals()["ENVS_PER_GPU"] = args.envs
+        globals()["K_SLABS"] = max(4, min(32, (32 * 4096) // args.envs))   # keep the cycled slabs > L2 but bounded
+        PPO_CFG["N"] = args.envs
     args.warmup = max(args.warmup, 3)
     # The contract is ONE JSON line on stdout.  Native libraries write there too (NCCL prints its version banner to fd 1
     # under NCCL_DEBUG=VERSION), so fd 1 is pointed at stderr for the run and the JSON line goes to the saved descriptor.
