@@ -52,6 +52,25 @@ struct EnvHandle {
 typedef B200LabEnvState Env;
 typedef B200LabSimView Sim;
 
+// Programmatic dependent launch (PDL): a kernel launched with the programmatic-stream-serialization attribute may start
+// while its predecessor in the stream is still running; it must not touch anything the predecessor writes before
+// pdl_wait() (griddepcontrol.wait: predecessor complete, its memory visible).  pdl_launch_dependents() in the predecessor
+// lets the scheduler place the successor's blocks as soon as SM resources free up, so the successor's launch latency,
+// parameter loads and predecessor-independent loads overlap the predecessor's tail.  Both are no-ops without the attribute.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+template <class... KArgs, class... Args>
+static cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr; cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kernel, KArgs(std::forward<Args>(args))...);
+}
+
 // ------------------------------------------------------------------------------------------------
 // process_action
 // ------------------------------------------------------------------------------------------------
@@ -95,6 +114,32 @@ __device__ __forceinline__ float tanhf_(float x) {
   float e = ex2_ftz(2.8853900817779268f * fabsf(x));   // exp(2|x|); overflow -> inf -> rcp -> 0 -> t = 1
   float t = fmaf(-2.0f, rcp_ftz(e + 1.0f), 1.0f);
   return copysignf(t, x);
+}
+
+// Two gate activations behind ONE reciprocal: 1/a and 1/b from r = 1/(a*b) (r*b, r*a).  The cell is MUFU-pipe bound
+// (ex2 + rcp per activation); pairing (input, forget), (output, tanh(cell gate)) and the tanh(c) of adjacent hidden units
+// takes a cell from 10 to 7.5 MUFU per unit.  Exponents are clamped at 2^60 so the product stays finite (the clamp moves
+// a sigmoid below 1e-18, far under the torque tolerance).
+#ifndef B200LAB_GATE_PAIR
+#define B200LAB_GATE_PAIR 1
+#endif
+__device__ __forceinline__ float gate_den(float x_scaled) { return 1.0f + ex2_ftz(fminf(x_scaled, 60.0f)); }
+__device__ __forceinline__ void sigmoid_pair(float x, float y, float& sx, float& sy) {
+  const float a = gate_den(-1.4426950408889634f * x), b = gate_den(-1.4426950408889634f * y);
+  const float r = rcp_ftz(a * b);
+  sx = r * b; sy = r * a;
+}
+__device__ __forceinline__ void sigmoid_tanh_pair(float x, float y, float& sx, float& ty) {
+  const float a = gate_den(-1.4426950408889634f * x), b = gate_den(2.8853900817779268f * fabsf(y));
+  const float r = rcp_ftz(a * b);
+  sx = r * b;
+  ty = copysignf(fmaf(-2.0f, r * a, 1.0f), y);
+}
+__device__ __forceinline__ void tanh_pair(float x, float y, float& tx, float& ty) {
+  const float a = gate_den(2.8853900817779268f * fabsf(x)), b = gate_den(2.8853900817779268f * fabsf(y));
+  const float r = rcp_ftz(a * b);
+  tx = copysignf(fmaf(-2.0f, r * b, 1.0f), x);
+  ty = copysignf(fmaf(-2.0f, r * a, 1.0f), y);
 }
 
 __device__ __forceinline__ float dc_motor_clip(float tau, float qd, float sat, float vlim, float elim) {
@@ -229,11 +274,27 @@ __device__ __forceinline__ float lstm_cells_const(const Net& net, float x0, floa
           acc = fma2(pack2(net.w2[o + 1 + in_dim + k].x, net.w2[o + 1 + in_dim + k].y), pack2(h[l][k], h[l][k]), acc);
         unpack2(acc, g4[2 * pr], g4[2 * pr + 1]);
       }
+#if B200LAB_GATE_PAIR
+      float ig, fg, gg, og;
+      sigmoid_pair(g4[0], g4[1], ig, fg);
+      sigmoid_tanh_pair(g4[3], g4[2], og, gg);
+      float cn = fmaf(fg, c[l][u], ig * gg);
+      c[l][u] = cn;
+      hn[u] = og;   // multiplied by tanh(c) below, two units per reciprocal
+    }
+#pragma unroll
+    for (int u = 0; u < H; u += 2) {
+      float t0, t1;
+      tanh_pair(c[l][u], c[l][u + 1], t0, t1);
+      hn[u] *= t0; hn[u + 1] *= t1;
+    }
+#else
       float ig = sigmoidf_(g4[0]), fg = sigmoidf_(g4[1]), gg = tanhf_(g4[2]), og = sigmoidf_(g4[3]);
       float cn = fmaf(fg, c[l][u], ig * gg);
       c[l][u] = cn;
       hn[u] = og * tanhf_(cn);
     }
+#endif
 #pragma unroll
     for (int k = 0; k < H; ++k) { h[l][k] = hn[k]; xin[k] = hn[k]; }
   }
@@ -526,6 +587,7 @@ decimation_fused_kernel(const __grid_constant__ Env env_param, const float* __re
                         const __grid_constant__ SimViews sv, int joint_blocks, int W, int envs_per_block,
                         const __grid_constant__ Net net) {
   const Env* __restrict__ e = &env_param;
+  pdl_launch_dependents();   // post_step may start its prologue under this kernel's tail (it waits before consuming)
   extern __shared__ float s_w[];
   const int N = e->N, J = e->J, B = e->B, A = e->A, S = sv.S;
   const float dt = e->physics_dt;
@@ -1029,21 +1091,20 @@ post_step_kernel(const __grid_constant__ Env env_param, Sim sim, int64_t step, c
   __syncthreads();
   const B200LabTerm* __restrict__ s_term = reinterpret_cast<const B200LabTerm*>(s_tab);
   const B200LabTerm* __restrict__ s_rew = s_term + e->num_term;
-  if (e->step_counter_dev) step = *e->step_counter_dev;
+  pdl_launch_dependents();   // compute_obs may be placed under this kernel's tail
   const int lane = threadIdx.x & 31;
   const int n = blockIdx.x * kStepWarps + (threadIdx.x >> 5);
   const int N = e->N, J = e->J, B = e->B, A = e->A;
-  if (n >= N) return;
+  if (n >= N) { pdl_wait(); return; }
   EnvCtx c;
   c.n = n; c.lane = lane;
+  // ---- loads of state the preceding kernel (decimation / sub-step) does not write: issued before the dependency wait
   float rs[13];
 #pragma unroll
   for (int k = 0; k < 13; ++k) rs[k] = sim.root_state_w[(int64_t)n * 13 + k];
-  load_rows(c, e, sim);
-  derive_state(c, rs);
   c.cmd = {0.f, 0.f, 0.f};
   if (e->has_command) c.cmd = {e->cmd_vel_b[n * 3], e->cmd_vel_b[n * 3 + 1], e->cmd_vel_b[n * 3 + 2]};
-  // Every per-env scalar the tail of the step reads is requested HERE, together with the rows above: the stores that
+  // Every per-env scalar the tail of the step reads is requested HERE, together with the rows below: the stores that
   // follow (no-alias cannot be proven) would otherwise serialise each of these loads behind an L2 round trip.
   float pre_mxy = 0.f, pre_myaw = 0.f, pre_tl = 0.f, pre_ht = 0.f;
   bool pre_ih = false, pre_is = false;
@@ -1056,16 +1117,24 @@ post_step_kernel(const __grid_constant__ Env env_param, Sim sim, int64_t step, c
 #pragma unroll
   for (int k = 0; k < B200LAB_MAX_INTERVAL_EVENTS; ++k) pre_itl[k] = k < e->num_interval ? e->ev_interval_time_left[k][n] : 0.f;
   const float pre_esum = lane < e->num_rew ? e->episode_sums[(int64_t)lane * N + n] : 0.f;
+  const int64_t pre_ep_len = e->episode_length_buf[n];
   bool pre_rc_flag = false;
   float pre_drift[3] = {0.f, 0.f, 0.f}, pre_rc_ts = 0.f;
   if (derived && e->rc_is_outdated) {
-    pre_rc_flag = e->rc_is_outdated[n] != 0;
-    pre_rc_ts = e->rc_timestamp[n];
 #pragma unroll
     for (int k = 0; k < 3; ++k) pre_drift[k] = e->rc_drift[n * 3 + k];
   }
+  derive_state(c, rs);
+  // ---- everything below reads what the preceding kernel wrote
+  pdl_wait();
+  if (e->step_counter_dev) step = *e->step_counter_dev;
+  load_rows(c, e, sim);
+  if (derived && e->rc_is_outdated) {
+    pre_rc_flag = e->rc_is_outdated[n] != 0;
+    pre_rc_ts = e->rc_timestamp[n];
+  }
   // -- episode counter (manager_based_rl_env.py:200)
-  int64_t ep_len = e->episode_length_buf[n] + 1;
+  int64_t ep_len = pre_ep_len + 1;
   // -- terminations (termination_manager.py:151-174)
   bool terminated = false, truncated = false;
   for (int t = 0; t < e->num_term; ++t) {
@@ -1388,7 +1457,8 @@ compute_obs_kernel(const __grid_constant__ Env env_param, Sim sim, int64_t step,
   const unsigned gid = n * D + k;
   const float* o = derived + (size_t)n * kDerived;
   const ObsCol* col = cols + k;
-  const float4 ca = __ldg(&col->a), cb = __ldg(&col->b);
+  const float4 ca = __ldg(&col->a), cb = __ldg(&col->b);   // static program: read before the dependency wait
+  pdl_wait();
   const unsigned w0 = __float_as_uint(ca.x);
   const int op = w0 & 0xffu, li = (w0 >> 8) & 0xffffu, kind = (w0 >> 24) & 0x3fu;
   float v = 0.f;
@@ -1840,8 +1910,12 @@ int b200lab_post_step(void* env, const B200LabSimView* sim, int64_t step_counter
   const size_t tab_bytes = (size_t)(s.num_term + s.num_rew) * sizeof(B200LabTerm);
   // a pending speculative scan is validated by the stand-alone derive kernel (it must be joined first)
   const bool fuse_derive = !h->spec_pending && s.obs_dim > 0;
-  post_step_kernel<<<(unsigned)ceil_div(s.N, kStepWarps), kStepWarps * 32, tab_bytes, (cudaStream_t)stream>>>(
-      h->host, *sim, step_counter, h->dev, fuse_derive ? h->derived : nullptr);
+  {
+    cudaError_t err = launch_pdl(post_step_kernel, dim3((unsigned)ceil_div(s.N, kStepWarps)), dim3(kStepWarps * 32), tab_bytes,
+                                 (cudaStream_t)stream, h->host, *sim, step_counter, (const Env*)h->dev,
+                                 fuse_derive ? h->derived : (float*)nullptr);
+    if (err != cudaSuccess) { set_error("post_step: %s", cudaGetErrorString(err)); return B200LAB_ERR_CUDA; }
+  }
   h->derived_root = fuse_derive ? sim->root_state_w : nullptr;
   count_launch();
   return check_launch("post_step");
@@ -1869,12 +1943,13 @@ int b200lab_compute_obs_range(void* env, const B200LabSimView* sim, int64_t step
   }
   int64_t total = (int64_t)cnt * s.obs_dim;
   if (total <= 0) return check_launch("compute_obs");
-  if (h->rays_vertical)
-    compute_obs_kernel<true><<<(unsigned)ceil_div(total, 256), 256, 0, st_>>>(
-        h->host, *sim, step_counter, h->cols, h->derived, h->mesh, h->has_mesh ? 1 : 0, h->spec_z, (unsigned)env_begin, (unsigned)cnt);
-  else
-    compute_obs_kernel<false><<<(unsigned)ceil_div(total, 256), 256, 0, st_>>>(
-        h->host, *sim, step_counter, h->cols, h->derived, h->mesh, h->has_mesh ? 1 : 0, h->spec_z, (unsigned)env_begin, (unsigned)cnt);
+  {
+    auto kern = h->rays_vertical ? compute_obs_kernel<true> : compute_obs_kernel<false>;
+    cudaError_t err = launch_pdl(kern, dim3((unsigned)ceil_div(total, 256)), dim3(256), 0, st_, h->host, *sim, step_counter,
+                                 (const ObsCol*)h->cols, (const float*)h->derived, h->mesh, h->has_mesh ? 1 : 0,
+                                 (const float*)h->spec_z, (unsigned)env_begin, (unsigned)cnt);
+    if (err != cudaSuccess) { set_error("compute_obs: %s", cudaGetErrorString(err)); return B200LAB_ERR_CUDA; }
+  }
   count_launch();
   return check_launch("compute_obs");
 }
