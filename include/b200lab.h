@@ -396,7 +396,10 @@ int b200lab_decimation_fused(void* env, const float* action_in, const B200LabSim
  * (manager_based_rl_env.py:198-236): episode_length_buf += 1, TerminationManager.compute,
  * RewardManager.compute, _reset_idx for the envs in reset_buf (masked, no host sync),
  * CommandManager.compute, interval events.  `step_counter` keys the Philox streams (perf mode) and is
- * env._sim_step_counter // decimation for the reset-event bookkeeping. */
+ * env._sim_step_counter // decimation for the reset-event bookkeeping.  * Stream ordering: b200lab_post_step and b200lab_compute_obs[_range] are launched with programmatic stream serialization;
+ * before the dependency on the preceding kernel of the stream is resolved they read only library-owned buffers that
+ * kernel cannot write (command state, episode sums, event timers, term/column tables) -- the caller's simulator tensors
+ * are read after it, so any kernel of the caller may directly precede them. */
 int b200lab_post_step(void* env, const B200LabSimView* sim, int64_t step_counter, void* stream);
 
 /* The `scene.write_data_to_sim()` that step() issues right after `_reset_idx` when ANY env was reset

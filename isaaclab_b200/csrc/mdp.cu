@@ -1098,10 +1098,9 @@ post_step_kernel(const __grid_constant__ Env env_param, Sim sim, int64_t step, c
   if (n >= N) { pdl_wait(); return; }
   EnvCtx c;
   c.n = n; c.lane = lane;
-  // ---- loads of state the preceding kernel (decimation / sub-step) does not write: issued before the dependency wait
-  float rs[13];
-#pragma unroll
-  for (int k = 0; k < 13; ++k) rs[k] = sim.root_state_w[(int64_t)n * 13 + k];
+  // ---- loads of LIBRARY-OWNED state that the preceding library kernel (decimation / sub-step) does not write: issued
+  // before the dependency wait.  The simulator's tensors (root state, joints, forces) belong to the caller, whose own
+  // kernel may be the predecessor on this stream: they are read after the wait.
   c.cmd = {0.f, 0.f, 0.f};
   if (e->has_command) c.cmd = {e->cmd_vel_b[n * 3], e->cmd_vel_b[n * 3 + 1], e->cmd_vel_b[n * 3 + 2]};
   // Every per-env scalar the tail of the step reads is requested HERE, together with the rows below: the stores that
@@ -1124,9 +1123,12 @@ post_step_kernel(const __grid_constant__ Env env_param, Sim sim, int64_t step, c
 #pragma unroll
     for (int k = 0; k < 3; ++k) pre_drift[k] = e->rc_drift[n * 3 + k];
   }
-  derive_state(c, rs);
   // ---- everything below reads what the preceding kernel wrote
   pdl_wait();
+  float rs[13];
+#pragma unroll
+  for (int k = 0; k < 13; ++k) rs[k] = sim.root_state_w[(int64_t)n * 13 + k];
+  derive_state(c, rs);
   if (e->step_counter_dev) step = *e->step_counter_dev;
   load_rows(c, e, sim);
   if (derived && e->rc_is_outdated) {
