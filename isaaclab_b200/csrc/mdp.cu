@@ -579,10 +579,13 @@ struct SimViews {
   int S;
 };
 
-constexpr int kFusedBlock = 128;   // 4 blocks / SM at <= 128 registers: the body-role blocks are pure memory latency
+#ifndef B200LAB_FUSED_THREADS
+#define B200LAB_FUSED_THREADS 128
+#endif
+constexpr int kFusedBlock = B200LAB_FUSED_THREADS;   // 512 threads / SM at <= 128 registers: the body-role blocks are pure memory latency
 
 template <class Net>
-__global__ void __launch_bounds__(kFusedBlock, 4)
+__global__ void __launch_bounds__(kFusedBlock, 512 / kFusedBlock)
 decimation_fused_kernel(const __grid_constant__ Env env_param, const float* __restrict__ action_in,
                         const __grid_constant__ SimViews sv, int joint_blocks, int W, int envs_per_block,
                         const __grid_constant__ Net net) {
@@ -1068,12 +1071,15 @@ __device__ __forceinline__ void derive_env(const Env* __restrict__ e, const floa
   o[18] = spec_ok;
 }
 
-constexpr int kStepWarps = 4;
+#ifndef B200LAB_STEP_WARPS
+#define B200LAB_STEP_WARPS 4
+#endif
+constexpr int kStepWarps = B200LAB_STEP_WARPS;
 #ifndef B200LAB_POST_BLOCKS
 #define B200LAB_POST_BLOCKS 6
 #endif
 
-__global__ void __launch_bounds__(kStepWarps * 32, B200LAB_POST_BLOCKS)
+__global__ void __launch_bounds__(kStepWarps * 32, B200LAB_POST_BLOCKS * 4 / kStepWarps)
 post_step_kernel(const __grid_constant__ Env env_param, Sim sim, int64_t step, const Env* __restrict__ env_dev,
                  float* __restrict__ derived) {
   const Env* __restrict__ e = &env_param;   // descriptor in the constant bank: warp-uniform reads, no global round trips
@@ -1447,7 +1453,10 @@ height_scan_spec_kernel(const __grid_constant__ Env env_param, Sim sim, const Ob
 #define B200LAB_OBS_BLOCKS 4
 #endif
 template <bool kVerticalRays>
-__global__ void __launch_bounds__(256, kVerticalRays ? B200LAB_OBS_BLOCKS : 2)
+#ifndef B200LAB_OBS_THREADS
+#define B200LAB_OBS_THREADS 64
+#endif
+__global__ void __launch_bounds__(B200LAB_OBS_THREADS, kVerticalRays ? B200LAB_OBS_BLOCKS * (256 / B200LAB_OBS_THREADS) : 2)
 compute_obs_kernel(const __grid_constant__ Env env_param, Sim sim, int64_t step, const ObsCol* __restrict__ cols,
                    const float* __restrict__ derived, const __grid_constant__ MeshAccel mesh, int has_mesh,
                    const float* __restrict__ spec_z, unsigned env_begin, unsigned env_count) {
@@ -1947,7 +1956,7 @@ int b200lab_compute_obs_range(void* env, const B200LabSimView* sim, int64_t step
   if (total <= 0) return check_launch("compute_obs");
   {
     auto kern = h->rays_vertical ? compute_obs_kernel<true> : compute_obs_kernel<false>;
-    cudaError_t err = launch_pdl(kern, dim3((unsigned)ceil_div(total, 256)), dim3(256), 0, st_, h->host, *sim, step_counter,
+    cudaError_t err = launch_pdl(kern, dim3((unsigned)ceil_div(total, B200LAB_OBS_THREADS)), dim3(B200LAB_OBS_THREADS), 0, st_, h->host, *sim, step_counter,
                                  (const ObsCol*)h->cols, (const float*)h->derived, h->mesh, h->has_mesh ? 1 : 0,
                                  (const float*)h->spec_z, (unsigned)env_begin, (unsigned)cnt);
     if (err != cudaSuccess) { set_error("compute_obs: %s", cudaGetErrorString(err)); return B200LAB_ERR_CUDA; }
