@@ -465,7 +465,7 @@ int b200lab_gae(const float* rewards, const float* values, const uint8_t* dones,
 typedef struct B200LabTransition {
   int32_t T, N, obs_dim, act_dim, t;
   float gamma;
-  const float* obs;          /* [N,obs_dim] */
+  const float* obs;          /* [N,obs_dim], or NULL when the caller has already stored the row of step t */
   const float* actions;      /* [N,A] */
   const float* rewards;      /* [N] */
   const uint8_t* dones;      /* [N] (u8) */

@@ -103,7 +103,8 @@ add_transition_kernel(B200LabTransition tr) {
   int64_t total_act = (int64_t)N * tr.act_dim;
   int64_t stride = (int64_t)gridDim.x * blockDim.x;
   size_t t = (size_t)tr.t;
-  for (int64_t i = n; i < total_obs; i += stride) tr.s_obs[t * total_obs + i] = tr.obs[i];
+  if (tr.obs)   // NULL: the caller already wrote the observation row of step t (PPO.act stores it before env.step)
+    for (int64_t i = n; i < total_obs; i += stride) tr.s_obs[t * total_obs + i] = tr.obs[i];
   for (int64_t i = n; i < total_act; i += stride) {
     tr.s_actions[t * total_act + i] = tr.actions[i];
     tr.s_mu[t * total_act + i] = tr.mu[i];

@@ -354,12 +354,14 @@ class ManagerBasedRLEnv:
                 gc_was_enabled = gc.isenabled()
                 gc.collect()
                 gc.disable()
+                host_counter = self.fused.step_counter   # the captured body advances it once; the replay below counts
                 try:
                     # thread_local: other threads of the process (e.g. the NCCL watchdog polling its events) must not
                     # invalidate the capture
                     with torch.cuda.graph(graph, capture_error_mode="thread_local"):
                         self._step_body(action, views, prev, results_out, pipelined=True)
                 finally:
+                    self.fused.step_counter = host_counter
                     if gc_was_enabled:
                         gc.enable()
                 self._graphs[key] = graph

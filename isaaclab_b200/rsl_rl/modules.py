@@ -284,9 +284,16 @@ class ActorCritic(nn.Module):
         return actions
 
     def act_inference(self, obs):
-        return self._a.forward(self.actor_input(obs), self.precision)
+        # public entry points return fresh tensors, as the reference does; the per-batch-size activation buffers
+        # (`_Net.buffers`) are reused by the next forward of the same batch size
+        return self._a.forward(self.actor_input(obs), self.precision).clone()
 
     def evaluate(self, obs, **kwargs):
+        return self._evaluate(obs).clone()
+
+    def _evaluate(self, obs):
+        """Zero-copy critic forward for PPO.act / compute_returns: the result is consumed (stored in the rollout slab)
+        before the next critic forward of the same batch size."""
         self._value = self._c.forward(self.critic_input(obs), self.precision)
         return self._value
 

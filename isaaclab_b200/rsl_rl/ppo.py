@@ -71,11 +71,15 @@ class PPO:
 
     def act(self, obs, eps=None):
         self.transition.actions = self.policy.act(obs, eps=eps)
-        self.transition.values = self.policy.evaluate(obs)
+        self.transition.values = self.policy._evaluate(obs)
         self.transition.actions_log_prob = self.policy.get_actions_log_prob(self.transition.actions)
         self.transition.action_mean = self.policy.action_mean
         self.transition.action_sigma = self.policy.action_std
+        # The reference keeps `obs` by reference until process_env_step (ppo.py:139) -- safe there because its
+        # ObservationManager returns a fresh tensor every step.  The fused env hands back the SAME observation buffer
+        # and overwrites it in env.step, so the row of step t is stored now, before the step.
         self.transition.observations = obs
+        self.transition.observations_stored = self.storage.store_observations(obs) if self.storage is not None else False
         return self.transition.actions
 
     def process_env_step(self, obs, rewards, dones, extras):
@@ -89,7 +93,7 @@ class PPO:
         self.policy.reset(dones)
 
     def compute_returns(self, obs):
-        last_values = self.policy.evaluate(obs)
+        last_values = self.policy._evaluate(obs)
         self.storage.compute_returns(last_values, self.gamma, self.lam,
                                      normalize_advantage=not self.normalize_advantage_per_mini_batch)
 

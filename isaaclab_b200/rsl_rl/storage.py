@@ -26,6 +26,7 @@ class RolloutStorage:
             self.action_sigma = None
             self.hidden_states = None
             self.time_outs = None  # b200 extension: fused bootstrap (ppo.py:161-164)
+            self.observations_stored = False  # the observation row of this step is already in the slab (PPO.act)
 
         def clear(self):
             self.__init__()
@@ -39,10 +40,8 @@ class RolloutStorage:
         self.num_envs = N = num_envs
         self.actions_shape = actions_shape
         keys = list(obs.keys())
-        if len(keys) != 1:
-            # several observation groups: keep one slab per group; the fused kernels act on the first one and
-            # the others are copied with torch (setup convenience, not the timed path)
-            pass
+        # several observation groups: one slab per group; the fused gather kernel moves the first one, the others are
+        # gathered per minibatch with one indexed copy each (mini_batch_generator)
         self._obs_key = keys[0]
         self.observations = TensorDict({k: torch.zeros(T, *obs[k].shape, device=device) for k in keys},
                                        batch_size=[T, N], device=device)
@@ -61,6 +60,16 @@ class RolloutStorage:
         self.step = 0
         self._gae_scratch = torch.zeros(max(1, _scratch_doubles(T, N)), dtype=torch.float64, device=device)
         self._mb = {}
+
+    def store_observations(self, obs) -> bool:
+        """Copies the observation of the CURRENT step into the slab (every group).  Called by `PPO.act`: the fused env
+        returns one persistent observation buffer that `env.step` overwrites, so the row has to be taken before the
+        step, not in `add_transitions` after it (rollout_storage.py:86 copies a tensor the reference env never reuses)."""
+        if self.step >= self.num_transitions_per_env:
+            raise OverflowError("Rollout buffer overflow! You should call clear() before adding new transitions.")
+        for k in self.observations.keys():
+            self.observations[k][self.step].copy_(obs[k])
+        return True
 
     def add_transitions(self, transition: "RolloutStorage.Transition", gamma: float = 0.0):
         if self.step >= self.num_transitions_per_env:
@@ -85,7 +94,8 @@ class RolloutStorage:
         obs_c, rew_c, dones_c = obs.contiguous(), transition.rewards.contiguous(), dones.contiguous()
         touts_c = touts.contiguous() if touts is not None else None
         lp_c = transition.actions_log_prob.contiguous()
-        tr.obs, tr.actions, tr.rewards = p(obs_c), p(transition.actions), p(rew_c)
+        stored = bool(getattr(transition, "observations_stored", False))
+        tr.obs, tr.actions, tr.rewards = (None if stored else p(obs_c)), p(transition.actions), p(rew_c)
         tr.dones, tr.time_outs, tr.values = p(dones_c), p(touts_c), p(transition.values)
         tr.log_prob, tr.mu, tr.sigma = p(lp_c), p(transition.action_mean), p(sigma)
         tr.s_obs, tr.s_actions, tr.s_rewards = p(self.observations[self._obs_key]), p(self.actions), p(self.rewards)
@@ -93,9 +103,10 @@ class RolloutStorage:
         tr.s_mu, tr.s_sigma = p(self.mu), p(self.sigma)
         import ctypes
         _lib.check(_lib.lib().b200lab_add_transition(ctypes.byref(tr), _lib.current_stream()))
-        for k in self.observations.keys():
-            if k != self._obs_key:
-                self.observations[k][self.step].copy_(transition.observations[k])
+        if not stored:
+            for k in self.observations.keys():
+                if k != self._obs_key:
+                    self.observations[k][self.step].copy_(transition.observations[k])
         self.step += 1
 
     def clear(self):
@@ -146,8 +157,13 @@ class RolloutStorage:
         indices = indices.to(device=self.device, dtype=torch.int64).contiguous()
         for _ in range(num_epochs):
             for i in range(num_mini_batches):
-                b = self.gather(indices[i * mini_batch_size:(i + 1) * mini_batch_size])
-                obs_batch = TensorDict({self._obs_key: b["obs"]}, batch_size=[mini_batch_size], device=self.device)
+                idx = indices[i * mini_batch_size:(i + 1) * mini_batch_size]
+                b = self.gather(idx)
+                groups = {self._obs_key: b["obs"]}
+                for k in self.observations.keys():   # further observation groups (e.g. an asymmetric critic's set)
+                    if k != self._obs_key:
+                        groups[k] = self.observations[k].flatten(0, 1)[idx]
+                obs_batch = TensorDict(groups, batch_size=[mini_batch_size], device=self.device)
                 yield (obs_batch, b["actions"], b["values"], b["advantages"], b["returns"], b["log_prob"], b["mu"],
                        b["sigma"], (None, None), None)
 

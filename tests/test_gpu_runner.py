@@ -120,3 +120,87 @@ def test_runner_learn_save_load(task, tmp_path, monkeypatch):
     assert a1.shape == (128, env2.num_actions) and torch.equal(a1, a2)
     r2.learn(1)  # resumes without a log dir: no files, no log read
     assert r2.current_learning_iteration == 2
+
+
+def test_rollout_stores_the_observation_act_saw(monkeypatch):
+    """the fused env returns ONE persistent observation buffer and overwrites it in `step`, so the
+    rollout slab must hold obs_t -- the observation `PPO.act` saw -- next to a_t / log_prob_t / mu_t / V_t, not obs_{t+1}.
+    Checked on the runner's own loop: storage.observations[t] == the tensor passed to act() at step t, and the policy
+    re-evaluated on the stored rows reproduces the stored mu / values / log-prob (importance ratio 1 before any update)."""
+    import copy
+    from isaaclab_b200.rsl_rl import OnPolicyRunner, RslRlVecEnvWrapper
+    from isaaclab_b200.rsl_rl.tensordict import TensorDict
+    monkeypatch.delenv("WORLD_SIZE", raising=False)
+    env = RslRlVecEnvWrapper(_make_env("Isaac-Velocity-Flat-Anymal-C-v0", 96))
+    runner = OnPolicyRunner(env, copy.deepcopy(TRAIN_CFG), log_dir=None, device="cuda")
+    alg, T = runner.alg, TRAIN_CFG["num_steps_per_env"]
+    obs = env.get_observations()
+    seen = []
+    for t in range(T):
+        seen.append(obs["policy"].clone())
+        actions = alg.act(obs)
+        obs, rew, dones, extras = env.step(actions)
+        assert not torch.equal(obs["policy"], seen[-1]), "env.step did not change the observation buffer"
+        alg.process_env_step(obs, rew, dones, extras)
+    st = alg.storage
+    for t in range(T):
+        assert torch.equal(st.observations["policy"][t], seen[t]), f"storage row {t} is not the observation act() saw"
+    pol = alg.policy
+    flat = TensorDict({"policy": st.observations["policy"].flatten(0, 1).contiguous()}, batch_size=[T * 96])
+    mu = pol.act_inference(flat)
+    val = pol.evaluate(flat)
+    torch.testing.assert_close(mu, st.mu.flatten(0, 1), rtol=1e-5, atol=1e-6)
+    torch.testing.assert_close(val, st.values.flatten(0, 1), rtol=1e-5, atol=1e-6)
+    sigma = pol.std.detach()
+    lp = (-((st.actions.flatten(0, 1) - mu) ** 2) / (2 * sigma ** 2) - torch.log(sigma) - 0.9189385332046727).sum(-1)
+    ratio = torch.exp(lp - st.actions_log_prob.flatten(0, 1).squeeze(-1))
+    torch.testing.assert_close(ratio, torch.ones_like(ratio), rtol=0, atol=2e-5)
+
+
+def test_policy_entry_points_return_fresh_tensors():
+    """act_inference / evaluate results must survive the next call with the same batch size."""
+    from isaaclab_b200.rsl_rl import ActorCritic
+    from isaaclab_b200.rsl_rl.tensordict import TensorDict
+    torch.manual_seed(0)
+    o1 = TensorDict({"policy": torch.randn(32, 10, device="cuda")}, batch_size=[32])
+    o2 = TensorDict({"policy": torch.randn(32, 10, device="cuda")}, batch_size=[32])
+    pol = ActorCritic(o1, {"policy": ["policy"], "critic": ["policy"]}, 3, actor_hidden_dims=[16], critic_hidden_dims=[16],
+                      device="cuda")
+    a1, v1 = pol.act_inference(o1), pol.evaluate(o1)
+    a1c, v1c = a1.clone(), v1.clone()
+    pol.act_inference(o2), pol.evaluate(o2)
+    assert torch.equal(a1, a1c) and torch.equal(v1, v1c)
+
+
+def test_asymmetric_critic_minibatches_carry_every_group():
+    """with obs_groups['critic'] = ['critic'] the minibatch TensorDict must hold both groups."""
+    from isaaclab_b200.rsl_rl import PPO, ActorCritic
+    from isaaclab_b200.rsl_rl.tensordict import TensorDict
+    N, T = 64, 4
+    g = torch.Generator(device="cuda").manual_seed(1)
+    mk = lambda: TensorDict({"policy": torch.randn(N, 9, device="cuda", generator=g),   # noqa: E731
+                             "critic": torch.randn(N, 14, device="cuda", generator=g)}, batch_size=[N])
+    obs = mk()
+    pol = ActorCritic(obs, {"policy": ["policy"], "critic": ["critic"]}, 3, actor_hidden_dims=[16], critic_hidden_dims=[16],
+                      device="cuda")
+    alg = PPO(pol, num_learning_epochs=1, num_mini_batches=2, device="cuda")
+    alg.init_storage("rl", N, T, obs, [3])
+    rows = []
+    for _ in range(T):
+        rows.append({k: obs[k].clone() for k in ("policy", "critic")})
+        alg.act(obs)
+        obs = mk()
+        alg.process_env_step(obs, torch.randn(N, device="cuda", generator=g), torch.zeros(N, dtype=torch.long, device="cuda"), {})
+    for t in range(T):
+        for k in ("policy", "critic"):
+            assert torch.equal(alg.storage.observations[k][t], rows[t][k])
+    alg.compute_returns(obs)
+    idx = torch.randperm(N * T, device="cuda")
+    for batch in alg.storage.mini_batch_generator(2, 1, indices=idx):
+        ob = batch[0]
+        assert set(ob.keys()) == {"policy", "critic"} and ob["critic"].shape == (N * T // 2, 14)
+        break
+    first = idx[: N * T // 2]
+    torch.testing.assert_close(ob["critic"], alg.storage.observations["critic"].flatten(0, 1)[first])
+    loss = alg.update(indices=idx)
+    assert all(torch.isfinite(torch.tensor(v)) for v in loss.values())
