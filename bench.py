@@ -208,7 +208,7 @@ def run_ours(args):
     from isaaclab_b200.envs.fused_env import FusedEnv
     from isaaclab_b200.envs.manager_based_rl_env import HostReplaySim, ManagerBasedRLEnv
     from isaaclab_b200.sim.synthetic import SyntheticSim
-    from tests.mdp_common import init_fused_state
+    from isaaclab_b200.sim.synthetic import init_fused_state
 
     cfg, spec, slabs, init = build_workload(dev, seed=rank)
     N = spec["N"]

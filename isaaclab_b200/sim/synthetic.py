@@ -59,6 +59,15 @@ def initial_env_state(spec: dict, seed: int) -> dict:
             "interval_time_left": torch.rand(N, generator=g) * 12.0}
 
 
+def init_fused_state(env, init):
+    """Loads `initial_env_state` into a FusedEnv (episode counters, command / interval timers)."""
+    env.episode_length_buf.copy_(init["episode_length_buf"])
+    if env.spec.get("command"):
+        env.cmd_time_left.copy_(init["cmd_time_left"])
+    for t in env.interval_time_left:
+        t.copy_(init["interval_time_left"])
+
+
 class SyntheticSim:
     """Device-resident slabs + SimViews.  `views(k)` -> (list of S sub-step views for env step k)."""
 

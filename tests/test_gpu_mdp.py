@@ -9,7 +9,8 @@ import pytest
 import torch
 
 from oracle.mdp_env import OracleEnv
-from tests.mdp_common import (draw_uniforms, init_fused_state, init_oracle_state, make_spec, slab_views_cpu)
+from tests.mdp_common import (close, draw_uniforms, exact, init_fused_state, init_oracle_state, make_spec,
+                              run_step_parity, slab_views_cpu)
 
 pytestmark = pytest.mark.gpu
 
@@ -17,97 +18,13 @@ TASKS = ["Isaac-Cartpole-v0", "Isaac-Velocity-Flat-Anymal-C-v0", "Isaac-Velocity
          "Isaac-Velocity-Rough-Unitree-Go1-v0", "Isaac-Velocity-Rough-H1-v0"]
 
 
-def close(a, b, name, rtol=1e-5, atol=1e-6):
-    torch.testing.assert_close(a.detach().cpu().float(), b.float(), rtol=rtol, atol=atol, msg=lambda m: f"{name}: {m}")
-
-
-def exact(a, b, name):
-    a, b = a.detach().cpu(), b
-    assert torch.equal(a.to(b.dtype), b), f"{name}: {(a.to(b.dtype) != b).sum().item()} mismatches"
-
-
 @pytest.mark.parametrize("fused", [True, False, "spec"], ids=["fused-decimation", "per-substep", "fused+speculative-scan"])
 @pytest.mark.parametrize("task", TASKS)
 def test_fused_step_matches_oracle(task, fused):
-    from isaaclab_b200.envs.fused_env import FusedEnv
-    from isaaclab_b200.sim.synthetic import SyntheticSim, generate_slabs, initial_env_state
     N, steps = (192, 6) if "Rough" in task else (384, 8)
     spec = make_spec(task, N)
-    slabs = generate_slabs(spec, steps + 1, seed=1234)
-    init = initial_env_state(spec, seed=5)
-    init["episode_length_buf"][::7] = spec["max_episode_length"] - 2  # force time-outs within the test horizon
-    orc = OracleEnv(copy.deepcopy(spec))
-    fus = FusedEnv(spec, device="cuda")
-    fus.speculative_scan = fused == "spec"   # height scan cast ahead on a side stream, reset envs recast (same results)
-    fused = bool(fused)
-    init_oracle_state(orc, init)
-    init_fused_state(fus, init)
-    sim = SyntheticSim(spec, K=steps + 1, device="cuda", slabs={k: v.clone() for k, v in slabs.items()})
-    us = draw_uniforms(steps, N, fus.n_u_reset, fus.n_u_step, fus.obs_dim, seed=99)
-    g = torch.Generator().manual_seed(3)
-    n_resets = n_resample = 0
-    prev_cpu, prev_gpu = slab_views_cpu(slabs, 0)[-1], sim.views(0)[-1]
-    for k in range(steps):
-        action = torch.randn(N, spec["A"], generator=g)
-        u_r, u_s, u_o = us[k]
-        views_cpu = slab_views_cpu(slabs, k + 1)
-        o_obs, o_rew, o_term, o_trunc = orc.step(action, views_cpu, u_r, u_s, u_o, prev_cpu)
-        ur, us_, uo = u_r.cuda(), u_s.cuda(), u_o.cuda()
-        fus.set_uniforms(ur, us_, uo)
-        f_obs, f_rew, f_term, f_trunc = fus.step(action.cuda(), sim.views(k + 1), prev_gpu, fused=fused)
-        torch.cuda.synchronize()
-        tag = f"{task} step {k}"
-        exact(f_term, o_term, tag + " terminated")
-        exact(f_trunc, o_trunc, tag + " truncated")
-        exact(fus.reset_buf, orc.reset_buf, tag + " reset_buf")
-        exact(fus.episode_length_buf, orc.episode_length_buf, tag + " episode_length_buf")
-        exact(fus.term_dones[:len(spec["terminations"])], orc.term_dones, tag + " term_dones")
-        close(f_rew, o_rew, tag + " reward")
-        close(fus.step_reward[:, :len(spec["rewards"])], orc.step_reward, tag + " step_reward", atol=2e-6)
-        close(fus.episode_sums[:len(spec["rewards"])], orc.episode_sums, tag + " episode_sums")
-        close(fus.computed_torque, orc.computed_torque, tag + " computed_torque", rtol=2e-5, atol=2e-5)
-        close(fus.applied_torque, orc.applied_torque, tag + " applied_torque", rtol=2e-5, atol=2e-5)
-        close(fus.joint_acc, orc.joint_acc, tag + " joint_acc", atol=1e-4)
-        close(fus.action, orc.action, tag + " action")
-        close(fus.prev_action, orc.prev_action, tag + " prev_action")
-        if spec.get("command"):
-            exact(fus.cmd_counter, orc.cmd_counter, tag + " command_counter (resample indices)")
-            exact(fus.cmd_is_heading, orc.cmd_is_heading, tag + " is_heading_env")
-            exact(fus.cmd_is_standing, orc.cmd_is_standing, tag + " is_standing_env")
-            close(fus.cmd_time_left, orc.cmd_time_left, tag + " time_left")
-            close(fus.cmd_vel_b, orc.cmd_vel_b, tag + " vel_command_b", atol=2e-6)
-            close(fus.cmd_heading_target, orc.cmd_heading_target, tag + " heading_target")
-            close(fus.cmd_metric_xy, orc.cmd_metric_xy, tag + " metric xy")
-            n_resample += len(orc.last_resample_ids)
-        if spec.get("contact"):
-            close(fus.cs_forces_hist, orc.cs_hist, tag + " force history")
-            for a, b in (("cs_last_air_time", "cs_last_air"), ("cs_current_air_time", "cs_cur_air"),
-                         ("cs_last_contact_time", "cs_last_contact"), ("cs_current_contact_time", "cs_cur_contact")):
-                close(getattr(fus, a), getattr(orc, b), tag + " " + a)
-        if spec.get("curriculum"):
-            exact(fus.terrain_levels, orc.terrain_levels, tag + " terrain_levels")
-            close(fus.env_origins, orc.env_origins, tag + " env_origins")
-        for i, t in enumerate(fus.interval_time_left):
-            close(t, orc.interval_time_left[i], tag + " interval time_left")
-        # simulator state written by reset / push events
-        close(sim.dev["root_state_w"][k + 1], views_cpu[-1]["root_state_w"], tag + " root_state_w after events", atol=2e-6)
-        close(sim.dev["joint_pos"][k + 1, -1], views_cpu[-1]["joint_pos"], tag + " joint_pos after events")
-        close(sim.dev["joint_vel"][k + 1, -1], views_cpu[-1]["joint_vel"], tag + " joint_vel after events")
-        if spec.get("raycaster"):
-            hz_f, hz_o = fus.rc_ray_hits_w[..., 2].cpu(), orc.rc_hits[..., 2]
-            bad = ~(((hz_f - hz_o).abs() <= 1e-4) | (torch.isinf(hz_f) & torch.isinf(hz_o)))
-            assert bad.sum().item() == 0, f"{tag}: {bad.sum().item()} ray hits differ by more than 1e-4 m"
-            close(fus.rc_drift, orc.rc_drift, tag + " drift")
-        close(f_obs, o_obs, tag + " obs", rtol=1e-5, atol=1e-4 if spec.get("raycaster") else 2e-6)
-        if spec.get("raycaster"):
-            D = fus.obs_dim - spec["R"]
-            close(f_obs[:, :D], o_obs[:, :D], tag + " obs (proprioceptive part)", atol=2e-6)
-        n_resets += int(orc.reset_buf.sum())
-        prev_cpu, prev_gpu = views_cpu[-1], sim.views(k + 1)[-1]
+    _, _, n_resets, _ = run_step_parity(spec, steps, fused=bool(fused), speculative=fused == "spec", tag=task)
     assert n_resets > 0, "test horizon produced no resets"
-    for st_f, st_o in zip(fus.act_state, orc.act_state):
-        for key in st_f:
-            close(st_f[key], st_o[key], f"{task} actuator state {key}", rtol=1e-4, atol=1e-5)
 
 
 class _AsOracle:
