@@ -202,8 +202,9 @@ void b200lab_mesh_destroy(void* mesh) {
 int b200lab_raycast_mesh(void* mesh, const float* ray_starts, const float* ray_dirs, int64_t n, float max_dist,
                          float* ray_hits, float* ray_distance, float* ray_normal, int32_t* ray_face_id,
                          void* stream) {
-  B200LAB_CHECK_ARG(mesh && ray_starts && ray_dirs && ray_hits, "null argument");
-  if (n == 0) return B200LAB_OK;
+  B200LAB_CHECK_ARG(mesh && n >= 0, "null mesh / negative ray count");
+  if (n == 0) return B200LAB_OK;   // empty batch: the tensors of an empty batch have no storage (NULL pointers)
+  B200LAB_CHECK_ARG(ray_starts && ray_dirs && ray_hits, "null argument");
   MeshHandle* h = (MeshHandle*)mesh;
   raycast_mesh_kernel<<<(unsigned)ceil_div(n, 256), 256, 0, (cudaStream_t)stream>>>(
       h->dev, ray_starts, ray_dirs, n, max_dist, ray_hits, ray_distance, ray_normal, ray_face_id);
