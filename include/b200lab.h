@@ -460,6 +460,21 @@ int b200lab_gae(const float* rewards, const float* values, const uint8_t* dones,
                 float* returns, float* advantages, int32_t T, int32_t N, float gamma, float lam,
                 int32_t normalize_advantage, void* scratch, void* stream);
 
+/* b200lab_gae WITHOUT caller scratch and without any allocation.  No counterpart in the reference: added
+ * for callers that cannot allocate (code under CUDA-graph capture, tight serving loops, harnesses
+ * that forbid cudaMalloc).  Same kernels, launch geometry and results (bitwise) as b200lab_gae; the per-CTA partial sums
+ * live in a file-scope `static __device__` array inside the library: 2 * (B200LAB_GAE_STATIC_MAX_ENVS / 64) + 2 doubles
+ * = 64 KB, held by every GPU that loads the library until the process exits.  N > B200LAB_GAE_STATIC_MAX_ENVS is rejected
+ * with B200LAB_ERR_ARG.  The call makes no cudaMalloc / cudaFree / allocating library call; the first call on a device
+ * resolves the array's device address (cudaGetSymbolAddress, with that device current) -- make it once before capturing.
+ * EVERY call on a device shares the one array and it keeps the previous call's contents (nothing needs clearing: each
+ * call overwrites the slots it reads), so two calls that overlap on the GPU -- different streams, or graphs replayed
+ * concurrently -- RACE on it: serialise them, or use b200lab_gae with separate scratch buffers. */
+#define B200LAB_GAE_STATIC_MAX_ENVS 262144
+int b200lab_gae_static(const float* rewards, const float* values, const uint8_t* dones, const float* last_values,
+                       float* returns, float* advantages, int32_t T, int32_t N, float gamma, float lam,
+                       int32_t normalize_advantage, void* stream);
+
 /* PPO.process_env_step time-out bootstrap + RolloutStorage.add_transitions (RSL/algorithms/ppo.py:142-169,
  * rollout_storage.py:77-103) for one step `t` of the [T,N,.] slabs. */
 typedef struct B200LabTransition {

@@ -197,6 +197,36 @@ gather_minibatch_kernel(B200LabGather g) {
   }
 }
 
+// ---- library-owned scratch for b200lab_gae_static (no allocation anywhere on that path) ----
+// File-scope device array: every GPU that loads the library holds these 64 KB until the process exits.  The name is a
+// HOST-SIDE STAND-IN in host code, not a device address -- the address a kernel may be given comes from
+// cudaGetSymbolAddress, resolved once per device with that device current (gae_static_scratch below).
+constexpr int kGaeStaticMaxEnvs = B200LAB_GAE_STATIC_MAX_ENVS;
+constexpr int kGaeStaticDoubles = 2 * (kGaeStaticMaxEnvs / kGaeBlock) + 2;
+static_assert(kGaeStaticMaxEnvs % kGaeBlock == 0, "B200LAB_GAE_STATIC_MAX_ENVS must be a multiple of the GAE block");
+static __device__ __align__(256) double g_gae_static_scratch[kGaeStaticDoubles];
+
+constexpr int kGaeStaticMaxDevices = 64;
+static double* g_gae_static_ptr[kGaeStaticMaxDevices];   // per-device address of the array, resolved on first use
+
+static int gae_static_scratch(double** out) {
+  int dev = -1;
+  cudaError_t err = cudaGetDevice(&dev);
+  if (err != cudaSuccess) { set_error("b200lab_gae_static: cudaGetDevice: %s", cudaGetErrorString(err)); return B200LAB_ERR_CUDA; }
+  if (dev < 0 || dev >= kGaeStaticMaxDevices) { set_error("b200lab_gae_static: device index %d out of range", dev); return B200LAB_ERR_ARG; }
+  if (!g_gae_static_ptr[dev]) {
+    double* p = nullptr;
+    err = cudaGetSymbolAddress((void**)&p, g_gae_static_scratch);
+    if (err != cudaSuccess || !p) {
+      set_error("b200lab_gae_static: cudaGetSymbolAddress: %s", cudaGetErrorString(err));
+      return B200LAB_ERR_CUDA;
+    }
+    g_gae_static_ptr[dev] = p;
+  }
+  *out = g_gae_static_ptr[dev];
+  return B200LAB_OK;
+}
+
 }  // namespace b200lab
 
 using namespace b200lab;
@@ -226,6 +256,38 @@ int b200lab_gae(const float* rewards, const float* values, const uint8_t* dones,
     gae_normalize_kernel<<<nb, 256, 0, s>>>(advantages, total, (const double*)scratch, blocks);
     count_launch();
     rc = check_launch("gae_normalize");
+  }
+  return rc;
+}
+
+int b200lab_gae_static(const float* rewards, const float* values, const uint8_t* dones, const float* last_values,
+                       float* returns, float* advantages, int32_t T, int32_t N, float gamma, float lam,
+                       int32_t normalize_advantage, void* stream) {
+  B200LAB_CHECK_ARG(T > 0 && N > 0, "T and N must be positive");
+  if (N > kGaeStaticMaxEnvs) {
+    set_error("b200lab_gae_static: N = %d exceeds B200LAB_GAE_STATIC_MAX_ENVS = %d (the library-owned scratch is fixed-size; "
+              "use b200lab_gae with caller scratch)", (int)N, kGaeStaticMaxEnvs);
+    return B200LAB_ERR_ARG;
+  }
+  B200LAB_CHECK_ARG(rewards && values && dones && last_values && returns && advantages, "null pointer");
+  double* scratch = nullptr;
+  int rc = gae_static_scratch(&scratch);
+  if (rc) return rc;
+  // Same two kernels, same launch geometry as b200lab_gae => bitwise the same results.  Nothing in the scratch has to
+  // start at zero: gae_scan_kernel overwrites partial slots [0, 2*blocks) and gae_normalize_kernel reads exactly those.
+  cudaStream_t s = (cudaStream_t)stream;
+  int blocks = (int)ceil_div(N, kGaeBlock);
+  gae_scan_kernel<<<blocks, kGaeBlock, 0, s>>>(rewards, values, dones, last_values, returns, advantages, T, N,
+                                               gamma, lam, scratch);
+  count_launch();
+  rc = check_launch("gae_scan (static scratch)");
+  if (rc) return rc;
+  if (normalize_advantage) {
+    int64_t total = (int64_t)T * N;
+    int nb = (int)min64(ceil_div(total, 256 * 4), 4 * kNumSMs);
+    gae_normalize_kernel<<<nb, 256, 0, s>>>(advantages, total, (const double*)scratch, blocks);
+    count_launch();
+    rc = check_launch("gae_normalize (static scratch)");
   }
   return rc;
 }
