@@ -17,16 +17,30 @@
 
 namespace b200lab {
 
+// Triangle order.  Triangles are RE-ORDERED at build time so that a patch of terrain is a few contiguous runs of
+// records (the fused height scan stages the patch under an env in shared memory with coalesced loads, mdp.cu):
+// a triangle whose conservative cell range spans at most kHomeMargin+1 cells in x and in y is "small"; small triangles
+// are sorted by their HOME cell (the min corner of that range, row-major) and `home_start` is the CSR over home cells.
+// Every small triangle overlapping cell (cx, cy) has its home in [cx-kHomeMargin, cx] x [cy-kHomeMargin, cy].  The
+// remaining ("large") triangles follow, ids >= first_large.  `orig_face` maps the sorted id back to the caller's face
+// index (ray_face_id).  A `cell_tris` entry is  id | dy << kEntryShift  with dy = cy - home row (0 for large triangles).
+constexpr int kHomeMargin = 3;
+constexpr int kEntryShift = 28;
+constexpr int kEntryIdMask = (1 << kEntryShift) - 1;
+
 struct MeshAccel {
   float ox, oy;          // grid origin (min corner)
   float cell, inv_cell;  // cell edge
   int nx, ny;
   const int* cell_start;   // [nx*ny + 1]
-  const int* cell_tris;    // [entries] triangle ids
-  const float4* rec;       // [F, 3] packed records (see above)
-  const float* tris;       // [F, 9] original v0 v1 v2 (fp64 re-checks, normals)
+  const int* cell_tris;    // [entries] triangle ids (sorted order) | dy << 28
+  const float4* rec;       // [F, 3] packed records (see above), sorted order; rec[3f+2].z carries the sorted id's bits
+  const float* tris;       // [F, 9] original v0 v1 v2 (fp64 re-checks, normals), sorted order
   int num_faces;
   float zmin, zmax;
+  const int* home_start;   // [nx*ny + 1] CSR of the small triangles over their home cells
+  const int* orig_face;    // [F] sorted id -> face index of the mesh as passed to b200lab_mesh_create
+  int first_large;         // ids >= first_large are large triangles (not covered by home_start)
 };
 
 // fp64 Moeller-Trumbore on the original vertices (rare: borderline barycentrics only).  Returns t or -1.
@@ -123,7 +137,7 @@ __device__ __forceinline__ bool raycast_vertical(const MeshAccel& m, f3 o, float
     for (int k = s; k < e; k += kVertBatch) {
       int f[kVertBatch];
 #pragma unroll
-      for (int i = 0; i < kVertBatch; ++i) f[i] = __ldg(m.cell_tris + min(k + i, e - 1));
+      for (int i = 0; i < kVertBatch; ++i) f[i] = __ldg(m.cell_tris + min(k + i, e - 1)) & kEntryIdMask;
       float4 ra[kVertBatch], rb[kVertBatch], rc[kVertBatch];
 #pragma unroll
       for (int i = 0; i < kVertBatch; ++i) {
@@ -146,7 +160,7 @@ __device__ __forceinline__ void test_cell(const MeshAccel& m, int cx, int cy, f3
   int c = cy * m.nx + cx;
   int s = __ldg(m.cell_start + c), e = __ldg(m.cell_start + c + 1);
   for (int k = s; k < e; ++k) {
-    int f = __ldg(m.cell_tris + k);
+    int f = __ldg(m.cell_tris + k) & kEntryIdMask;
     float t = ray_tri(m, f, o, d);
     if (t > 0.0f && t <= t_best) { t_best = t; face_best = f; }
   }
