@@ -10,6 +10,7 @@
 // Memory: everything is env-major fp32 as the reference keeps it; each warp / thread group touches contiguous
 // per-env rows so every sector read is fully used.  Compiled with -fmad=false (bit-exact masks); the tiny
 // actuator nets use explicit fmaf().
+#include <climits>
 #include <cstdlib>
 #include <cstring>
 #include <vector>
@@ -25,6 +26,7 @@ struct EnvHandle {
   B200LabEnvState* dev;   // device copy (kept for callers that want the descriptor on the device)
   float* derived;      // [N, kDerived] per-env derived state for compute_obs
   bool rays_vertical;  // all ray directions are (0,0,dz), dz != 0, and the sensor is yaw-only
+  int obs_impl;        // 0 (default): per-ray kernel; 1: staged height scan (compute_obs_patch_kernel), opt-in via B200LAB_OBS_IMPL
   struct ObsCol* cols; // [obs_dim] per-column program of the observation group (compute_obs_kernel)
   MeshAccel mesh;      // host copy of the ray-caster mesh descriptor (passed by value to compute_obs)
   bool has_mesh;
@@ -1449,6 +1451,9 @@ height_scan_spec_kernel(const __grid_constant__ Env env_param, Sim sim, const Ob
 // env_create, the env-level quantities from the derived scratch.  Height-scan columns cast their ray.
 // ------------------------------------------------------------------------------------------------
 
+__device__ __forceinline__ float obs_finish(const Env* __restrict__ e, float v, float4 ca, float4 cb, unsigned w0, int kind,
+                                            int64_t step, unsigned n, unsigned k, unsigned gid);
+
 #ifndef B200LAB_OBS_BLOCKS
 #define B200LAB_OBS_BLOCKS 4
 #endif
@@ -1487,7 +1492,7 @@ compute_obs_kernel(const __grid_constant__ Env env_param, Sim sim, int64_t step,
     case B200LAB_OBS_EXTERNAL: v = e->ext_values[((size_t)__float_as_int(cb.w) + li) * N + n]; break;
     case B200LAB_OBS_HEIGHT_SCAN: {
       float pz = o[11], hz;
-      float* hp = e->rc_ray_hits_w + ((size_t)n * e->R + li) * 3;
+      float* hp = e->rc_ray_hits_w ? e->rc_ray_hits_w + ((size_t)n * e->R + li) * 3 : nullptr;
       if (o[17] != 0.f) {
         // ray start = quat_apply(_yaw)(q, local start) + pos ; directions unrotated when attach_yaw_only (ray_caster.py:243-253)
         const float4 cc = __ldg(&col->c);
@@ -1511,16 +1516,21 @@ compute_obs_kernel(const __grid_constant__ Env env_param, Sim sim, int64_t step,
           if (has_mesh && raycast_mesh_dev(mesh, st, dr, e->rc_max_distance, tt, face))
             hit = {st.x + tt * dr.x, st.y + tt * dr.y, st.z + tt * dr.z};
         }
-        hp[0] = hit.x; hp[1] = hit.y; hp[2] = hit.z;
+        if (hp) { hp[0] = hit.x; hp[1] = hit.y; hp[2] = hit.z; }
         hz = hit.z;
       } else {
-        hz = hp[2];
+        hz = hp ? hp[2] : INFINITY;   // the host drops the hit buffer only for sensors that are outdated at every compute
       }
       v = (pz - hz) - cb.z;  // observations.py:173
       break;
     }
   }
-  // noise -> clip -> scale (observation_manager.py:313-318)
+  e->obs_buf[gid] = obs_finish(e, v, ca, cb, w0, kind, step, n, k, gid);
+}
+
+// noise -> clip -> scale of one observation element (observation_manager.py:313-318)
+__device__ __forceinline__ float obs_finish(const Env* __restrict__ e, float v, float4 ca, float4 cb, unsigned w0, int kind,
+                                            int64_t step, unsigned n, unsigned k, unsigned gid) {
   if (kind != B200LAB_NOISE_NONE) {
     const float noise_lo = ca.y, noise_span = ca.z;
     if (e->step_counter_dev) step = *e->step_counter_dev;
@@ -1549,8 +1559,295 @@ compute_obs_kernel(const __grid_constant__ Env env_param, Sim sim, int64_t step,
   }
   if (w0 & (1u << 30)) v = fminf(fmaxf(v, cb.x), cb.y);
   if (w0 & (1u << 31)) v = v * ca.w;
-  e->obs_buf[gid] = v;
+  return v;
 }
+
+// ------------------------------------------------------------------------------------------------
+// compute_obs, STAGED variant: the height scan of one env runs out of shared memory.
+//
+// One CTA per env.  The 187 rays of an env land in a ~1.6 x 1.0 m yaw-rotated footprint, i.e. a few dozen rows of the
+// mesh's cell grid.  Instead of every ray walking  cell range -> triangle ids -> records  through three dependent,
+// fully divergent L1/L2 requests (the per-ray kernel above), the CTA
+//   A. computes its rays' cells and, per grid row, the span of cells they touch (shared-memory atomics),
+//   B. stages, with coalesced loads, (1) the `cell_start` values of those spans, (2) the entry lists of those cells,
+//      translated on the fly into shared-memory record slots, and (3) the packed records of every small triangle whose
+//      home cell can overlap the spans -- triangles are sorted by home cell at build time (raycast.cuh), so this is one
+//      contiguous run per grid row;
+//   C. runs the unchanged per-ray test (same candidates, same arithmetic => bitwise the per-ray kernel's hits) against
+//      shared memory.  Entries that were not staged (large triangles, capacity overflow) fall back to the global record.
+// The proprioceptive columns ride in the same CTA; the observation row is written coalesced.
+// ------------------------------------------------------------------------------------------------
+constexpr int kPatchThreads = 256;
+#ifndef B200LAB_PATCH_REC
+#define B200LAB_PATCH_REC 704
+#endif
+#ifndef B200LAB_PATCH_BLOCKS
+#define B200LAB_PATCH_BLOCKS 4
+#endif
+constexpr int kPatchRec = B200LAB_PATCH_REC;   // staged records (48 B each)
+constexpr int kPatchIds = 2816;                // staged cell entries
+constexpr int kPatchCs = 2048;                 // staged cell_start values
+constexpr int kPatchRows = 56;                 // grid rows under one footprint (<= 64: two per lane of one warp)
+constexpr int kPatchHRows = kPatchRows + kHomeMargin;
+constexpr int kPatchMaxCols = 2;               // observation columns per thread (obs_dim <= 512)
+
+struct PatchSmem {
+  float4 rec[kPatchRec * 3];
+  int ids[kPatchIds];
+  int cs[kPatchCs];
+  int row_xmin[kPatchRows], row_xmax[kPatchRows];
+  int row_cs_off[kPatchRows];     // offset in cs[] of the row's span; -1: row not staged
+  int row_cs_end[kPatchRows];     // end offset (== start for a row that is not staged)
+  int row_ids_off[kPatchRows];    // offset in ids[] of the row's first entry
+  int row_ids_end[kPatchRows];
+  int row_ids_base[kPatchRows];   // index in mesh.cell_tris of that entry
+  int hrow_h0[kPatchHRows], hrow_h1[kPatchHRows], hrow_off[kPatchHRows];   // staged id range / first slot per home row
+  int ymin, ymax;
+  int tot_rec, tot_cs, tot_ids;   // staged item counts (flat staging loops)
+};
+
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"((unsigned)__cvta_generic_to_shared(smem_dst)), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async4(void* smem_dst, const void* gsrc) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((unsigned)__cvta_generic_to_shared(smem_dst)), "l"(gsrc) : "memory");
+}
+
+__device__ __forceinline__ int warp_excl_scan(int v, int lane, int& total) {
+  int incl = v;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    int t = __shfl_up_sync(0xffffffffu, incl, d);
+    if (lane >= d) incl += t;
+  }
+  total = __shfl_sync(0xffffffffu, incl, 31);
+  return incl - v;
+}
+
+template <int kCols>   // observation columns per thread: 1 for obs_dim <= 256 (half the live registers), else 2
+__global__ void __launch_bounds__(kPatchThreads, B200LAB_PATCH_BLOCKS)
+compute_obs_patch_kernel(const __grid_constant__ Env env_param, Sim sim, int64_t step, const ObsCol* __restrict__ cols,
+                         const float* __restrict__ derived, const __grid_constant__ MeshAccel mesh, unsigned env_begin) {
+  extern __shared__ __align__(16) unsigned char patch_smem_raw[];
+  PatchSmem& S = *reinterpret_cast<PatchSmem*>(patch_smem_raw);
+  const Env* __restrict__ e = &env_param;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const unsigned n = env_begin + blockIdx.x;
+  const unsigned N = (unsigned)e->N, D = (unsigned)e->obs_dim;
+  const float* o = derived + (size_t)n * kDerived;
+  // static per-column programs: read before the dependency wait
+  float4 ca[kCols], cb[kCols], cc[kCols];
+#pragma unroll
+  for (int s = 0; s < kCols; ++s) {
+    const unsigned k = tid + s * kPatchThreads;
+    ca[s] = cb[s] = cc[s] = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (k < D) { ca[s] = __ldg(&cols[k].a); cb[s] = __ldg(&cols[k].b); cc[s] = __ldg(&cols[k].c); }
+  }
+  if (tid == 0) { S.ymin = INT_MAX; S.ymax = INT_MIN; S.tot_rec = S.tot_cs = S.tot_ids = 0; }
+  if (tid < kPatchRows) { S.row_xmin[tid] = INT_MAX; S.row_xmax[tid] = INT_MIN; S.row_cs_off[tid] = -1; }
+  __syncthreads();
+  pdl_wait();
+  // ---- A: ray starts and their cells
+  const bool outdated = o[17] != 0.f;
+  const float pos_x = o[9], pos_y = o[10], pos_z = o[11];
+  const f4 qy{o[12], o[13], o[14], o[15]};
+  f3 st[kCols];
+  int cx[kCols], cy[kCols];
+  bool is_ray[kCols], in_grid[kCols];
+#pragma unroll
+  for (int s = 0; s < kCols; ++s) {
+    const unsigned k = tid + s * kPatchThreads;
+    const int op = __float_as_uint(ca[s].x) & 0xffu;
+    is_ray[s] = k < D && op == B200LAB_OBS_HEIGHT_SCAN && outdated;
+    in_grid[s] = false;
+    cx[s] = cy[s] = 0;
+    st[s] = f3{0.f, 0.f, 0.f};
+    if (is_ray[s]) {
+      // ray start = quat_apply_yaw(q, local start) + pos (ray_caster.py:243-253); same expressions as the per-ray kernel
+      f3 p = quat_apply(qy, f3{cc[s].x, cc[s].y, cc[s].z});
+      p.x += pos_x; p.y += pos_y; p.z += pos_z;
+      st[s] = p;
+      cx[s] = (int)floorf((p.x - mesh.ox) * mesh.inv_cell);
+      cy[s] = (int)floorf((p.y - mesh.oy) * mesh.inv_cell);
+      in_grid[s] = cx[s] >= 0 && cy[s] >= 0 && cx[s] < mesh.nx && cy[s] < mesh.ny;
+    }
+  }
+  {
+    int lo = INT_MAX, hi = INT_MIN;
+#pragma unroll
+    for (int s = 0; s < kCols; ++s)
+      if (in_grid[s]) { lo = min(lo, cy[s]); hi = max(hi, cy[s]); }
+    lo = __reduce_min_sync(0xffffffffu, lo);
+    hi = __reduce_max_sync(0xffffffffu, hi);
+    if (lane == 0 && lo <= hi) { atomicMin(&S.ymin, lo); atomicMax(&S.ymax, hi); }
+  }
+  __syncthreads();
+  const int ry0 = S.ymin;
+  const int nrows = S.ymax >= ry0 ? S.ymax - ry0 + 1 : 0;
+  const bool staged = nrows > 0 && nrows <= kPatchRows;
+  if (staged) {
+#pragma unroll
+    for (int s = 0; s < kCols; ++s)
+      if (in_grid[s]) { atomicMin(&S.row_xmin[cy[s] - ry0], cx[s]); atomicMax(&S.row_xmax[cy[s] - ry0], cx[s]); }
+  }
+  __syncthreads();
+  // ---- B1: per-row spans -> global ranges and shared-memory offsets (warp 0: cell rows, warp 1: home rows).
+  // Offsets are the raw exclusive scans; a row that would overflow the staging area keeps count 0 (its rays take the
+  // global path), which leaves a hole in the item index space that the flat loops below skip.
+  if (staged && warp == 0) {
+    int carry_ids = 0, carry_cs = 0;
+#pragma unroll
+    for (int half = 0; half < 2; ++half) {
+      const int r = lane + 32 * half;
+      int nids = 0, ncs = 0, a = 0;
+      if (r < nrows) {
+        const int x0 = S.row_xmin[r], x1 = S.row_xmax[r];
+        if (x0 <= x1) {
+          const int base = (ry0 + r) * mesh.nx;
+          a = __ldg(mesh.cell_start + base + x0);
+          nids = __ldg(mesh.cell_start + base + x1 + 1) - a;
+          ncs = x1 - x0 + 2;
+        }
+      }
+      int tot_ids, tot_cs;
+      const int off_ids = carry_ids + warp_excl_scan(nids, lane, tot_ids);
+      const int off_cs = carry_cs + warp_excl_scan(ncs, lane, tot_cs);
+      carry_ids += tot_ids; carry_cs += tot_cs;
+      if (r < kPatchRows) {
+        const bool ok = r < nrows && ncs > 0 && off_ids + nids <= kPatchIds && off_cs + ncs <= kPatchCs;
+        S.row_cs_off[r] = ok ? off_cs : -1;
+        S.row_cs_end[r] = off_cs + (ok ? ncs : 0);
+        S.row_ids_off[r] = off_ids;
+        S.row_ids_end[r] = off_ids + (ok ? nids : 0);
+        S.row_ids_base[r] = a;
+      }
+    }
+    if (lane == 0) { S.tot_ids = min(carry_ids, kPatchIds); S.tot_cs = min(carry_cs, kPatchCs); }
+  } else if (staged && warp == 1) {
+    int carry = 0;
+    const int nh = nrows + kHomeMargin;
+#pragma unroll
+    for (int half = 0; half < 2; ++half) {
+      const int t = lane + 32 * half;     // home row ry0 - kHomeMargin + t serves cell rows t-kHomeMargin .. t
+      int h0 = 0, cnt = 0;
+      if (t < nh) {
+        int hx0 = INT_MAX, hx1 = INT_MIN;
+        for (int r = max(t - kHomeMargin, 0); r <= min(t, nrows - 1); ++r) {
+          const int x0 = S.row_xmin[r], x1 = S.row_xmax[r];
+          if (x0 <= x1) { hx0 = min(hx0, x0 - kHomeMargin); hx1 = max(hx1, x1); }
+        }
+        const int hr = ry0 - kHomeMargin + t;
+        if (hx0 <= hx1 && hr >= 0 && hr < mesh.ny) {
+          hx0 = max(hx0, 0);
+          const int base = hr * mesh.nx;
+          h0 = __ldg(mesh.home_start + base + hx0);
+          cnt = __ldg(mesh.home_start + base + hx1 + 1) - h0;
+        }
+      }
+      int tot;
+      const int off = carry + warp_excl_scan(cnt, lane, tot);
+      carry += tot;
+      if (t < kPatchHRows) {
+        if (t >= nh || off + cnt > kPatchRec) cnt = 0;   // capacity: the row's triangles stay in global memory
+        S.hrow_h0[t] = h0; S.hrow_h1[t] = h0 + cnt; S.hrow_off[t] = off;
+      }
+    }
+    if (lane == 0) S.tot_rec = min(carry, kPatchRec);
+  }
+  __syncthreads();
+  // ---- B2: stage with cp.async (global -> shared without a register round trip): a warp owns rows round-robin and
+  // issues the copies of ALL its rows back to back -- nothing here waits on a load, so every structure costs the CTA one
+  // L2 round trip.  Cell entries are staged raw; they are translated to record slots where they are used (stage C).
+  if (staged) {
+    const int nh = nrows + kHomeMargin;
+    for (int t = warp; t < nh; t += kPatchThreads / 32) {
+      const int h0 = S.hrow_h0[t], n3 = (S.hrow_h1[t] - h0) * 3;
+      const float4* src = mesh.rec + (size_t)h0 * 3;
+      float4* dst = S.rec + S.hrow_off[t] * 3;
+      for (int i = lane; i < n3; i += 32) cp_async16(dst + i, src + i);
+    }
+    for (int r = warp; r < nrows; r += kPatchThreads / 32) {
+      const int cs_off = S.row_cs_off[r];
+      if (cs_off < 0) continue;
+      const int ncs = S.row_cs_end[r] - cs_off;
+      const int* src = mesh.cell_start + (ry0 + r) * mesh.nx + S.row_xmin[r];
+      for (int i = lane; i < ncs; i += 32) cp_async4(S.cs + cs_off + i, src + i);
+      const int ids_off = S.row_ids_off[r], nids = S.row_ids_end[r] - ids_off;
+      const int* isrc = mesh.cell_tris + S.row_ids_base[r];
+      for (int i = lane; i < nids; i += 32) cp_async4(S.ids + ids_off + i, isrc + i);
+    }
+    asm volatile("cp.async.wait_all;" ::: "memory");
+  }
+  __syncthreads();
+  // ---- C + D: per-column values
+#pragma unroll
+  for (int s = 0; s < kCols; ++s) {
+    const unsigned k = tid + s * kPatchThreads;
+    if (k >= D) continue;
+    const unsigned gid = n * D + k;
+    const unsigned w0 = __float_as_uint(ca[s].x);
+    const int op = w0 & 0xffu, li = (w0 >> 8) & 0xffffu, kind = (w0 >> 24) & 0x3fu;
+    float v = 0.f;
+    switch (op) {
+      case B200LAB_OBS_BASE_LIN_VEL: v = o[li]; break;
+      case B200LAB_OBS_BASE_ANG_VEL: v = o[3 + li]; break;
+      case B200LAB_OBS_PROJECTED_GRAVITY: v = o[6 + li]; break;
+      case B200LAB_OBS_GENERATED_COMMANDS: v = e->cmd_vel_b[n * 3 + li]; break;
+      case B200LAB_OBS_JOINT_POS_REL: v = sim.joint_pos[(size_t)n * e->J + li] - e->default_joint_pos[li]; break;
+      case B200LAB_OBS_JOINT_VEL_REL: v = sim.joint_vel[(size_t)n * e->J + li] - e->default_joint_vel[li]; break;
+      case B200LAB_OBS_JOINT_POS: v = sim.joint_pos[(size_t)n * e->J + li]; break;
+      case B200LAB_OBS_JOINT_VEL: v = sim.joint_vel[(size_t)n * e->J + li]; break;
+      case B200LAB_OBS_LAST_ACTION: v = e->action[(size_t)n * e->A + li]; break;
+      case B200LAB_OBS_BASE_POS_Z: v = o[16]; break;
+      case B200LAB_OBS_EXTERNAL: v = e->ext_values[((size_t)__float_as_int(cb[s].w) + li) * N + n]; break;
+      case B200LAB_OBS_HEIGHT_SCAN: {
+        float* hp = e->rc_ray_hits_w ? e->rc_ray_hits_w + ((size_t)n * e->R + li) * 3 : nullptr;
+        float hz;
+        if (is_ray[s]) {
+          const float dz = cc[s].w;
+          float t_best = e->rc_max_distance;
+          int face_best = -1;
+          const int r = cy[s] - ry0;
+          if (in_grid[s] && staged && S.row_cs_off[r] >= 0) {
+            const int ci = S.row_cs_off[r] + (cx[s] - S.row_xmin[r]);
+            const int k0 = S.cs[ci], k1 = S.cs[ci + 1];
+            const int ib = S.row_ids_off[r] - S.row_ids_base[r];
+            const float inv_dz = 1.0f / dz;
+            for (int kk = k0; kk < k1; ++kk) {
+              const int ent = S.ids[ib + kk];
+              const int f = ent & kEntryIdMask;
+              const int t = r - (ent >> kEntryShift) + kHomeMargin;   // home row of a small triangle, relative to the patch
+              float4 ra, rb, rc;
+              int h0;
+              if (f < mesh.first_large && t >= 0 && f >= (h0 = S.hrow_h0[t]) && f < S.hrow_h1[t]) {
+                const int slot = S.hrow_off[t] + (f - h0);
+                ra = S.rec[slot * 3]; rb = S.rec[slot * 3 + 1]; rc = S.rec[slot * 3 + 2];
+              } else {   // large triangle, or a home row that did not fit the staging area
+                const float4* rp = mesh.rec + (size_t)f * 3;
+                ra = __ldg(rp); rb = __ldg(rp + 1); rc = __ldg(rp + 2);
+              }
+              const float th = ray_tri_vertical_rec(mesh, f, ra, rb, rc, st[s], dz, inv_dz);
+              if (th > 0.0f && th <= t_best) { t_best = th; face_best = f; }
+            }
+          } else if (in_grid[s]) {
+            float tt; int face;
+            if (raycast_vertical(mesh, st[s], dz, e->rc_max_distance, tt, face)) { t_best = tt; face_best = face; }
+          }
+          f3 hit{INFINITY, INFINITY, INFINITY};
+          if (face_best >= 0) hit = {st[s].x, st[s].y, st[s].z + t_best * dz};
+          if (hp) { hp[0] = hit.x; hp[1] = hit.y; hp[2] = hit.z; }
+          hz = hit.z;
+        } else {
+          hz = hp ? hp[2] : INFINITY;
+        }
+        v = (pos_z - hz) - cb[s].z;   // observations.py:173
+        break;
+      }
+    }
+    e->obs_buf[gid] = obs_finish(e, v, ca[s], cb[s], w0, kind, step, n, k, gid);
+  }
+}
+
 
 static int launch_geometry(int width, int* wpad, int* epb) {
   int w = width < 1 ? 1 : width;
@@ -1710,6 +2007,10 @@ void* b200lab_env_create(const B200LabEnvState* st) {
   h->host = *st;
   h->cols = nullptr;
   h->has_mesh = false;
+  {
+    const char* impl = getenv("B200LAB_OBS_IMPL");
+    h->obs_impl = impl ? atoi(impl) : 0;   // measured on B200 (profiles/r2_notes.md): per-ray 45 us, staged 90 us at 4096 envs
+  }
   h->side2 = nullptr;
   h->ev_spec_fork = h->ev_spec_done = nullptr;
   h->spec_z = h->spec_pose = nullptr;
@@ -1939,10 +2240,12 @@ int b200lab_compute_obs_range(void* env, const B200LabSimView* sim, int64_t step
   const B200LabEnvState& s = h->host;
   B200LAB_CHECK_ARG(env_begin >= 0 && env_begin <= env_end && env_end <= s.N, "env range out of bounds");
   cudaStream_t st_ = (cudaStream_t)stream;
+  bool joined_spec = false;
   if (h->spec_pending) {   // join the speculative scan
     cudaError_t err = cudaStreamWaitEvent(st_, h->ev_spec_done, 0);
     if (err != cudaSuccess) { set_error("b200lab_compute_obs: %s", cudaGetErrorString(err)); return B200LAB_ERR_CUDA; }
     h->spec_pending = false;
+    joined_spec = true;
   }
   const int cnt = env_end - env_begin;
   if (cnt == 0) return B200LAB_OK;
@@ -1954,6 +2257,25 @@ int b200lab_compute_obs_range(void* env, const B200LabSimView* sim, int64_t step
   }
   int64_t total = (int64_t)cnt * s.obs_dim;
   if (total <= 0) return check_launch("compute_obs");
+  if (h->obs_impl == 1 && h->rays_vertical && h->has_mesh && !joined_spec && s.obs_dim <= kPatchMaxCols * kPatchThreads) {
+    // staged height scan: one CTA per env (a speculated scan, when one was joined, is consumed by the per-ray kernel)
+    static bool attr_set = false;
+    if (!attr_set) {
+      cudaError_t aerr = cudaFuncSetAttribute(compute_obs_patch_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                              (int)sizeof(PatchSmem));
+      if (aerr == cudaSuccess)
+        aerr = cudaFuncSetAttribute(compute_obs_patch_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(PatchSmem));
+      if (aerr != cudaSuccess) { set_error("compute_obs: %s", cudaGetErrorString(aerr)); return B200LAB_ERR_CUDA; }
+      attr_set = true;
+    }
+    auto pk = s.obs_dim <= kPatchThreads ? compute_obs_patch_kernel<1> : compute_obs_patch_kernel<2>;
+    cudaError_t err = launch_pdl(pk, dim3((unsigned)cnt), dim3(kPatchThreads), sizeof(PatchSmem), st_,
+                                 h->host, *sim, step_counter, (const ObsCol*)h->cols, (const float*)h->derived, h->mesh,
+                                 (unsigned)env_begin);
+    if (err != cudaSuccess) { set_error("compute_obs: %s", cudaGetErrorString(err)); return B200LAB_ERR_CUDA; }
+    count_launch();
+    return check_launch("compute_obs");
+  }
   {
     auto kern = h->rays_vertical ? compute_obs_kernel<true> : compute_obs_kernel<false>;
     cudaError_t err = launch_pdl(kern, dim3((unsigned)ceil_div(total, B200LAB_OBS_THREADS)), dim3(B200LAB_OBS_THREADS), 0, st_, h->host, *sim, step_counter,

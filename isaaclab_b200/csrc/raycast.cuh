@@ -24,7 +24,7 @@ namespace b200lab {
 // Every small triangle overlapping cell (cx, cy) has its home in [cx-kHomeMargin, cx] x [cy-kHomeMargin, cy].  The
 // remaining ("large") triangles follow, ids >= first_large.  `orig_face` maps the sorted id back to the caller's face
 // index (ray_face_id).  A `cell_tris` entry is  id | dy << kEntryShift  with dy = cy - home row (0 for large triangles).
-constexpr int kHomeMargin = 3;
+constexpr int kHomeMargin = 2;   // a height-field triangle (two cells wide) spans three cells
 constexpr int kEntryShift = 28;
 constexpr int kEntryIdMask = (1 << kEntryShift) - 1;
 

@@ -60,7 +60,11 @@ class SimView:
 
 
 class FusedEnv:
-    def __init__(self, spec: dict, device="cuda", seed: int = 0):
+    def __init__(self, spec: dict, device="cuda", seed: int = 0, store_ray_hits: bool = True):
+        """`store_ray_hits=False`: RayCasterData.ray_hits_w [N,R,3] is not materialised -- the hit heights go straight from
+        registers into the observation row.  Only valid for a sensor that is outdated at every observation
+        (update_period <= env step dt), which is checked here."""
+        self.store_ray_hits = bool(store_ray_hits)
         self.spec = s = spec
         self.device = dev = torch.device(device)
         self.L = _lib.lib()
@@ -248,7 +252,11 @@ class FusedEnv:
         if r:
             self.rc_timestamp, self.rc_timestamp_last_update = z(N), z(N)
             self.rc_is_outdated = torch.ones(N, dtype=torch.uint8, device=dev)
-            self.rc_drift, self.rc_pos_w, self.rc_quat_w, self.rc_ray_hits_w = z(N, 3), z(N, 3), z(N, 4), z(N, R, 3)
+            if not self.store_ray_hits and float(r["update_period"]) > float(s["step_dt"]) + 1e-6:
+                raise ValueError("store_ray_hits=False needs a ray caster that updates at every observation "
+                                 "(update_period <= env step dt): a sensor that skips updates re-reads its stored hits")
+            self.rc_drift, self.rc_pos_w, self.rc_quat_w = z(N, 3), z(N, 3), z(N, 4)
+            self.rc_ray_hits_w = z(N, R, 3) if self.store_ray_hits else None
             st.rc_timestamp, st.rc_timestamp_last_update = p(self.rc_timestamp), p(self.rc_timestamp_last_update)
             st.rc_is_outdated, st.rc_drift = p(self.rc_is_outdated), p(self.rc_drift)
             st.rc_pos_w, st.rc_quat_w, st.rc_ray_hits_w = p(self.rc_pos_w), p(self.rc_quat_w), p(self.rc_ray_hits_w)
