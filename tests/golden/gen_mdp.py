@@ -64,15 +64,19 @@ class Replay:
     """Cursor over the slabs: state after physics sub-step s of env step k.  Event writes mutate the slab in place,
     exactly as the reference mutates PhysX state."""
 
-    def __init__(self, slabs):
+    def __init__(self, slabs, wrap=False):
         self.slabs = slabs
         self.S = slabs["joint_pos"].shape[1]
+        self.K = slabs["joint_pos"].shape[0]
+        self.wrap = wrap                 # timing runs cycle through the slabs; fixture generation never wraps
         self.k, self.s = 0, self.S - 1   # "before the first sub-step" = last state of slab 0
 
     def advance(self):
         self.s += 1
         if self.s == self.S:
             self.k, self.s = self.k + 1, 0
+            if self.wrap:
+                self.k %= self.K
 
     @property
     def root(self):
@@ -525,7 +529,10 @@ def build_ray_caster(cfg, spec, art_view):
     s._data = RayCasterData()
     s._view = art_view
     r = spec["raycaster"]
-    s.meshes = {s.cfg.mesh_prim_paths[0]: _OracleMeshHandle(oracle_raycast.Mesh(r["mesh_vertices"], r["mesh_faces"]))}
+    mesh = oracle_raycast.Mesh(r["mesh_vertices"], r["mesh_faces"])
+    if mesh.F.shape[0] > 200_000:   # full-size terrain (timing runs): exact xy pre-filter, same hits as brute force
+        mesh.enable_grid(0.25)
+    s.meshes = {s.cfg.mesh_prim_paths[0]: _OracleMeshHandle(mesh)}
     s._initialize_rays_impl()
     return s
 
@@ -586,7 +593,7 @@ def hard_joint_limits(task, spec):
     return lim
 
 
-def build_reference_env(task, spec, slabs, init, tmpdir):
+def build_reference_env(task, spec, slabs, init, tmpdir, wrap=False):
     import importlib
     mod, cls = REF_TASK_CFG[task]
     cfg = getattr(importlib.import_module(mod), cls)()
@@ -601,7 +608,7 @@ def build_reference_env(task, spec, slabs, init, tmpdir):
         term = getattr(cfg.commands, name)
         if hasattr(term, "debug_vis"):
             term.debug_vis = False
-    replay = Replay(slabs)
+    replay = Replay(slabs, wrap=wrap)
     env = _new(ManagerBasedRLEnv)
     env._is_closed = True
     env.cfg = cfg

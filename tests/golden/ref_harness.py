@@ -19,7 +19,16 @@ import types
 
 import torch
 
-REFERENCE_ROOT = os.environ.get("B200LAB_REFERENCE_ROOT", "/root/reference")
+def _default_root():
+    """/root/reference where it exists (authoring container); else the unmodified copy that baseline/install_ref.py put
+    under baseline/_ref/ (the GPU box)."""
+    if os.path.isdir("/root/reference/source/isaaclab"):
+        return "/root/reference"
+    here = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    return os.path.join(here, "baseline", "_ref")
+
+
+REFERENCE_ROOT = os.environ.get("B200LAB_REFERENCE_ROOT") or _default_root()
 
 _STUB_ROOTS = (
     "omni", "carb", "isaacsim", "pxr", "prettytable", "warp", "trimesh", "gymnasium", "matplotlib",
