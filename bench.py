@@ -1,12 +1,18 @@
 """bench.py -- headline benchmark of the B200-native non-physics step (BASELINE.json metric).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--configs cfg1,cfg2,...]
 
 One "step" = one ManagerBasedRLEnv.step worth of non-physics work over the env shard of one GPU:
 process_action + S x (actuator model, contact/joint-acc update) + terminations/rewards/resets/commands/events +
 observations incl. the 187-ray height scan -- on synthetic ArticulationData-shaped state (PhysX is out of scope).
-Workload at N=1: BASELINE.json configs[2] "Isaac-Velocity-Rough-Anymal-C-v0, 4096 envs/GPU" (the config the metric is
-quoted on).  Prints ONE JSON line (rank 0).  See DESIGN.md "Measurement" for every field.
+
+Headline (`value`, `e2e`, `roofline`): BASELINE.json configs[2] "Isaac-Velocity-Rough-Anymal-C-v0, 4096 envs/GPU", the
+config the metric is quoted on.  `configs` carries one sub-record per BASELINE config (cfg1..cfg5 of SURVEY 8) with its
+own env-step time, roofline fraction, end-to-end number and PPO update time, each at that config's envs/GPU.
+Arms per config: `replay` (all S post-physics states known: the physics loop is ONE launch; the step replayed as a
+CUDA graph), `live` (what a running simulator can use: process_action + S x (substep_pre, substep_post) + post_step +
+post_reset_write + compute_obs, eager), `e2e` (public API, host buffers).  Prints ONE JSON line (rank 0).
+See DESIGN.md "Measurement" for every field.
 """
 from __future__ import annotations
 
@@ -25,11 +31,32 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
-TASK = "Isaac-Velocity-Rough-Anymal-C-v0"
-ENVS_PER_GPU = 4096
-K_SLABS = 32
-METRIC = "non-physics env-steps/s (Anymal-C rough, 4096 envs/GPU)"
 UNIT = "env-steps/s"
+L2_BYTES = 126e6
+
+_PPO_COMMON = dict(epochs=5, mini_batches=4, clip_param=0.2, gamma=0.99, lam=0.95, value_loss_coef=1.0, learning_rate=1e-3,
+                   max_grad_norm=1.0, desired_kl=0.01)
+# BASELINE.json configs.  `ppo`: agents/rsl_rl_ppo_cfg.py of each task.
+CONFIGS = {
+    "cfg1": dict(task="Isaac-Velocity-Flat-Anymal-C-v0", envs=4096, env_arms=False,   # PPO-only config (runs on CPU in the reference)
+                 ppo=dict(T=24, hidden=[128, 128, 128], entropy_coef=0.005)),
+    "cfg2": dict(task="Isaac-Cartpole-v0", envs=4096, env_arms=True, ppo=dict(T=16, hidden=[32, 32], entropy_coef=0.005)),
+    "cfg3": dict(task="Isaac-Velocity-Rough-Anymal-C-v0", envs=4096, env_arms=True,
+                 ppo=dict(T=24, hidden=[512, 256, 128], entropy_coef=0.005)),
+    "cfg4": dict(task="Isaac-Velocity-Rough-Unitree-Go1-v0", envs=16384, env_arms=True,
+                 ppo=dict(T=24, hidden=[512, 256, 128], entropy_coef=0.01)),
+    "cfg5": dict(task="Isaac-Velocity-Rough-H1-v0", envs=8192, env_arms=True,
+                 ppo=dict(T=24, hidden=[512, 256, 128], entropy_coef=0.01)),
+}
+HEADLINE = "cfg3"
+TASK = CONFIGS[HEADLINE]["task"]
+ENVS_PER_GPU = CONFIGS[HEADLINE]["envs"]
+METRIC = "non-physics env-steps/s (Anymal-C rough, 4096 envs/GPU)"
+
+
+def _term_dim(spec, t):
+    from isaaclab_b200.envs.term_dims import term_dim
+    return term_dim(spec, t)
 
 
 def algorithmic_bytes(spec):
@@ -57,11 +84,6 @@ def algorithmic_bytes(spec):
     per["post_reset_write"] = per["substep_pre"]
     per_step = per["decimation_fused"] + per["post_step"] + per["post_reset_write"] + per["compute_obs"]
     return per, per_step
-
-
-def _term_dim(spec, t):
-    from isaaclab_b200.envs.term_dims import term_dim
-    return term_dim(spec, t)
 
 
 class ClockSampler(threading.Thread):
@@ -150,20 +172,42 @@ def ncu_traffic(kernel):
     return None
 
 
-def workload_name(spec):
-    return (f"{TASK} non-physics step, {spec['N']} envs/GPU, 187-ray height scan, ActuatorNetLSTM, "
+_TERRAIN, _MESH = {}, {}
+
+
+def workload_name(cfg_id, spec):
+    c = CONFIGS[cfg_id]
+    act = "/".join(sorted({a["kind"] for a in spec["actuators"]}))
+    return (f"{c['task']} non-physics step, {spec['N']} envs/GPU, {spec.get('R', 0)}-ray height scan, actuators {act}, "
             f"decimation {spec['decimation']}")
 
 
-def build_workload(device, seed):
+def build_workload(cfg_id, seed, device=None, envs=None):
+    """Spec + K state slabs (CPU tensors) + initial env state of one BASELINE config.  K is sized so that the cycled slabs
+    exceed the L2 (126 MB); the terrain and its device mesh are built once per process and shared between configs."""
     from isaaclab_b200 import terrains
     from isaaclab_b200.envs.compile import compile_env_cfg
     from isaaclab_b200.sim.synthetic import generate_slabs, initial_env_state
     from isaaclab_b200.tasks import TASKS
-    cfg = TASKS[TASK]()
-    terrain = terrains.TerrainGenerator(cfg.scene.terrain.terrain_generator)
-    spec = compile_env_cfg(cfg, num_envs=ENVS_PER_GPU, terrain=terrain, seed=seed)
-    slabs = generate_slabs(spec, K_SLABS, seed=1234 + 3 + seed)
+    c = CONFIGS[cfg_id]
+    cfg = TASKS[c["task"]]()
+    terrain = None
+    if cfg.scene.terrain is not None and cfg.scene.terrain.terrain_type == "generator":
+        if "t" not in _TERRAIN:
+            _TERRAIN["t"] = terrains.TerrainGenerator(cfg.scene.terrain.terrain_generator)
+        terrain = _TERRAIN["t"]
+    N = int(envs or c["envs"])
+    spec = compile_env_cfg(cfg, num_envs=N, terrain=terrain, seed=seed)
+    if device is not None and spec.get("raycaster") and terrain is not None:
+        if "m" not in _MESH:
+            from isaaclab_b200.sensors.ray_caster import WarpFreeMesh
+            r = spec["raycaster"]
+            _MESH["m"] = WarpFreeMesh(r["mesh_vertices"], r["mesh_faces"])
+        spec["raycaster"]["mesh"] = _MESH["m"]
+    S, J, B = spec["decimation"], spec["J"], spec["B"]
+    slab_bytes = 4 * N * (13 + S * 2 * J + S * B * 3 + B * 3)
+    K = int(min(1024, max(4, math.ceil(1.3 * L2_BYTES / slab_bytes))))
+    slabs = generate_slabs(spec, K, seed=1234 + int(cfg_id[3:]) + seed)
     init = initial_env_state(spec, seed=7 + seed)
     return cfg, spec, slabs, init
 
@@ -195,133 +239,148 @@ def time_kernels(fus, sim, action, steps):
     return {n: sum(a.elapsed_time(b) for a, b in ev[n]) / max(1, len(ev[n])) for n in names}
 
 
-def run_ours(args):
+def _timed(fn, steps, world, dev):
+    """EXACTLY `steps` calls of fn(k) between a barrier + synchronize on both sides; CUDA events; MAX over ranks (ms)."""
     import torch.distributed as dist
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    rank = int(os.environ.get("RANK", "0"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
+    torch.cuda.synchronize()
     if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for k in range(steps):
+        fn(k)
+    e1.record()
+    torch.cuda.synchronize()
+    t = torch.tensor([e0.elapsed_time(e1)], device=dev)
+    if world > 1:
+        dist.barrier()
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def measure_env(cfg_id, spec, slabs, init, steps, warmup, world, rank, dev, peak, sampler=None):
+    """Device-resident arms of one config: `replay` (graph-replayed fused step = the headline `value` path), `replay_eager`
+    (same kernels launched from Python), `live` (per-sub-step entry points, eager), per-kernel times and roofline."""
     from isaaclab_b200 import _lib
     from isaaclab_b200.envs.fused_env import FusedEnv
-    from isaaclab_b200.envs.manager_based_rl_env import HostReplaySim, ManagerBasedRLEnv
-    from isaaclab_b200.sim.synthetic import SyntheticSim
-    from isaaclab_b200.sim.synthetic import init_fused_state
-
-    cfg, spec, slabs, init = build_workload(dev, seed=rank)
-    N = spec["N"]
+    from isaaclab_b200.sim.synthetic import SyntheticSim, init_fused_state
     L = _lib.lib()
-    # ---- device-resident arm: inputs in HBM, K slabs (> L2) cycled
-    sim = SyntheticSim(spec, K=K_SLABS, device=dev, slabs=slabs)
-    fus = FusedEnv(spec, device=dev, seed=rank)
+    N, K = spec["N"], slabs["root_state_w"].shape[0]
+    sim = SyntheticSim(spec, K=K, device=dev, slabs=slabs)
+    # the bench's consumers read observations, not RayCasterData.ray_hits_w: the hit buffer is not materialised
+    fus = FusedEnv(spec, device=dev, seed=rank, store_ray_hits=False)
     init_fused_state(fus, init)
     g = torch.Generator().manual_seed(11 + rank)
     action = torch.randn(N, spec["A"], generator=g).to(dev)
 
-    def one_step(k):
+    def eager(k):
         fus.step(action, sim.views(k + 1), sim.views(k)[-1])
 
-    for k in range(args.warmup):
-        one_step(k)
+    def live(k):
+        fus.step(action, sim.views(k + 1), sim.views(k)[-1], fused=False)
+
+    for k in range(warmup):
+        eager(k)
+    l0 = L.b200lab_launch_count()
+    eager(warmup)
     torch.cuda.synchronize()
-    if world > 1:
-        dist.barrier()
-    sampler = ClockSampler(local)
-    sampler.start()
+    launches_per_step = L.b200lab_launch_count() - l0
+    ms_eager = _timed(lambda k: eager(warmup + k), steps, world, dev)
+    # ---- graph-replayed step: one captured graph per slab index (the step counter lives on the device)
+    fus.use_device_step_counter()
+    graphs = []
+    import gc
+    gc.collect()
+    gc.disable()
+    try:
+        for j in range(K):
+            gr = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(gr, capture_error_mode="thread_local"):
+                fus.step(action, sim.views(j + 1), sim.views(j)[-1])
+            graphs.append(gr)
+    finally:
+        gc.enable()
+    for k in range(warmup):
+        graphs[k % K].replay()
+    if sampler is not None:
+        sampler.start()
+    ms = _timed(lambda k: graphs[(warmup + k) % K].replay(), steps, world, dev)
+    clocks = sampler.finish() if sampler is not None else None
+    del graphs
+    # ---- live arm (what a running simulator can use): 2 + 2S + 2 launches per step, eager
+    fus_live = FusedEnv(spec, device=dev, seed=rank, store_ray_hits=False)
+    init_fused_state(fus_live, init)
+    fus, fus_replay = fus_live, fus
+    for k in range(warmup):
+        live(k)
+    l0 = L.b200lab_launch_count()
+    live(warmup)
     torch.cuda.synchronize()
-    launches0 = L.b200lab_launch_count()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    for k in range(args.steps):
-        one_step(args.warmup + k)
-    e1.record()
-    torch.cuda.synchronize()
-    launches = L.b200lab_launch_count() - launches0
-    ms = e0.elapsed_time(e1)
-    t = torch.tensor([ms], device=dev)
-    if world > 1:
-        dist.barrier()
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms = float(t.item())
-    clocks = sampler.finish()
-    value = world * N * args.steps / (ms * 1e-3)
-    # ---- per-kernel timing + roofline of the dominant kernel
-    per_kernel_ms = time_kernels(fus, sim, action, max(8, min(args.steps, 64)))
+    live_launches = L.b200lab_launch_count() - l0
+    live_steps = max(10, steps // 4)
+    ms_live = _timed(lambda k: live(warmup + k), live_steps, world, dev)
+    fus = fus_replay
+    # ---- per-kernel timing + roofline
+    per_kernel_ms = time_kernels(fus, sim, action, max(8, min(steps, 64)))
     bytes_per, bytes_step = algorithmic_bytes(spec)
-    S = spec["decimation"]
     dom = max(per_kernel_ms, key=per_kernel_ms.get)
-    peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else {}
-    peak = float(peaks.get("hbm_gbs", 6650.0))
     achieved = bytes_per[dom] * N / (per_kernel_ms[dom] * 1e-3) / 1e9
-    roof = {"bound": "hbm", "kernel": dom, "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
-            "frac": round(achieved / peak, 4), "traffic": ncu_traffic(dom), "peak_source": "measured" if peaks else "fallback",
-            "algorithmic_bytes_per_launch": bytes_per[dom] * N,
+    roof = {"bound": "hbm", "kernel": dom, "achieved": round(achieved, 1), "peak": peak[0], "unit": "GB/s",
+            "frac": round(achieved / peak[0], 4), "traffic": ncu_traffic(dom) if cfg_id == HEADLINE else None,
+            "peak_source": peak[1], "algorithmic_bytes_per_launch": bytes_per[dom] * N,
             "per_kernel_us": {n: round(v * 1e3, 2) for n, v in per_kernel_ms.items()},
             "step_algorithmic_bytes": bytes_step * N,
-            "step_frac": round(bytes_step * N / (ms / args.steps * 1e-3) / 1e9 / peak, 4)}
-    # ---- end-to-end arm: public API with HOST buffers (pinned), H2D of each step's simulator state + action and
-    # D2H of obs / reward / dones inside the timed region
+            "step_frac": round(bytes_step * N / (ms / steps * 1e-3) / 1e9 / peak[0], 4)}
+    out = {"ms_per_step": round(ms / steps, 5), "value": round(world * N * steps / (ms * 1e-3), 1),
+           "replay_eager_ms_per_step": round(ms_eager / steps, 5),
+           "live": {"ms_per_step": round(ms_live / live_steps, 5), "value": round(world * N * live_steps / (ms_live * 1e-3), 1),
+                    "launches_per_step": int(live_launches),
+                    "path": "process_action + S x (substep_pre, substep_post) + post_step + post_reset_write + compute_obs, eager"},
+           "launches_per_step": int(launches_per_step), "slabs": K, "slab_bytes_total": sim.bytes(), "roofline": roof}
+    del fus, fus_live, fus_replay, sim
+    torch.cuda.empty_cache()
+    return out, clocks
+
+
+def measure_e2e(cfg, spec, slabs, init, steps, warmup, world, rank, dev):
+    """End to end through the public API with HOST buffers: every step the pinned simulator-state slab + action cross to the
+    device and observations / reward / dones come back, inside the timed region; results synchronised every step."""
+    import torch.distributed as dist
+    from isaaclab_b200.envs.manager_based_rl_env import HostReplaySim, ManagerBasedRLEnv
+    from isaaclab_b200.sim.synthetic import init_fused_state
+    N = spec["N"]
     host_sim = HostReplaySim(spec, slabs, device=dev)
     env = ManagerBasedRLEnv(cfg, sim=host_sim, device=dev, spec=spec, seed=rank, use_cuda_graph=True)
     init_fused_state(env.fused, init)
+    g = torch.Generator().manual_seed(12 + rank)
     act_host = torch.randn(N, spec["A"], generator=g).pin_memory()
     env.result_chunks = 4
     res_host = torch.empty(env.fused.result.numel(), dtype=torch.uint8).pin_memory()
 
-    def e2e_step():
-        # obs, reward, terminated, time-outs, reset mask stream into the pinned slab behind the kernels that produce them
+    def e2e_step(_k):
         env.step(act_host, results_out=res_host)
         env.wait_results()  # the caller consumes the result before the next step
 
-    for _ in range(args.warmup):
-        e2e_step()
-    torch.cuda.synchronize()
-    if world > 1:
-        dist.barrier()
-    t0 = time.perf_counter()
-    e0.record()
-    for _ in range(args.steps):
-        e2e_step()
-    e1.record()
-    torch.cuda.synchronize()
-    ms_e2e = torch.tensor([e0.elapsed_time(e1)], device=dev)
-    if world > 1:
-        dist.all_reduce(ms_e2e, op=dist.ReduceOp.MAX)
-    ms_e2e = float(ms_e2e.item())
+    for k in range(max(warmup, 3 * HostReplaySim._SETS)):   # every staging set has its graph before the timed region
+        e2e_step(k)
+    ms = _timed(e2e_step, steps, world, dev)
     h2d = host_sim.h2d_bytes_per_step + act_host.numel() * 4
     d2h = res_host.numel()
-    e2e = {"value": round(world * N * args.steps / (ms_e2e * 1e-3), 1), "unit": UNIT, "h2d_bytes_per_step": h2d,
-           "d2h_bytes_per_step": d2h, "ms_per_step": round(ms_e2e / args.steps, 4)}
-    out = {"metric": METRIC, "value": round(value, 1), "unit": UNIT, "n_gpus": world, "steps": args.steps,
-           "warmup": args.warmup, "ms_per_step": round(ms / args.steps, 5), "higher_is_better": True, "scaling": "weak",
-           "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-           "config": {"workload": workload_name(spec), "envs_per_gpu": N,
-                      "e2e_mode": "ManagerBasedRLEnv.step(action, results_out) with pinned host buffers, the step captured "
-                                  "as a CUDA graph per staging set (H2D action, kernels, D2H of reward/masks after "
-                                  "post_step and of the obs rows range by range behind the obs kernels); results "
-                                  "synchronised every step; next step's simulator state prefetched H2D on a copy "
-                                  "stream while the current step computes", "l2_policy": f"{K_SLABS} state slabs "
-                                  f"({sim.bytes() >> 20} MiB > 126 MiB L2) cycled", "parallelism": f"env-shard x{world}"},
-           "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roof}
-    del env, host_sim, fus, sim
+    out = {"value": round(world * N * steps / (ms * 1e-3), 1), "unit": UNIT, "h2d_bytes_per_step": h2d,
+           "d2h_bytes_per_step": d2h, "ms_per_step": round(ms / steps, 4),
+           "pcie_gbs_per_gpu": {"h2d": round(h2d / (ms / steps * 1e-3) / 1e9, 2), "d2h": round(d2h / (ms / steps * 1e-3) / 1e9, 2),
+                                "note": "bytes per step / end-to-end step time (copies overlap the kernels; not a link peak)"}}
+    del env, host_sim
     torch.cuda.empty_cache()
-    mg = {"global_rank": rank, "local_rank": local, "world_size": world} if world > 1 else None
-    out["ppo_update"] = time_ppo_update(dev, precision=2, multi_gpu_cfg=mg)   # N>1: one NCCL all-reduce per minibatch
-    out["ppo_update"]["fp32_ffma_s_per_iter"] = time_ppo_update(dev, precision=0, multi_gpu_cfg=mg)["s_per_iter"]
-    if rank == 0:
-        if world == 1 and not args.no_cpu_baseline:
-            out["cpu_baseline"] = cpu_baseline(spec, slabs, init, budget_s=15.0)
-            out["cpu_baseline"]["ppo_update"] = cpu_ppo_baseline()
-    if world > 1:
-        dist.destroy_process_group()
-    return json.dumps(out) if rank == 0 else None
+    return out
 
 
-PPO_CFG = dict(N=ENVS_PER_GPU, T=24, obs_dim=235, act_dim=12, hidden=[512, 256, 128], epochs=5, mini_batches=4, clip_param=0.2,
-               gamma=0.99, lam=0.95, value_loss_coef=1.0, entropy_coef=0.005, learning_rate=1e-3, max_grad_norm=1.0,
-               desired_kl=0.01)   # config 3: TASKS/.../anymal_c/agents/rsl_rl_ppo_cfg.py (AnymalCRoughPPORunnerCfg)
+def ppo_cfg(cfg_id, spec, envs=None):
+    from isaaclab_b200.envs.term_dims import term_dim
+    c = CONFIGS[cfg_id]
+    obs = sum(term_dim(spec, t) for t in spec["observations"]["terms"])
+    return dict(_PPO_COMMON, N=int(envs or spec["N"]), obs_dim=obs, act_dim=spec["A"], **c["ppo"])
 
 
 def synthetic_rollout(c, seed, forward=None):
@@ -352,11 +411,12 @@ def ppo_flops_per_iter(c):
     return 3.0 * fwd * c["T"] * c["N"] * c["epochs"]   # fwd + dX + dW (upper bound)
 
 
-def time_ppo_update(dev, reps=3, precision=2, multi_gpu_cfg=None):
-    """Second half of the metric: PPO update s/iter = GAE + 5 epochs x 4 minibatches (gather, actor/critic fwd, fused
-    loss fwd+bwd, bwd GEMMs, KL-adaptive LR, clip + Adam) at config-3 shapes, CUDA events on the launching stream."""
+def time_ppo_update(dev, c, reps=3, precision=2, multi_gpu_cfg=None):
+    """Second half of the metric: PPO update s/iter = GAE + epochs x minibatches (gather, actor/critic fwd, fused loss
+    fwd+bwd, bwd GEMMs, KL-adaptive LR, clip + Adam), CUDA events on the launching stream; N>1: one NCCL all-reduce per
+    minibatch."""
+    from isaaclab_b200 import _lib
     from isaaclab_b200.rsl_rl import PPO, ActorCritic, TensorDict
-    c = PPO_CFG
     torch.manual_seed(1234 + 3)
     obs0 = TensorDict({"policy": torch.zeros(c["N"], c["obs_dim"], device=dev)}, batch_size=[c["N"]])
     pol = ActorCritic(obs0, {"policy": ["policy"], "critic": ["policy"]}, c["act_dim"], actor_hidden_dims=c["hidden"],
@@ -368,13 +428,14 @@ def time_ppo_update(dev, reps=3, precision=2, multi_gpu_cfg=None):
     if multi_gpu_cfg is not None:
         alg.broadcast_parameters()
     alg.init_storage("rl", c["N"], c["T"], obs0, [c["act_dim"]])
+
     def forward(o):
         od = TensorDict({"policy": o.to(dev)}, batch_size=[o.shape[0]])
-        return pol.act_inference(od).clone(), pol.evaluate(od).clone()
+        return pol.act_inference(od), pol.evaluate(od)
 
     roll = {k: v.to(dev) for k, v in synthetic_rollout(c, 1234 + 3, forward).items()}
     st = alg.storage
-    L = __import__("isaaclab_b200._lib", fromlist=["lib"]).lib()
+    L = _lib.lib()
 
     def load():
         st.observations["policy"].copy_(roll["observations"])
@@ -399,23 +460,33 @@ def time_ppo_update(dev, reps=3, precision=2, multi_gpu_cfg=None):
             times_upd.append(e[1].elapsed_time(e[2]))
             launches = L.b200lab_launch_count() - l0
     gae_ms, upd_ms = min(times_gae), sorted(times_upd)[len(times_upd) // 2]
-    s_iter = (gae_ms + upd_ms) * 1e-3
-    return {"s_per_iter": round(s_iter, 5), "gae_ms": round(gae_ms, 4), "update_ms": round(upd_ms, 3),
-            "tflops": round(ppo_flops_per_iter(c) / (upd_ms * 1e-3) / 1e12, 2), "gpu_launches": int(launches),
-            "precision": {0: "fp32 FFMA (SIMT)", 1: "tf32 tcgen05 (reduced precision)",
-                          2: "3xTF32 tcgen05 (fp32-accurate hi/lo split, all layers)"}[pol.precision],
-            "config": f"cfg 3: N={c['N']} T={c['T']} obs={c['obs_dim']} act={c['act_dim']} hidden={c['hidden']} "
-                      f"{c['epochs']} epochs x {c['mini_batches']} minibatches of {c['N'] * c['T'] // c['mini_batches']}",
-            "loss": {k: round(float(v), 6) for k, v in loss.items()}}
+    out = {"s_per_iter": round((gae_ms + upd_ms) * 1e-3, 5), "gae_ms": round(gae_ms, 4), "update_ms": round(upd_ms, 3),
+           "tflops": round(ppo_flops_per_iter(c) / (upd_ms * 1e-3) / 1e12, 2), "gpu_launches": int(launches),
+           "precision": {0: "fp32 FFMA (SIMT)", 1: "tf32 tcgen05 (what the reference's train.py enables on GPU)",
+                         2: "3xTF32 tcgen05 (fp32-accurate hi/lo split; the parity setting)"}[pol.precision],
+           "config": f"N={c['N']} T={c['T']} obs={c['obs_dim']} act={c['act_dim']} hidden={c['hidden']} "
+                     f"{c['epochs']} epochs x {c['mini_batches']} minibatches of {c['N'] * c['T'] // c['mini_batches']}",
+           "loss": {k: round(float(v), 6) for k, v in loss.items()}}
+    del alg, pol, roll
+    torch.cuda.empty_cache()
+    return out
 
 
-def cpu_ppo_baseline(budget_updates=2, threads=None):
+def ppo_record(dev, c, mg, reps=3):
+    """Both precisions: 3xTF32 is the parity setting (headline s_per_iter), plain TF32 the like-for-like of the reference
+    on GPU (scripts/reinforcement_learning/rsl_rl/train.py:97 enables TF32 matmuls)."""
+    r = time_ppo_update(dev, c, reps=reps, precision=2, multi_gpu_cfg=mg)
+    t = time_ppo_update(dev, c, reps=reps, precision=1, multi_gpu_cfg=mg)
+    r["tf32"] = {"s_per_iter": t["s_per_iter"], "update_ms": t["update_ms"], "tflops": t["tflops"], "precision": t["precision"]}
+    return r
+
+
+def cpu_ppo_baseline_port(c, budget_updates=2, threads=None):
     """Oracle port of PPO.update on the host cores: `budget_updates` of the 20 minibatch updates of one iteration at
     config-3 shapes (+ GAE), scaled to s/iter."""
     from oracle import rsl_rl as O
     threads = threads or os.cpu_count()
     torch.set_num_threads(threads)
-    c = PPO_CFG
     g = torch.Generator().manual_seed(7)
     dims = [c["obs_dim"], *c["hidden"]]
     params = {}
@@ -456,13 +527,13 @@ def cpu_ppo_baseline(budget_updates=2, threads=None):
             "sample": f"GAE + {budget_updates} of {c['mini_batches'] * c['epochs']} minibatch updates (scaled), torch CPU autograd"}
 
 
-def cpu_baseline(spec, slabs, init, budget_s=15.0, threads=None, max_steps=10**9):
+def cpu_baseline_port(spec, slabs, init, budget_s=15.0, threads=None, max_steps=10**9):
     """The oracle port of the reference torch path (device='cpu') on the host cores, bounded sample of the same
     workload: full-size env steps (4096 envs) until `budget_s` is used (at least 2)."""
     import copy
 
     from oracle.mdp_env import OracleEnv, n_u_reset, n_u_step, obs_dim
-    from tests.mdp_common import init_oracle_state, slab_views_cpu
+    from tests.mdp_common import init_oracle_state, slab_views_cpu   # checker-side helpers (CPU leg only)
     threads = threads or os.cpu_count()
     torch.set_num_threads(threads)
     os.environ.setdefault("OMP_NUM_THREADS", str(threads))
@@ -494,36 +565,143 @@ def cpu_baseline(spec, slabs, init, budget_s=15.0, threads=None, max_steps=10**9
             "ms_per_step": round(t_used / n_done * 1e3, 2)}
 
 
+
+
+def cpu_env_baseline(cfg_id, spec, slabs, init, budget_s, max_steps=10**9):
+    """CPU leg of the env step: the UNMODIFIED reference (baseline/ref_arm.py over baseline/_ref) when its sources are
+    present, else -- and saying so -- the oracle port."""
+    spec = dict(spec)
+    if spec.get("raycaster"):   # the CPU legs deep-copy the spec: drop the live device-mesh handle
+        spec["raycaster"] = {k: v for k, v in spec["raycaster"].items() if k != "mesh"}
+    try:
+        from baseline import ref_arm
+        if ref_arm.available():
+            return ref_arm.time_env_step(CONFIGS[cfg_id]["task"], spec, slabs, init, budget_s=budget_s, max_steps=max_steps)
+        why = "baseline/_ref absent"
+    except Exception as e:   # a broken reference install must not take the bench down: fall back, and say why
+        why = f"reference arm failed: {type(e).__name__}: {e}"
+    r = cpu_baseline_port(spec, slabs, init, budget_s=budget_s, max_steps=max_steps)
+    r["fallback_reason"] = why
+    return r
+
+
+def cpu_ppo_baseline(c):
+    try:
+        from baseline import ref_arm
+        if ref_arm.available():
+            return ref_arm.time_ppo_update(c)
+        why = "baseline/_ref absent"
+    except Exception as e:
+        why = f"reference arm failed: {type(e).__name__}: {e}"
+    r = cpu_ppo_baseline_port(c)
+    r["fallback_reason"] = why
+    return r
+
+
+def _peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return float(json.load(open(p)).get("hbm_gbs", 6650.0)), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def run_ours(args):
+    import torch.distributed as dist
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    from isaaclab_b200 import _lib
+    _lib.lib()
+    peak = _peak()
+    mg = {"global_rank": rank, "local_rank": local, "world_size": world} if world > 1 else None
+    wanted = [c.strip() for c in args.configs.split(",") if c.strip()]
+    records, head, clocks, head_data = {}, None, None, None
+    for cfg_id in [HEADLINE] + [c for c in wanted if c != HEADLINE]:
+        c = CONFIGS[cfg_id]
+        is_head = cfg_id == HEADLINE
+        envs = args.envs if (is_head and args.envs) else c["envs"]
+        steps = args.steps if is_head else max(20, min(args.steps, args.sub_steps))
+        warm = args.warmup if is_head else max(3, min(args.warmup, 10))
+        cfg, spec, slabs, init = build_workload(cfg_id, seed=rank, device=dev, envs=envs)
+        rec = {"workload": workload_name(cfg_id, spec), "envs_per_gpu": spec["N"], "steps": steps}
+        if c["env_arms"]:
+            # the clock sampler polls NVML on rank 0 only, and only around the headline's timed loop
+            sampler = ClockSampler(local) if (is_head and rank == 0) else None
+            env_rec, ck = measure_env(cfg_id, spec, slabs, init, steps, warm, world, rank, dev, peak, sampler)
+            rec.update(env_rec)
+            rec["e2e"] = measure_e2e(cfg, spec, slabs, init, max(20, steps // (1 if is_head else 2)), warm, world, rank, dev)
+            if is_head:
+                clocks = ck
+        if cfg_id != "cfg2" or not args.quick:
+            rec["ppo_update"] = ppo_record(dev, ppo_cfg(cfg_id, spec, envs), mg, reps=3 if is_head else 2)
+        records[cfg_id] = rec
+        if is_head:
+            head, head_data = rec, (spec, slabs, init)
+        else:
+            del slabs
+    spec, slabs, init = head_data
+    N = spec["N"]
+    out = {"metric": METRIC, "value": head["value"], "unit": UNIT, "n_gpus": world, "steps": args.steps,
+           "warmup": args.warmup, "ms_per_step": head["ms_per_step"], "higher_is_better": True, "scaling": "weak",
+           "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+           "config": {"workload": head["workload"], "envs_per_gpu": N,
+                      "value_mode": "device-resident state, the fused step (decimation_fused, post_step, post_reset_write || "
+                                    "compute_obs) replayed as one CUDA graph per state slab",
+                      "e2e_mode": "ManagerBasedRLEnv.step(action, results_out) with pinned host buffers, the step captured "
+                                  "as a CUDA graph per staging set (H2D action, kernels, D2H of reward/masks after "
+                                  "post_step and of the obs rows range by range behind the obs kernels); results "
+                                  "synchronised every step; next step's simulator state prefetched H2D on a copy "
+                                  "stream while the current step computes",
+                      "l2_policy": f"{head['slabs']} state slabs ({head['slab_bytes_total'] >> 20} MiB > 126 MB L2) cycled",
+                      "parallelism": f"env-shard x{world}"},
+           "clocks": clocks, "e2e": head["e2e"], "gpu_launches": int(head["launches_per_step"]) * args.steps,
+           "roofline": head["roofline"], "live": head["live"], "replay_eager_ms_per_step": head["replay_eager_ms_per_step"],
+           "ppo_update": head.get("ppo_update"), "configs": records}
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        out["cpu_baseline"] = cpu_env_baseline(HEADLINE, spec, slabs, init, budget_s=12.0)
+        out["cpu_baseline"]["ppo_update"] = cpu_ppo_baseline(ppo_cfg(HEADLINE, spec))
+    if world > 1:
+        dist.destroy_process_group()
+    return json.dumps(out) if rank == 0 else None
+
+
 def run_reference(args):
+    """The reference arm: the reference's own CPU implementation of the path on the host cores (rank 0 only), on the
+    headline config; each "step" = one full 4096-env step, bounded so that the W+K run ends within minutes."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
-        return
-    cfg, spec, slabs, init = build_workload("cpu", seed=0)
-    # each "step" of this arm = one full env step on the CPU; bounded so W+K steps end within minutes
-    cb = cpu_baseline(spec, slabs, init, budget_s=20.0, max_steps=max(2, args.steps))
+        return None
+    cfg, spec, slabs, init = build_workload(HEADLINE, seed=0)
+    cb = cpu_env_baseline(HEADLINE, spec, slabs, init, budget_s=25.0, max_steps=max(2, args.steps))
     out = {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": int(os.environ.get("WORLD_SIZE", "1")),
            "steps": args.steps, "warmup": args.warmup, "ms_per_step": cb["ms_per_step"], "higher_is_better": True,
            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-           "config": {"workload": workload_name(spec), "envs_per_gpu": spec["N"],
-                      "arm": "reference torch path restated (oracle port) on the host cores; each step = one full env step"},
-           "cpu_baseline": cb, "ppo_update": cpu_ppo_baseline(), "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+           "config": {"workload": workload_name(HEADLINE, spec), "envs_per_gpu": spec["N"],
+                      "arm": "the unmodified reference ManagerBasedRLEnv.step (baseline/_ref) on the host cores"
+                             if cb["kind"] == "reference" else "oracle port of the reference torch path on the host cores "
+                             "(fallback: " + cb.get("fallback_reason", "") + ")"},
+           "cpu_baseline": cb, "ppo_update": cpu_ppo_baseline(ppo_cfg(HEADLINE, spec)),
+           "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     return json.dumps(out)
 
 
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=2000)
+    ap.add_argument("--steps", type=int, default=1000)
     ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--impl", default="ours")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--envs", type=int, default=ENVS_PER_GPU,
-                    help="envs per GPU; anything but the default is an exploration run, not the headline workload")
+    ap.add_argument("--configs", default="cfg1,cfg2,cfg3,cfg4,cfg5", help="BASELINE configs to add as sub-records")
+    ap.add_argument("--sub-steps", type=int, default=200, help="timed steps of the non-headline configs")
+    ap.add_argument("--quick", action="store_true")
+    ap.add_argument("--envs", type=int, default=0,
+                    help="headline envs per GPU; anything but the default is an exploration run, not the headline workload")
     args = ap.parse_args()
-    if args.envs != ENVS_PER_GPU:
-        globals()["ENVS_PER_GPU"] = args.envs
-        globals()["K_SLABS"] = max(4, min(32, (32 * 4096) // args.envs))   # keep the cycled slabs > L2 but bounded
-        PPO_CFG["N"] = args.envs
     args.warmup = max(args.warmup, 3)
     # The contract is ONE JSON line on stdout.  Native libraries write there too (NCCL prints its version banner to fd 1
     # under NCCL_DEBUG=VERSION), so fd 1 is pointed at stderr for the run and the JSON line goes to the saved descriptor.

@@ -36,8 +36,12 @@ class HostReplaySim:
         self.spec, self.S = spec, spec["decimation"]
         self.K = slabs_cpu["root_state_w"].shape[0]
         has_contact = spec.get("contact") is not None
+        # body velocities cross PCIe only when a term reads them (feet_slide); net forces only with a contact sensor
+        needs_body_vel = any(t["op"] == "feet_slide" for t in spec["rewards"])
         self._fields, off = [], 0
         for name in self._ORDER:
+            if (name == "body_lin_vel_w" and not needs_body_vel) or (name == "net_forces_w" and not has_contact):
+                continue
             v = slabs_cpu[name]
             nbytes = v[0].numel() * v.element_size()
             self._fields.append((name, off, nbytes, tuple(v.shape[1:]), v.dtype))
@@ -53,7 +57,8 @@ class HostReplaySim:
             self.stage.append(buf)
             self.dev.append(st)
             self._views.append([SimView(st["root_state_w"], st["joint_pos"][s], st["joint_vel"][s],
-                                        st["net_forces_w"][s] if has_contact else None, st["body_lin_vel_w"])
+                                        st["net_forces_w"][s] if has_contact else None,
+                                        st["body_lin_vel_w"] if needs_body_vel else None)
                                 for s in range(self.S)])
         self.h2d_bytes_per_step = sum(f[2] for f in self._fields)
         self.prefetch_enabled = prefetch
