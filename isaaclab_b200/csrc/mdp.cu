@@ -47,8 +47,9 @@ struct EnvHandle {
   // env (process_action, decimation_fused, substep_pre/post, env_update)
   const float* derived_root;   // root_state_w pointer of the view post_step derived from (or NULL)
   bool lstm_const;
+  bool mlp_const;          // the ActuatorNetMLP has the 6-32-32-32-1 shape of NetMlp63 (compile-time-shaped kernels)
   const float* lstm_src;   // device pointer the copy was taken from
-  float lstm_w[1024];   // packed NetLstm<8,2> image (see NetLstm)
+  float lstm_w[2560];   // packed NetLstm<8,2> image (see NetLstm) or the raw NetMlp<6,32,3> weights
 };
 
 typedef B200LabEnvState Env;
@@ -222,7 +223,7 @@ __device__ __forceinline__ float lstm_forward(const float* __restrict__ w, int L
 // Every lane of a warp reads the same weight.  From shared memory that is one LDS per FMA, and the single LSU port per SM
 // (vs. four FMA pipes) makes the cell LDS-bound; as immediate-offset constant-bank operands the weights ride on the FFMA
 // itself and no load instruction is issued.  All indices below are compile-time after unrolling (H, L template params).
-struct NetNone { static constexpr bool kLstm = false; };
+struct NetNone { static constexpr bool kLstm = false, kMlp = false; };
 
 // Packed layout for the two-wide FMA (fma.rn.f32x2 -> FFMA2, one FMA-pipe slot for two IEEE fp32 FMAs; the cell is
 // FMA-pipe bound).  Two gate rows of the same hidden unit share their input vector, so the rows are paired --
@@ -232,7 +233,7 @@ struct NetNone { static constexpr bool kLstm = false; };
 // Every half of an FFMA2 is the scalar fmaf of the unpacked code, in the same order: results are bitwise unchanged.
 template <int H, int L>
 struct NetLstm {
-  static constexpr bool kLstm = true;
+  static constexpr bool kLstm = true, kMlp = false;
   static constexpr int kH = H, kL = L;
   static constexpr int kRawCount = (4 * H * 2 + 4 * H * H + 8 * H) + (L - 1) * (8 * H * H + 8 * H) + H + 1;
   static constexpr int in_dim(int l) { return l == 0 ? 2 : H; }
@@ -374,6 +375,130 @@ __device__ __forceinline__ float mlp_forward32(const float* __restrict__ w, cons
   return a[0];
 }
 
+// ---- ActuatorNetMLP with compile-time shape, weights as a kernel parameter (constant bank) -------------------------------
+// IN inputs -> NH hidden layers of width H -> 1 (the walk-these-ways actuator net of the Unitree configs: 6-32-32-32-1).
+// Raw layout as the host packs it (b200lab.h): W0[H,IN] b0[H] W1[H,H] b1[H] ... Wout[1,H] bout[1].  The accumulation order
+// is the one of mlp_forward32 (acc = bias; acc = fmaf(W[o][i], a[i], acc) for i ascending) => bitwise the same torques;
+// what changes is that no load instruction is issued per FMA and no predicated padding up to 32 x 32 is executed.
+template <int IN, int H, int NH>
+struct NetMlp {
+  static constexpr bool kLstm = false, kMlp = true;
+  static constexpr int kIn = IN, kH = H, kNH = NH;
+  static constexpr int kCount = IN * H + H + (NH - 1) * (H * H + H) + H + 1;
+  // shape tag only: 9.5 KB of weights as constant-bank operands thrash the constant cache (measured: 461 us per fused
+  // launch at 16384 envs), so the weights are staged in shared memory and the H-wide rows are read with 128-bit loads
+};
+
+// shared-memory weight loads as volatile asm: the weights are invariant across the sub-step loop, and the compiler would
+// otherwise hoist all 2369 of them out of it and spill them to local memory (9.5 KB stack frame)
+__device__ __forceinline__ float lds1(const float* p) {
+  float v;
+  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"((unsigned)__cvta_generic_to_shared(p)));
+  return v;
+}
+__device__ __forceinline__ float4 lds4(const float* p) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"((unsigned)__cvta_generic_to_shared(p)));
+  return v;
+}
+
+// softsign through the SFU reciprocal (1 ulp-level error; torque tolerance of the parity tests is 2e-5, as for the
+// LSTM's SFU gate activations): the IEEE division was a third of the net's instructions
+__device__ __forceinline__ float mlp_act_fast(float x, int kind) {
+  if (kind == 0) return x * rcp_ftz(1.0f + fabsf(x));
+  return mlp_act(x, kind);
+}
+
+// `sb`: this thread's column of a [H][stride] shared-memory scratch (element o at sb[o * stride]; thread-contiguous =>
+// conflict-free).  The loop over output neurons is ROLLED -- fully unrolled the net is ~70 KB of code and the kernel
+// stalls on instruction fetch (ncu: no_instruction 5.8 per issue, issue-active 29 %) -- so a layer's outputs are parked in
+// `sb` and re-read into registers for the next layer's unrolled 128-bit-weight inner products.
+template <class Net>
+__device__ __forceinline__ float mlp_const(const float* w, float* sb, int stride, const float (&in)[Net::kIn], int act) {
+  constexpr int IN = Net::kIn, H = Net::kH, NH = Net::kNH;
+  static_assert(H % 4 == 0 && (IN * H + H) % 4 == 0, "128-bit weight rows");
+  float a[H];
+#pragma unroll 1
+  for (int o = 0; o < H; ++o) {
+    float acc = lds1(w + IN * H + o);
+#pragma unroll
+    for (int i = 0; i < IN; ++i) acc = fmaf(lds1(w + o * IN + i), in[i], acc);
+    sb[o * stride] = mlp_act_fast(acc, act);
+  }
+#pragma unroll 1
+  for (int l = 1; l < NH; ++l) {
+    const float* wl = w + (IN * H + H) + (l - 1) * (H * H + H);
+#pragma unroll
+    for (int i = 0; i < H; ++i) a[i] = sb[i * stride];
+#pragma unroll 1
+    for (int o = 0; o < H; ++o) {
+      float acc = lds1(wl + H * H + o);
+#pragma unroll
+      for (int i = 0; i < H; i += 4) {
+        const float4 w4 = lds4(wl + o * H + i);
+        acc = fmaf(w4.x, a[i], acc); acc = fmaf(w4.y, a[i + 1], acc); acc = fmaf(w4.z, a[i + 2], acc); acc = fmaf(w4.w, a[i + 3], acc);
+      }
+      sb[o * stride] = mlp_act_fast(acc, act);
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < H; ++i) a[i] = sb[i * stride];
+  const float* wo = w + (IN * H + H) + (NH - 1) * (H * H + H);
+  float out = lds1(wo + H);
+#pragma unroll
+  for (int i = 0; i < H; i += 4) {
+    const float4 w4 = lds4(wo + i);
+    out = fmaf(w4.x, a[i], out); out = fmaf(w4.y, a[i + 1], out); out = fmaf(w4.z, a[i + 2], out); out = fmaf(w4.w, a[i + 3], out);
+  }
+  return out;
+}
+
+constexpr int kMlpMaxHist = 4;
+__device__ __forceinline__ float hist_at(const float (&h)[kMlpMaxHist], int idx) {
+  return idx == 0 ? h[0] : idx == 1 ? h[1] : idx == 2 ? h[2] : h[3];
+}
+
+// one ActuatorNetMLP evaluation on register-resident histories (actuator_net.py:147-189): roll, insert, select, scale, net
+template <class Net>
+__device__ __forceinline__ float mlp_actuator_step(const float* w, float* sb, int stride, const B200LabActuatorGroup& g, float err_p, float qd,
+                                                   float (&ph)[kMlpMaxHist], float (&vh)[kMlpMaxHist]) {
+#pragma unroll
+  for (int k = kMlpMaxHist - 1; k > 0; --k) { ph[k] = ph[k - 1]; vh[k] = vh[k - 1]; }   // slots >= hist are never read
+  ph[0] = err_p; vh[0] = qd;
+  constexpr int NI = Net::kIn / 2;
+  float in[Net::kIn];
+#pragma unroll
+  for (int k = 0; k < NI; ++k) {
+    const float pv = hist_at(ph, g.mlp_input_idx[k]) * g.mlp_pos_scale;
+    const float vv = hist_at(vh, g.mlp_input_idx[k]) * g.mlp_vel_scale;
+    if (g.mlp_vel_pos_order) { in[k] = vv; in[NI + k] = pv; } else { in[k] = pv; in[NI + k] = vv; }
+  }
+  return mlp_const<Net>(w, sb, stride, in, g.mlp_act) * g.mlp_torque_scale;
+}
+
+template <int HIST_MAX = kMlpMaxHist>
+__device__ __forceinline__ void mlp_hist_load(const B200LabActuatorGroup& g, int n, int jl, float (&ph)[HIST_MAX], float (&vh)[HIST_MAX]) {
+  const int Jg = g.group_joints, Hh = g.mlp_hist;
+#pragma unroll
+  for (int k = 0; k < HIST_MAX; ++k) {
+    ph[k] = vh[k] = 0.f;
+    if (k < Hh) {
+      ph[k] = g.mlp_pos_hist[((int64_t)n * Hh + k) * Jg + jl];
+      vh[k] = g.mlp_vel_hist[((int64_t)n * Hh + k) * Jg + jl];
+    }
+  }
+}
+template <int HIST_MAX = kMlpMaxHist>
+__device__ __forceinline__ void mlp_hist_store(const B200LabActuatorGroup& g, int n, int jl, const float (&ph)[HIST_MAX], const float (&vh)[HIST_MAX]) {
+  const int Jg = g.group_joints, Hh = g.mlp_hist;
+#pragma unroll
+  for (int k = 0; k < HIST_MAX; ++k)
+    if (k < Hh) {
+      g.mlp_pos_hist[((int64_t)n * Hh + k) * Jg + jl] = ph[k];
+      g.mlp_vel_hist[((int64_t)n * Hh + k) * Jg + jl] = vh[k];
+    }
+}
+
 // stage the weights of the (single) net-based actuator group, if any, in shared memory (block-cooperative)
 __device__ __forceinline__ void stage_net_weights(const Env* __restrict__ e, float* s_w) {
   int net_group = -1;
@@ -475,6 +600,18 @@ substep_pre_kernel(const __grid_constant__ Env env_param, Sim sim, bool apply_ac
       computed = lstm_cells_const(net, q_t - sim.joint_pos[gid], qd, h, c);   // actuator_net.py:76-90
       applied = dc_motor_clip(computed, qd, g.saturation_effort, g.velocity_limit[j], g.effort_limit[j]);
       lstm_state_store<Net>(g, row, rows, h, c);
+      done = true;
+    }
+  }
+  if constexpr (Net::kMlp) {
+    if (g.kind == B200LAB_ACT_NET_MLP) {
+      float ph[kMlpMaxHist], vh[kMlpMaxHist];
+      const int jl = e->joint_local[j];
+      mlp_hist_load(g, n, jl, ph, vh);
+      const float qd = sim.joint_vel[gid];
+      computed = mlp_actuator_step<Net>(s_w, s_w + ((Net::kCount + 3) & ~3) + threadIdx.x, (int)blockDim.x, g, q_t - sim.joint_pos[gid], qd, ph, vh);
+      applied = dc_motor_clip(computed, qd, g.saturation_effort, g.velocity_limit[j], g.effort_limit[j]);
+      mlp_hist_store(g, n, jl, ph, vh);
       done = true;
     }
   }
@@ -658,6 +795,28 @@ decimation_fused_kernel(const __grid_constant__ Env env_param, const float* __re
           qd = qdn;
         }
         lstm_state_store<Net>(g, row, rows, h, c);
+        done = true;
+      }
+    }
+    if constexpr (Net::kMlp) {
+      if (gi >= 0 && e->act[gi].kind == B200LAB_ACT_NET_MLP) {
+        // the position-error / velocity histories stay in registers across the S evaluations (actuator_net.py:147-189)
+        const B200LabActuatorGroup& g = e->act[gi];
+        float ph[kMlpMaxHist], vh[kMlpMaxHist];
+        const int jl = e->joint_local[j];
+        mlp_hist_load(g, n, jl, ph, vh);
+        const float sat = g.saturation_effort, vlim = g.velocity_limit[j], elim = g.effort_limit[j];
+#pragma unroll 1
+        for (int s = 0; s < S; ++s) {
+          const float qn = sv.v[s].joint_pos[o], qdn = sv.v[s].joint_vel[o];
+          computed = mlp_actuator_step<Net>(s_w, s_w + ((Net::kCount + 3) & ~3) + threadIdx.x, (int)blockDim.x, g, q_t - q, qd, ph, vh);
+          applied = dc_motor_clip(computed, qd, sat, vlim, elim);
+          acc = (qdn - prev_qd) / dt;
+          prev_qd = qdn;
+          q = qn;
+          qd = qdn;
+        }
+        mlp_hist_store(g, n, jl, ph, vh);
         done = true;
       }
     }
@@ -1942,13 +2101,32 @@ static int upload_obs_tables(EnvHandle* h) {
 }
 
 typedef NetLstm<8, 2> NetLstm82;
-static_assert(sizeof(NetLstm82) <= 1024 * sizeof(float), "EnvHandle::lstm_w too small");
+typedef NetMlp<6, 32, 3> NetMlp63;
+static_assert(sizeof(NetLstm82) <= 2560 * sizeof(float), "EnvHandle::lstm_w too small");
+
+// dynamic shared memory of the NetMlp63 kernels: raw weights (16-byte padded) + one [H][threads] activation scratch
+static size_t mlp63_smem(int threads) {
+  return (size_t)(((NetMlp63::kCount + 3) & ~3) + NetMlp63::kH * threads) * sizeof(float);
+}
 
 static int stage_const_net(EnvHandle* h) {
   const B200LabEnvState& s = h->host;
   const B200LabActuatorGroup* net = nullptr;
   for (int g = 0; g < s.num_act_groups; ++g)
     if (s.act[g].kind == B200LAB_ACT_NET_LSTM) net = &s.act[g];
+  // ActuatorNetMLP of the shape that has a constant-bank instantiation (6-32-32-32-1, history <= 4)
+  const B200LabActuatorGroup* mlp = nullptr;
+  for (int g = 0; g < s.num_act_groups; ++g)
+    if (s.act[g].kind == B200LAB_ACT_NET_MLP) mlp = &s.act[g];
+  h->mlp_const = false;
+  if (!net && mlp && mlp->net_weights && mlp->mlp_layers == NetMlp63::kNH + 1 && mlp->mlp_dims[0] == NetMlp63::kIn &&
+      mlp->mlp_dims[1] == NetMlp63::kH && mlp->mlp_dims[2] == NetMlp63::kH && mlp->mlp_dims[3] == NetMlp63::kH &&
+      mlp->mlp_dims[4] == 1 && mlp->mlp_hist <= kMlpMaxHist && 2 * mlp->mlp_num_idx == NetMlp63::kIn) {
+    h->mlp_const = true;
+    h->lstm_const = false;
+    h->lstm_src = nullptr;
+    return B200LAB_OK;
+  }
   if (!net || net->lstm_hidden != NetLstm82::kH || net->lstm_layers != NetLstm82::kL || !net->net_weights) {
     h->lstm_const = false;
     h->lstm_src = nullptr;
@@ -1994,6 +2172,8 @@ static void launch_substep_pre(EnvHandle* h, const B200LabSimView* sim, bool app
   if (h->lstm_const)
     substep_pre_kernel<NetLstm82><<<blocks, kActBlock, 0, stream>>>(h->host, *sim, apply_action, only_if_any_reset,
                                                                     *reinterpret_cast<const NetLstm82*>(h->lstm_w));
+  else if (h->mlp_const)
+    substep_pre_kernel<NetMlp63><<<blocks, kActBlock, mlp63_smem(kActBlock), stream>>>(h->host, *sim, apply_action, only_if_any_reset, NetMlp63{});
   else
     substep_pre_kernel<NetNone><<<blocks, kActBlock, smem, stream>>>(h->host, *sim, apply_action, only_if_any_reset, NetNone{});
 }
@@ -2018,6 +2198,7 @@ void* b200lab_env_create(const B200LabEnvState* st) {
   h->spec_pending = false;
   h->derived = nullptr;
   h->lstm_const = false;
+  h->mlp_const = false;
   h->lstm_src = nullptr;
   h->dev = nullptr;
   h->side = nullptr;
@@ -2206,6 +2387,9 @@ int b200lab_decimation_fused(void* env, const float* action_in, const B200LabSim
   if (h->lstm_const) {
     decimation_fused_kernel<NetLstm82><<<(unsigned)(joint_blocks + body_blocks), kFusedBlock, 0, (cudaStream_t)stream>>>(
         h->host, action_in, sv, joint_blocks, W, epb, *reinterpret_cast<const NetLstm82*>(h->lstm_w));
+  } else if (h->mlp_const) {
+    decimation_fused_kernel<NetMlp63><<<(unsigned)(joint_blocks + body_blocks), kFusedBlock, mlp63_smem(kFusedBlock), (cudaStream_t)stream>>>(
+        h->host, action_in, sv, joint_blocks, W, epb, NetMlp63{});
   } else {
     decimation_fused_kernel<NetNone><<<(unsigned)(joint_blocks + body_blocks), kFusedBlock, smem, (cudaStream_t)stream>>>(
         h->host, action_in, sv, joint_blocks, W, epb, NetNone{});
