@@ -338,7 +338,10 @@ typedef struct B200LabEnvState {
    * read by post_reset_write (required by that call, else optional) */
   int32_t* any_reset_dev;
   /* --- episode log accumulators (extras["log"], LAB/envs/manager_based_rl_env.py:365-389) --- */
-  double* log_accum;           /* [B200LAB_LOG_SLOTS] doubles, zeroed by the caller before post_step */
+  double* log_accum;           /* [B200LAB_LOG_SLOTS] per-step sums over the envs reset in this step (post_step adds,
+                                  b200lab_log_fold consumes and zeroes) */
+  double* log_running;         /* [2 * B200LAB_LOG_SLOTS] or NULL: running sums of the per-step log VALUES (slot 0 = number of
+                                  steps that had resets), then the values of the last folded step (slot 0 = its reset count) */
 } B200LabEnvState;
 
 /* Layout of u_reset columns (per reset env): */
@@ -355,6 +358,16 @@ typedef struct B200LabEnvState {
 /* log_accum layout: [0] = number of reset envs; [1 .. 1+num_rew) = sum over reset envs of episode_sums;
  * then num_term termination counts; then 2 command metric sums; then 1 terrain level sum (all envs). */
 #define B200LAB_LOG_SLOTS 128
+/* extras["log"] with the reference's semantics (manager_based_rl_env.py:365-389: one dict per step that had resets, each
+ * value a statistic over THAT step's reset envs; the runner averages the dicts).  Per-step values, in log_accum's slot
+ * order: Episode_Reward/<term> = mean over the step's reset envs of the episodic sum / max_episode_length_s
+ * (reward_manager.py:100-126); Episode_Termination/<term> = number of those envs the term fired for
+ * (termination_manager.py:127-149); Metrics/<command>/error_vel_{xy,yaw} = mean metric (command_manager.py:120-149);
+ * slot 3+num_rew+num_term: Curriculum/terrain_levels = mean level over ALL envs (curriculums.py:55).
+ * b200lab_log_fold turns the sums post_step left in log_accum into these values, adds them to log_running, keeps them as
+ * "last step", and zeroes log_accum.  b200lab_step_tail[_begin] issues it on the library's side stream; callers that use
+ * post_step / compute_obs separately call it once per step after post_step. */
+int b200lab_log_fold(void* env, void* stream);
 
 /* The env descriptor is uploaded to the device once; kernels read it through a pointer (it is constant per
  * environment instance).  b200lab_env_update re-uploads after a cfg change (e.g. RewardManager.set_term_cfg). */

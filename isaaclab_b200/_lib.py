@@ -99,6 +99,7 @@ _SIGS = {
     "b200lab_post_reset_write": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
     "b200lab_step_tail": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]),
     "b200lab_compute_obs": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]),
+    "b200lab_log_fold": (C.c_int, [C.c_void_p, C.c_void_p]),
     "b200lab_compute_obs_range": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_int32, C.c_void_p]),
     "b200lab_step_tail_begin": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
     "b200lab_step_tail_end": (C.c_int, [C.c_void_p, C.c_void_p]),

@@ -2008,6 +2008,43 @@ compute_obs_patch_kernel(const __grid_constant__ Env env_param, Sim sim, int64_t
 }
 
 
+// extras["log"] fold (see b200lab.h): one block; runs on the side stream of step_tail, off the critical path
+__global__ void __launch_bounds__(256)
+log_fold_kernel(const __grid_constant__ Env env_param) {
+  const Env* __restrict__ e = &env_param;
+  __shared__ double s_red[256];
+  const int tid = threadIdx.x, nr = e->num_rew, nt = e->num_term;
+  const double cnt = e->log_accum[0];
+  double lv = 0.0;
+  if (cnt > 0.0 && e->has_terrain_curriculum)
+    for (int n = tid; n < e->N; n += blockDim.x) lv += (double)e->terrain_levels[n];
+  s_red[tid] = lv;
+  __syncthreads();
+  for (int o = 128; o > 0; o >>= 1) {
+    if (tid < o) s_red[tid] += s_red[tid + o];
+    __syncthreads();
+  }
+  const double mean_level = s_red[0] / (double)e->N;
+  const int slots = 4 + nr + nt;
+  double* run = e->log_running;
+  double* last = run + B200LAB_LOG_SLOTS;
+  for (int i = tid; i < slots; i += blockDim.x) {
+    double v = 0.0;
+    if (cnt > 0.0) {
+      const double a = e->log_accum[i];
+      if (i == 0) v = 1.0;
+      else if (i < 1 + nr) v = a / cnt / (double)e->max_episode_length_s;
+      else if (i < 1 + nr + nt) v = a;
+      else if (i < 3 + nr + nt) v = a / cnt;
+      else v = mean_level;
+      run[i] += v;
+    }
+    last[i] = i == 0 ? cnt : v;
+  }
+  __syncthreads();
+  for (int i = tid; i < slots; i += blockDim.x) e->log_accum[i] = 0.0;
+}
+
 static int launch_geometry(int width, int* wpad, int* epb) {
   int w = width < 1 ? 1 : width;
   if (w > 256) return -1;
@@ -2471,6 +2508,16 @@ int b200lab_compute_obs_range(void* env, const B200LabSimView* sim, int64_t step
   return check_launch("compute_obs");
 }
 
+int b200lab_log_fold(void* env, void* stream) {
+  B200LAB_CHECK_ARG(env, "null argument");
+  EnvHandle* h = (EnvHandle*)env;
+  if (!h->host.log_accum || !h->host.log_running) return B200LAB_OK;
+  B200LAB_CHECK_ARG(4 + h->host.num_rew + h->host.num_term <= B200LAB_LOG_SLOTS, "too many log slots");
+  log_fold_kernel<<<1, 256, 0, (cudaStream_t)stream>>>(h->host);
+  count_launch();
+  return check_launch("log_fold");
+}
+
 int b200lab_compute_obs(void* env, const B200LabSimView* sim, int64_t step_counter, void* stream) {
   B200LAB_CHECK_ARG(env, "null argument");
   return b200lab_compute_obs_range(env, sim, step_counter, 0, ((EnvHandle*)env)->host.N, stream);
@@ -2486,6 +2533,8 @@ int b200lab_step_tail_begin(void* env, const B200LabSimView* sim, void* stream) 
   if (err == cudaSuccess) err = cudaStreamWaitEvent(h->side, h->ev_fork, 0);
   if (err != cudaSuccess) { set_error("b200lab_step_tail: %s", cudaGetErrorString(err)); return B200LAB_ERR_CUDA; }
   int rc = b200lab_post_reset_write(env, sim, h->side);
+  if (rc) return rc;
+  rc = b200lab_log_fold(env, h->side);
   if (rc) return rc;
   err = cudaEventRecord(h->ev_join, h->side);
   if (err != cudaSuccess) { set_error("b200lab_step_tail: %s", cudaGetErrorString(err)); return B200LAB_ERR_CUDA; }

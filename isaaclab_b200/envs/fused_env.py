@@ -406,6 +406,8 @@ class FusedEnv:
         st.n_u_reset, st.n_u_step = self.n_u_reset, self.n_u_step
         self.log_accum = z(C["B200LAB_LOG_SLOTS"], dtype=torch.float64)
         st.log_accum = p(self.log_accum)
+        self.log_running = z(2 * C["B200LAB_LOG_SLOTS"], dtype=torch.float64)
+        st.log_running = p(self.log_running)
         self.any_reset = z(1, dtype=torch.int32)
         st.any_reset_dev = p(self.any_reset)
         self._u = (None, None, None)
@@ -463,6 +465,47 @@ class FusedEnv:
 
     def post_step(self, sim: SimView):
         _lib.check(self.L.b200lab_post_step(self.handle, sim.ref, self.step_counter, _lib.current_stream()))
+
+    def log_fold(self):
+        """Folds the per-step log sums into extras["log"] values (b200lab_log_fold); `step_tail` does it itself."""
+        _lib.check(self.L.b200lab_log_fold(self.handle, _lib.current_stream()))
+
+    def log_keys(self):
+        """Keys of extras["log"] in slot order 1.. (manager_based_rl_env.py:365-389 of the reference)."""
+        s = self.spec
+        keys = ["Episode_Reward/" + t["name"] for t in s["rewards"]]
+        keys += ["Episode_Termination/" + t["name"] for t in s["terminations"]]
+        cname = s["command"]["name"] if s.get("command") else "base_velocity"
+        keys += [f"Metrics/{cname}/error_vel_xy", f"Metrics/{cname}/error_vel_yaw"]
+        keys += ["Curriculum/" + (s["curriculum"]["name"] if s.get("curriculum") else "terrain_levels")]
+        return keys
+
+    def _log_dict(self, vals):
+        s = self.spec
+        out = {}
+        for i, k in enumerate(self.log_keys()):
+            if k.startswith("Metrics/") and not s.get("command"):
+                continue
+            if k.startswith("Curriculum/") and not s.get("curriculum"):
+                continue
+            out[k] = float(vals[1 + i])
+        return out
+
+    def last_step_log(self):
+        """extras["log"] of the most recent step (one device->host read; {} when no env was reset in it)."""
+        S = C["B200LAB_LOG_SLOTS"]
+        v = self.log_running[S:].cpu()
+        return self._log_dict(v) if float(v[0]) > 0 else {}
+
+    def mean_log(self, reset: bool = True):
+        """Mean of the per-step extras["log"] dicts since the last call -- what the reference runner computes from the
+        dicts it collects (on_policy_runner.py:log) -- from ONE device->host read."""
+        S = C["B200LAB_LOG_SLOTS"]
+        v = self.log_running[:S].cpu()
+        if reset:
+            self.log_running[:S].zero_()
+        n = float(v[0])
+        return self._log_dict(v / n) if n > 0 else {}
 
     def post_reset_write(self, sim: SimView):
         """`scene.write_data_to_sim()` after `_reset_idx` (manager_based_rl_env.py:217-223); device-side condition."""
@@ -529,6 +572,7 @@ class FusedEnv:
             self.step_tail(prev)
         else:
             self.post_reset_write(prev)
+            self.log_fold()
             self.compute_obs(prev)
         self.step_counter += 1
         return self.obs_buf, self.reward_buf, self.terminated, self.truncated

@@ -194,7 +194,12 @@ class ObservationManager(_ManagerView):
 
 
 class ManagerBasedRLEnv:
-    def __init__(self, cfg, sim=None, device="cuda", num_envs=None, terrain=None, seed=0, spec=None, use_cuda_graph=False):
+    def __init__(self, cfg, sim=None, device="cuda", num_envs=None, terrain=None, seed=0, spec=None, use_cuda_graph=False,
+                 log_every_step=False):
+        """`log_every_step=True`: `extras["log"]` is filled after every step that reset an env, as the reference does
+        (one device->host read per step).  Default: the log is accumulated on the device and read once per iteration
+        through `episode_log()` (what the runner mirror does) -- same values after the runner's averaging."""
+        self.log_every_step = bool(log_every_step)
         self.cfg = cfg
         self.device = torch.device(device)
         self.spec = spec if spec is not None else compile_env_cfg(cfg, num_envs=num_envs, terrain=terrain, seed=seed)
@@ -386,6 +391,12 @@ class ManagerBasedRLEnv:
             else:
                 self._prefetch_next()
         self.common_step_counter += 1
+        if self.log_every_step:
+            log = self.fused.last_step_log()
+            if log:
+                self.extras["log"] = log
+            else:
+                self.extras.pop("log", None)
         return self.obs_buf, self.reward_buf, self.reset_terminated, self.reset_time_outs, self.extras
 
     def result_views(self, host_slab: torch.Tensor):
@@ -408,20 +419,6 @@ class ManagerBasedRLEnv:
                 **{k: host_slab[lay[k][0]:lay[k][1]] for k in ("terminated", "truncated", "reset_buf")}}
 
     def episode_log(self):
-        """extras["log"] aggregates (manager_based_rl_env.py:365-389) accumulated on the device since the last call;
-        ONE device->host read instead of the reference's per-reset `.item()` syncs."""
-        f, s = self.fused, self.spec
-        acc = f.log_accum.cpu()
-        f.log_accum.zero_()
-        n = float(acc[0])
-        log = {}
-        if n > 0:
-            nr, nt = len(s["rewards"]), len(s["terminations"])
-            for i, t in enumerate(s["rewards"]):
-                log["Episode_Reward/" + t["name"]] = float(acc[1 + i]) / n / s["max_episode_length_s"]
-            for i, t in enumerate(s["terminations"]):
-                log["Episode_Termination/" + t["name"]] = float(acc[1 + nr + i])
-            if s.get("command"):
-                log["Metrics/base_velocity/error_vel_xy"] = float(acc[1 + nr + nt]) / n
-                log["Metrics/base_velocity/error_vel_yaw"] = float(acc[2 + nr + nt]) / n
-        return log
+        """Mean of the per-step extras["log"] dicts (manager_based_rl_env.py:365-389) since the last call: the value the
+        reference runner logs for an iteration, read from the device ONCE instead of `.item()` syncs at every reset."""
+        return self.fused.mean_log()

@@ -65,6 +65,7 @@ def test_fused_step_matches_reference_golden(task, fused):
     sim = SyntheticSim(spec, K=steps + 1, device="cuda", slabs={k: v.clone() for k, v in fx["slabs"].items()})
     view = _AsOracle(fus, spec)
     prev = sim.views(0)[-1]
+    logs_seen, n_logs = {}, 0
     for k in range(steps):
         ref = fx["out"][k]
         ur, us_, uo = ref["u_reset"].cuda(), ref["u_step"].cuda(), ref["u_obs"].cuda()
@@ -83,7 +84,23 @@ def test_fused_step_matches_reference_golden(task, fused):
         for st_f, st_r in zip(fus.act_state, ref["act_state"]):
             for key in st_r:
                 close(st_f[key], st_r[key], tag + f" actuator state {key}", rtol=1e-4, atol=1e-5)
+        # extras["log"] of this step (manager_based_rl_env.py:365-389 of the reference): same keys, same values
+        log = fus.last_step_log()
+        if int(ref["reset_buf"].sum()) == 0:   # the reference's extras["log"] then still holds an older step's dict
+            assert log == {}
+        else:
+            assert set(log) == set(ref["log"]), f"{tag}: log keys {sorted(set(log) ^ set(ref['log']))} differ"
+            for key, val in ref["log"].items():
+                assert abs(log[key] - val) <= 1e-5 + 1e-5 * abs(val), f"{tag}: log[{key}] {log[key]} vs {val}"
+                logs_seen[key] = logs_seen.get(key, 0.0) + val
+            n_logs += 1
         prev = sim.views(k + 1)[-1]
+    # the device-side mean over the steps that had resets == the mean of the reference's per-step dicts
+    mean = fus.mean_log()
+    assert n_logs > 0 and set(mean) == set(logs_seen)
+    for key, tot in logs_seen.items():
+        assert abs(mean[key] - tot / n_logs) <= 1e-5 + 1e-5 * abs(tot / n_logs), f"{task}: mean log[{key}]"
+    assert fus.mean_log() == {}, "mean_log() did not reset the running sums"
 
 
 @pytest.mark.parametrize("task", ["Isaac-Velocity-Rough-Anymal-C-v0", "Isaac-Cartpole-v0"])
