@@ -62,23 +62,69 @@ def _per_joint(val, names, default=None):
     return out
 
 
-def _resolve_func(func):
-    if isinstance(func, str):  # "module:attr" (manager_base.py:317-318)
+def _resolve_func(name, term_cfg, min_argc=1):
+    """ManagerBase._resolve_common_term_cfg (LAB/managers/manager_base.py:278-351): "module:attr" strings -> callables,
+    class terms must derive from ManagerTermBase, and the term's signature must be matched by `params` -- the same
+    exceptions with the same messages, raised at construction time."""
+    import inspect
+    from ..managers import ManagerTermBase
+    if not isinstance(term_cfg, ManagerTermBaseCfg):
+        raise TypeError(f"Configuration for the term '{name}' is not of type ManagerTermBaseCfg."
+                        f" Received: '{type(term_cfg)}'.")
+    func = term_cfg.func
+    if isinstance(func, str):  # string_to_callable, "module:attr" (manager_base.py:317-318)
         import importlib
-        mod, attr = func.split(":")
-        func = getattr(importlib.import_module(mod), attr)
+        try:
+            mod, attr = func.split(":")
+            func = getattr(importlib.import_module(mod), attr)
+        except Exception as e:
+            raise ValueError(f"Could not resolve the input string '{func}' into callable object. Received the error:\n {e}.")
+        term_cfg.func = func
     if not callable(func):
-        raise AttributeError(f"The term's function is not callable: {func}")
+        raise AttributeError(f"The term '{name}' is not callable. Received: {func}")
+    if inspect.isclass(func):
+        if not issubclass(func, ManagerTermBase):
+            raise TypeError(f"Configuration for the term '{name}' is not of type ManagerTermBase."
+                            f" Received: '{type(func)}'.")
+        func_static = func.__call__
+        min_argc += 1  # 'self'
+    else:
+        func_static = func
+    if hasattr(func, "_b200_op"):   # fused identities accept any params; each opcode checks its own in FusedEnv._term
+        return func
+    term_params = list(term_cfg.params.keys())
+    args = inspect.signature(func_static).parameters
+    with_defaults = [a for a in args if args[a].default is not inspect.Parameter.empty]
+    without_defaults = [a for a in args if args[a].default is inspect.Parameter.empty]
+    args = without_defaults + with_defaults
+    if len(args) > min_argc:
+        if set(args[min_argc:]) != set(term_params + with_defaults):
+            raise ValueError(f"The term '{name}' expects mandatory parameters: {without_defaults[min_argc:]}"
+                             f" and optional parameters: {with_defaults}, but received: {term_params}.")
     return func
 
 
-def _fused(func, name, kinds):
-    func = _resolve_func(func)
-    if not hasattr(func, "_b200_op") or func._b200_kind not in kinds:
-        raise NotImplementedError(
-            f"term '{name}': function {getattr(func, '__name__', func)} has no fused opcode; supported terms are the "
-            f"identities in isaaclab_b200.envs.mdp")
-    return func
+# modules whose functions ARE the fused term library under the reference's own names: a cfg that passes the reference's
+# function objects (isaaclab.envs.mdp.*, the locomotion-velocity and cartpole task mdp packages) compiles to the same
+# opcodes as one that passes isaaclab_b200.envs.mdp identities
+_REFERENCE_MDP_MODULES = ("isaaclab.envs.mdp.", "isaaclab_tasks.manager_based.locomotion.velocity.mdp.",
+                          "isaaclab_tasks.manager_based.classic.cartpole.mdp.")
+
+
+def _fused(term_cfg, name, kinds, min_argc=1):
+    """The fused identity behind a term's `func`, or None when the term has to be evaluated in Python every step
+    (`func(env, **params) -> Tensor`, LAB/managers/manager_term_cfg.py:29-52) and enters the kernels as an EXTERNAL column."""
+    func = _resolve_func(name, term_cfg, min_argc)
+    if hasattr(func, "_b200_op"):
+        if func._b200_kind not in kinds:
+            raise ValueError(f"term '{name}': {func._b200_op} is a {func._b200_kind} term, expected one of {kinds}")
+        return func
+    modname = (getattr(func, "__module__", "") or "") + "."
+    if modname.startswith(_REFERENCE_MDP_MODULES):
+        ident = mdp._REGISTRY.get(getattr(func, "__name__", ""))
+        if ident is not None and ident._b200_kind in kinds:
+            return ident
+    return None
 
 
 def compile_env_cfg(cfg: ManagerBasedRLEnvCfg, num_envs: int | None = None, terrain: "terrain_mod.TerrainGenerator" = None,
@@ -217,18 +263,30 @@ def compile_env_cfg(cfg: ManagerBasedRLEnvCfg, num_envs: int | None = None, terr
                 out[k] = v
         return out
 
+    def external(name, t):
+        """A term evaluated in Python every step as `func(env, **params)` (manager_term_cfg.py:29-52): SceneEntityCfg
+        params are resolved in place and handed to the function as objects, as the reference does
+        (manager_base.py:374-390); class terms are instantiated when the env is built (manager_base.py:393-395)."""
+        import inspect
+        for v in t.params.values():
+            if isinstance(v, SceneEntityCfg):
+                v.resolve(scene)
+        return {"name": name, "op": "external", "func": t.func, "params": dict(t.params), "is_class": inspect.isclass(t.func),
+                "cfg": t}
+
     # --- terminations / rewards
     spec["terminations"] = []
     for name, t in _terms(cfg.terminations):
-        f = _fused(t.func, name, ("term",))
-        spec["terminations"].append({"name": name, "op": f._b200_op, "time_out": bool(t.time_out),
-                                     **resolve_params(name, t.params)})
+        f = _fused(t, name, ("term",))
+        d = {"op": f._b200_op, **resolve_params(name, t.params)} if f is not None else external(name, t)
+        spec["terminations"].append({**d, "name": name, "time_out": bool(t.time_out)})
     spec["rewards"] = []
     for name, t in _terms(cfg.rewards):
         if not isinstance(t.weight, (float, int)):
             raise TypeError(f"Weight for the term '{name}' is not of type float or int. Received: '{type(t.weight)}'.")
-        f = _fused(t.func, name, ("rew",))
-        spec["rewards"].append({"name": name, "op": f._b200_op, "weight": float(t.weight), **resolve_params(name, t.params)})
+        f = _fused(t, name, ("rew",))
+        d = {"op": f._b200_op, **resolve_params(name, t.params)} if f is not None else external(name, t)
+        spec["rewards"].append({**d, "name": name, "weight": float(t.weight)})
     # --- observations: the policy group (concatenated)
     groups = _terms(cfg.observations)
     if len(groups) != 1:
@@ -243,8 +301,11 @@ def compile_env_cfg(cfg: ManagerBasedRLEnvCfg, num_envs: int | None = None, terr
             continue
         if t.modifiers or t.history_length:
             raise NotImplementedError(f"observation term '{name}': modifiers / history are not on the fused path")
-        f = _fused(t.func, name, ("obs",))
-        d = {"name": name, "op": f._b200_op, **f._b200_defaults, **resolve_params(name, t.params)}
+        f = _fused(t, name, ("obs",))
+        if f is not None:
+            d = {"name": name, "op": f._b200_op, **f._b200_defaults, **resolve_params(name, t.params)}
+        else:   # width inferred by calling the term once when the env is built (observation_manager.py:420-450)
+            d = {**external(name, t), "dim": None}
         if t.noise is not None and t.noise.operation not in ("add", "scale", "abs"):
             raise ValueError(f"Unknown operation in noise: {t.noise.operation}")   # noise_model.py:41,69,97
         if isinstance(t.noise, UniformNoiseCfg):
@@ -278,7 +339,10 @@ def compile_env_cfg(cfg: ManagerBasedRLEnvCfg, num_envs: int | None = None, terr
     # --- events
     ev = {"reset_joints": [], "interval_push": []}
     for name, t in _terms(cfg.events):
-        f = _fused(t.func, name, ("event",))
+        f = _fused(t, name, ("event",), min_argc=2)
+        if f is None:
+            raise NotImplementedError(f"event '{name}': user event terms write simulator state from Python; only the "
+                                      "event functions of isaaclab_b200.envs.mdp are on the fused path")
         op = f._b200_op
         if t.mode == "startup" or op == "apply_external_force_torque":
             continue  # PhysX property / wrench writers: simulator side, outside the non-physics step
@@ -301,7 +365,8 @@ def compile_env_cfg(cfg: ManagerBasedRLEnvCfg, num_envs: int | None = None, terr
     spec["events"] = ev
     # --- curriculum
     for name, t in _terms(cfg.curriculum):
-        _fused(t.func, name, ("curriculum",))
+        if _fused(t, name, ("curriculum",), min_argc=2) is None:
+            raise NotImplementedError(f"curriculum '{name}': only terrain_levels_vel is on the fused path")
         if terrain_info is None:
             raise ValueError("terrain_levels_vel needs the 'generator' terrain type")
         spec["curriculum"] = {"name": name, **terrain_info}

@@ -187,6 +187,12 @@ class FusedEnv:
     def _term(self, dst, kind, t):
         """Fill one B200LabTerm from a spec term dict."""
         prefix = {"rew": "B200LAB_REW_", "term": "B200LAB_TERM_", "obs": "B200LAB_OBS_"}[kind]
+        if t["op"] == "external":   # user term evaluated in Python: its value enters through ext_values[row .. row+dim)
+            dst.op = C[prefix + "EXTERNAL"]
+            dst.weight = float(t.get("weight", 0.0))
+            dst.time_out = 1 if t.get("time_out", False) else 0
+            dst.i0 = int(t["ext_row"])
+            return
         key = prefix + t["op"].upper()
         if key not in C:
             raise ValueError(f"term '{t['op']}' has no fused opcode ({key})")
@@ -275,6 +281,18 @@ class FusedEnv:
         st.max_episode_length = int(s["max_episode_length"])
         st.step_dt, st.physics_dt = float(s["step_dt"]), float(s["physics_dt"])
         st.max_episode_length_s = float(s["max_episode_length_s"])
+        # --- user (Python) terms: one row of ext_values per reward / termination term, `dim` rows per observation term
+        from . import term_dims as _tdx
+        row = 0
+        for t in list(s["terminations"]) + list(s["rewards"]):
+            if t["op"] == "external":
+                t["ext_row"], row = row, row + 1
+        for t in s["observations"]["terms"]:
+            if t["op"] == "external":
+                t["ext_row"], row = row, row + _tdx.term_dim(s, t)
+        self.n_ext = row
+        self.ext_values = z(max(row, 1), N)
+        st.ext_values = p(self.ext_values) if row else None
         # --- terminations / rewards
         nt, nr = len(s["terminations"]), len(s["rewards"])
         if max(nt, nr, len(s["observations"]["terms"])) > C["B200LAB_MAX_TERMS"]:
@@ -547,7 +565,8 @@ class FusedEnv:
         _lib.check(self.L.b200lab_decimation_fused(self.handle, _lib.ptr(action), sim_prev.ref, arr, len(sims),
                                                    _lib.current_stream()))
 
-    def step(self, action, sims, sim_prev, fused: bool = True, obs_ranges=None, after_post_step=None, after_range=None):
+    def step(self, action, sims, sim_prev, fused: bool = True, obs_ranges=None, after_post_step=None, after_range=None,
+             before_post_step=None):
         """One env step on S known post-physics states: [process_action -> S x (pre(previous state), post(new state))]
         -> post_step -> compute_obs (manager_based_rl_env.py:153-242; mirrors oracle.mdp_env.OracleEnv.step).
         `fused=True` runs the bracketed part as one launch, `fused=False` as the 1 + 2S calls a live simulator uses."""
@@ -563,6 +582,8 @@ class FusedEnv:
                 prev = sim
         if self.speculative_scan:
             self.height_scan_prefetch(prev)
+        if before_post_step is not None:   # user reward / termination terms are evaluated on the post-physics state
+            before_post_step()
         self.post_step(prev)
         if after_post_step is not None:
             after_post_step()

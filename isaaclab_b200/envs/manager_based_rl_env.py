@@ -128,69 +128,31 @@ class DeviceReplaySim:
         return self.syn.views(self.k)[-1]
 
 
-class _ManagerView:
-    def __init__(self, env):
-        self._env = env
+from .manager_views import (ActionManager, CommandManager, CurriculumManager, EventManager, ObservationManager,  # noqa: E402
+                            RewardManager, TerminationManager)
+from .scene import SceneView  # noqa: E402
 
 
-class RewardManager(_ManagerView):
-    @property
-    def active_terms(self):
-        return [t["name"] for t in self._env.spec["rewards"]]
+class LiveSimBackend:
+    """Protocol of a RUNNING simulator behind `ManagerBasedRLEnv.step` (manager_based_rl_env.py:182-196 of the reference):
 
-    def compute(self, dt=None):
-        return self._env.reward_buf
+        current_view() -> SimView   PhysX-view-shaped tensors of the simulator's CURRENT state (root_state_w [N,13],
+                                    joint_pos / joint_vel [N,J], net contact forces [N,B,3], body velocities);
+        physics_step(env)           one `sim.step()`: consume the efforts / targets the actuator pass left in
+                                    `env.fused.joint_effort_target_sim` / `joint_pos_target_sim`, advance, refresh the tensors.
 
+    The env then runs `process_action`, S x (`substep_pre`, `physics_step`, `substep_post`), `post_step`,
+    `post_reset_write`, `compute_obs` -- the per-sub-step entry points, since the post-physics states are not known in
+    advance.  Replay backends (`advance()` / `last_view()`) use the one-launch fused decimation instead."""
 
-class TerminationManager(_ManagerView):
-    @property
-    def active_terms(self):
-        return [t["name"] for t in self._env.spec["terminations"]]
+    def current_view(self):
+        raise NotImplementedError
 
-    @property
-    def terminated(self):
-        return self._env.reset_terminated
+    def physics_step(self, env):
+        raise NotImplementedError
 
-    @property
-    def time_outs(self):
-        return self._env.reset_time_outs
-
-    @property
-    def dones(self):
-        return self._env.reset_buf
-
-    def get_term(self, name):
-        return self._env.fused.term_dones[self.active_terms.index(name)].bool()
-
-
-class CommandManager(_ManagerView):
-    def get_command(self, name):
-        if self._env.spec.get("command") is None or name != self._env.spec["command"]["name"]:
-            raise ValueError(f"Command term '{name}' not found")
-        return self._env.fused.cmd_vel_b
-
-
-class ActionManager(_ManagerView):
-    @property
-    def action(self):
-        return self._env.fused.action
-
-    @property
-    def prev_action(self):
-        return self._env.fused.prev_action
-
-    @property
-    def total_action_dim(self):
-        return self._env.fused.A
-
-
-class ObservationManager(_ManagerView):
-    @property
-    def group_obs_dim(self):
-        return {self._env.spec["observations"]["group"]: (self._env.fused.obs_dim,)}
-
-    def compute(self):
-        return {self._env.spec["observations"]["group"]: self._env.fused.obs_buf}
+    def last_view(self):
+        return self.current_view()
 
 
 class ManagerBasedRLEnv:
@@ -204,16 +166,42 @@ class ManagerBasedRLEnv:
         self.device = torch.device(device)
         self.spec = spec if spec is not None else compile_env_cfg(cfg, num_envs=num_envs, terrain=terrain, seed=seed)
         self.num_envs = self.spec["N"]
+        ext_obs = [t for t in self.spec["observations"]["terms"] if t["op"] == "external" and t.get("dim") is None]
+        if ext_obs and self.spec.get("raycaster") and "mesh" not in self.spec["raycaster"]:
+            from ..sensors.ray_caster import WarpFreeMesh   # one device mesh shared by the probe env and the final one
+            r = self.spec["raycaster"]
+            r["mesh"] = WarpFreeMesh(r["mesh_vertices"], r["mesh_faces"], cell_size=r.get("cell_size", 0.0))
+        for t in ext_obs:
+            t["dim"] = 1   # placeholder width for the probe env below
         self.fused = FusedEnv(self.spec, device=device, seed=seed)
         if sim is None:
             from ..sim.synthetic import SyntheticSim
             sim = DeviceReplaySim(SyntheticSim(self.spec, K=8, seed=1234 + seed, device=device))
         self.sim = sim
+        if ext_obs:
+            # ObservationManager._prepare_terms (observation_manager.py:420-450): the width of a term is the shape of one
+            # call.  The probe env provides the buffers the term reads; the final env is built with the real widths.
+            self.scene = SceneView(self)
+            self._ep_offset = 0
+            for t in ext_obs:
+                fn = t["func"](t["cfg"], self) if t["is_class"] else t["func"]
+                val = fn(self, **t["params"])
+                if val.dim() != 2 or val.shape[0] != self.num_envs:
+                    raise ValueError(f"observation term '{t['name']}' must return a [num_envs, D] tensor, got {tuple(val.shape)}")
+                t["dim"] = int(val.shape[1])
+            self.fused.L.b200lab_env_destroy(self.fused.handle)
+            self.fused.handle = None
+            self.fused = FusedEnv(self.spec, device=device, seed=seed)
         self.step_dt, self.physics_dt = self.spec["step_dt"], self.spec["physics_dt"]
         self.max_episode_length, self.max_episode_length_s = self.spec["max_episode_length"], self.spec["max_episode_length_s"]
         self.reward_manager, self.termination_manager = RewardManager(self), TerminationManager(self)
         self.command_manager, self.action_manager = CommandManager(self), ActionManager(self)
         self.observation_manager = ObservationManager(self)
+        self.event_manager, self.curriculum_manager = EventManager(self), CurriculumManager(self)
+        self.scene = SceneView(self)
+        self._live = hasattr(self.sim, "physics_step")
+        self._ep_offset = 0
+        self._bind_external_terms()
         self.extras = {}
         self.common_step_counter = 0
         self._group = self.spec["observations"]["group"]
@@ -232,11 +220,53 @@ class ManagerBasedRLEnv:
         self.use_cuda_graph = bool(use_cuda_graph)
         self._graphs, self._graph_warm = {}, False
         if self.use_cuda_graph:
+            if self._ext_pre or self._ext_obs or self._live:
+                raise ValueError("use_cuda_graph=True needs a replay backend and fused terms only: user (Python) terms "
+                                 "and a live simulator run host code between the kernels of a step")
             f.use_device_step_counter()
+
+    # -- user (Python) terms: func(env, **params) -> Tensor, evaluated every step into ext_values (manager_term_cfg.py:29-52)
+    def _bind_external_terms(self):
+        def bind(t):
+            fn = t["func"](t["cfg"], self) if t["is_class"] else t["func"]   # class terms: manager_base.py:393-395
+            return (t, fn)
+        s = self.spec
+        self._ext_pre = [bind(t) for t in list(s["terminations"]) + list(s["rewards"]) if t["op"] == "external"]
+        self._ext_obs = [bind(t) for t in s["observations"]["terms"] if t["op"] == "external"]
+        self._class_terms = [fn for t, fn in self._ext_pre + self._ext_obs if t["is_class"]]
+
+    def _eval_external_pre(self):
+        """Reward / termination terms on the post-physics state, before the step kernel consumes them.  As in the
+        reference they see `episode_length_buf` already incremented (manager_based_rl_env.py:200); a reward term that
+        reads `termination_manager.terminated` sees the previous step's mask (terminations and rewards share one kernel)."""
+        self._ep_offset = 1
+        try:
+            ext, N = self.fused.ext_values, self.num_envs
+            for t, fn in self._ext_pre:
+                val = fn(self, **t["params"])
+                if val.numel() != N:
+                    raise ValueError(f"term '{t['name']}' must return a [num_envs] tensor, got {tuple(val.shape)}")
+                ext[t["ext_row"]].copy_(val.reshape(N))
+        finally:
+            self._ep_offset = 0
+
+    def _eval_external_obs(self):
+        ext, N = self.fused.ext_values, self.num_envs
+        for t, fn in self._ext_obs:
+            val = fn(self, **t["params"])
+            if tuple(val.shape) != (N, t["dim"]):
+                raise ValueError(f"observation term '{t['name']}' returned {tuple(val.shape)}, expected {(N, t['dim'])}")
+            ext[t["ext_row"]:t["ext_row"] + t["dim"]].copy_(val.t())
+        if self._class_terms:   # class terms keep per-env state: reset it for the envs this step reset (one host sync)
+            ids = self.reset_buf.nonzero(as_tuple=False).squeeze(-1)
+            if ids.numel() > 0:
+                for term in self._class_terms:
+                    term.reset(ids)
 
     @property
     def episode_length_buf(self):
-        return self.fused.episode_length_buf
+        buf = self.fused.episode_length_buf
+        return buf + self._ep_offset if self._ep_offset else buf
 
     @episode_length_buf.setter
     def episode_length_buf(self, v):
@@ -286,6 +316,8 @@ class ManagerBasedRLEnv:
 
     def reset(self, seed=None):
         """Initial observations (ManagerBasedEnv.reset, LAB/envs/manager_based_env.py:264): obs of the current state."""
+        if self._ext_obs:
+            self._eval_external_obs()
         self.fused.compute_obs(self.sim.last_view())
         return self.obs_buf, self.extras
 
@@ -308,7 +340,8 @@ class ManagerBasedRLEnv:
         a captured graph, where the extra enqueue calls cost nothing at replay); otherwise one copy at the end."""
         f = self.fused
         if results_out is None or not pipelined:
-            f.step(action, views, prev)
+            f.step(action, views, prev, before_post_step=self._eval_external_pre if self._ext_pre else None,
+                   after_post_step=self._eval_external_obs if (self._ext_obs or self._class_terms) else None)
             if results_out is not None:
                 results_out.copy_(f.result, non_blocking=True)
             return
@@ -338,11 +371,13 @@ class ManagerBasedRLEnv:
         call `wait_results()` before reading it.  With `use_cuda_graph=True` the whole step -- action staging, kernels,
         pipelined read-back -- is captured once per (action buffer, result slab, simulator staging set) and replayed
         with one launch; the first step runs eagerly."""
-        prev = self.sim.last_view()
-        views = self.sim.advance()
         if action.device != self.device:  # host action: staged through a fixed device buffer
             self._action_dev.copy_(action, non_blocking=True)
             action = self._action_dev
+        if self._live:
+            return self._step_live(action, results_out)
+        prev = self.sim.last_view()
+        views = self.sim.advance()
         # The staging set of the NEXT step was last read by the previous step, which precedes everything queued below on
         # this stream: its H2D copy only has to wait for this point (after the small action copy -- H2D copies share one
         # engine and run in issue order) and crosses PCIe while this step's kernels run.  The copy itself is queued after
@@ -393,6 +428,38 @@ class ManagerBasedRLEnv:
         self.common_step_counter += 1
         if self.log_every_step:
             log = self.fused.last_step_log()
+            if log:
+                self.extras["log"] = log
+            else:
+                self.extras.pop("log", None)
+        return self.obs_buf, self.reward_buf, self.reset_terminated, self.reset_time_outs, self.extras
+
+    def _step_live(self, action, results_out):
+        """One env step around a RUNNING simulator (`LiveSimBackend`): the order of manager_based_rl_env.py:173-236."""
+        f, sim = self.fused, self.sim
+        f.process_action(action)
+        for _ in range(self.spec["decimation"]):
+            f.substep_pre(sim.current_view())     # apply_action + actuator models on the pre-physics state
+            sim.physics_step(self)                # sim.step()
+            f.substep_post(sim.current_view())    # scene.update(dt): joint_acc, contact sensor, sensor clocks
+        view = sim.current_view()
+        if self._ext_pre:
+            self._eval_external_pre()
+        f.post_step(view)
+        if self._ext_obs or self._class_terms:
+            self._eval_external_obs()
+        f.post_reset_write(view)
+        f.log_fold()
+        f.compute_obs(view)
+        f.step_counter += 1
+        if results_out is not None:
+            results_out.copy_(f.result, non_blocking=True)
+            if self._d2h_done is None:
+                self._d2h_done = torch.cuda.Event()
+            self._d2h_done.record(torch.cuda.current_stream())
+        self.common_step_counter += 1
+        if self.log_every_step:
+            log = f.last_step_log()
             if log:
                 self.extras["log"] = log
             else:

@@ -14,4 +14,8 @@ def term_dim(spec, t):
         return spec["R"]
     if op == "base_pos_z":
         return 1
+    if op == "external":
+        if t.get("dim") is None:
+            raise ValueError(f"observation term '{t.get('name')}': the width of a user term is set when the env is built")
+        return int(t["dim"])
     raise ValueError(f"unknown observation term '{op}'")

@@ -31,6 +31,29 @@ class SceneEntityCfg:
             self.body_ids = slice(None) if len(ids) == entity.num_bodies and not self.preserve_order else ids
 
 
+class ManagerTermBase:
+    """Base of class-type terms (LAB/managers/manager_base.py:28-115): constructed once with `(cfg, env)` when the env is
+    built, called as `term(env, **params)` every step, `reset(env_ids)` for the envs that were reset."""
+
+    def __init__(self, cfg, env):
+        self.cfg = cfg
+        self._env = env
+
+    @property
+    def num_envs(self) -> int:
+        return self._env.num_envs
+
+    @property
+    def device(self):
+        return self._env.device
+
+    def reset(self, env_ids=None) -> None:
+        pass
+
+    def __call__(self, *args):
+        raise NotImplementedError("The method '__call__' should be implemented by the term.")
+
+
 @dataclass
 class ManagerTermBaseCfg:
     func: Callable | str = None
