@@ -71,3 +71,28 @@ def test_no_product_module_imports_the_oracle():
                 if re.search(r"^\s*(from|import)\s+oracle\b", src, re.M):
                     bad.append(os.path.join(dirpath, f))
     assert not bad, bad
+
+
+def test_integration_md_binding_stub_is_generated_from_the_header_and_executes(L):
+    """INTEGRATION.md section 1 is the output of tools/gen_integration.py (no drift), it executes against the built
+    library, and its signatures agree with the product's own binding table (two independent derivations of the header)."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("gen_integration", os.path.join(ROOT, "tools", "gen_integration.py"))
+    gen = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(gen)
+    doc = open(os.path.join(ROOT, "INTEGRATION.md")).read()
+    assert gen.render(doc) == doc, "INTEGRATION.md is stale: run python tools/gen_integration.py"
+    block = doc[doc.index(gen.BEGIN):doc.index(gen.END)]
+    code = block[block.index("```python") + len("```python"):block.rindex("```")]
+    code = code.replace('C.CDLL("libb200lab.so")', f'C.CDLL({_lib.LIB_PATH!r})')
+    ns = {}
+    exec(compile(code, "INTEGRATION.md", "exec"), ns)
+    sigs = ns["_SIGS"]
+    assert set(sigs) == set(_lib.declared_symbols()) == set(_lib._SIGS)
+    for name, (res, args) in sigs.items():
+        want_res, want_args = _lib._SIGS[name]
+        assert res is want_res, f"{name}: restype {res} vs {want_res}"
+        assert len(args) == len(want_args), f"{name}: {len(args)} arguments documented, {len(want_args)} bound"
+        for i, (a, b) in enumerate(zip(args, want_args)):
+            assert a is b, f"{name} argument {i}: documented {a}, bound {b}"
+    assert ns["_L"].b200lab_version() >= 1 and ns["ptr"](None) is None
