@@ -582,6 +582,45 @@ REF_TASK_CFG = {
 }
 
 
+COVERAGE_TASK = "B200-Opcode-Coverage-v0"
+
+
+def coverage_reference_cfg():
+    """The reference-side twin of isaaclab_b200.tasks.coverage.OpcodeCoverageEnvCfg: the reference's flat Anymal-C cfg with
+    the reference's OWN IdealPDActuatorCfg / DCMotorCfg classes and mdp functions plugged in, from the same data tables."""
+    import importlib
+    from isaaclab_b200.tasks import coverage as cov
+    from isaaclab.actuators import DCMotorCfg, IdealPDActuatorCfg
+    import isaaclab.envs.mdp as rmdp
+    from isaaclab.managers import ObservationTermCfg, RewardTermCfg, SceneEntityCfg, TerminationTermCfg
+    from isaaclab.utils.noise import AdditiveUniformNoiseCfg as Unoise
+    flat = importlib.import_module(REF_TASK_CFG["Isaac-Velocity-Flat-Anymal-C-v0"][0])
+    cfg = flat.AnymalCFlatEnvCfg()
+    acts = {}
+    for name, a in cov.ACTUATORS.items():
+        a = dict(a)
+        cls = IdealPDActuatorCfg if a.pop("kind") == "ideal_pd" else DCMotorCfg
+        acts[name] = cls(**a)
+    cfg.scene.robot = cfg.scene.robot.replace(actuators=acts)
+    cfg.actions.joint_pos.clip = dict(cov.ACTION_CLIP)
+    for name, r in cov.REWARDS.items():
+        params = {}
+        for k, v in r["params"].items():
+            if k == "sensor_cfg":
+                v = SceneEntityCfg(v[0], body_names=v[1])
+            elif k == "asset_cfg":
+                v = SceneEntityCfg(v[0], joint_names=v[1])
+            params[k] = v
+        setattr(cfg.rewards, "cov_" + name, RewardTermCfg(func=getattr(rmdp, name), weight=r["weight"], params=params))
+    for name, t in cov.TERMINATIONS.items():
+        setattr(cfg.terminations, "cov_" + name, TerminationTermCfg(func=getattr(rmdp, name), params=dict(t["params"])))
+    for name, (fn, nz, clip, scale) in cov.OBSERVATIONS.items():
+        setattr(cfg.observations.policy, name,
+                ObservationTermCfg(func=getattr(rmdp, fn), noise=Unoise(n_min=nz[0], n_max=nz[1]) if nz else None, clip=clip,
+                                   scale=scale))
+    return cfg
+
+
 def hard_joint_limits(task, spec):
     """Joint position limits the reference would read from USD (stated in isaaclab_b200.assets)."""
     from isaaclab_b200.tasks import TASKS
@@ -595,8 +634,11 @@ def hard_joint_limits(task, spec):
 
 def build_reference_env(task, spec, slabs, init, tmpdir, wrap=False):
     import importlib
-    mod, cls = REF_TASK_CFG[task]
-    cfg = getattr(importlib.import_module(mod), cls)()
+    if task == COVERAGE_TASK:
+        cfg = coverage_reference_cfg()
+    else:
+        mod, cls = REF_TASK_CFG[task]
+        cfg = getattr(importlib.import_module(mod), cls)()
     cfg.scene.num_envs = spec["N"]
     # startup-mode events randomise PhysX materials / masses: PhysX-side, outside the path
     for name in list(vars(cfg.events)):
@@ -689,6 +731,8 @@ def generate(task, N, steps, slab_seed=1234, init_seed=5, action_seed=3, draw_se
     slabs = generate_slabs(spec, steps + 1, seed=slab_seed)
     init = initial_env_state(spec, seed=init_seed)
     init["episode_length_buf"][::7] = spec["max_episode_length"] - 2
+    if task == COVERAGE_TASK:   # some bases below the minimum height (the synthetic z never gets there on its own)
+        slabs["root_state_w"][:, ::9, 2] -= 0.25
     slabs_in = {k: v.clone() for k, v in slabs.items()}
     spec["joint_pos_limits"] = hard_joint_limits(task, spec)
     log = DrawLog(draw_seed)
@@ -718,7 +762,7 @@ def generate(task, N, steps, slab_seed=1234, init_seed=5, action_seed=3, draw_se
                 reference="IsaacLab 2.1.0 ManagerBasedRLEnv.step (unmodified) over replayed PhysX views; see gen_mdp.py")
 
 
-SIZES = {"Isaac-Cartpole-v0": (64, 8), "Isaac-Velocity-Flat-Anymal-C-v0": (40, 8), "Isaac-Velocity-Rough-Anymal-C-v0": (36, 6),
+SIZES = {COVERAGE_TASK: (48, 8), "Isaac-Cartpole-v0": (64, 8), "Isaac-Velocity-Flat-Anymal-C-v0": (40, 8), "Isaac-Velocity-Rough-Anymal-C-v0": (36, 6),
          "Isaac-Velocity-Rough-Unitree-Go1-v0": (36, 6), "Isaac-Velocity-Rough-H1-v0": (36, 6)}
 
 
@@ -727,7 +771,7 @@ def fixture_path(task):
 
 
 def main(tasks=None):
-    for task in tasks or list(REF_TASK_CFG):
+    for task in tasks or (list(REF_TASK_CFG) + [COVERAGE_TASK]):
         N, steps = SIZES[task]
         fx = generate(task, N, steps)
         n_reset = sum(int(s["reset_buf"].sum()) for s in fx["out"])

@@ -15,7 +15,8 @@ from tests.mdp_common import (close, draw_uniforms, exact, init_fused_state, ini
 pytestmark = pytest.mark.gpu
 
 TASKS = ["Isaac-Cartpole-v0", "Isaac-Velocity-Flat-Anymal-C-v0", "Isaac-Velocity-Rough-Anymal-C-v0",
-         "Isaac-Velocity-Rough-Unitree-Go1-v0", "Isaac-Velocity-Rough-H1-v0"]
+         "Isaac-Velocity-Rough-Unitree-Go1-v0", "Isaac-Velocity-Rough-H1-v0",
+         "B200-Opcode-Coverage-v0"]   # synthetic cfg: the opcodes / actuator kinds / options the five tasks do not use
 
 
 @pytest.mark.parametrize("fused", [True, False, "spec"], ids=["fused-decimation", "per-substep", "fused+speculative-scan"])

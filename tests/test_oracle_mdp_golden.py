@@ -15,7 +15,8 @@ from tests.mdp_common import init_oracle_state, make_spec, slab_views_cpu
 
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 TASKS = ["Isaac-Cartpole-v0", "Isaac-Velocity-Flat-Anymal-C-v0", "Isaac-Velocity-Rough-Anymal-C-v0",
-         "Isaac-Velocity-Rough-Unitree-Go1-v0", "Isaac-Velocity-Rough-H1-v0"]
+         "Isaac-Velocity-Rough-Unitree-Go1-v0", "Isaac-Velocity-Rough-H1-v0",
+         "B200-Opcode-Coverage-v0"]   # synthetic cfg: the opcodes / actuator kinds / options the five tasks do not use
 
 
 def fixture_path(task):
