@@ -646,7 +646,7 @@ def build_reference_env(task, spec, slabs, init, tmpdir, wrap=False):
         if term is not None and getattr(term, "mode", None) == "startup":
             setattr(cfg.events, name, None)
     # debug visualisation draws USD markers: Kit-only
-    for name in vars(cfg.commands):
+    for name in (vars(cfg.commands) if hasattr(cfg.commands, "__dict__") else ()):
         term = getattr(cfg.commands, name)
         if hasattr(term, "debug_vis"):
             term.debug_vis = False
