@@ -576,6 +576,15 @@ int b200lab_empirical_norm_update(const float* x, int64_t M, int32_t D, int64_t 
                                   float* std, void* stream);
 int b200lab_empirical_norm_apply(const float* x, const float* mean, const float* std, float eps, float* out, int64_t M,
                                  int32_t D, void* stream);
+/* The same update with GLOBAL statistics over the ranks of a multi-GPU run (normalization.py:50-66 applied to the union of
+ * the ranks' batches; BASELINE north_star: "NCCL ... for global observation-normaliser statistics").  `partial` reduces the
+ * rank's batch to sums[0..D) = sum x, sums[D..2D) = sum x^2 (fp64), sums[2D] = M; the caller all-reduces (SUM) the 2D+1
+ * doubles; `merge` applies the running update with rate = M_total / (count_old + M_total), count_old = samples seen by ALL
+ * ranks before this batch.  With one rank the result equals b200lab_empirical_norm_update up to fp32 rounding of the
+ * batch variance (one-pass fp64 instead of two-pass fp32). */
+int b200lab_empirical_norm_partial(const float* x, int64_t M, int32_t D, double* sums, void* stream);
+int b200lab_empirical_norm_merge(const double* sums, int32_t D, int64_t count_old, float* mean, float* var, float* std,
+                                 void* stream);
 
 #ifdef __cplusplus
 }

@@ -115,6 +115,8 @@ _SIGS = {
     "b200lab_gae_static": (C.c_int, [C.c_void_p] * 6 + [C.c_int32, C.c_int32, C.c_float, C.c_float, C.c_int32, C.c_void_p]),
     "b200lab_add_transition": (C.c_int, [C.c_void_p, C.c_void_p]),
     "b200lab_empirical_norm_update": (C.c_int, [C.c_void_p, C.c_int64, C.c_int32, C.c_int64] + [C.c_void_p] * 4),
+    "b200lab_empirical_norm_partial": (C.c_int, [C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p]),
+    "b200lab_empirical_norm_merge": (C.c_int, [C.c_void_p, C.c_int32, C.c_int64] + [C.c_void_p] * 4),
     "b200lab_empirical_norm_apply": (C.c_int, [C.c_void_p] * 3 + [C.c_float, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p]),
     "b200lab_episode_stats": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32] + [C.c_void_p] * 4
                               + [C.c_int32, C.c_void_p, C.c_void_p]),

@@ -222,6 +222,55 @@ empirical_norm_update_kernel(const float* __restrict__ x, int64_t M, int D, floa
   }
 }
 
+// Global statistics across ranks (north_star: NCCL all-reduce of the observation-normaliser statistics): every rank
+// reduces its batch to per-column (sum, sum of squares) in fp64, the [2D+1] buffers (last slot: the rank's sample count)
+// are summed over the ranks by ONE all-reduce, and the merge applies the reference's running update
+// (normalization.py:50-66) with the batch mean / biased variance of the UNION of the ranks' batches.
+__global__ void __launch_bounds__(256)
+empirical_norm_partial_kernel(const float* __restrict__ x, int64_t M, int D, double* __restrict__ sums) {
+  __shared__ double sh1[8][33], sh2[8][33];
+  const int cl = threadIdx.x & 31, rl = threadIdx.x >> 5;
+  const int c = blockIdx.x * 32 + cl;
+  double s = 0.0, q = 0.0;
+  if (c < D)
+    for (int64_t r = rl; r < M; r += 8) {
+      const double v = (double)__ldg(x + r * D + c);
+      s += v;
+      q += v * v;
+    }
+  sh1[rl][cl] = s;
+  sh2[rl][cl] = q;
+  __syncthreads();
+  if (rl == 0 && c < D) {
+    double a = 0.0, b = 0.0;
+#pragma unroll
+    for (int k = 0; k < 8; ++k) { a += sh1[k][cl]; b += sh2[k][cl]; }
+    sums[c] = a;
+    sums[D + c] = b;
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0) sums[2 * D] = (double)M;
+}
+
+__global__ void __launch_bounds__(256)
+empirical_norm_merge_kernel(const double* __restrict__ sums, int D, int64_t count_old, float* __restrict__ mean,
+                            float* __restrict__ var, float* __restrict__ stdv) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= D) return;
+  const double Mtot = sums[2 * D];
+  const float rate = (float)(Mtot / ((double)count_old + Mtot));
+  const double mxd = sums[c] / Mtot;
+  double vxd = sums[D + c] / Mtot - mxd * mxd;
+  if (vxd < 0.0) vxd = 0.0;
+  const float mx = (float)mxd, var_x = (float)vxd;
+  const float m_old = mean[c];
+  const float delta = mx - m_old;
+  const float m_new = m_old + rate * delta;
+  const float v_new = var[c] + rate * (var_x - var[c] + delta * (mx - m_new));
+  mean[c] = m_new;
+  var[c] = v_new;
+  stdv[c] = sqrtf(v_new);
+}
+
 // forward: (x - mean) / (std + eps)
 __global__ void __launch_bounds__(256)
 empirical_norm_apply_kernel(const float* __restrict__ x, const float* __restrict__ mean, const float* __restrict__ stdv,
@@ -294,6 +343,21 @@ int b200lab_empirical_norm_update(const float* x, int64_t M, int32_t D, int64_t 
   empirical_norm_update_kernel<<<(unsigned)ceil_div(D, 32), 256, 0, (cudaStream_t)stream>>>(x, M, D, rate, mean, var, std);
   count_launch();
   return check_launch("empirical_norm_update");
+}
+
+int b200lab_empirical_norm_partial(const float* x, int64_t M, int32_t D, double* sums, void* stream) {
+  B200LAB_CHECK_ARG(x && sums && M > 0 && D > 0, "bad argument");
+  empirical_norm_partial_kernel<<<(unsigned)ceil_div(D, 32), 256, 0, (cudaStream_t)stream>>>(x, M, D, sums);
+  count_launch();
+  return check_launch("empirical_norm_partial");
+}
+
+int b200lab_empirical_norm_merge(const double* sums, int32_t D, int64_t count_old, float* mean, float* var, float* std,
+                                 void* stream) {
+  B200LAB_CHECK_ARG(sums && mean && var && std && D > 0 && count_old >= 0, "bad argument");
+  empirical_norm_merge_kernel<<<(unsigned)ceil_div(D, 256), 256, 0, (cudaStream_t)stream>>>(sums, D, count_old, mean, var, std);
+  count_launch();
+  return check_launch("empirical_norm_merge");
 }
 
 int b200lab_empirical_norm_apply(const float* x, const float* mean, const float* std, float eps, float* out, int64_t M,

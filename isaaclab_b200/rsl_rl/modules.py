@@ -90,9 +90,14 @@ class EmpiricalNormalization(nn.Module):
     (`_mean`, `_var`, `_std` of shape [1, D], `count`) so state dicts interchange; `forward` and `update` are one kernel
     each.  The sample counter is mirrored on the host (the batch size is known there), so neither call synchronises."""
 
-    def __init__(self, shape, eps=1e-2, until=None, device="cuda"):
+    def __init__(self, shape, eps=1e-2, until=None, device="cuda", global_stats=True):
+        """`global_stats`: in a multi-GPU run (torch.distributed initialised, world size > 1) every update learns the
+        UNION of the ranks' batches -- one all-reduce of 2D+1 doubles -- so all ranks normalise identically (the
+        reference updates rank-locally and lets the statistics drift apart).  No effect with one process."""
         super().__init__()
         self.eps, self.until = eps, until
+        self.global_stats = bool(global_stats)
+        self._sums = None
         D = int(shape if isinstance(shape, int) else shape[0])
         self.register_buffer("_mean", torch.zeros(1, D, device=device))
         self.register_buffer("_var", torch.ones(1, D, device=device))
@@ -129,9 +134,20 @@ class EmpiricalNormalization(nn.Module):
             return
         x = x.contiguous()
         M, D = x.shape
+        p = _lib.ptr
+        dist = torch.distributed
+        if self.global_stats and dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+            if self._sums is None:
+                self._sums = torch.zeros(2 * D + 1, dtype=torch.float64, device=x.device)
+            L, s = _lib.lib(), _lib.current_stream()
+            _lib.check(L.b200lab_empirical_norm_partial(p(x), M, D, p(self._sums), s))
+            dist.all_reduce(self._sums, op=dist.ReduceOp.SUM)
+            _lib.check(L.b200lab_empirical_norm_merge(p(self._sums), D, self._count, p(self._mean), p(self._var), p(self._std), s))
+            self._count += M * dist.get_world_size()   # env shards are equal-sized; the kernels use the exact reduced count
+            self.count.fill_(self._count)
+            return
         self._count += M
         self.count.fill_(self._count)
-        p = _lib.ptr
         _lib.check(_lib.lib().b200lab_empirical_norm_update(p(x), M, D, self._count, p(self._mean), p(self._var),
                                                            p(self._std), _lib.current_stream()))
 

@@ -188,3 +188,46 @@ def test_linear_rejects_unknown_precision():
     x = torch.zeros(64, 64, device="cuda")
     rc = L.b200lab_linear_fwd(_lib.ptr(x), _lib.ptr(x), _lib.ptr(x[0]), _lib.ptr(x.clone()), 64, 64, 64, 0, 7, _lib.current_stream())
     assert rc != 0 and b"precision" in L.b200lab_last_error()
+
+
+def test_global_normalizer_statistics_equal_the_update_on_the_union_of_the_ranks_batches():
+    """N1 (north_star): partial sums per rank + ONE all-reduce + merge == the reference's running update
+    (normalization.py:50-66) applied to the concatenation of the ranks' batches.  Two 'ranks' are emulated on one GPU by
+    adding their partial buffers (what the SUM all-reduce does); tests/test_gpu_multi.py runs the real NCCL exchange."""
+    from isaaclab_b200 import _lib
+    L, p, s = _lib.lib(), _lib.ptr, _lib.current_stream
+    D = 235
+    g = torch.Generator().manual_seed(4)
+    scale, shift = 0.5 + 3.0 * torch.rand(D, generator=g), 2.0 * torch.randn(D, generator=g)
+    mean_g, var_g, std_g = (torch.zeros(D, device="cuda"), torch.ones(D, device="cuda"), torch.ones(D, device="cuda"))
+    mean_r, var_r, count = torch.zeros(D, dtype=torch.float64), torch.ones(D, dtype=torch.float64), 0
+    for it in range(3):
+        xs = [(torch.randn(m, D, generator=g) * scale + shift + it).cuda() for m in (4096, 1000)]   # unequal shards
+        bufs = [torch.zeros(2 * D + 1, dtype=torch.float64, device="cuda") for _ in xs]
+        for x, b in zip(xs, bufs):
+            _lib.check(L.b200lab_empirical_norm_partial(p(x), x.shape[0], D, p(b), s()))
+        total = bufs[0] + bufs[1]
+        _lib.check(L.b200lab_empirical_norm_merge(p(total), D, count, p(mean_g), p(var_g), p(std_g), s()))
+        # reference update on the union, in fp64
+        x = torch.cat(xs).cpu().double()
+        count += x.shape[0]
+        rate = x.shape[0] / count
+        mx, vx = x.mean(0), x.var(0, unbiased=False)
+        delta = mx - mean_r
+        mean_r = mean_r + rate * delta
+        var_r = var_r + rate * (vx - var_r + delta * (mx - mean_r))
+        torch.cuda.synchronize()
+        assert float(total[2 * D]) == 5096.0
+        torch.testing.assert_close(mean_g.cpu().double(), mean_r, rtol=1e-5, atol=1e-5)
+        torch.testing.assert_close(var_g.cpu().double(), var_r, rtol=1e-4, atol=1e-5)
+        torch.testing.assert_close(std_g.cpu().double(), var_r.sqrt(), rtol=1e-4, atol=1e-5)
+    # one rank: the global path equals the rank-local kernel
+    x = (torch.randn(2048, D, generator=g) * scale + shift).cuda()
+    m1, v1, s1 = torch.zeros(D, device="cuda"), torch.ones(D, device="cuda"), torch.ones(D, device="cuda")
+    m2, v2, s2 = m1.clone(), v1.clone(), s1.clone()
+    _lib.check(L.b200lab_empirical_norm_update(p(x), 2048, D, 2048, p(m1), p(v1), p(s1), s()))
+    b = torch.zeros(2 * D + 1, dtype=torch.float64, device="cuda")
+    _lib.check(L.b200lab_empirical_norm_partial(p(x), 2048, D, p(b), s()))
+    _lib.check(L.b200lab_empirical_norm_merge(p(b), D, 0, p(m2), p(v2), p(s2), s()))
+    torch.testing.assert_close(m2, m1, rtol=1e-6, atol=1e-6)
+    torch.testing.assert_close(v2, v1, rtol=1e-5, atol=1e-5)
