@@ -239,6 +239,30 @@ def time_kernels(fus, sim, action, steps):
     return {n: sum(a.elapsed_time(b) for a, b in ev[n]) / max(1, len(ev[n])) for n in names}
 
 
+_LAST_PER_RANK_MS = []   # ms per step of every rank in the last _timed() region (the reported time is their MAX)
+
+
+def bind_to_gpu_numa_node(local):
+    """Pins this process to the CPU cores NVML reports as local to its GPU BEFORE any pinned host memory is allocated, so
+    that the H2D / D2H staging slabs of the end-to-end arm are first-touched on the GPU's NUMA node."""
+    try:
+        import pynvml as nv
+        nv.nvmlInit()
+        vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+        idx = int(vis.split(",")[local]) if vis else local
+        h = nv.nvmlDeviceGetHandleByIndex(idx)
+        n_words = (os.cpu_count() + 63) // 64
+        mask = nv.nvmlDeviceGetCpuAffinity(h, n_words)
+        cpus = {64 * w + b for w, word in enumerate(mask) for b in range(64) if (int(word) >> b) & 1}
+        cpus &= set(os.sched_getaffinity(0))
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            return sorted(cpus)
+    except Exception:
+        pass
+    return None
+
+
 def _timed(fn, steps, world, dev):
     """EXACTLY `steps` calls of fn(k) between a barrier + synchronize on both sides; CUDA events; MAX over ranks (ms)."""
     import torch.distributed as dist
@@ -255,7 +279,12 @@ def _timed(fn, steps, world, dev):
     t = torch.tensor([e0.elapsed_time(e1)], device=dev)
     if world > 1:
         dist.barrier()
+        per_rank = [torch.empty_like(t) for _ in range(world)]
+        dist.all_gather(per_rank, t)
+        _LAST_PER_RANK_MS[:] = [round(float(x.item()) / steps, 5) for x in per_rank]
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    else:
+        _LAST_PER_RANK_MS[:] = [round(float(t.item()) / steps, 5)]
     return float(t.item())
 
 
@@ -306,6 +335,7 @@ def measure_env(cfg_id, spec, slabs, init, steps, warmup, world, rank, dev, peak
     if sampler is not None:
         sampler.start()
     ms = _timed(lambda k: graphs[(warmup + k) % K].replay(), steps, world, dev)
+    rank_ms = list(_LAST_PER_RANK_MS)
     clocks = sampler.finish() if sampler is not None else None
     del graphs
     # ---- live arm (what a running simulator can use): 2 + 2S + 2 launches per step, eager
@@ -337,7 +367,7 @@ def measure_env(cfg_id, spec, slabs, init, steps, warmup, world, rank, dev, peak
            "live": {"ms_per_step": round(ms_live / live_steps, 5), "value": round(world * N * live_steps / (ms_live * 1e-3), 1),
                     "launches_per_step": int(live_launches),
                     "path": "process_action + S x (substep_pre, substep_post) + post_step + post_reset_write + compute_obs, eager"},
-           "launches_per_step": int(launches_per_step), "slabs": K, "slab_bytes_total": sim.bytes(), "roofline": roof}
+           "per_rank_ms_per_step": rank_ms, "launches_per_step": int(launches_per_step), "slabs": K, "slab_bytes_total": sim.bytes(), "roofline": roof}
     del fus, fus_live, fus_replay, sim
     torch.cuda.empty_cache()
     return out, clocks
@@ -365,10 +395,11 @@ def measure_e2e(cfg, spec, slabs, init, steps, warmup, world, rank, dev):
     for k in range(max(warmup, 3 * HostReplaySim._SETS)):   # every staging set has its graph before the timed region
         e2e_step(k)
     ms = _timed(e2e_step, steps, world, dev)
+    rank_ms = list(_LAST_PER_RANK_MS)
     h2d = host_sim.h2d_bytes_per_step + act_host.numel() * 4
     d2h = res_host.numel()
     out = {"value": round(world * N * steps / (ms * 1e-3), 1), "unit": UNIT, "h2d_bytes_per_step": h2d,
-           "d2h_bytes_per_step": d2h, "ms_per_step": round(ms / steps, 4),
+           "d2h_bytes_per_step": d2h, "ms_per_step": round(ms / steps, 4), "per_rank_ms_per_step": rank_ms,
            "pcie_gbs_per_gpu": {"h2d": round(h2d / (ms / steps * 1e-3) / 1e9, 2), "d2h": round(d2h / (ms / steps * 1e-3) / 1e9, 2),
                                 "note": "bytes per step / end-to-end step time (copies overlap the kernels; not a link peak)"}}
     del env, host_sim
@@ -610,6 +641,7 @@ def run_ours(args):
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
+    cpus = bind_to_gpu_numa_node(local)
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
@@ -657,7 +689,8 @@ def run_ours(args):
                                   "synchronised every step; next step's simulator state prefetched H2D on a copy "
                                   "stream while the current step computes",
                       "l2_policy": f"{head['slabs']} state slabs ({head['slab_bytes_total'] >> 20} MiB > 126 MB L2) cycled",
-                      "parallelism": f"env-shard x{world}"},
+                      "parallelism": f"env-shard x{world}",
+                      "cpu_affinity": f"rank bound to the {len(cpus)} cores NVML reports local to its GPU" if cpus else "unchanged"},
            "clocks": clocks, "e2e": head["e2e"], "gpu_launches": int(head["launches_per_step"]) * args.steps,
            "roofline": head["roofline"], "live": head["live"], "replay_eager_ms_per_step": head["replay_eager_ms_per_step"],
            "ppo_update": head.get("ppo_update"), "configs": records}
