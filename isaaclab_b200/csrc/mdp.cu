@@ -1240,6 +1240,14 @@ constexpr int kStepWarps = B200LAB_STEP_WARPS;
 #define B200LAB_POST_BLOCKS 6
 #endif
 
+// kMode 0: the whole of post_step in one kernel.  The split form runs the same body as two kernels so that the code a
+// step executes for (almost) every env stays small enough for the instruction cache:
+//   kMode 1 "hot" : counters, terminations, rewards for every env; command countdown / interval events / derive for the
+//                   envs that were NOT reset.  No reset code is compiled in.
+//   kMode 2 "cold": one warp per env again, exits at once unless the hot kernel set reset_buf; reloads the env's context,
+//                   runs _reset_idx and then the same tail.  The reference has the same structure: work on
+//                   `reset_env_ids` only (manager_based_rl_env.py:215-220).
+template <int kMode>
 __global__ void __launch_bounds__(kStepWarps * 32, B200LAB_POST_BLOCKS * 4 / kStepWarps)
 post_step_kernel(const __grid_constant__ Env env_param, Sim sim, int64_t step, const Env* __restrict__ env_dev,
                  float* __restrict__ derived) {
@@ -1248,7 +1256,7 @@ post_step_kernel(const __grid_constant__ Env env_param, Sim sim, int64_t step, c
   // through the constant bank they push the kernel's constant footprint past ~4 KB, where every launch pays several
   // microseconds of serialised constant-cache misses (tools/imc_probe.cu).
   extern __shared__ uint2 s_tab[];   // the tables sit at 8-byte-aligned offsets of the descriptor
-  {
+  if constexpr (kMode != 2) {
     const int n8_term = e->num_term * (int)(sizeof(B200LabTerm) / 8), n8_rew = e->num_rew * (int)(sizeof(B200LabTerm) / 8);
     const uint2* g_term = reinterpret_cast<const uint2*>(env_dev->term);
     const uint2* g_rew = reinterpret_cast<const uint2*>(env_dev->rew);
@@ -1263,6 +1271,9 @@ post_step_kernel(const __grid_constant__ Env env_param, Sim sim, int64_t step, c
   const int n = blockIdx.x * kStepWarps + (threadIdx.x >> 5);
   const int N = e->N, J = e->J, B = e->B, A = e->A;
   if (n >= N) { pdl_wait(); return; }
+  if constexpr (kMode == 2) {
+    if (!e->reset_buf[n]) return;   // the hot kernel finished this env
+  }
   EnvCtx c;
   c.n = n; c.lane = lane;
   // ---- loads of LIBRARY-OWNED state that the preceding library kernel (decimation / sub-step) does not write: issued
@@ -1297,7 +1308,7 @@ post_step_kernel(const __grid_constant__ Env env_param, Sim sim, int64_t step, c
   for (int k = 0; k < 13; ++k) rs[k] = sim.root_state_w[(int64_t)n * 13 + k];
   derive_state(c, rs);
   if (e->step_counter_dev) step = *e->step_counter_dev;
-  load_rows(c, e, sim);
+  if constexpr (kMode != 2) load_rows(c, e, sim);
   if (derived && e->rc_is_outdated) {
     pre_rc_flag = e->rc_is_outdated[n] != 0;
     pre_rc_ts = e->rc_timestamp[n];
@@ -1306,15 +1317,16 @@ post_step_kernel(const __grid_constant__ Env env_param, Sim sim, int64_t step, c
   int64_t ep_len = pre_ep_len + 1;
   // -- terminations (termination_manager.py:151-174)
   bool terminated = false, truncated = false;
+  if constexpr (kMode != 2)
   for (int t = 0; t < e->num_term; ++t) {
     bool v = eval_termination(e, sim, s_term[t], c, ep_len) != 0.f;
     if (s_term[t].time_out) truncated |= v; else terminated |= v;
     if (lane == 0) e->term_dones[(int64_t)t * N + n] = v;
   }
   c.terminated = terminated;
-  const bool reset = terminated || truncated;
+  const bool reset = kMode == 2 ? true : (terminated || truncated);
   // -- rewards (reward_manager.py:128-157)
-  {
+  if constexpr (kMode != 2) {
     float total = 0.f;
     const float dt = e->step_dt;
     float mine = 0.f;        // lane r keeps term r's value: the per-term buffers are then updated by all lanes at once
@@ -1338,7 +1350,14 @@ post_step_kernel(const __grid_constant__ Env env_param, Sim sim, int64_t step, c
     }
   }
   __syncwarp();
+  if constexpr (kMode == 1) {
+    if (reset) {   // the cold kernel takes this env from here
+      if (lane == 0 && e->any_reset_dev) *e->any_reset_dev = 1;
+      return;
+    }
+  }
   // -- _reset_idx (manager_based_rl_env.py:347-392), masked per env
+  if constexpr (kMode != 1)
   if (reset) {
     if (lane == 0 && e->any_reset_dev) *e->any_reset_dev = 1;
     // curriculum: terrain_levels_vel (curriculums.py:26-55) + update_env_origins (terrain_importer.py:307-322)
@@ -2444,9 +2463,23 @@ int b200lab_post_step(void* env, const B200LabSimView* sim, int64_t step_counter
   // a pending speculative scan is validated by the stand-alone derive kernel (it must be joined first)
   const bool fuse_derive = !h->spec_pending && s.obs_dim > 0;
   {
-    cudaError_t err = launch_pdl(post_step_kernel, dim3((unsigned)ceil_div(s.N, kStepWarps)), dim3(kStepWarps * 32), tab_bytes,
-                                 (cudaStream_t)stream, h->host, *sim, step_counter, (const Env*)h->dev,
-                                 fuse_derive ? h->derived : (float*)nullptr);
+    // measured on B200 at 4096 envs (profiles/r2_notes.md): combined kernel 36.9 us, hot + cold 43.5 us -> default combined
+    static const int split = [] { const char* v = getenv("B200LAB_POST_SPLIT"); return v ? atoi(v) : 0; }();
+    const dim3 grid((unsigned)ceil_div(s.N, kStepWarps)), block(kStepWarps * 32);
+    float* dptr = fuse_derive ? h->derived : (float*)nullptr;
+    cudaError_t err;
+    if (split) {
+      err = launch_pdl(post_step_kernel<1>, grid, block, tab_bytes, (cudaStream_t)stream, h->host, *sim, step_counter,
+                       (const Env*)h->dev, dptr);
+      if (err == cudaSuccess) {   // full dependency on the hot kernel (it reads reset_buf); compute_obs may overlap ITS tail
+        post_step_kernel<2><<<grid, block, 0, (cudaStream_t)stream>>>(h->host, *sim, step_counter, (const Env*)h->dev, dptr);
+        err = cudaGetLastError();
+        count_launch();
+      }
+    } else {
+      err = launch_pdl(post_step_kernel<0>, grid, block, tab_bytes, (cudaStream_t)stream, h->host, *sim, step_counter,
+                       (const Env*)h->dev, dptr);
+    }
     if (err != cudaSuccess) { set_error("post_step: %s", cudaGetErrorString(err)); return B200LAB_ERR_CUDA; }
   }
   h->derived_root = fuse_derive ? sim->root_state_w : nullptr;
