@@ -309,6 +309,20 @@ typedef struct B200LabEnvState {
   float* ev_interval_time_left[B200LAB_MAX_INTERVAL_EVENTS]; /* [N] each */
   float ev_interval_range[B200LAB_MAX_INTERVAL_EVENTS][2];  /* (lo, span) */
   float ev_push_range[B200LAB_MAX_INTERVAL_EVENTS][12];     /* (lo, span) x 6 */
+  /* EventManager gating (LAB/managers/event_manager.py:204-270).
+   * reset mode, min_step_count_between_reset > 0: the term is applied to an env being reset only if
+   * global_step - last_triggered >= min_steps, or it has never been triggered; state per term: last_step i32 [N], once u8 [N]
+   * (NULL pointers / 0 = apply on every reset).  global_step = env._sim_step_counter // decimation = step_counter + 1.
+   * interval mode, is_global_time: ONE timer for all envs, kept as two floats indexed by step parity (read [step & 1], env 0
+   * writes [(step + 1) & 1]); when it fires every env is pushed and the new interval is env 0's draw. */
+  int32_t ev_root_min_steps;
+  int32_t ev_reset_joints_min_steps[B200LAB_MAX_RESET_JOINT_EVENTS];
+  int32_t* ev_root_last_step;
+  uint8_t* ev_root_once;
+  int32_t* ev_reset_joints_last_step[B200LAB_MAX_RESET_JOINT_EVENTS];
+  uint8_t* ev_reset_joints_once[B200LAB_MAX_RESET_JOINT_EVENTS];
+  int32_t ev_interval_global[B200LAB_MAX_INTERVAL_EVENTS];
+  float* ev_interval_global_time[B200LAB_MAX_INTERVAL_EVENTS];   /* [2] each, or NULL */
   /* --- curriculum: terrain_levels_vel (TASKS/.../velocity/mdp/curriculums.py:26-55) --- */
   int32_t has_terrain_curriculum;
   int64_t* terrain_levels;     /* [N] */

@@ -1292,7 +1292,7 @@ post_step_kernel(const __grid_constant__ Env env_param, Sim sim, int64_t step, c
   }
   float pre_itl[B200LAB_MAX_INTERVAL_EVENTS];
 #pragma unroll
-  for (int k = 0; k < B200LAB_MAX_INTERVAL_EVENTS; ++k) pre_itl[k] = k < e->num_interval ? e->ev_interval_time_left[k][n] : 0.f;
+  for (int k = 0; k < B200LAB_MAX_INTERVAL_EVENTS; ++k) pre_itl[k] = (k < e->num_interval && e->ev_interval_time_left[k]) ? e->ev_interval_time_left[k][n] : 0.f;
   const float pre_esum = lane < e->num_rew ? e->episode_sums[(int64_t)lane * N + n] : 0.f;
   const int64_t pre_ep_len = e->episode_length_buf[n];
   bool pre_rc_flag = false;
@@ -1422,8 +1422,19 @@ post_step_kernel(const __grid_constant__ Env env_param, Sim sim, int64_t step, c
         e->rc_drift[n * 3 + k] = pre_drift[k];
       }
     }
+    // EventManager.apply(mode="reset") trigger gating (event_manager.py:232-270)
+    const int64_t gstep = step + 1;   // env._sim_step_counter // decimation at the time of _reset_idx
+    auto gate = [&](int32_t min_steps, int32_t* last_step, uint8_t* once) -> bool {
+      if (min_steps <= 0 || !last_step || !once) return true;
+      const int32_t last = last_step[n];
+      const bool valid = (gstep - (int64_t)last >= (int64_t)min_steps) || (last == 0 && once[n] == 0);
+      __syncwarp();
+      if (valid && lane == 0) { last_step[n] = (int32_t)gstep; once[n] = 1; }
+      __syncwarp();
+      return valid;
+    };
     // reset events: reset_root_state_uniform (events.py:823-865)
-    if (e->ev_reset_root_state) {
+    if (e->ev_reset_root_state && gate(e->ev_root_min_steps, e->ev_root_last_step, e->ev_root_once)) {
       float up[6], uv[6];
 #pragma unroll
       for (int k = 0; k < 6; ++k) {
@@ -1446,6 +1457,7 @@ post_step_kernel(const __grid_constant__ Env env_param, Sim sim, int64_t step, c
     }
     // reset events: reset_joints_by_scale / by_offset (events.py:987-1051)
     for (int k = 0; k < e->ev_num_reset_joints; ++k) {
+      if (!gate(e->ev_reset_joints_min_steps[k], e->ev_reset_joints_last_step[k], e->ev_reset_joints_once[k])) continue;
       const int base = B200LAB_U_RESET_JOINT + 2 * J * k;
       for (int j = lane; j < J; j += 32) {
         float u0 = u_reset_at(e, n, base + j, step), u1 = u_reset_at(e, n, base + J + j, step);
@@ -1542,17 +1554,20 @@ post_step_kernel(const __grid_constant__ Env env_param, Sim sim, int64_t step, c
 #pragma unroll
     for (int k = 0; k < B200LAB_MAX_INTERVAL_EVENTS; ++k) {
       if (k >= e->num_interval) break;
-      float tl = pre_itl[k] - e->step_dt;
+      const bool global_time = e->ev_interval_global[k] != 0 && e->ev_interval_global_time[k] != nullptr;
+      float tl = (global_time ? e->ev_interval_global_time[k][step & 1] : pre_itl[k]) - e->step_dt;
       if (tl < 1e-6f) {
         int base = B200LAB_U_STEP_INTERVAL + 7 * k;
-        tl = u_step_at(e, n, base, step) * e->ev_interval_range[k][1] + e->ev_interval_range[k][0];
+        // is_global_time: one draw for the new interval (env 0's slot), every env is pushed (event_manager.py:213-220)
+        tl = u_step_at(e, global_time ? 0 : n, base, step) * e->ev_interval_range[k][1] + e->ev_interval_range[k][0];
         for (int a = 0; a < 6; ++a) {
           float lo = e->ev_push_range[k][2 * a], span = e->ev_push_range[k][2 * a + 1];
           rs[7 + a] = rs[7 + a] + (u_step_at(e, n, base + 1 + a, step) * span + lo);
           sim.root_state_w[(int64_t)n * 13 + 7 + a] = rs[7 + a];
         }
       }
-      e->ev_interval_time_left[k][n] = tl;
+      if (global_time) { if (n == 0) e->ev_interval_global_time[k][(step + 1) & 1] = tl; }
+      else e->ev_interval_time_left[k][n] = tl;
     }
     // the quantities compute_obs shares across the columns of this env, from the final root state of the step (lane 0
     // holds it: resets were applied by every lane, pushes by lane 0) -- saves the derive launch on the critical path

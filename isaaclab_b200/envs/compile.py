@@ -346,19 +346,18 @@ def compile_env_cfg(cfg: ManagerBasedRLEnvCfg, num_envs: int | None = None, terr
         op = f._b200_op
         if t.mode == "startup" or op == "apply_external_force_torque":
             continue  # PhysX property / wrench writers: simulator side, outside the non-physics step
-        if t.min_step_count_between_reset != 0 or t.is_global_time:
-            raise NotImplementedError(f"event '{name}': min_step_count_between_reset / is_global_time")
+        gate = int(t.min_step_count_between_reset or 0)
         if op == "reset_root_state_uniform" and t.mode == "reset":
             if "reset_root_state" in ev:
                 raise NotImplementedError("more than one reset_root_state_uniform term")
             ev["reset_root_state"] = {"pose_range": dict(t.params["pose_range"]),
-                                      "velocity_range": dict(t.params["velocity_range"])}
+                                      "velocity_range": dict(t.params["velocity_range"]), "min_step_count": gate}
         elif op in ("reset_joints_by_scale", "reset_joints_by_offset") and t.mode == "reset":
             ev["reset_joints"].append({"mode": "scale" if op.endswith("scale") else "offset",
                                        "position_range": tuple(t.params["position_range"]),
-                                       "velocity_range": tuple(t.params["velocity_range"])})
+                                       "velocity_range": tuple(t.params["velocity_range"]), "min_step_count": gate})
         elif op == "push_by_setting_velocity" and t.mode == "interval":
-            ev["interval_push"].append({"interval_range_s": tuple(t.interval_range_s),
+            ev["interval_push"].append({"interval_range_s": tuple(t.interval_range_s), "is_global_time": bool(t.is_global_time),
                                         "velocity_range": dict(t.params["velocity_range"])})
         else:
             raise NotImplementedError(f"event '{name}' ({op}, mode={t.mode})")

@@ -350,12 +350,30 @@ class FusedEnv:
                 st.ev_pose_range[2 * k], st.ev_pose_range[2 * k + 1] = float(lo), _f32span_tensor(lo, hi)
                 lo, hi = e["velocity_range"].get(key, (0.0, 0.0))
                 st.ev_vel_range[2 * k], st.ev_vel_range[2 * k + 1] = float(lo), _f32span_tensor(lo, hi)
+        def gate_state(min_steps):
+            """last-triggered step / triggered-once buffers of a gated reset term (event_manager.py:232-270)."""
+            if not min_steps:
+                return None, None
+            last, once = z(N, dtype=torch.int32), z(N, dtype=torch.uint8)
+            self._keep += [last, once]
+            return last, once
+
+        self.ev_gate_state = {}
+        if e:
+            st.ev_root_min_steps = int(e.get("min_step_count", 0))
+            last, once = gate_state(st.ev_root_min_steps)
+            st.ev_root_last_step, st.ev_root_once = p(last), p(once)
+            self.ev_gate_state["reset_root_state"] = (last, once)
         rj = ev.get("reset_joints", [])
         if len(rj) > C["B200LAB_MAX_RESET_JOINT_EVENTS"]:
             raise ValueError("too many reset_joints_by_* events")
         st.ev_num_reset_joints = len(rj)
         for k, e in enumerate(rj):
             st.ev_reset_joints_mode[k] = 1 if e["mode"] == "scale" else 2
+            st.ev_reset_joints_min_steps[k] = int(e.get("min_step_count", 0))
+            last, once = gate_state(st.ev_reset_joints_min_steps[k])
+            st.ev_reset_joints_last_step[k], st.ev_reset_joints_once[k] = p(last), p(once)
+            self.ev_gate_state[f"reset_joints_{k}"] = (last, once)
             lo, hi = e["position_range"]
             st.ev_joint_pos_range[k][0], st.ev_joint_pos_range[k][1] = float(lo), _f32span_py(lo, hi)
             lo, hi = e["velocity_range"]
@@ -365,10 +383,16 @@ class FusedEnv:
             raise ValueError("too many interval events")
         st.num_interval = len(pushes)
         self.interval_time_left = []
+        self.interval_global_time = {}
         for k, e in enumerate(pushes):
             t = z(N)
             self.interval_time_left.append(t)
             st.ev_interval_time_left[k] = p(t)
+            st.ev_interval_global[k] = 1 if e.get("is_global_time") else 0
+            if e.get("is_global_time"):   # one timer for all envs, two slots indexed by step parity
+                gt = z(2)
+                self.interval_global_time[k] = gt
+                st.ev_interval_global_time[k] = p(gt)
             lo, hi = e["interval_range_s"]
             st.ev_interval_range[k][0], st.ev_interval_range[k][1] = float(lo), _f32span_py(lo, hi)
             for a, key in enumerate(_KEYS6):
@@ -443,6 +467,17 @@ class FusedEnv:
                 self.handle = None
         except Exception:
             pass
+
+    def interval_timer(self, k):
+        """time_left of interval term k as the reference holds it (event_manager.py:368-372): [N] per env, or [1] for an
+        `is_global_time` term -- whose two device slots alternate by step parity, so that env 0 can write the new value
+        while the other envs of the same launch still read the old one."""
+        gt = self.interval_global_time.get(k)
+        if gt is None:
+            return self.interval_time_left[k]
+        t = getattr(self, "step_counter_t", None)
+        step = int(t.item()) + 1 if t is not None else self.step_counter
+        return gt[step & 1].reshape(1)
 
     def use_device_step_counter(self):
         """Keeps the step counter (the Philox key of perf mode) on the device: `process_action` / `decimation_fused`

@@ -56,7 +56,8 @@ def initial_env_state(spec: dict, seed: int) -> dict:
     ep = torch.randint(0, ml, (N,), generator=g)
     ep[torch.rand(N, generator=g) < 0.01] = ml - 1
     return {"episode_length_buf": ep.to(torch.int64), "cmd_time_left": torch.rand(N, generator=g) * 10.0,
-            "interval_time_left": torch.rand(N, generator=g) * 12.0}
+            "interval_time_left": torch.rand(N, generator=g) * 12.0,
+            "interval_global_time_left": 0.03}   # is_global_time terms: one timer, about to fire
 
 
 def init_fused_state(env, init):
@@ -66,6 +67,8 @@ def init_fused_state(env, init):
         env.cmd_time_left.copy_(init["cmd_time_left"])
     for t in env.interval_time_left:
         t.copy_(init["interval_time_left"])
+    for gt in getattr(env, "interval_global_time", {}).values():   # is_global_time terms: one timer, both parity slots
+        gt.fill_(float(init.get("interval_global_time_left", 0.03)))
 
 
 class SyntheticSim:

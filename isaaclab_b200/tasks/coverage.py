@@ -5,7 +5,8 @@ LAB/envs/mdp/rewards.py:245-283, terminations.py:60-88, observations.py:33,104,1
 
 Base: the flat Anymal-C velocity task.  Changes: IdealPD + stand-alone DCMotor actuator groups instead of the LSTM net;
 action clip; rewards contact_forces / action_l2 / joint_vel_l2 / is_alive / is_terminated; terminations
-root_height_below_minimum / bad_orientation; observations base_pos_z / joint_pos / joint_vel with scale and clip."""
+root_height_below_minimum / bad_orientation; observations base_pos_z / joint_pos / joint_vel with scale and clip;
+reset events gated by min_step_count_between_reset and an interval push on one global timer (is_global_time)."""
 from __future__ import annotations
 
 from ..actuators import DCMotorCfg, IdealPDActuatorCfg
@@ -42,8 +43,20 @@ OBSERVATIONS = {   # name: (func name, noise range | None, clip | None, scale | 
 }
 
 
+# EventManager gating (event_manager.py:204-270): reset terms that may only re-trigger after a number of env steps, and an
+# interval term on ONE global timer
+EVENT_GATES = {"reset_base": 3, "reset_robot_joints": 2}
+GLOBAL_PUSH = dict(interval_range_s=(0.03, 0.07), velocity_range={"x": (-0.5, 0.5), "y": (-0.5, 0.5)})
+
+
 def OpcodeCoverageEnvCfg():
+    from ..managers import EventTermCfg
     cfg = AnymalCFlatEnvCfg()
+    for name, m in EVENT_GATES.items():
+        getattr(cfg.events, name).min_step_count_between_reset = m
+    cfg.events.push_all = EventTermCfg(func=mdp.push_by_setting_velocity, mode="interval", is_global_time=True,
+                                       interval_range_s=GLOBAL_PUSH["interval_range_s"],
+                                       params={"velocity_range": dict(GLOBAL_PUSH["velocity_range"])})
     acts = {}
     for name, a in ACTUATORS.items():
         a = dict(a)

@@ -137,6 +137,10 @@ class OracleEnv:
             self.cmd_metric_xy, self.cmd_metric_yaw = z(N), z(N)
         ev = s.get("events", {})
         self.interval_time_left = [z(N) for _ in ev.get("interval_push", [])]
+        # is_global_time terms keep ONE timer (event_manager.py:113-118); gated reset terms keep the last trigger step
+        self.interval_global_time = {k: torch.zeros(1) for k, e in enumerate(ev.get("interval_push", [])) if e.get("is_global_time")}
+        self.common_step_counter = 0
+        self._gate = {}
         cur = s.get("curriculum")
         if cur:
             self.terrain_origins = _t(cur["terrain_origins"])
@@ -541,39 +545,62 @@ class OracleEnv:
         # reset events in cfg order (LAB/envs/mdp/events.py:823-865, 987-1051)
         ev = s.get("events", {})
         keys = ["x", "y", "z", "roll", "pitch", "yaw"]
+        def gated(key, e, env_ids):
+            """EventManager.apply(mode="reset") trigger logic (event_manager.py:232-270): the envs of `env_ids` the term
+            applies to; min_step_count_between_reset == 0 bypasses the bookkeeping."""
+            m = int(e.get("min_step_count", 0) or 0)
+            if m == 0:
+                return env_ids
+            last, once = self._gate.setdefault(key, (torch.zeros(self.N, dtype=torch.int32),
+                                                     torch.zeros(self.N, dtype=torch.bool)))
+            gstep = self.common_step_counter + 1   # env._sim_step_counter // decimation inside this step
+            valid = (gstep - last[env_ids]) >= m
+            valid |= (last[env_ids] == 0) & ~once[env_ids]
+            vids = env_ids[valid]
+            once[vids] = True
+            last[vids] = gstep
+            return vids
+
         if ev.get("reset_root_state"):
             e = ev["reset_root_state"]
-            root = self.default_root_state.unsqueeze(0).repeat(len(ids), 1)
-            rg = torch.tensor([e["pose_range"].get(k, (0.0, 0.0)) for k in keys], dtype=F32)
-            smp = mu.scale_uniform(ur[:, U_RESET_POSE:U_RESET_POSE + 6], rg[:, 0], rg[:, 1])
-            positions = root[:, 0:3] + self.env_origins[ids] + smp[:, 0:3]
-            dq = mu.quat_from_euler_xyz(smp[:, 3], smp[:, 4], smp[:, 5])
-            orientations = mu.quat_mul(root[:, 3:7], dq)
-            rg = torch.tensor([e["velocity_range"].get(k, (0.0, 0.0)) for k in keys], dtype=F32)
-            smp = mu.scale_uniform(ur[:, U_RESET_VEL:U_RESET_VEL + 6], rg[:, 0], rg[:, 1])
-            velocities = root[:, 7:13] + smp
-            sim["root_state_w"][ids, 0:3] = positions
-            sim["root_state_w"][ids, 3:7] = orientations
-            sim["root_state_w"][ids, 7:13] = velocities
+            vids = gated("root", e, ids)
+            if len(vids) > 0:
+                uv = u[vids]
+                root = self.default_root_state.unsqueeze(0).repeat(len(vids), 1)
+                rg = torch.tensor([e["pose_range"].get(k, (0.0, 0.0)) for k in keys], dtype=F32)
+                smp = mu.scale_uniform(uv[:, U_RESET_POSE:U_RESET_POSE + 6], rg[:, 0], rg[:, 1])
+                positions = root[:, 0:3] + self.env_origins[vids] + smp[:, 0:3]
+                dq = mu.quat_from_euler_xyz(smp[:, 3], smp[:, 4], smp[:, 5])
+                orientations = mu.quat_mul(root[:, 3:7], dq)
+                rg = torch.tensor([e["velocity_range"].get(k, (0.0, 0.0)) for k in keys], dtype=F32)
+                smp = mu.scale_uniform(uv[:, U_RESET_VEL:U_RESET_VEL + 6], rg[:, 0], rg[:, 1])
+                velocities = root[:, 7:13] + smp
+                sim["root_state_w"][vids, 0:3] = positions
+                sim["root_state_w"][vids, 3:7] = orientations
+                sim["root_state_w"][vids, 7:13] = velocities
         # every reset_joints_by_* term rewrites ALL joints (the reference ignores asset_cfg.joint_ids there)
         for k, e in enumerate(ev.get("reset_joints", [])):
+            vids = gated(f"joints{k}", e, ids)
+            if len(vids) == 0:
+                continue
+            uv = u[vids]
             J = self.J
             base = U_RESET_JOINT + 2 * J * k
-            jp = self.default_joint_pos.unsqueeze(0).repeat(len(ids), 1)
-            jv = self.default_joint_vel.unsqueeze(0).repeat(len(ids), 1)
-            up, uv = ur[:, base:base + J], ur[:, base + J:base + 2 * J]
+            jp = self.default_joint_pos.unsqueeze(0).repeat(len(vids), 1)
+            jv = self.default_joint_vel.unsqueeze(0).repeat(len(vids), 1)
+            up, uvv = uv[:, base:base + J], uv[:, base + J:base + 2 * J]
             (plo, phi), (vlo, vhi) = e["position_range"], e["velocity_range"]
-            sp, sv = up * (phi - plo) + plo, uv * (vhi - vlo) + vlo  # python-float span (math.py:1331)
+            sp, sv = up * (phi - plo) + plo, uvv * (vhi - vlo) + vlo  # python-float span (math.py:1331)
             if e["mode"] == "scale":
                 jp, jv = jp * sp, jv * sv
             else:
                 jp, jv = jp + sp, jv + sv
             jp = jp.clamp_(self.soft_joint_pos_limits[:, 0], self.soft_joint_pos_limits[:, 1])
             jv = jv.clamp_(-self.soft_joint_vel_limits, self.soft_joint_vel_limits)
-            sim["joint_pos"][ids] = jp  # write_joint_state_to_sim (articulation.py:516,548-550)
-            sim["joint_vel"][ids] = jv
-            self.prev_joint_vel[ids] = jv
-            self.joint_acc[ids] = 0.0
+            sim["joint_pos"][vids] = jp  # write_joint_state_to_sim (articulation.py:516,548-550)
+            sim["joint_vel"][vids] = jv
+            self.prev_joint_vel[vids] = jv
+            self.joint_acc[vids] = 0.0
         # manager resets in the order of manager_based_rl_env.py:364-389
         self.prev_action[ids], self.action[ids], self.raw_actions[ids] = 0.0, 0.0, 0.0
         for i, t in enumerate(s["rewards"]):  # reward_manager.py:100-126
@@ -631,13 +658,22 @@ class OracleEnv:
             self._command_compute(d, u_step)
         # EventManager.apply(mode="interval") (event_manager.py:204-229) + push_by_setting_velocity (events.py:795-820)
         for k, e in enumerate(s.get("events", {}).get("interval_push", [])):
-            tl = self.interval_time_left[k]
-            tl -= dt
-            vid = (tl < 1e-6).nonzero().flatten()
+            if e.get("is_global_time"):   # event_manager.py:213-220: one timer, one draw, every env is pushed
+                tl = self.interval_global_time[k]
+                tl -= dt
+                vid = torch.arange(self.N) if float(tl) < 1e-6 else torch.zeros(0, dtype=torch.long)
+                if len(vid) > 0:
+                    lo, hi = e["interval_range_s"]
+                    tl[:] = u_step[0, U_STEP_INTERVAL + 7 * k] * (hi - lo) + lo
+            else:
+                tl = self.interval_time_left[k]
+                tl -= dt
+                vid = (tl < 1e-6).nonzero().flatten()
             if len(vid) > 0:
                 base = U_STEP_INTERVAL + 7 * k
                 lo, hi = e["interval_range_s"]
-                tl[vid] = u_step[vid, base] * (hi - lo) + lo
+                if not e.get("is_global_time"):
+                    tl[vid] = u_step[vid, base] * (hi - lo) + lo
                 keys = ["x", "y", "z", "roll", "pitch", "yaw"]
                 rg = torch.tensor([e["velocity_range"].get(kk, (0.0, 0.0)) for kk in keys], dtype=F32)
                 vel = sim["root_state_w"][vid, 7:13]
@@ -678,4 +714,5 @@ class OracleEnv:
             prev = sim
         self.post_step(prev, u_reset, u_step)
         self.compute_obs(prev, u_obs)
+        self.common_step_counter += 1
         return self.obs_buf, self.reward_buf, self.terminated, self.truncated

@@ -274,13 +274,15 @@ class DrawLog:
 
     def _site(self):
         f = sys._getframe(2)
-        first, chain = None, []
+        first, chain, event = None, [], None
         while f is not None:
             fn = f.f_code.co_filename
             if fn.startswith(REF):
                 if first is None and not fn.endswith(self._SKIP_FILES):
                     first = f
                 chain.append(f.f_code.co_name)
+                if f.f_code.co_name == "apply" and fn.endswith("event_manager.py") and "index" in f.f_locals:
+                    event = (int(f.f_locals["index"]), bool(f.f_locals["term_cfg"].is_global_time))   # (term index, global timer)
             f = f.f_back
         if first is None:
             return None
@@ -288,14 +290,14 @@ class DrawLog:
         ids = loc.get("valid_env_ids", loc.get("env_ids", None))
         if isinstance(ids, torch.Tensor):
             ids = ids.clone()
-        return first.f_code.co_name, ids, tuple(chain)
+        return first.f_code.co_name, ids, tuple(chain), event
 
     def _log(self, u, extra=None):
         if not self.enabled:
             return
         site = self._site()
         if site is not None:
-            self.draws.append(dict(func=site[0], env_ids=site[1], chain=site[2], u=u.clone(), extra=extra))
+            self.draws.append(dict(func=site[0], env_ids=site[1], chain=site[2], event=site[3], u=u.clone(), extra=extra))
 
     def install(self):
         log = self
@@ -355,7 +357,6 @@ def layout_uniforms(draws, spec, N, filler):
         if t.get("noise") is not None and spec["observations"].get("enable_corruption", True):
             noisy_cols.append((c, w))
         c += w
-    n_interval = 0
     unused = []
     for d in draws:
         f, ids, chain, u = d["func"], d["env_ids"], d["chain"], d["u"]
@@ -384,13 +385,17 @@ def layout_uniforms(draws, spec, N, filler):
             order = [1, 2, 3] + ([4, 5] if heading else []) + [6]
             slot = order[k % len(order)]
             (u_r if in_reset else u_s)[ids, (omdp.U_RESET_CMD if in_reset else omdp.U_STEP_CMD) + slot] = u
-        elif f == "apply":   # EventManager.apply(mode="interval"): new time_left of the k-th interval term this step
-            base = omdp.U_STEP_INTERVAL + 7 * n_interval
-            u_s[ids, base] = u
+        elif f == "apply":   # EventManager.apply(mode="interval"): new time_left of interval term `index` this step
+            index, is_global = d["event"]
+            base = omdp.U_STEP_INTERVAL + 7 * index
+            if is_global:    # torch.rand(1), one timer for all envs (event_manager.py:213-217): env 0's slot
+                u_s[0, base] = u[0]
+            else:
+                u_s[ids, base] = u
         elif f == "push_by_setting_velocity":
-            base = omdp.U_STEP_INTERVAL + 7 * n_interval
-            u_s[ids, base + 1:base + 7] = u
-            n_interval += 1
+            index, is_global = d["event"]
+            base = omdp.U_STEP_INTERVAL + 7 * index
+            u_s[torch.arange(N) if is_global else ids, base + 1:base + 7] = u
         elif f == "uniform_noise":
             s0, w = noisy_cols[obs_col]
             assert u.shape == (N, w), (u.shape, w)
@@ -618,6 +623,12 @@ def coverage_reference_cfg():
         setattr(cfg.observations.policy, name,
                 ObservationTermCfg(func=getattr(rmdp, fn), noise=Unoise(n_min=nz[0], n_max=nz[1]) if nz else None, clip=clip,
                                    scale=scale))
+    from isaaclab.managers import EventTermCfg
+    for name, m in cov.EVENT_GATES.items():
+        getattr(cfg.events, name).min_step_count_between_reset = m
+    cfg.events.push_all = EventTermCfg(func=rmdp.push_by_setting_velocity, mode="interval", is_global_time=True,
+                                       interval_range_s=cov.GLOBAL_PUSH["interval_range_s"],
+                                       params={"velocity_range": dict(cov.GLOBAL_PUSH["velocity_range"])})
     return cfg
 
 
@@ -674,7 +685,7 @@ def build_reference_env(task, spec, slabs, init, tmpdir, wrap=False):
         term = env.command_manager.get_term(spec["command"]["name"])
         term.time_left[:] = init["cmd_time_left"]
     for tl in env.event_manager._interval_term_time_left:
-        tl[:] = init["interval_time_left"]
+        tl[:] = init["interval_time_left"] if tl.numel() > 1 else init.get("interval_global_time_left", 0.03)   # [1]: is_global_time
     return env, replay
 
 

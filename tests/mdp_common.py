@@ -47,6 +47,8 @@ def init_oracle_state(env, init):
         env.cmd_time_left[:] = init["cmd_time_left"]
     for t in env.interval_time_left:
         t[:] = init["interval_time_left"]
+    for gt in env.interval_global_time.values():
+        gt[:] = init.get("interval_global_time_left", 0.03)
 
 
 def init_fused_state(env, init):
@@ -117,7 +119,10 @@ def compare_fused_vs_oracle(fus, orc, spec, tag, f_out, o_out):
         exact(fus.terrain_levels, orc.terrain_levels, tag + " terrain_levels")
         close(fus.env_origins, orc.env_origins, tag + " env_origins")
     for i, t in enumerate(fus.interval_time_left):
-        close(t, orc.interval_time_left[i], tag + " interval time_left")
+        if i in orc.interval_global_time:   # is_global_time: one timer (the fused path double-buffers it by step parity)
+            close(fus.interval_timer(i), orc.interval_global_time[i], tag + " global interval time_left")
+        else:
+            close(t, orc.interval_time_left[i], tag + " interval time_left")
     if spec.get("raycaster"):
         if getattr(fus, "rc_ray_hits_w", None) is not None:
             hz_f, hz_o = fus.rc_ray_hits_w[..., 2].cpu(), orc.rc_hits[..., 2]

@@ -46,6 +46,8 @@ class _AsOracle:
             return f.step_reward[:, :len(spec["rewards"])].cpu()
         if name == "interval_time_left":
             return [t.cpu() for t in f.interval_time_left]
+        if name == "interval_global_time":
+            return {k: f.interval_timer(k).cpu() for k in f.interval_global_time}
         v = getattr(f, self._MAP.get(name, name))
         return v.cpu() if isinstance(v, torch.Tensor) else v
 

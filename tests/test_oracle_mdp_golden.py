@@ -69,6 +69,8 @@ def compare_state(env, ref, spec, tag, rtol=1e-6, atol=1e-6, torque_tol=None, ra
         exact(env.terrain_levels, ref["terrain_levels"], tag + " terrain_levels")
     close(env.env_origins, ref["env_origins"], tag + " env_origins", rtol, atol)
     for i, t in enumerate(env.interval_time_left):
+        if i in env.interval_global_time:   # is_global_time: the reference keeps a [1] tensor (event_manager.py:368-372)
+            t = env.interval_global_time[i]
         close(t, ref["interval_time_left"][i], tag + f" interval[{i}] time_left", rtol, atol)
     if spec.get("raycaster"):
         close(env.rc_drift, ref["rc_drift"], tag + " drift", rtol, atol)
