@@ -26,6 +26,7 @@ struct EnvHandle {
   B200LabEnvState* dev;   // device copy (kept for callers that want the descriptor on the device)
   float* derived;      // [N, kDerived] per-env derived state for compute_obs
   bool rays_vertical;  // all ray directions are (0,0,dz), dz != 0, and the sensor is yaw-only
+  int vert_batch;      // candidates per round trip of the vertical ray query (B200LAB_VERT_BATCH: 2 default, 3, 4)
   int obs_impl;        // 0 (default): per-ray kernel; 1: staged height scan (compute_obs_patch_kernel), opt-in via B200LAB_OBS_IMPL
   struct ObsCol* cols; // [obs_dim] per-column program of the observation group (compute_obs_kernel)
   MeshAccel mesh;      // host copy of the ray-caster mesh descriptor (passed by value to compute_obs)
@@ -1650,11 +1651,13 @@ __device__ __forceinline__ float obs_finish(const Env* __restrict__ e, float v, 
 #ifndef B200LAB_OBS_BLOCKS
 #define B200LAB_OBS_BLOCKS 4
 #endif
-template <bool kVerticalRays>
 #ifndef B200LAB_OBS_THREADS
 #define B200LAB_OBS_THREADS 64
 #endif
-__global__ void __launch_bounds__(B200LAB_OBS_THREADS, kVerticalRays ? B200LAB_OBS_BLOCKS * (256 / B200LAB_OBS_THREADS) : 2)
+// kBatch: candidates of the ray's cell requested per round trip (raycast_vertical); kBatch = 4 trades the 64-register cap
+// (and with it a quarter of the resident warps) for half the dependent round trips of a 4-candidate cell
+template <bool kVerticalRays, int kBatch = kVertBatch>
+__global__ void __launch_bounds__(B200LAB_OBS_THREADS, kVerticalRays ? (kBatch > 2 ? 3 : B200LAB_OBS_BLOCKS) * (256 / B200LAB_OBS_THREADS) : 2)
 compute_obs_kernel(const __grid_constant__ Env env_param, Sim sim, int64_t step, const ObsCol* __restrict__ cols,
                    const float* __restrict__ derived, const __grid_constant__ MeshAccel mesh, int has_mesh,
                    const float* __restrict__ spec_z, unsigned env_begin, unsigned env_count) {
@@ -1700,7 +1703,7 @@ compute_obs_kernel(const __grid_constant__ Env env_param, Sim sim, int64_t step,
           if (o[18] != 0.f) {   // speculative scan cast from this very pose (height_scan_spec_kernel)
             float z = spec_z[(size_t)n * e->R + li];
             if (z != INFINITY) hit = {st.x, st.y, z};
-          } else if (has_mesh && raycast_vertical(mesh, st, cc.w, e->rc_max_distance, tt, face)) {
+          } else if (has_mesh && raycast_vertical<kBatch>(mesh, st, cc.w, e->rc_max_distance, tt, face)) {
             hit = {st.x, st.y, st.z + tt * cc.w};
           }
         } else {
@@ -2260,6 +2263,8 @@ void* b200lab_env_create(const B200LabEnvState* st) {
   h->has_mesh = false;
   {
     const char* impl = getenv("B200LAB_OBS_IMPL");
+    const char* vb = getenv("B200LAB_VERT_BATCH");
+    h->vert_batch = vb ? atoi(vb) : kVertBatch;
     h->obs_impl = impl ? atoi(impl) : 0;   // measured on B200 (profiles/r2_notes.md): per-ray 45 us, staged 90 us at 4096 envs
   }
   h->side2 = nullptr;
@@ -2546,7 +2551,8 @@ int b200lab_compute_obs_range(void* env, const B200LabSimView* sim, int64_t step
     return check_launch("compute_obs");
   }
   {
-    auto kern = h->rays_vertical ? compute_obs_kernel<true> : compute_obs_kernel<false>;
+    auto kern = !h->rays_vertical ? compute_obs_kernel<false> : h->vert_batch == 4 ? compute_obs_kernel<true, 4>
+              : h->vert_batch == 3 ? compute_obs_kernel<true, 3> : compute_obs_kernel<true>;
     cudaError_t err = launch_pdl(kern, dim3((unsigned)ceil_div(total, B200LAB_OBS_THREADS)), dim3(B200LAB_OBS_THREADS), 0, st_, h->host, *sim, step_counter,
                                  (const ObsCol*)h->cols, (const float*)h->derived, h->mesh, h->has_mesh ? 1 : 0,
                                  (const float*)h->spec_z, (unsigned)env_begin, (unsigned)cnt);

@@ -125,6 +125,7 @@ __device__ __forceinline__ float ray_tri_vertical_rec(const MeshAccel& m, int f,
 // round trip).  The kernel is bound by the number of divergent L2 requests in flight, not by the tests.
 constexpr int kVertBatch = 2;
 
+template <int kBatch = kVertBatch>
 __device__ __forceinline__ bool raycast_vertical(const MeshAccel& m, f3 o, float dz, float max_dist, float& t_out,
                                                  int& face_out) {
   float t_best = max_dist;
@@ -134,18 +135,18 @@ __device__ __forceinline__ bool raycast_vertical(const MeshAccel& m, f3 o, float
     int c = cy * m.nx + cx;
     int s = __ldg(m.cell_start + c), e = __ldg(m.cell_start + c + 1);
     float inv_dz = 1.0f / dz;
-    for (int k = s; k < e; k += kVertBatch) {
-      int f[kVertBatch];
+    for (int k = s; k < e; k += kBatch) {
+      int f[kBatch];
 #pragma unroll
-      for (int i = 0; i < kVertBatch; ++i) f[i] = __ldg(m.cell_tris + min(k + i, e - 1)) & kEntryIdMask;
-      float4 ra[kVertBatch], rb[kVertBatch], rc[kVertBatch];
+      for (int i = 0; i < kBatch; ++i) f[i] = __ldg(m.cell_tris + min(k + i, e - 1)) & kEntryIdMask;
+      float4 ra[kBatch], rb[kBatch], rc[kBatch];
 #pragma unroll
-      for (int i = 0; i < kVertBatch; ++i) {
+      for (int i = 0; i < kBatch; ++i) {
         const float4* r = m.rec + (size_t)f[i] * 3;
         ra[i] = __ldg(r); rb[i] = __ldg(r + 1); rc[i] = __ldg(r + 2);
       }
 #pragma unroll
-      for (int i = 0; i < kVertBatch; ++i) {
+      for (int i = 0; i < kBatch; ++i) {
         float t = ray_tri_vertical_rec(m, f[i], ra[i], rb[i], rc[i], o, dz, inv_dz);   // padded slots repeat the last id
         if (t > 0.0f && t <= t_best) { t_best = t; face_best = f[i]; }
       }

@@ -20,6 +20,7 @@ def main():
     ap.add_argument("--impl", default="0,1")
     ap.add_argument("--task", default="Isaac-Velocity-Rough-Anymal-C-v0")
     ap.add_argument("--no-hits", action="store_true")
+    ap.add_argument("--cell", type=float, default=0.0, help="bin-grid cell edge of the terrain mesh (0: the builder's default)")
     args = ap.parse_args()
     from isaaclab_b200 import terrains
     from isaaclab_b200.envs.compile import compile_env_cfg
@@ -29,6 +30,8 @@ def main():
     cfg = TASKS[args.task]()
     terrain = terrains.TerrainGenerator(cfg.scene.terrain.terrain_generator)
     spec = compile_env_cfg(cfg, num_envs=args.envs, terrain=terrain, seed=0)
+    if args.cell > 0:
+        spec["raycaster"]["cell_size"] = args.cell
     K = 16
     slabs = generate_slabs(spec, K, seed=1237)
     init = initial_env_state(spec, seed=7)
