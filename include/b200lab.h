@@ -541,6 +541,25 @@ int b200lab_episode_stats(const float* rewards, const void* dones, int32_t dones
                           float* cur_reward_sum, float* cur_episode_length, float* ring_reward, float* ring_length,
                           int32_t ring_size, int64_t* pushed, void* stream);
 
+/* Recurrent policy cells (RSL/networks/memory.py:21-38 -> torch.nn.LSTM / torch.nn.GRU; used by
+ * RSL/modules/actor_critic_recurrent.py:141-160).  The matrix products of a step are b200lab_linear_fwd calls
+ * (gi = x W_ih^T + b_ih for all time steps at once, gh = h W_hh^T + b_hh per step); these entry points are the gate
+ * arithmetic and its derivative.  All tensors row-major fp32; B = trajectories in the batch, H = hidden size.
+ * LSTM: gi, gh, gates, dgates [B,4H] in torch's gate order i,f,g,o; `gates` (post-activation, may be NULL in inference)
+ * is what backward reads.  `dc` is read as dL/dc_t and overwritten with dL/dc_{t-1}; dh_out / dh_rec (either may be NULL)
+ * are the gradient of h_t from the layer above / from step t+1.
+ * GRU: gi, gh, dgi, dgh [B,3H] in order r,z,n; `saved` [B,4H] = r|z|n|(W_hn h + b_hn).  dh_dir_in / dh_dir_out carry
+ * the z * h_{t-1} path of dL/dh between steps (they may be the same buffer); dh_rec is dgh . W_hh of step t+1. */
+int b200lab_lstm_cell_fwd(const float* gi, const float* gh, const float* c_prev, float* h, float* c, float* gates,
+                          int64_t B, int32_t H, void* stream);
+int b200lab_lstm_cell_bwd(const float* gates, const float* c_prev, const float* c, const float* dh_out,
+                          const float* dh_rec, float* dc, float* dgates, int64_t B, int32_t H, void* stream);
+int b200lab_gru_cell_fwd(const float* gi, const float* gh, const float* h_prev, float* h, float* saved, int64_t B,
+                         int32_t H, void* stream);
+int b200lab_gru_cell_bwd(const float* saved, const float* h_prev, const float* dh_out, const float* dh_rec,
+                         const float* dh_dir_in, float* dh_dir_out, float* dgi, float* dgh, int64_t B, int32_t H,
+                         void* stream);
+
 /* Actor-critic MLP (RSL/networks/mlp.py:60-80: Linear+ELU ... Linear).  Y = act(X W^T + b).
  * X [M,K] row-major, W [Nout,K] row-major (nn.Linear.weight), b [Nout], Y [M,Nout].
  * precision: 0 = fp32 FFMA (exact-order reference path), 1 = tcgen05 kind::tf32, 2 = tcgen05 3xTF32 split. */

@@ -103,6 +103,10 @@ _SIGS = {
     "b200lab_compute_obs_range": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_int32, C.c_void_p]),
     "b200lab_step_tail_begin": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p]),
     "b200lab_step_tail_end": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "b200lab_lstm_cell_fwd": (C.c_int, [C.c_void_p] * 6 + [C.c_int64, C.c_int32, C.c_void_p]),
+    "b200lab_lstm_cell_bwd": (C.c_int, [C.c_void_p] * 7 + [C.c_int64, C.c_int32, C.c_void_p]),
+    "b200lab_gru_cell_fwd": (C.c_int, [C.c_void_p] * 5 + [C.c_int64, C.c_int32, C.c_void_p]),
+    "b200lab_gru_cell_bwd": (C.c_int, [C.c_void_p] * 8 + [C.c_int64, C.c_int32, C.c_void_p]),
     "b200lab_mesh_create": (C.c_void_p, [C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.c_float]),
     "b200lab_mesh_device_ptr": (C.c_void_p, [C.c_void_p]),
     "b200lab_mesh_bytes": (C.c_int64, [C.c_void_p]),

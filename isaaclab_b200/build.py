@@ -29,6 +29,7 @@ UNITS = {
     "mlp.cu": [],
     "mlp_tc.cu": [],
     "ppo.cu": [],
+    "rnn.cu": [],
 }
 
 

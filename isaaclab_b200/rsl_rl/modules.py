@@ -66,23 +66,27 @@ class _Net:
             inp = b["acts"][i]
         return inp
 
-    def backward(self, x, d_out, precision):
-        """Gradients of the last forward(x); d_out is dLoss/dOutput [M, out]; fills every layer's .grad view."""
+    def backward(self, x, d_out, precision, need_dx=False):
+        """Gradients of the last forward(x); d_out is dLoss/dOutput [M, out]; fills every layer's .grad view.  With
+        `need_dx` the gradient w.r.t. `x` is computed too and returned (the recurrent policy feeds it to the RNN)."""
         L = _lib.lib()
         M = x.shape[0]
         b = self.buffers(M, x.device)
         s = _lib.current_stream()
         dy = d_out
+        if need_dx and "dx0" not in b:
+            b["dx0"] = torch.empty(M, self.dims[0], device=x.device)
         for i in reversed(range(len(self.linears))):
             lin = self.linears[i]
             last = i == len(self.linears) - 1
             inp = x if i == 0 else b["acts"][i - 1]
-            dx = None if i == 0 else b["grads"][i - 1]
+            dx = (b["dx0"] if need_dx else None) if i == 0 else b["grads"][i - 1]
             _lib.check(L.b200lab_linear_bwd(_lib.ptr(inp), _lib.ptr(lin.weight), _lib.ptr(b["acts"][i]), _lib.ptr(dy),
                                             _lib.ptr(b["dz"]), _lib.ptr(dx), _lib.ptr(lin.weight.grad),
                                             _lib.ptr(lin.bias.grad), M, self.dims[i], self.dims[i + 1],
                                             0 if last else 1, precision, _lib.ptr(b["work"]), s))
             dy = dx
+        return b["dx0"] if need_dx else None
 
 
 class EmpiricalNormalization(nn.Module):
@@ -324,3 +328,263 @@ class ActorCritic(nn.Module):
             self.actor_obs_normalizer.update(self.get_actor_obs(obs))
         if self.critic_obs_normalization:
             self.critic_obs_normalizer.update(self.get_critic_obs(obs))
+
+
+def unpad_trajectories(trajectories, masks):
+    """Inverse of `split_and_pad_trajectories` (RSL/utils/utils.py:133-141): [T, n_traj, H] + masks [T, n_traj] ->
+    [T, n_envs, H], the valid steps in env-major order."""
+    T = trajectories.shape[0]
+    tr, t = masks.t().nonzero(as_tuple=True)           # valid (trajectory, step) pairs, trajectory-major = env-major
+    return trajectories[t, tr].view(-1, T, trajectories.shape[-1]).transpose(1, 0)
+
+
+class Memory(nn.Module):
+    """RSL/networks/memory.py:14-70 -- the recurrent core of `ActorCriticRecurrent` (GRU or LSTM, `num_layers` deep).
+
+    `self.rnn` is a torch.nn.LSTM / GRU used as the PARAMETER CONTAINER only (same state_dict keys as the reference:
+    `rnn.weight_ih_l0`, ...); the arithmetic is explicit: per layer ONE GEMM projects every time step's input, then each
+    step is one h.W_hh^T GEMM + one cell kernel (b200lab_lstm_cell_fwd / b200lab_gru_cell_fwd).  Batch mode keeps what
+    back-propagation through time needs; `backward` walks the steps in reverse with the cell-derivative kernels and leaves
+    dW_ih / dW_hh / db in the parameters' `.grad` views (two GEMMs per layer over all steps at once)."""
+
+    def __init__(self, input_size, type="lstm", num_layers=1, hidden_size=256, device="cuda", precision=0):
+        super().__init__()
+        self.is_lstm = type.lower() != "gru"
+        rnn_cls = nn.LSTM if self.is_lstm else nn.GRU
+        self.rnn = rnn_cls(input_size=input_size, hidden_size=hidden_size, num_layers=num_layers).to(device)
+        self.input_size, self.hidden_size, self.num_layers = int(input_size), int(hidden_size), int(num_layers)
+        self.G = 4 if self.is_lstm else 3
+        self.hidden_states = None
+        self.precision = precision
+        self._saved = None
+        self._zero_bias = None
+
+    def _w(self, l):
+        r = self.rnn
+        return (getattr(r, f"weight_ih_l{l}"), getattr(r, f"weight_hh_l{l}"), getattr(r, f"bias_ih_l{l}"),
+                getattr(r, f"bias_hh_l{l}"))
+
+    def _linear(self, x, w, b, out):
+        M, K = x.shape
+        _lib.check(_lib.lib().b200lab_linear_fwd(_lib.ptr(x), _lib.ptr(w), _lib.ptr(b), _lib.ptr(out), M, K, w.shape[0], 0,
+                                                 self.precision, _lib.current_stream()))
+        return out
+
+    def _run(self, x, h0, c0, save):
+        """x [T, B, I]; h0 (and c0) [L, B, H].  Returns out [T, B, H] and the final states [L, B, H]."""
+        L, s, p = _lib.lib(), _lib.current_stream(), _lib.ptr
+        T, B, _ = x.shape
+        H, G, dev = self.hidden_size, self.G, x.device
+        hn = torch.empty(self.num_layers, B, H, device=dev)
+        cn = torch.empty(self.num_layers, B, H, device=dev) if self.is_lstm else None
+        saved = []
+        inp = x.contiguous()
+        gh = torch.empty(B, G * H, device=dev)
+        for l in range(self.num_layers):
+            w_ih, w_hh, b_ih, b_hh = self._w(l)
+            gi = self._linear(inp.view(T * B, -1), w_ih, b_ih, torch.empty(T * B, G * H, device=dev)).view(T, B, G * H)
+            hall = torch.empty(T + 1, B, H, device=dev)
+            hall[0].copy_(h0[l])
+            call = None
+            if self.is_lstm:
+                call = torch.empty(T + 1, B, H, device=dev)
+                call[0].copy_(c0[l])
+            act = torch.empty(T, B, 4 * H, device=dev) if save else None
+            for t in range(T):
+                self._linear(hall[t], w_hh, b_hh, gh)
+                a_t = p(act[t]) if save else None
+                if self.is_lstm:
+                    _lib.check(L.b200lab_lstm_cell_fwd(p(gi[t]), p(gh), p(call[t]), p(hall[t + 1]), p(call[t + 1]), a_t, B, H, s))
+                else:
+                    _lib.check(L.b200lab_gru_cell_fwd(p(gi[t]), p(gh), p(hall[t]), p(hall[t + 1]), a_t, B, H, s))
+            hn[l].copy_(hall[T])
+            if self.is_lstm:
+                cn[l].copy_(call[T])
+            if save:
+                saved.append(dict(inp=inp, hall=hall, call=call, act=act))
+            inp = hall[1:]
+        self._saved = saved if save else None
+        return inp, hn, cn
+
+    def forward(self, input, masks=None, hidden_states=None):
+        batch_mode = masks is not None
+        if batch_mode:   # policy update: padded trajectories [T, n_traj, I] from the saved hidden states (memory.py:29-34)
+            if hidden_states is None:
+                raise ValueError("Hidden states not passed to memory module during policy update")
+            h0, c0 = (hidden_states if self.is_lstm else (hidden_states, None))
+            out, _, _ = self._run(input, h0.contiguous(), c0.contiguous() if c0 is not None else None, save=True)
+            self._masks = masks
+            self._padded_shape = out.shape
+            return unpad_trajectories(out, masks)
+        # inference / rollout: one step from the hidden states of the last step (memory.py:36-37)
+        x = input.unsqueeze(0)
+        B = x.shape[1]
+        if self.hidden_states is None:
+            z = torch.zeros(self.num_layers, B, self.hidden_size, device=x.device)
+            h0, c0 = z, (z.clone() if self.is_lstm else None)
+        else:
+            h0, c0 = (self.hidden_states if self.is_lstm else (self.hidden_states, None))
+        out, hn, cn = self._run(x, h0, c0, save=False)
+        self.hidden_states = (hn, cn) if self.is_lstm else hn
+        return out
+
+    def backward(self, d_out):
+        """d_out: gradient of the UNPADDED output of the last batch-mode forward, [T, n_envs, H].  Padded steps receive
+        zero gradient (their outputs were dropped by `unpad_trajectories`), which is what autograd gives the reference."""
+        L, s, p = _lib.lib(), _lib.current_stream(), _lib.ptr
+        masks = self._masks
+        T, B, H = self._padded_shape
+        G, dev = self.G, d_out.device
+        tr, t_idx = masks.t().nonzero(as_tuple=True)
+        d_pad = torch.zeros(T, B, H, device=dev)
+        d_pad[t_idx, tr] = d_out.transpose(1, 0).reshape(-1, H)
+        if self._zero_bias is None:
+            self._zero_bias = torch.zeros(H, device=dev)
+        dh_top = d_pad
+        for l in reversed(range(self.num_layers)):
+            sv = self._saved[l]
+            w_ih, w_hh, b_ih, b_hh = self._w(l)
+            w_hh_t = w_hh.t().contiguous()                       # [H, G*H]: dh_{t-1} += dgates_t . W_hh as a linear_fwd
+            dgi = torch.empty(T, B, G * H, device=dev)
+            dgh = dgi if self.is_lstm else torch.empty(T, B, G * H, device=dev)
+            dh_rec = torch.empty(B, H, device=dev)
+            carry = torch.zeros(B, H, device=dev)                # LSTM: dL/dc; GRU: the z * h_{t-1} path of dL/dh
+            for t in reversed(range(T)):
+                rec = p(dh_rec) if t < T - 1 else None
+                if self.is_lstm:
+                    _lib.check(L.b200lab_lstm_cell_bwd(p(sv["act"][t]), p(sv["call"][t]), p(sv["call"][t + 1]), p(dh_top[t]), rec,
+                                                       p(carry), p(dgi[t]), B, H, s))
+                else:
+                    _lib.check(L.b200lab_gru_cell_bwd(p(sv["act"][t]), p(sv["hall"][t]), p(dh_top[t]), rec, p(carry), p(carry),
+                                                      p(dgi[t]), p(dgh[t]), B, H, s))
+                if t > 0:
+                    self._linear(dgh[t], w_hh_t, self._zero_bias, dh_rec)
+            inp = sv["inp"].view(T * B, -1)
+            K = inp.shape[1]
+            ws = max(L.b200lab_linear_bwd_workspace_bytes(T * B, K, G * H), L.b200lab_linear_bwd_workspace_bytes(T * B, H, G * H))
+            work = torch.empty((ws + 3) // 4, device=dev)
+            dx = torch.empty(T, B, K, device=dev) if l > 0 else None
+            _lib.check(L.b200lab_linear_bwd(p(inp), p(w_ih), None, p(dgi), None, p(dx), p(w_ih.grad), p(b_ih.grad), T * B, K,
+                                            G * H, 0, self.precision, p(work), s))
+            hprev = sv["hall"][:T].view(T * B, H)
+            _lib.check(L.b200lab_linear_bwd(p(hprev), p(w_hh), None, p(dgh), None, None, p(w_hh.grad), p(b_hh.grad), T * B, H,
+                                            G * H, 0, self.precision, p(work), s))
+            dh_top = dx
+        self._saved = None
+
+    def reset(self, dones=None, hidden_states=None):
+        if dones is None:   # reset all hidden states (memory.py:41-45)
+            self.hidden_states = hidden_states
+        elif self.hidden_states is not None:   # zero the rows of the finished envs, on the device, no sync
+            if hidden_states is not None:
+                raise NotImplementedError("Resetting hidden states of done environments with custom hidden states is not implemented")
+            m = (dones == 1).view(1, -1, 1)
+            for hs in (self.hidden_states if isinstance(self.hidden_states, tuple) else (self.hidden_states,)):
+                hs.masked_fill_(m, 0.0)
+
+    def detach_hidden_states(self, dones=None):
+        """No autograd graph hangs off the hidden states on this path (memory.py:57-70 is a no-op here)."""
+
+
+class ActorCriticRecurrent(ActorCritic):
+    """RSL/modules/actor_critic_recurrent.py:17-190: `Memory` (LSTM / GRU) in front of the actor and critic MLPs.  Same
+    constructor kwargs, method surface and state_dict keys (`memory_a.rnn.*`, `actor.*`, `memory_c.rnn.*`, `critic.*`,
+    `std`); parameters live in the same flat buffers as `ActorCritic`'s."""
+    is_recurrent = True
+
+    def __init__(self, obs, obs_groups, num_actions, actor_obs_normalization=False, critic_obs_normalization=False,
+                 actor_hidden_dims=[256, 256, 256], critic_hidden_dims=[256, 256, 256], activation="elu",
+                 init_noise_std=1.0, noise_std_type: str = "scalar", rnn_type="lstm", rnn_hidden_dim=256, rnn_num_layers=1,
+                 device=None, precision: int = 0, **kwargs):
+        if "rnn_hidden_size" in kwargs:   # deprecated spelling (actor_critic_recurrent.py:36-43)
+            import warnings
+            warnings.warn("The argument `rnn_hidden_size` is deprecated and will be removed in a future version. "
+                          "Please use `rnn_hidden_dim` instead.", DeprecationWarning)
+            size = kwargs.pop("rnn_hidden_size")
+            if rnn_hidden_dim == 256:
+                rnn_hidden_dim = size
+        if kwargs:
+            print("ActorCriticRecurrent.__init__ got unexpected arguments, which will be ignored: " + str(kwargs.keys()))
+        nn.Module.__init__(self)
+        if activation.lower() != "elu":
+            raise ValueError("isaaclab_b200 ActorCriticRecurrent implements the ELU MLP used by the supported configs")
+        if noise_std_type != "scalar":
+            raise ValueError("isaaclab_b200 ActorCriticRecurrent supports noise_std_type='scalar'")
+        self.obs_groups = obs_groups
+        for g in list(obs_groups["policy"]) + list(obs_groups["critic"]):
+            assert len(obs[g].shape) == 2, "The ActorCriticRecurrent module only supports 1D observations."
+        num_actor_obs = sum(obs[g].shape[-1] for g in obs_groups["policy"])
+        num_critic_obs = sum(obs[g].shape[-1] for g in obs_groups["critic"])
+        if device is None:
+            device = next(iter(obs.values())).device if hasattr(obs, "values") else "cuda"
+        # registration order = the reference's, so named_parameters() / optimizer state indices line up
+        self.memory_a = Memory(num_actor_obs, type=rnn_type, num_layers=rnn_num_layers, hidden_size=rnn_hidden_dim,
+                               device=device, precision=precision)
+        self.actor = _mlp(rnn_hidden_dim, num_actions, actor_hidden_dims)
+        self.actor_obs_normalization = bool(actor_obs_normalization)
+        self.actor_obs_normalizer = (EmpiricalNormalization(num_actor_obs, device=device)
+                                     if actor_obs_normalization else nn.Identity())
+        self.memory_c = Memory(num_critic_obs, type=rnn_type, num_layers=rnn_num_layers, hidden_size=rnn_hidden_dim,
+                               device=device, precision=precision)
+        self.critic = _mlp(rnn_hidden_dim, 1, critic_hidden_dims)
+        self.critic_obs_normalization = bool(critic_obs_normalization)
+        self.critic_obs_normalizer = (EmpiricalNormalization(num_critic_obs, device=device)
+                                      if critic_obs_normalization else nn.Identity())
+        self.noise_std_type = noise_std_type
+        self.std = nn.Parameter(init_noise_std * torch.ones(num_actions))
+        self.num_actions = num_actions
+        self.precision = precision
+        self._flatten(torch.device(device))
+        self._a = _Net(self.actor)
+        self._c = _Net(self.critic)
+        self._mean = None
+        self._value = None
+        self._sigma_cache = {}
+
+    def reset(self, dones=None):
+        self.memory_a.reset(dones)
+        self.memory_c.reset(dones)
+
+    def get_hidden_states(self):
+        return self.memory_a.hidden_states, self.memory_c.hidden_states
+
+    def _normalized(self, x, normalizer, on):
+        x = x.contiguous().float()
+        if not on:
+            return x
+        return normalizer(x.view(-1, x.shape[-1])).view(x.shape)   # padded trajectories are [T, n_traj, D]
+
+    def actor_features(self, obs, masks=None, hidden_states=None):
+        """Normalised actor observations through `memory_a`: [B, H] in rollout mode, [T * n_envs, H] in batch mode."""
+        x = self._normalized(self.get_actor_obs(obs), self.actor_obs_normalizer, self.actor_obs_normalization)
+        out = self.memory_a(x, masks, hidden_states)
+        return out.squeeze(0) if masks is None else out.reshape(-1, out.shape[-1])
+
+    def critic_features(self, obs, masks=None, hidden_states=None):
+        x = self._normalized(self.get_critic_obs(obs), self.critic_obs_normalizer, self.critic_obs_normalization)
+        out = self.memory_c(x, masks, hidden_states)
+        return out.squeeze(0) if masks is None else out.reshape(-1, out.shape[-1])
+
+    def act(self, obs, masks=None, hidden_states=None, eps=None, **kwargs):
+        f = self.actor_features(obs, masks, hidden_states).contiguous()
+        self._mean = self._a.forward(f, self.precision)
+        M, A = self._mean.shape
+        if eps is None:
+            eps = torch.randn(M, A, device=f.device)
+        actions = torch.empty(M, A, device=f.device)
+        self._log_prob = torch.empty(M, device=f.device)
+        _lib.check(_lib.lib().b200lab_sample_actions(_lib.ptr(self._mean), _lib.ptr(self.std), _lib.ptr(eps),
+                                                    _lib.ptr(actions), _lib.ptr(self._log_prob), None, M, A,
+                                                    _lib.current_stream()))
+        self._last_actions = actions
+        return actions
+
+    def act_inference(self, obs):
+        return self._a.forward(self.actor_features(obs).contiguous(), self.precision).clone()
+
+    def evaluate(self, obs, masks=None, hidden_states=None, **kwargs):
+        return self._evaluate(obs, masks, hidden_states).clone()
+
+    def _evaluate(self, obs, masks=None, hidden_states=None):
+        self._value = self._c.forward(self.critic_features(obs, masks, hidden_states).contiguous(), self.precision)
+        return self._value

@@ -70,6 +70,8 @@ class PPO:
         self.storage = RolloutStorage(training_type, num_envs, num_transitions_per_env, obs, actions_shape, self.device)
 
     def act(self, obs, eps=None):
+        if self.policy.is_recurrent:   # the states the step STARTS from (ppo.py:130-131); the memories replace them in act
+            self.transition.hidden_states = self.policy.get_hidden_states()
         self.transition.actions = self.policy.act(obs, eps=eps)
         self.transition.values = self.policy._evaluate(obs)
         self.transition.actions_log_prob = self.policy.get_actions_log_prob(self.transition.actions)
@@ -104,11 +106,25 @@ class PPO:
         self._stat_sum.zero_()
         num_updates = 0
         inv_world = 1.0 / self.gpu_world_size
+        recurrent = pol.is_recurrent
+        if recurrent:   # ppo.py:194-197
+            generator = self.storage.recurrent_mini_batch_generator(self.num_mini_batches, self.num_learning_epochs)
+        else:
+            generator = self.storage.mini_batch_generator(self.num_mini_batches, self.num_learning_epochs, indices=indices)
         for (obs_batch, actions_batch, target_values_batch, advantages_batch, returns_batch, old_lp_batch, old_mu_batch,
-             old_sigma_batch, _, _) in self.storage.mini_batch_generator(self.num_mini_batches, self.num_learning_epochs,
-                                                                         indices=indices):
-            x = pol.actor_input(obs_batch)
-            xc = pol.critic_input(obs_batch)
+             old_sigma_batch, hid_states_batch, masks_batch) in generator:
+            if recurrent:
+                # padded trajectories through the memories from the saved hidden states (ppo.py:249-252), then the
+                # [T, n_envs, .] slabs flattened time-major to the rows the MLP / loss kernels see
+                x = pol.actor_features(obs_batch, masks_batch, hid_states_batch[0]).contiguous()
+                xc = pol.critic_features(obs_batch, masks_batch, hid_states_batch[1]).contiguous()
+                flat = lambda v: v.reshape(-1, v.shape[-1]).contiguous()   # noqa: E731
+                actions_batch, target_values_batch, advantages_batch = flat(actions_batch), flat(target_values_batch), flat(advantages_batch)
+                returns_batch, old_lp_batch = flat(returns_batch), flat(old_lp_batch)
+                old_mu_batch, old_sigma_batch = flat(old_mu_batch), flat(old_sigma_batch)
+            else:
+                x = pol.actor_input(obs_batch)
+                xc = pol.critic_input(obs_batch)
             M, A = actions_batch.shape
             mu = pol._a.forward(x, pol.precision)
             value = pol._c.forward(xc, pol.precision)
@@ -127,8 +143,12 @@ class PPO:
             a.d_std = pol.std.grad.data_ptr()
             a.stats = pol.stats.data_ptr()
             _lib.check(L.b200lab_ppo_loss(ctypes.byref(a), s))
-            pol._a.backward(x, d[0], pol.precision)
-            pol._c.backward(xc, d[1], pol.precision)
+            dxa = pol._a.backward(x, d[0], pol.precision, need_dx=recurrent)
+            dxc = pol._c.backward(xc, d[1], pol.precision, need_dx=recurrent)
+            if recurrent:   # back-propagation through time into memory_a / memory_c
+                T = self.storage.num_transitions_per_env
+                pol.memory_a.backward(dxa.view(T, -1, dxa.shape[-1]))
+                pol.memory_c.backward(dxc.view(T, -1, dxc.shape[-1]))
             if self.is_multi_gpu:
                 self.reduce_parameters()
             if self.desired_kl is not None and self.schedule == "adaptive":

@@ -19,10 +19,10 @@ import warnings
 import torch
 
 from .. import _lib
-from .modules import ActorCritic
+from .modules import ActorCritic, ActorCriticRecurrent
 from .ppo import PPO
 
-_POLICIES = {"ActorCritic": ActorCritic}
+_POLICIES = {"ActorCritic": ActorCritic, "ActorCriticRecurrent": ActorCriticRecurrent}
 _ALGORITHMS = {"PPO": PPO}
 _RING = 100  # deque(maxlen=100), on_policy_runner.py:83-84
 

@@ -107,7 +107,25 @@ class RolloutStorage:
             for k in self.observations.keys():
                 if k != self._obs_key:
                     self.observations[k][self.step].copy_(transition.observations[k])
+        self._save_hidden_states(transition.hidden_states)
         self.step += 1
+
+    def _save_hidden_states(self, hidden_states):
+        """The recurrent policy's states BEFORE the step, per transition (rollout_storage.py:105-123): lists of
+        [T, num_layers, N, H] slabs -- (h, c) for an LSTM, (h,) for a GRU -- for the actor and the critic memory."""
+        if hidden_states is None or hidden_states == (None, None):
+            return
+        T = self.num_transitions_per_env
+        per_net = []
+        for hs in hidden_states:
+            per_net.append(hs if isinstance(hs, (tuple, list)) else (hs,))
+        if self.saved_hidden_states_a is None:
+            self.saved_hidden_states_a = [torch.zeros(T, *h.shape, device=self.device) for h in per_net[0]]
+            self.saved_hidden_states_c = [torch.zeros(T, *h.shape, device=self.device) for h in per_net[1]]
+        for slab, h in zip(self.saved_hidden_states_a, per_net[0]):
+            slab[self.step].copy_(h)
+        for slab, h in zip(self.saved_hidden_states_c, per_net[1]):
+            slab[self.step].copy_(h)
 
     def clear(self):
         self.step = 0
@@ -166,6 +184,73 @@ class RolloutStorage:
                 obs_batch = TensorDict(groups, batch_size=[mini_batch_size], device=self.device)
                 yield (obs_batch, b["actions"], b["values"], b["advantages"], b["returns"], b["log_prob"], b["mu"],
                        b["sigma"], (None, None), None)
+
+
+    def recurrent_mini_batch_generator(self, num_mini_batches, num_epochs=8):
+        """rollout_storage.py:206-260: minibatches are CONTIGUOUS ENV RANGES (whole rollouts, time-major), the observations
+        come as zero-padded trajectories [T, n_traj, D] with their validity masks, and the hidden states are those saved
+        at each trajectory's first step.  The per-env slabs are returned as views of the storage (no gather)."""
+        if self.training_type != "rl":
+            raise ValueError("This function is only available for reinforcement learning training.")
+        T, N = self.num_transitions_per_env, self.num_envs
+        padded_obs, masks, starts = split_and_pad_trajectories(self.observations, self.dones, return_starts=True)
+        mb = N // num_mini_batches
+        # trajectories are numbered env-major, so an env range owns a contiguous run of them
+        per_env = starts.sum(dim=0)                                   # [N] trajectories that begin in each env
+        bounds = torch.zeros(num_mini_batches + 1, dtype=torch.int64)
+        bounds[1:] = per_env[:num_mini_batches * mb].view(num_mini_batches, mb).sum(1).cumsum(0).cpu()   # one sync per update
+        bounds = bounds.tolist()
+        start_env_major = starts.t()                                  # [N, T] True where a trajectory begins
+
+        def first_states(slabs):   # [T, L, N, H] -> [n_traj, L, H], trajectory order
+            return [sl.permute(2, 0, 1, 3)[start_env_major] for sl in slabs]
+
+        hid_a_all, hid_c_all = first_states(self.saved_hidden_states_a), first_states(self.saved_hidden_states_c)
+        for _ in range(num_epochs):
+            for i in range(num_mini_batches):
+                lo, hi = i * mb, (i + 1) * mb
+                t0, t1 = bounds[i], bounds[i + 1]
+                hid_a = [h[t0:t1].transpose(1, 0).contiguous() for h in hid_a_all]
+                hid_c = [h[t0:t1].transpose(1, 0).contiguous() for h in hid_c_all]
+                hid_a = hid_a[0] if len(hid_a) == 1 else hid_a        # a GRU has one state tensor
+                hid_c = hid_c[0] if len(hid_c) == 1 else hid_c
+                yield (padded_obs[:, t0:t1], self.actions[:, lo:hi], self.values[:, lo:hi], self.advantages[:, lo:hi],
+                       self.returns[:, lo:hi], self.actions_log_prob[:, lo:hi], self.mu[:, lo:hi], self.sigma[:, lo:hi],
+                       (hid_a, hid_c), masks[:, t0:t1])
+
+
+def split_and_pad_trajectories(tensor, dones, return_starts=False):
+    """RSL/utils/utils.py:78-130.  Cuts every env's rollout at its done flags, stacks the pieces (env-major order) as
+    columns of a zero-padded [T, n_traj, ...] tensor and returns it with the [T, n_traj] validity masks:
+
+        [[a1 a2 a3 a4 | a5 a6],        [[a1 a2 a3 a4], [a5 a6 0 0],
+         [b1 b2 | b3 b4 b5 | b6]]  ->   [b1 b2 0 0], [b3 b4 b5 0], [b6 0 0 0]]   (shown transposed)
+
+    `tensor`: [T, N, ...] tensor or a TensorDict of such.  Built with index arithmetic on the device (no per-trajectory
+    Python split); the one host read is the trajectory count."""
+    T, N = dones.shape[0], dones.shape[1]
+    d = dones.reshape(T, N) != 0
+    starts = torch.ones(T, N, dtype=torch.bool, device=d.device)
+    starts[1:] = d[:-1]                                   # a trajectory begins at t = 0 and after every done
+    flat_starts = starts.t().reshape(-1)                  # env-major
+    traj_id = torch.cumsum(flat_starts.to(torch.int64), 0) - 1
+    n_traj = int(traj_id[-1].item()) + 1
+    step_in_env = torch.arange(T, device=d.device).repeat(N)
+    start_step = step_in_env[flat_starts]                 # [n_traj]
+    pos = step_in_env - start_step[traj_id]               # step index inside its trajectory
+    lengths = torch.bincount(traj_id, minlength=n_traj)
+    masks = lengths.unsqueeze(0) > torch.arange(T, device=d.device).unsqueeze(1)
+
+    def pad(v):
+        out = torch.zeros(T, n_traj, *v.shape[2:], device=v.device, dtype=v.dtype)
+        out[pos, traj_id] = v.transpose(1, 0).flatten(0, 1)
+        return out
+
+    if isinstance(tensor, TensorDict):
+        padded = TensorDict({k: pad(v) for k, v in tensor.items()}, batch_size=[T, n_traj], device=dones.device)
+    else:
+        padded = pad(tensor)
+    return (padded, masks, starts) if return_starts else (padded, masks)
 
 
 def _scratch_doubles(T, N):

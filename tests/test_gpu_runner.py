@@ -204,3 +204,31 @@ def test_asymmetric_critic_minibatches_carry_every_group():
     torch.testing.assert_close(ob["critic"], alg.storage.observations["critic"].flatten(0, 1)[first])
     loss = alg.update(indices=idx)
     assert all(torch.isfinite(torch.tensor(v)) for v in loss.values())
+
+
+@pytest.mark.parametrize("rnn_type,layers", [("lstm", 1), ("gru", 2)])
+def test_runner_learns_with_recurrent_policy(rnn_type, layers, tmp_path, monkeypatch):
+    """`class_name: "ActorCriticRecurrent"` through the runner's own loop -- rollout with carried and
+    reset hidden states, recurrent minibatches, BPTT update, checkpoint round trip (`memory_a.rnn.*` keys)."""
+    import copy
+    from isaaclab_b200.rsl_rl import OnPolicyRunner, RslRlVecEnvWrapper
+    monkeypatch.delenv("WORLD_SIZE", raising=False)
+    cfg = copy.deepcopy(TRAIN_CFG)
+    cfg["policy"].update(class_name="ActorCriticRecurrent", rnn_type=rnn_type, rnn_hidden_dim=64, rnn_num_layers=layers)
+    env = RslRlVecEnvWrapper(_make_env("Isaac-Velocity-Flat-Anymal-C-v0", 128))
+    runner = OnPolicyRunner(env, copy.deepcopy(cfg), log_dir=str(tmp_path), device="cuda")
+    pol = runner.alg.policy
+    assert pol.is_recurrent and f"memory_a.rnn.weight_hh_l{layers - 1}" in pol.state_dict()
+    before = pol.flat_param.clone()
+    runner.learn(3, init_at_random_ep_len=True)
+    assert torch.isfinite(pol.flat_param).all() and not torch.equal(before, pol.flat_param)
+    rnn_slice = pol.memory_a.rnn.weight_hh_l0
+    assert not torch.equal(rnn_slice, torch.load(tmp_path / "model_0.pt", weights_only=False)["model_state_dict"]
+                           ["memory_a.rnn.weight_hh_l0"].to(rnn_slice.device))   # the RNN weights were trained too
+    h = pol.get_hidden_states()[0]
+    h = h[0] if isinstance(h, tuple) else h
+    assert h.shape == (layers, 128, 64) and torch.isfinite(h).all()
+    r2 = OnPolicyRunner(RslRlVecEnvWrapper(_make_env("Isaac-Velocity-Flat-Anymal-C-v0", 128)), copy.deepcopy(cfg), log_dir=None,
+                        device="cuda")
+    r2.load(str(tmp_path / "model_2.pt"))
+    assert torch.equal(r2.alg.policy.flat_param, pol.flat_param)
