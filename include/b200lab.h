@@ -135,6 +135,15 @@ typedef struct B200LabTerm {
   float clip_lo, clip_hi;
   float scale;               /* obs terms; 1.0 when cfg.scale is None */
   int32_t scale_on;
+  /* obs terms, LAB/managers/observation_manager.py:305-329.  history_length > 0: the term occupies dim * history_length
+   * columns, oldest row first (CircularBuffer.buffer flattened), kept in the ring at float offset `hist_offset` of the
+   * env's obs_hist row.  Function modifiers (LAB/utils/modifiers/modifier.py:23-66) run before the noise, in order:
+   * kind 1 scale (x * p), 2 bias (x + p), 3 clip (p, p+1); parameters consecutive in mod_p. */
+  int32_t history_length;
+  int32_t hist_offset;
+  int32_t num_mod;
+  int32_t mod_kind[3];
+  float mod_p[4];
 } B200LabTerm;
 
 enum B200LabActuatorKind {
@@ -142,7 +151,8 @@ enum B200LabActuatorKind {
   B200LAB_ACT_IDEAL_PD = 2,   /* actuator_pd.py:184-198 */
   B200LAB_ACT_DC_MOTOR = 3,   /* actuator_pd.py:264-286 */
   B200LAB_ACT_NET_LSTM = 4,   /* LAB/actuators/actuator_net.py:76-99 */
-  B200LAB_ACT_NET_MLP = 5     /* actuator_net.py:147-189 */
+  B200LAB_ACT_NET_MLP = 5,    /* actuator_net.py:147-189 */
+  B200LAB_ACT_DELAYED_PD = 6  /* actuator_pd.py:289-347: IdealPD behind a per-env command delay (DelayBuffer) */
 };
 
 /* One actuator group (Articulation.actuators[name], LAB/assets/articulation/articulation.py:1432-1469).
@@ -176,6 +186,16 @@ typedef struct B200LabActuatorGroup {
   float* mlp_vel_hist;
   int32_t group_joints;        /* Jg */
   int32_t _pad2;
+  /* DelayedPDActuator (LAB/utils/buffers/delay_buffer.py, circular_buffer.py): per (env, local joint) a ring of
+   * max_delay+1 rows {pos, vel, effort set-point} and its push count since the last reset (the first push after a
+   * reset fills the ring); per env the lag in physics steps, re-drawn at reset as
+   * min_delay + floor(u * (max_delay - min_delay + 1)) from reset-uniform slot `delay_u_slot`. */
+  int32_t min_delay, max_delay;
+  int32_t delay_u_slot;
+  int32_t _pad3;
+  float* delay_ring;           /* [N, Jg, max_delay+1, 3] */
+  int32_t* delay_count;        /* [N, Jg] */
+  int32_t* delay_lag;          /* [N] */
 } B200LabActuatorGroup;
 
 /* ------------------------------------------------------------------------------------------------
@@ -337,6 +357,19 @@ typedef struct B200LabEnvState {
   B200LabTerm obs[B200LAB_MAX_TERMS];
   float* obs_buf;              /* [N, obs_dim] */
   int32_t obs_enable_corruption;
+  /* observation history (ObservationTermCfg.history_length, LAB/utils/buffers/circular_buffer.py): obs_hist [N,
+   * obs_hist_total] holds every history term's ring, row-major [history_length, dim] at the term's hist_offset.
+   * obs_hist_count[0] = appends so far (b200lab_post_step advances it once per step, so the observation computed at
+   * reset time and the one of the first step use consecutive slots).  obs_hist_reset_step[n] = env step at which env n
+   * was last reset (written by post_step): a compute_obs of that same step fills every slot of the env's rings with the
+   * fresh row (the first push after a reset).  The host initialises it to the current step counter, so the first
+   * compute fills every env, and sets it to -1 after a compute_obs issued outside a step (the observation returned by
+   * env.reset()).  All NULL / 0 when no term keeps history. */
+  int32_t obs_hist_total;
+  int32_t _pad_hist;
+  float* obs_hist;
+  int32_t* obs_hist_count;
+  int64_t* obs_hist_reset_step;
   /* --- randomness (SURVEY.md 7 hard part 3) --- */
   /* parity mode: pre-drawn uniforms in [0,1): u_reset [N, n_u_reset], u_step [N, n_u_step], u_obs [N, obs_dim];
    * perf mode (pointers NULL): Philox4x32-10 keyed by (seed, step_counter, env, slot). */

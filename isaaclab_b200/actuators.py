@@ -1,5 +1,5 @@
 """Actuator cfg classes with the reference's names and fields (LAB/actuators/actuator_cfg.py): ImplicitActuatorCfg,
-IdealPDActuatorCfg, DCMotorCfg, ActuatorNetLSTMCfg, ActuatorNetMLPCfg.  The models themselves are fused into
+IdealPDActuatorCfg, DCMotorCfg, DelayedPDActuatorCfg, ActuatorNetLSTMCfg, ActuatorNetMLPCfg.  The models themselves are fused into
 `substep_pre` (csrc/mdp.cu); `network_file` may be a TorchScript path or an in-memory module."""
 from __future__ import annotations
 
@@ -33,6 +33,15 @@ class IdealPDActuatorCfg(ActuatorBaseCfg):
 class DCMotorCfg(IdealPDActuatorCfg):
     saturation_effort: float = None
     kind: str = "dc_motor"
+
+
+@dataclass
+class DelayedPDActuatorCfg(IdealPDActuatorCfg):
+    """IdealPD behind a per-env command delay of min_delay..max_delay physics steps, re-drawn at reset
+    (LAB/actuators/actuator_cfg.py:216-228, actuator_pd.py:289-347)."""
+    min_delay: int = 0
+    max_delay: int = 0
+    kind: str = "delayed_pd"
 
 
 @dataclass

@@ -27,6 +27,7 @@ struct EnvHandle {
   float* derived;      // [N, kDerived] per-env derived state for compute_obs
   bool rays_vertical;  // all ray directions are (0,0,dz), dz != 0, and the sensor is yaw-only
   int vert_batch;      // candidates per round trip of the vertical ray query (B200LAB_VERT_BATCH: 2 default, 3, 4)
+  bool obs_plain;      // no observation term keeps history or carries modifiers
   int obs_impl;        // 0 (default): per-ray kernel; 1: staged height scan (compute_obs_patch_kernel), opt-in via B200LAB_OBS_IMPL
   struct ObsCol* cols; // [obs_dim] per-column program of the observation group (compute_obs_kernel)
   MeshAccel mesh;      // host copy of the ray-caster mesh descriptor (passed by value to compute_obs)
@@ -526,9 +527,30 @@ __device__ __noinline__ void actuator_eval(const Env* __restrict__ e, const floa
                                               float q_t, float qd_t, float ff, float& computed, float& applied) {
   const int N = e->N;
   const B200LabActuatorGroup& g = e->act[e->joint_group[j]];
+  if (g.kind == B200LAB_ACT_DELAYED_PD) {
+    // DelayBuffer.compute on the three set-points (actuator_pd.py:336-344, delay_buffer.py:150-176): push, then read the
+    // row pushed `lag` steps ago (capped at what has been pushed since the reset; the first push fills the ring)
+    const int L = g.max_delay + 1;
+    const int64_t row = (int64_t)n * g.group_joints + e->joint_local[j];
+    float* ring = g.delay_ring + row * L * 3;
+    int cnt = g.delay_count[row];
+    const int slot = cnt % L;
+    if (cnt == 0) {
+      for (int k = 0; k < L; ++k) { ring[k * 3] = q_t; ring[k * 3 + 1] = qd_t; ring[k * 3 + 2] = ff; }
+    } else {
+      ring[slot * 3] = q_t; ring[slot * 3 + 1] = qd_t; ring[slot * 3 + 2] = ff;
+    }
+    const int lag = min(g.delay_lag[n], cnt);
+    const int rd = (slot - lag + L) % L;
+    q_t = ring[rd * 3]; qd_t = ring[rd * 3 + 1]; ff = ring[rd * 3 + 2];
+    cnt += 1;
+    if (cnt >= 2 * L) cnt -= L;   // keeps cnt mod L and cnt >= L >= lag: no overflow however long the episode
+    g.delay_count[row] = cnt;
+  }
   float err_p = q_t - q, err_v = qd_t - qd;
   float elim = g.effort_limit[j];
-  if (g.kind == B200LAB_ACT_IMPLICIT || g.kind == B200LAB_ACT_IDEAL_PD || g.kind == B200LAB_ACT_DC_MOTOR) {
+  if (g.kind == B200LAB_ACT_IMPLICIT || g.kind == B200LAB_ACT_IDEAL_PD || g.kind == B200LAB_ACT_DC_MOTOR ||
+      g.kind == B200LAB_ACT_DELAYED_PD) {
     computed = (g.stiffness[j] * err_p + g.damping[j] * err_v) + ff;  // actuator_pd.py:136 / :190
     if (g.kind == B200LAB_ACT_DC_MOTOR)
       applied = dc_motor_clip(computed, qd, g.saturation_effort, g.velocity_limit[j], elim);
@@ -1399,6 +1421,12 @@ post_step_kernel(const __grid_constant__ Env env_param, Sim sim, int64_t step, c
           ag.mlp_pos_hist[(int64_t)n * per + k] = 0.f;
           ag.mlp_vel_hist[(int64_t)n * per + k] = 0.f;
         }
+      } else if (ag.kind == B200LAB_ACT_DELAYED_PD) {   // DelayedPDActuator.reset (actuator_pd.py:311-334)
+        for (int k = lane; k < ag.group_joints; k += 32) ag.delay_count[(int64_t)n * ag.group_joints + k] = 0;
+        if (lane == 0) {
+          const int span = ag.max_delay - ag.min_delay + 1;
+          ag.delay_lag[n] = ag.min_delay + min((int)(u_reset_at(e, n, ag.delay_u_slot, step) * (float)span), span - 1);
+        }
       }
     }
     // scene.reset: contact sensor (contact_sensor.py:143-162, sensor_base.py:182-195)
@@ -1552,6 +1580,10 @@ post_step_kernel(const __grid_constant__ Env env_param, Sim sim, int64_t step, c
   }
   // -- interval events: push_by_setting_velocity (event_manager.py:204-229, events.py:795-820)
   if (lane == 0) {
+    if (e->obs_hist_reset_step) {   // observation history: reset envs refill their rings in this step's compute; one append per step
+      if (reset) e->obs_hist_reset_step[n] = step;
+      if (n == 0) *e->obs_hist_count = (*e->obs_hist_count + 1) & 0x3fffffff;
+    }
 #pragma unroll
     for (int k = 0; k < B200LAB_MAX_INTERVAL_EVENTS; ++k) {
       if (k >= e->num_interval) break;
@@ -1580,7 +1612,10 @@ post_step_kernel(const __grid_constant__ Env env_param, Sim sim, int64_t step, c
 //   a = {op | src << 8 | noise_kind << 24 | clip_on << 30 | scale_on << 31, noise_lo, noise_span, scale}
 //   b = {clip_lo, clip_hi, p[0], EXTERNAL column}
 //   c = {ray local start xyz, ray direction z}   (height-scan columns)
-struct ObsCol { float4 a, b, c; };
+//   d = {history: H | row << 8 | modifier kinds << 16 (3 x 2 bits), ring offset of (term, element) in the env's obs_hist
+//        row, term width, column of the NEWEST row's element (where the element's noise draw is indexed)}   as bit patterns
+//   m = modifier parameters
+struct ObsCol { float4 a, b, c, d, m; };
 
 
 __global__ void __launch_bounds__(128)
@@ -1669,10 +1704,23 @@ compute_obs_kernel(const __grid_constant__ Env env_param, Sim sim, int64_t step,
   const unsigned gid = n * D + k;
   const float* o = derived + (size_t)n * kDerived;
   const ObsCol* col = cols + k;
-  const float4 ca = __ldg(&col->a), cb = __ldg(&col->b);   // static program: read before the dependency wait
+  const float4 ca = __ldg(&col->a), cb = __ldg(&col->b), cd = __ldg(&col->d);   // static program: read before the dependency wait
   pdl_wait();
   const unsigned w0 = __float_as_uint(ca.x);
   const int op = w0 & 0xffu, li = (w0 >> 8) & 0xffffu, kind = (w0 >> 24) & 0x3fu;
+  // history (observation_manager.py:319-325): column = (row h of H, element); rows oldest first, the newest row is the
+  // one computed now.  Slot of row h in the ring: (appends so far + 1 + h) mod H.
+  const unsigned hw = __float_as_uint(cd.x), H = hw & 0xffu, hrow = (hw >> 8) & 0xffu, modk = hw >> 16;
+  float* ring = nullptr;
+  if (H) {
+    if (e->step_counter_dev) step = *e->step_counter_dev;
+    const unsigned cnt = (unsigned)*e->obs_hist_count;
+    ring = e->obs_hist + (size_t)n * e->obs_hist_total + __float_as_uint(cd.y) + ((cnt + 1u + hrow) % H) * __float_as_uint(cd.z);
+    if (hrow != H - 1 && e->obs_hist_reset_step[n] != step) {   // an older row: already noised / clipped / scaled when it was new
+      e->obs_buf[gid] = *ring;
+      return;
+    }
+  }
   float v = 0.f;
   switch (op) {
     case B200LAB_OBS_BASE_LIN_VEL: v = o[li]; break;
@@ -1721,7 +1769,21 @@ compute_obs_kernel(const __grid_constant__ Env env_param, Sim sim, int64_t step,
       break;
     }
   }
-  e->obs_buf[gid] = obs_finish(e, v, ca, cb, w0, kind, step, n, k, gid);
+  if (modk) {   // function modifiers, before the noise (observation_manager.py:310-312)
+    const float4 cm = __ldg(&col->m);
+    float p0 = cm.x, p1 = cm.y, p2 = cm.z, p3 = cm.w;   // parameters are consumed front to back
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+      const unsigned mk = (modk >> (2 * i)) & 3u;
+      if (mk == 3u) { v = fminf(fmaxf(v, p0), p1); p0 = p2; p1 = p3; }
+      else if (mk != 0u) { v = mk == 1u ? v * p0 : v + p0; p0 = p1; p1 = p2; p2 = p3; }
+    }
+  }
+  // the element's noise draw is indexed by the column of its newest row (one draw per element and step)
+  const unsigned kn = H ? __float_as_uint(cd.w) : k;
+  v = obs_finish(e, v, ca, cb, w0, kind, step, n, kn, n * D + kn);
+  if (H) *ring = v;   // the newest row's slot -- or, right after a reset, this row's slot: the ring is filled with the fresh row
+  e->obs_buf[gid] = v;
 }
 
 // noise -> clip -> scale of one observation element (observation_manager.py:313-318)
@@ -2136,6 +2198,7 @@ static int upload_obs_tables(EnvHandle* h) {
   if (D <= 0) return B200LAB_OK;
   if ((int64_t)s.N * D >= (int64_t)1 << 31) { set_error("N * obs_dim must be < 2^31"); return B200LAB_ERR_ARG; }
   std::vector<ObsCol> cols((size_t)D);
+  h->obs_plain = true;   // no history, no modifiers: the staged kernel (which knows neither) may be used
   auto as_f = [](uint32_t u) { float f; memcpy(&f, &u, 4); return f; };
   int k = 0;
   for (int t = 0; t < s.num_obs; ++t) {
@@ -2143,6 +2206,20 @@ static int upload_obs_tables(EnvHandle* h) {
     bool joint = tm.op == B200LAB_OBS_JOINT_POS_REL || tm.op == B200LAB_OBS_JOINT_VEL_REL ||
                  tm.op == B200LAB_OBS_JOINT_POS || tm.op == B200LAB_OBS_JOINT_VEL;
     if (tm.op < 0 || tm.op > 255 || tm.noise_kind < 0 || tm.noise_kind > 63) { set_error("observation term %d: bad op / noise kind", t); return B200LAB_ERR_ARG; }
+    const int Hn = tm.history_length > 0 ? tm.history_length : 0, rows = Hn > 0 ? Hn : 1;
+    if (Hn > 255 || tm.num_mod < 0 || tm.num_mod > 3) { set_error("observation term %d: history_length > 255 or > 3 modifiers", t); return B200LAB_ERR_ARG; }
+    if (Hn > 0 && (!s.obs_hist || !s.obs_hist_count || !s.obs_hist_reset_step || tm.hist_offset < 0 ||
+                   tm.hist_offset + Hn * tm.dim > s.obs_hist_total)) {
+      set_error("observation term %d: history buffers missing or too small", t); return B200LAB_ERR_ARG;
+    }
+    uint32_t modk = 0;
+    for (int q = 0; q < tm.num_mod; ++q) {
+      if (tm.mod_kind[q] < 1 || tm.mod_kind[q] > 3) { set_error("observation term %d: bad modifier kind", t); return B200LAB_ERR_ARG; }
+      modk |= (uint32_t)tm.mod_kind[q] << (2 * q);
+    }
+    if (Hn > 0 || modk) h->obs_plain = false;
+    const int k_term = k;
+    for (int row = 0; row < rows; ++row) {
     uint64_t m = tm.joint_mask;
     for (int li = 0; li < tm.dim; ++li) {
       if (k >= D) { set_error("observation term dims exceed obs_dim"); return B200LAB_ERR_ARG; }
@@ -2163,7 +2240,11 @@ static int upload_obs_tables(EnvHandle* h) {
         if (li >= s.R || starts.empty()) { set_error("height_scan term wider than the ray pattern"); return B200LAB_ERR_ARG; }
         c.c = make_float4(starts[3 * li], starts[3 * li + 1], starts[3 * li + 2], dirs[3 * li + 2]);
       }
+      c.d = make_float4(as_f((uint32_t)Hn | ((uint32_t)row << 8) | (modk << 16)), as_f((uint32_t)(tm.hist_offset + li)),
+                        as_f((uint32_t)tm.dim), as_f((uint32_t)(k_term + (rows - 1) * tm.dim + li)));
+      c.m = make_float4(tm.mod_p[0], tm.mod_p[1], tm.mod_p[2], tm.mod_p[3]);
       ++k;
+    }
     }
   }
   if (k != D) { set_error("observation term dims (%d) do not add up to obs_dim (%d)", k, D); return B200LAB_ERR_ARG; }
@@ -2531,7 +2612,7 @@ int b200lab_compute_obs_range(void* env, const B200LabSimView* sim, int64_t step
   }
   int64_t total = (int64_t)cnt * s.obs_dim;
   if (total <= 0) return check_launch("compute_obs");
-  if (h->obs_impl == 1 && h->rays_vertical && h->has_mesh && !joined_spec && s.obs_dim <= kPatchMaxCols * kPatchThreads) {
+  if (h->obs_impl == 1 && h->obs_plain && h->rays_vertical && h->has_mesh && !joined_spec && s.obs_dim <= kPatchMaxCols * kPatchThreads) {
     // staged height scan: one CTA per env (a speculated scan, when one was joined, is consumed by the per-ray kernel)
     static bool attr_set = false;
     if (!attr_set) {

@@ -127,6 +127,30 @@ def _fused(term_cfg, name, kinds, min_argc=1):
     return None
 
 
+def _compile_modifiers(name, mods):
+    """`ObservationTermCfg.modifiers` -> [("scale", m) | ("bias", v) | ("clip", lo, hi)] (LAB/utils/modifiers/modifier.py:23-66).
+    Class modifiers (DigitalFilter, Integrator) keep per-env state in Python objects and are not on the fused path."""
+    out = []
+    for m in mods:
+        kind = getattr(m.func, "_b200_modifier", None)
+        if kind is None:
+            mod = (getattr(m.func, "__module__", "") or "")
+            if mod.startswith("isaaclab.utils.modifiers") and getattr(m.func, "__name__", "") in ("scale", "clip", "bias"):
+                kind = m.func.__name__
+        if kind == "scale":
+            out.append(("scale", float(m.params["multiplier"])))
+        elif kind == "bias":
+            out.append(("bias", float(m.params["value"])))
+        elif kind == "clip":
+            lo, hi = m.params["bounds"]
+            out.append(("clip", -math.inf if lo is None else float(lo), math.inf if hi is None else float(hi)))
+        else:
+            raise NotImplementedError(f"observation term '{name}': modifier {m.func} (only scale / clip / bias are fused)")
+    if len(out) > 3 or sum(len(m) - 1 for m in out) > 4:
+        raise NotImplementedError(f"observation term '{name}': at most 3 modifiers with 4 parameters in total")
+    return out
+
+
 def compile_env_cfg(cfg: ManagerBasedRLEnvCfg, num_envs: int | None = None, terrain: "terrain_mod.TerrainGenerator" = None,
                     seed: int = 0) -> dict:
     robot: ArticulationCfg = cfg.scene.robot
@@ -167,6 +191,10 @@ def compile_env_cfg(cfg: ManagerBasedRLEnvCfg, num_envs: int | None = None, terr
              "effort_limit": _per_joint(ac.effort_limit, names, [float("inf")] * len(ids)),
              "velocity_limit": _per_joint(ac.velocity_limit, names, [float("inf")] * len(ids)),
              "saturation_effort": getattr(ac, "saturation_effort", None)}
+        if ac.kind == "delayed_pd":
+            a["min_delay"], a["max_delay"] = int(ac.min_delay), int(ac.max_delay)
+            if not 0 <= a["min_delay"] <= a["max_delay"]:
+                raise ValueError(f"actuator '{name}': need 0 <= min_delay <= max_delay")
         if ac.kind == "lstm":
             nf = ac.network_file
             a["lstm"] = nf if isinstance(nf, dict) else (load_lstm_net(nf) if nf else synthetic_lstm_net(seed=seed))
@@ -299,13 +327,22 @@ def compile_env_cfg(cfg: ManagerBasedRLEnvCfg, num_envs: int | None = None, terr
     for name, t in _terms(grp):
         if isinstance(t, ObservationGroupCfg):
             continue
-        if t.modifiers or t.history_length:
-            raise NotImplementedError(f"observation term '{name}': modifiers / history are not on the fused path")
         f = _fused(t, name, ("obs",))
         if f is not None:
             d = {"name": name, "op": f._b200_op, **f._b200_defaults, **resolve_params(name, t.params)}
         else:   # width inferred by calling the term once when the env is built (observation_manager.py:420-450)
             d = {**external(name, t), "dim": None}
+        # history: the group's setting overrides the terms' (observation_manager.py:411-414)
+        hist = gcfg.history_length if gcfg.history_length is not None else t.history_length
+        flat = gcfg.flatten_history_dim if gcfg.history_length is not None else t.flatten_history_dim
+        if hist:
+            if hist < 0:
+                raise ValueError(f"observation term '{name}': history_length must be >= 0")
+            if not flat:
+                raise NotImplementedError(f"observation term '{name}': flatten_history_dim=False in a concatenated group")
+            d["history_length"] = int(hist)
+        if t.modifiers:
+            d["modifiers"] = _compile_modifiers(name, t.modifiers)
         if t.noise is not None and t.noise.operation not in ("add", "scale", "abs"):
             raise ValueError(f"Unknown operation in noise: {t.noise.operation}")   # noise_model.py:41,69,97
         if isinstance(t.noise, UniformNoiseCfg):

@@ -34,6 +34,7 @@ def _f32span_py(lo, hi):
 
 
 _ACT_KIND = {"implicit": "B200LAB_ACT_IMPLICIT", "ideal_pd": "B200LAB_ACT_IDEAL_PD", "dc_motor": "B200LAB_ACT_DC_MOTOR",
+             "delayed_pd": "B200LAB_ACT_DELAYED_PD",
              "lstm": "B200LAB_ACT_NET_LSTM", "mlp": "B200LAB_ACT_NET_MLP"}
 _MLP_ACT = {"softsign": 0, "elu": 1, "relu": 2, "tanh": 3}
 _KEYS6 = ("x", "y", "z", "roll", "pitch", "yaw")
@@ -179,6 +180,13 @@ class FusedEnv:
                 g.mlp_torque_scale = float(net["torque_scale"])
                 stt["pos_hist"], stt["vel_hist"] = z(N, hist, Jg), z(N, hist, Jg)
                 g.mlp_pos_hist, g.mlp_vel_hist = p(stt["pos_hist"]), p(stt["vel_hist"])
+            elif act["kind"] == "delayed_pd":
+                g.min_delay, g.max_delay = int(act["min_delay"]), int(act["max_delay"])
+                k = sum(1 for a_ in acts[:gi] if a_["kind"] == "delayed_pd")
+                g.delay_u_slot = C["B200LAB_U_RESET_JOINT"] + 2 * J * max(1, len(s.get("events", {}).get("reset_joints", []))) + k
+                stt["ring"] = z(N, Jg, g.max_delay + 1, 3)
+                stt["count"], stt["lags"] = z(N, Jg, dtype=torch.int32), z(N, dtype=torch.int32)
+                g.delay_ring, g.delay_count, g.delay_lag = p(stt["ring"]), p(stt["count"]), p(stt["lags"])
             self.act_state.append(stt)
         self._st = st
         self._finish_init(seed)
@@ -417,11 +425,24 @@ class FusedEnv:
         st.obs_enable_corruption = 1 if o.get("enable_corruption", True) else 0
         D = 0
         from . import term_dims
+        hist_total = 0
+        _MOD = {"scale": 1, "bias": 2, "clip": 3}
         for i, t in enumerate(o["terms"]):
             dst = st.obs[i]
             self._term(dst, "obs", t)
-            dst.dim = term_dims.term_dim(s, t)
-            D += dst.dim
+            dst.dim = term_dims.term_raw_dim(s, t)
+            D += term_dims.term_dim(s, t)
+            H = int(t.get("history_length", 0) or 0)
+            if H:   # ring [H, dim] inside the env's obs_hist row (observation_manager.py:422-433)
+                dst.history_length, dst.hist_offset = H, hist_total
+                hist_total += H * dst.dim
+            q = 0
+            for k, m in enumerate(t.get("modifiers") or ()):
+                dst.mod_kind[k] = _MOD[m[0]]
+                for v in m[1:]:
+                    dst.mod_p[q] = float(v)
+                    q += 1
+                dst.num_mod = k + 1
             nz = t.get("noise")
             dst.noise_kind = C["B200LAB_NOISE_NONE"]
             if nz is not None:
@@ -437,13 +458,23 @@ class FusedEnv:
                 dst.clip_lo, dst.clip_hi = float(t["clip"][0]), float(t["clip"][1])
             dst.scale_on = 1 if t.get("scale") is not None else 0
             dst.scale = float(t["scale"]) if dst.scale_on else 1.0
+        self.obs_hist = None
+        self._hist_started = False
+        if hist_total:
+            self.obs_hist = z(N, hist_total)
+            self.obs_hist_count = z(1, dtype=torch.int32)
+            self.obs_hist_reset_step = z(N, dtype=torch.int64)   # = the first step counter: the first compute fills every ring
+            st.obs_hist_total = hist_total
+            st.obs_hist, st.obs_hist_count = p(self.obs_hist), p(self.obs_hist_count)
+            st.obs_hist_reset_step = p(self.obs_hist_reset_step)
         st.obs_dim = D
         self.obs_dim = D
         assert D == self.obs_buf.shape[1]
         st.obs_buf = p(self.obs_buf)
         # --- randomness / logs
         st.seed = int(seed)
-        self.n_u_reset = C["B200LAB_U_RESET_JOINT"] + 2 * J * max(1, len(rj))
+        self.n_u_reset = (C["B200LAB_U_RESET_JOINT"] + 2 * J * max(1, len(rj))
+                          + sum(1 for a_ in s["actuators"] if a_["kind"] == "delayed_pd"))
         self.n_u_step = C["B200LAB_U_STEP_INTERVAL"] + 7 * len(pushes)
         st.n_u_reset, st.n_u_step = self.n_u_reset, self.n_u_step
         self.log_accum = z(C["B200LAB_LOG_SLOTS"], dtype=torch.float64)
@@ -569,8 +600,21 @@ class FusedEnv:
         _lib.check(self.L.b200lab_step_tail(self.handle, sim.ref, self.step_counter, _lib.current_stream()))
         return self.obs_buf
 
-    def compute_obs(self, sim: SimView):
+    def compute_obs(self, sim: SimView, in_step: bool = False):
+        """ObservationManager.compute.  Outside a step (the observation `env.reset()` returns) the history rings of every
+        env are filled by the first call, and no env is re-filled by the next step's compute unless that step resets it
+        (b200lab.h: obs_hist_reset_step)."""
+        standalone = self.obs_hist is not None and not in_step
+        if standalone and not self._hist_started:
+            t = getattr(self, "step_counter_t", None)
+            if t is not None:
+                self.obs_hist_reset_step.copy_(t.expand(self.N))
+            else:
+                self.obs_hist_reset_step.fill_(self.step_counter)
         _lib.check(self.L.b200lab_compute_obs(self.handle, sim.ref, self.step_counter, _lib.current_stream()))
+        if standalone:
+            self.obs_hist_reset_step.fill_(-1)
+        self._hist_started = True
         return self.obs_buf
 
     def step_tail_ranges(self, sim: SimView, ranges, after_range):
@@ -629,6 +673,7 @@ class FusedEnv:
         else:
             self.post_reset_write(prev)
             self.log_fold()
-            self.compute_obs(prev)
+            self.compute_obs(prev, in_step=True)
+        self._hist_started = True
         self.step_counter += 1
         return self.obs_buf, self.reward_buf, self.terminated, self.truncated

@@ -3,6 +3,12 @@ LAB/managers/observation_manager.py:420-450; here it follows from the term ident
 
 
 def term_dim(spec, t):
+    """Width in the concatenated group: the term's own width times its flattened history length
+    (observation_manager.py:422-433)."""
+    return term_raw_dim(spec, t) * max(1, int(t.get("history_length", 0) or 0))
+
+
+def term_raw_dim(spec, t):
     op = t["op"]
     if op in ("base_lin_vel", "base_ang_vel", "projected_gravity", "generated_commands"):
         return 3

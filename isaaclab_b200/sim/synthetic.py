@@ -60,6 +60,12 @@ def initial_env_state(spec: dict, seed: int) -> dict:
             "interval_global_time_left": 0.03}   # is_global_time terms: one timer, about to fire
 
 
+def initial_delay_lags(act: dict, init: dict) -> torch.Tensor:
+    """Command delay (physics steps) each env of a DelayedPD group starts with: spread over [min_delay, max_delay]."""
+    span = act["max_delay"] - act["min_delay"] + 1
+    return (init["episode_length_buf"] % span + act["min_delay"]).to(torch.int64)
+
+
 def init_fused_state(env, init):
     """Loads `initial_env_state` into a FusedEnv (episode counters, command / interval timers)."""
     env.episode_length_buf.copy_(init["episode_length_buf"])
@@ -69,6 +75,9 @@ def init_fused_state(env, init):
         t.copy_(init["interval_time_left"])
     for gt in getattr(env, "interval_global_time", {}).values():   # is_global_time terms: one timer, both parity slots
         gt.fill_(float(init.get("interval_global_time_left", 0.03)))
+    for act, st in zip(env.spec["actuators"], env.act_state):
+        if act["kind"] == "delayed_pd":
+            st["lags"].copy_(initial_delay_lags(act, init))
 
 
 class SyntheticSim:

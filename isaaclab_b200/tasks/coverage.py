@@ -6,10 +6,11 @@ LAB/envs/mdp/rewards.py:245-283, terminations.py:60-88, observations.py:33,104,1
 Base: the flat Anymal-C velocity task.  Changes: IdealPD + stand-alone DCMotor actuator groups instead of the LSTM net;
 action clip; rewards contact_forces / action_l2 / joint_vel_l2 / is_alive / is_terminated; terminations
 root_height_below_minimum / bad_orientation; observations base_pos_z / joint_pos / joint_vel with scale and clip;
-reset events gated by min_step_count_between_reset and an interval push on one global timer (is_global_time)."""
+reset events gated by min_step_count_between_reset and an interval push on one global timer (is_global_time); a DelayedPD
+actuator group; observation history (with and without noise) and the scale / clip / bias modifiers."""
 from __future__ import annotations
 
-from ..actuators import DCMotorCfg, IdealPDActuatorCfg
+from ..actuators import DCMotorCfg, DelayedPDActuatorCfg, IdealPDActuatorCfg
 from ..envs import mdp
 from ..managers import ObservationTermCfg as ObsTerm
 from ..managers import RewardTermCfg as RewTerm
@@ -20,7 +21,9 @@ from .velocity import AnymalCFlatEnvCfg
 
 # shared with the reference-side twin in tests/golden/gen_mdp.py
 ACTUATORS = {
-    "hips": dict(kind="ideal_pd", joint_names_expr=[".*HAA"], stiffness=40.0, damping=2.0, effort_limit=30.0, velocity_limit=7.5),
+    "hips": dict(kind="ideal_pd", joint_names_expr=[".*F_HAA"], stiffness=40.0, damping=2.0, effort_limit=30.0, velocity_limit=7.5),
+    "hips_hind": dict(kind="delayed_pd", joint_names_expr=[".*H_HAA"], stiffness=40.0, damping=2.0, effort_limit=30.0,
+                      velocity_limit=7.5, min_delay=1, max_delay=3),
     "legs": dict(kind="dc_motor", joint_names_expr=[".*HFE", ".*KFE"], stiffness={".*HFE": 60.0, ".*KFE": 50.0}, damping=3.0,
                  effort_limit=80.0, velocity_limit=7.5, saturation_effort=120.0),
 }
@@ -36,10 +39,11 @@ TERMINATIONS = {
     "root_height_below_minimum": dict(params={"minimum_height": 0.45}),
     "bad_orientation": dict(params={"limit_angle": 0.2}),
 }
-OBSERVATIONS = {   # name: (func name, noise range | None, clip | None, scale | None)
-    "base_height": ("base_pos_z", None, None, 2.0),
-    "joint_pos_abs": ("joint_pos", (-0.01, 0.01), (-1.2, 1.2), None),
-    "joint_vel_abs": ("joint_vel", (-0.5, 0.5), (-4.0, 4.0), 0.25),
+OBSERVATIONS = {   # name: (func name, noise range | None, clip | None, scale | None, history_length, modifiers)
+    "base_height": ("base_pos_z", None, None, 2.0, 3, None),
+    "joint_pos_abs": ("joint_pos", (-0.01, 0.01), (-1.2, 1.2), None, 0,
+                      [("scale", {"multiplier": 0.5}), ("clip", {"bounds": (-0.4, None)}), ("bias", {"value": 0.1})]),
+    "joint_vel_abs": ("joint_vel", (-0.5, 0.5), (-4.0, 4.0), 0.25, 2, [("clip", {"bounds": (-3.0, 3.0)})]),
 }
 
 
@@ -60,7 +64,7 @@ def OpcodeCoverageEnvCfg():
     acts = {}
     for name, a in ACTUATORS.items():
         a = dict(a)
-        cls = IdealPDActuatorCfg if a.pop("kind") == "ideal_pd" else DCMotorCfg
+        cls = {"ideal_pd": IdealPDActuatorCfg, "dc_motor": DCMotorCfg, "delayed_pd": DelayedPDActuatorCfg}[a.pop("kind")]
         acts[name] = cls(**a)
     cfg.scene.robot.actuators = acts
     cfg.actions.joint_pos.clip = dict(ACTION_CLIP)
@@ -75,7 +79,10 @@ def OpcodeCoverageEnvCfg():
         setattr(cfg.rewards, "cov_" + name, RewTerm(func=getattr(mdp, name), weight=r["weight"], params=params))
     for name, t in TERMINATIONS.items():
         setattr(cfg.terminations, "cov_" + name, DoneTerm(func=getattr(mdp, name), params=dict(t["params"])))
-    for name, (fn, nz, clip, scale) in OBSERVATIONS.items():
+    from ..utils import modifiers
+    for name, (fn, nz, clip, scale, hist, mods) in OBSERVATIONS.items():
+        mods = [modifiers.ModifierCfg(func=getattr(modifiers, m), params=dict(pr)) for m, pr in mods] if mods else None
         setattr(cfg.observations.policy, name,
-                ObsTerm(func=getattr(mdp, fn), noise=Unoise(n_min=nz[0], n_max=nz[1]) if nz else None, clip=clip, scale=scale))
+                ObsTerm(func=getattr(mdp, fn), noise=Unoise(n_min=nz[0], n_max=nz[1]) if nz else None, clip=clip, scale=scale,
+                        history_length=hist, modifiers=mods))
     return cfg

@@ -28,8 +28,13 @@ def _t(x, dtype=F32):
     return x.clone().to(dtype) if isinstance(x, torch.Tensor) else torch.tensor(x, dtype=dtype)
 
 
-def n_u_reset(spec):
+def u_reset_delay(spec):
+    """First of the per-group time-lag slots of the DelayedPD actuator groups (one draw per group and reset)."""
     return U_RESET_JOINT + 2 * spec["J"] * max(1, len(spec.get("events", {}).get("reset_joints", [])))
+
+
+def n_u_reset(spec):
+    return u_reset_delay(spec) + sum(1 for a in spec["actuators"] if a["kind"] == "delayed_pd")
 
 
 def n_u_step(spec):
@@ -41,6 +46,12 @@ def obs_dim(spec):
 
 
 def term_dim(spec, t):
+    """Width of the term in the concatenated group: its own width times the flattened history length
+    (observation_manager.py:422-433)."""
+    return term_raw_dim(spec, t) * max(1, int(t.get("history_length", 0) or 0))
+
+
+def term_raw_dim(spec, t):
     op = t["op"]
     if op in ("base_lin_vel", "base_ang_vel", "projected_gravity", "generated_commands"):
         return 3
@@ -79,6 +90,53 @@ def apply_noise(x, u, nz):
     return torch.zeros_like(x) + lo
 
 
+class Ring:
+    """Batched ring buffer with the semantics of LAB/utils/buffers/circular_buffer.py:13-160: one write pointer for all
+    envs; the first push after a reset fills every slot of that env with the pushed row."""
+
+    def __init__(self, length, N):
+        self.L, self.N = int(length), N
+        self.buf, self.ptr = None, -1
+        self.pushes = torch.zeros(N, dtype=torch.int64)
+
+    def reset(self, ids):
+        self.pushes[ids] = 0
+        if self.buf is not None:
+            self.buf[:, ids] = 0.0
+
+    def append(self, x):
+        if self.buf is None:
+            self.buf = torch.zeros(self.L, *x.shape, dtype=x.dtype)
+        self.ptr = (self.ptr + 1) % self.L
+        self.buf[self.ptr] = x
+        fresh = self.pushes == 0
+        self.buf[:, fresh] = x[fresh]
+        self.pushes += 1
+
+    def lagged(self, lags):
+        """Row pushed `lags` appends ago, per env (capped at what has been pushed): circular_buffer.py:140-160."""
+        k = torch.minimum(lags.to(torch.int64), self.pushes - 1)
+        return self.buf[torch.remainder(self.ptr - k, self.L), torch.arange(self.N)]
+
+    def oldest_first(self):
+        """[N, L, ...] with the newest row last (circular_buffer.py:74-83)."""
+        return torch.roll(self.buf, shifts=self.L - self.ptr - 1, dims=0).transpose(0, 1)
+
+
+def apply_modifiers(x, mods):
+    """Function modifiers of an observation term, in order (LAB/utils/modifiers/modifier.py:23-66)."""
+    for m in mods or ():
+        if m[0] == "scale":
+            x = x * m[1]
+        elif m[0] == "bias":
+            x = x + m[1]
+        elif m[0] == "clip":
+            x = x.clip(min=m[1], max=m[2])
+        else:
+            raise ValueError(m[0])
+    return x
+
+
 class OracleEnv:
     def __init__(self, spec):
         self.spec = s = spec
@@ -108,7 +166,13 @@ class OracleEnv:
             elif a["kind"] == "mlp":
                 hist = max(a["mlp"]["input_idx"]) + 1
                 st["pos_hist"], st["vel_hist"] = z(N, hist, Jg), z(N, hist, Jg)
+            elif a["kind"] == "delayed_pd":   # DelayBuffer x3 with shared lags (actuator_pd.py:303-330, delay_buffer.py)
+                st["ring"] = Ring(a["max_delay"] + 1, N)
+                st["lags"] = torch.zeros(N, dtype=torch.int64)
             self.act_state.append(st)
+        # observation history (observation_manager.py:384-433)
+        self.obs_hist = {i: Ring(t["history_length"], N) for i, t in enumerate(s["observations"]["terms"])
+                         if t.get("history_length")}
         # contact sensor (LAB/sensors/contact_sensor/contact_sensor.py)
         if s.get("contact"):
             H = s["contact"]["history_length"]
@@ -208,7 +272,11 @@ class OracleEnv:
             q_t, qd_t, ff = self.joint_pos_target[:, j], self.joint_vel_target[:, j], self.joint_effort_target[:, j]
             elim = _t(act["effort_limit"]).expand(len(j))
             kind = act["kind"]
-            if kind in ("implicit", "ideal_pd", "dc_motor"):
+            if kind == "delayed_pd":   # the three set-points go through the delay line, then IdealPD (actuator_pd.py:336-347)
+                st["ring"].append(torch.stack([q_t, qd_t, ff], dim=-1))
+                d3 = st["ring"].lagged(st["lags"])
+                q_t, qd_t, ff = d3[..., 0], d3[..., 1], d3[..., 2]
+            if kind in ("implicit", "ideal_pd", "dc_motor", "delayed_pd"):
                 err_p, err_v = q_t - q, qd_t - qd
                 computed = _t(act["stiffness"]) * err_p + _t(act["damping"]) * err_v + ff
             elif kind == "lstm":
@@ -217,7 +285,7 @@ class OracleEnv:
                 computed = self._mlp(act["mlp"], st, q_t - q, qd)
             else:
                 raise ValueError(kind)
-            if kind in ("implicit", "ideal_pd"):
+            if kind in ("implicit", "ideal_pd", "delayed_pd"):
                 applied = torch.clip(computed, min=-elim, max=elim)  # actuator_base.py:309-318
             else:  # DCMotor._clip_effort (actuator_pd.py:276-286)
                 sat = float(act["saturation_effort"])
@@ -530,6 +598,14 @@ class OracleEnv:
             elif act["kind"] == "mlp":
                 st["pos_hist"][ids] = 0.0
                 st["vel_hist"][ids] = 0.0
+            elif act["kind"] == "delayed_pd":   # new lag = randint(min_delay, max_delay + 1), buffers cleared (actuator_pd.py:311-334)
+                k = [a_ for a_ in s["actuators"] if a_["kind"] == "delayed_pd"].index(act)
+                span = act["max_delay"] - act["min_delay"] + 1
+                lag = act["min_delay"] + torch.clamp((ur[:, u_reset_delay(s) + k] * span).to(torch.int64), max=span - 1)
+                st["lags"][ids] = lag
+                st["ring"].reset(ids)
+        for ring in self.obs_hist.values():   # ObservationManager.reset (observation_manager.py:226-230)
+            ring.reset(ids)
         # scene.reset: sensors (sensor_base.py:182-195, contact_sensor.py:143-162, ray_caster.py:107-114)
         if s.get("contact"):
             self.cs_ts[ids], self.cs_ts_last[ids], self.cs_outdated[ids] = 0.0, 0.0, True
@@ -686,19 +762,24 @@ class OracleEnv:
         o = self.spec["observations"]
         d = self.derived(sim)
         outs, col = [], 0
-        for t in o["terms"]:
+        for i, t in enumerate(o["terms"]):
             x = self.eval_obs(t, sim, d).clone()
             w = x.shape[1]
+            H = max(1, int(t.get("history_length", 0) or 0))
+            x = apply_modifiers(x, t.get("modifiers"))   # observation_manager.py:310-312: before the noise
             nz = t.get("noise")
             if nz is not None and o.get("enable_corruption", True):
-                u = u_obs[:, col:col + w]
+                u = u_obs[:, col + (H - 1) * w:col + H * w]   # a history term's draw sits at the columns of its newest row
                 x = apply_noise(x, u, nz)
             if t.get("clip") is not None:
                 x = x.clip_(min=t["clip"][0], max=t["clip"][1])
             if t.get("scale") is not None:
                 x = x.mul_(t["scale"])
+            if i in self.obs_hist:   # observation_manager.py:319-325: append, then the whole window, oldest first, flattened
+                self.obs_hist[i].append(x)
+                x = self.obs_hist[i].oldest_first().reshape(self.N, -1)
             outs.append(x)
-            col += w
+            col += H * w
         self.obs_buf = torch.cat(outs, dim=-1)
         return self.obs_buf
 

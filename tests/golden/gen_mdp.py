@@ -330,12 +330,25 @@ class DrawLog:
             log._log((r.to(torch.float32) + 0.5) / high, extra=("randint", high))
             return r
 
+        o_randint = torch.randint
+        self._orig["randint"] = o_randint
+
+        def randint(*a, **kw):   # torch.randint(low=, high=, size=, ...) as DelayedPDActuator.reset calls it
+            if "generator" in kw or not log.enabled or a:
+                return o_randint(*a, **kw)
+            low, high, size = kw.get("low", 0), kw["high"], kw["size"]
+            r = o_randint(low, high, size, generator=log.gen, dtype=kw.get("dtype", torch.int64))
+            log._log((r.to(torch.float32) - low + 0.5) / (high - low), extra=("randint", low, high))
+            return r
+
         torch.rand, torch.rand_like, torch.Tensor.uniform_, torch.randint_like = rand, rand_like, uniform_, randint_like
+        torch.randint = randint
 
     def uninstall(self):
         o = self._orig
         torch.rand, torch.rand_like, torch.Tensor.uniform_, torch.randint_like = (o["rand"], o["rand_like"], o["uniform_"],
                                                                                  o["randint_like"])
+        torch.randint = o["randint"]
 
     def take(self):
         d, self.draws = self.draws, []
@@ -353,10 +366,10 @@ def layout_uniforms(draws, spec, N, filler):
     noisy_cols = []   # (start, width) of obs terms that carry noise, in term order
     c = 0
     for t in spec["observations"]["terms"]:
-        w = omdp.term_dim(spec, t)
+        w, wt = omdp.term_raw_dim(spec, t), omdp.term_dim(spec, t)
         if t.get("noise") is not None and spec["observations"].get("enable_corruption", True):
-            noisy_cols.append((c, w))
-        c += w
+            noisy_cols.append((c + wt - w, w))   # a history term's draw sits at the columns of its newest row
+        c += wt
     unused = []
     for d in draws:
         f, ids, chain, u = d["func"], d["env_ids"], d["chain"], d["u"]
@@ -367,7 +380,13 @@ def layout_uniforms(draws, spec, N, filler):
             ids = torch.arange(N)
         if f == "update_env_origins":
             u_r[ids, omdp.U_RESET_CURRICULUM] = u
-        elif f == "reset":   # RayCaster.reset (the only sensor/asset reset that draws)
+        elif f == "reset" and d["extra"] is not None and d["extra"][0] == "randint":
+            # DelayedPDActuator.reset (actuator_pd.py:320-326): one lag per env, groups in articulation order
+            n_delayed = sum(1 for a_ in spec["actuators"] if a_["kind"] == "delayed_pd")
+            kk = seen.get("delay_total", 0)
+            seen["delay_total"] = kk + 1
+            u_r[ids, omdp.u_reset_delay(spec) + kk % n_delayed] = u
+        elif f == "reset":   # RayCaster.reset (the only sensor reset that draws)
             u_r[ids, omdp.U_RESET_DRIFT:omdp.U_RESET_DRIFT + 3] = u
         elif f == "reset_root_state_uniform":
             base = omdp.U_RESET_POSE if k == 0 else omdp.U_RESET_VEL
@@ -595,7 +614,8 @@ def coverage_reference_cfg():
     the reference's OWN IdealPDActuatorCfg / DCMotorCfg classes and mdp functions plugged in, from the same data tables."""
     import importlib
     from isaaclab_b200.tasks import coverage as cov
-    from isaaclab.actuators import DCMotorCfg, IdealPDActuatorCfg
+    from isaaclab.actuators import DCMotorCfg, DelayedPDActuatorCfg, IdealPDActuatorCfg
+    from isaaclab.utils import modifiers as rmod
     import isaaclab.envs.mdp as rmdp
     from isaaclab.managers import ObservationTermCfg, RewardTermCfg, SceneEntityCfg, TerminationTermCfg
     from isaaclab.utils.noise import AdditiveUniformNoiseCfg as Unoise
@@ -604,7 +624,7 @@ def coverage_reference_cfg():
     acts = {}
     for name, a in cov.ACTUATORS.items():
         a = dict(a)
-        cls = IdealPDActuatorCfg if a.pop("kind") == "ideal_pd" else DCMotorCfg
+        cls = {"ideal_pd": IdealPDActuatorCfg, "dc_motor": DCMotorCfg, "delayed_pd": DelayedPDActuatorCfg}[a.pop("kind")]
         acts[name] = cls(**a)
     cfg.scene.robot = cfg.scene.robot.replace(actuators=acts)
     cfg.actions.joint_pos.clip = dict(cov.ACTION_CLIP)
@@ -619,10 +639,11 @@ def coverage_reference_cfg():
         setattr(cfg.rewards, "cov_" + name, RewardTermCfg(func=getattr(rmdp, name), weight=r["weight"], params=params))
     for name, t in cov.TERMINATIONS.items():
         setattr(cfg.terminations, "cov_" + name, TerminationTermCfg(func=getattr(rmdp, name), params=dict(t["params"])))
-    for name, (fn, nz, clip, scale) in cov.OBSERVATIONS.items():
+    for name, (fn, nz, clip, scale, hist, mods) in cov.OBSERVATIONS.items():
+        mods = [rmod.ModifierCfg(func=getattr(rmod, m), params=dict(pr)) for m, pr in mods] if mods else None
         setattr(cfg.observations.policy, name,
                 ObservationTermCfg(func=getattr(rmdp, fn), noise=Unoise(n_min=nz[0], n_max=nz[1]) if nz else None, clip=clip,
-                                   scale=scale))
+                                   scale=scale, history_length=hist, modifiers=mods))
     from isaaclab.managers import EventTermCfg
     for name, m in cov.EVENT_GATES.items():
         getattr(cfg.events, name).min_step_count_between_reset = m
@@ -684,6 +705,12 @@ def build_reference_env(task, spec, slabs, init, tmpdir, wrap=False):
     if spec.get("command"):
         term = env.command_manager.get_term(spec["command"]["name"])
         term.time_left[:] = init["cmd_time_left"]
+    from isaaclab_b200.sim.synthetic import initial_delay_lags
+    for (name, actuator), aspec in zip(env.scene["robot"].actuators.items(), spec["actuators"]):
+        if aspec["kind"] == "delayed_pd":
+            lags = initial_delay_lags(aspec, init).to(torch.int)
+            for buf in (actuator.positions_delay_buffer, actuator.velocities_delay_buffer, actuator.efforts_delay_buffer):
+                buf.set_time_lag(lags)
     for tl in env.event_manager._interval_term_time_left:
         tl[:] = init["interval_time_left"] if tl.numel() > 1 else init.get("interval_global_time_left", 0.03)   # [1]: is_global_time
     return env, replay

@@ -49,6 +49,10 @@ def init_oracle_state(env, init):
         t[:] = init["interval_time_left"]
     for gt in env.interval_global_time.values():
         gt[:] = init.get("interval_global_time_left", 0.03)
+    from isaaclab_b200.sim.synthetic import initial_delay_lags
+    for act, st in zip(env.spec["actuators"], env.act_state):
+        if act["kind"] == "delayed_pd":
+            st["lags"][:] = initial_delay_lags(act, init)
 
 
 def init_fused_state(env, init):
@@ -181,6 +185,17 @@ def run_step_parity(spec, steps, fused=True, speculative=False, oracle_grid=None
         n_resets += int(orc.reset_buf.sum())
         prev_cpu, prev_gpu = views_cpu[-1], sim.views(k + 1)[-1]
     for st_f, st_o in zip(fus.act_state, orc.act_state):
+        if "ring" in st_f:   # DelayedPD: same lags, and the same set-points at every lag (the ring layouts differ:
+            # the CUDA path keeps one write pointer per joint, the reference one per buffer)
+            assert torch.equal(st_f["lags"].cpu().long(), st_o["lags"]), f"{tag} delay lags"
+            ring_f, cnt = st_f["ring"].cpu(), st_f["count"].cpu().long()          # [N, Jg, L, 3], [N, Jg]
+            L = ring_f.shape[2]
+            for lag in range(L):
+                k = torch.minimum(torch.full_like(cnt, lag), cnt - 1).clamp(min=0)
+                got = torch.gather(ring_f, 2, ((cnt - 1 - k) % L)[..., None, None].expand(-1, -1, 1, 3)).squeeze(2)
+                want = st_o["ring"].lagged(torch.full((fus.N,), lag))
+                close(got, want, f"{tag} delayed set-points at lag {lag}", rtol=1e-6, atol=1e-7)
+            continue
         for key in st_f:
             close(st_f[key], st_o[key], f"{tag} actuator state {key}", rtol=1e-4, atol=1e-5)
     return fus, orc, n_resets, n_resample

@@ -223,3 +223,42 @@ def test_live_simulator_backend_matches_replay(task):
     for k, (a, b) in enumerate(zip(*outs)):
         for x, y, name in zip(a, b, ("obs", "reward", "terminated", "time_outs")):
             assert torch.equal(x, y), f"{task} step {k}: {name} differs between the live backend and the replay"
+
+
+def test_observation_history_through_the_public_env():
+    """LAB test_observation_manager.py:357-508 in spirit, through `ManagerBasedRLEnv`: with a group-level history_length the
+    observation returned by reset() holds the first row repeated (circular_buffer.py:118-123); every step shifts the window
+    by one row for envs that kept running and refills it for the envs the step reset (observation_manager.py:226-230) --
+    including the height-scan columns."""
+    from isaaclab_b200.tasks import TASKS
+    cfg = TASKS[TASK]()
+    cfg.observations.policy._group.history_length = 3
+    cfg.observations.policy._group.enable_corruption = False
+    env = _env(cfg)
+    H, dims = 3, [d[0] // 3 for d in env.observation_manager.group_obs_term_dim["policy"]]
+    assert sum(dims) == 235 and env.observation_manager.group_obs_dim["policy"] == (705,)
+
+    def rows(obs):   # [N, 705] -> per term [N, H, d]
+        out, c = [], 0
+        for d in dims:
+            out.append(obs[:, c:c + H * d].reshape(N, H, d).clone())
+            c += H * d
+        return out
+
+    obs, _ = env.reset()
+    prev = rows(obs["policy"])
+    for r in prev:
+        assert torch.equal(r[:, 0], r[:, 2]) and torch.equal(r[:, 1], r[:, 2])
+    g = torch.Generator(device="cuda").manual_seed(0)
+    n_reset = 0
+    for _ in range(5):
+        obs, _, term, trunc, _ = env.step(torch.randn(N, 12, device="cuda", generator=g))
+        cur = rows(obs["policy"])
+        done = term | trunc
+        n_reset += int(done.sum())
+        for p_, c_ in zip(prev, cur):
+            assert torch.equal(c_[~done][:, :2], p_[~done][:, 1:])          # window moved by one row
+            assert torch.equal(c_[done][:, 0], c_[done][:, 2]) and torch.equal(c_[done][:, 1], c_[done][:, 2])   # refilled
+        assert not torch.equal(cur[3][~done][:, 2], cur[3][~done][:, 1])   # and the newest row is new (joint_pos moves)
+        prev = cur
+    assert n_reset > 0

@@ -51,9 +51,9 @@ def test_unknown_classes_fail_loudly():
     r = object.__new__(OnPolicyRunner)
     r.cfg = {"obs_groups": {"policy": ["policy"], "critic": ["policy"]}}
     r.device, r.multi_gpu_cfg = "cpu", None
-    r.policy_cfg = {"class_name": "ActorCriticRecurrent"}
+    r.policy_cfg = {"class_name": "StudentTeacher"}
     r.alg_cfg = {"class_name": "PPO"}
-    with pytest.raises(NotImplementedError, match="ActorCriticRecurrent"):
+    with pytest.raises(NotImplementedError, match="StudentTeacher"):
         r._construct_algorithm(_obs(policy=5))
     r.alg_cfg = {"class_name": "PPO", "rnd_cfg": {"weight": 1.0}}
     with pytest.raises(NotImplementedError, match="RND"):

@@ -130,3 +130,49 @@ def test_reference_mdp_functions_compile_to_the_same_opcodes():
         assert all(t["op"] != "external" for t in got[key])
     assert [t["op"] for t in got["observations"]["terms"]] == [t["op"] for t in want["observations"]["terms"]]
     assert mdp._REGISTRY  # the registry the recognition goes through
+
+
+def test_history_and_modifiers_compile_like_the_reference():
+    """observation_manager.py:411-433: the group's history_length overrides the terms'; a term with history occupies
+    dim x history_length columns; function modifiers compile in order; class modifiers are refused with a reason."""
+    from isaaclab_b200.envs.compile import compile_env_cfg
+    from isaaclab_b200.envs.term_dims import term_dim, term_raw_dim
+    from isaaclab_b200.tasks import TASKS
+    from isaaclab_b200.utils import modifiers
+    cfg = TASKS["Isaac-Velocity-Flat-Anymal-C-v0"]()
+    cfg.observations.policy.joint_pos.history_length = 4
+    cfg.observations.policy.joint_vel.modifiers = [modifiers.ModifierCfg(func=modifiers.scale, params={"multiplier": 2.0}),
+                                                   modifiers.ModifierCfg(func=modifiers.clip, params={"bounds": (None, 1.5)})]
+    spec = compile_env_cfg(cfg, num_envs=4)
+    terms = {t["name"]: t for t in spec["observations"]["terms"]}
+    assert term_raw_dim(spec, terms["joint_pos"]) == 12 and term_dim(spec, terms["joint_pos"]) == 48
+    assert terms["joint_vel"]["modifiers"] == [("scale", 2.0), ("clip", -float("inf"), 1.5)]
+    assert sum(term_dim(spec, t) for t in spec["observations"]["terms"]) == 48 + 36
+    cfg.observations.policy._group.history_length = 2       # group setting wins over every term's
+    spec = compile_env_cfg(cfg, num_envs=4)
+    assert all(t["history_length"] == 2 for t in spec["observations"]["terms"])
+    assert sum(term_dim(spec, t) for t in spec["observations"]["terms"]) == 96
+    cfg.observations.policy._group.flatten_history_dim = False
+    with pytest.raises(NotImplementedError, match="flatten_history_dim"):
+        compile_env_cfg(cfg, num_envs=4)
+    cfg.observations.policy._group.history_length = None
+
+    class Integrator:
+        pass
+    cfg.observations.policy.joint_vel.modifiers = [modifiers.ModifierCfg(func=Integrator, params={"dt": 0.1})]
+    with pytest.raises(NotImplementedError, match="only scale / clip / bias"):
+        compile_env_cfg(cfg, num_envs=4)
+
+
+def test_delayed_pd_cfg_compiles_and_checks_its_range():
+    from isaaclab_b200.actuators import DelayedPDActuatorCfg
+    from isaaclab_b200.envs.compile import compile_env_cfg
+    from isaaclab_b200.tasks import TASKS
+    cfg = TASKS["B200-Opcode-Coverage-v0"]()
+    spec = compile_env_cfg(cfg, num_envs=4)
+    d = [a for a in spec["actuators"] if a["kind"] == "delayed_pd"]
+    assert len(d) == 1 and (d[0]["min_delay"], d[0]["max_delay"]) == (1, 3) and len(d[0]["joint_ids"]) == 2
+    cfg.scene.robot.actuators["hips_hind"] = DelayedPDActuatorCfg(joint_names_expr=[".*H_HAA"], stiffness=1.0, damping=0.1,
+                                                                 min_delay=3, max_delay=1)
+    with pytest.raises(ValueError, match="min_delay <= max_delay"):
+        compile_env_cfg(cfg, num_envs=4)
