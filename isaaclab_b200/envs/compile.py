@@ -253,8 +253,14 @@ def compile_env_cfg(cfg: ManagerBasedRLEnvCfg, num_envs: int | None = None, terr
         terrain_info = None
     hs = cfg.scene.height_scanner
     if hs is not None:
-        starts, dirs = grid_pattern(hs.pattern_cfg.size, hs.pattern_cfg.resolution, hs.pattern_cfg.direction,
-                                    hs.pattern_cfg.ordering)
+        pc = hs.pattern_cfg
+        if type(pc).__name__ in ("LidarPatternCfg", "BpearlPatternCfg"):   # sensors/patterns.py: general (non-vertical) rays
+            st_, dr_ = pc.func(pc, "cpu")
+            starts, dirs = st_.numpy().astype(np.float32), dr_.numpy().astype(np.float32)
+        elif type(pc).__name__ == "PinholeCameraPatternCfg":
+            raise NotImplementedError("the pinhole pattern belongs to RayCasterCamera (per-env intrinsics), not to RayCaster")
+        else:
+            starts, dirs = grid_pattern(pc.size, pc.resolution, pc.direction, pc.ordering)
         if tuple(hs.offset.rot) != (1.0, 0.0, 0.0, 0.0):
             raise NotImplementedError("ray caster offset rotation")
         starts = starts + np.asarray(hs.offset.pos, dtype=np.float32)  # ray_caster.py:207-208
