@@ -191,3 +191,30 @@ def test_observation_noise_kinds_match_oracle():
     z = (f_noisy.compute_obs(sim.views(1)[-1]) - f_clean.compute_obs(sim.views(1)[-1])).flatten()
     assert abs(float(z.mean())) < 0.05 and abs(float(z.std()) - 1.0) < 0.05, (float(z.mean()), float(z.std()))
     assert abs(float((z ** 3).mean())) < 0.15 and abs(float((z ** 4).mean()) - 3.0) < 0.3
+
+
+@pytest.mark.parametrize("pattern", ["lidar", "bpearl"])
+def test_height_scan_with_lidar_patterns_matches_oracle(pattern):
+    """Non-vertical ray patterns (LAB/sensors/ray_caster/patterns/patterns.py:106-180) through the step: the observation
+    kernel's general-ray instantiation (2-D DDA over the bin grid) against the oracle's brute-force query, incl. misses
+    (inf -> clipped by the term) and a sensor that follows the full base orientation."""
+    from isaaclab_b200.envs.compile import compile_env_cfg
+    from isaaclab_b200.sensors import patterns as P
+    from isaaclab_b200.tasks import TASKS as REG
+    from tests.mdp_common import small_terrain
+    cfg = REG["Isaac-Velocity-Rough-Anymal-C-v0"]()
+    cfg.scene.terrain.max_init_terrain_level = 2
+    hs = cfg.scene.height_scanner
+    if pattern == "lidar":
+        hs.pattern_cfg = P.LidarPatternCfg(channels=4, vertical_fov_range=(-60.0, -20.0), horizontal_fov_range=(-180.0, 180.0),
+                                           horizontal_res=20.0)
+        hs.attach_yaw_only = False
+    else:
+        hs.pattern_cfg = P.BpearlPatternCfg(horizontal_res=30.0, vertical_ray_angles=[-80.0, -60.0, -35.0, -10.0])   # negative: the rays of an upright mount point down
+    hs.offset.pos = (0.0, 0.0, 2.0)     # the height scanner's 20 m mast would put most slanted rays off the terrain
+    hs.max_distance = 8.0               # ... and the flattest ones still miss: both outcomes are covered
+    spec = compile_env_cfg(cfg, num_envs=96, terrain=small_terrain(), seed=0)
+    assert spec["R"] == (4 * 17 if pattern == "lidar" else 4 * 12)
+    _, orc, n_resets, _ = run_step_parity(spec, 4, fused=True, tag=f"rough-anymal/{pattern}")
+    hits = orc.rc_hits[..., 2]
+    assert torch.isfinite(hits).any() and torch.isinf(hits).any() and n_resets > 0
