@@ -1682,6 +1682,7 @@ height_scan_spec_kernel(const __grid_constant__ Env env_param, Sim sim, const Ob
 
 __device__ __forceinline__ float obs_finish(const Env* __restrict__ e, float v, float4 ca, float4 cb, unsigned w0, int kind,
                                             int64_t step, unsigned n, unsigned k, unsigned gid);
+__device__ __forceinline__ float obs_apply(float v, float4 ca, float4 cb, unsigned w0, int kind, float u1, float u2, bool recorded);
 
 #ifndef B200LAB_OBS_BLOCKS
 #define B200LAB_OBS_BLOCKS 4
@@ -1691,7 +1692,9 @@ __device__ __forceinline__ float obs_finish(const Env* __restrict__ e, float v, 
 #endif
 // kBatch: candidates of the ray's cell requested per round trip (raycast_vertical); kBatch = 4 trades the 64-register cap
 // (and with it a quarter of the resident warps) for half the dependent round trips of a 4-candidate cell
-template <bool kVerticalRays, int kBatch = kVertBatch>
+// kPlain: no term keeps history or carries modifiers -- that code (and its column-program word) is compiled out, which is
+// what the 64-register budget of the headline configs was tuned for
+template <bool kVerticalRays, int kBatch = kVertBatch, bool kPlain = true>
 __global__ void __launch_bounds__(B200LAB_OBS_THREADS, kVerticalRays ? (kBatch > 2 ? 3 : B200LAB_OBS_BLOCKS) * (256 / B200LAB_OBS_THREADS) : 2)
 compute_obs_kernel(const __grid_constant__ Env env_param, Sim sim, int64_t step, const ObsCol* __restrict__ cols,
                    const float* __restrict__ derived, const __grid_constant__ MeshAccel mesh, int has_mesh,
@@ -1704,13 +1707,14 @@ compute_obs_kernel(const __grid_constant__ Env env_param, Sim sim, int64_t step,
   const unsigned gid = n * D + k;
   const float* o = derived + (size_t)n * kDerived;
   const ObsCol* col = cols + k;
-  const float4 ca = __ldg(&col->a), cb = __ldg(&col->b), cd = __ldg(&col->d);   // static program: read before the dependency wait
+  const float4 ca = __ldg(&col->a), cb = __ldg(&col->b);   // static program: read before the dependency wait
+  const float4 cd = kPlain ? make_float4(0.f, 0.f, 0.f, 0.f) : __ldg(&col->d);
   pdl_wait();
   const unsigned w0 = __float_as_uint(ca.x);
   const int op = w0 & 0xffu, li = (w0 >> 8) & 0xffffu, kind = (w0 >> 24) & 0x3fu;
   // history (observation_manager.py:319-325): column = (row h of H, element); rows oldest first, the newest row is the
   // one computed now.  Slot of row h in the ring: (appends so far + 1 + h) mod H.
-  const unsigned hw = __float_as_uint(cd.x), H = hw & 0xffu, hrow = (hw >> 8) & 0xffu, modk = hw >> 16;
+  const unsigned hw = kPlain ? 0u : __float_as_uint(cd.x), H = hw & 0xffu, hrow = (hw >> 8) & 0xffu, modk = hw >> 16;
   float* ring = nullptr;
   if (H) {
     if (e->step_counter_dev) step = *e->step_counter_dev;
@@ -1786,29 +1790,188 @@ compute_obs_kernel(const __grid_constant__ Env env_param, Sim sim, int64_t step,
   e->obs_buf[gid] = v;
 }
 
-// noise -> clip -> scale of one observation element (observation_manager.py:313-318)
-__device__ __forceinline__ float obs_finish(const Env* __restrict__ e, float v, float4 ca, float4 cb, unsigned w0, int kind,
-                                            int64_t step, unsigned n, unsigned k, unsigned gid) {
+// ------------------------------------------------------------------------------------------------
+// compute_obs, Q columns per thread (vertical rays, no history / modifiers).
+//
+// The one-column kernel above is a chain of dependent L2 round trips per ray (cell range -> entries -> records) run by
+// ~27 warps per SM; ncu shows it latency-bound with nothing saturated, and half of its time is the per-thread prologue
+// (column program, derived pose, Philox) paid by N * obs_dim threads (profiles/r2_notes.md).  Here a thread owns Q
+// consecutive columns of one env: the pose and the Philox block are fetched once per thread, and the Q ray queries advance
+// in lockstep -- the entry of candidate i+1 of every ray is requested together with the records of candidate i, so each trip
+// of the loop is ONE round trip with 4Q independent loads in flight per thread.  The loop body is call-free: a borderline
+// barycentric (|.| < 2e-5) only flags its ray, which is then redone by raycast_vertical (the fp64 decision) -- same bits as
+// the one-column kernel for every ray.
+// ------------------------------------------------------------------------------------------------
+template <int Q>
+__global__ void __launch_bounds__(64, Q >= 4 ? 8 : 12)
+compute_obs_quad_kernel(const __grid_constant__ Env env_param, Sim sim, int64_t step, const ObsCol* __restrict__ cols,
+                        const float* __restrict__ derived, const __grid_constant__ MeshAccel mesh, int has_mesh,
+                        const float* __restrict__ spec_z, unsigned env_begin, unsigned env_count) {
+  const Env* __restrict__ e = &env_param;
+  const unsigned N = (unsigned)e->N, D = (unsigned)e->obs_dim, QD = (D + Q - 1) / Q;
+  const unsigned lid = blockIdx.x * blockDim.x + threadIdx.x;
+  if (lid >= env_count * QD) return;
+  const unsigned n = env_begin + lid / QD, k0 = (lid - (lid / QD) * QD) * Q;
+  float4 ca[Q], cb[Q];
+  bool has_hs = false;
+#pragma unroll
+  for (int j = 0; j < Q; ++j) {   // static program: read before the dependency wait; the tail of a row repeats its last column
+    const ObsCol* col = cols + min(k0 + j, D - 1);
+    ca[j] = __ldg(&col->a); cb[j] = __ldg(&col->b);
+    has_hs |= (__float_as_uint(ca[j].x) & 0xffu) == B200LAB_OBS_HEIGHT_SCAN;
+  }
+  pdl_wait();
+  const float* o = derived + (size_t)n * kDerived;
+  float px = 0.f, py = 0.f, pz = 0.f;
+  f4 qy{1.f, 0.f, 0.f, 0.f};
+  bool upd = false, spec = false;
+  if (has_hs) {
+    px = o[9]; py = o[10]; pz = o[11];
+    qy = f4{o[12], o[13], o[14], o[15]};
+    upd = o[17] != 0.f; spec = o[18] != 0.f;
+  }
+  float v[Q], sx[Q], sy[Q], sz[Q], inv_dz[Q], dzv[Q], tb[Q];
+  int s0[Q], cnt[Q];
+  bool hs[Q], hit[Q], border[Q];
+#pragma unroll
+  for (int j = 0; j < Q; ++j) {
+    const unsigned w0 = __float_as_uint(ca[j].x);
+    const int op = w0 & 0xffu, li = (w0 >> 8) & 0xffffu;
+    v[j] = 0.f; cnt[j] = 0; s0[j] = 0; hs[j] = false; hit[j] = false; border[j] = false;
+    sx[j] = sy[j] = sz[j] = 0.f; inv_dz[j] = dzv[j] = -1.f; tb[j] = e->rc_max_distance;
+    switch (op) {
+      case B200LAB_OBS_BASE_LIN_VEL: v[j] = o[li]; break;
+      case B200LAB_OBS_BASE_ANG_VEL: v[j] = o[3 + li]; break;
+      case B200LAB_OBS_PROJECTED_GRAVITY: v[j] = o[6 + li]; break;
+      case B200LAB_OBS_GENERATED_COMMANDS: v[j] = e->cmd_vel_b[n * 3 + li]; break;
+      case B200LAB_OBS_JOINT_POS_REL: v[j] = sim.joint_pos[(size_t)n * e->J + li] - e->default_joint_pos[li]; break;
+      case B200LAB_OBS_JOINT_VEL_REL: v[j] = sim.joint_vel[(size_t)n * e->J + li] - e->default_joint_vel[li]; break;
+      case B200LAB_OBS_JOINT_POS: v[j] = sim.joint_pos[(size_t)n * e->J + li]; break;
+      case B200LAB_OBS_JOINT_VEL: v[j] = sim.joint_vel[(size_t)n * e->J + li]; break;
+      case B200LAB_OBS_LAST_ACTION: v[j] = e->action[(size_t)n * e->A + li]; break;
+      case B200LAB_OBS_BASE_POS_Z: v[j] = o[16]; break;
+      case B200LAB_OBS_EXTERNAL: v[j] = e->ext_values[((size_t)__float_as_int(cb[j].w) + li) * N + n]; break;
+      case B200LAB_OBS_HEIGHT_SCAN: {
+        hs[j] = true;
+        if (upd) {   // ray start = quat_apply_yaw(q, local start) + pos (ray_caster.py:243-253)
+          const float4 cc = __ldg(&cols[min(k0 + j, D - 1)].c);
+          f3 st = quat_apply(qy, f3{cc.x, cc.y, cc.z});
+          sx[j] = st.x + px; sy[j] = st.y + py; sz[j] = st.z + pz;
+          dzv[j] = cc.w; inv_dz[j] = 1.0f / cc.w;
+          if (!spec && has_mesh) {
+            const int cx = (int)floorf((sx[j] - mesh.ox) * mesh.inv_cell), cy = (int)floorf((sy[j] - mesh.oy) * mesh.inv_cell);
+            if (cx >= 0 && cy >= 0 && cx < mesh.nx && cy < mesh.ny) {
+              const int c = cy * mesh.nx + cx;
+              s0[j] = __ldg(mesh.cell_start + c);
+              cnt[j] = __ldg(mesh.cell_start + c + 1) - s0[j];
+            }
+          }
+        }
+        break;
+      }
+    }
+  }
+  // ---- the Q ray queries in lockstep
+  int maxc = 0;
+  int fn[Q];
+#pragma unroll
+  for (int j = 0; j < Q; ++j) {
+    maxc = max(maxc, cnt[j]);
+    fn[j] = cnt[j] > 0 ? __ldg(mesh.cell_tris + s0[j]) : -1;
+  }
+  for (int it = 0; it < maxc; ++it) {
+    float4 ra[Q], rb[Q], rc[Q];
+    bool on[Q];
+#pragma unroll
+    for (int j = 0; j < Q; ++j) {
+      on[j] = fn[j] >= 0;
+      const float4* r = mesh.rec + (size_t)(on[j] ? (fn[j] & kEntryIdMask) : 0) * 3;
+      if (on[j]) { ra[j] = __ldg(r); rb[j] = __ldg(r + 1); rc[j] = __ldg(r + 2); }
+    }
+#pragma unroll
+    for (int j = 0; j < Q; ++j) fn[j] = it + 1 < cnt[j] ? __ldg(mesh.cell_tris + s0[j] + it + 1) : -1;
+#pragma unroll
+    for (int j = 0; j < Q; ++j) {
+      if (on[j]) {
+        const float t = ray_tri_vertical_fast(ra[j], rb[j], rc[j], sx[j], sy[j], sz[j], inv_dz[j], border[j]);
+        if (t > 0.0f && t <= tb[j]) { tb[j] = t; hit[j] = true; }
+      }
+    }
+  }
+  // ---- finish: hit heights, noise (one Philox block for the thread's columns), clip, scale
+  const bool recorded = e->u_obs != nullptr;
+  bool need3 = false, need4 = false;
+#pragma unroll
+  for (int j = 0; j < Q; ++j) {
+    const int kind = (__float_as_uint(ca[j].x) >> 24) & 0x3fu;
+    const bool rnd = (kind >= B200LAB_NOISE_UNIFORM_ADD && kind <= B200LAB_NOISE_UNIFORM_ABS) || kind > B200LAB_NOISE_CONSTANT_ABS;
+    need3 |= rnd; need4 |= kind > B200LAB_NOISE_CONSTANT_ABS;
+  }
+  uint4 r3 = make_uint4(0, 0, 0, 0), r4 = r3;
+  if (!recorded && need3) {   // Q divides 4: the thread's columns share one counter block (slot >> 2), as philox_uniform forms it
+    if (e->step_counter_dev) step = *e->step_counter_dev;
+    const uint2 key = make_uint2((uint32_t)e->seed, (uint32_t)(e->seed >> 32));
+    const uint32_t hi = (uint32_t)((uint64_t)step >> 32);
+    r3 = philox4x32_10(make_uint4(n, k0 >> 2, (uint32_t)step, hi ^ (3u << 24)), key);
+    if (need4) r4 = philox4x32_10(make_uint4(n, k0 >> 2, (uint32_t)step, hi ^ (4u << 24)), key);
+  }
+#pragma unroll
+  for (int j = 0; j < Q; ++j) {
+    const unsigned k = k0 + j;
+    if (k >= D) break;
+    const unsigned w0 = __float_as_uint(ca[j].x), gid = n * D + k;
+    const int li = (w0 >> 8) & 0xffffu, kind = (w0 >> 24) & 0x3fu;
+    if (hs[j]) {
+      float* hp = e->rc_ray_hits_w ? e->rc_ray_hits_w + ((size_t)n * e->R + li) * 3 : nullptr;
+      float hz;
+      if (upd) {
+        f3 h3{INFINITY, INFINITY, INFINITY};
+        if (spec) {   // speculative scan cast from this very pose (height_scan_spec_kernel)
+          const float z = spec_z[(size_t)n * e->R + li];
+          if (z != INFINITY) h3 = {sx[j], sy[j], z};
+        } else if (border[j]) {   // some candidate sat on an edge: the fp64 path decides the whole ray
+          float tt; int face;
+          if (raycast_vertical(mesh, f3{sx[j], sy[j], sz[j]}, dzv[j], e->rc_max_distance, tt, face)) h3 = {sx[j], sy[j], sz[j] + tt * dzv[j]};
+        } else if (hit[j]) {
+          h3 = {sx[j], sy[j], sz[j] + tb[j] * dzv[j]};
+        }
+        if (hp) { hp[0] = h3.x; hp[1] = h3.y; hp[2] = h3.z; }
+        hz = h3.z;
+      } else {
+        hz = hp ? hp[2] : INFINITY;
+      }
+      v[j] = (pz - hz) - cb[j].z;   // observations.py:173
+    }
+    float u1 = 0.f, u2 = 0.f;
+    if (recorded) u1 = e->u_obs[gid];
+    else {
+      const unsigned lane = k & 3u;
+      const uint32_t a3 = lane == 0 ? r3.x : lane == 1 ? r3.y : lane == 2 ? r3.z : r3.w;
+      const uint32_t a4 = lane == 0 ? r4.x : lane == 1 ? r4.y : lane == 2 ? r4.z : r4.w;
+      u1 = (float)(a3 >> 8) * (1.0f / 16777216.0f);
+      u2 = (float)(a4 >> 8) * (1.0f / 16777216.0f);
+    }
+    e->obs_buf[gid] = obs_apply(v[j], ca[j], cb[j], w0, kind, u1, u2, recorded);
+  }
+}
+
+// noise -> clip -> scale of one observation element (observation_manager.py:313-318).  u1: the element's uniform draw (or,
+// in parity mode, the recorded draw of whatever distribution the term uses); u2: second uniform of a Gaussian's Box-Muller.
+__device__ __forceinline__ float obs_apply(float v, float4 ca, float4 cb, unsigned w0, int kind, float u1, float u2, bool recorded) {
   if (kind != B200LAB_NOISE_NONE) {
     const float noise_lo = ca.y, noise_span = ca.z;
-    if (e->step_counter_dev) step = *e->step_counter_dev;
     if (kind == B200LAB_NOISE_CONSTANT_ADD) v = v + noise_lo;             // noise_model.py:33-38
     else if (kind == B200LAB_NOISE_CONSTANT_SCALE) v = v * noise_lo;
     else if (kind == B200LAB_NOISE_CONSTANT_ABS) v = 0.0f + noise_lo;
     else if (kind <= B200LAB_NOISE_UNIFORM_ABS) {
-      float u = e->u_obs ? e->u_obs[gid] : philox_uniform(e->seed, step, 3u, n, k);
+      float u = u1;
       float nz = u * noise_span + noise_lo;
       if (kind == B200LAB_NOISE_UNIFORM_ADD) v = (v + u * noise_span) + noise_lo;  // noise_model.py:64
       else if (kind == B200LAB_NOISE_UNIFORM_SCALE) v = v * nz;
       else v = nz;
     } else {
-      float z;
-      if (e->u_obs) z = e->u_obs[gid];   // parity mode: the recorded randn_like draw
-      else {                             // Box-Muller on two Philox uniforms of this element
-        float u1 = philox_uniform(e->seed, step, 3u, n, k);
-        float u2 = philox_uniform(e->seed, step, 4u, n, k);
-        z = sqrtf(-2.0f * logf(1.0f - u1)) * cospif(2.0f * u2);
-      }
+      // parity mode: the recorded randn_like draw; else Box-Muller on two Philox uniforms of this element
+      float z = recorded ? u1 : sqrtf(-2.0f * logf(1.0f - u1)) * cospif(2.0f * u2);
       float nz = noise_lo + noise_span * z;
       if (kind == B200LAB_NOISE_GAUSSIAN_ADD) v = (v + noise_lo) + noise_span * z;   // noise_model.py:91
       else if (kind == B200LAB_NOISE_GAUSSIAN_SCALE) v = v * nz;
@@ -1818,6 +1981,21 @@ __device__ __forceinline__ float obs_finish(const Env* __restrict__ e, float v, 
   if (w0 & (1u << 30)) v = fminf(fmaxf(v, cb.x), cb.y);
   if (w0 & (1u << 31)) v = v * ca.w;
   return v;
+}
+
+__device__ __forceinline__ float obs_finish(const Env* __restrict__ e, float v, float4 ca, float4 cb, unsigned w0, int kind,
+                                            int64_t step, unsigned n, unsigned k, unsigned gid) {
+  float u1 = 0.f, u2 = 0.f;
+  if (kind >= B200LAB_NOISE_UNIFORM_ADD && kind != B200LAB_NOISE_CONSTANT_ADD && kind != B200LAB_NOISE_CONSTANT_SCALE &&
+      kind != B200LAB_NOISE_CONSTANT_ABS) {
+    if (e->u_obs) u1 = e->u_obs[gid];
+    else {
+      if (e->step_counter_dev) step = *e->step_counter_dev;
+      u1 = philox_uniform(e->seed, step, 3u, n, k);
+      if (kind > B200LAB_NOISE_CONSTANT_ABS) u2 = philox_uniform(e->seed, step, 4u, n, k);
+    }
+  }
+  return obs_apply(v, ca, cb, w0, kind, u1, u2, e->u_obs != nullptr);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -2176,7 +2354,7 @@ static int upload_obs_tables(EnvHandle* h) {
   if (s.rc_mesh) {
     cudaError_t err = cudaMemcpy(&h->mesh, s.rc_mesh, sizeof(MeshAccel), cudaMemcpyDeviceToHost);
     if (err != cudaSuccess) { set_error("ray-caster mesh descriptor: %s", cudaGetErrorString(err)); return B200LAB_ERR_CUDA; }
-    h->has_mesh = true;
+    h->has_mesh = getenv("B200LAB_OBS_NOMESH") == nullptr;   // measurement knob (tools/obs_probe.py): every ray misses
   }
   // speculative-scan buffers; any descriptor change invalidates the recorded poses (NaN never compares equal to a pose)
   if (h->side2) cudaStreamSynchronize(h->side2);
@@ -2631,8 +2809,21 @@ int b200lab_compute_obs_range(void* env, const B200LabSimView* sim, int64_t step
     count_launch();
     return check_launch("compute_obs");
   }
+  if (h->obs_impl >= 2 && h->obs_plain && h->rays_vertical) {
+    // Q columns per thread; obs_impl 2 -> Q = 4, 3 -> Q = 2
+    const int Q = h->obs_impl == 3 ? 2 : 4;
+    auto kq = Q == 4 ? compute_obs_quad_kernel<4> : compute_obs_quad_kernel<2>;
+    const int64_t threads = (int64_t)cnt * ((s.obs_dim + Q - 1) / Q);
+    cudaError_t err = launch_pdl(kq, dim3((unsigned)ceil_div(threads, 64)), dim3(64), 0, st_, h->host, *sim, step_counter,
+                                 (const ObsCol*)h->cols, (const float*)h->derived, h->mesh, h->has_mesh ? 1 : 0,
+                                 (const float*)h->spec_z, (unsigned)env_begin, (unsigned)cnt);
+    if (err != cudaSuccess) { set_error("compute_obs: %s", cudaGetErrorString(err)); return B200LAB_ERR_CUDA; }
+    count_launch();
+    return check_launch("compute_obs");
+  }
   {
-    auto kern = !h->rays_vertical ? compute_obs_kernel<false> : h->vert_batch == 4 ? compute_obs_kernel<true, 4>
+    auto kern = !h->obs_plain ? (h->rays_vertical ? compute_obs_kernel<true, kVertBatch, false> : compute_obs_kernel<false, kVertBatch, false>)
+              : !h->rays_vertical ? compute_obs_kernel<false> : h->vert_batch == 4 ? compute_obs_kernel<true, 4>
               : h->vert_batch == 3 ? compute_obs_kernel<true, 3> : compute_obs_kernel<true>;
     cudaError_t err = launch_pdl(kern, dim3((unsigned)ceil_div(total, B200LAB_OBS_THREADS)), dim3(B200LAB_OBS_THREADS), 0, st_, h->host, *sim, step_counter,
                                  (const ObsCol*)h->cols, (const float*)h->derived, h->mesh, h->has_mesh ? 1 : 0,

@@ -116,6 +116,22 @@ __device__ __forceinline__ float ray_tri_vertical_rec(const MeshAccel& m, int f,
   return t > 0.0f ? t : -1.0f;
 }
 
+// Projected test without the out-of-line fp64 branch: a borderline barycentric only raises `border` (the caller then
+// redoes that ray with raycast_vertical, which decides it in fp64) -- keeps call-free the loops that interleave several rays.
+__device__ __forceinline__ float ray_tri_vertical_fast(float4 a, float4 b, float4 c, float ox, float oy, float oz, float inv_dz,
+                                                       bool& border) {
+  float tx = ox - a.x, ty = oy - a.y;
+  if (a.w == 0.0f) return -1.0f;
+  float u = (tx * c.x - ty * b.w) * a.w;
+  float v = (ty * b.x - tx * b.y) * a.w;
+  float w = 1.0f - u - v;
+  if (u < -kBaryBand || v < -kBaryBand || w < -kBaryBand) return -1.0f;
+  if (u < kBaryBand || v < kBaryBand || w < kBaryBand) { border = true; return -1.0f; }
+  float zh = a.z + u * b.z + v * c.y;
+  float t = (zh - oz) * inv_dz;
+  return t > 0.0f ? t : -1.0f;
+}
+
 // Vertical closest hit: one cell.  The query is three dependent round trips to L2 (cell range -> triangle ids ->
 // records), so each level is requested for up to kVertBatch candidates at once: a typical cell (<= 4 candidates)
 // costs exactly three latencies, and every lane of a warp runs the same single trip.

@@ -34,7 +34,7 @@ def _compare(spec, steps=2, drift=0.3):
     slabs = generate_slabs(spec, steps, seed=21)
     g = torch.Generator().manual_seed(4)
     N = spec["N"]
-    envs = [_env(spec, 0), _env(spec, 1), _env(spec, 1, store_ray_hits=False)]
+    envs = [_env(spec, 0), _env(spec, 1), _env(spec, 1, store_ray_hits=False), _env(spec, 2), _env(spec, 3)]   # 2, 3: Q = 4, 2 columns / thread
     sims = [SyntheticSim(spec, K=steps, device="cuda", slabs={k: v.clone() for k, v in slabs.items()}) for _ in envs]
     u_obs = torch.rand(N, envs[0].obs_dim, generator=g).cuda()
     d = ((torch.rand(N, 3, generator=g) * 2 - 1) * drift).cuda()
@@ -51,6 +51,18 @@ def _compare(spec, steps=2, drift=0.3):
         assert torch.equal(outs[0], outs[2]), f"step {k}: observations change when the hit buffer is not stored"
         assert torch.equal(envs[0].rc_ray_hits_w, envs[1].rc_ray_hits_w), f"step {k}: ray hits differ"
         assert envs[2].rc_ray_hits_w is None
+        for i in (3, 4):
+            assert torch.equal(outs[0], outs[i]), f"step {k}: the {4 if i == 3 else 2}-column kernel differs from the per-ray kernel"
+            assert torch.equal(envs[0].rc_ray_hits_w, envs[i].rc_ray_hits_w), f"step {k}: ray hits differ (multi-column kernel)"
+        # perf mode: Philox noise, one counter block per thread in the multi-column kernels -- same stream, same bits
+        philox = []
+        for env, sim in zip(envs, sims):
+            env.set_uniforms(None, None, None)
+            env.rc_is_outdated.fill_(1)
+            philox.append(env.compute_obs(sim.views(k)[-1]).clone())
+        assert not torch.equal(philox[0], outs[0])
+        for i in (1, 3, 4):
+            assert torch.equal(philox[0], philox[i]), f"step {k}: Philox noise differs in kernel variant {i}"
     # a sensor that is NOT outdated re-reads its stored hits in both kernels
     for env, sim in zip(envs[:2], sims[:2]):
         env.rc_is_outdated.fill_(0)
