@@ -563,6 +563,8 @@ typedef struct B200LabGather {
   const float* log_prob; const float* advantages; const float* mu; const float* sigma;
   float* o_obs; float* o_actions; float* o_values; float* o_returns;
   float* o_log_prob; float* o_advantages; float* o_mu; float* o_sigma;
+  int64_t o_obs_ld;   /* row stride of o_obs in elements; 0 = obs_dim.  A caller that wants 16-byte aligned observation rows
+                       * (the first MLP layer's TMA operand) passes a zero-initialised [M, ld] buffer: pad columns are not written */
 } B200LabGather;
 int b200lab_gather_minibatch(const B200LabGather* g, void* stream);
 

@@ -183,7 +183,7 @@ gather_minibatch_kernel(B200LabGather g) {
   for (int64_t m = warp; m < g.M; m += nwarps) {
     int64_t src = __ldg(g.idx + m);
     const float* so = g.obs + src * g.obs_dim;
-    float* dobs = g.o_obs + m * g.obs_dim;
+    float* dobs = g.o_obs + m * (g.o_obs_ld > 0 ? g.o_obs_ld : (int64_t)g.obs_dim);
     for (int c = lane; c < g.obs_dim; c += 32) dobs[c] = __ldg(so + c);
     for (int c = lane; c < g.act_dim; c += 32) {
       g.o_actions[m * g.act_dim + c] = __ldg(g.actions + src * g.act_dim + c);

@@ -31,6 +31,8 @@
 //                           have): offset(mn,k) = swz((mn/32)*LBO + (k/4)*SBO + (k%4)*128 + (mn%32)*4), LBO = 4096,
 //                           SBO = 512, swz: byte-address bits [5,7) ^= bits [7,9)
 // so dX (B = W read along its rows) and dW (both operands read along the sample dimension) need no transposition.
+#include <cuda.h>   // CUtensorMap and the cuTensorMapEncodeTiled prototype; the entry point is resolved at run time
+
 #include "common.cuh"
 
 namespace b200lab {
@@ -61,6 +63,17 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
       "DONE:\n\t"
       "}" ::"r"(bar), "r"(parity)
       : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+// TMA: one 2-D box (c0 = element index along K, c1 = row) global -> shared, completion counted in bytes on `bar`
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, int c0, int c1, uint32_t bar) {
+  asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+               ::"r"(dst), "l"(map), "r"(c0), "r"(c1), "r"(bar) : "memory");
+}
+__device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* map) {
+  asm volatile("prefetch.tensormap [%0];" ::"l"(map) : "memory");
 }
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
@@ -131,6 +144,8 @@ enum OperandMode {
   kKScalar = 1,   // k fastest but unaligned (235-wide)   ->  4-byte copies,            K-major layout
   kMnVec = 2,     // ld_r == 1, k-columns 16-byte aligned -> 16-byte copies along rows, MN-major layout
   kMnScalar = 3,  // rows fastest but unaligned           ->  4-byte copies,            MN-major layout
+  kKTma = 4,      // as kKVec, moved by TMA: ONE thread issues a ROWS x BK box per k-tile (SWIZZLE_128B tensor map writes
+                  // exactly the K-major layout; rows / K beyond the matrix arrive as zeros), completion on an mbarrier
 };
 
 template <int ROWS>
@@ -221,6 +236,20 @@ struct Cursor {
   }
 };
 
+template <int ROWS>
+struct Cursor<ROWS, kKTma> {
+  const CUtensorMap* map;
+  int r0, k_next;
+  bool leader;
+  __device__ __forceinline__ void init(const CUtensorMap* m, int64_t row0, int64_t k_begin, int tid) {
+    map = m; r0 = (int)row0; k_next = (int)k_begin; leader = tid == 0;
+  }
+  __device__ __forceinline__ void issue(uint32_t s_raw, uint32_t bar) {
+    if (leader) tma_load_2d(s_raw, map, k_next, r0, bar);
+    k_next += BK;
+  }
+};
+
 // Shared memory: a ring of kStages RAW stages (A | B, filled by cp.async) and TWO lo buffers (A lo | B lo).  Only the
 // k-tile being multiplied needs its lo part, so the bytes in flight from L2 are not halved by it: kStages-1 raw tiles
 // are outstanding while one tile is split and another is multiplied.
@@ -230,8 +259,8 @@ struct Smem {
   static constexpr uint32_t kA = Tile<BM>::kBytes, kB = Tile<BN>::kBytes;
   static constexpr uint32_t kStage = kA + kB;                      // A raw, B raw   (lo buffer: A lo, B lo)
   static constexpr uint32_t kLo = kStages * kStage;                // two lo buffers follow the raw ring
-  static constexpr uint32_t kCtl = kLo + 2 * kStage;               // full[kStages], empty[kStages], done, tmem pointer
-  static constexpr uint32_t kTotal = kCtl + 16 * kStages + 16 + 1024;   // + slack to align the base to 1024
+  static constexpr uint32_t kCtl = kLo + 2 * kStage;               // full[kStages], empty[kStages], done, tmem pointer, tma[kStages]
+  static constexpr uint32_t kTotal = kCtl + 24 * kStages + 16 + 1024;   // + slack to align the base to 1024
 };
 
 __device__ __forceinline__ float exp2f_fast(float x) { float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
@@ -270,8 +299,11 @@ template <int BN, int AMODE, int BMODE>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_tf32_kernel(const float* __restrict__ A, int64_t lda_i, int64_t lda_k, const float* __restrict__ B, int64_t ldb_k,
                  int64_t ldb_j, float* __restrict__ C, int64_t ldc, int64_t M, int N, int64_t K, int64_t k_per_split,
-                 const float* __restrict__ bias, int epi, int split) {
+                 const float* __restrict__ bias, int epi, int split, const __grid_constant__ CUtensorMap map_a,
+                 const __grid_constant__ CUtensorMap map_b) {
   extern __shared__ uint8_t smem_dyn[];
+  constexpr bool kTmaA = AMODE == kKTma, kTmaB = BMODE == kKTma, kAnyTma = kTmaA || kTmaB, kAllTma = kTmaA && kTmaB;
+  constexpr uint32_t kTmaBytes = (kTmaA ? Tile<BM>::kBytes : 0u) + (kTmaB ? Tile<BN>::kBytes : 0u);
   using S = Smem<BN>;
   constexpr int kStages = S::kStages;
   constexpr int kMmaWarp = kProducers / 32;
@@ -286,11 +318,15 @@ gemm_tf32_kernel(const float* __restrict__ A, int64_t lda_i, int64_t lda_k, cons
   uint8_t* ctl = smem + S::kCtl;
   const uint32_t bar_full = smem_u32(ctl), bar_empty = bar_full + 8 * kStages, bar_done = bar_full + 16 * kStages;
   uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(ctl + 16 * kStages + 8);
+  const uint32_t bar_tma = bar_full + 16 * kStages + 16;
 
   if (tid == 0) {
+    if (kTmaA) tma_prefetch_desc(&map_a);
+    if (kTmaB) tma_prefetch_desc(&map_b);
     for (int s = 0; s < kStages; ++s) {
       mbar_init(bar_full + 8 * s, kProducers);
       mbar_init(bar_empty + 8 * s, 1);
+      mbar_init(bar_tma + 8 * s, 1);
     }
     mbar_init(bar_done, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -305,27 +341,31 @@ gemm_tf32_kernel(const float* __restrict__ A, int64_t lda_i, int64_t lda_k, cons
     // ---------------- producers ----------------
     Cursor<BM, AMODE> ca;
     Cursor<BN, BMODE> cb;
-    ca.init(A, lda_i, lda_k, i0, M, k_begin, k_end, tid);
-    cb.init(B, ldb_j, ldb_k, j0, N, k_begin, k_end, tid);
+    if constexpr (kTmaA) ca.init(&map_a, i0, k_begin, tid); else ca.init(A, lda_i, lda_k, i0, M, k_begin, k_end, tid);
+    if constexpr (kTmaB) cb.init(&map_b, j0, k_begin, tid); else cb.init(B, ldb_j, ldb_k, j0, N, k_begin, k_end, tid);
     auto issue = [&](int kt_new) {
-      const uint32_t st = smem_u32(smem + (kt_new % kStages) * S::kStage);
-      ca.issue(st);
-      cb.issue(st + S::kA);
+      const int sn = kt_new % kStages;
+      const uint32_t st = smem_u32(smem + sn * S::kStage);
+      if constexpr (kAnyTma) { if (tid == 0) mbar_arrive_expect_tx(bar_tma + 8 * sn, kTmaBytes); }
+      if constexpr (kTmaA) ca.issue(st, bar_tma + 8 * sn); else ca.issue(st);
+      if constexpr (kTmaB) cb.issue(st + S::kA, bar_tma + 8 * sn); else cb.issue(st + S::kA);
     };
 #pragma unroll
     for (int p = 0; p < kStages - 1; ++p) {
       if (p < num_kt) issue(p);
-      cp_async_commit();
+      if constexpr (!kAllTma) cp_async_commit();
     }
 #pragma unroll 1
     for (int kt = 0; kt < num_kt; ++kt) {
       const int s = kt % kStages;
-      cp_async_wait<kStages - 2>();   // this thread's copies of k-tile kt have landed ...
+      if constexpr (!kAllTma) cp_async_wait<kStages - 2>();   // this thread's copies of k-tile kt have landed ...
+      // ... the TMA boxes of the tile too (the mbarrier completes when all their bytes are in shared memory, for every waiter)
+      if constexpr (kAnyTma) mbar_wait(bar_tma + 8 * s, (uint32_t)((kt / kStages) & 1));
       if (split) {
-        // ... and, after the producers' barrier, everybody's: the lo sweep is linear over the stage, so a thread reads
-        // bytes other threads copied.  Lo buffer kt&1 was last read by the MMAs of k-tile kt-2 (waited for below, one
-        // iteration ago).
-        asm volatile("bar.sync 1, %0;" ::"n"(kProducers) : "memory");
+        // ... and, after the producers' barrier, everybody's cp.async copies: the lo sweep is linear over the stage, so a
+        // thread reads bytes other threads copied (no barrier when both operands came by TMA).  Lo buffer kt&1 was last
+        // read by the MMAs of k-tile kt-2 (waited for below, one iteration ago).
+        if constexpr (!kAllTma) asm volatile("bar.sync 1, %0;" ::"n"(kProducers) : "memory");
         lo_sweep<S::kStage>(smem + s * S::kStage, smem + S::kLo + (kt & 1) * S::kStage, tid);
       }
       fence_proxy_async();            // cp.async / st.shared (generic proxy) -> visible to the tensor core (async proxy)
@@ -334,11 +374,11 @@ gemm_tf32_kernel(const float* __restrict__ A, int64_t lda_i, int64_t lda_k, cons
       // its lo buffer rewritten -- so this wait is unconditional
       if (kt >= 1) mbar_wait(bar_empty + 8 * ((kt - 1) % kStages), (uint32_t)(((kt - 1) / kStages) & 1));
       if (kt + kStages - 1 < num_kt) issue(kt + kStages - 1);
-      cp_async_commit();
+      if constexpr (!kAllTma) cp_async_commit();
     }
   } else if (lane == 0) {
     // ---------------- MMA issuer ----------------
-    constexpr bool a_mn = AMODE >= kMnVec, b_mn = BMODE >= kMnVec;
+    constexpr bool a_mn = AMODE == kMnVec || AMODE == kMnScalar, b_mn = BMODE == kMnVec || BMODE == kMnScalar;
     constexpr uint32_t idesc = make_idesc(BM, BN) | ((uint32_t)a_mn << 15) | ((uint32_t)b_mn << 16);
 #pragma unroll 1
     for (int kt = 0; kt < num_kt; ++kt) {
@@ -405,11 +445,47 @@ gemm_tf32_kernel(const float* __restrict__ A, int64_t lda_i, int64_t lda_k, cons
   if (warp == kMmaWarp) tmem_dealloc(tmem_d, BN);
 }
 
+// cuTensorMapEncodeTiled, resolved through the runtime (no link-time dependency on libcuda)
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn encode_tiled_fn() {
+  static EncodeTiledFn fn = nullptr;
+  static bool tried = false;
+  if (!tried) {
+    tried = true;
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+      fn = (EncodeTiledFn)p;
+    (void)cudaGetLastError();
+  }
+  return fn;
+}
+
+// Tensor map of a K-contiguous fp32 operand [rows, K] with row stride ld_r (elements): boxes of box_rows x BK, written to
+// shared memory in the K-major SWIZZLE_128B layout the MMA descriptors expect; out-of-range elements arrive as zeros.
+static bool make_k_major_map(CUtensorMap* map, const float* base, int64_t rows, int64_t K, int64_t ld_r, int box_rows) {
+  EncodeTiledFn fn = encode_tiled_fn();
+  if (!fn) return false;
+  const cuuint64_t gdim[2] = {(cuuint64_t)K, (cuuint64_t)rows};
+  const cuuint64_t gstride[1] = {(cuuint64_t)ld_r * 4u};
+  const cuuint32_t box[2] = {(cuuint32_t)BK, (cuuint32_t)box_rows};
+  const cuuint32_t estr[2] = {1u, 1u};
+  return fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, (void*)base, gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+            CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
 template <int BN, int AMODE, int BMODE>
 static int launch(const float* A, int64_t lda_i, int64_t lda_k, const float* B, int64_t ldb_k, int64_t ldb_j, float* C,
                   int64_t ldc, int64_t M, int N, int64_t K, int64_t k_per_split, int splits, const float* bias, int epi,
                   int split, cudaStream_t s) {
   auto kern = gemm_tf32_kernel<BN, AMODE, BMODE>;
+  alignas(64) CUtensorMap map_a, map_b;
+  memset(&map_a, 0, sizeof(map_a));
+  memset(&map_b, 0, sizeof(map_b));
+  if (AMODE == kKTma && !make_k_major_map(&map_a, A, M, K, lda_i, BM)) { set_error("tcgen05 gemm: cuTensorMapEncodeTiled (A) failed"); return B200LAB_ERR_CUDA; }
+  if (BMODE == kKTma && !make_k_major_map(&map_b, B, N, K, ldb_j, BN)) { set_error("tcgen05 gemm: cuTensorMapEncodeTiled (B) failed"); return B200LAB_ERR_CUDA; }
   static bool configured = false;
   if (!configured) {
     cudaError_t err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Smem<BN>::kTotal);
@@ -417,7 +493,8 @@ static int launch(const float* A, int64_t lda_i, int64_t lda_k, const float* B, 
     configured = true;
   }
   dim3 grid((unsigned)ceil_div(M, BM), (unsigned)ceil_div(N, BN), (unsigned)splits);
-  kern<<<grid, kThreads, Smem<BN>::kTotal, s>>>(A, lda_i, lda_k, B, ldb_k, ldb_j, C, ldc, M, N, K, k_per_split, bias, epi, split);
+  kern<<<grid, kThreads, Smem<BN>::kTotal, s>>>(A, lda_i, lda_k, B, ldb_k, ldb_j, C, ldc, M, N, K, k_per_split, bias, epi, split,
+                                                map_a, map_b);
   count_launch();
   return B200LAB_OK;
 }
@@ -429,7 +506,7 @@ static int launch_b(int b_mode, const float* A, int64_t lda_i, int64_t lda_k, co
 #define B200LAB_TC_B(MODE) \
   case MODE: return launch<BN, AMODE, MODE>(A, lda_i, lda_k, B, ldb_k, ldb_j, C, ldc, M, N, K, k_per_split, splits, bias, epi, split, s)
   switch (b_mode) {
-    B200LAB_TC_B(kKVec); B200LAB_TC_B(kKScalar); B200LAB_TC_B(kMnVec);
+    B200LAB_TC_B(kKVec); B200LAB_TC_B(kKScalar); B200LAB_TC_B(kMnVec); B200LAB_TC_B(kKTma);
     default: return launch<BN, AMODE, kMnScalar>(A, lda_i, lda_k, B, ldb_k, ldb_j, C, ldc, M, N, K, k_per_split, splits, bias, epi, split, s);
   }
 #undef B200LAB_TC_B
@@ -442,7 +519,7 @@ static int launch_a(int a_mode, int b_mode, const float* A, int64_t lda_i, int64
 #define B200LAB_TC_A(MODE) \
   case MODE: return launch_b<BN, MODE>(b_mode, A, lda_i, lda_k, B, ldb_k, ldb_j, C, ldc, M, N, K, k_per_split, splits, bias, epi, split, s)
   switch (a_mode) {
-    B200LAB_TC_A(kKVec); B200LAB_TC_A(kKScalar); B200LAB_TC_A(kMnVec);
+    B200LAB_TC_A(kKVec); B200LAB_TC_A(kKScalar); B200LAB_TC_A(kMnVec); B200LAB_TC_A(kKTma);
     default: return launch_b<BN, kMnScalar>(b_mode, A, lda_i, lda_k, B, ldb_k, ldb_j, C, ldc, M, N, K, k_per_split, splits, bias, epi, split, s);
   }
 #undef B200LAB_TC_A
@@ -466,7 +543,14 @@ int gemm_tc(const float* A, int64_t lda_i, int64_t lda_k, const float* B, int64_
     if (ld_r == 1) return (base_ok && ld_k % 4 == 0) ? tc::kMnVec : tc::kMnScalar;
     return ld_k < ld_r ? tc::kKScalar : tc::kMnScalar;
   };
-  const int a_mode = mode_of(A, lda_i, lda_k), b_mode = mode_of(B, ldb_j, ldb_k);
+  int a_mode = mode_of(A, lda_i, lda_k), b_mode = mode_of(B, ldb_j, ldb_k);
+  // K-contiguous, 16-byte aligned operands go by TMA (B200LAB_GEMM_TMA=0 keeps the cp.async path, for A/B measurements);
+  // a K split must fall on k-tile boundaries, since a box reads BK columns whatever the split's end
+  static const bool use_tma = [] { const char* v = getenv("B200LAB_GEMM_TMA"); return !(v && v[0] == '0'); }() && tc::encode_tiled_fn() != nullptr;
+  if (use_tma && (splits == 1 || k_per_split % tc::BK == 0) && K < (1ll << 31) && M < (1ll << 31)) {
+    if (a_mode == tc::kKVec) a_mode = tc::kKTma;
+    if (b_mode == tc::kKVec) b_mode = tc::kKTma;
+  }
   const int split = precision == 2 ? 1 : 0;
   if (N > 64) return tc::launch_a<128>(a_mode, b_mode, A, lda_i, lda_k, B, ldb_k, ldb_j, C, ldc, M, N, K, k_per_split, splits, bias, epi, split, s);
   return tc::launch_a<64>(a_mode, b_mode, A, lda_i, lda_k, B, ldb_k, ldb_j, C, ldc, M, N, K, k_per_split, splits, bias, epi, split, s);

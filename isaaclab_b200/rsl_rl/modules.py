@@ -29,13 +29,35 @@ def _mlp(in_dim, out_dim, hidden):
     return nn.Sequential(*layers)  # module names "0","1",... as RSL/networks/mlp.py:77-80
 
 
+def _padded_k(weight):
+    """Row stride of a 2-D weight's storage block: in_features, or the next multiple of 4 when `_flatten` padded it."""
+    return int(weight.stride(0)) if weight.dim() == 2 else int(weight.shape[-1])
+
+
 class _Net:
     """Per-network forward/backward driver over raw pointers."""
 
     def __init__(self, seq: nn.Sequential):
         self.linears = [m for m in seq if isinstance(m, nn.Linear)]
-        self.dims = [self.linears[0].in_features] + [l.out_features for l in self.linears]
+        self.in_features = self.linears[0].in_features
+        # the first layer's weight may live in a K-padded block (ActorCritic._flatten): its GEMMs then run on the padded
+        # width, against an input padded with zero columns
+        self.dims = [_padded_k(self.linears[0].weight)] + [l.out_features for l in self.linears]
         self._cache = {}
+
+    def _input(self, x, b):
+        """x [M, in_features] -> the [M, dims[0]] operand of layer 0 (zero columns beyond in_features)."""
+        if self.dims[0] == self.in_features:
+            return x
+        if x.stride(0) == self.dims[0] and x.stride(1) == 1 and x.data_ptr() % 16 == 0 and getattr(x, "_b200_row_padded", False):
+            b["x0"] = x          # already the [M, in_features] view of a zero-padded [M, dims[0]] block (RolloutStorage.gather)
+            return x
+        xp = b.get("xpad")
+        if xp is None:
+            xp = b["xpad"] = torch.zeros(x.shape[0], self.dims[0], device=x.device)
+        xp[:, :self.in_features].copy_(x)
+        b["x0"] = xp
+        return xp
 
     def buffers(self, M, device):
         key = (M, str(device))
@@ -57,10 +79,11 @@ class _Net:
         M = x.shape[0]
         b = self.buffers(M, x.device)
         s = _lib.current_stream()
-        inp = x
+        inp = self._input(x, b)
         for i, lin in enumerate(self.linears):
             last = i == len(self.linears) - 1
-            _lib.check(L.b200lab_linear_fwd(_lib.ptr(inp), _lib.ptr(lin.weight), _lib.ptr(lin.bias),
+            # weights by raw address: a K-padded first-layer weight is a strided view of its (contiguous) block
+            _lib.check(L.b200lab_linear_fwd(inp.data_ptr(), lin.weight.data_ptr(), _lib.ptr(lin.bias),
                                             _lib.ptr(b["acts"][i]), M, self.dims[i], self.dims[i + 1],
                                             0 if last else 1, precision, s))
             inp = b["acts"][i]
@@ -76,17 +99,18 @@ class _Net:
         dy = d_out
         if need_dx and "dx0" not in b:
             b["dx0"] = torch.empty(M, self.dims[0], device=x.device)
+        x0 = b["x0"] if self.dims[0] != self.in_features else x   # the padded operand forward(x) used
         for i in reversed(range(len(self.linears))):
             lin = self.linears[i]
             last = i == len(self.linears) - 1
-            inp = x if i == 0 else b["acts"][i - 1]
+            inp = x0 if i == 0 else b["acts"][i - 1]
             dx = (b["dx0"] if need_dx else None) if i == 0 else b["grads"][i - 1]
-            _lib.check(L.b200lab_linear_bwd(_lib.ptr(inp), _lib.ptr(lin.weight), _lib.ptr(b["acts"][i]), _lib.ptr(dy),
-                                            _lib.ptr(b["dz"]), _lib.ptr(dx), _lib.ptr(lin.weight.grad),
+            _lib.check(L.b200lab_linear_bwd(inp.data_ptr(), lin.weight.data_ptr(), _lib.ptr(b["acts"][i]), _lib.ptr(dy),
+                                            _lib.ptr(b["dz"]), _lib.ptr(dx), lin.weight.grad.data_ptr(),
                                             _lib.ptr(lin.bias.grad), M, self.dims[i], self.dims[i + 1],
                                             0 if last else 1, precision, _lib.ptr(b["work"]), s))
             dy = dx
-        return b["dx0"] if need_dx else None
+        return b["dx0"][:, :self.in_features] if need_dx else None
 
 
 class EmpiricalNormalization(nn.Module):
@@ -205,20 +229,37 @@ class ActorCritic(nn.Module):
 
     # -- flat parameter / gradient storage ---------------------------------------------------------
     def _flatten(self, device):
+        """All parameters as views of ONE flat buffer.  The first layer of each MLP reads the observation row (235 wide for
+        the rough tasks): when that width is not a multiple of 4 its weight is stored in a block padded to the next
+        multiple -- the parameter stays a [out, in] (strided) view with the reference's shape and state_dict entry, the pad
+        columns are zero and receive zero gradients, and the layer's GEMMs see 16-byte aligned rows (TMA / vector copies
+        instead of the 4-byte path: profiles/r2_notes.md)."""
         params = list(self.parameters())
-        n = sum(p.numel() for p in params)
-        self.flat_param = torch.empty(n, device=device)
+        padded = {id(m[0].weight) for m in (getattr(self, "actor", None), getattr(self, "critic", None))
+                  if isinstance(m, nn.Sequential) and m[0].in_features % 4 != 0}
+        blocks = []
+        for p in params:
+            kp = (p.shape[1] + 3) // 4 * 4 if id(p) in padded else None
+            blocks.append((p.shape[0] * kp) if kp else p.numel())
+        n = sum(blocks)
+        self.flat_param = torch.zeros(n, device=device)
         # gradient buffer carries 8 extra floats (loss statistics incl. the KL) so one all-reduce moves both
         self.flat_grad_ext = torch.zeros(n + 8, device=device)
         self.flat_grad = self.flat_grad_ext[:n]
         self.stats = self.flat_grad_ext[n:]
         off = 0
         self._views = []
-        for p in params:
-            k = p.numel()
-            self.flat_param[off:off + k].copy_(p.data.reshape(-1))
-            p.data = self.flat_param[off:off + k].view(p.shape)
-            p.grad = self.flat_grad[off:off + k].view(p.shape)
+        for p, k in zip(params, blocks):
+            if id(p) in padded:
+                kp = k // p.shape[0]
+                view = self.flat_param[off:off + k].view(p.shape[0], kp)[:, :p.shape[1]]
+                view.copy_(p.data)
+                p.data = view
+                p.grad = self.flat_grad[off:off + k].view(p.shape[0], kp)[:, :p.shape[1]]
+            else:
+                self.flat_param[off:off + k].copy_(p.data.reshape(-1))
+                p.data = self.flat_param[off:off + k].view(p.shape)
+                p.grad = self.flat_grad[off:off + k].view(p.shape)
             p.requires_grad_(False)
             self._views.append((off, k))
             off += k
@@ -263,12 +304,16 @@ class ActorCritic(nn.Module):
 
     def actor_input(self, obs):
         """Actor observation set, normalised when enabled (actor_critic.py:115-117)."""
-        x = self.get_actor_obs(obs).contiguous().float()
-        return self.actor_obs_normalizer(x) if self.actor_obs_normalization else x
+        x = self.get_actor_obs(obs)
+        if self.actor_obs_normalization:
+            return self.actor_obs_normalizer(x.contiguous().float())
+        return x if getattr(x, "_b200_row_padded", False) else x.contiguous().float()
 
     def critic_input(self, obs):
-        x = self.get_critic_obs(obs).contiguous().float()
-        return self.critic_obs_normalizer(x) if self.critic_obs_normalization else x
+        x = self.get_critic_obs(obs)
+        if self.critic_obs_normalization:
+            return self.critic_obs_normalizer(x.contiguous().float())
+        return x if getattr(x, "_b200_row_padded", False) else x.contiguous().float()
 
     @property
     def action_mean(self):

@@ -190,23 +190,35 @@ class _OptimizerView:
     def state_dict(self):
         alg, pol = self.alg, self.alg.policy
         state = {}
+        params = list(pol.parameters())
+
+        def as_param(buf, i, off, k):   # the slice of a flat buffer in parameter i's shape (K-padded blocks: drop the pad)
+            shape = params[i].shape
+            if k != params[i].numel():
+                return buf[off:off + k].view(shape[0], k // shape[0])[:, :shape[1]]
+            return buf[off:off + k].view(shape)
+
         for i, (off, k) in enumerate(pol._views):
-            shape = list(pol.parameters())[i].shape
             state[i] = {"step": torch.tensor(float(alg.adam_step)),
-                        "exp_avg": alg.exp_avg[off:off + k].view(shape).clone(),
-                        "exp_avg_sq": alg.exp_avg_sq[off:off + k].view(shape).clone()}
+                        "exp_avg": as_param(alg.exp_avg, i, off, k).clone(),
+                        "exp_avg_sq": as_param(alg.exp_avg_sq, i, off, k).clone()}
         group = {"lr": alg.learning_rate, "betas": (0.9, 0.999), "eps": 1e-8, "weight_decay": 0, "amsgrad": False,
                  "params": list(range(len(pol._views)))}
         return {"state": state, "param_groups": [group]}
 
     def load_state_dict(self, sd):
         alg, pol = self.alg, self.alg.policy
+        params = list(pol.parameters())
         for i, (off, k) in enumerate(pol._views):
             st = sd["state"].get(i)
             if st is None:
                 continue
-            alg.exp_avg[off:off + k].copy_(st["exp_avg"].reshape(-1))
-            alg.exp_avg_sq[off:off + k].copy_(st["exp_avg_sq"].reshape(-1))
+            shape = params[i].shape
+            for buf, key in ((alg.exp_avg, "exp_avg"), (alg.exp_avg_sq, "exp_avg_sq")):
+                if k != params[i].numel():   # K-padded block
+                    buf[off:off + k].view(shape[0], k // shape[0])[:, :shape[1]].copy_(st[key].reshape(shape))
+                else:
+                    buf[off:off + k].copy_(st[key].reshape(-1))
             alg.adam_step = int(float(st["step"]))
         if sd.get("param_groups"):
             alg.learning_rate = sd["param_groups"][0]["lr"]

@@ -143,10 +143,15 @@ class RolloutStorage:
         b = self._mb.get(M)
         if b is None:
             D, A, dev = self.observations[self._obs_key].shape[-1], self.actions.shape[-1], self.device
-            b = self._mb[M] = dict(obs=torch.empty(M, D, device=dev), actions=torch.empty(M, A, device=dev),
+            # observation rows padded to a multiple of 4 floats (zero pad columns, never written): the first MLP layer reads
+            # the [M, D] view of this buffer in place as a 16-byte aligned GEMM operand (modules._Net._input)
+            Dp = (D + 3) // 4 * 4
+            b = self._mb[M] = dict(obs_block=torch.zeros(M, Dp, device=dev), actions=torch.empty(M, A, device=dev),
                                    values=torch.empty(M, 1, device=dev), returns=torch.empty(M, 1, device=dev),
                                    log_prob=torch.empty(M, 1, device=dev), advantages=torch.empty(M, 1, device=dev),
                                    mu=torch.empty(M, A, device=dev), sigma=torch.empty(M, A, device=dev))
+            b["obs"] = b["obs_block"][:, :D]
+            b["obs"]._b200_row_padded = Dp != D   # marks the view for the first MLP layer (pad columns stay zero)
         return b
 
     def gather(self, batch_idx):
@@ -156,11 +161,12 @@ class RolloutStorage:
         b = self._mb_buffers(M)
         g = _lib.structs["B200LabGather"]()
         g.M, g.obs_dim, g.act_dim = M, b["obs"].shape[1], b["actions"].shape[1]
+        g.o_obs_ld = b["obs_block"].shape[1]
         p = _lib.ptr
         g.idx = p(batch_idx)
         g.obs, g.actions, g.values, g.returns = p(self.observations[self._obs_key]), p(self.actions), p(self.values), p(self.returns)
         g.log_prob, g.advantages, g.mu, g.sigma = p(self.actions_log_prob), p(self.advantages), p(self.mu), p(self.sigma)
-        g.o_obs, g.o_actions, g.o_values, g.o_returns = p(b["obs"]), p(b["actions"]), p(b["values"]), p(b["returns"])
+        g.o_obs, g.o_actions, g.o_values, g.o_returns = p(b["obs_block"]), p(b["actions"]), p(b["values"]), p(b["returns"])
         g.o_log_prob, g.o_advantages, g.o_mu, g.o_sigma = p(b["log_prob"]), p(b["advantages"]), p(b["mu"]), p(b["sigma"])
         _lib.check(_lib.lib().b200lab_gather_minibatch(ctypes.byref(g), _lib.current_stream()))
         return b
