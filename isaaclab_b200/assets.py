@@ -114,6 +114,30 @@ UNITREE_GO1_CFG = ArticulationCfg(  # unitree.py:102-134
     joint_pos_limits={".*_hip_joint": (-0.863, 0.863), ".*_thigh_joint": (-0.686, 4.501), ".*_calf_joint": (-2.818, -0.888)},
     actuators={"base_legs": GO1_ACTUATOR_CFG}, soft_joint_pos_limit_factor=0.9)
 
+# ANYmal-B / ANYmal-D: the same leg layout, defaults and ANYdrive 3.0 actuator net as ANYmal-C (ASSETS/robots/anymal.py:59-160);
+# the three differ in their USD geometry and masses, which live on the simulator side of the boundary
+ANYMAL_B_CFG = ANYMAL_C_CFG.copy()
+ANYMAL_D_CFG = ANYMAL_C_CFG.copy()
+
+
+def _unitree_quadruped(base_body, init_z, effort, velocity):
+    """A1 / Go2 (ASSETS/robots/unitree.py:49-97,138-176): Go1's joint layout driven by a DC-motor model."""
+    return ArticulationCfg(
+        joint_names=[f"{l}_{j}_joint" for j in ("hip", "thigh", "calf") for l in _GO1_LEGS],
+        body_names=[base_body] + [f"{l}_{b}" for b in ("hip", "thigh", "calf", "foot") for l in _GO1_LEGS],
+        init_pos=(0.0, 0.0, init_z),
+        joint_pos={".*L_hip_joint": 0.1, ".*R_hip_joint": -0.1, "F[L,R]_thigh_joint": 0.8, "R[L,R]_thigh_joint": 1.0,
+                   ".*_calf_joint": -1.5},
+        joint_pos_limits={".*_hip_joint": (-0.863, 0.863), ".*_thigh_joint": (-0.686, 4.501), ".*_calf_joint": (-2.818, -0.888)},
+        actuators={"base_legs": DCMotorCfg(joint_names_expr=[".*_hip_joint", ".*_thigh_joint", ".*_calf_joint"],
+                                           effort_limit=effort, saturation_effort=effort, velocity_limit=velocity,
+                                           stiffness=25.0, damping=0.5, friction=0.0)},
+        soft_joint_pos_limit_factor=0.9)
+
+
+UNITREE_A1_CFG = _unitree_quadruped("trunk", 0.42, 33.5, 21.0)
+UNITREE_GO2_CFG = _unitree_quadruped("base", 0.4, 23.5, 30.0)
+
 _H1_JOINTS = ["left_hip_yaw", "right_hip_yaw", "torso", "left_hip_roll", "right_hip_roll", "left_shoulder_pitch",
               "right_shoulder_pitch", "left_hip_pitch", "right_hip_pitch", "left_shoulder_roll", "right_shoulder_roll",
               "left_knee", "right_knee", "left_shoulder_yaw", "right_shoulder_yaw", "left_ankle", "right_ankle",

@@ -7,7 +7,8 @@ import copy
 import math
 from dataclasses import dataclass, field
 
-from ..assets import ANYMAL_C_CFG, H1_MINIMAL_CFG, UNITREE_GO1_CFG
+from ..assets import (ANYMAL_B_CFG, ANYMAL_C_CFG, ANYMAL_D_CFG, H1_MINIMAL_CFG, UNITREE_A1_CFG, UNITREE_GO1_CFG,
+                      UNITREE_GO2_CFG)
 from ..envs import mdp
 from ..envs.cfg import (ContactSensorCfg, GridPatternCfg, ManagerBasedRLEnvCfg, RayCasterCfg, SceneCfg, SimCfg,
                         TerrainImporterCfg)
@@ -166,8 +167,64 @@ def AnymalCFlatEnvCfg() -> ManagerBasedRLEnvCfg:
 
 def UnitreeGo1RoughEnvCfg() -> ManagerBasedRLEnvCfg:
     """config/go1/rough_env_cfg.py:17-60 (Isaac-Velocity-Rough-Unitree-Go1-v0)."""
-    cfg = LocomotionVelocityRoughEnvCfg(UNITREE_GO1_CFG.replace())
-    cfg.scene.height_scanner.prim_path = "{ENV_REGEX_NS}/Robot/trunk"
+    return _unitree_rough(UNITREE_GO1_CFG, "trunk")
+
+
+def UnitreeA1RoughEnvCfg() -> ManagerBasedRLEnvCfg:
+    """config/a1/rough_env_cfg.py:18-61 (Isaac-Velocity-Rough-Unitree-A1-v0): Go1's overrides on the A1 (DC-motor actuators)."""
+    return _unitree_rough(UNITREE_A1_CFG, "trunk")
+
+
+def UnitreeGo2RoughEnvCfg() -> ManagerBasedRLEnvCfg:
+    """config/go2/rough_env_cfg.py:18-61 (Isaac-Velocity-Rough-Unitree-Go2-v0): base body "base"."""
+    return _unitree_rough(UNITREE_GO2_CFG, "base")
+
+
+def AnymalBRoughEnvCfg() -> ManagerBasedRLEnvCfg:
+    """config/anymal_b/rough_env_cfg.py:17-23."""
+    return LocomotionVelocityRoughEnvCfg(ANYMAL_B_CFG.replace())
+
+
+def AnymalDRoughEnvCfg() -> ManagerBasedRLEnvCfg:
+    """config/anymal_d/rough_env_cfg.py:17-23."""
+    return LocomotionVelocityRoughEnvCfg(ANYMAL_D_CFG.replace())
+
+
+def _unitree_flat(cfg):
+    """config/{a1,go1,go2}/flat_env_cfg.py:12-30: as `_flatten`, with the Unitree reward weights."""
+    cfg = _flatten(cfg)
+    cfg.rewards.flat_orientation_l2.weight = -2.5
+    cfg.rewards.feet_air_time.weight = 0.25
+    cfg.rewards.dof_torques_l2.weight = -0.0002   # the rough value: the Unitree flat cfgs do not touch it
+    return cfg
+
+
+def UnitreeGo1FlatEnvCfg(): return _unitree_flat(UnitreeGo1RoughEnvCfg())      # noqa: E704
+def UnitreeA1FlatEnvCfg(): return _unitree_flat(UnitreeA1RoughEnvCfg())        # noqa: E704
+def UnitreeGo2FlatEnvCfg(): return _unitree_flat(UnitreeGo2RoughEnvCfg())      # noqa: E704
+def AnymalBFlatEnvCfg(): return _flatten(AnymalBRoughEnvCfg())                 # noqa: E704
+def AnymalDFlatEnvCfg(): return _flatten(AnymalDRoughEnvCfg())                 # noqa: E704
+
+
+def play(cfg: ManagerBasedRLEnvCfg) -> ManagerBasedRLEnvCfg:
+    """The `*_PLAY` variant every config package defines the same way (e.g. config/anymal_c/rough_env_cfg.py:27-47): 50 envs,
+    a 5 x 5 terrain without curriculum, spawn on any level, no observation corruption, no pushes."""
+    cfg.scene.num_envs = 50
+    cfg.scene.env_spacing = 2.5
+    if cfg.scene.terrain is not None:
+        cfg.scene.terrain.max_init_terrain_level = None
+        gen = getattr(cfg.scene.terrain, "terrain_generator", None)
+        if gen is not None:
+            gen.num_rows, gen.num_cols, gen.curriculum = 5, 5, False
+    cfg.observations.policy._group.enable_corruption = False
+    cfg.events.base_external_force_torque = None
+    cfg.events.push_robot = None
+    return cfg
+
+
+def _unitree_rough(robot, base_body) -> ManagerBasedRLEnvCfg:
+    cfg = LocomotionVelocityRoughEnvCfg(robot.replace())
+    cfg.scene.height_scanner.prim_path = "{ENV_REGEX_NS}/Robot/" + base_body
     gen = cfg.scene.terrain.terrain_generator
     gen.sub_terrains["boxes"].grid_height_range = (0.025, 0.1)
     gen.sub_terrains["random_rough"].noise_range = (0.01, 0.06)
@@ -175,8 +232,8 @@ def UnitreeGo1RoughEnvCfg() -> ManagerBasedRLEnvCfg:
     cfg.actions.joint_pos.scale = 0.25
     cfg.events.push_robot = None
     cfg.events.add_base_mass.params["mass_distribution_params"] = (-1.0, 3.0)
-    cfg.events.add_base_mass.params["asset_cfg"].body_names = "trunk"
-    cfg.events.base_external_force_torque.params["asset_cfg"].body_names = "trunk"
+    cfg.events.add_base_mass.params["asset_cfg"].body_names = base_body
+    cfg.events.base_external_force_torque.params["asset_cfg"].body_names = base_body
     cfg.events.reset_robot_joints.params["position_range"] = (1.0, 1.0)
     cfg.events.reset_base.params = {"pose_range": {"x": (-0.5, 0.5), "y": (-0.5, 0.5), "yaw": (-3.14, 3.14)},
                                     "velocity_range": {k: (0.0, 0.0) for k in ("x", "y", "z", "roll", "pitch", "yaw")}}
@@ -187,7 +244,7 @@ def UnitreeGo1RoughEnvCfg() -> ManagerBasedRLEnvCfg:
     cfg.rewards.track_lin_vel_xy_exp.weight = 1.5
     cfg.rewards.track_ang_vel_z_exp.weight = 0.75
     cfg.rewards.dof_acc_l2.weight = -2.5e-7
-    cfg.terminations.base_contact.params["sensor_cfg"].body_names = "trunk"
+    cfg.terminations.base_contact.params["sensor_cfg"].body_names = base_body
     return cfg
 
 
