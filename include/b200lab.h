@@ -152,7 +152,8 @@ enum B200LabActuatorKind {
   B200LAB_ACT_DC_MOTOR = 3,   /* actuator_pd.py:264-286 */
   B200LAB_ACT_NET_LSTM = 4,   /* LAB/actuators/actuator_net.py:76-99 */
   B200LAB_ACT_NET_MLP = 5,    /* actuator_net.py:147-189 */
-  B200LAB_ACT_DELAYED_PD = 6  /* actuator_pd.py:289-347: IdealPD behind a per-env command delay (DelayBuffer) */
+  B200LAB_ACT_DELAYED_PD = 6, /* actuator_pd.py:289-347: IdealPD behind a per-env command delay (DelayBuffer) */
+  B200LAB_ACT_REMOTIZED_PD = 7 /* actuator_pd.py:349-416: DelayedPD + torque clamp to an angle-dependent limit (lookup table) */
 };
 
 /* One actuator group (Articulation.actuators[name], LAB/assets/articulation/articulation.py:1432-1469).
@@ -196,6 +197,12 @@ typedef struct B200LabActuatorGroup {
   float* delay_ring;           /* [N, Jg, max_delay+1, 3] */
   int32_t* delay_count;        /* [N, Jg] */
   int32_t* delay_lag;          /* [N] */
+  /* RemotizedPD: |applied torque| <= y(joint_pos), y piecewise linear through (lookup_x[i], lookup_y[i]), i < lookup_n,
+   * x ascending, zero-order hold outside (LAB/utils/interpolation/linear_interpolation.py:53-77) */
+  int32_t lookup_n;
+  int32_t _pad4;
+  const float* lookup_x;
+  const float* lookup_y;
 } B200LabActuatorGroup;
 
 /* ------------------------------------------------------------------------------------------------

@@ -1,5 +1,5 @@
 """Actuator cfg classes with the reference's names and fields (LAB/actuators/actuator_cfg.py): ImplicitActuatorCfg,
-IdealPDActuatorCfg, DCMotorCfg, DelayedPDActuatorCfg, ActuatorNetLSTMCfg, ActuatorNetMLPCfg.  The models themselves are fused into
+IdealPDActuatorCfg, DCMotorCfg, DelayedPDActuatorCfg, RemotizedPDActuatorCfg, ActuatorNetLSTMCfg, ActuatorNetMLPCfg.  The models themselves are fused into
 `substep_pre` (csrc/mdp.cu); `network_file` may be a TorchScript path or an in-memory module."""
 from __future__ import annotations
 
@@ -42,6 +42,15 @@ class DelayedPDActuatorCfg(IdealPDActuatorCfg):
     min_delay: int = 0
     max_delay: int = 0
     kind: str = "delayed_pd"
+
+
+@dataclass
+class RemotizedPDActuatorCfg(DelayedPDActuatorCfg):
+    """DelayedPD whose output torque is clamped to an angle-dependent limit interpolated from `joint_parameter_lookup`
+    [n, 3] = (joint angle, transmission ratio, max torque); the box effort / velocity limits are removed
+    (LAB/actuators/actuator_cfg.py:261-277, actuator_pd.py:349-416)."""
+    joint_parameter_lookup: list = None
+    kind: str = "remotized_pd"
 
 
 @dataclass

@@ -527,7 +527,7 @@ __device__ __noinline__ void actuator_eval(const Env* __restrict__ e, const floa
                                               float q_t, float qd_t, float ff, float& computed, float& applied) {
   const int N = e->N;
   const B200LabActuatorGroup& g = e->act[e->joint_group[j]];
-  if (g.kind == B200LAB_ACT_DELAYED_PD) {
+  if (g.kind == B200LAB_ACT_DELAYED_PD || g.kind == B200LAB_ACT_REMOTIZED_PD) {
     // DelayBuffer.compute on the three set-points (actuator_pd.py:336-344, delay_buffer.py:150-176): push, then read the
     // row pushed `lag` steps ago (capped at what has been pushed since the reset; the first push fills the ring)
     const int L = g.max_delay + 1;
@@ -550,12 +550,22 @@ __device__ __noinline__ void actuator_eval(const Env* __restrict__ e, const floa
   float err_p = q_t - q, err_v = qd_t - qd;
   float elim = g.effort_limit[j];
   if (g.kind == B200LAB_ACT_IMPLICIT || g.kind == B200LAB_ACT_IDEAL_PD || g.kind == B200LAB_ACT_DC_MOTOR ||
-      g.kind == B200LAB_ACT_DELAYED_PD) {
+      g.kind == B200LAB_ACT_DELAYED_PD || g.kind == B200LAB_ACT_REMOTIZED_PD) {
     computed = (g.stiffness[j] * err_p + g.damping[j] * err_v) + ff;  // actuator_pd.py:136 / :190
     if (g.kind == B200LAB_ACT_DC_MOTOR)
       applied = dc_motor_clip(computed, qd, g.saturation_effort, g.velocity_limit[j], elim);
     else
       applied = fminf(fmaxf(computed, -elim), elim);  // actuator_base.py:309-318
+    if (g.kind == B200LAB_ACT_REMOTIZED_PD) {
+      // LinearInterpolation.compute(joint_pos): samples below q -> bracket -> weight, zero-order hold outside the table
+      int ns = 0;
+      for (int i = 0; i < g.lookup_n; ++i) ns += g.lookup_x[i] < q ? 1 : 0;
+      const int lo = max(ns - 1, 0), hi = min(ns, g.lookup_n - 1);
+      const float xl = g.lookup_x[lo], xh = g.lookup_x[hi], yl = g.lookup_y[lo], yh = g.lookup_y[hi];
+      const float w = hi == lo ? 0.0f : (q - xl) / (xh - xl);
+      const float lim = yl + w * (yh - yl);
+      applied = fminf(fmaxf(applied, -lim), lim);   // actuator_pd.py:411-414
+    }
   } else if (g.kind == B200LAB_ACT_NET_LSTM) {
     int64_t rows = (int64_t)N * g.group_joints;
     int64_t row = (int64_t)n * g.group_joints + e->joint_local[j];
@@ -1421,7 +1431,7 @@ post_step_kernel(const __grid_constant__ Env env_param, Sim sim, int64_t step, c
           ag.mlp_pos_hist[(int64_t)n * per + k] = 0.f;
           ag.mlp_vel_hist[(int64_t)n * per + k] = 0.f;
         }
-      } else if (ag.kind == B200LAB_ACT_DELAYED_PD) {   // DelayedPDActuator.reset (actuator_pd.py:311-334)
+      } else if (ag.kind == B200LAB_ACT_DELAYED_PD || ag.kind == B200LAB_ACT_REMOTIZED_PD) {   // DelayedPDActuator.reset (actuator_pd.py:311-334)
         for (int k = lane; k < ag.group_joints; k += 32) ag.delay_count[(int64_t)n * ag.group_joints + k] = 0;
         if (lane == 0) {
           const int span = ag.max_delay - ag.min_delay + 1;

@@ -191,10 +191,19 @@ def compile_env_cfg(cfg: ManagerBasedRLEnvCfg, num_envs: int | None = None, terr
              "effort_limit": _per_joint(ac.effort_limit, names, [float("inf")] * len(ids)),
              "velocity_limit": _per_joint(ac.velocity_limit, names, [float("inf")] * len(ids)),
              "saturation_effort": getattr(ac, "saturation_effort", None)}
-        if ac.kind == "delayed_pd":
+        if ac.kind in ("delayed_pd", "remotized_pd"):
             a["min_delay"], a["max_delay"] = int(ac.min_delay), int(ac.max_delay)
             if not 0 <= a["min_delay"] <= a["max_delay"]:
                 raise ValueError(f"actuator '{name}': need 0 <= min_delay <= max_delay")
+        if ac.kind == "remotized_pd":   # actuator_pd.py:372-385: box limits removed, torque limit from the lookup table
+            a["effort_limit"] = [float("inf")] * len(ids)
+            a["velocity_limit"] = [float("inf")] * len(ids)
+            tab = np.asarray(ac.joint_parameter_lookup, dtype=np.float32).reshape(-1, 3)
+            if tab.shape[0] == 0:
+                raise ValueError("Input tensor x is empty!")                              # linear_interpolation.py:46
+            if np.any(tab[1:, 0] < tab[:-1, 0]):
+                raise ValueError("Input tensor x is not sorted in ascending order!")     # linear_interpolation.py:50
+            a["lookup_angle"], a["lookup_torque"] = tab[:, 0].copy(), tab[:, 2].copy()
         if ac.kind == "lstm":
             nf = ac.network_file
             a["lstm"] = nf if isinstance(nf, dict) else (load_lstm_net(nf) if nf else synthetic_lstm_net(seed=seed))

@@ -34,7 +34,7 @@ def _f32span_py(lo, hi):
 
 
 _ACT_KIND = {"implicit": "B200LAB_ACT_IMPLICIT", "ideal_pd": "B200LAB_ACT_IDEAL_PD", "dc_motor": "B200LAB_ACT_DC_MOTOR",
-             "delayed_pd": "B200LAB_ACT_DELAYED_PD",
+             "delayed_pd": "B200LAB_ACT_DELAYED_PD", "remotized_pd": "B200LAB_ACT_REMOTIZED_PD",
              "lstm": "B200LAB_ACT_NET_LSTM", "mlp": "B200LAB_ACT_NET_MLP"}
 _MLP_ACT = {"softsign": 0, "elu": 1, "relu": 2, "tanh": 3}
 _KEYS6 = ("x", "y", "z", "roll", "pitch", "yaw")
@@ -180,13 +180,16 @@ class FusedEnv:
                 g.mlp_torque_scale = float(net["torque_scale"])
                 stt["pos_hist"], stt["vel_hist"] = z(N, hist, Jg), z(N, hist, Jg)
                 g.mlp_pos_hist, g.mlp_vel_hist = p(stt["pos_hist"]), p(stt["vel_hist"])
-            elif act["kind"] == "delayed_pd":
+            elif act["kind"] in ("delayed_pd", "remotized_pd"):
                 g.min_delay, g.max_delay = int(act["min_delay"]), int(act["max_delay"])
-                k = sum(1 for a_ in acts[:gi] if a_["kind"] == "delayed_pd")
+                k = sum(1 for a_ in acts[:gi] if a_["kind"] in ("delayed_pd", "remotized_pd"))
                 g.delay_u_slot = C["B200LAB_U_RESET_JOINT"] + 2 * J * max(1, len(s.get("events", {}).get("reset_joints", []))) + k
                 stt["ring"] = z(N, Jg, g.max_delay + 1, 3)
                 stt["count"], stt["lags"] = z(N, Jg, dtype=torch.int32), z(N, dtype=torch.int32)
                 g.delay_ring, g.delay_count, g.delay_lag = p(stt["ring"]), p(stt["count"]), p(stt["lags"])
+                if act["kind"] == "remotized_pd":
+                    g.lookup_n = len(act["lookup_angle"])
+                    g.lookup_x, g.lookup_y = p(const(act["lookup_angle"])), p(const(act["lookup_torque"]))
             self.act_state.append(stt)
         self._st = st
         self._finish_init(seed)
@@ -474,7 +477,7 @@ class FusedEnv:
         # --- randomness / logs
         st.seed = int(seed)
         self.n_u_reset = (C["B200LAB_U_RESET_JOINT"] + 2 * J * max(1, len(rj))
-                          + sum(1 for a_ in s["actuators"] if a_["kind"] == "delayed_pd"))
+                          + sum(1 for a_ in s["actuators"] if a_["kind"] in ("delayed_pd", "remotized_pd")))
         self.n_u_step = C["B200LAB_U_STEP_INTERVAL"] + 7 * len(pushes)
         st.n_u_reset, st.n_u_step = self.n_u_reset, self.n_u_step
         self.log_accum = z(C["B200LAB_LOG_SLOTS"], dtype=torch.float64)

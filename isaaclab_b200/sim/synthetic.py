@@ -76,7 +76,7 @@ def init_fused_state(env, init):
     for gt in getattr(env, "interval_global_time", {}).values():   # is_global_time terms: one timer, both parity slots
         gt.fill_(float(init.get("interval_global_time_left", 0.03)))
     for act, st in zip(env.spec["actuators"], env.act_state):
-        if act["kind"] == "delayed_pd":
+        if act["kind"] in ("delayed_pd", "remotized_pd"):
             st["lags"].copy_(initial_delay_lags(act, init))
 
 

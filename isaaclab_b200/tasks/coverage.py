@@ -10,7 +10,7 @@ reset events gated by min_step_count_between_reset and an interval push on one g
 actuator group; observation history (with and without noise) and the scale / clip / bias modifiers."""
 from __future__ import annotations
 
-from ..actuators import DCMotorCfg, DelayedPDActuatorCfg, IdealPDActuatorCfg
+from ..actuators import DCMotorCfg, DelayedPDActuatorCfg, IdealPDActuatorCfg, RemotizedPDActuatorCfg
 from ..envs import mdp
 from ..managers import ObservationTermCfg as ObsTerm
 from ..managers import RewardTermCfg as RewTerm
@@ -24,8 +24,12 @@ ACTUATORS = {
     "hips": dict(kind="ideal_pd", joint_names_expr=[".*F_HAA"], stiffness=40.0, damping=2.0, effort_limit=30.0, velocity_limit=7.5),
     "hips_hind": dict(kind="delayed_pd", joint_names_expr=[".*H_HAA"], stiffness=40.0, damping=2.0, effort_limit=30.0,
                       velocity_limit=7.5, min_delay=1, max_delay=3),
-    "legs": dict(kind="dc_motor", joint_names_expr=[".*HFE", ".*KFE"], stiffness={".*HFE": 60.0, ".*KFE": 50.0}, damping=3.0,
+    "legs": dict(kind="dc_motor", joint_names_expr=[".*HFE", ".*F_KFE"], stiffness={".*HFE": 60.0, ".*KFE": 50.0}, damping=3.0,
                  effort_limit=80.0, velocity_limit=7.5, saturation_effort=120.0),
+    # angle-dependent torque limit: (joint angle, transmission ratio, max torque) samples; the targets saturate it often
+    "knees_hind": dict(kind="remotized_pd", joint_names_expr=[".*H_KFE"], stiffness=50.0, damping=3.0, min_delay=0, max_delay=2,
+                       joint_parameter_lookup=[[-1.5, 1.0, 6.0], [-0.5, 1.1, 14.0], [0.4, 1.2, 25.0], [0.9, 1.2, 18.0],
+                                               [1.6, 1.0, 9.0]]),
 }
 ACTION_CLIP = {".*HAA": (-0.8, 0.8), ".*HFE": (-1.5, 1.5), ".*KFE": (-2.0, 1.0)}
 REWARDS = {
@@ -64,7 +68,8 @@ def OpcodeCoverageEnvCfg():
     acts = {}
     for name, a in ACTUATORS.items():
         a = dict(a)
-        cls = {"ideal_pd": IdealPDActuatorCfg, "dc_motor": DCMotorCfg, "delayed_pd": DelayedPDActuatorCfg}[a.pop("kind")]
+        cls = {"ideal_pd": IdealPDActuatorCfg, "dc_motor": DCMotorCfg, "delayed_pd": DelayedPDActuatorCfg,
+               "remotized_pd": RemotizedPDActuatorCfg}[a.pop("kind")]
         acts[name] = cls(**a)
     cfg.scene.robot.actuators = acts
     cfg.actions.joint_pos.clip = dict(ACTION_CLIP)

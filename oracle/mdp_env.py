@@ -28,13 +28,27 @@ def _t(x, dtype=F32):
     return x.clone().to(dtype) if isinstance(x, torch.Tensor) else torch.tensor(x, dtype=dtype)
 
 
+DELAYED_KINDS = ("delayed_pd", "remotized_pd")
+
+
+def linear_interpolation(x, y, q):
+    """LAB/utils/interpolation/linear_interpolation.py:53-77: piecewise-linear y(x) at q, zero-order hold outside."""
+    q1 = q.reshape(-1)
+    n_smaller = torch.sum(x.unsqueeze(1) < q1.unsqueeze(0), dim=0, dtype=torch.int64)
+    lo = torch.clamp(n_smaller - 1, min=0)
+    hi = torch.clamp(n_smaller, max=x.numel() - 1)
+    w = (q1 - x[lo]) / (x[hi] - x[lo])
+    w[hi == lo] = 0.0
+    return (y[lo] + w * (y[hi] - y[lo])).reshape(q.shape)
+
+
 def u_reset_delay(spec):
     """First of the per-group time-lag slots of the DelayedPD actuator groups (one draw per group and reset)."""
     return U_RESET_JOINT + 2 * spec["J"] * max(1, len(spec.get("events", {}).get("reset_joints", [])))
 
 
 def n_u_reset(spec):
-    return u_reset_delay(spec) + sum(1 for a in spec["actuators"] if a["kind"] == "delayed_pd")
+    return u_reset_delay(spec) + sum(1 for a in spec["actuators"] if a["kind"] in DELAYED_KINDS)
 
 
 def n_u_step(spec):
@@ -166,7 +180,7 @@ class OracleEnv:
             elif a["kind"] == "mlp":
                 hist = max(a["mlp"]["input_idx"]) + 1
                 st["pos_hist"], st["vel_hist"] = z(N, hist, Jg), z(N, hist, Jg)
-            elif a["kind"] == "delayed_pd":   # DelayBuffer x3 with shared lags (actuator_pd.py:303-330, delay_buffer.py)
+            elif a["kind"] in DELAYED_KINDS:   # DelayBuffer x3 with shared lags (actuator_pd.py:303-330, delay_buffer.py)
                 st["ring"] = Ring(a["max_delay"] + 1, N)
                 st["lags"] = torch.zeros(N, dtype=torch.int64)
             self.act_state.append(st)
@@ -272,11 +286,11 @@ class OracleEnv:
             q_t, qd_t, ff = self.joint_pos_target[:, j], self.joint_vel_target[:, j], self.joint_effort_target[:, j]
             elim = _t(act["effort_limit"]).expand(len(j))
             kind = act["kind"]
-            if kind == "delayed_pd":   # the three set-points go through the delay line, then IdealPD (actuator_pd.py:336-347)
+            if kind in DELAYED_KINDS:   # the three set-points go through the delay line, then IdealPD (actuator_pd.py:336-347)
                 st["ring"].append(torch.stack([q_t, qd_t, ff], dim=-1))
                 d3 = st["ring"].lagged(st["lags"])
                 q_t, qd_t, ff = d3[..., 0], d3[..., 1], d3[..., 2]
-            if kind in ("implicit", "ideal_pd", "dc_motor", "delayed_pd"):
+            if kind in ("implicit", "ideal_pd", "dc_motor") + DELAYED_KINDS:
                 err_p, err_v = q_t - q, qd_t - qd
                 computed = _t(act["stiffness"]) * err_p + _t(act["damping"]) * err_v + ff
             elif kind == "lstm":
@@ -285,8 +299,11 @@ class OracleEnv:
                 computed = self._mlp(act["mlp"], st, q_t - q, qd)
             else:
                 raise ValueError(kind)
-            if kind in ("implicit", "ideal_pd", "delayed_pd"):
+            if kind in ("implicit", "ideal_pd") + DELAYED_KINDS:
                 applied = torch.clip(computed, min=-elim, max=elim)  # actuator_base.py:309-318
+                if kind == "remotized_pd":   # angle-dependent limit at the CURRENT joint position (actuator_pd.py:405-416)
+                    lim = linear_interpolation(_t(act["lookup_angle"]), _t(act["lookup_torque"]), q)
+                    applied = torch.clamp(applied, min=-lim, max=lim)
             else:  # DCMotor._clip_effort (actuator_pd.py:276-286)
                 sat = float(act["saturation_effort"])
                 vlim = _t(act["velocity_limit"]).expand(len(j))
@@ -598,8 +615,8 @@ class OracleEnv:
             elif act["kind"] == "mlp":
                 st["pos_hist"][ids] = 0.0
                 st["vel_hist"][ids] = 0.0
-            elif act["kind"] == "delayed_pd":   # new lag = randint(min_delay, max_delay + 1), buffers cleared (actuator_pd.py:311-334)
-                k = [a_ for a_ in s["actuators"] if a_["kind"] == "delayed_pd"].index(act)
+            elif act["kind"] in DELAYED_KINDS:   # new lag = randint(min_delay, max_delay + 1), buffers cleared (actuator_pd.py:311-334)
+                k = [a_ for a_ in s["actuators"] if a_["kind"] in DELAYED_KINDS].index(act)
                 span = act["max_delay"] - act["min_delay"] + 1
                 lag = act["min_delay"] + torch.clamp((ur[:, u_reset_delay(s) + k] * span).to(torch.int64), max=span - 1)
                 st["lags"][ids] = lag

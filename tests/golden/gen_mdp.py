@@ -382,7 +382,7 @@ def layout_uniforms(draws, spec, N, filler):
             u_r[ids, omdp.U_RESET_CURRICULUM] = u
         elif f == "reset" and d["extra"] is not None and d["extra"][0] == "randint":
             # DelayedPDActuator.reset (actuator_pd.py:320-326): one lag per env, groups in articulation order
-            n_delayed = sum(1 for a_ in spec["actuators"] if a_["kind"] == "delayed_pd")
+            n_delayed = sum(1 for a_ in spec["actuators"] if a_["kind"] in ("delayed_pd", "remotized_pd"))
             kk = seen.get("delay_total", 0)
             seen["delay_total"] = kk + 1
             u_r[ids, omdp.u_reset_delay(spec) + kk % n_delayed] = u
@@ -614,7 +614,7 @@ def coverage_reference_cfg():
     the reference's OWN IdealPDActuatorCfg / DCMotorCfg classes and mdp functions plugged in, from the same data tables."""
     import importlib
     from isaaclab_b200.tasks import coverage as cov
-    from isaaclab.actuators import DCMotorCfg, DelayedPDActuatorCfg, IdealPDActuatorCfg
+    from isaaclab.actuators import DCMotorCfg, DelayedPDActuatorCfg, IdealPDActuatorCfg, RemotizedPDActuatorCfg
     from isaaclab.utils import modifiers as rmod
     import isaaclab.envs.mdp as rmdp
     from isaaclab.managers import ObservationTermCfg, RewardTermCfg, SceneEntityCfg, TerminationTermCfg
@@ -624,7 +624,8 @@ def coverage_reference_cfg():
     acts = {}
     for name, a in cov.ACTUATORS.items():
         a = dict(a)
-        cls = {"ideal_pd": IdealPDActuatorCfg, "dc_motor": DCMotorCfg, "delayed_pd": DelayedPDActuatorCfg}[a.pop("kind")]
+        cls = {"ideal_pd": IdealPDActuatorCfg, "dc_motor": DCMotorCfg, "delayed_pd": DelayedPDActuatorCfg,
+               "remotized_pd": RemotizedPDActuatorCfg}[a.pop("kind")]
         acts[name] = cls(**a)
     cfg.scene.robot = cfg.scene.robot.replace(actuators=acts)
     cfg.actions.joint_pos.clip = dict(cov.ACTION_CLIP)
@@ -707,7 +708,7 @@ def build_reference_env(task, spec, slabs, init, tmpdir, wrap=False):
         term.time_left[:] = init["cmd_time_left"]
     from isaaclab_b200.sim.synthetic import initial_delay_lags
     for (name, actuator), aspec in zip(env.scene["robot"].actuators.items(), spec["actuators"]):
-        if aspec["kind"] == "delayed_pd":
+        if aspec["kind"] in ("delayed_pd", "remotized_pd"):
             lags = initial_delay_lags(aspec, init).to(torch.int)
             for buf in (actuator.positions_delay_buffer, actuator.velocities_delay_buffer, actuator.efforts_delay_buffer):
                 buf.set_time_lag(lags)

@@ -51,7 +51,7 @@ def init_oracle_state(env, init):
         gt[:] = init.get("interval_global_time_left", 0.03)
     from isaaclab_b200.sim.synthetic import initial_delay_lags
     for act, st in zip(env.spec["actuators"], env.act_state):
-        if act["kind"] == "delayed_pd":
+        if act["kind"] in ("delayed_pd", "remotized_pd"):
             st["lags"][:] = initial_delay_lags(act, init)
 
 
