@@ -166,3 +166,56 @@ def test_raycast_mesh_known_answers():
     assert torch.isinf(h[2]).all() and torch.isinf(h[3]).all() and torch.isinf(h[4]).all()
     assert torch.isinf(h[5]).all(), "a horizontal ray between the two layers hits neither"
     assert abs(abs(nrm.cpu()[0, 2].item()) - 1.0) < 1e-6
+
+
+def test_ray_caster_camera_depth_images_match_brute_force():
+    """LAB/sensors/ray_caster/ray_caster_camera.py:257-318 on the mesh kernel: tilted pinhole cameras over the terrain; depth
+    along the optical axis, ray length and normals against the oracle's brute-force query pushed through the same formulas."""
+    from isaaclab_b200.sensors import patterns as P
+    from isaaclab_b200.sensors.ray_caster import WarpFreeMesh
+    from isaaclab_b200.sensors.ray_caster_camera import RayCasterCamera, RayCasterCameraCfg
+    from isaaclab_b200.utils import math as M
+    from oracle import raycast as orc
+    from tests.mdp_common import small_terrain
+    V, F = small_terrain().terrain_mesh
+    mesh = WarpFreeMesh(V, F)
+    N = 6
+    g = torch.Generator().manual_seed(4)
+    cfg = RayCasterCameraCfg(pattern_cfg=P.PinholeCameraPatternCfg(width=16, height=12, focal_length=24.0, horizontal_aperture=36.0),
+                             data_types=["distance_to_image_plane", "distance_to_camera", "normals"], max_distance=6.0,
+                             depth_clipping_behavior="max")
+    cam = RayCasterCamera(cfg, mesh, N)
+    pos = torch.stack([torch.rand(N, generator=g) * 6 - 3, torch.rand(N, generator=g) * 6 - 3, 2.0 + torch.rand(N, generator=g)], dim=1)
+    # cameras looking forward and down by 30-70 degrees, random heading (rotation about y, then about z)
+    pitch, yaw = 0.5 + 0.7 * torch.rand(N, generator=g), 6.28 * torch.rand(N, generator=g)
+    qy = torch.stack([torch.cos(pitch / 2), torch.zeros(N), torch.sin(pitch / 2), torch.zeros(N)], dim=1)
+    qz = torch.stack([torch.cos(yaw / 2), torch.zeros(N), torch.zeros(N), torch.sin(yaw / 2)], dim=1)
+
+    def qmul(a, b):
+        w1, x1, y1, z1 = a.unbind(-1)
+        w2, x2, y2, z2 = b.unbind(-1)
+        return torch.stack([w1 * w2 - x1 * x2 - y1 * y2 - z1 * z2, w1 * x2 + x1 * w2 + y1 * z2 - z1 * y2,
+                            w1 * y2 - x1 * z2 + y1 * w2 + z1 * x2, w1 * z2 + x1 * y2 - y1 * x2 + z1 * w2], dim=-1)
+
+    quat = qmul(qz, qy)
+    out = cam.update(pos.cuda(), quat.cuda())
+    assert out["distance_to_image_plane"].shape == (N, 12, 16, 1) and out["normals"].shape == (N, 12, 16, 3)
+    # the same images from the brute-force closest hit
+    R = cam.num_rays
+    q = quat.unsqueeze(1).expand(N, R, 4)
+    starts = M.quat_apply(q, cam.ray_starts.cpu()) + pos.unsqueeze(1)
+    dirs = M.quat_apply(q, cam.ray_directions.cpu())
+    _, t, _ = orc.Mesh(V, F).raycast(starts.reshape(-1, 3), dirs.reshape(-1, 3), max_dist=1e6, return_t=True)
+    t = t.float().view(N, R)
+    assert torch.isfinite(t).float().mean() > 0.5
+    want_cam = torch.clip(t, max=6.0)
+    q_inv = torch.cat([quat[:, :1], -quat[:, 1:]], dim=1).unsqueeze(1).expand(N, R, 4)
+    want_plane = torch.clip(M.quat_apply(q_inv, t.unsqueeze(-1) * dirs)[..., 0], max=6.0)
+    want_plane[torch.isnan(want_plane)] = 6.0
+    torch.testing.assert_close(out["distance_to_camera"].cpu().view(N, R), want_cam, rtol=1e-4, atol=2e-4)
+    torch.testing.assert_close(out["distance_to_image_plane"].cpu().view(N, R), want_plane, rtol=1e-4, atol=2e-4)
+    hit = torch.isfinite(t)
+    nrm = out["normals"].cpu().view(N, R, 3)
+    assert torch.allclose(nrm[hit].norm(dim=-1), torch.ones(int(hit.sum())), atol=1e-4)
+    with pytest.raises(ValueError, match="does not support"):
+        RayCasterCamera(RayCasterCameraCfg(pattern_cfg=cfg.pattern_cfg, data_types=["rgb"]), mesh, N)
