@@ -415,10 +415,16 @@ __device__ __forceinline__ float mlp_act_fast(float x, int kind) {
 // conflict-free).  The loop over output neurons is ROLLED -- fully unrolled the net is ~70 KB of code and the kernel
 // stalls on instruction fetch (ncu: no_instruction 5.8 per issue, issue-active 29 %) -- so a layer's outputs are parked in
 // `sb` and re-read into registers for the next layer's unrolled 128-bit-weight inner products.
+#ifndef B200LAB_MLP_NEURONS
+#define B200LAB_MLP_NEURONS 4
+#endif
+constexpr int kMlpNeurons = B200LAB_MLP_NEURONS;
+
 template <class Net>
 __device__ __forceinline__ float mlp_const(const float* w, float* sb, int stride, const float (&in)[Net::kIn], int act) {
   constexpr int IN = Net::kIn, H = Net::kH, NH = Net::kNH;
   static_assert(H % 4 == 0 && (IN * H + H) % 4 == 0, "128-bit weight rows");
+  static_assert(H % kMlpNeurons == 0, "neurons per trip must divide the layer width");
   float a[H];
 #pragma unroll 1
   for (int o = 0; o < H; ++o) {
@@ -432,15 +438,29 @@ __device__ __forceinline__ float mlp_const(const float* w, float* sb, int stride
     const float* wl = w + (IN * H + H) + (l - 1) * (H * H + H);
 #pragma unroll
     for (int i = 0; i < H; ++i) a[i] = sb[i * stride];
+    // kMlpNeurons output neurons per trip of the rolled loop: their inner products are independent FMA chains (each in
+    // the reference order, i ascending), so the 4-cycle dependent-issue latency of one chain is covered by the others
 #pragma unroll 1
-    for (int o = 0; o < H; ++o) {
-      float acc = lds1(wl + H * H + o);
+    for (int o = 0; o < H; o += kMlpNeurons) {
+      float acc[kMlpNeurons];
+#pragma unroll
+      for (int u = 0; u < kMlpNeurons; ++u) acc[u] = lds1(wl + H * H + o + u);
 #pragma unroll
       for (int i = 0; i < H; i += 4) {
-        const float4 w4 = lds4(wl + o * H + i);
-        acc = fmaf(w4.x, a[i], acc); acc = fmaf(w4.y, a[i + 1], acc); acc = fmaf(w4.z, a[i + 2], acc); acc = fmaf(w4.w, a[i + 3], acc);
+        float4 w4[kMlpNeurons];
+#pragma unroll
+        for (int u = 0; u < kMlpNeurons; ++u) w4[u] = lds4(wl + (o + u) * H + i);
+#pragma unroll
+        for (int u = 0; u < kMlpNeurons; ++u) acc[u] = fmaf(w4[u].x, a[i], acc[u]);
+#pragma unroll
+        for (int u = 0; u < kMlpNeurons; ++u) acc[u] = fmaf(w4[u].y, a[i + 1], acc[u]);
+#pragma unroll
+        for (int u = 0; u < kMlpNeurons; ++u) acc[u] = fmaf(w4[u].z, a[i + 2], acc[u]);
+#pragma unroll
+        for (int u = 0; u < kMlpNeurons; ++u) acc[u] = fmaf(w4[u].w, a[i + 3], acc[u]);
       }
-      sb[o * stride] = mlp_act_fast(acc, act);
+#pragma unroll
+      for (int u = 0; u < kMlpNeurons; ++u) sb[(o + u) * stride] = mlp_act_fast(acc[u], act);
     }
   }
 #pragma unroll

@@ -20,6 +20,7 @@ def main():
     ap.add_argument("--impl", default="0,1")
     ap.add_argument("--task", default="Isaac-Velocity-Rough-Anymal-C-v0")
     ap.add_argument("--no-hits", action="store_true")
+    ap.add_argument("--no-noise", action="store_true", help="observation corruption off (no Philox in the kernel)")
     ap.add_argument("--cell", type=float, default=0.0, help="bin-grid cell edge of the terrain mesh (0: the builder's default)")
     args = ap.parse_args()
     from isaaclab_b200 import terrains
@@ -28,6 +29,8 @@ def main():
     from isaaclab_b200.sim.synthetic import SyntheticSim, generate_slabs, init_fused_state, initial_env_state
     from isaaclab_b200.tasks import TASKS
     cfg = TASKS[args.task]()
+    if args.no_noise:
+        cfg.observations.policy._group.enable_corruption = False
     terrain = terrains.TerrainGenerator(cfg.scene.terrain.terrain_generator)
     spec = compile_env_cfg(cfg, num_envs=args.envs, terrain=terrain, seed=0)
     if args.cell > 0:
