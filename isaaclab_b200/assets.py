@@ -169,6 +169,70 @@ H1_CFG = ArticulationCfg(  # unitree.py:182-261
     })
 H1_MINIMAL_CFG = H1_CFG.copy()
 
+# Unitree G1 (ASSETS/robots/unitree.py:273-381): 37 joints -- 2 x 6 leg, torso, 2 x 5 arm, 2 x 7 hand.  The joint / body
+# ORDER of the real asset is PhysX's traversal of its USD; here it is a fixed listing (names as the cfg's regexes need them)
+_G1_SIDES = ("left", "right")
+_G1_JOINTS = ([f"{s}_{j}_joint" for j in ("hip_pitch", "hip_roll", "hip_yaw", "knee", "ankle_pitch", "ankle_roll") for s in _G1_SIDES]
+              + ["torso_joint"]
+              + [f"{s}_{j}_joint" for j in ("shoulder_pitch", "shoulder_roll", "shoulder_yaw", "elbow_pitch", "elbow_roll") for s in _G1_SIDES]
+              + [f"{s}_{j}_joint" for j in ("zero", "one", "two", "three", "four", "five", "six") for s in _G1_SIDES])
+_G1_ARM_JOINTS = [".*_shoulder_pitch_joint", ".*_shoulder_roll_joint", ".*_shoulder_yaw_joint", ".*_elbow_pitch_joint",
+                  ".*_elbow_roll_joint", ".*_five_joint", ".*_three_joint", ".*_six_joint", ".*_four_joint", ".*_zero_joint",
+                  ".*_one_joint", ".*_two_joint"]
+G1_CFG = ArticulationCfg(
+    joint_names=_G1_JOINTS, body_names=["pelvis"] + [j[:-len("_joint")] + "_link" for j in _G1_JOINTS], init_pos=(0.0, 0.0, 0.74),
+    joint_pos={".*_hip_pitch_joint": -0.20, ".*_knee_joint": 0.42, ".*_ankle_pitch_joint": -0.23, ".*_elbow_pitch_joint": 0.87,
+               "left_shoulder_roll_joint": 0.16, "left_shoulder_pitch_joint": 0.35, "right_shoulder_roll_joint": -0.16,
+               "right_shoulder_pitch_joint": 0.35, "left_one_joint": 1.0, "right_one_joint": -1.0, "left_two_joint": 0.52,
+               "right_two_joint": -0.52},
+    joint_pos_limits={".*_hip_pitch_joint": (-2.35, 3.05), ".*_hip_roll_joint": (-0.26, 2.53), ".*_hip_yaw_joint": (-2.75, 2.75),
+                      ".*_knee_joint": (-0.33, 2.54), ".*_ankle_pitch_joint": (-0.68, 0.73), ".*_ankle_roll_joint": (-0.26, 0.26),
+                      "torso_joint": (-2.62, 2.62), ".*_shoulder_pitch_joint": (-2.97, 2.79), ".*_shoulder_roll_joint": (-2.25, 2.25),
+                      ".*_shoulder_yaw_joint": (-2.62, 2.62), ".*_elbow_pitch_joint": (-0.23, 3.42),
+                      ".*_elbow_roll_joint": (-2.09, 2.09), ".*_(zero|one|two|three|four|five|six)_joint": (-1.84, 1.84)},
+    soft_joint_pos_limit_factor=0.9,
+    actuators={
+        "legs": ImplicitActuatorCfg(joint_names_expr=[".*_hip_yaw_joint", ".*_hip_roll_joint", ".*_hip_pitch_joint", ".*_knee_joint",
+                                                      "torso_joint"], effort_limit=300, velocity_limit=100.0,
+                                    stiffness={".*_hip_yaw_joint": 150.0, ".*_hip_roll_joint": 150.0, ".*_hip_pitch_joint": 200.0,
+                                               ".*_knee_joint": 200.0, "torso_joint": 200.0},
+                                    damping={".*_hip_yaw_joint": 5.0, ".*_hip_roll_joint": 5.0, ".*_hip_pitch_joint": 5.0,
+                                             ".*_knee_joint": 5.0, "torso_joint": 5.0},
+                                    armature={".*_hip_.*": 0.01, ".*_knee_joint": 0.01, "torso_joint": 0.01}),
+        "feet": ImplicitActuatorCfg(effort_limit=20, joint_names_expr=[".*_ankle_pitch_joint", ".*_ankle_roll_joint"],
+                                    stiffness=20.0, damping=2.0, armature=0.01),
+        "arms": ImplicitActuatorCfg(joint_names_expr=list(_G1_ARM_JOINTS), effort_limit=300, velocity_limit=100.0, stiffness=40.0,
+                                    damping=10.0,
+                                    armature={".*_shoulder_.*": 0.01, ".*_elbow_.*": 0.01, ".*_five_joint": 0.001,
+                                              ".*_three_joint": 0.001, ".*_six_joint": 0.001, ".*_four_joint": 0.001,
+                                              ".*_zero_joint": 0.001, ".*_one_joint": 0.001, ".*_two_joint": 0.001}),
+    })
+G1_MINIMAL_CFG = G1_CFG.copy()
+
+# Agility Cassie (ASSETS/robots/cassie.py:24-92): the 12 joints the cfg names
+_CASSIE_JOINTS = [f"{j}_{s}" for j in ("hip_abduction", "hip_rotation", "hip_flexion", "thigh_joint", "ankle_joint", "toe_joint")
+                  for s in ("left", "right")]
+CASSIE_CFG = ArticulationCfg(
+    joint_names=_CASSIE_JOINTS,
+    body_names=["pelvis"] + [f"{s}_{b}" for b in ("pelvis_abduction", "pelvis_rotation", "hip", "thigh", "shin", "toe")
+                             for s in ("left", "right")],
+    init_pos=(0.0, 0.0, 0.9),
+    joint_pos={"hip_abduction_left": 0.1, "hip_rotation_left": 0.0, "hip_flexion_left": 1.0, "thigh_joint_left": -1.8,
+               "ankle_joint_left": 1.57, "toe_joint_left": -1.57, "hip_abduction_right": -0.1, "hip_rotation_right": 0.0,
+               "hip_flexion_right": 1.0, "thigh_joint_right": -1.8, "ankle_joint_right": 1.57, "toe_joint_right": -1.57},
+    joint_pos_limits={"hip_abduction_.*": (-0.26, 0.39), "hip_rotation_.*": (-0.39, 0.39), "hip_flexion_.*": (-0.87, 1.40),
+                      "thigh_joint_.*": (-2.86, -0.65), "ankle_joint_.*": (0.87, 2.97), "toe_joint_.*": (-2.44, -0.52)},
+    soft_joint_pos_limit_factor=0.9,
+    actuators={
+        "legs": ImplicitActuatorCfg(joint_names_expr=["hip_.*", "thigh_.*", "ankle_.*"], effort_limit=200.0, velocity_limit=10.0,
+                                    stiffness={"hip_abduction.*": 100.0, "hip_rotation.*": 100.0, "hip_flexion.*": 200.0,
+                                               "thigh_joint.*": 200.0, "ankle_joint.*": 200.0},
+                                    damping={"hip_abduction.*": 3.0, "hip_rotation.*": 3.0, "hip_flexion.*": 6.0,
+                                             "thigh_joint.*": 6.0, "ankle_joint.*": 6.0}),
+        "toes": ImplicitActuatorCfg(joint_names_expr=["toe_.*"], effort_limit=20.0, velocity_limit=10.0,
+                                    stiffness={"toe_joint.*": 20.0}, damping={"toe_joint.*": 1.0}),
+    })
+
 CARTPOLE_CFG = ArticulationCfg(  # ASSETS/robots/cartpole.py
     joint_names=["slider_to_cart", "cart_to_pole"], body_names=["rail", "cart", "pole"], init_pos=(0.0, 0.0, 2.0),
     joint_pos={"slider_to_cart": 0.0, "cart_to_pole": 0.0},

@@ -1,7 +1,8 @@
 from .cartpole import CartpoleEnvCfg
 from .coverage import OpcodeCoverageEnvCfg
 from .velocity import (AnymalBFlatEnvCfg, AnymalBRoughEnvCfg, AnymalCFlatEnvCfg, AnymalCRoughEnvCfg, AnymalDFlatEnvCfg,
-                       AnymalDRoughEnvCfg, H1RoughEnvCfg, UnitreeA1FlatEnvCfg, UnitreeA1RoughEnvCfg, UnitreeGo1FlatEnvCfg,
+                       AnymalDRoughEnvCfg, CassieFlatEnvCfg, CassieRoughEnvCfg, G1FlatEnvCfg, G1RoughEnvCfg, H1FlatEnvCfg,
+                       H1RoughEnvCfg, UnitreeA1FlatEnvCfg, UnitreeA1RoughEnvCfg, UnitreeGo1FlatEnvCfg,
                        UnitreeGo1RoughEnvCfg, UnitreeGo2FlatEnvCfg, UnitreeGo2RoughEnvCfg, play)
 
 TASKS = {
@@ -20,6 +21,12 @@ TASKS = {
     "Isaac-Velocity-Flat-Unitree-Go1-v0": UnitreeGo1FlatEnvCfg,
     "Isaac-Velocity-Flat-Unitree-Go2-v0": UnitreeGo2FlatEnvCfg,
     "Isaac-Velocity-Rough-Unitree-Go2-v0": UnitreeGo2RoughEnvCfg,
+    # the other bipeds
+    "Isaac-Velocity-Flat-H1-v0": H1FlatEnvCfg,
+    "Isaac-Velocity-Flat-G1-v0": G1FlatEnvCfg,
+    "Isaac-Velocity-Rough-G1-v0": G1RoughEnvCfg,
+    "Isaac-Velocity-Flat-Cassie-v0": CassieFlatEnvCfg,
+    "Isaac-Velocity-Rough-Cassie-v0": CassieRoughEnvCfg,
     "B200-Opcode-Coverage-v0": OpcodeCoverageEnvCfg,   # synthetic: opcodes / actuator kinds the tasks above do not use
 }
 # "<id minus -v0>-Play-v0": the 50-env evaluation variant of every task above (velocity.play)

@@ -7,8 +7,8 @@ import copy
 import math
 from dataclasses import dataclass, field
 
-from ..assets import (ANYMAL_B_CFG, ANYMAL_C_CFG, ANYMAL_D_CFG, H1_MINIMAL_CFG, UNITREE_A1_CFG, UNITREE_GO1_CFG,
-                      UNITREE_GO2_CFG)
+from ..assets import (ANYMAL_B_CFG, ANYMAL_C_CFG, ANYMAL_D_CFG, CASSIE_CFG, G1_MINIMAL_CFG, H1_MINIMAL_CFG, UNITREE_A1_CFG,
+                      UNITREE_GO1_CFG, UNITREE_GO2_CFG)
 from ..envs import mdp
 from ..envs.cfg import (ContactSensorCfg, GridPatternCfg, ManagerBasedRLEnvCfg, RayCasterCfg, SceneCfg, SimCfg,
                         TerrainImporterCfg)
@@ -291,3 +291,134 @@ def H1RoughEnvCfg() -> ManagerBasedRLEnvCfg:
     cfg.commands.base_velocity.ranges.ang_vel_z = (-1.0, 1.0)
     cfg.terminations.base_contact.params["sensor_cfg"].body_names = ".*torso_link"
     return cfg
+
+
+def _flat_biped(cfg):
+    """The terrain part of config/{h1,g1,cassie}/flat_env_cfg.py."""
+    cfg.scene.terrain.terrain_type = "plane"
+    cfg.scene.terrain.terrain_generator = None
+    cfg.scene.height_scanner = None
+    cfg.observations.policy.height_scan = None
+    cfg.curriculum.terrain_levels = None
+    return cfg
+
+
+def H1FlatEnvCfg() -> ManagerBasedRLEnvCfg:
+    """config/h1/flat_env_cfg.py:12-25 (Isaac-Velocity-Flat-H1-v0)."""
+    cfg = _flat_biped(H1RoughEnvCfg())
+    cfg.rewards.feet_air_time.weight = 1.0
+    cfg.rewards.feet_air_time.params["threshold"] = 0.6
+    return cfg
+
+
+_ZERO_VEL = {k: (0.0, 0.0) for k in ("x", "y", "z", "roll", "pitch", "yaw")}
+
+
+def G1RoughEnvCfg() -> ManagerBasedRLEnvCfg:
+    """config/g1/rough_env_cfg.py:18-143 (Isaac-Velocity-Rough-G1-v0): 37 joints, H1's reward structure plus the fingers."""
+    cfg = LocomotionVelocityRoughEnvCfg(G1_MINIMAL_CFG.replace())
+    r = cfg.rewards
+    # G1Rewards(RewardsCfg): overridden fields keep their position, new fields are appended in class-body order
+    r.track_lin_vel_xy_exp = RewTerm(func=mdp.track_lin_vel_xy_yaw_frame_exp, weight=1.0,
+                                     params={"command_name": "base_velocity", "std": 0.5})
+    r.track_ang_vel_z_exp = RewTerm(func=mdp.track_ang_vel_z_world_exp, weight=2.0,
+                                    params={"command_name": "base_velocity", "std": 0.5})
+    r.feet_air_time = RewTerm(func=mdp.feet_air_time_positive_biped, weight=0.25,
+                              params={"command_name": "base_velocity",
+                                      "sensor_cfg": SceneEntityCfg("contact_forces", body_names=".*_ankle_roll_link"),
+                                      "threshold": 0.4})
+    r.dof_pos_limits = RewTerm(func=mdp.joint_pos_limits, weight=-1.0,
+                               params={"asset_cfg": SceneEntityCfg("robot", joint_names=[".*_ankle_pitch_joint", ".*_ankle_roll_joint"])})
+    r.termination_penalty = RewTerm(func=mdp.is_terminated, weight=-200.0)
+    r.feet_slide = RewTerm(func=mdp.feet_slide, weight=-0.1,
+                           params={"sensor_cfg": SceneEntityCfg("contact_forces", body_names=".*_ankle_roll_link"),
+                                   "asset_cfg": SceneEntityCfg("robot", body_names=".*_ankle_roll_link")})
+    r.joint_deviation_hip = RewTerm(func=mdp.joint_deviation_l1, weight=-0.1,
+                                    params={"asset_cfg": SceneEntityCfg("robot", joint_names=[".*_hip_yaw_joint", ".*_hip_roll_joint"])})
+    r.joint_deviation_arms = RewTerm(func=mdp.joint_deviation_l1, weight=-0.1, params={"asset_cfg": SceneEntityCfg(
+        "robot", joint_names=[".*_shoulder_pitch_joint", ".*_shoulder_roll_joint", ".*_shoulder_yaw_joint", ".*_elbow_pitch_joint",
+                              ".*_elbow_roll_joint"])})
+    r.joint_deviation_fingers = RewTerm(func=mdp.joint_deviation_l1, weight=-0.05, params={"asset_cfg": SceneEntityCfg(
+        "robot", joint_names=[".*_five_joint", ".*_three_joint", ".*_six_joint", ".*_four_joint", ".*_zero_joint", ".*_one_joint",
+                              ".*_two_joint"])})
+    r.joint_deviation_torso = RewTerm(func=mdp.joint_deviation_l1, weight=-0.1,
+                                      params={"asset_cfg": SceneEntityCfg("robot", joint_names="torso_joint")})
+    cfg.scene.height_scanner.prim_path = "{ENV_REGEX_NS}/Robot/torso_link"
+    cfg.events.push_robot = None
+    cfg.events.add_base_mass = None
+    cfg.events.reset_robot_joints.params["position_range"] = (1.0, 1.0)
+    cfg.events.base_external_force_torque.params["asset_cfg"].body_names = ["torso_link"]
+    cfg.events.reset_base.params = {"pose_range": {"x": (-0.5, 0.5), "y": (-0.5, 0.5), "yaw": (-3.14, 3.14)},
+                                    "velocity_range": dict(_ZERO_VEL)}
+    r.lin_vel_z_l2.weight = 0.0
+    r.undesired_contacts = None
+    r.flat_orientation_l2.weight = -1.0
+    r.action_rate_l2.weight = -0.005
+    r.dof_acc_l2.weight = -1.25e-7
+    r.dof_acc_l2.params["asset_cfg"] = SceneEntityCfg("robot", joint_names=[".*_hip_.*", ".*_knee_joint"])
+    r.dof_torques_l2.weight = -1.5e-7
+    r.dof_torques_l2.params["asset_cfg"] = SceneEntityCfg("robot", joint_names=[".*_hip_.*", ".*_knee_joint", ".*_ankle_.*"])
+    cfg.commands.base_velocity.ranges.lin_vel_x = (0.0, 1.0)
+    cfg.commands.base_velocity.ranges.lin_vel_y = (-0.0, 0.0)
+    cfg.commands.base_velocity.ranges.ang_vel_z = (-1.0, 1.0)
+    cfg.terminations.base_contact.params["sensor_cfg"].body_names = "torso_link"
+    return cfg
+
+
+def G1FlatEnvCfg() -> ManagerBasedRLEnvCfg:
+    """config/g1/flat_env_cfg.py:14-42 (Isaac-Velocity-Flat-G1-v0)."""
+    cfg = _flat_biped(G1RoughEnvCfg())
+    r = cfg.rewards
+    r.track_ang_vel_z_exp.weight = 1.0
+    r.lin_vel_z_l2.weight = -0.2
+    r.action_rate_l2.weight = -0.005
+    r.dof_acc_l2.weight = -1.0e-7
+    r.feet_air_time.weight = 0.75
+    r.feet_air_time.params["threshold"] = 0.4
+    r.dof_torques_l2.weight = -2.0e-6
+    r.dof_torques_l2.params["asset_cfg"] = SceneEntityCfg("robot", joint_names=[".*_hip_.*", ".*_knee_joint"])
+    cfg.commands.base_velocity.ranges.lin_vel_x = (0.0, 1.0)
+    cfg.commands.base_velocity.ranges.lin_vel_y = (-0.5, 0.5)
+    cfg.commands.base_velocity.ranges.ang_vel_z = (-1.0, 1.0)
+    return cfg
+
+
+def CassieRoughEnvCfg() -> ManagerBasedRLEnvCfg:
+    """config/cassie/rough_env_cfg.py:18-83 (Isaac-Velocity-Rough-Cassie-v0)."""
+    cfg = LocomotionVelocityRoughEnvCfg(CASSIE_CFG.replace())
+    r = cfg.rewards
+    r.feet_air_time = RewTerm(func=mdp.feet_air_time_positive_biped, weight=2.5,
+                              params={"sensor_cfg": SceneEntityCfg("contact_forces", body_names=".*toe"),
+                                      "command_name": "base_velocity", "threshold": 0.3})
+    r.dof_pos_limits = RewTerm(func=mdp.joint_pos_limits, weight=-1.0,
+                               params={"asset_cfg": SceneEntityCfg("robot", joint_names="toe_joint_.*")})
+    r.termination_penalty = RewTerm(func=mdp.is_terminated, weight=-200.0)
+    r.joint_deviation_hip = RewTerm(func=mdp.joint_deviation_l1, weight=-0.2,
+                                    params={"asset_cfg": SceneEntityCfg("robot", joint_names=["hip_abduction_.*", "hip_rotation_.*"])})
+    r.joint_deviation_toes = RewTerm(func=mdp.joint_deviation_l1, weight=-0.2,
+                                     params={"asset_cfg": SceneEntityCfg("robot", joint_names=["toe_joint_.*"])})
+    cfg.scene.height_scanner.prim_path = "{ENV_REGEX_NS}/Robot/pelvis"
+    cfg.actions.joint_pos.scale = 0.5
+    cfg.events.push_robot = None
+    cfg.events.add_base_mass = None
+    cfg.events.reset_robot_joints.params["position_range"] = (1.0, 1.0)
+    cfg.events.base_external_force_torque.params["asset_cfg"].body_names = [".*pelvis"]
+    cfg.events.reset_base.params = {"pose_range": {"x": (-0.5, 0.5), "y": (-0.5, 0.5), "yaw": (-3.14, 3.14)},
+                                    "velocity_range": dict(_ZERO_VEL)}
+    cfg.terminations.base_contact.params["sensor_cfg"].body_names = [".*pelvis"]
+    r.undesired_contacts = None
+    r.dof_torques_l2.weight = -5.0e-6
+    r.track_lin_vel_xy_exp.weight = 2.0
+    r.track_ang_vel_z_exp.weight = 1.0
+    r.action_rate_l2.weight *= 1.5
+    r.dof_acc_l2.weight *= 1.5
+    return cfg
+
+
+def CassieFlatEnvCfg() -> ManagerBasedRLEnvCfg:
+    """config/cassie/flat_env_cfg.py:12-27 (Isaac-Velocity-Flat-Cassie-v0)."""
+    cfg = CassieRoughEnvCfg()
+    cfg.rewards.flat_orientation_l2.weight = -2.5
+    cfg.rewards.feet_air_time.weight = 5.0
+    cfg.rewards.joint_deviation_hip.params["asset_cfg"].joint_names = ["hip_rotation_.*"]
+    return _flat_biped(cfg)

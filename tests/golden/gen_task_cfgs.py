@@ -31,6 +31,11 @@ REF = {
     "Isaac-Velocity-Rough-Unitree-Go2-v0": (V + "go2.rough_env_cfg", "UnitreeGo2RoughEnvCfg"),
     "Isaac-Velocity-Rough-Unitree-Go2-Play-v0": (V + "go2.rough_env_cfg", "UnitreeGo2RoughEnvCfg_PLAY"),
     "Isaac-Velocity-Rough-H1-v0": (V + "h1.rough_env_cfg", "H1RoughEnvCfg"),
+    "Isaac-Velocity-Flat-H1-v0": (V + "h1.flat_env_cfg", "H1FlatEnvCfg"),
+    "Isaac-Velocity-Rough-G1-v0": (V + "g1.rough_env_cfg", "G1RoughEnvCfg"),
+    "Isaac-Velocity-Flat-G1-v0": (V + "g1.flat_env_cfg", "G1FlatEnvCfg"),
+    "Isaac-Velocity-Rough-Cassie-v0": (V + "cassie.rough_env_cfg", "CassieRoughEnvCfg"),
+    "Isaac-Velocity-Flat-Cassie-v0": (V + "cassie.flat_env_cfg", "CassieFlatEnvCfg"),
 }
 
 
