@@ -19,6 +19,21 @@ TASKS = ["Isaac-Cartpole-v0", "Isaac-Velocity-Flat-Anymal-C-v0", "Isaac-Velocity
          "B200-Opcode-Coverage-v0"]   # synthetic cfg: the opcodes / actuator kinds / options the five tasks do not use
 
 
+# tasks without a reference fixture of their own (their cfgs are pinned by tests/test_task_cfgs_golden.py): CUDA vs oracle
+MORE_TASKS = ["Isaac-Velocity-Rough-G1-v0", "Isaac-Velocity-Flat-Cassie-v0", "Isaac-Velocity-Rough-Unitree-A1-v0",
+              "Isaac-Velocity-Rough-Anymal-D-v0"]
+
+
+@pytest.mark.parametrize("task", MORE_TASKS)
+def test_fused_step_matches_oracle_more_robots(task):
+    """37-joint G1 (three implicit actuator groups, finger joints, joint-subset torque / acceleration penalties), Cassie,
+    A1 (DC motor) and Anymal-D through the same kernels."""
+    N, steps = (128, 5) if "Rough" in task else (256, 6)
+    spec = make_spec(task, N)
+    _, _, n_resets, _ = run_step_parity(spec, steps, fused=True, tag=task)
+    assert n_resets > 0
+
+
 @pytest.mark.parametrize("fused", [True, False, "spec"], ids=["fused-decimation", "per-substep", "fused+speculative-scan"])
 @pytest.mark.parametrize("task", TASKS)
 def test_fused_step_matches_oracle(task, fused):
