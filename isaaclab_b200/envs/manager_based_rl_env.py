@@ -328,6 +328,8 @@ class ManagerBasedRLEnv:
         edges = [N * i // C for i in range(C + 1)]
         self._d2h_ranges = [(edges[i], edges[i + 1]) for i in range(C) if edges[i + 1] > edges[i]]
 
+    results_mode = "all"   # "all": the whole result slab is read back; "metrics": everything but the observation rows
+
     def wait_results(self):
         """Blocks until the `results_out` slab of the last `step` is complete on the host."""
         if self._d2h_done is not None:
@@ -343,7 +345,8 @@ class ManagerBasedRLEnv:
             f.step(action, views, prev, before_post_step=self._eval_external_pre if self._ext_pre else None,
                    after_post_step=self._eval_external_obs if (self._ext_obs or self._class_terms) else None)
             if results_out is not None:
-                results_out.copy_(f.result, non_blocking=True)
+                lo = f.result_layout["reward"][0] if self.results_mode == "metrics" else 0
+                results_out[lo:].copy_(f.result[lo:], non_blocking=True)
             return
         if self._d2h_stream is None:
             self._setup_d2h()
@@ -358,9 +361,14 @@ class ManagerBasedRLEnv:
             with torch.cuda.stream(cs):
                 results_out[lo:hi].copy_(f.result[lo:hi], non_blocking=True)
 
-        f.step(action, views, prev, obs_ranges=self._d2h_ranges,
-               after_post_step=lambda: push(o_rew, f.result.numel()),
-               after_range=lambda b, e: push(b * row, e * row))
+        if self.results_mode == "metrics":
+            # reward / terminated / time-outs / reset mask only: the observations stay on the device for a policy that
+            # runs there (what the reference's runner does); the slab's observation part is left untouched
+            f.step(action, views, prev, after_post_step=lambda: push(o_rew, f.result.numel()))
+        else:
+            f.step(action, views, prev, obs_ranges=self._d2h_ranges,
+                   after_post_step=lambda: push(o_rew, f.result.numel()),
+                   after_range=lambda b, e: push(b * row, e * row))
         e = next(it)
         e.record(cs)
         cur.wait_event(e)   # join: everything is ordered on the current stream again
@@ -388,7 +396,7 @@ class ManagerBasedRLEnv:
         graph = None
         if self.use_cuda_graph:
             key = (action.data_ptr(), -1 if results_out is None else results_out.data_ptr(),
-                   tuple(id(v) for v in views), id(prev))
+                   tuple(id(v) for v in views), id(prev), self.results_mode)
             graph = self._graphs.get(key)
             if graph is None and self._graph_warm:
                 if len(self._graphs) >= 64:

@@ -233,3 +233,33 @@ def test_height_scan_with_lidar_patterns_matches_oracle(pattern):
     _, orc, n_resets, _ = run_step_parity(spec, 4, fused=True, tag=f"rough-anymal/{pattern}")
     hits = orc.rc_hits[..., 2]
     assert torch.isfinite(hits).any() and torch.isinf(hits).any() and n_resets > 0
+
+
+def test_metrics_only_readback_matches_full_readback():
+    """`ManagerBasedRLEnv.results_mode = "metrics"`: reward / terminated / time-outs / reset mask arrive in the host slab
+    exactly as in the full read-back, the slab's observation part is not touched, the device observations are the same."""
+    from isaaclab_b200.envs.manager_based_rl_env import HostReplaySim, ManagerBasedRLEnv
+    from isaaclab_b200.sim.synthetic import generate_slabs
+    from isaaclab_b200.tasks import TASKS as REG
+    task, N = "Isaac-Velocity-Rough-Anymal-C-v0", 192
+    spec = make_spec(task, N)
+    slabs = generate_slabs(spec, 8, seed=3)
+    outs = []
+    for mode in ("all", "metrics"):
+        env = ManagerBasedRLEnv(REG[task](), sim=HostReplaySim(spec, slabs, device="cuda"), device="cuda", spec=copy.deepcopy(spec),
+                                seed=1, use_cuda_graph=True)
+        env.results_mode = mode
+        env.episode_length_buf[::5] = spec["max_episode_length"] - 3
+        res = torch.full((env.fused.result.numel(),), 0x5A, dtype=torch.uint8).pin_memory()
+        act = torch.randn(N, spec["A"], generator=torch.Generator().manual_seed(2)).pin_memory()
+        rec = []
+        for _ in range(6):
+            env.step(act, results_out=res)
+            env.wait_results()
+            rec.append((res.clone(), env.fused.obs_buf.clone()))
+        outs.append(rec)
+    o_rew = env.fused.result_layout["reward"][0]
+    for k, ((full, obs_f), (met, obs_m)) in enumerate(zip(*outs)):
+        assert torch.equal(full[o_rew:], met[o_rew:]), f"step {k}: metrics differ"
+        assert bool((met[:o_rew] == 0x5A).all()), f"step {k}: observation part of the slab was written"
+        assert torch.equal(obs_f, obs_m), f"step {k}: device observations differ"
