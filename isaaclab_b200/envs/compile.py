@@ -127,16 +127,22 @@ def _fused(term_cfg, name, kinds, min_argc=1):
     return None
 
 
+def _modifier_kind(func):
+    """"scale" | "clip" | "bias" for the three function modifiers (ours or the reference's own), else None."""
+    kind = getattr(func, "_b200_modifier", None)
+    if kind is None:
+        mod = (getattr(func, "__module__", "") or "")
+        if mod.startswith("isaaclab.utils.modifiers") and getattr(func, "__name__", "") in ("scale", "clip", "bias"):
+            kind = func.__name__
+    return kind
+
+
 def _compile_modifiers(name, mods):
     """`ObservationTermCfg.modifiers` -> [("scale", m) | ("bias", v) | ("clip", lo, hi)] (LAB/utils/modifiers/modifier.py:23-66).
     Class modifiers (DigitalFilter, Integrator) keep per-env state in Python objects and are not on the fused path."""
     out = []
     for m in mods:
-        kind = getattr(m.func, "_b200_modifier", None)
-        if kind is None:
-            mod = (getattr(m.func, "__module__", "") or "")
-            if mod.startswith("isaaclab.utils.modifiers") and getattr(m.func, "__name__", "") in ("scale", "clip", "bias"):
-                kind = m.func.__name__
+        kind = _modifier_kind(m.func)
         if kind == "scale":
             out.append(("scale", float(m.params["multiplier"])))
         elif kind == "bias":
@@ -342,11 +348,17 @@ def compile_env_cfg(cfg: ManagerBasedRLEnvCfg, num_envs: int | None = None, terr
     for name, t in _terms(grp):
         if isinstance(t, ObservationGroupCfg):
             continue
+        import inspect
         f = _fused(t, name, ("obs",))
-        if f is not None:
+        # class modifiers (DigitalFilter, Integrator: modifier.py:69-260) keep per-env state in Python objects: a term that
+        # carries one is evaluated in Python (fused identities through their one-term program) and enters as an EXTERNAL column
+        class_mods = any(inspect.isclass(m.func) or _modifier_kind(m.func) is None for m in (t.modifiers or ()))   # or any user modifier
+        if f is not None and not class_mods:
             d = {"name": name, "op": f._b200_op, **f._b200_defaults, **resolve_params(name, t.params)}
         else:   # width inferred by calling the term once when the env is built (observation_manager.py:420-450)
             d = {**external(name, t), "dim": None}
+            if class_mods:
+                d["py_modifiers"] = list(t.modifiers)
         # history: the group's setting overrides the terms' (observation_manager.py:411-414)
         hist = gcfg.history_length if gcfg.history_length is not None else t.history_length
         flat = gcfg.flatten_history_dim if gcfg.history_length is not None else t.flatten_history_dim
@@ -356,7 +368,7 @@ def compile_env_cfg(cfg: ManagerBasedRLEnvCfg, num_envs: int | None = None, terr
             if not flat:
                 raise NotImplementedError(f"observation term '{name}': flatten_history_dim=False in a concatenated group")
             d["history_length"] = int(hist)
-        if t.modifiers:
+        if t.modifiers and not class_mods:
             d["modifiers"] = _compile_modifiers(name, t.modifiers)
         if t.noise is not None and t.noise.operation not in ("add", "scale", "abs"):
             raise ValueError(f"Unknown operation in noise: {t.noise.operation}")   # noise_model.py:41,69,97

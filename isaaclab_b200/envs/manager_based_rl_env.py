@@ -252,8 +252,25 @@ class ManagerBasedRLEnv:
 
     def _eval_external_obs(self):
         ext, N = self.fused.ext_values, self.num_envs
+        reset_ids = None
         for t, fn in self._ext_obs:
             val = fn(self, **t["params"])
+            mods = t.get("py_modifiers")
+            if mods:   # observation_manager.py:310-312 (and :231-233: class modifiers are reset for the envs that reset)
+                import inspect
+                inst = t.get("_mod_instances")
+                if inst is None:   # class modifiers are constructed with the term's output shape (observation_manager.py:456-470)
+                    inst = t["_mod_instances"] = [m.func(cfg=m, data_dim=tuple(val.shape), device=self.device)
+                                                  if inspect.isclass(m.func) else None for m in mods]
+                elif any(i is not None for i in inst):
+                    if reset_ids is None:
+                        reset_ids = self.reset_buf.nonzero(as_tuple=False).squeeze(-1)
+                    if reset_ids.numel() > 0:
+                        for i in inst:
+                            if i is not None:
+                                i.reset(reset_ids)
+                for m, i in zip(mods, inst):
+                    val = i(val) if i is not None else m.func(val, **m.params)
             if tuple(val.shape) != (N, t["dim"]):
                 raise ValueError(f"observation term '{t['name']}' returned {tuple(val.shape)}, expected {(N, t['dim'])}")
             ext[t["ext_row"]:t["ext_row"] + t["dim"]].copy_(val.t())
@@ -295,12 +312,44 @@ class ManagerBasedRLEnv:
             f.L.b200lab_env_destroy(f.handle)
             f.handle = None
 
+    def _observation_term(self, op, params):
+        """An observation identity called directly (`mdp.joint_vel_rel(env, asset_cfg=...)`): its definition on the scene
+        views (LAB/envs/mdp/observations.py:33-173,512-531), fresh tensors.  This is the path of terms that carry Python-side
+        modifiers; the step's own observations come from `b200lab_compute_obs`."""
+        d = self.scene["robot"].data
+        cfg = params.get("asset_cfg")
+        ids = slice(None) if cfg is None or cfg.joint_ids is None or isinstance(cfg.joint_ids, slice) else list(cfg.joint_ids)
+        if op == "base_pos_z":
+            return d.root_pos_w[:, 2:3].clone()
+        if op == "base_lin_vel":
+            return d.root_lin_vel_b.clone()
+        if op == "base_ang_vel":
+            return d.root_ang_vel_b.clone()
+        if op == "projected_gravity":
+            return d.projected_gravity_b.clone()
+        if op == "joint_pos":
+            return d.joint_pos[:, ids].clone()
+        if op == "joint_vel":
+            return d.joint_vel[:, ids].clone()
+        if op == "joint_pos_rel":
+            return d.joint_pos[:, ids] - d.default_joint_pos[:, ids]
+        if op == "joint_vel_rel":
+            return d.joint_vel[:, ids] - d.default_joint_vel[:, ids]
+        if op == "last_action":
+            return self.action_manager.action.clone()
+        if op == "generated_commands":
+            return self.command_manager.get_command(params["command_name"]).clone()
+        raise NotImplementedError(f"observation term '{op}' is only evaluated inside b200lab_compute_obs (the height scan's "
+                                  "ray hits do not exist before it)")
+
     def evaluate_term(self, fn, *args, **params):
         """Value of a reward / termination term function called directly (`mdp.track_lin_vel_xy_exp(env, ...)`),
         as the term programs evaluated it in the most recent `step` -- the state the reference function would read
         between steps.  The term must be part of this env's cfg with the same params; anything else has no fused
         program to run and raises."""
         kind, op = getattr(fn, "_b200_kind", None), getattr(fn, "_b200_op", None)
+        if kind == "obs":
+            return self._observation_term(op, params)
         table = {"rew": "rewards", "term": "terminations"}.get(kind)
         if table is None:
             raise NotImplementedError(f"term '{op}' ({kind}) is only evaluated inside the fused step kernels")

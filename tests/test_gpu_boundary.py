@@ -295,3 +295,41 @@ def test_recording_hook_reproduces_the_run_it_recorded():
     for k, (a, b) in enumerate(zip(*runs)):
         for x, y, name in zip(a, b, ("obs", "reward", "terminated", "time_outs")):
             assert torch.equal(x, y), f"step {k}: {name} differs between the recorded run and its replay"
+
+
+def test_class_and_user_modifiers_on_a_fused_term():
+    """A term with a class modifier (Integrator) or a user modifier function is evaluated in Python -- the fused identity
+    through its one-term program -- modified, and enters the kernels as an EXTERNAL column; noise / clip / scale still run in
+    the kernel.  Checked against the same env without the modifier: integral of joint_vel_rel by the trapezoid rule, reset
+    to zero for the envs a step resets (observation_manager.py:231-233)."""
+    from isaaclab_b200.tasks import TASKS
+    from isaaclab_b200.utils import modifiers as MOD
+    outs = {}
+    for variant in ("plain", "integrated"):
+        cfg = TASKS[TASK]()
+        cfg.observations.policy._group.enable_corruption = False
+        if variant == "integrated":
+            cfg.observations.policy.joint_vel.modifiers = [MOD.ModifierCfg(func=lambda data, gain: data * gain, params={"gain": 2.0}),
+                                                           MOD.IntegratorCfg(dt=0.5)]
+        env = _env(cfg)
+        assert ({t["name"]: t["op"] for t in env.spec["observations"]["terms"]}["joint_vel"] ==
+                ("external" if variant == "integrated" else "joint_vel_rel"))
+        env.reset()
+        g = torch.Generator(device="cuda").manual_seed(0)
+        rec = []
+        for _ in range(5):
+            obs, _, term, trunc, _ = env.step(torch.randn(N, 12, device="cuda", generator=g))
+            rec.append((obs["policy"][:, 24:36].clone(), (term | trunc).clone()))   # joint_vel columns of the rough policy group
+        outs[variant] = rec
+    n_done = 0
+    for k in range(1, 5):   # step 0's integral also holds the reset-time sample, which the plain run did not record
+        (jv, done), (jv_prev, _) = outs["plain"][k], outs["plain"][k - 1]
+        (got, done2), (got_prev, _) = outs["integrated"][k], outs["integrated"][k - 1]
+        assert torch.equal(done, done2)
+        d = done.unsqueeze(1)
+        base = torch.where(d, torch.zeros_like(got_prev), got_prev)        # Integrator.reset for the envs this step reset
+        x_prev = torch.where(d, torch.zeros_like(jv_prev), 2.0 * jv_prev)
+        want = base + (2.0 * jv + x_prev) / 2 * 0.5
+        torch.testing.assert_close(got, want, rtol=1e-5, atol=1e-5, msg=lambda m: f"step {k}: {m}")
+        n_done += int(done.sum())
+    assert n_done > 0

@@ -157,11 +157,19 @@ def test_history_and_modifiers_compile_like_the_reference():
         compile_env_cfg(cfg, num_envs=4)
     cfg.observations.policy._group.history_length = None
 
-    class Integrator:
-        pass
-    cfg.observations.policy.joint_vel.modifiers = [modifiers.ModifierCfg(func=Integrator, params={"dt": 0.1})]
-    with pytest.raises(NotImplementedError, match="only scale / clip / bias"):
-        compile_env_cfg(cfg, num_envs=4)
+    # a class modifier moves the term to the Python-evaluated (EXTERNAL) path with all its modifiers, in order
+    cfg.observations.policy.joint_vel.modifiers = [modifiers.ModifierCfg(func=modifiers.scale, params={"multiplier": 2.0}),
+                                                   modifiers.IntegratorCfg(dt=0.1)]
+    spec = compile_env_cfg(cfg, num_envs=4)
+    jv = {t["name"]: t for t in spec["observations"]["terms"]}["joint_vel"]
+    assert jv["op"] == "external" and len(jv["py_modifiers"]) == 2 and "modifiers" not in jv
+
+    def my_modifier(data, gain):
+        return data * gain
+    cfg.observations.policy.joint_vel.modifiers = [modifiers.ModifierCfg(func=my_modifier, params={"gain": 2.0})]
+    spec = compile_env_cfg(cfg, num_envs=4)   # a user modifier function: Python path as well
+    jv = {t["name"]: t for t in spec["observations"]["terms"]}["joint_vel"]
+    assert jv["op"] == "external" and jv["py_modifiers"][0].func is my_modifier
 
 
 def test_delayed_pd_cfg_compiles_and_checks_its_range():
