@@ -385,7 +385,7 @@ def measure_e2e(cfg, spec, slabs, init, steps, warmup, world, rank, dev):
     init_fused_state(env.fused, init)
     g = torch.Generator().manual_seed(12 + rank)
     act_host = torch.randn(N, spec["A"], generator=g).pin_memory()
-    env.result_chunks = 4
+    env.result_chunks = 2   # tools/e2e_probe.py: 2 ranges 200 us, 4 ranges 210 us, 1 range 209 us per step
     res_host = torch.empty(env.fused.result.numel(), dtype=torch.uint8).pin_memory()
 
     def e2e_step(_k):

@@ -216,7 +216,7 @@ class ManagerBasedRLEnv:
         self._d2h_stream = None
         self._d2h_events = []
         self._d2h_done = None
-        self.result_chunks = 4
+        self.result_chunks = 2   # observation ranges of the pipelined read-back (measured: 2 beats 1 and 4, tools/e2e_probe.py)
         self.use_cuda_graph = bool(use_cuda_graph)
         self._graphs, self._graph_warm = {}, False
         if self.use_cuda_graph:

@@ -17,7 +17,7 @@ from tests.mdp_common import init_fused_state  # noqa: E402
 
 steps = int(sys.argv[1]) if len(sys.argv) > 1 else 300
 dev = torch.device("cuda", 0)
-cfg, spec, slabs, init = bench.build_workload(dev, seed=0)
+cfg, spec, slabs, init = bench.build_workload("cfg3", seed=0, device=dev)
 N = spec["N"]
 g = torch.Generator().manual_seed(1)
 act_host = torch.randn(N, spec["A"], generator=g).pin_memory()
@@ -28,7 +28,7 @@ def run(name, sim_kind, graph, results, prefetch=True, chunks=4):
     if sim_kind == "host":
         sim = HostReplaySim(spec, slabs, device=dev, prefetch=prefetch)
     else:
-        sim = DeviceReplaySim(SyntheticSim(spec, K=bench.K_SLABS, device=dev, slabs=slabs))
+        sim = DeviceReplaySim(SyntheticSim(spec, K=slabs["root_state_w"].shape[0], device=dev, slabs=slabs))
     env = ManagerBasedRLEnv(cfg, sim=sim, device=dev, spec=spec, seed=0, use_cuda_graph=graph)
     env.result_chunks = chunks
     init_fused_state(env.fused, init)
