@@ -12,16 +12,22 @@
 //     Araw.Braw + Araw.Blo + Alo.Braw  ("3xTF32").  The dropped Alo.Blo term and the truncation of lo are O(2^-22)
 // relative: the result agrees with an fp32 FFMA GEMM to a few ulp.  precision 1 = the first MMA only (opt-in).
 //
-// Structure (one CTA = one 128 x BN tile; 16 producer warps + 1 MMA warp; ring of kStages raw stages + 2 lo buffers):
-//   producer warps : cp.async global -> shared (16-byte copies wherever the operand is contiguous and aligned along K
-//                    or along M/N, 4-byte copies otherwise; zero-fill for out-of-range rows / K tail), then each thread
-//                    re-reads exactly the bytes it copied, writes lo = x - trunc(x) to the stage's lo buffer,
-//                    fence.proxy.async, mbarrier.arrive(full[s]).  Loads for tile kt+kStages-1 are issued right after
-//                    tile kt has been handed over, so kStages-2 tiles are always in flight under the MMAs.
-//   MMA warp       : one lane waits full[s], issues the BK/8 x {1,3} tcgen05.mma.cta_group::1.kind::tf32, and
-//                    tcgen05.commit -> empty[s] (releases the stage to the producers); the last commit -> done.
-//   epilogue       : producer warps tcgen05.ld the accumulator (lane = row), transpose 32x32 through shared memory,
-//                    +bias, ELU, coalesced stores.
+// Structure (persistent: one CTA per SM walks the 128 x BN output tiles b, b + gridDim.x, ...; 16 producer warps + 1 MMA
+// warp + 4 epilogue warps; ring of kStages raw stages + 2 lo buffers; TWO accumulators in TMEM):
+//   producer warps : TMA boxes (K-contiguous, aligned operands: one thread issues, completion by mbarrier transaction
+//                    bytes) or cp.async global -> shared (16-byte copies wherever the operand is contiguous and aligned
+//                    along M/N, 4-byte copies otherwise; zero-fill for out-of-range rows / K tail), then a linear sweep
+//                    writes lo = x - trunc(x) of the stage to a lo buffer, fence.proxy.async, mbarrier.arrive(full[s]).
+//                    The ring does not drain between tiles: the k-tiles of the CTA's next output tile are requested
+//                    while the last MMAs of the current one run.
+//   MMA warp       : one lane waits full[s], issues the BK/8 x {1,3} tcgen05.mma.cta_group::1.kind::tf32 into accumulator
+//                    n & 1, and tcgen05.commit -> empty[s] (releases the stage to the producers); after the tile's last
+//                    k-tile, commit -> acc_full[n & 1].
+//   epilogue warps : wait acc_full, tcgen05.ld the accumulator (lane = row, one warp per lane quarter), arrive acc_empty
+//                    as soon as the last columns are in registers, transpose 32 x 32 through shared memory, +bias, ELU,
+//                    128-bit stores of 4 rows x 128 contiguous bytes -- all under the MMAs of the next tile.
+//   Measured (profiles/r2_notes.md): the one-tile-per-CTA form of this kernel paid ~40 % of a short-K tile's time in
+//   prologue (barrier init, TMEM allocation, ring fill) and epilogue; cfg 3 update 22.5 -> 20.6 ms.
 // Shared-memory operand layouts (word maps read back from the hardware with tools/umma_probe.cu):
 //   K-contiguous operand  : K-major SWIZZLE_128B (layout type 2): offset(r,k) = (r/8)*1024 + (r%8)*128 +
 //                           (((k/4) ^ (r%8))*16) + (k%4)*4 -- a row's 32 tf32 are one 128-byte line, so the copies of a
@@ -41,8 +47,10 @@ namespace tc {
 
 constexpr int BM = 128;               // UMMA M (cta_group::1)
 constexpr int BK = 32;                // K elements per stage = 4 MMA K-steps of 8 tf32
-constexpr int kProducers = 512;       // 16 warps stage operands and run the epilogue (4 per scheduler hide the ALU latency)
-constexpr int kThreads = kProducers + 32;   // + the MMA warp
+constexpr int kProducers = 512;       // 16 warps stage operands (4 per scheduler hide the ALU latency of the lo sweep)
+constexpr int kEpiWarps = 4;          // one per TMEM lane quarter: drain accumulator n while the MMAs fill accumulator n+1
+constexpr int kThreads = kProducers + 32 + kEpiWarps * 32;   // producers | the MMA warp | epilogue warps
+constexpr int kEpiLd = 36;            // floats per row of an epilogue warp's 32 x 32 transpose tile
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -255,12 +263,14 @@ struct Cursor<ROWS, kKTma> {
 // are outstanding while one tile is split and another is multiplied.
 template <int BN>
 struct Smem {
-  static constexpr int kStages = BN > 64 ? 5 : 7;
+  static constexpr int kStages = BN > 64 ? 4 : 6;
   static constexpr uint32_t kA = Tile<BM>::kBytes, kB = Tile<BN>::kBytes;
   static constexpr uint32_t kStage = kA + kB;                      // A raw, B raw   (lo buffer: A lo, B lo)
   static constexpr uint32_t kLo = kStages * kStage;                // two lo buffers follow the raw ring
-  static constexpr uint32_t kCtl = kLo + 2 * kStage;               // full[kStages], empty[kStages], done, tmem pointer, tma[kStages]
-  static constexpr uint32_t kTotal = kCtl + 24 * kStages + 16 + 1024;   // + slack to align the base to 1024
+  static constexpr uint32_t kEpi = kLo + 2 * kStage;               // one 32 x 32 transpose tile per epilogue warp
+  static constexpr uint32_t kEpiBytes = kEpiWarps * 32 * kEpiLd * 4;
+  static constexpr uint32_t kCtl = kEpi + kEpiBytes;               // full / empty / tma [kStages], acc_full[2], acc_empty[2], tmem pointer
+  static constexpr uint32_t kTotal = kCtl + 24 * kStages + 32 + 16 + 1024;   // + slack to align the base to 1024
 };
 
 __device__ __forceinline__ float exp2f_fast(float x) { float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
@@ -294,12 +304,34 @@ __device__ __forceinline__ uint64_t operand_desc(uint32_t base, int ks, bool mn_
                   : make_desc(base + (uint32_t)ks * 32u, 16u, Tile<ROWS>::kSboK, 2u);
 }
 
+// One unit of work of the persistent loop: output tile (i0, j0) of K range [k_begin, k_end) (a split of K writes slab z).
+struct Unit {
+  int64_t i0, k_begin, k_end;
+  int j0, z, num_kt;
+};
+__device__ __forceinline__ Unit unit_of(int64_t u, int n_i, int n_j, int64_t K, int64_t k_per_split) {
+  // j fastest: CTAs that run side by side share the A panel (read from HBM once, then from L2)
+  const int64_t per_z = (int64_t)n_i * n_j;
+  Unit w;
+  w.z = (int)(u / per_z);
+  const int64_t r = u - (int64_t)w.z * per_z;
+  w.i0 = (r / n_j) * BM;
+  w.j0 = (int)(r % n_j);
+  w.k_begin = (int64_t)w.z * k_per_split;
+  w.k_end = min64(K, w.k_begin + k_per_split);
+  w.num_kt = (int)((w.k_end - w.k_begin + BK - 1) / BK);
+  return w;
+}
+
 // epi: 0 = store, 1 = +bias, 2 = +bias then ELU.  split: 3xTF32 (1) or single TF32 (0).
+// Persistent: CTA b works through units b, b + gridDim.x, ... .  The operand ring runs across unit boundaries (the loads
+// of the next tile are in flight under the last MMAs of this one) and the accumulator is double-buffered in TMEM, so the
+// epilogue of unit n (TMEM -> registers -> transpose -> global, by its own 4 warps) runs under the MMAs of unit n+1.
 template <int BN, int AMODE, int BMODE>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_tf32_kernel(const float* __restrict__ A, int64_t lda_i, int64_t lda_k, const float* __restrict__ B, int64_t ldb_k,
                  int64_t ldb_j, float* __restrict__ C, int64_t ldc, int64_t M, int N, int64_t K, int64_t k_per_split,
-                 const float* __restrict__ bias, int epi, int split, const __grid_constant__ CUtensorMap map_a,
+                 int splits, const float* __restrict__ bias, int epi, int split, const __grid_constant__ CUtensorMap map_a,
                  const __grid_constant__ CUtensorMap map_b) {
   extern __shared__ uint8_t smem_dyn[];
   constexpr bool kTmaA = AMODE == kKTma, kTmaB = BMODE == kKTma, kAnyTma = kTmaA || kTmaB, kAllTma = kTmaA && kTmaB;
@@ -309,16 +341,13 @@ gemm_tf32_kernel(const float* __restrict__ A, int64_t lda_i, int64_t lda_k, cons
   constexpr int kMmaWarp = kProducers / 32;
   uint8_t* smem = smem_dyn + ((1024u - (smem_u32(smem_dyn) & 1023u)) & 1023u);   // MN-major swizzle atoms: 1024-byte aligned
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int64_t i0 = (int64_t)blockIdx.x * BM;
-  const int j0 = blockIdx.y * BN;
-  const int64_t k_begin = (int64_t)blockIdx.z * k_per_split;
-  const int64_t k_end = min64(K, k_begin + k_per_split);
-  const int num_kt = (int)((k_end - k_begin + BK - 1) / BK);
+  const int n_i = (int)((M + BM - 1) / BM), n_j = (N + BN - 1) / BN;
+  const int64_t num_units = (int64_t)n_i * n_j * splits;
 
   uint8_t* ctl = smem + S::kCtl;
-  const uint32_t bar_full = smem_u32(ctl), bar_empty = bar_full + 8 * kStages, bar_done = bar_full + 16 * kStages;
-  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(ctl + 16 * kStages + 8);
-  const uint32_t bar_tma = bar_full + 16 * kStages + 16;
+  const uint32_t bar_full = smem_u32(ctl), bar_empty = bar_full + 8 * kStages, bar_tma = bar_full + 16 * kStages;
+  const uint32_t bar_acc_full = bar_full + 24 * kStages, bar_acc_empty = bar_acc_full + 16;
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(ctl + 24 * kStages + 32);
 
   if (tid == 0) {
     if (kTmaA) tma_prefetch_desc(&map_a);
@@ -328,10 +357,13 @@ gemm_tf32_kernel(const float* __restrict__ A, int64_t lda_i, int64_t lda_k, cons
       mbar_init(bar_empty + 8 * s, 1);
       mbar_init(bar_tma + 8 * s, 1);
     }
-    mbar_init(bar_done, 1);
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(bar_acc_full + 8 * b, 1);
+      mbar_init(bar_acc_empty + 8 * b, kEpiWarps);
+    }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  if (warp == kMmaWarp) tmem_alloc(smem_u32(tmem_ptr_smem), BN);   // BN in {64,128}: power of two >= 32 columns
+  if (warp == kMmaWarp) tmem_alloc(smem_u32(tmem_ptr_smem), 2 * BN);   // two accumulators; 2*BN in {128, 256}: a power of two
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -339,12 +371,25 @@ gemm_tf32_kernel(const float* __restrict__ A, int64_t lda_i, int64_t lda_k, cons
 
   if (warp < kMmaWarp) {
     // ---------------- producers ----------------
+    int total_g = 0;   // k-tiles of all my units
+    for (int64_t u = blockIdx.x; u < num_units; u += gridDim.x) total_g += unit_of(u, n_i, n_j, K, k_per_split).num_kt;
     Cursor<BM, AMODE> ca;
     Cursor<BN, BMODE> cb;
-    if constexpr (kTmaA) ca.init(&map_a, i0, k_begin, tid); else ca.init(A, lda_i, lda_k, i0, M, k_begin, k_end, tid);
-    if constexpr (kTmaB) cb.init(&map_b, j0, k_begin, tid); else cb.init(B, ldb_j, ldb_k, j0, N, k_begin, k_end, tid);
-    auto issue = [&](int kt_new) {
-      const int sn = kt_new % kStages;
+    int64_t u_issue = blockIdx.x;
+    int kt_issue = 0, nkt_issue = 0;
+    auto open_unit = [&]() {
+      const Unit w = unit_of(u_issue, n_i, n_j, K, k_per_split);
+      nkt_issue = w.num_kt;
+      kt_issue = 0;
+      if constexpr (kTmaA) ca.init(&map_a, w.i0, w.k_begin, tid); else ca.init(A, lda_i, lda_k, w.i0, M, w.k_begin, w.k_end, tid);
+      if constexpr (kTmaB) cb.init(&map_b, (int64_t)w.j0 * BN, w.k_begin, tid);
+      else cb.init(B, ldb_j, ldb_k, (int64_t)w.j0 * BN, N, w.k_begin, w.k_end, tid);
+    };
+    if (u_issue < num_units) open_unit();
+    auto issue = [&](int g_new) {   // loads of my g_new-th k-tile (callers keep g_new < total_g)
+      if (kt_issue == nkt_issue) { u_issue += gridDim.x; open_unit(); }
+      ++kt_issue;
+      const int sn = g_new % kStages;
       const uint32_t st = smem_u32(smem + sn * S::kStage);
       if constexpr (kAnyTma) { if (tid == 0) mbar_arrive_expect_tx(bar_tma + 8 * sn, kTmaBytes); }
       if constexpr (kTmaA) ca.issue(st, bar_tma + 8 * sn); else ca.issue(st);
@@ -352,97 +397,152 @@ gemm_tf32_kernel(const float* __restrict__ A, int64_t lda_i, int64_t lda_k, cons
     };
 #pragma unroll
     for (int p = 0; p < kStages - 1; ++p) {
-      if (p < num_kt) issue(p);
+      if (p < total_g) issue(p);
       if constexpr (!kAllTma) cp_async_commit();
     }
 #pragma unroll 1
-    for (int kt = 0; kt < num_kt; ++kt) {
-      const int s = kt % kStages;
-      if constexpr (!kAllTma) cp_async_wait<kStages - 2>();   // this thread's copies of k-tile kt have landed ...
+    for (int g = 0; g < total_g; ++g) {
+      const int s = g % kStages;
+      if constexpr (!kAllTma) cp_async_wait<kStages - 2>();   // this thread's copies of k-tile g have landed ...
       // ... the TMA boxes of the tile too (the mbarrier completes when all their bytes are in shared memory, for every waiter)
-      if constexpr (kAnyTma) mbar_wait(bar_tma + 8 * s, (uint32_t)((kt / kStages) & 1));
+      if constexpr (kAnyTma) mbar_wait(bar_tma + 8 * s, (uint32_t)((g / kStages) & 1));
       if (split) {
         // ... and, after the producers' barrier, everybody's cp.async copies: the lo sweep is linear over the stage, so a
-        // thread reads bytes other threads copied (no barrier when both operands came by TMA).  Lo buffer kt&1 was last
-        // read by the MMAs of k-tile kt-2 (waited for below, one iteration ago).
+        // thread reads bytes other threads copied (no barrier when both operands came by TMA).  Lo buffer g&1 was last
+        // read by the MMAs of k-tile g-2 (waited for below, one iteration ago).
         if constexpr (!kAllTma) asm volatile("bar.sync 1, %0;" ::"n"(kProducers) : "memory");
-        lo_sweep<S::kStage>(smem + s * S::kStage, smem + S::kLo + (kt & 1) * S::kStage, tid);
+        lo_sweep<S::kStage>(smem + s * S::kStage, smem + S::kLo + (g & 1) * S::kStage, tid);
       }
       fence_proxy_async();            // cp.async / st.shared (generic proxy) -> visible to the tensor core (async proxy)
       mbar_arrive(bar_full + 8 * s);
-      // k-tile kt-1's MMAs done: its raw stage can be refilled (with k-tile kt+kStages-1) and, one iteration from now,
+      // k-tile g-1's MMAs done: its raw stage can be refilled (with k-tile g+kStages-1) and, one iteration from now,
       // its lo buffer rewritten -- so this wait is unconditional
-      if (kt >= 1) mbar_wait(bar_empty + 8 * ((kt - 1) % kStages), (uint32_t)(((kt - 1) / kStages) & 1));
-      if (kt + kStages - 1 < num_kt) issue(kt + kStages - 1);
+      if (g >= 1) mbar_wait(bar_empty + 8 * ((g - 1) % kStages), (uint32_t)(((g - 1) / kStages) & 1));
+      if (g + kStages - 1 < total_g) issue(g + kStages - 1);
       if constexpr (!kAllTma) cp_async_commit();
     }
-  } else if (lane == 0) {
-    // ---------------- MMA issuer ----------------
-    constexpr bool a_mn = AMODE == kMnVec || AMODE == kMnScalar, b_mn = BMODE == kMnVec || BMODE == kMnScalar;
-    constexpr uint32_t idesc = make_idesc(BM, BN) | ((uint32_t)a_mn << 15) | ((uint32_t)b_mn << 16);
+  } else if (warp == kMmaWarp) {
+    if (lane == 0) {
+      // ---------------- MMA issuer ----------------
+      constexpr bool a_mn = AMODE == kMnVec || AMODE == kMnScalar, b_mn = BMODE == kMnVec || BMODE == kMnScalar;
+      constexpr uint32_t idesc = make_idesc(BM, BN) | ((uint32_t)a_mn << 15) | ((uint32_t)b_mn << 16);
+      int g = 0, n = 0;
 #pragma unroll 1
-    for (int kt = 0; kt < num_kt; ++kt) {
-      const int s = kt % kStages;
-      const uint32_t sa = smem_u32(smem + s * S::kStage), sb = sa + S::kA;
-      const uint32_t sa_lo = smem_u32(smem + S::kLo + (kt & 1) * S::kStage), sb_lo = sa_lo + S::kA;
-      mbar_wait(bar_full + 8 * s, (uint32_t)((kt / kStages) & 1));
-      tc_fence_after();
-#pragma unroll
-      for (int ks = 0; ks < BK / 8; ++ks) {
-        const uint64_t da = operand_desc<BM>(sa, ks, a_mn), db = operand_desc<BN>(sb, ks, b_mn);
-        umma_tf32(tmem_d, da, db, idesc, (kt | ks) != 0);
-        if (split) {
-          umma_tf32(tmem_d, da, operand_desc<BN>(sb_lo, ks, b_mn), idesc, 1u);
-          umma_tf32(tmem_d, operand_desc<BM>(sa_lo, ks, a_mn), db, idesc, 1u);
+      for (int64_t u = blockIdx.x; u < num_units; u += gridDim.x, ++n) {
+        const int num_kt = unit_of(u, n_i, n_j, K, k_per_split).num_kt;
+        const int buf = n & 1, use = n >> 1;
+        if (use >= 1) {   // the epilogue has read this accumulator's previous tile out of TMEM
+          mbar_wait(bar_acc_empty + 8 * buf, (uint32_t)((use - 1) & 1));
+          tc_fence_after();
         }
+        const uint32_t acc = tmem_d + (uint32_t)(buf * BN);
+#pragma unroll 1
+        for (int kt = 0; kt < num_kt; ++kt, ++g) {
+          const int s = g % kStages;
+          const uint32_t sa = smem_u32(smem + s * S::kStage), sb = sa + S::kA;
+          const uint32_t sa_lo = smem_u32(smem + S::kLo + (g & 1) * S::kStage), sb_lo = sa_lo + S::kA;
+          mbar_wait(bar_full + 8 * s, (uint32_t)((g / kStages) & 1));
+          tc_fence_after();
+#pragma unroll
+          for (int ks = 0; ks < BK / 8; ++ks) {
+            const uint64_t da = operand_desc<BM>(sa, ks, a_mn), db = operand_desc<BN>(sb, ks, b_mn);
+            umma_tf32(acc, da, db, idesc, (kt | ks) != 0);
+            if (split) {
+              umma_tf32(acc, da, operand_desc<BN>(sb_lo, ks, b_mn), idesc, 1u);
+              umma_tf32(acc, operand_desc<BM>(sa_lo, ks, a_mn), db, idesc, 1u);
+            }
+          }
+          umma_commit(bar_empty + 8 * s);   // releases the stage once these MMAs have read it
+        }
+        umma_commit(bar_acc_full + 8 * buf);   // accumulator complete
       }
-      umma_commit(bar_empty + 8 * s);   // releases the stage once these MMAs have read it
     }
-    if (num_kt > 0) umma_commit(bar_done);   // accumulator complete
-  }
-  // ---- epilogue: TMEM -> registers -> (32 x 32 transpose through shared memory) -> global.  Warp w may read TMEM lanes
-  // 32*(w%4)..+31 (= tile rows, one per lane); the warps that share a lane quarter split the columns in groups of 32.
-  // Written straight from the TMEM layout every store instruction would touch 32 rows (32 sectors); after the transpose
-  // it writes 128 contiguous bytes of one row.
-  if (warp < 4 * (BN / 32)) {
-    if (num_kt > 0) mbar_wait(bar_done, 0);
-    tc_fence_after();
-    const int q = warp & 3, c0 = (warp >> 2) * 32;
-    float* Cz = C + (int64_t)blockIdx.z * M * ldc;
-    float* tile = reinterpret_cast<float*>(smem) + warp * (32 * 33);   // raw stages are free: every MMA has completed
-    if (j0 + c0 < N) {   // warp-uniform
-      float v[32];
-      if (num_kt > 0) {
-        float lo16[16], hi16[16];
-        tmem_ld16(tmem_d + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, lo16);
-        tmem_ld16(tmem_d + ((uint32_t)(q * 32) << 16) + (uint32_t)(c0 + 16), hi16);
+  } else {
+    // ---------------- epilogue: TMEM -> registers -> (32 x 32 transpose through shared memory) -> global.  A warp may read
+    // the TMEM lanes 32*(warp%4)..+31 (= tile rows, one per lane); it walks the BN columns in groups of 32.  Written
+    // straight from the TMEM layout every store instruction would touch 32 rows (32 sectors); after the transpose it
+    // writes 128 contiguous bytes of one row.
+    const int q = warp & 3;
+    float* tile = reinterpret_cast<float*>(smem + S::kEpi) + (warp - kMmaWarp - 1) * (32 * kEpiLd);
+    const bool elu = epi == 2;
+    // 128-bit path: a lane re-reads 4 columns of one row, so a store instruction writes 4 rows x 128 contiguous bytes
+    const bool vec = ldc % 4 == 0 && N % 4 == 0 && (reinterpret_cast<uintptr_t>(C) & 15u) == 0;
+    int n = 0;
+#pragma unroll 1
+    for (int64_t u = blockIdx.x; u < num_units; u += gridDim.x, ++n) {
+      const Unit w = unit_of(u, n_i, n_j, K, k_per_split);
+      const int buf = n & 1, use = n >> 1;
+      const int j0 = w.j0 * BN;
+      float* Cz = C + (int64_t)w.z * M * ldc;
+      mbar_wait(bar_acc_full + 8 * buf, (uint32_t)(use & 1));
+      tc_fence_after();
+      const uint32_t acc = tmem_d + (uint32_t)(buf * BN) + ((uint32_t)(q * 32) << 16);
+#pragma unroll 1
+      for (int c0 = 0; c0 < BN; c0 += 32) {
+        const bool last = c0 + 32 == BN;
+        if (j0 + c0 < N) {   // warp-uniform
+          float lo16[16], hi16[16];
+          tmem_ld16(acc + (uint32_t)c0, lo16);
+          tmem_ld16(acc + (uint32_t)(c0 + 16), hi16);
+          if (last) {   // every column of this warp's quarter is in registers: hand the accumulator back
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar_acc_empty + 8 * buf);
+          }
+          float4* trow = reinterpret_cast<float4*>(tile + lane * kEpiLd);   // row stride 144 B: conflict-free 128-bit accesses
 #pragma unroll
-        for (int i = 0; i < 16; ++i) { v[i] = lo16[i]; v[16 + i] = hi16[i]; }
-      } else {
+          for (int i = 0; i < 4; ++i) {
+            trow[i] = make_float4(lo16[4 * i], lo16[4 * i + 1], lo16[4 * i + 2], lo16[4 * i + 3]);
+            trow[4 + i] = make_float4(hi16[4 * i], hi16[4 * i + 1], hi16[4 * i + 2], hi16[4 * i + 3]);
+          }
+          __syncwarp();
+          if (vec) {
+            const int cg = (lane & 7) * 4, gj = j0 + c0 + cg;
+            const bool col_ok = gj < N;   // N % 4 == 0: the whole vector is inside
+            float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (epi >= 1 && col_ok) bv = make_float4(__ldg(bias + gj), __ldg(bias + gj + 1), __ldg(bias + gj + 2), __ldg(bias + gj + 3));
 #pragma unroll
-        for (int i = 0; i < 32; ++i) v[i] = 0.f;
-      }
-#pragma unroll
-      for (int i = 0; i < 32; ++i) tile[lane * 33 + i] = v[i];
-      __syncwarp();
-      const int gj = j0 + c0 + lane;
-      const bool col_ok = gj < N;
-      float bv = 0.f;
-      if (epi >= 1 && col_ok) bv = __ldg(bias + gj);
-      const bool elu = epi == 2;
+            for (int rr = 0; rr < 8; ++rr) {
+              const int r = rr * 4 + (lane >> 3);
+              const int64_t gi = w.i0 + q * 32 + r;
+              float4 x = *reinterpret_cast<const float4*>(tile + r * kEpiLd + cg);
+              x.x += bv.x; x.y += bv.y; x.z += bv.z; x.w += bv.w;
+              if (elu) {   // |abs err| ~1e-7
+                x.x = x.x > 0.0f ? x.x : exp2f_fast(1.4426950408889634f * x.x) - 1.0f;
+                x.y = x.y > 0.0f ? x.y : exp2f_fast(1.4426950408889634f * x.y) - 1.0f;
+                x.z = x.z > 0.0f ? x.z : exp2f_fast(1.4426950408889634f * x.z) - 1.0f;
+                x.w = x.w > 0.0f ? x.w : exp2f_fast(1.4426950408889634f * x.w) - 1.0f;
+              }
+#ifndef B200LAB_GEMM_NOSTORE
+              if (col_ok && gi < M) *reinterpret_cast<float4*>(Cz + gi * ldc + gj) = x;
+#endif
+            }
+          } else {
+            const int gj = j0 + c0 + lane;
+            const bool col_ok = gj < N;
+            float bv = 0.f;
+            if (epi >= 1 && col_ok) bv = __ldg(bias + gj);
 #pragma unroll 8
-      for (int rr = 0; rr < 32; ++rr) {
-        const int64_t gi = i0 + q * 32 + rr;
-        if (gi >= M) break;      // warp-uniform
-        float x = tile[rr * 33 + lane] + bv;
-        if (elu) x = x > 0.0f ? x : exp2f_fast(1.4426950408889634f * x) - 1.0f;   // |abs err| ~1e-7
-        if (col_ok) Cz[gi * ldc + gj] = x;
+            for (int rr = 0; rr < 32; ++rr) {
+              const int64_t gi = w.i0 + q * 32 + rr;
+              if (gi >= M) break;      // warp-uniform
+              float x = tile[rr * kEpiLd + lane] + bv;
+              if (elu) x = x > 0.0f ? x : exp2f_fast(1.4426950408889634f * x) - 1.0f;
+              if (col_ok) Cz[gi * ldc + gj] = x;
+            }
+          }
+          __syncwarp();   // the tile is rewritten by the next column group
+        } else if (last) {
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(bar_acc_empty + 8 * buf);
+        }
       }
     }
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == kMmaWarp) tmem_dealloc(tmem_d, BN);
+  if (warp == kMmaWarp) tmem_dealloc(tmem_d, 2 * BN);
 }
 
 // cuTensorMapEncodeTiled, resolved through the runtime (no link-time dependency on libcuda)
@@ -492,9 +592,15 @@ static int launch(const float* A, int64_t lda_i, int64_t lda_k, const float* B, 
     if (err != cudaSuccess) { set_error("tcgen05 gemm: %s", cudaGetErrorString(err)); return B200LAB_ERR_CUDA; }
     configured = true;
   }
-  dim3 grid((unsigned)ceil_div(M, BM), (unsigned)ceil_div(N, BN), (unsigned)splits);
-  kern<<<grid, kThreads, Smem<BN>::kTotal, s>>>(A, lda_i, lda_k, B, ldb_k, ldb_j, C, ldc, M, N, K, k_per_split, bias, epi, split,
-                                                map_a, map_b);
+  static const int sm_count = [] {
+    int dev = 0, n = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = kNumSMs;
+    return n;
+  }();
+  const int64_t units = ceil_div(M, BM) * ceil_div(N, BN) * splits;
+  const unsigned grid = (unsigned)(units < sm_count ? units : sm_count);   // one persistent CTA per SM
+  kern<<<grid, kThreads, Smem<BN>::kTotal, s>>>(A, lda_i, lda_k, B, ldb_k, ldb_j, C, ldc, M, N, K, k_per_split, splits, bias, epi,
+                                                split, map_a, map_b);
   count_launch();
   return B200LAB_OK;
 }
