@@ -154,6 +154,8 @@ enum OperandMode {
   kMnScalar = 3,  // rows fastest but unaligned           ->  4-byte copies,            MN-major layout
   kKTma = 4,      // as kKVec, moved by TMA: ONE thread issues a ROWS x BK box per k-tile (SWIZZLE_128B tensor map writes
                   // exactly the K-major layout; rows / K beyond the matrix arrive as zeros), completion on an mbarrier
+  kMnTma = 5,     // as kMnVec, moved by TMA: ROWS/32 boxes of 32 rows x BK per k-tile (SWIZZLE_128B_ATOM_32B tensor map = the
+                  // MN-major layout: a box is one 4 KB group of BK/4 k-atoms)
 };
 
 template <int ROWS>
@@ -258,6 +260,23 @@ struct Cursor<ROWS, kKTma> {
   }
 };
 
+template <int ROWS>
+struct Cursor<ROWS, kMnTma> {
+  const CUtensorMap* map;
+  int r0, k_next;
+  bool leader;
+  __device__ __forceinline__ void init(const CUtensorMap* m, int64_t row0, int64_t k_begin, int tid) {
+    map = m; r0 = (int)row0; k_next = (int)k_begin; leader = tid == 0;
+  }
+  __device__ __forceinline__ void issue(uint32_t s_raw, uint32_t bar) {
+    if (leader) {
+#pragma unroll
+      for (int grp = 0; grp < ROWS / 32; ++grp) tma_load_2d(s_raw + (uint32_t)grp * Tile<ROWS>::kLboMn, map, r0 + grp * 32, k_next, bar);
+    }
+    k_next += BK;
+  }
+};
+
 // Shared memory: a ring of kStages RAW stages (A | B, filled by cp.async) and TWO lo buffers (A lo | B lo).  Only the
 // k-tile being multiplied needs its lo part, so the bytes in flight from L2 are not halved by it: kStages-1 raw tiles
 // are outstanding while one tile is split and another is multiplied.
@@ -334,7 +353,7 @@ gemm_tf32_kernel(const float* __restrict__ A, int64_t lda_i, int64_t lda_k, cons
                  int splits, const float* __restrict__ bias, int epi, int split, const __grid_constant__ CUtensorMap map_a,
                  const __grid_constant__ CUtensorMap map_b) {
   extern __shared__ uint8_t smem_dyn[];
-  constexpr bool kTmaA = AMODE == kKTma, kTmaB = BMODE == kKTma, kAnyTma = kTmaA || kTmaB, kAllTma = kTmaA && kTmaB;
+  constexpr bool kTmaA = AMODE == kKTma || AMODE == kMnTma, kTmaB = BMODE == kKTma || BMODE == kMnTma, kAnyTma = kTmaA || kTmaB, kAllTma = kTmaA && kTmaB;
   constexpr uint32_t kTmaBytes = (kTmaA ? Tile<BM>::kBytes : 0u) + (kTmaB ? Tile<BN>::kBytes : 0u);
   using S = Smem<BN>;
   constexpr int kStages = S::kStages;
@@ -353,7 +372,7 @@ gemm_tf32_kernel(const float* __restrict__ A, int64_t lda_i, int64_t lda_k, cons
     if (kTmaA) tma_prefetch_desc(&map_a);
     if (kTmaB) tma_prefetch_desc(&map_b);
     for (int s = 0; s < kStages; ++s) {
-      mbar_init(bar_full + 8 * s, kProducers);
+      mbar_init(bar_full + 8 * s, kProducers / 32);   // one arrival per producer warp
       mbar_init(bar_empty + 8 * s, 1);
       mbar_init(bar_tma + 8 * s, 1);
     }
@@ -391,6 +410,9 @@ gemm_tf32_kernel(const float* __restrict__ A, int64_t lda_i, int64_t lda_k, cons
       ++kt_issue;
       const int sn = g_new % kStages;
       const uint32_t st = smem_u32(smem + sn * S::kStage);
+#ifdef B200LAB_GEMM_NOLOAD   // timing experiment: no operand traffic (results are garbage)
+      return;
+#endif
       if constexpr (kAnyTma) { if (tid == 0) mbar_arrive_expect_tx(bar_tma + 8 * sn, kTmaBytes); }
       if constexpr (kTmaA) ca.issue(st, bar_tma + 8 * sn); else ca.issue(st);
       if constexpr (kTmaB) cb.issue(st + S::kA, bar_tma + 8 * sn); else cb.issue(st + S::kA);
@@ -405,16 +427,21 @@ gemm_tf32_kernel(const float* __restrict__ A, int64_t lda_i, int64_t lda_k, cons
       const int s = g % kStages;
       if constexpr (!kAllTma) cp_async_wait<kStages - 2>();   // this thread's copies of k-tile g have landed ...
       // ... the TMA boxes of the tile too (the mbarrier completes when all their bytes are in shared memory, for every waiter)
+#ifndef B200LAB_GEMM_NOLOAD
       if constexpr (kAnyTma) mbar_wait(bar_tma + 8 * s, (uint32_t)((g / kStages) & 1));
+#endif
       if (split) {
         // ... and, after the producers' barrier, everybody's cp.async copies: the lo sweep is linear over the stage, so a
         // thread reads bytes other threads copied (no barrier when both operands came by TMA).  Lo buffer g&1 was last
         // read by the MMAs of k-tile g-2 (waited for below, one iteration ago).
         if constexpr (!kAllTma) asm volatile("bar.sync 1, %0;" ::"n"(kProducers) : "memory");
+#ifndef B200LAB_GEMM_NOSWEEP   // timing experiment: the MMAs read stale lo buffers
         lo_sweep<S::kStage>(smem + s * S::kStage, smem + S::kLo + (g & 1) * S::kStage, tid);
+#endif
       }
       fence_proxy_async();            // cp.async / st.shared (generic proxy) -> visible to the tensor core (async proxy)
-      mbar_arrive(bar_full + 8 * s);
+      __syncwarp();                   // one arrival per warp: 512 arrivals on one mbarrier word serialise in shared memory
+      if (lane == 0) mbar_arrive(bar_full + 8 * s);
       // k-tile g-1's MMAs done: its raw stage can be refilled (with k-tile g+kStages-1) and, one iteration from now,
       // its lo buffer rewritten -- so this wait is unconditional
       if (g >= 1) mbar_wait(bar_empty + 8 * ((g - 1) % kStages), (uint32_t)(((g - 1) / kStages) & 1));
@@ -424,7 +451,7 @@ gemm_tf32_kernel(const float* __restrict__ A, int64_t lda_i, int64_t lda_k, cons
   } else if (warp == kMmaWarp) {
     if (lane == 0) {
       // ---------------- MMA issuer ----------------
-      constexpr bool a_mn = AMODE == kMnVec || AMODE == kMnScalar, b_mn = BMODE == kMnVec || BMODE == kMnScalar;
+      constexpr bool a_mn = AMODE == kMnVec || AMODE == kMnScalar || AMODE == kMnTma, b_mn = BMODE == kMnVec || BMODE == kMnScalar || BMODE == kMnTma;
       constexpr uint32_t idesc = make_idesc(BM, BN) | ((uint32_t)a_mn << 15) | ((uint32_t)b_mn << 16);
       int g = 0, n = 0;
 #pragma unroll 1
@@ -443,7 +470,11 @@ gemm_tf32_kernel(const float* __restrict__ A, int64_t lda_i, int64_t lda_k, cons
           const uint32_t sa_lo = smem_u32(smem + S::kLo + (g & 1) * S::kStage), sb_lo = sa_lo + S::kA;
           mbar_wait(bar_full + 8 * s, (uint32_t)((g / kStages) & 1));
           tc_fence_after();
+#ifndef B200LAB_GEMM_NOMMA   // timing experiment: no tensor-core work (results are garbage)
 #pragma unroll
+#else
+          if (g < 0)
+#endif
           for (int ks = 0; ks < BK / 8; ++ks) {
             const uint64_t da = operand_desc<BM>(sa, ks, a_mn), db = operand_desc<BN>(sb, ks, b_mn);
             umma_tf32(acc, da, db, idesc, (kt | ks) != 0);
@@ -576,6 +607,19 @@ static bool make_k_major_map(CUtensorMap* map, const float* base, int64_t rows, 
             CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
+// Tensor map of an M/N-contiguous fp32 operand (element (r, k) at base + r + k*ld_k): boxes of 32 rows x BK, written in the
+// MN-major SWIZZLE_128B_BASE32B layout (32-byte chunks of a 128-byte line XORed with the line index mod 4).
+static bool make_mn_major_map(CUtensorMap* map, const float* base, int64_t rows, int64_t K, int64_t ld_k) {
+  EncodeTiledFn fn = encode_tiled_fn();
+  if (!fn) return false;
+  const cuuint64_t gdim[2] = {(cuuint64_t)rows, (cuuint64_t)K};
+  const cuuint64_t gstride[1] = {(cuuint64_t)ld_k * 4u};
+  const cuuint32_t box[2] = {32u, (cuuint32_t)BK};
+  const cuuint32_t estr[2] = {1u, 1u};
+  return fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, (void*)base, gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+            CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
 template <int BN, int AMODE, int BMODE>
 static int launch(const float* A, int64_t lda_i, int64_t lda_k, const float* B, int64_t ldb_k, int64_t ldb_j, float* C,
                   int64_t ldc, int64_t M, int N, int64_t K, int64_t k_per_split, int splits, const float* bias, int epi,
@@ -586,6 +630,8 @@ static int launch(const float* A, int64_t lda_i, int64_t lda_k, const float* B, 
   memset(&map_b, 0, sizeof(map_b));
   if (AMODE == kKTma && !make_k_major_map(&map_a, A, M, K, lda_i, BM)) { set_error("tcgen05 gemm: cuTensorMapEncodeTiled (A) failed"); return B200LAB_ERR_CUDA; }
   if (BMODE == kKTma && !make_k_major_map(&map_b, B, N, K, ldb_j, BN)) { set_error("tcgen05 gemm: cuTensorMapEncodeTiled (B) failed"); return B200LAB_ERR_CUDA; }
+  if (AMODE == kMnTma && !make_mn_major_map(&map_a, A, M, K, lda_k)) { set_error("tcgen05 gemm: cuTensorMapEncodeTiled (A, MN-major) failed"); return B200LAB_ERR_CUDA; }
+  if (BMODE == kMnTma && !make_mn_major_map(&map_b, B, N, K, ldb_k)) { set_error("tcgen05 gemm: cuTensorMapEncodeTiled (B, MN-major) failed"); return B200LAB_ERR_CUDA; }
   static bool configured = false;
   if (!configured) {
     cudaError_t err = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)Smem<BN>::kTotal);
@@ -612,7 +658,7 @@ static int launch_b(int b_mode, const float* A, int64_t lda_i, int64_t lda_k, co
 #define B200LAB_TC_B(MODE) \
   case MODE: return launch<BN, AMODE, MODE>(A, lda_i, lda_k, B, ldb_k, ldb_j, C, ldc, M, N, K, k_per_split, splits, bias, epi, split, s)
   switch (b_mode) {
-    B200LAB_TC_B(kKVec); B200LAB_TC_B(kKScalar); B200LAB_TC_B(kMnVec); B200LAB_TC_B(kKTma);
+    B200LAB_TC_B(kKVec); B200LAB_TC_B(kKScalar); B200LAB_TC_B(kMnVec); B200LAB_TC_B(kKTma); B200LAB_TC_B(kMnTma);
     default: return launch<BN, AMODE, kMnScalar>(A, lda_i, lda_k, B, ldb_k, ldb_j, C, ldc, M, N, K, k_per_split, splits, bias, epi, split, s);
   }
 #undef B200LAB_TC_B
@@ -625,7 +671,7 @@ static int launch_a(int a_mode, int b_mode, const float* A, int64_t lda_i, int64
 #define B200LAB_TC_A(MODE) \
   case MODE: return launch_b<BN, MODE>(b_mode, A, lda_i, lda_k, B, ldb_k, ldb_j, C, ldc, M, N, K, k_per_split, splits, bias, epi, split, s)
   switch (a_mode) {
-    B200LAB_TC_A(kKVec); B200LAB_TC_A(kKScalar); B200LAB_TC_A(kMnVec); B200LAB_TC_A(kKTma);
+    B200LAB_TC_A(kKVec); B200LAB_TC_A(kKScalar); B200LAB_TC_A(kMnVec); B200LAB_TC_A(kKTma); B200LAB_TC_A(kMnTma);
     default: return launch_b<BN, kMnScalar>(b_mode, A, lda_i, lda_k, B, ldb_k, ldb_j, C, ldc, M, N, K, k_per_split, splits, bias, epi, split, s);
   }
 #undef B200LAB_TC_A
@@ -656,6 +702,9 @@ int gemm_tc(const float* A, int64_t lda_i, int64_t lda_k, const float* B, int64_
   if (use_tma && (splits == 1 || k_per_split % tc::BK == 0) && K < (1ll << 31) && M < (1ll << 31)) {
     if (a_mode == tc::kKVec) a_mode = tc::kKTma;
     if (b_mode == tc::kKVec) b_mode = tc::kKTma;
+    static const bool mn_tma = [] { const char* v = getenv("B200LAB_GEMM_MN_TMA"); return !(v && v[0] == '0'); }();
+    if (mn_tma && a_mode == tc::kMnVec) a_mode = tc::kMnTma;
+    if (mn_tma && b_mode == tc::kMnVec && N < (1 << 30)) b_mode = tc::kMnTma;
   }
   const int split = precision == 2 ? 1 : 0;
   if (N > 64) return tc::launch_a<128>(a_mode, b_mode, A, lda_i, lda_k, B, ldb_k, ldb_j, C, ldc, M, N, K, k_per_split, splits, bias, epi, split, s);
