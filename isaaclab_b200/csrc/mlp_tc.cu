@@ -49,7 +49,8 @@ constexpr int BM = 128;               // UMMA M (cta_group::1)
 constexpr int BK = 32;                // K elements per stage = 4 MMA K-steps of 8 tf32
 constexpr int kProducers = 512;       // 16 warps stage operands (4 per scheduler hide the ALU latency of the lo sweep)
 constexpr int kEpiWarps = 4;          // one per TMEM lane quarter: drain accumulator n while the MMAs fill accumulator n+1
-constexpr int kThreads = kProducers + 32 + kEpiWarps * 32;   // producers | the MMA warp | epilogue warps
+constexpr int kThreads = kProducers + 32 + kEpiWarps * 32 + 32;   // producers | the MMA warp | epilogue warps | the TMA warp
+constexpr int kMaxStages = 8;
 constexpr int kEpiLd = 36;            // floats per row of an epilogue warp's 32 x 32 transpose tile
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -114,6 +115,23 @@ __device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t desc_a, uint
       "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t"
       "}" ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
       : "memory");
+}
+// same with the A operand in tensor memory (lane = row, one 32-bit column per tf32 element; tools/umma_tmem_a_probe.cu)
+__device__ __forceinline__ void umma_tf32_ta(uint32_t tmem_d, uint32_t tmem_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t"
+      "}" ::"r"(tmem_d), "r"(tmem_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// 8 consecutive columns of this thread's TMEM lane (warp w owns lanes 32*(w%4)..+31)
+__device__ __forceinline__ void tmem_st8(uint32_t taddr, const float (&v)[8]) {
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"r"(taddr),
+               "r"(__float_as_uint(v[0])), "r"(__float_as_uint(v[1])), "r"(__float_as_uint(v[2])), "r"(__float_as_uint(v[3])),
+               "r"(__float_as_uint(v[4])), "r"(__float_as_uint(v[5])), "r"(__float_as_uint(v[6])), "r"(__float_as_uint(v[7]))
+               : "memory");
 }
 // mbarrier arrive once every tcgen05.mma issued so far by this thread has completed
 __device__ __forceinline__ void umma_commit(uint32_t bar) {
@@ -282,14 +300,21 @@ struct Cursor<ROWS, kMnTma> {
 // are outstanding while one tile is split and another is multiplied.
 template <int BN>
 struct Smem {
-  static constexpr int kStages = BN > 64 ? 4 : 6;
   static constexpr uint32_t kA = Tile<BM>::kBytes, kB = Tile<BN>::kBytes;
-  static constexpr uint32_t kStage = kA + kB;                      // A raw, B raw   (lo buffer: A lo, B lo)
-  static constexpr uint32_t kLo = kStages * kStage;                // two lo buffers follow the raw ring
-  static constexpr uint32_t kEpi = kLo + 2 * kStage;               // one 32 x 32 transpose tile per epilogue warp
+  static constexpr uint32_t kStage = kA + kB;                      // one k-tile: A | B (raw, or their lo parts)
+  static constexpr int kSlots = BN > 64 ? 6 : 8;                   // k-tile slots of 32 KB / 24 KB
+  // all-TMA pipeline: TF32 -> kSlots raw stages; 3xTF32 -> kNsSplit raw stages + as many lo buffers of the B part only (the
+  // A operand of the split goes to the tensor core through tensor memory: 64 columns per stage next to the accumulators)
+  static constexpr int kNsSplit = (kSlots * kStage) / (kStage + kB);
+  static_assert(2 * BN + 64 * kNsSplit <= 512, "accumulators + A stages exceed tensor memory");
+  // cp.async pipeline: kSlots - 2 raw stages + 2 lo buffers
+  static constexpr int kStages = kSlots - 2;
+  static constexpr uint32_t kLo = kStages * kStage;
+  static constexpr uint32_t kEpi = kSlots * kStage;                // one 32 x 32 transpose tile per epilogue warp
   static constexpr uint32_t kEpiBytes = kEpiWarps * 32 * kEpiLd * 4;
-  static constexpr uint32_t kCtl = kEpi + kEpiBytes;               // full / empty / tma [kStages], acc_full[2], acc_empty[2], tmem pointer
-  static constexpr uint32_t kTotal = kCtl + 24 * kStages + 32 + 16 + 1024;   // + slack to align the base to 1024
+  static constexpr uint32_t kCtl = kEpi + kEpiBytes;               // full / empty / tma [kMaxStages], acc_full[2], acc_empty[2], tmem pointer
+  static constexpr uint32_t kTotal = kCtl + 24 * kMaxStages + 32 + 16 + 1024;   // + slack to align the base to 1024
+  static_assert(kSlots <= kMaxStages, "barrier arrays too small");
 };
 
 __device__ __forceinline__ float exp2f_fast(float x) { float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
@@ -364,14 +389,17 @@ gemm_tf32_kernel(const float* __restrict__ A, int64_t lda_i, int64_t lda_k, cons
   const int64_t num_units = (int64_t)n_i * n_j * splits;
 
   uint8_t* ctl = smem + S::kCtl;
-  const uint32_t bar_full = smem_u32(ctl), bar_empty = bar_full + 8 * kStages, bar_tma = bar_full + 16 * kStages;
-  const uint32_t bar_acc_full = bar_full + 24 * kStages, bar_acc_empty = bar_acc_full + 16;
-  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(ctl + 24 * kStages + 32);
+  const uint32_t bar_full = smem_u32(ctl), bar_empty = bar_full + 8 * kMaxStages, bar_tma = bar_full + 16 * kMaxStages;
+  const uint32_t bar_acc_full = bar_full + 24 * kMaxStages, bar_acc_empty = bar_acc_full + 16;
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(ctl + 24 * kMaxStages + 32);
+  // all-TMA pipeline: ns raw stages (+ ns lo buffers behind them with the 3xTF32 split); cp.async pipeline: kStages + 2 lo
+  const int ns = kAllTma ? (split ? S::kNsSplit : S::kSlots) : kStages;
+  constexpr uint32_t kTmemCols = kAllTma ? 512u : 2u * BN;   // two accumulators (+ A raw | A lo, 32 + 32 columns per stage)
 
   if (tid == 0) {
     if (kTmaA) tma_prefetch_desc(&map_a);
     if (kTmaB) tma_prefetch_desc(&map_b);
-    for (int s = 0; s < kStages; ++s) {
+    for (int s = 0; s < kMaxStages; ++s) {
       mbar_init(bar_full + 8 * s, kProducers / 32);   // one arrival per producer warp
       mbar_init(bar_empty + 8 * s, 1);
       mbar_init(bar_tma + 8 * s, 1);
@@ -382,78 +410,128 @@ gemm_tf32_kernel(const float* __restrict__ A, int64_t lda_i, int64_t lda_k, cons
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  if (warp == kMmaWarp) tmem_alloc(smem_u32(tmem_ptr_smem), 2 * BN);   // two accumulators; 2*BN in {128, 256}: a power of two
+  if (warp == kMmaWarp) tmem_alloc(smem_u32(tmem_ptr_smem), kTmemCols);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_d = *tmem_ptr_smem;
+  const uint32_t tmem_a = tmem_d + 2u * BN;   // stage s: raw A in columns [64 s, 64 s + 32), its lo part in the next 32
 
   if (warp < kMmaWarp) {
-    // ---------------- producers ----------------
-    int total_g = 0;   // k-tiles of all my units
-    for (int64_t u = blockIdx.x; u < num_units; u += gridDim.x) total_g += unit_of(u, n_i, n_j, K, k_per_split).num_kt;
-    Cursor<BM, AMODE> ca;
-    Cursor<BN, BMODE> cb;
-    int64_t u_issue = blockIdx.x;
-    int kt_issue = 0, nkt_issue = 0;
-    auto open_unit = [&]() {
-      const Unit w = unit_of(u_issue, n_i, n_j, K, k_per_split);
-      nkt_issue = w.num_kt;
-      kt_issue = 0;
-      if constexpr (kTmaA) ca.init(&map_a, w.i0, w.k_begin, tid); else ca.init(A, lda_i, lda_k, w.i0, M, w.k_begin, w.k_end, tid);
-      if constexpr (kTmaB) cb.init(&map_b, (int64_t)w.j0 * BN, w.k_begin, tid);
-      else cb.init(B, ldb_j, ldb_k, (int64_t)w.j0 * BN, N, w.k_begin, w.k_end, tid);
-    };
-    if (u_issue < num_units) open_unit();
-    auto issue = [&](int g_new) {   // loads of my g_new-th k-tile (callers keep g_new < total_g)
-      if (kt_issue == nkt_issue) { u_issue += gridDim.x; open_unit(); }
-      ++kt_issue;
-      const int sn = g_new % kStages;
-      const uint32_t st = smem_u32(smem + sn * S::kStage);
-#ifdef B200LAB_GEMM_NOLOAD   // timing experiment: no operand traffic (results are garbage)
-      return;
-#endif
-      if constexpr (kAnyTma) { if (tid == 0) mbar_arrive_expect_tx(bar_tma + 8 * sn, kTmaBytes); }
-      if constexpr (kTmaA) ca.issue(st, bar_tma + 8 * sn); else ca.issue(st);
-      if constexpr (kTmaB) cb.issue(st + S::kA, bar_tma + 8 * sn); else cb.issue(st + S::kA);
-    };
-#pragma unroll
-    for (int p = 0; p < kStages - 1; ++p) {
-      if (p < total_g) issue(p);
-      if constexpr (!kAllTma) cp_async_commit();
-    }
-#pragma unroll 1
-    for (int g = 0; g < total_g; ++g) {
-      const int s = g % kStages;
-      if constexpr (!kAllTma) cp_async_wait<kStages - 2>();   // this thread's copies of k-tile g have landed ...
-      // ... the TMA boxes of the tile too (the mbarrier completes when all their bytes are in shared memory, for every waiter)
-#ifndef B200LAB_GEMM_NOLOAD
-      if constexpr (kAnyTma) mbar_wait(bar_tma + 8 * s, (uint32_t)((g / kStages) & 1));
-#endif
+    if constexpr (kAllTma) {
+      // ---------------- sweepers (3xTF32 only).  Per k-tile the TMA warp brings in:  B -> lo = x - trunc(x) to the stage's
+      // lo buffer (linear sweep);  A -> each thread reads 8 k of its row from the raw stage and stores them and their lo
+      // parts to tensor memory (lane = row: warp w owns rows 32*(w%4)..+31 and the k octet w/4), from where the MMAs take
+      // the A operand -- no lo copy of A in shared memory and no tensor-core reads of A from it.  Their only dependency is
+      // the stage's TMA barrier: the box is requested after the MMAs of the stage's previous k-tile have completed.
       if (split) {
-        // ... and, after the producers' barrier, everybody's cp.async copies: the lo sweep is linear over the stage, so a
-        // thread reads bytes other threads copied (no barrier when both operands came by TMA).  Lo buffer g&1 was last
-        // read by the MMAs of k-tile g-2 (waited for below, one iteration ago).
-        if constexpr (!kAllTma) asm volatile("bar.sync 1, %0;" ::"n"(kProducers) : "memory");
-#ifndef B200LAB_GEMM_NOSWEEP   // timing experiment: the MMAs read stale lo buffers
-        lo_sweep<S::kStage>(smem + s * S::kStage, smem + S::kLo + (g & 1) * S::kStage, tid);
+        int total_g = 0;   // k-tiles of all my units
+        for (int64_t u = blockIdx.x; u < num_units; u += gridDim.x) total_g += unit_of(u, n_i, n_j, K, k_per_split).num_kt;
+        const int row = (warp & 3) * 32 + lane, kq = warp >> 2;
+        const uint32_t a_lane = ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)(kq * 8);
+        uint32_t a_off[2];   // K-major: the two 16-byte chunks of k = 8 kq .. 8 kq + 7;  MN-major: offset of k = 8 kq (see below)
+        if constexpr (AMODE == kKTma) { a_off[0] = k_offset(row, kq * 8); a_off[1] = k_offset(row, kq * 8 + 4); }
+        else { a_off[0] = (uint32_t)(row >> 5) * Tile<BM>::kLboMn + (uint32_t)(kq * 2) * Tile<BM>::kSboMn + (uint32_t)(row & 31) * 4; a_off[1] = 0; }
+        int s = 0;
+        uint32_t ph = 0;
+#pragma unroll 1
+        for (int g = 0; g < total_g; ++g) {
+#ifndef B200LAB_GEMM_NOLOAD
+          mbar_wait(bar_tma + 8 * s, ph);
 #endif
+#ifndef B200LAB_GEMM_NOSWEEP
+          const uint8_t* raw = smem + s * S::kStage;
+          float v[8], l[8];
+          if constexpr (AMODE == kKTma) {
+            const float4 x0 = *reinterpret_cast<const float4*>(raw + a_off[0]), x1 = *reinterpret_cast<const float4*>(raw + a_off[1]);
+            v[0] = x0.x; v[1] = x0.y; v[2] = x0.z; v[3] = x0.w; v[4] = x1.x; v[5] = x1.y; v[6] = x1.z; v[7] = x1.w;
+          } else {
+#pragma unroll
+            for (int k = 0; k < 8; ++k)   // k-atom (k/4), line k%4 of it; 32-byte chunks of a line XORed with the line index
+              v[k] = *reinterpret_cast<const float*>(raw + swz_mn(a_off[0] + (uint32_t)(k >> 2) * Tile<BM>::kSboMn + (uint32_t)(k & 3) * 128));
+          }
+#pragma unroll
+          for (int k = 0; k < 8; ++k) l[k] = v[k] - __uint_as_float(__float_as_uint(v[k]) & 0xFFFFE000u);
+          tmem_st8(tmem_a + (uint32_t)(s * 64) + a_lane, v);
+          tmem_st8(tmem_a + (uint32_t)(s * 64 + 32) + a_lane, l);
+          lo_sweep<S::kB>(raw + S::kA, smem + ns * S::kStage + s * S::kB, tid);
+          asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+#endif
+          tc_fence_before();
+          fence_proxy_async();            // st.shared (generic proxy) -> visible to the tensor core (async proxy)
+          __syncwarp();                   // one arrival per warp
+          if (lane == 0) mbar_arrive(bar_full + 8 * s);
+          if (++s == ns) { s = 0; ph ^= 1u; }
+        }
       }
-      fence_proxy_async();            // cp.async / st.shared (generic proxy) -> visible to the tensor core (async proxy)
-      __syncwarp();                   // one arrival per warp: 512 arrivals on one mbarrier word serialise in shared memory
-      if (lane == 0) mbar_arrive(bar_full + 8 * s);
-      // k-tile g-1's MMAs done: its raw stage can be refilled (with k-tile g+kStages-1) and, one iteration from now,
-      // its lo buffer rewritten -- so this wait is unconditional
-      if (g >= 1) mbar_wait(bar_empty + 8 * ((g - 1) % kStages), (uint32_t)(((g - 1) / kStages) & 1));
-      if (g + kStages - 1 < total_g) issue(g + kStages - 1);
-      if constexpr (!kAllTma) cp_async_commit();
+    } else {
+      // ---------------- producers (an operand that cannot go by TMA: unaligned, or TMA switched off) ----------------
+      int total_g = 0;   // k-tiles of all my units
+      for (int64_t u = blockIdx.x; u < num_units; u += gridDim.x) total_g += unit_of(u, n_i, n_j, K, k_per_split).num_kt;
+      Cursor<BM, AMODE> ca;
+      Cursor<BN, BMODE> cb;
+      int64_t u_issue = blockIdx.x;
+      int kt_issue = 0, nkt_issue = 0;
+      auto open_unit = [&]() {
+        const Unit w = unit_of(u_issue, n_i, n_j, K, k_per_split);
+        nkt_issue = w.num_kt;
+        kt_issue = 0;
+        if constexpr (kTmaA) ca.init(&map_a, w.i0, w.k_begin, tid); else ca.init(A, lda_i, lda_k, w.i0, M, w.k_begin, w.k_end, tid);
+        if constexpr (kTmaB) cb.init(&map_b, (int64_t)w.j0 * BN, w.k_begin, tid);
+        else cb.init(B, ldb_j, ldb_k, (int64_t)w.j0 * BN, N, w.k_begin, w.k_end, tid);
+      };
+      if (u_issue < num_units) open_unit();
+      auto issue = [&](int g_new) {   // loads of my g_new-th k-tile (callers keep g_new < total_g)
+        if (kt_issue == nkt_issue) { u_issue += gridDim.x; open_unit(); }
+        ++kt_issue;
+        const int sn = g_new % kStages;
+        const uint32_t st = smem_u32(smem + sn * S::kStage);
+#ifdef B200LAB_GEMM_NOLOAD   // timing experiment: no operand traffic (results are garbage)
+        return;
+#endif
+        if constexpr (kAnyTma) { if (tid == 0) mbar_arrive_expect_tx(bar_tma + 8 * sn, kTmaBytes); }
+        if constexpr (kTmaA) ca.issue(st, bar_tma + 8 * sn); else ca.issue(st);
+        if constexpr (kTmaB) cb.issue(st + S::kA, bar_tma + 8 * sn); else cb.issue(st + S::kA);
+      };
+#pragma unroll
+      for (int p = 0; p < kStages - 1; ++p) {
+        if (p < total_g) issue(p);
+        if constexpr (!kAllTma) cp_async_commit();
+      }
+#pragma unroll 1
+      for (int g = 0; g < total_g; ++g) {
+        const int s = g % kStages;
+        if constexpr (!kAllTma) cp_async_wait<kStages - 2>();   // this thread's copies of k-tile g have landed ...
+        // ... the TMA boxes of the tile too (the mbarrier completes when all their bytes are in shared memory, for every waiter)
+#ifndef B200LAB_GEMM_NOLOAD
+        if constexpr (kAnyTma) mbar_wait(bar_tma + 8 * s, (uint32_t)((g / kStages) & 1));
+#endif
+        if (split) {
+          // ... and, after the producers' barrier, everybody's cp.async copies: the lo sweep is linear over the stage, so a
+          // thread reads bytes other threads copied (no barrier when both operands came by TMA).  Lo buffer g&1 was last
+          // read by the MMAs of k-tile g-2 (waited for below, one iteration ago).
+          if constexpr (!kAllTma) asm volatile("bar.sync 1, %0;" ::"n"(kProducers) : "memory");
+#ifndef B200LAB_GEMM_NOSWEEP   // timing experiment: the MMAs read stale lo buffers
+          lo_sweep<S::kStage>(smem + s * S::kStage, smem + S::kLo + (g & 1) * S::kStage, tid);
+#endif
+        }
+        fence_proxy_async();            // cp.async / st.shared (generic proxy) -> visible to the tensor core (async proxy)
+        __syncwarp();                   // one arrival per warp: 512 arrivals on one mbarrier word serialise in shared memory
+        if (lane == 0) mbar_arrive(bar_full + 8 * s);
+        // k-tile g-1's MMAs done: its raw stage can be refilled (with k-tile g+kStages-1) and, one iteration from now,
+        // its lo buffer rewritten -- so this wait is unconditional
+        if (g >= 1) mbar_wait(bar_empty + 8 * ((g - 1) % kStages), (uint32_t)(((g - 1) / kStages) & 1));
+        if (g + kStages - 1 < total_g) issue(g + kStages - 1);
+        if constexpr (!kAllTma) cp_async_commit();
+      }
     }
   } else if (warp == kMmaWarp) {
     if (lane == 0) {
       // ---------------- MMA issuer ----------------
       constexpr bool a_mn = AMODE == kMnVec || AMODE == kMnScalar || AMODE == kMnTma, b_mn = BMODE == kMnVec || BMODE == kMnScalar || BMODE == kMnTma;
       constexpr uint32_t idesc = make_idesc(BM, BN) | ((uint32_t)a_mn << 15) | ((uint32_t)b_mn << 16);
-      int g = 0, n = 0;
+      int g = 0, n = 0, s = 0;
+      uint32_t ph = 0;   // parity of stage s's current use
 #pragma unroll 1
       for (int64_t u = blockIdx.x; u < num_units; u += gridDim.x, ++n) {
         const int num_kt = unit_of(u, n_i, n_j, K, k_per_split).num_kt;
@@ -465,10 +543,15 @@ gemm_tf32_kernel(const float* __restrict__ A, int64_t lda_i, int64_t lda_k, cons
         const uint32_t acc = tmem_d + (uint32_t)(buf * BN);
 #pragma unroll 1
         for (int kt = 0; kt < num_kt; ++kt, ++g) {
-          const int s = g % kStages;
           const uint32_t sa = smem_u32(smem + s * S::kStage), sb = sa + S::kA;
-          const uint32_t sa_lo = smem_u32(smem + S::kLo + (g & 1) * S::kStage), sb_lo = sa_lo + S::kA;
-          mbar_wait(bar_full + 8 * s, (uint32_t)((g / kStages) & 1));
+          // lo part: behind the raw ring, one buffer per stage (all-TMA) or two alternating ones (cp.async pipeline)
+          const uint32_t sa_lo = smem_u32(smem + (kStages + (g & 1)) * S::kStage);            // cp.async pipeline only
+          const uint32_t sb_lo = kAllTma ? smem_u32(smem + ns * S::kStage + s * S::kB) : sa_lo + S::kA;
+          const uint32_t ta = tmem_a + (uint32_t)(s * 64);                                      // all-TMA split only
+#ifndef B200LAB_GEMM_NOLOAD
+          if constexpr (kAllTma) mbar_wait(bar_tma + 8 * s, ph);     // raw operands: straight from the TMA's barrier
+#endif
+          if (!kAllTma || split) mbar_wait(bar_full + 8 * s, ph);     // cp.async copies landed / lo part written
           tc_fence_after();
 #ifndef B200LAB_GEMM_NOMMA   // timing experiment: no tensor-core work (results are garbage)
 #pragma unroll
@@ -477,18 +560,55 @@ gemm_tf32_kernel(const float* __restrict__ A, int64_t lda_i, int64_t lda_k, cons
 #endif
           for (int ks = 0; ks < BK / 8; ++ks) {
             const uint64_t da = operand_desc<BM>(sa, ks, a_mn), db = operand_desc<BN>(sb, ks, b_mn);
-            umma_tf32(acc, da, db, idesc, (kt | ks) != 0);
-            if (split) {
-              umma_tf32(acc, da, operand_desc<BN>(sb_lo, ks, b_mn), idesc, 1u);
-              umma_tf32(acc, operand_desc<BM>(sa_lo, ks, a_mn), db, idesc, 1u);
+            if (kAllTma && split) {   // A from tensor memory (always "K-major" there)
+              constexpr uint32_t idesc_ta = make_idesc(BM, BN) | ((uint32_t)b_mn << 16);
+              umma_tf32_ta(acc, ta + (uint32_t)(ks * 8), db, idesc_ta, (kt | ks) != 0);
+              umma_tf32_ta(acc, ta + (uint32_t)(ks * 8), operand_desc<BN>(sb_lo, ks, b_mn), idesc_ta, 1u);
+              umma_tf32_ta(acc, ta + 32u + (uint32_t)(ks * 8), db, idesc_ta, 1u);
+            } else {
+              umma_tf32(acc, da, db, idesc, (kt | ks) != 0);
+              if (split) {
+                umma_tf32(acc, da, operand_desc<BN>(sb_lo, ks, b_mn), idesc, 1u);
+                umma_tf32(acc, operand_desc<BM>(sa_lo, ks, a_mn), db, idesc, 1u);
+              }
             }
           }
-          umma_commit(bar_empty + 8 * s);   // releases the stage once these MMAs have read it
+          umma_commit(bar_empty + 8 * s);   // releases the stage (and its lo buffer) once these MMAs have read it
+          if (++s == ns) { s = 0; ph ^= 1u; }
         }
         umma_commit(bar_acc_full + 8 * buf);   // accumulator complete
       }
     }
-  } else {
+  } else if (warp == kMmaWarp + kEpiWarps + 1) {
+    // ---------------- TMA warp (all-TMA pipeline): refills stage s as soon as the MMAs of its previous k-tile are done --
+    // nobody else is in that loop, so ns - 1 k-tiles stay in flight whatever the sweepers and the MMA warp are doing
+    if constexpr (kAllTma) {
+      if (lane == 0) {
+        Cursor<BM, AMODE> ca;
+        Cursor<BN, BMODE> cb;
+        int s = 0;
+        uint32_t ph = 0;
+        bool wrapped = false;
+#pragma unroll 1
+        for (int64_t u = blockIdx.x; u < num_units; u += gridDim.x) {
+          const Unit w = unit_of(u, n_i, n_j, K, k_per_split);
+          ca.init(&map_a, w.i0, w.k_begin, 0);
+          cb.init(&map_b, (int64_t)w.j0 * BN, w.k_begin, 0);
+#pragma unroll 1
+          for (int kt = 0; kt < w.num_kt; ++kt) {
+            if (wrapped) mbar_wait(bar_empty + 8 * s, ph ^ 1u);   // the stage's previous use has been multiplied
+#ifndef B200LAB_GEMM_NOLOAD
+            const uint32_t st = smem_u32(smem + s * S::kStage);
+            mbar_arrive_expect_tx(bar_tma + 8 * s, kTmaBytes);
+            ca.issue(st, bar_tma + 8 * s);
+            cb.issue(st + S::kA, bar_tma + 8 * s);
+#endif
+            if (++s == ns) { s = 0; ph ^= 1u; wrapped = true; }
+          }
+        }
+      }
+    }
+  } else if (warp > kMmaWarp) {
     // ---------------- epilogue: TMEM -> registers -> (32 x 32 transpose through shared memory) -> global.  A warp may read
     // the TMEM lanes 32*(warp%4)..+31 (= tile rows, one per lane); it walks the BN columns in groups of 32.  Written
     // straight from the TMEM layout every store instruction would touch 32 rows (32 sectors); after the transpose it
@@ -573,7 +693,7 @@ gemm_tf32_kernel(const float* __restrict__ A, int64_t lda_i, int64_t lda_k, cons
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == kMmaWarp) tmem_dealloc(tmem_d, 2 * BN);
+  if (warp == kMmaWarp) tmem_dealloc(tmem_d, kTmemCols);
 }
 
 // cuTensorMapEncodeTiled, resolved through the runtime (no link-time dependency on libcuda)
