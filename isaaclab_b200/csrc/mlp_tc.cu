@@ -150,6 +150,22 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, float (&v)[16]) {
   for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
 }
 
+// 32 consecutive columns with ONE wait (two x16 loads in flight together)
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
+  uint32_t r[32];
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, %17, %18, "
+      "%19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]), "=r"(r[17]),
+        "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]),
+        "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr));
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+  for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
+}
+
 // Shared-memory matrix descriptor (cute::UMMA::SmemDescriptor bit layout, version 1):
 //   [0,14) start address >> 4 | [16,30) leading-dimension byte offset >> 4 | [32,46) stride-dimension byte offset >> 4
 //   [46,48) version = 1 | [61,64) layout type (0 = SWIZZLE_NONE, 1 = SWIZZLE_128B_BASE32B, 2 = SWIZZLE_128B)
@@ -625,16 +641,22 @@ gemm_tf32_kernel(const float* __restrict__ A, int64_t lda_i, int64_t lda_k, cons
       const int buf = n & 1, use = n >> 1;
       const int j0 = w.j0 * BN;
       float* Cz = C + (int64_t)w.z * M * ldc;
+      float4 bvs[BN / 32];   // the tile's bias values, fetched while the MMAs are still running
+#pragma unroll
+      for (int c = 0; c < BN / 32; ++c) {
+        const int gj = j0 + c * 32 + (lane & 7) * 4;
+        bvs[c] = (vec && epi >= 1 && gj < N) ? make_float4(__ldg(bias + gj), __ldg(bias + gj + 1), __ldg(bias + gj + 2), __ldg(bias + gj + 3))
+                                             : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
       mbar_wait(bar_acc_full + 8 * buf, (uint32_t)(use & 1));
       tc_fence_after();
       const uint32_t acc = tmem_d + (uint32_t)(buf * BN) + ((uint32_t)(q * 32) << 16);
-#pragma unroll 1
+#pragma unroll
       for (int c0 = 0; c0 < BN; c0 += 32) {
         const bool last = c0 + 32 == BN;
         if (j0 + c0 < N) {   // warp-uniform
-          float lo16[16], hi16[16];
-          tmem_ld16(acc + (uint32_t)c0, lo16);
-          tmem_ld16(acc + (uint32_t)(c0 + 16), hi16);
+          float v32[32];
+          tmem_ld32(acc + (uint32_t)c0, v32);
           if (last) {   // every column of this warp's quarter is in registers: hand the accumulator back
             tc_fence_before();
             __syncwarp();
@@ -642,16 +664,12 @@ gemm_tf32_kernel(const float* __restrict__ A, int64_t lda_i, int64_t lda_k, cons
           }
           float4* trow = reinterpret_cast<float4*>(tile + lane * kEpiLd);   // row stride 144 B: conflict-free 128-bit accesses
 #pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            trow[i] = make_float4(lo16[4 * i], lo16[4 * i + 1], lo16[4 * i + 2], lo16[4 * i + 3]);
-            trow[4 + i] = make_float4(hi16[4 * i], hi16[4 * i + 1], hi16[4 * i + 2], hi16[4 * i + 3]);
-          }
+          for (int i = 0; i < 8; ++i) trow[i] = make_float4(v32[4 * i], v32[4 * i + 1], v32[4 * i + 2], v32[4 * i + 3]);
           __syncwarp();
           if (vec) {
             const int cg = (lane & 7) * 4, gj = j0 + c0 + cg;
             const bool col_ok = gj < N;   // N % 4 == 0: the whole vector is inside
-            float4 bv = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (epi >= 1 && col_ok) bv = make_float4(__ldg(bias + gj), __ldg(bias + gj + 1), __ldg(bias + gj + 2), __ldg(bias + gj + 3));
+            const float4 bv = bvs[c0 / 32];
 #pragma unroll
             for (int rr = 0; rr < 8; ++rr) {
               const int r = rr * 4 + (lane >> 3);
