@@ -615,6 +615,20 @@ int64_t b200lab_linear_bwd_workspace_bytes(int64_t M, int32_t K, int32_t Nout);
 int b200lab_linear_bwd(const float* X, const float* W, const float* Y, const float* dY, float* dZ, float* dX,
                        float* dW, float* db, int64_t M, int32_t K, int32_t Nout, int32_t elu, int32_t precision,
                        void* workspace, void* stream);
+/* The same backward for a layer inside a Linear+ELU chain (autograd of RSL/networks/mlp.py:60-80 walks the layers from the
+ * output back; each ELU's backward is an elementwise pass between two matrix products).  flags:
+ *   B200LAB_BWD_ELU_OUT  as elu = 1 above: dZ = dY * ELU'(Y), db = column sums of dZ
+ *   B200LAB_BWD_ELU_IN   X is itself an ELU output (the previous layer's activation): dX receives (dZ W) * ELU'(X), i.e. the
+ *                        previous layer's dZ (in place), and db_in [K] its column sums (that layer's bias gradient); the
+ *                        reductions of dW, db and db_in then share one launch
+ *   B200LAB_BWD_DZ_GIVEN dY already is this layer's dZ and db is already filled (the previous call ran with ELU_IN)
+ * Everything else as b200lab_linear_bwd (same workspace size). */
+#define B200LAB_BWD_ELU_OUT 1
+#define B200LAB_BWD_ELU_IN 2
+#define B200LAB_BWD_DZ_GIVEN 4
+int b200lab_linear_bwd_chain(const float* X, const float* W, const float* Y, const float* dY, float* dZ, float* dX,
+                             float* dW, float* db, float* db_in, int64_t M, int32_t K, int32_t Nout, int32_t flags,
+                             int32_t precision, void* workspace, void* stream);
 
 /* Rollout-side sampling (ActorCritic.act / get_actions_log_prob, RSL/modules/actor_critic.py:115-143):
  * actions = mu + std*eps; log_prob = sum_a Normal(mu,std).log_prob(actions). eps [M,A] standard normal draws. */

@@ -130,6 +130,8 @@ _SIGS = {
     "b200lab_linear_bwd_workspace_bytes": (C.c_int64, [C.c_int64, C.c_int32, C.c_int32]),
     "b200lab_linear_bwd": (C.c_int, [C.c_void_p] * 8 + [C.c_int64, C.c_int32, C.c_int32, C.c_int32, C.c_int32,
                                      C.c_void_p, C.c_void_p]),
+    "b200lab_linear_bwd_chain": (C.c_int, [C.c_void_p] * 9 + [C.c_int64, C.c_int32, C.c_int32, C.c_int32, C.c_int32,
+                                           C.c_void_p, C.c_void_p]),
     "b200lab_sample_actions": (C.c_int, [C.c_void_p] * 6 + [C.c_int64, C.c_int32, C.c_void_p]),
     "b200lab_ppo_loss": (C.c_int, [C.c_void_p, C.c_void_p]),
     "b200lab_adapt_lr": (C.c_int, [C.c_void_p, C.c_void_p, C.c_float, C.c_float, C.c_void_p]),

@@ -130,7 +130,7 @@ colsum_partial_kernel(const float* __restrict__ dZ, int64_t M, int N, int64_t ro
 // VEC = false: scalar columns for N % 4 != 0.
 template <bool VEC>
 __global__ void __launch_bounds__(256)
-elu_bwd_colsum_kernel(const float* __restrict__ Y, const float* __restrict__ dY, float* __restrict__ dZ, int64_t M, int N,
+elu_bwd_colsum_kernel(const float* __restrict__ Y, const float* dY, float* dZ, int64_t M, int N,   // dZ may be dY (in place)
                       int64_t rows_per_block, float* __restrict__ part) {
   constexpr int kCols = VEC ? 128 : 32;
   __shared__ float sh[8][kCols + 4];
@@ -144,7 +144,7 @@ elu_bwd_colsum_kernel(const float* __restrict__ Y, const float* __restrict__ dY,
 #pragma unroll 8
         for (int64_t r = r0 + warp; r < r1; r += 8) {
           const float4 y = __ldg(reinterpret_cast<const float4*>(Y + r * N + c));
-          float4 g = __ldg(reinterpret_cast<const float4*>(dY + r * N + c));
+          float4 g = *reinterpret_cast<const float4*>(dY + r * N + c);
           g.x *= y.x > 0.0f ? 1.0f : y.x + 1.0f;
           g.y *= y.y > 0.0f ? 1.0f : y.y + 1.0f;
           g.z *= y.z > 0.0f ? 1.0f : y.z + 1.0f;
@@ -161,7 +161,7 @@ elu_bwd_colsum_kernel(const float* __restrict__ Y, const float* __restrict__ dY,
       if (c < N)
         for (int64_t r = r0 + warp; r < r1; r += 8) {
           const float y = __ldg(Y + r * N + c);
-          const float g = __ldg(dY + r * N + c) * (y > 0.0f ? 1.0f : y + 1.0f);
+          const float g = dY[r * N + c] * (y > 0.0f ? 1.0f : y + 1.0f);
           dZ[r * N + c] = g;
           acc += g;
         }
@@ -178,30 +178,6 @@ elu_bwd_colsum_kernel(const float* __restrict__ Y, const float* __restrict__ dY,
   }
 }
 
-// out[c] = sum_z part[z, c] for MANY slabs and few columns (bias gradient: 384 slabs x <= 512 columns): one warp per
-// column, lanes stride the slabs, fixed-order shuffle tree => deterministic.
-__global__ void __launch_bounds__(256)
-reduce_cols_kernel(const float* __restrict__ part, int slabs, int n, float* __restrict__ out) {
-  int lane = threadIdx.x & 31;
-  int c = blockIdx.x * 8 + (threadIdx.x >> 5);
-  if (c >= n) return;
-  float s = 0.0f;
-  for (int z = lane; z < slabs; z += 32) s += __ldg(part + (int64_t)z * n + c);
-#pragma unroll
-  for (int d = 16; d > 0; d >>= 1) s += __shfl_down_sync(0xffffffffu, s, d);
-  if (lane == 0) out[c] = s;
-}
-
-// out[i] = sum_z part[z, i]  (fixed order => deterministic)
-__global__ void __launch_bounds__(256)
-reduce_slabs_kernel(const float* __restrict__ part, int splits, int64_t n, float* __restrict__ out) {
-  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
-  float s = 0.0f;
-  for (int z = 0; z < splits; ++z) s += __ldg(part + (int64_t)z * n + i);
-  out[i] = s;
-}
-
 // rows per block of the bias-gradient column sum: 64 rows -> M/64 blocks (384 at M = 24576: 2.6 waves of 148 SMs; at 512
 // rows per block the grid was 48 blocks and this memory-bound pass took longer than the GEMMs)
 constexpr int kColsumRows = 64;
@@ -216,6 +192,109 @@ static int dw_splits(int64_t M, int K, int Nout, bool use_tc) {
   return (int)(s < 1 ? 1 : s);
 }
 
+// The tail of a layer's backward in ONE launch: dW = sum of the K-split slabs, and up to two bias gradients (column sums
+// of row-block partials).  Blocks [0, slab_blocks) take the slabs, the rest one warp per column (fixed order: deterministic).
+struct ColTask {
+  const float* part;
+  int rows, n;
+  float* out;
+};
+__global__ void __launch_bounds__(256)
+reduce_tail_kernel(const float* __restrict__ slabs, int splits, int64_t n, float* __restrict__ out, int slab_blocks, ColTask c0,
+                   ColTask c1) {
+  if ((int)blockIdx.x < slab_blocks) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float s = 0.0f;
+    for (int z = 0; z < splits; ++z) s += __ldg(slabs + (int64_t)z * n + i);
+    out[i] = s;
+    return;
+  }
+  int b = (int)blockIdx.x - slab_blocks;
+  const int c0_blocks = (c0.n + 7) / 8;
+  const ColTask t = b < c0_blocks ? c0 : c1;
+  if (b >= c0_blocks) b -= c0_blocks;
+  const int lane = threadIdx.x & 31, c = b * 8 + (threadIdx.x >> 5);
+  if (c >= t.n) return;
+  float s = 0.0f;
+  for (int z = lane; z < t.rows; z += 32) s += __ldg(t.part + (int64_t)z * t.n + c);
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) s += __shfl_down_sync(0xffffffffu, s, d);
+  if (lane == 0) t.out[c] = s;
+}
+
+static int linear_bwd_impl(const float* X, const float* W, const float* Y, const float* dY, float* dZ, float* dX, float* dW,
+                           float* db, float* db_in, int64_t M, int32_t K, int32_t Nout, int32_t flags, int32_t precision,
+                           void* workspace, cudaStream_t s) {
+  const bool elu = flags & B200LAB_BWD_ELU_OUT, elu_in = flags & B200LAB_BWD_ELU_IN, dz_given = flags & B200LAB_BWD_DZ_GIVEN;
+  B200LAB_CHECK_ARG(X && W && dY && dW && db && workspace && M > 0 && K > 0 && Nout > 0, "bad argument");
+  B200LAB_CHECK_ARG(!elu || (Y && dZ), "ELU backward needs the saved output Y and the dZ scratch");
+  B200LAB_CHECK_ARG(precision >= 0 && precision <= 2, "precision must be 0 (fp32 FFMA), 1 (tf32) or 2 (tf32x3)");
+  const bool use_tc = precision != 0 && (Nout >= kMinTcWidth || K >= kMinTcWidth);
+  const float* dz = dY;
+  float* ws = (float*)workspace;
+  float* colsum_part = ws + (int64_t)dw_splits(M, K, Nout, use_tc) * Nout * K;
+  float* in_part = colsum_part + ceil_div(M, kColsumRows) * Nout;
+  const int colsum_blocks = (int)ceil_div(M, kColsumRows);
+  ColTask own{nullptr, 0, 0, nullptr}, in{nullptr, 0, 0, nullptr};
+  if (!dz_given) {
+    if (elu) {   // dZ and the bias-gradient partial sums in one pass
+      const bool vec = Nout % 4 == 0 && ((uintptr_t)Y | (uintptr_t)dY | (uintptr_t)dZ) % 16 == 0;
+      if (vec) elu_bwd_colsum_kernel<true><<<colsum_blocks, 256, 0, s>>>(Y, dY, dZ, M, Nout, kColsumRows, colsum_part);
+      else     elu_bwd_colsum_kernel<false><<<colsum_blocks, 256, 0, s>>>(Y, dY, dZ, M, Nout, kColsumRows, colsum_part);
+      count_launch();
+      dz = dZ;
+    } else {
+      colsum_partial_kernel<<<colsum_blocks, 256, 0, s>>>(dz, M, Nout, kColsumRows, colsum_part);
+      count_launch();
+    }
+    own = ColTask{colsum_part, colsum_blocks, Nout, db};
+  }
+  if (dX) {  // dX[M,K] = dZ[M,Nout] . W[Nout,K]
+    if (use_tc) {
+      int rc = gemm_tc(dz, Nout, 1, W, K, 1, dX, K, M, K, Nout, Nout, 1, nullptr, 0, precision, s);
+      if (rc) return rc;
+    } else {
+      dim3 grid((unsigned)ceil_div(M, BM), (unsigned)ceil_div(K, BN), 1);
+      sgemm_kernel<0><<<grid, kGemmThreads, 0, s>>>(dz, Nout, 1, W, K, 1, dX, K, M, K, Nout, Nout, nullptr);
+      count_launch();
+    }
+    if (elu_in) {
+      // X is the ELU output this gradient belongs to: dX becomes the input-side layer's dZ, in place, with the partial sums
+      // of its bias gradient.  (Doing this in the epilogue of the dX product was measured: four epilogue warps per SM cannot
+      // keep enough loads of X in flight, the product ran 3x longer -- profiles/r2_notes.md.)
+      const bool vec = K % 4 == 0 && ((uintptr_t)X | (uintptr_t)dX) % 16 == 0;
+      if (vec) elu_bwd_colsum_kernel<true><<<colsum_blocks, 256, 0, s>>>(X, dX, dX, M, K, kColsumRows, in_part);
+      else     elu_bwd_colsum_kernel<false><<<colsum_blocks, 256, 0, s>>>(X, dX, dX, M, K, kColsumRows, in_part);
+      count_launch();
+      in = ColTask{in_part, colsum_blocks, K, db_in};
+    }
+  }
+  // dW[Nout,K] = sum_m dZ[m,n] X[m,k]: A(i=n,k=m) = dZ[m*Nout + n], B(k=m,j=k) = X[m*K + k]
+  int splits = dw_splits(M, K, Nout, use_tc);
+  int64_t k_per = ceil_div(ceil_div(M, splits), 32) * 32;   // multiple of both paths' K tile
+  splits = (int)ceil_div(M, k_per);
+  float* dst = splits == 1 ? dW : ws;
+  if (use_tc) {
+    int rc = gemm_tc(dz, 1, Nout, X, K, 1, dst, K, Nout, K, M, k_per, splits, nullptr, 0, precision, s);
+    if (rc) return rc;
+  } else {
+    dim3 grid((unsigned)ceil_div(Nout, BM), (unsigned)ceil_div(K, BN), (unsigned)splits);
+    sgemm_kernel<0><<<grid, kGemmThreads, 0, s>>>(dz, 1, Nout, X, K, 1, dst, K, Nout, K, M, k_per, nullptr);
+    count_launch();
+  }
+  {
+    const int64_t n = (int64_t)Nout * K;
+    const int slab_blocks = splits > 1 ? (int)ceil_div(n, 256) : 0;
+    const int col_blocks = (own.n + 7) / 8 + (in.n + 7) / 8;
+    if (slab_blocks + col_blocks > 0) {
+      reduce_tail_kernel<<<(unsigned)(slab_blocks + col_blocks), 256, 0, s>>>(ws, splits, n, dW, slab_blocks, own, in);
+      count_launch();
+    }
+  }
+  return check_launch("linear_bwd");
+}
+
 }  // namespace b200lab
 
 using namespace b200lab;
@@ -226,7 +305,8 @@ int64_t b200lab_linear_bwd_workspace_bytes(int64_t M, int32_t K, int32_t Nout) {
   int s_simt = dw_splits(M, K, Nout, false), s_tc = dw_splits(M, K, Nout, true);
   int splits = s_simt > s_tc ? s_simt : s_tc;   // the caller does not say which path will run
   int64_t colsum_blocks = ceil_div(M, kColsumRows);
-  return ((int64_t)splits * Nout * K + colsum_blocks * Nout) * (int64_t)sizeof(float);
+  // + the partials of the input side's bias gradient (b200lab_linear_bwd_chain)
+  return ((int64_t)splits * Nout * K + colsum_blocks * Nout + colsum_blocks * K) * (int64_t)sizeof(float);
 }
 
 int b200lab_linear_fwd(const float* X, const float* W, const float* b, float* Y, int64_t M, int32_t K, int32_t Nout,
@@ -250,57 +330,17 @@ int b200lab_linear_fwd(const float* X, const float* W, const float* b, float* Y,
 int b200lab_linear_bwd(const float* X, const float* W, const float* Y, const float* dY, float* dZ, float* dX,
                        float* dW, float* db, int64_t M, int32_t K, int32_t Nout, int32_t elu, int32_t precision,
                        void* workspace, void* stream) {
-  B200LAB_CHECK_ARG(X && W && dY && dW && db && workspace && M > 0 && K > 0 && Nout > 0, "bad argument");
-  B200LAB_CHECK_ARG(!elu || (Y && dZ), "ELU backward needs the saved output Y and the dZ scratch");
-  B200LAB_CHECK_ARG(precision >= 0 && precision <= 2, "precision must be 0 (fp32 FFMA), 1 (tf32) or 2 (tf32x3)");
-  const bool use_tc = precision != 0 && (Nout >= kMinTcWidth || K >= kMinTcWidth);
-  cudaStream_t s = (cudaStream_t)stream;
-  const float* dz = dY;
-  float* ws = (float*)workspace;
-  float* colsum_part = ws + (int64_t)dw_splits(M, K, Nout, use_tc) * Nout * K;
-  const int colsum_blocks = (int)ceil_div(M, kColsumRows);
-  if (elu) {   // dZ and the bias-gradient partial sums in one pass
-    const bool vec = Nout % 4 == 0 && ((uintptr_t)Y | (uintptr_t)dY | (uintptr_t)dZ) % 16 == 0;
-    if (vec) elu_bwd_colsum_kernel<true><<<colsum_blocks, 256, 0, s>>>(Y, dY, dZ, M, Nout, kColsumRows, colsum_part);
-    else     elu_bwd_colsum_kernel<false><<<colsum_blocks, 256, 0, s>>>(Y, dY, dZ, M, Nout, kColsumRows, colsum_part);
-    count_launch();
-    dz = dZ;
-  } else {
-    colsum_partial_kernel<<<colsum_blocks, 256, 0, s>>>(dz, M, Nout, kColsumRows, colsum_part);
-    count_launch();
-  }
-  reduce_cols_kernel<<<(unsigned)ceil_div(Nout, 8), 256, 0, s>>>(colsum_part, colsum_blocks, Nout, db);
-  count_launch();
-  if (dX) {  // dX[M,K] = dZ[M,Nout] . W[Nout,K]
-    if (use_tc) {
-      int rc = gemm_tc(dz, Nout, 1, W, K, 1, dX, K, M, K, Nout, Nout, 1, nullptr, 0, precision, s);
-      if (rc) return rc;
-    } else {
-      dim3 grid((unsigned)ceil_div(M, BM), (unsigned)ceil_div(K, BN), 1);
-      sgemm_kernel<0><<<grid, kGemmThreads, 0, s>>>(dz, Nout, 1, W, K, 1, dX, K, M, K, Nout, Nout, nullptr);
-      count_launch();
-    }
-  }
-  // dW[Nout,K] = sum_m dZ[m,n] X[m,k]: A(i=n,k=m) = dZ[m*Nout + n], B(k=m,j=k) = X[m*K + k]
-  int splits = dw_splits(M, K, Nout, use_tc);
-  int64_t k_per = ceil_div(ceil_div(M, splits), 32) * 32;   // multiple of both paths' K tile
-  splits = (int)ceil_div(M, k_per);
-  {
-    float* dst = splits == 1 ? dW : ws;
-    if (use_tc) {
-      int rc = gemm_tc(dz, 1, Nout, X, K, 1, dst, K, Nout, K, M, k_per, splits, nullptr, 0, precision, s);
-      if (rc) return rc;
-    } else {
-      dim3 grid((unsigned)ceil_div(Nout, BM), (unsigned)ceil_div(K, BN), (unsigned)splits);
-      sgemm_kernel<0><<<grid, kGemmThreads, 0, s>>>(dz, 1, Nout, X, K, 1, dst, K, Nout, K, M, k_per, nullptr);
-      count_launch();
-    }
-    if (splits > 1) {
-      int64_t n = (int64_t)Nout * K;
-      reduce_slabs_kernel<<<(unsigned)ceil_div(n, 256), 256, 0, s>>>(ws, splits, n, dW);
-      count_launch();
-    }
-  }
-  return check_launch("linear_bwd");
+  return linear_bwd_impl(X, W, Y, dY, dZ, dX, dW, db, nullptr, M, K, Nout, elu ? B200LAB_BWD_ELU_OUT : 0, precision, workspace,
+                         (cudaStream_t)stream);
 }
+
+int b200lab_linear_bwd_chain(const float* X, const float* W, const float* Y, const float* dY, float* dZ, float* dX,
+                             float* dW, float* db, float* db_in, int64_t M, int32_t K, int32_t Nout, int32_t flags,
+                             int32_t precision, void* workspace, void* stream) {
+  B200LAB_CHECK_ARG((flags & ~(B200LAB_BWD_ELU_OUT | B200LAB_BWD_ELU_IN | B200LAB_BWD_DZ_GIVEN)) == 0, "unknown flag");
+  B200LAB_CHECK_ARG(!(flags & B200LAB_BWD_ELU_IN) || (dX && db_in), "B200LAB_BWD_ELU_IN needs dX and db_in");
+  B200LAB_CHECK_ARG(!((flags & B200LAB_BWD_ELU_OUT) && (flags & B200LAB_BWD_DZ_GIVEN)), "ELU_OUT and DZ_GIVEN exclude each other");
+  return linear_bwd_impl(X, W, Y, dY, dZ, dX, dW, db, db_in, M, K, Nout, flags, precision, workspace, (cudaStream_t)stream);
 }
+
+}  // extern "C"

@@ -34,6 +34,9 @@ def _padded_k(weight):
     return int(weight.stride(0)) if weight.dim() == 2 else int(weight.shape[-1])
 
 
+_BWD_ELU_OUT, _BWD_ELU_IN, _BWD_DZ_GIVEN = 1, 2, 4   # include/b200lab.h: B200LAB_BWD_*
+
+
 class _Net:
     """Per-network forward/backward driver over raw pointers."""
 
@@ -67,11 +70,10 @@ class _Net:
                 self._cache.clear()
             acts = [torch.empty(M, d, device=device) for d in self.dims[1:]]
             grads = [torch.empty(M, d, device=device) for d in self.dims[1:]]
-            dz = torch.empty(M, max(self.dims[1:]), device=device)
             ws = max(_lib.lib().b200lab_linear_bwd_workspace_bytes(M, self.dims[i], self.dims[i + 1])
                      for i in range(len(self.linears)))
             work = torch.empty((ws + 3) // 4, device=device)
-            b = self._cache[key] = dict(acts=acts, grads=grads, dz=dz, work=work)
+            b = self._cache[key] = dict(acts=acts, grads=grads, work=work)
         return b
 
     def forward(self, x, precision):
@@ -100,15 +102,19 @@ class _Net:
         if need_dx and "dx0" not in b:
             b["dx0"] = torch.empty(M, self.dims[0], device=x.device)
         x0 = b["x0"] if self.dims[0] != self.in_features else x   # the padded operand forward(x) used
+        # every layer below the last one receives its dZ (and its bias gradient) from the epilogue of the dX product of
+        # the layer above it (B200LAB_BWD_ELU_IN there, B200LAB_BWD_DZ_GIVEN here): no stand-alone ELU-backward pass
         for i in reversed(range(len(self.linears))):
             lin = self.linears[i]
             last = i == len(self.linears) - 1
             inp = x0 if i == 0 else b["acts"][i - 1]
             dx = (b["dx0"] if need_dx else None) if i == 0 else b["grads"][i - 1]
-            _lib.check(L.b200lab_linear_bwd(inp.data_ptr(), lin.weight.data_ptr(), _lib.ptr(b["acts"][i]), _lib.ptr(dy),
-                                            _lib.ptr(b["dz"]), _lib.ptr(dx), lin.weight.grad.data_ptr(),
-                                            _lib.ptr(lin.bias.grad), M, self.dims[i], self.dims[i + 1],
-                                            0 if last else 1, precision, _lib.ptr(b["work"]), s))
+            flags = (0 if last else _BWD_DZ_GIVEN) | (_BWD_ELU_IN if i > 0 else 0)
+            db_in = self.linears[i - 1].bias.grad if i > 0 else None
+            _lib.check(L.b200lab_linear_bwd_chain(inp.data_ptr(), lin.weight.data_ptr(), None, _lib.ptr(dy), None,
+                                                  _lib.ptr(dx), lin.weight.grad.data_ptr(), _lib.ptr(lin.bias.grad),
+                                                  _lib.ptr(db_in), M, self.dims[i], self.dims[i + 1], flags, precision,
+                                                  _lib.ptr(b["work"]), s))
             dy = dx
         return b["dx0"][:, :self.in_features] if need_dx else None
 
