@@ -514,12 +514,36 @@ def time_ppo_update(dev, c, reps=3, precision=2, multi_gpu_cfg=None):
     return out
 
 
+def tensor_peak():
+    """Dense TF32 tensor peak in TFLOP/s: half of the measured sustained bf16 cuBLAS rate (kind::tf32 issues at half the
+    kind::f16 rate); fallback = the profiling recipe's 1590 / 2."""
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        m = json.load(open(p))
+        v = m.get("bf16_tflops_sustained") or m.get("bf16_tflops")
+        if v:
+            return float(v) / 2.0, "MEASURED_PEAKS.json bf16_tflops_sustained / 2 (tf32 = half the bf16 rate)"
+    return 795.0, "fallback (B200_PROFILING.md 1.59 PFLOP/s bf16 / 2)"
+
+
+def gemm_roofline(rec, issued_per_flop):
+    """Tensor roofline of the update: `achieved` = algorithmic matrix flops of one PPO iteration / event-timed update;
+    `issued` = what the tensor pipe executes (x3 with the 3xTF32 split).  The update also contains ~28 % non-GEMM kernels."""
+    peak, src = tensor_peak()
+    ach = rec["tflops"]
+    return {"bound": "tensor", "achieved": ach, "issued": round(ach * issued_per_flop, 2), "peak": round(peak, 1),
+            "unit": "TFLOP/s", "frac": round(ach / peak, 4), "issued_frac": round(ach * issued_per_flop / peak, 4),
+            "peak_source": src, "traffic": None}
+
+
 def ppo_record(dev, c, mg, reps=3):
     """Both precisions: 3xTF32 is the parity setting (headline s_per_iter), plain TF32 the like-for-like of the reference
     on GPU (scripts/reinforcement_learning/rsl_rl/train.py:97 enables TF32 matmuls)."""
     r = time_ppo_update(dev, c, reps=reps, precision=2, multi_gpu_cfg=mg)
     t = time_ppo_update(dev, c, reps=reps, precision=1, multi_gpu_cfg=mg)
-    r["tf32"] = {"s_per_iter": t["s_per_iter"], "update_ms": t["update_ms"], "tflops": t["tflops"], "precision": t["precision"]}
+    r["roofline"] = gemm_roofline(r, 3)
+    r["tf32"] = {"s_per_iter": t["s_per_iter"], "update_ms": t["update_ms"], "tflops": t["tflops"], "precision": t["precision"],
+                 "roofline": gemm_roofline(t, 1)}
     return r
 
 
