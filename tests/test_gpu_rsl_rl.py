@@ -148,7 +148,8 @@ def test_linear_fwd_bwd_vs_torch_fp32(M, K, N):
 
 @pytest.mark.parametrize("precision,tol", [(2, 3e-5), (1, 3e-3)], ids=["tf32x3", "tf32"])
 @pytest.mark.parametrize("M,K,N", [(24576, 512, 256), (24576, 235, 512), (1000, 128, 256), (384, 96, 128), (333, 77, 40),
-                                   (4096, 256, 128), (24576, 128, 12), (5000, 128, 1), (777, 4, 32), (130, 33, 19)])
+                                   (4096, 256, 128), (24576, 128, 12), (5000, 128, 1), (777, 4, 32), (130, 33, 19),
+                                   (20011, 236, 300), (9999, 512, 303), (40000, 64, 640)])
 def test_linear_tcgen05_vs_fp64(M, K, N, precision, tol):
     """tcgen05 kind::tf32 GEMM paths (csrc/mlp_tc.cu): forward with fused bias+ELU, dX and split-K dW, against torch fp64.
     3xTF32 (precision 2) must stay at fp32-level accuracy; single TF32 (precision 1) at TF32 level.  Errors are measured
@@ -180,6 +181,64 @@ def test_linear_tcgen05_vs_fp64(M, K, N, precision, tol):
     assert rel(dX, Xr.grad) < tol, f"dX {rel(dX, Xr.grad):.2e}"
     assert rel(dW, Wr.grad) < tol, f"dW {rel(dW, Wr.grad):.2e}"
     assert rel(db, br.grad) < tol, f"db {rel(db, br.grad):.2e}"   # through ELU'(Y): inherits the forward error
+
+
+@pytest.mark.parametrize("precision,tol", [(2, 3e-5), (1, 3e-3), (0, 1e-5)], ids=["tf32x3", "tf32", "ffma"])
+@pytest.mark.parametrize("M,dims", [(24576, [236, 512, 256, 128, 12]), (1000, [48, 128, 130, 1]), (333, [77, 64, 32, 5])])
+def test_linear_bwd_chain_vs_fp64(M, dims, precision, tol):
+    """b200lab_linear_bwd_chain over a Linear+ELU ... Linear stack (RSL/networks/mlp.py:60-80): every layer below the last
+    receives its dZ and bias gradient from the call of the layer above (ELU_IN there, DZ_GIVEN here); all weight, bias
+    and input gradients against torch autograd in fp64."""
+    from isaaclab_b200 import _lib
+    L = _lib.lib()
+    g = torch.Generator().manual_seed(M + sum(dims))
+    n = len(dims) - 1
+    X = torch.randn(M, dims[0], generator=g)
+    Ws = [torch.randn(dims[i + 1], dims[i], generator=g) / dims[i] ** 0.5 for i in range(n)]
+    bs = [torch.randn(dims[i + 1], generator=g) * 0.1 for i in range(n)]
+    dOut = torch.randn(M, dims[-1], generator=g) / M
+    Xr = X.double().requires_grad_()
+    Wr = [w.double().requires_grad_() for w in Ws]
+    br = [b.double().requires_grad_() for b in bs]
+    h = Xr
+    for i in range(n):
+        h = torch.nn.functional.linear(h, Wr[i], br[i])
+        if i < n - 1:
+            h = torch.nn.functional.elu(h)
+    h.backward(dOut.double())
+    s = _lib.current_stream()
+    Xc, Wc, bc = X.cuda(), [w.cuda() for w in Ws], [b.cuda() for b in bs]
+    acts, inp = [], Xc
+    for i in range(n):
+        Y = torch.empty(M, dims[i + 1], device="cuda")
+        _lib.check(L.b200lab_linear_fwd(_lib.ptr(inp), _lib.ptr(Wc[i]), _lib.ptr(bc[i]), _lib.ptr(Y), M, dims[i], dims[i + 1],
+                                        0 if i == n - 1 else 1, precision, s))
+        acts.append(Y)
+        inp = Y
+    dW = [torch.empty_like(w) for w in Wc]
+    db = [torch.empty_like(b) for b in bc]
+    grads = [torch.empty(M, dims[i], device="cuda") for i in range(n)]   # grads[i] = gradient w.r.t. the input of layer i
+    ws = torch.empty(max(L.b200lab_linear_bwd_workspace_bytes(M, dims[i], dims[i + 1]) for i in range(n)) // 4 + 1, device="cuda")
+    dy = dOut.cuda()
+    for i in reversed(range(n)):
+        flags = (0 if i == n - 1 else 4) | (2 if i > 0 else 0)
+        x_in = Xc if i == 0 else acts[i - 1]
+        _lib.check(L.b200lab_linear_bwd_chain(_lib.ptr(x_in), _lib.ptr(Wc[i]), None, _lib.ptr(dy), None, _lib.ptr(grads[i]),
+                                              _lib.ptr(dW[i]), _lib.ptr(db[i]), _lib.ptr(db[i - 1]) if i > 0 else None, M,
+                                              dims[i], dims[i + 1], flags, precision, _lib.ptr(ws), s))
+        dy = grads[i]
+    torch.cuda.synchronize()
+
+    def rel(a, r):
+        return ((a.cpu().double() - r).abs().max() / r.abs().max()).item()
+    assert rel(grads[0], Xr.grad) < tol, f"dX {rel(grads[0], Xr.grad):.2e}"
+    for i in range(n):
+        assert rel(dW[i], Wr[i].grad) < tol, f"dW[{i}] {rel(dW[i], Wr[i].grad):.2e}"
+        assert rel(db[i], br[i].grad) < tol, f"db[{i}] {rel(db[i], br[i].grad):.2e}"
+    # flags that contradict each other are refused
+    rc = L.b200lab_linear_bwd_chain(_lib.ptr(Xc), _lib.ptr(Wc[0]), None, _lib.ptr(dy), None, None, _lib.ptr(dW[0]), _lib.ptr(db[0]),
+                                    None, M, dims[0], dims[1], 1 | 4, precision, _lib.ptr(ws), s)
+    assert rc != 0
 
 
 def test_linear_rejects_unknown_precision():
