@@ -319,10 +319,13 @@ struct Smem {
   static constexpr uint32_t kA = Tile<BM>::kBytes, kB = Tile<BN>::kBytes;
   static constexpr uint32_t kStage = kA + kB;                      // one k-tile: A | B (raw, or their lo parts)
   static constexpr int kSlots = BN > 64 ? 6 : 8;                   // k-tile slots of 32 KB / 24 KB
-  // all-TMA pipeline: TF32 -> kSlots raw stages; 3xTF32 -> kNsSplit raw stages + as many lo buffers of the B part only (the
+  // all-TMA pipeline: TF32 -> kSlots raw stages; 3xTF32 -> kNsSplit raw stages + kLoRing lo buffers of the B part only (the
   // A operand of the split goes to the tensor core through tensor memory: 64 columns per stage next to the accumulators)
-  static constexpr int kNsSplit = (kSlots * kStage) / (kStage + kB);
-  static_assert(2 * BN + 64 * kNsSplit <= 512, "accumulators + A stages exceed tensor memory");
+  // kLoRing: lo buffers of B (shared memory) and raw | lo copies of A (tensor memory) live from a k-tile's sweep to the end
+  // of its MMAs only, so a ring of 2 serves any number of raw stages (the sweep of k-tile g waits for the MMAs of g - 2)
+  static constexpr int kLoRing = 2;
+  static constexpr int kNsSplit = (kSlots * kStage - kLoRing * kB) / kStage;
+  static_assert(2 * BN + 64 * kLoRing <= 512, "accumulators + A copies exceed tensor memory");
   // cp.async pipeline: kSlots - 2 raw stages + 2 lo buffers
   static constexpr int kStages = kSlots - 2;
   static constexpr uint32_t kLo = kStages * kStage;
@@ -410,7 +413,7 @@ gemm_tf32_kernel(const float* __restrict__ A, int64_t lda_i, int64_t lda_k, cons
   uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(ctl + 24 * kMaxStages + 32);
   // all-TMA pipeline: ns raw stages (+ ns lo buffers behind them with the 3xTF32 split); cp.async pipeline: kStages + 2 lo
   const int ns = kAllTma ? (split ? S::kNsSplit : S::kSlots) : kStages;
-  constexpr uint32_t kTmemCols = kAllTma ? 512u : 2u * BN;   // two accumulators (+ A raw | A lo, 32 + 32 columns per stage)
+  constexpr uint32_t kTmemCols = kAllTma ? 512u : 2u * BN;   // two accumulators (+ a ring of 2 x (A raw | A lo), 32 + 32 columns each)
 
   if (tid == 0) {
     if (kTmaA) tma_prefetch_desc(&map_a);
@@ -431,15 +434,16 @@ gemm_tf32_kernel(const float* __restrict__ A, int64_t lda_i, int64_t lda_k, cons
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_d = *tmem_ptr_smem;
-  const uint32_t tmem_a = tmem_d + 2u * BN;   // stage s: raw A in columns [64 s, 64 s + 32), its lo part in the next 32
+  const uint32_t tmem_a = tmem_d + 2u * BN;   // k-tile g: raw A in columns [64 (g&1), +32), its lo part in the next 32
 
   if (warp < kMmaWarp) {
     if constexpr (kAllTma) {
       // ---------------- sweepers (3xTF32 only).  Per k-tile the TMA warp brings in:  B -> lo = x - trunc(x) to the stage's
       // lo buffer (linear sweep);  A -> each thread reads 8 k of its row from the raw stage and stores them and their lo
       // parts to tensor memory (lane = row: warp w owns rows 32*(w%4)..+31 and the k octet w/4), from where the MMAs take
-      // the A operand -- no lo copy of A in shared memory and no tensor-core reads of A from it.  Their only dependency is
-      // the stage's TMA barrier: the box is requested after the MMAs of the stage's previous k-tile have completed.
+      // the A operand -- no lo copy of A in shared memory and no tensor-core reads of A from it.  They wait for the stage's
+      // TMA barrier and for the MMAs of k-tile g - 2 (the previous user of lo ring slot g & 1), so they run at most two
+      // k-tiles ahead of the tensor core while the TMA warp keeps all the other raw stages in flight.
       if (split) {
         int total_g = 0;   // k-tiles of all my units
         for (int64_t u = blockIdx.x; u < num_units; u += gridDim.x) total_g += unit_of(u, n_i, n_j, K, k_per_split).num_kt;
@@ -448,13 +452,18 @@ gemm_tf32_kernel(const float* __restrict__ A, int64_t lda_i, int64_t lda_k, cons
         uint32_t a_off[2];   // K-major: the two 16-byte chunks of k = 8 kq .. 8 kq + 7;  MN-major: offset of k = 8 kq (see below)
         if constexpr (AMODE == kKTma) { a_off[0] = k_offset(row, kq * 8); a_off[1] = k_offset(row, kq * 8 + 4); }
         else { a_off[0] = (uint32_t)(row >> 5) * Tile<BM>::kLboMn + (uint32_t)(kq * 2) * Tile<BM>::kSboMn + (uint32_t)(row & 31) * 4; a_off[1] = 0; }
-        int s = 0;
-        uint32_t ph = 0;
+        int s = 0, s2 = 0;   // stage of k-tile g, of k-tile g - 2
+        uint32_t ph = 0, ph2 = 0;
 #pragma unroll 1
         for (int g = 0; g < total_g; ++g) {
 #ifndef B200LAB_GEMM_NOLOAD
           mbar_wait(bar_tma + 8 * s, ph);
 #endif
+          if (g >= 2) {   // lo ring slot g & 1 (B lo in shared memory, A raw | lo in tensor memory): the MMAs of k-tile g - 2 are done
+            mbar_wait(bar_empty + 8 * s2, ph2);
+            if (++s2 == ns) { s2 = 0; ph2 ^= 1u; }
+          }
+          tc_fence_after();
 #ifndef B200LAB_GEMM_NOSWEEP
           const uint8_t* raw = smem + s * S::kStage;
           float v[8], l[8];
@@ -468,9 +477,9 @@ gemm_tf32_kernel(const float* __restrict__ A, int64_t lda_i, int64_t lda_k, cons
           }
 #pragma unroll
           for (int k = 0; k < 8; ++k) l[k] = v[k] - __uint_as_float(__float_as_uint(v[k]) & 0xFFFFE000u);
-          tmem_st8(tmem_a + (uint32_t)(s * 64) + a_lane, v);
-          tmem_st8(tmem_a + (uint32_t)(s * 64 + 32) + a_lane, l);
-          lo_sweep<S::kB>(raw + S::kA, smem + ns * S::kStage + s * S::kB, tid);
+          tmem_st8(tmem_a + (uint32_t)((g & 1) * 64) + a_lane, v);
+          tmem_st8(tmem_a + (uint32_t)((g & 1) * 64 + 32) + a_lane, l);
+          lo_sweep<S::kB>(raw + S::kA, smem + ns * S::kStage + (g & 1) * S::kB, tid);
           asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
 #endif
           tc_fence_before();
@@ -562,8 +571,8 @@ gemm_tf32_kernel(const float* __restrict__ A, int64_t lda_i, int64_t lda_k, cons
           const uint32_t sa = smem_u32(smem + s * S::kStage), sb = sa + S::kA;
           // lo part: behind the raw ring, one buffer per stage (all-TMA) or two alternating ones (cp.async pipeline)
           const uint32_t sa_lo = smem_u32(smem + (kStages + (g & 1)) * S::kStage);            // cp.async pipeline only
-          const uint32_t sb_lo = kAllTma ? smem_u32(smem + ns * S::kStage + s * S::kB) : sa_lo + S::kA;
-          const uint32_t ta = tmem_a + (uint32_t)(s * 64);                                      // all-TMA split only
+          const uint32_t sb_lo = kAllTma ? smem_u32(smem + ns * S::kStage + (g & 1) * S::kB) : sa_lo + S::kA;
+          const uint32_t ta = tmem_a + (uint32_t)((g & 1) * 64);                                // all-TMA split only
 #ifndef B200LAB_GEMM_NOLOAD
           if constexpr (kAllTma) mbar_wait(bar_tma + 8 * s, ph);     // raw operands: straight from the TMA's barrier
 #endif
