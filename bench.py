@@ -547,6 +547,49 @@ def ppo_record(dev, c, mg, reps=3):
     return r
 
 
+def train_iteration_record(cfg_id, cfg, spec, slabs, init, dev, iters=5):
+    """One full OnPolicyRunner iteration (RSL/runners/on_policy_runner.py:70-140) on the config's workload with the state
+    replayed from device slabs: collection = T x {PPO.act, env.step, process_env_step}, learning = GAE + update, timed by
+    the runner itself with CUDA events (`Perf/collection time`, `Perf/learning_time`); default policy precision (3xTF32)."""
+    import tempfile
+    from isaaclab_b200.envs.manager_based_rl_env import DeviceReplaySim, ManagerBasedRLEnv
+    from isaaclab_b200.rsl_rl import OnPolicyRunner, RslRlVecEnvWrapper
+    from isaaclab_b200.sim.synthetic import SyntheticSim
+    from tests.mdp_common import init_fused_state
+    c = ppo_cfg(cfg_id, spec)
+    train_cfg = {
+        "num_steps_per_env": c["T"], "save_interval": 10 ** 9, "obs_groups": {"policy": ["policy"]},
+        "policy": {"class_name": "ActorCritic", "init_noise_std": 1.0, "actor_hidden_dims": list(c["hidden"]),
+                   "critic_hidden_dims": list(c["hidden"]), "activation": "elu"},
+        "algorithm": {"class_name": "PPO", "value_loss_coef": 1.0, "use_clipped_value_loss": True, "clip_param": 0.2,
+                      "entropy_coef": 0.005, "num_learning_epochs": c["epochs"], "num_mini_batches": c["mini_batches"],
+                      "learning_rate": 1e-3, "schedule": "adaptive", "gamma": c["gamma"], "lam": c["lam"],
+                      "desired_kl": 0.01, "max_grad_norm": 1.0}}
+    out = {}
+    for mode, graph in (("eager_step", False), ("graph_step", True)):
+        sim = DeviceReplaySim(SyntheticSim(spec, K=slabs["root_state_w"].shape[0], device=dev, slabs=slabs))
+        env = ManagerBasedRLEnv(cfg, sim=sim, device=dev, spec=spec, seed=0, use_cuda_graph=graph)
+        init_fused_state(env.fused, init)
+        runner = OnPolicyRunner(RslRlVecEnvWrapper(env), train_cfg, log_dir=tempfile.mkdtemp(prefix="b200lab_bench_"),
+                                device=str(dev))
+        rows = []
+        for _ in range(iters + 1):
+            runner.learn(1)
+            torch.cuda.synchronize()
+            rows.append((runner.last_log["Perf/collection time"], runner.last_log["Perf/learning_time"]))
+        rows = rows[1:]   # first iteration: buffer allocation, graph capture
+        coll = sorted(r[0] for r in rows)[len(rows) // 2]
+        learn = sorted(r[1] for r in rows)[len(rows) // 2]
+        out[mode] = {"collection_ms": round(coll * 1e3, 2), "collection_us_per_step": round(coll / c["T"] * 1e6, 1),
+                     "learning_ms": round(learn * 1e3, 2), "total_fps": round(spec["N"] * c["T"] / (coll + learn))}
+        env.close()
+        del runner, env, sim
+        torch.cuda.empty_cache()
+    out["what"] = (f"OnPolicyRunner.learn: {c['T']} steps x {spec['N']} envs per iteration, simulator state replayed from "
+                   "device slabs (no physics), policy and rollout on the GPU")
+    return out
+
+
 def cpu_ppo_baseline_port(c, budget_updates=2, threads=None):
     """Oracle port of PPO.update on the host cores: `budget_updates` of the 20 minibatch updates of one iteration at
     config-3 shapes (+ GAE), scaled to s/iter."""
@@ -705,6 +748,11 @@ def run_ours(args):
                 clocks = ck
         if cfg_id != "cfg2" or not args.quick:
             rec["ppo_update"] = ppo_record(dev, ppo_cfg(cfg_id, spec, envs), mg, reps=3 if is_head else 2)
+        if is_head and world == 1 and c["env_arms"]:
+            try:
+                rec["train_iteration"] = train_iteration_record(cfg_id, cfg, spec, slabs, init, dev)
+            except Exception as e:   # a probe, never the reason a bench line is missing
+                rec["train_iteration"] = {"error": f"{type(e).__name__}: {e}"}
         records[cfg_id] = rec
         if is_head:
             head, head_data = rec, (spec, slabs, init)

@@ -199,7 +199,7 @@ class ActorCritic(nn.Module):
 
     def __init__(self, obs, obs_groups, num_actions, actor_obs_normalization=False, critic_obs_normalization=False,
                  actor_hidden_dims=[256, 256, 256], critic_hidden_dims=[256, 256, 256], activation="elu",
-                 init_noise_std=1.0, noise_std_type: str = "scalar", device=None, precision: int = 0, **kwargs):
+                 init_noise_std=1.0, noise_std_type: str = "scalar", device=None, precision: int = 2, **kwargs):
         if kwargs:
             print("ActorCritic.__init__ got unexpected arguments, which will be ignored: " + str(list(kwargs.keys())))
         super().__init__()
@@ -398,7 +398,7 @@ class Memory(nn.Module):
     back-propagation through time needs; `backward` walks the steps in reverse with the cell-derivative kernels and leaves
     dW_ih / dW_hh / db in the parameters' `.grad` views (two GEMMs per layer over all steps at once)."""
 
-    def __init__(self, input_size, type="lstm", num_layers=1, hidden_size=256, device="cuda", precision=0):
+    def __init__(self, input_size, type="lstm", num_layers=1, hidden_size=256, device="cuda", precision=2):
         super().__init__()
         self.is_lstm = type.lower() != "gru"
         rnn_cls = nn.LSTM if self.is_lstm else nn.GRU
@@ -546,7 +546,7 @@ class ActorCriticRecurrent(ActorCritic):
     def __init__(self, obs, obs_groups, num_actions, actor_obs_normalization=False, critic_obs_normalization=False,
                  actor_hidden_dims=[256, 256, 256], critic_hidden_dims=[256, 256, 256], activation="elu",
                  init_noise_std=1.0, noise_std_type: str = "scalar", rnn_type="lstm", rnn_hidden_dim=256, rnn_num_layers=1,
-                 device=None, precision: int = 0, **kwargs):
+                 device=None, precision: int = 2, **kwargs):
         if "rnn_hidden_size" in kwargs:   # deprecated spelling (actor_critic_recurrent.py:36-43)
             import warnings
             warnings.warn("The argument `rnn_hidden_size` is deprecated and will be removed in a future version. "
