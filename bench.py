@@ -747,7 +747,7 @@ def run_ours(args):
             if is_head:
                 clocks = ck
         if cfg_id != "cfg2" or not args.quick:
-            rec["ppo_update"] = ppo_record(dev, ppo_cfg(cfg_id, spec, envs), mg, reps=3 if is_head else 2)
+            rec["ppo_update"] = ppo_record(dev, ppo_cfg(cfg_id, spec, envs), mg, reps=5 if is_head else 3)   # median of the repetitions
         if is_head and world == 1 and c["env_arms"]:
             try:
                 rec["train_iteration"] = train_iteration_record(cfg_id, cfg, spec, slabs, init, dev)
