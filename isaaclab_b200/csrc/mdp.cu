@@ -1014,6 +1014,18 @@ __device__ __forceinline__ float u_step_at(const Env* e, int n, int slot, int64_
   return e->u_step ? e->u_step[(int64_t)n * e->n_u_step + slot] : philox_uniform(e->seed, step, 2u, (uint32_t)n, (uint32_t)slot);
 }
 
+// The uniforms one env consumes from a stream in this step, drawn ONCE, lane-parallel (slot = lane, lane + 32, ...), into a
+// per-warp shared-memory table.  post_step used to inline philox_uniform at every use (~30 copies of the 10-round generator,
+// 2850 instructions = 45 KB that only the resetting warps -- the kernel's critical path -- ever fetched).  Same counters,
+// same values.
+constexpr int kDrawCapReset = 384, kDrawCapStep = 64;
+__device__ __noinline__ void fill_draws(float* dst, const float* __restrict__ recorded, int width, uint64_t seed, int64_t step,
+                                        uint32_t stream_id, int n, int lane) {
+  for (int s = lane; s < width; s += 32)
+    dst[s] = recorded ? recorded[(int64_t)n * width + s] : philox_uniform(seed, step, stream_id, (uint32_t)n, (uint32_t)s);
+  __syncwarp();
+}
+
 __device__ __forceinline__ void derive_state(EnvCtx& c, const float* rs) {
   c.pos = {rs[0], rs[1], rs[2]};
   c.q = {rs[3], rs[4], rs[5], rs[6]};
@@ -1305,6 +1317,7 @@ __global__ void __launch_bounds__(kStepWarps * 32, B200LAB_POST_BLOCKS * 4 / kSt
 post_step_kernel(const __grid_constant__ Env env_param, Sim sim, int64_t step, const Env* __restrict__ env_dev,
                  float* __restrict__ derived) {
   const Env* __restrict__ e = &env_param;   // descriptor in the constant bank: warp-uniform reads, no global round trips
+  __shared__ float s_draw_reset[kStepWarps][kDrawCapReset], s_draw_step[kStepWarps][kDrawCapStep];
   // The termination / reward term tables are staged from the device copy of the descriptor into shared memory: read
   // through the constant bank they push the kernel's constant footprint past ~4 KB, where every launch pays several
   // microseconds of serialised constant-cache misses (tools/imc_probe.cu).
@@ -1322,6 +1335,8 @@ post_step_kernel(const __grid_constant__ Env env_param, Sim sim, int64_t step, c
   pdl_launch_dependents();   // compute_obs may be placed under this kernel's tail
   const int lane = threadIdx.x & 31;
   const int n = blockIdx.x * kStepWarps + (threadIdx.x >> 5);
+  float* const ur = s_draw_reset[threadIdx.x >> 5];   // this env's reset-stream / step-stream uniforms (fill_draws)
+  float* const us = s_draw_step[threadIdx.x >> 5];
   const int N = e->N, J = e->J, B = e->B, A = e->A;
   if (n >= N) { pdl_wait(); return; }
   if constexpr (kMode == 2) {
@@ -1413,6 +1428,7 @@ post_step_kernel(const __grid_constant__ Env env_param, Sim sim, int64_t step, c
   if constexpr (kMode != 1)
   if (reset) {
     if (lane == 0 && e->any_reset_dev) *e->any_reset_dev = 1;
+    fill_draws(ur, e->u_reset, e->n_u_reset, e->seed, step, 1u, n, lane);   // every reset-stream uniform of this env
     // curriculum: terrain_levels_vel (curriculums.py:26-55) + update_env_origins (terrain_importer.py:307-322)
     if (e->has_terrain_curriculum) {
       float ox = e->env_origins[n * 3], oy = e->env_origins[n * 3 + 1];
@@ -1423,7 +1439,7 @@ post_step_kernel(const __grid_constant__ Env env_param, Sim sim, int64_t step, c
       down = down && !up;
       int64_t lvl = e->terrain_levels[n] + (up ? 1 : 0) - (down ? 1 : 0);
       if (lvl >= e->terrain_rows) {
-        float u = u_reset_at(e, n, B200LAB_U_RESET_CURRICULUM, step);
+        float u = ur[B200LAB_U_RESET_CURRICULUM];
         lvl = min((int64_t)(u * (float)e->terrain_rows), (int64_t)e->terrain_rows - 1);
       } else if (lvl < 0) lvl = 0;
       const float* to = e->terrain_origins + ((int64_t)lvl * e->terrain_cols + e->terrain_types[n]) * 3;
@@ -1455,7 +1471,7 @@ post_step_kernel(const __grid_constant__ Env env_param, Sim sim, int64_t step, c
         for (int k = lane; k < ag.group_joints; k += 32) ag.delay_count[(int64_t)n * ag.group_joints + k] = 0;
         if (lane == 0) {
           const int span = ag.max_delay - ag.min_delay + 1;
-          ag.delay_lag[n] = ag.min_delay + min((int)(u_reset_at(e, n, ag.delay_u_slot, step) * (float)span), span - 1);
+          ag.delay_lag[n] = ag.min_delay + min((int)(ur[ag.delay_u_slot] * (float)span), span - 1);
         }
       }
     }
@@ -1477,7 +1493,7 @@ post_step_kernel(const __grid_constant__ Env env_param, Sim sim, int64_t step, c
       e->rc_timestamp[n] = 0.f; e->rc_timestamp_last_update[n] = 0.f; e->rc_is_outdated[n] = 1;
       pre_rc_ts = 0.f; pre_rc_flag = true;
       for (int k = 0; k < 3; ++k) {
-        pre_drift[k] = u_reset_at(e, n, B200LAB_U_RESET_DRIFT + k, step) * e->rc_drift_span + e->rc_drift_lo;
+        pre_drift[k] = ur[B200LAB_U_RESET_DRIFT + k] * e->rc_drift_span + e->rc_drift_lo;
         e->rc_drift[n * 3 + k] = pre_drift[k];
       }
     }
@@ -1497,7 +1513,7 @@ post_step_kernel(const __grid_constant__ Env env_param, Sim sim, int64_t step, c
       float up[6], uv[6];
 #pragma unroll
       for (int k = 0; k < 6; ++k) {
-        float a = u_reset_at(e, n, B200LAB_U_RESET_POSE + k, step), b = u_reset_at(e, n, B200LAB_U_RESET_VEL + k, step);
+        float a = ur[B200LAB_U_RESET_POSE + k], b = ur[B200LAB_U_RESET_VEL + k];
         up[k] = a * e->ev_pose_range[2 * k + 1] + e->ev_pose_range[2 * k];
         uv[k] = b * e->ev_vel_range[2 * k + 1] + e->ev_vel_range[2 * k];
       }
@@ -1519,7 +1535,7 @@ post_step_kernel(const __grid_constant__ Env env_param, Sim sim, int64_t step, c
       if (!gate(e->ev_reset_joints_min_steps[k], e->ev_reset_joints_last_step[k], e->ev_reset_joints_once[k])) continue;
       const int base = B200LAB_U_RESET_JOINT + 2 * J * k;
       for (int j = lane; j < J; j += 32) {
-        float u0 = u_reset_at(e, n, base + j, step), u1 = u_reset_at(e, n, base + J + j, step);
+        float u0 = ur[base + j], u1 = ur[base + J + j];
         float sp = u0 * e->ev_joint_pos_range[k][1] + e->ev_joint_pos_range[k][0];
         float sv = u1 * e->ev_joint_vel_range[k][1] + e->ev_joint_vel_range[k][0];
         float qp = e->default_joint_pos[j], qv = e->default_joint_vel[j];
@@ -1564,7 +1580,7 @@ post_step_kernel(const __grid_constant__ Env env_param, Sim sim, int64_t step, c
       }
       float u[7];
 #pragma unroll
-      for (int k = 0; k < 7; ++k) u[k] = u_reset_at(e, n, B200LAB_U_RESET_CMD + k, step);
+      for (int k = 0; k < 7; ++k) u[k] = ur[B200LAB_U_RESET_CMD + k];
       __syncwarp();
       if (lane == 0) resample_command(e, n, u, c.cmd);
       c.cmd.x = __shfl_sync(0xffffffffu, c.cmd.x, 0);
@@ -1580,6 +1596,19 @@ post_step_kernel(const __grid_constant__ Env env_param, Sim sim, int64_t step, c
   }
   if (lane == 0) e->episode_length_buf[n] = ep_len;
   __syncwarp();
+  // step-stream uniforms (command resampling, interval pushes): drawn only by the envs that consume some this step; the
+  // predicates repeat, warp-uniformly, the tests lane 0 makes below
+  {
+    bool need_us = e->has_command && (__shfl_sync(0xffffffffu, pre_tl, 0) - e->step_dt) <= 0.0f;
+#pragma unroll
+    for (int k = 0; k < B200LAB_MAX_INTERVAL_EVENTS; ++k) {
+      if (k >= e->num_interval) break;
+      const bool global_time = e->ev_interval_global[k] != 0 && e->ev_interval_global_time[k] != nullptr;
+      const float tl = (global_time ? e->ev_interval_global_time[k][step & 1] : pre_itl[k]) - e->step_dt;
+      need_us = need_us || tl < 1e-6f;
+    }
+    if (need_us) fill_draws(us, e->u_step, e->n_u_step, e->seed, step, 2u, n, lane);
+  }
   // -- command_manager.compute (command_manager.py:151-166)
   if (e->has_command) {
     if (lane == 0) {
@@ -1592,7 +1621,7 @@ post_step_kernel(const __grid_constant__ Env env_param, Sim sim, int64_t step, c
       if (tl <= 0.0f) {
         float u[7];
 #pragma unroll
-        for (int k = 0; k < 7; ++k) u[k] = u_step_at(e, n, B200LAB_U_STEP_CMD + k, step);
+        for (int k = 0; k < 7; ++k) u[k] = us[B200LAB_U_STEP_CMD + k];
         resample_command(e, n, u, c.cmd);
         pre_is = e->cmd_is_standing[n] != 0;
         if (e->cmd_heading_command) { pre_ih = e->cmd_is_heading[n] != 0; pre_ht = e->cmd_heading_target[n]; }
@@ -1622,10 +1651,10 @@ post_step_kernel(const __grid_constant__ Env env_param, Sim sim, int64_t step, c
       if (tl < 1e-6f) {
         int base = B200LAB_U_STEP_INTERVAL + 7 * k;
         // is_global_time: one draw for the new interval (env 0's slot), every env is pushed (event_manager.py:213-220)
-        tl = u_step_at(e, global_time ? 0 : n, base, step) * e->ev_interval_range[k][1] + e->ev_interval_range[k][0];
+        tl = (global_time ? u_step_at(e, 0, base, step) : us[base]) * e->ev_interval_range[k][1] + e->ev_interval_range[k][0];
         for (int a = 0; a < 6; ++a) {
           float lo = e->ev_push_range[k][2 * a], span = e->ev_push_range[k][2 * a + 1];
-          rs[7 + a] = rs[7 + a] + (u_step_at(e, n, base + 1 + a, step) * span + lo);
+          rs[7 + a] = rs[7 + a] + (us[base + 1 + a] * span + lo);
           sim.root_state_w[(int64_t)n * 13 + 7 + a] = rs[7 + a];
         }
       }
@@ -2768,6 +2797,7 @@ int b200lab_post_step(void* env, const B200LabSimView* sim, int64_t step_counter
   EnvHandle* h = (EnvHandle*)env;
   const B200LabEnvState& s = h->host;
   B200LAB_CHECK_ARG(s.J <= 64 && s.B <= 64, "joint/body masks support up to 64 joints/bodies");
+  B200LAB_CHECK_ARG(s.n_u_reset <= kDrawCapReset && s.n_u_step <= kDrawCapStep, "more random draws per env than the draw tables hold");
   const size_t tab_bytes = (size_t)(s.num_term + s.num_rew) * sizeof(B200LabTerm);
   // a pending speculative scan is validated by the stand-alone derive kernel (it must be joined first)
   const bool fuse_derive = !h->spec_pending && s.obs_dim > 0;
